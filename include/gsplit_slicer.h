@@ -1,0 +1,174 @@
+/*
+ * gsplit_slicer.h -- C ABI of the B200-native minibatch slicer.
+ *
+ * This is the drop-in boundary for ONE path of sandeep06011991/OCC-GNN: the
+ * `cslicer` module (per-minibatch neighbour sampling over CSR, frontier dedup +
+ * relabel, split of every layer into per-GPU bipartites).  Each entry point
+ * names the reference interface it replaces; citations are relative to
+ * /root/reference/cslicer/.  Plain pointers and sizes only: no C++ or torch
+ * types cross this boundary, no exceptions; every call returns a gs_status and
+ * gs_last_error() describes the last failure on the calling thread.
+ *
+ * Execution model: a slicer owns `num_slots` sample slots (the reference's
+ * bounded queue, WorkerPool.cpp:23-24).  gs_slicer_submit() enqueues one
+ * minibatch on a slot's CUDA stream as a single pre-captured CUDA graph
+ * (seed upload, every kernel, result download) and returns at once;
+ * gs_slicer_wait() blocks until that slot's sample is complete;
+ * gs_slicer_release() hands the slot back.  There is no CPU fallback: without a
+ * CUDA device gs_graph_create() fails with GS_ERR_CUDA.
+ */
+#ifndef GSPLIT_SLICER_H
+#define GSPLIT_SLICER_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_MAX_LAYERS 8
+#define GS_MAX_PARTS 8
+#define GS_ABI_VERSION 1
+
+typedef enum {
+  GS_OK = 0,
+  GS_ERR_INVALID = 1,  /* bad argument / configuration */
+  GS_ERR_CUDA = 2,     /* CUDA runtime failure (incl. no device) */
+  GS_ERR_BUSY = 3,     /* no free sample slot: release one first */
+  GS_ERR_OVERFLOW = 4, /* a sample outgrew its workspace: raise the capacities */
+  GS_ERR_SEED = 5,     /* seed id out of range */
+  GS_ERR_STATE = 6     /* slot not in the state the call needs */
+} gs_status;
+
+typedef enum { GS_RNG_PHILOX = 0, GS_RNG_DRAWS = 1 } gs_rng_mode;
+
+/* Per-bipartite lists.  The first seven are the reference's fields
+ * (bipartite.h:9-24, exposed at pyfrontend.cpp:128-138); for from_ids/to_ids the
+ * list is slot [own part], the only slot the reference ever fills
+ * (slicer.cpp:41-42).  The reference's `indptr` (all ones, one per out node) and
+ * `indices` (always empty) carry no information and are synthesised by the
+ * host-side mirror; CSR_INDPTR / CSR_INDICES are the repaired block structure:
+ * rows = out_nodes, indices = positions in in_nodes, edge multiplicity kept. */
+typedef enum {
+  GS_F_IN_NODES = 0,
+  GS_F_OUT_NODES = 1,
+  GS_F_OWNED_OUT = 2,
+  GS_F_FROM_IDS = 3,
+  GS_F_TO_IDS = 4,
+  GS_F_SELF_IN = 5,
+  GS_F_SELF_OUT = 6,
+  GS_F_CSR_INDPTR = 7,
+  GS_F_CSR_INDICES = 8,
+  GS_NUM_FIELDS = 9
+} gs_field_id;
+
+typedef struct {
+  int32_t off; /* element offset into the sample slab (int32 units) */
+  int32_t len;
+} gs_span;
+
+/* One sample's table of contents.  Written by the device, mirrored to pinned
+ * host memory at the end of every sample. */
+typedef struct {
+  int32_t status;      /* 0 or a gs_status raised on the device */
+  int32_t num_layers;
+  int32_t num_parts;
+  int32_t n_seeds;
+  uint64_t batch_index;
+  uint64_t draw_cursor; /* GS_RNG_DRAWS: draws consumed so far (carried) */
+  int64_t edges;        /* real (non-self) edges in this sample */
+  int64_t slab_used;    /* int32 elements of the slab in use */
+  int32_t frontier_len[GS_MAX_LAYERS + 1]; /* F_l: nodes entering layer l; [L] = input nodes */
+  int32_t cand_len[GS_MAX_LAYERS];         /* C_l = F_l self entries + sampled entries */
+  gs_span frontier[GS_MAX_LAYERS + 1];
+  gs_span field[GS_MAX_LAYERS][GS_MAX_PARTS][GS_NUM_FIELDS];
+  uint64_t draw_base[GS_MAX_LAYERS];
+  int32_t reserved[6];
+} gs_sample_header;
+
+typedef struct {
+  int32_t abi_version;             /* GS_ABI_VERSION */
+  int32_t num_layers;              /* reference: 3 (slicer.cpp:75) */
+  int32_t fanouts[GS_MAX_LAYERS];  /* reference: 10 (slicer.cpp:10,15); -1 = all neighbours */
+  int32_t num_parts;               /* reference: 4 (bipartite.h:19) */
+  int32_t rng_mode;                /* gs_rng_mode */
+  uint64_t seed;                   /* philox key */
+  const int32_t *owner_host;       /* [num_nodes] or NULL = id % num_parts (pyfrontend.cpp:57) */
+  const uint32_t *draws_host;      /* GS_RNG_DRAWS: 32-bit draw stream (e.g. mt19937 replay) */
+  uint64_t n_draws;
+  int32_t max_batch;               /* minibatch_size (pyfrontend.cpp:42) */
+  int32_t num_slots;               /* queue_size; samples in flight / unreleased */
+  int32_t num_streams;             /* no_worker_threads; concurrent CUDA streams */
+  int32_t host_output;             /* 1: mirror every sample's slab to pinned host memory */
+  int64_t frontier_capacity;       /* 0 = derive from fanouts */
+  int64_t cand_capacity;           /* 0 = derive */
+  int64_t slab_capacity;           /* 0 = derive (int32 elements) */
+  int32_t grid_ctas;               /* 0 = 2 x SM count */
+  int32_t use_graph;               /* 1 (default via gs_config_default): CUDA-graph replay */
+} gs_config;
+
+typedef struct gs_graph gs_graph;
+typedef struct gs_slicer gs_slicer;
+
+const char *gs_last_error(void);
+int gs_abi_version(void);
+void gs_config_default(gs_config *cfg);
+
+/* Replaces Dataset::read_graph's in-memory product (dataset.cpp:18-36,
+ * dataset.h:39-41): CSR in host memory -> device-resident graph (int64 row
+ * offsets, int32 neighbour ids; num_nodes must be < 2^31). */
+int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
+                    const int64_t *indptr_host, const int64_t *indices_host,
+                    gs_graph **out);
+int gs_graph_destroy(gs_graph *g);
+int64_t gs_graph_num_nodes(const gs_graph *g);
+int64_t gs_graph_num_edges(const gs_graph *g);
+
+/* Replaces CSlicer::CSlicer + WorkerPool::WorkerPool + Slicer::Slicer
+ * (pyfrontend.cpp:41-70, WorkerPool.cpp:4-35, slicer.h:41-72): allocates the
+ * per-slot dedup tables, workspaces and sample slabs and captures one CUDA graph
+ * per slot. */
+int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out);
+int gs_slicer_destroy(gs_slicer *s);
+
+/* Replaces WorkerPool::run's push of one batch (WorkerPool.cpp:41-49) and the
+ * Slicer::run iteration that consumes it (slicer.cpp:120-139).  seeds_host:
+ * n int64 node ids, distinct.  Returns GS_ERR_BUSY when every slot is in use. */
+int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n,
+                     uint64_t batch_index, int32_t *slot_out);
+
+/* Replaces CSlicer::getSample / ConQueue::pop_object (pyfrontend.cpp:73-78,
+ * conqueue.h:42-60) for one slot: blocks until the sample is complete, then
+ * returns its header (host memory, valid until release). */
+int gs_slicer_wait(gs_slicer *s, int32_t slot, const gs_sample_header **hdr_out);
+
+/* Base pointers of a completed slot's slab: every gs_span indexes into these.
+ * host_slab is NULL unless host_output was set. */
+int gs_slicer_slab(gs_slicer *s, int32_t slot, const int32_t **device_slab,
+                   const int32_t **host_slab);
+
+/* Replaces PySample's destructor (pybipartite.cpp:68-76). */
+int gs_slicer_release(gs_slicer *s, int32_t slot);
+
+/* Diagnostics: run one minibatch eagerly (no graph) on slot 0 with a CUDA event
+ * between kernels; ms[i] receives the duration of launch i, names[i] a static
+ * string.  Returns the number of launches through *n_out (<= cap). */
+int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n,
+                      uint64_t batch_index, float *ms, const char **names,
+                      int32_t cap, int32_t *n_out);
+
+/* Replaces the epoch shuffle of WorkerPool::run (WorkerPool.cpp:40):
+ * std::random_shuffle over nodes[0..n) driven by the C library's rand(), i.e.
+ * swap(nodes[i], nodes[rand() % (i+1)]) for i = 1..n-1.  reset != 0 first puts
+ * rand() in the state of a process that never called srand() (the reference
+ * never seeds it), so epoch e of a fresh run is reproduced by calling this e+1
+ * times with reset only on the first call.  Host-only; no device work. */
+int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
+
+/* Number of kernel launches one submitted minibatch performs. */
+int gs_slicer_launches_per_sample(const gs_slicer *s);
+/* Device bytes held by one slot / by the slicer. */
+int64_t gs_slicer_slot_bytes(const gs_slicer *s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,107 @@
+"""ctypes binding of the C ABI in include/gsplit_slicer.h (libgsplit_slicer.so).
+
+The library is the product: it is built in-tree by `__graft_entry__.build()`
+(nvcc, sm_100a) and there is NO fallback -- a missing library raises
+ImportError, a missing GPU raises RuntimeError from the first call that needs it.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgsplit_slicer.so")
+
+MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 1
+RNG_PHILOX, RNG_DRAWS = 0, 1
+OK, ERR_INVALID, ERR_CUDA, ERR_BUSY, ERR_OVERFLOW, ERR_SEED, ERR_STATE = range(7)
+FIELDS = ["in_nodes", "out_nodes", "owned_out_nodes", "from_ids", "to_ids", "self_ids_in",
+          "self_ids_out", "csr_indptr", "csr_indices"]
+NUM_FIELDS = len(FIELDS)
+
+# every symbol include/gsplit_slicer.h declares (tests check the export table)
+SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_create",
+           "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
+           "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
+           "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
+           "gs_slicer_slot_bytes", "gs_reference_shuffle"]
+
+
+class Span(C.Structure):
+    _fields_ = [("off", C.c_int32), ("len", C.c_int32)]
+
+
+class SampleHeader(C.Structure):
+    _fields_ = [("status", C.c_int32), ("num_layers", C.c_int32), ("num_parts", C.c_int32),
+                ("n_seeds", C.c_int32), ("batch_index", C.c_uint64), ("draw_cursor", C.c_uint64),
+                ("edges", C.c_int64), ("slab_used", C.c_int64),
+                ("frontier_len", C.c_int32 * (MAX_LAYERS + 1)),
+                ("cand_len", C.c_int32 * MAX_LAYERS),
+                ("frontier", Span * (MAX_LAYERS + 1)),
+                ("field", ((Span * NUM_FIELDS) * MAX_PARTS) * MAX_LAYERS),
+                ("draw_base", C.c_uint64 * MAX_LAYERS),
+                ("reserved", C.c_int32 * 6)]
+
+
+class Config(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("num_layers", C.c_int32),
+                ("fanouts", C.c_int32 * MAX_LAYERS), ("num_parts", C.c_int32),
+                ("rng_mode", C.c_int32), ("seed", C.c_uint64), ("owner_host", C.c_void_p),
+                ("draws_host", C.c_void_p), ("n_draws", C.c_uint64), ("max_batch", C.c_int32),
+                ("num_slots", C.c_int32), ("num_streams", C.c_int32), ("host_output", C.c_int32),
+                ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
+                ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (nvcc, sm_100a). There is no CPU or PyTorch fallback for the slicer.")
+    L = C.CDLL(LIB_PATH)
+    L.gs_last_error.restype = C.c_char_p
+    L.gs_abi_version.restype = C.c_int
+    L.gs_config_default.argtypes = [C.POINTER(Config)]
+    L.gs_graph_create.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                  C.POINTER(C.c_void_p)]
+    L.gs_graph_destroy.argtypes = [C.c_void_p]
+    L.gs_graph_num_nodes.restype = C.c_int64
+    L.gs_graph_num_nodes.argtypes = [C.c_void_p]
+    L.gs_graph_num_edges.restype = C.c_int64
+    L.gs_graph_num_edges.argtypes = [C.c_void_p]
+    L.gs_slicer_create.argtypes = [C.c_void_p, C.POINTER(Config), C.POINTER(C.c_void_p)]
+    L.gs_slicer_destroy.argtypes = [C.c_void_p]
+    L.gs_slicer_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64,
+                                   C.POINTER(C.c_int32)]
+    L.gs_slicer_wait.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.POINTER(SampleHeader))]
+    L.gs_slicer_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                 C.POINTER(C.c_void_p)]
+    L.gs_slicer_release.argtypes = [C.c_void_p, C.c_int32]
+    L.gs_slicer_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64,
+                                    C.POINTER(C.c_float), C.POINTER(C.c_char_p), C.c_int32,
+                                    C.POINTER(C.c_int32)]
+    L.gs_slicer_launches_per_sample.argtypes = [C.c_void_p]
+    L.gs_slicer_slot_bytes.restype = C.c_int64
+    L.gs_slicer_slot_bytes.argtypes = [C.c_void_p]
+    L.gs_reference_shuffle.argtypes = [C.c_void_p, C.c_int64, C.c_int]
+    if L.gs_abi_version() != ABI_VERSION:
+        raise ImportError("libgsplit_slicer.so ABI version mismatch; rebuild")
+    _lib = L
+    return L
+
+
+class SlicerError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+def check(rc):
+    if rc != OK:
+        raise SlicerError(rc, lib().gs_last_error().decode() or f"gs error {rc}")

@@ -1,0 +1,233 @@
+"""Array-level host API over the C ABI: Graph, Slicer, SampleView.
+
+This is the layer the reference-facing classes in `cslicer/__init__.py` sit on
+(and what bench.py times).  It adds nothing to the computation: it stages
+seeds, submits, waits and wraps the slab spans as numpy (pinned host mirror) or
+torch (device) views.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+
+class _DevSpan:
+    """Minimal __cuda_array_interface__ carrier so torch can wrap a slab span."""
+
+    def __init__(self, ptr, n, owner):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i4",
+                                         "data": (int(ptr), False), "version": 2,
+                                         "strides": None}
+        self._owner = owner
+
+
+class Graph:
+    """Device-resident CSR (replaces the in-memory product of Dataset::read_graph,
+    /root/reference/cslicer/dataset.cpp:18-36)."""
+
+    def __init__(self, indptr, indices, device=0):
+        ip = np.ascontiguousarray(indptr, dtype=np.int64)
+        ix = np.ascontiguousarray(indices, dtype=np.int64)
+        self.num_nodes, self.num_edges, self.device = int(ip.size - 1), int(ix.size), int(device)
+        h = C.c_void_p()
+        N.check(N.lib().gs_graph_create(self.device, self.num_nodes, self.num_edges,
+                                        ip.ctypes.data, ix.ctypes.data, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            N.lib().gs_graph_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+class SampleView:
+    """One completed sample in a slot: header + views into the slab."""
+
+    def __init__(self, slicer, slot, hdr, dev_ptr, host_ptr):
+        self._slicer, self.slot = slicer, slot
+        self.num_layers, self.num_parts = hdr.num_layers, hdr.num_parts
+        self.n_seeds, self.batch_index = hdr.n_seeds, hdr.batch_index
+        self.edges, self.slab_used = int(hdr.edges), int(hdr.slab_used)
+        self.draw_cursor = int(hdr.draw_cursor)
+        L, P = self.num_layers, self.num_parts
+        self.frontier_len = [hdr.frontier_len[l] for l in range(L + 1)]
+        self.cand_len = [hdr.cand_len[l] for l in range(L)]
+        self._frontier = [(hdr.frontier[l].off, hdr.frontier[l].len) for l in range(L + 1)]
+        self._spans = [[[(hdr.field[l][g][f].off, hdr.field[l][g][f].len)
+                         for f in range(N.NUM_FIELDS)] for g in range(P)] for l in range(L)]
+        self._dev_ptr, self._host_ptr = dev_ptr, host_ptr
+        self._host = None
+        self._released = False
+        if host_ptr:
+            n = max(self.slab_used, 1)
+            self._host = np.ctypeslib.as_array(
+                C.cast(host_ptr, C.POINTER(C.c_int32)), shape=(n,))
+
+    # ---- host views (zero-copy into the pinned mirror until detach/release)
+    def _span(self, l, g, name):
+        return self._spans[l][g][N.FIELDS.index(name)]
+
+    def numpy(self, l, g, name):
+        if self._host is None:
+            raise RuntimeError("slicer was created with host_output=0: use .tensor()")
+        off, ln = self._span(l, g, name)
+        return self._host[off:off + ln]
+
+    def frontier_numpy(self, l):
+        if self._host is None:
+            raise RuntimeError("slicer was created with host_output=0: use .frontier_tensor()")
+        off, ln = self._frontier[l]
+        return self._host[off:off + ln]
+
+    # ---- device views (torch is plumbing here: it only wraps the pointer)
+    def _dev(self, off, ln):
+        import torch
+        if self._released:
+            raise RuntimeError("sample slot already released")
+        if ln == 0:
+            return torch.empty(0, dtype=torch.int32, device=f"cuda:{self._slicer.graph.device}")
+        return torch.as_tensor(_DevSpan(self._dev_ptr + 4 * off, ln, self),
+                               device=f"cuda:{self._slicer.graph.device}")
+
+    def tensor(self, l, g, name):
+        return self._dev(*self._span(l, g, name))
+
+    def frontier_tensor(self, l):
+        return self._dev(*self._frontier[l])
+
+    def field_len(self, l, g, name):
+        return self._span(l, g, name)[1]
+
+    def detach(self):
+        """Copy the host mirror out of the slot and give the slot back."""
+        if not self._released:
+            if self._host is not None:
+                self._host = self._host.copy()
+            self.release()
+
+    def release(self):
+        if not self._released:
+            self._released = True
+            self._slicer._release(self.slot)
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+    def algorithmic_bytes(self, owner_bytes=0, w=4):
+        """Compulsory traffic of this sample per SURVEY 8(d): every input read
+        once, every output written once (ids/positions `w` bytes, CSR row
+        offsets of the graph 8 bytes each, own csr_indptr `w` bytes)."""
+        L, P = self.num_layers, self.num_parts
+        total = 0
+        for l in range(L):
+            F, Fn = self.frontier_len[l], self.frontier_len[l + 1]
+            E = sum(self.field_len(l, g, "csr_indices") for g in range(P))
+            total += F * (w + 16 + owner_bytes) + E * (w + owner_bytes) + Fn * w
+            for g in range(P):
+                n = {k: self.field_len(l, g, k) for k in N.FIELDS}
+                total += (n["in_nodes"] + n["out_nodes"] + n["owned_out_nodes"] + n["from_ids"] +
+                          n["to_ids"] + n["self_ids_in"] + n["self_ids_out"]) * w
+                total += n["csr_indptr"] * w + n["csr_indices"] * w
+        return total
+
+
+class Slicer:
+    """gs_slicer: per-slot workspaces + CUDA graphs over one Graph."""
+
+    def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
+                 seed=0, owner=None, draws=None, host_output=True, use_graph=True,
+                 frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0):
+        L = N.lib()
+        self.graph = graph
+        cfg = N.Config()
+        L.gs_config_default(C.byref(cfg))
+        cfg.num_layers = len(fanouts)
+        for i, f in enumerate(fanouts):
+            cfg.fanouts[i] = int(f)
+        cfg.num_parts = int(num_parts)
+        cfg.seed = int(seed)
+        cfg.max_batch, cfg.num_slots, cfg.num_streams = int(max_batch), int(num_slots), int(num_streams)
+        cfg.host_output, cfg.use_graph = int(bool(host_output)), int(bool(use_graph))
+        cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)
+        cfg.slab_capacity, cfg.grid_ctas = int(slab_capacity), int(grid_ctas)
+        keep = []
+        if owner is not None:
+            o = np.ascontiguousarray(owner, dtype=np.int32)
+            if o.size != graph.num_nodes:
+                raise ValueError("owner map must have num_nodes entries")
+            keep.append(o)
+            cfg.owner_host = o.ctypes.data
+        if draws is not None:
+            d = np.ascontiguousarray(draws, dtype=np.uint32)
+            keep.append(d)
+            cfg.rng_mode, cfg.draws_host, cfg.n_draws = N.RNG_DRAWS, d.ctypes.data, d.size
+        h = C.c_void_p()
+        N.check(L.gs_slicer_create(graph._h, C.byref(cfg), C.byref(h)))
+        self._h = h
+        self.fanouts, self.num_parts, self.num_slots = list(fanouts), int(num_parts), int(num_slots)
+        self.launches_per_sample = L.gs_slicer_launches_per_sample(h)
+        self.slot_bytes = L.gs_slicer_slot_bytes(h)
+
+    def submit(self, seeds, batch_index=0):
+        s = np.ascontiguousarray(seeds, dtype=np.int64)
+        slot = C.c_int32(-1)
+        N.check(N.lib().gs_slicer_submit(self._h, s.ctypes.data, s.size, int(batch_index),
+                                         C.byref(slot)))
+        return slot.value
+
+    def wait(self, slot):
+        hp = C.POINTER(N.SampleHeader)()
+        try:
+            N.check(N.lib().gs_slicer_wait(self._h, slot, C.byref(hp)))
+        except N.SlicerError:
+            N.lib().gs_slicer_release(self._h, slot)
+            raise
+        dev, host = C.c_void_p(), C.c_void_p()
+        N.check(N.lib().gs_slicer_slab(self._h, slot, C.byref(dev), C.byref(host)))
+        return SampleView(self, slot, hp.contents, dev.value or 0, host.value or 0)
+
+    def wait_header(self, slot):
+        """Wait without building views (bench inner loop): -> (edges, slab_used)."""
+        hp = C.POINTER(N.SampleHeader)()
+        N.check(N.lib().gs_slicer_wait(self._h, slot, C.byref(hp)))
+        return hp.contents
+
+    def _release(self, slot):
+        if getattr(self, "_h", None):
+            N.lib().gs_slicer_release(self._h, slot)
+
+    release = _release
+
+    def slice(self, seeds, batch_index=0):
+        return self.wait(self.submit(seeds, batch_index))
+
+    def profile(self, seeds, batch_index=0):
+        """-> list of (kernel name, ms) for one eager run with events between launches."""
+        s = np.ascontiguousarray(seeds, dtype=np.int64)
+        cap = 4 + 8 * N.MAX_LAYERS
+        ms = (C.c_float * cap)()
+        names = (C.c_char_p * cap)()
+        n = C.c_int32(0)
+        N.check(N.lib().gs_slicer_profile(self._h, s.ctypes.data, s.size, int(batch_index), ms,
+                                          names, cap, C.byref(n)))
+        return [(names[i].decode(), float(ms[i])) for i in range(n.value)]
+
+    def close(self):
+        if getattr(self, "_h", None):
+            N.lib().gs_slicer_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def reference_shuffle(nodes, reset):
+    """In-place WorkerPool.cpp:40 epoch shuffle (libstdc++ random_shuffle + rand())."""
+    assert nodes.dtype == np.int64 and nodes.flags.c_contiguous
+    N.check(N.lib().gs_reference_shuffle(nodes.ctypes.data, nodes.size, int(bool(reset))))
+    return nodes

@@ -1,0 +1,567 @@
+// slicer_api.cu -- host side of the C ABI declared in include/gsplit_slicer.h.
+// Owns device memory, streams and the per-slot CUDA graphs; contains no
+// slicing logic of its own (that is slicer_kernels.cu) and no CPU fallback.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "slicer_internal.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                       \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess)                                                             \
+      return fail(GS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                  __FILE__, __LINE__);                                                 \
+  } while (0)
+
+enum SlotState { SLOT_FREE = 0, SLOT_BUSY = 1, SLOT_DONE = 2 };
+
+struct Slot {
+  GsWs ws{};
+  std::vector<void *> dev;  // device allocations owned by the slot
+  GsInput *input = nullptr; // pinned, mapped
+  int64_t *seeds = nullptr; // pinned, mapped
+  gs_sample_header *hdr_host = nullptr;
+  int32_t *slab_host = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaEvent_t done = nullptr;
+  cudaStream_t stream = nullptr;
+  int state = SLOT_FREE;
+};
+
+}  // namespace
+
+struct gs_graph {
+  int device = 0;
+  int64_t num_nodes = 0, num_edges = 0;
+  int64_t *indptr = nullptr;
+  int32_t *indices = nullptr;
+};
+
+struct gs_slicer {
+  gs_graph *g = nullptr;
+  gs_config cfg{};
+  int grid = 0;
+  int64_t Fcap = 0, Ccap = 0, slab_cap = 0;
+  uint8_t *owner = nullptr;
+  uint32_t *draws = nullptr;
+  uint64_t *draw_cursor = nullptr;
+  std::vector<cudaStream_t> streams;
+  std::vector<Slot> slots;
+  int next_slot = 0;
+  int64_t slot_bytes = 0;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(Slot &sl, T **p, size_t n, int64_t *bytes) {
+  void *q = nullptr;
+  size_t b = std::max<size_t>(n, 1) * sizeof(T);
+  CU(cudaMalloc(&q, b));
+  sl.dev.push_back(q);
+  *p = (T *)q;
+  *bytes += (int64_t)b;
+  return GS_OK;
+}
+
+// The static launch sequence of one minibatch.  `ev` (optional) receives one
+// event after every launch, for gs_slicer_profile.
+int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEvent_t> *ev,
+                   std::vector<const char *> *names) {
+  static const char *kNames[] = {"rows_count", "rows_scan",   "expand",      "cand_flags",
+                                 "cand_apply", "front_count", "front_apply", "relabel"};
+  auto mark = [&](const char *nm) -> int {
+    if (ev) {
+      cudaEvent_t e;
+      CU(cudaEventCreate(&e));
+      CU(cudaEventRecord(e, st));
+      ev->push_back(e);
+      names->push_back(nm);
+    }
+    return GS_OK;
+  };
+  int rc;
+  if ((rc = mark("start"))) return rc;
+  gs_launch_begin(sl.ws, st);
+  if ((rc = mark("begin"))) return rc;
+  for (int l = 0; l < s->cfg.num_layers; l++) {
+    gs_launch_rows_count(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[0]))) return rc;
+    gs_launch_rows_scan(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[1]))) return rc;
+    gs_launch_expand(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[2]))) return rc;
+    gs_launch_cand_flags(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[3]))) return rc;
+    gs_launch_cand_apply(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[4]))) return rc;
+    gs_launch_front_count(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[5]))) return rc;
+    gs_launch_front_apply(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[6]))) return rc;
+    gs_launch_relabel(sl.ws, l, s->grid, st);
+    if ((rc = mark(kNames[7]))) return rc;
+  }
+  gs_launch_finish(sl.ws, s->grid, st);
+  if ((rc = mark("finish"))) return rc;
+  CU(cudaGetLastError());
+  return GS_OK;
+}
+
+int stage_input(gs_slicer *s, Slot &sl, const int64_t *seeds, int32_t n, uint64_t batch_index) {
+  if (n < 0 || n > s->cfg.max_batch)
+    return fail(GS_ERR_INVALID, "batch of %d seeds exceeds max_batch=%d", n, s->cfg.max_batch);
+  if (n && !seeds) return fail(GS_ERR_INVALID, "seeds_host is NULL");
+  memcpy(sl.seeds, seeds, (size_t)n * sizeof(int64_t));
+  sl.input->n_seeds = n;
+  sl.input->want_host = s->cfg.host_output;
+  sl.input->batch_index = batch_index;
+  return GS_OK;
+}
+
+void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap, int64_t *Ccap,
+                        int64_t *slab) {
+  int64_t F = c.max_batch, fmax = F, cmax = 0, sl = F + 8;
+  const int64_t P = c.num_parts;
+  for (int l = 0; l < c.num_layers; l++) {
+    F = std::min(F, N);
+    fmax = std::max(fmax, F);
+    const int64_t fan = c.fanouts[l];
+    const int64_t E = fan >= 0 ? std::min(F * fan, M) : M;
+    const int64_t C = F + E;
+    cmax = std::max(cmax, C);
+    sl += std::min(N, C) + std::min(N, E) + E + 3 * std::min(P * F, E) + P + 4 * F +
+          4 * GS_NUM_FIELDS * P + 8;
+    F = std::min(N, C);
+  }
+  *Fcap = c.frontier_capacity > 0 ? c.frontier_capacity : fmax;
+  *Ccap = c.cand_capacity > 0 ? c.cand_capacity : cmax;
+  *slab = c.slab_capacity > 0 ? c.slab_capacity : sl;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *gs_last_error(void) { return g_err.c_str(); }
+int gs_abi_version(void) { return GS_ABI_VERSION; }
+
+void gs_config_default(gs_config *c) {
+  memset(c, 0, sizeof *c);
+  c->abi_version = GS_ABI_VERSION;
+  c->num_layers = 3;
+  for (int i = 0; i < GS_MAX_LAYERS; i++) c->fanouts[i] = 10;
+  c->num_parts = 4;
+  c->rng_mode = GS_RNG_PHILOX;
+  c->max_batch = 4096;
+  c->num_slots = 4;
+  c->num_streams = 4;
+  c->host_output = 1;
+  c->use_graph = 1;
+}
+
+int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
+                    const int64_t *indptr_host, const int64_t *indices_host, gs_graph **out) {
+  if (!out || !indptr_host || (num_edges && !indices_host))
+    return fail(GS_ERR_INVALID, "NULL argument");
+  if (num_nodes < 1 || num_nodes >= (1ll << 31) - 1 || num_edges < 0)
+    return fail(GS_ERR_INVALID, "num_nodes must be in [1, 2^31-2] (int32 ids on device)");
+  if (indptr_host[0] != 0 || indptr_host[num_nodes] != num_edges)
+    return fail(GS_ERR_INVALID, "indptr[0] != 0 or indptr[N] != num_edges");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(GS_ERR_CUDA, "no CUDA device (%s): this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  CU(cudaSetDevice(device));
+  gs_graph *g = new (std::nothrow) gs_graph();
+  if (!g) return fail(GS_ERR_INVALID, "out of host memory");
+  g->device = device;
+  g->num_nodes = num_nodes;
+  g->num_edges = num_edges;
+  CU(cudaMalloc((void **)&g->indptr, (size_t)(num_nodes + 1) * sizeof(int64_t)));
+  CU(cudaMemcpy(g->indptr, indptr_host, (size_t)(num_nodes + 1) * sizeof(int64_t),
+                cudaMemcpyHostToDevice));
+  CU(cudaMalloc((void **)&g->indices, (size_t)std::max<int64_t>(num_edges, 1) * sizeof(int32_t)));
+  // narrow int64 -> int32 on the device, in bounded chunks
+  const int64_t chunk = 1ll << 26;
+  int64_t *tmp = nullptr;
+  CU(cudaMalloc((void **)&tmp, (size_t)std::min(chunk, std::max<int64_t>(num_edges, 1)) *
+                                   sizeof(int64_t)));
+  for (int64_t o = 0; o < num_edges; o += chunk) {
+    const int64_t n = std::min(chunk, num_edges - o);
+    CU(cudaMemcpy(tmp, indices_host + o, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice));
+    gs_launch_narrow_ids(tmp, g->indices + o, (size_t)n, 0);
+    CU(cudaGetLastError());
+  }
+  CU(cudaDeviceSynchronize());
+  CU(cudaFree(tmp));
+  *out = g;
+  return GS_OK;
+}
+
+int gs_graph_destroy(gs_graph *g) {
+  if (!g) return GS_OK;
+  cudaSetDevice(g->device);
+  cudaFree(g->indptr);
+  cudaFree(g->indices);
+  delete g;
+  return GS_OK;
+}
+int64_t gs_graph_num_nodes(const gs_graph *g) { return g ? g->num_nodes : 0; }
+int64_t gs_graph_num_edges(const gs_graph *g) { return g ? g->num_edges : 0; }
+
+}  // extern "C"
+
+extern "C" {
+
+int gs_slicer_destroy(gs_slicer *s) {
+  if (!s) return GS_OK;
+  cudaSetDevice(s->g->device);
+  cudaDeviceSynchronize();
+  for (Slot &sl : s->slots) {
+    if (sl.exec) cudaGraphExecDestroy(sl.exec);
+    if (sl.done) cudaEventDestroy(sl.done);
+    for (void *p : sl.dev) cudaFree(p);
+    if (sl.input) cudaFreeHost(sl.input);
+    if (sl.seeds) cudaFreeHost(sl.seeds);
+    if (sl.hdr_host) cudaFreeHost(sl.hdr_host);
+    if (sl.slab_host) cudaFreeHost(sl.slab_host);
+  }
+  for (cudaStream_t st : s->streams) cudaStreamDestroy(st);
+  cudaFree(s->owner);
+  cudaFree(s->draws);
+  cudaFree(s->draw_cursor);
+  delete s;
+  return GS_OK;
+}
+
+int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
+  if (!g || !cfg || !out) return fail(GS_ERR_INVALID, "NULL argument");
+  if (cfg->abi_version != GS_ABI_VERSION)
+    return fail(GS_ERR_INVALID, "gs_config.abi_version %d != %d", cfg->abi_version, GS_ABI_VERSION);
+  if (cfg->num_layers < 1 || cfg->num_layers > GS_MAX_LAYERS)
+    return fail(GS_ERR_INVALID, "num_layers must be in [1,%d]", GS_MAX_LAYERS);
+  if (cfg->num_parts < 1 || cfg->num_parts > GS_MAX_PARTS)
+    return fail(GS_ERR_INVALID, "num_parts must be in [1,%d]", GS_MAX_PARTS);
+  for (int l = 0; l < cfg->num_layers; l++)
+    if (cfg->fanouts[l] < -1 || cfg->fanouts[l] == 0 || cfg->fanouts[l] > 1023)
+      return fail(GS_ERR_INVALID, "fanouts[%d]=%d: use -1 (all neighbours) or 1..1023", l,
+                  cfg->fanouts[l]);
+  if (cfg->max_batch < 1) return fail(GS_ERR_INVALID, "max_batch must be >= 1");
+  if (cfg->num_slots < 1 || cfg->num_slots > 256)
+    return fail(GS_ERR_INVALID, "num_slots must be in [1,256]");
+  if (cfg->rng_mode != GS_RNG_PHILOX && cfg->rng_mode != GS_RNG_DRAWS)
+    return fail(GS_ERR_INVALID, "unknown rng_mode %d", cfg->rng_mode);
+  if (cfg->rng_mode == GS_RNG_DRAWS && (!cfg->draws_host || cfg->n_draws == 0))
+    return fail(GS_ERR_INVALID, "GS_RNG_DRAWS needs draws_host / n_draws");
+  CU(cudaSetDevice(g->device));
+
+  gs_slicer *s = new (std::nothrow) gs_slicer();
+  if (!s) return fail(GS_ERR_INVALID, "out of host memory");
+  s->g = g;
+  s->cfg = *cfg;
+  s->cfg.owner_host = nullptr;
+  s->cfg.draws_host = nullptr;
+  const int64_t N = g->num_nodes, M = g->num_edges;
+  compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap);
+  if (s->Ccap >= (1ll << 31) - 2 * GS_TILE || s->Fcap >= (1ll << 31) - 2 * GS_TILE ||
+      s->slab_cap >= (1ll << 31) - 16) {
+    delete s;
+    return fail(GS_ERR_INVALID, "derived capacities exceed 2^31 positions; lower max_batch or set "
+                                "cand_capacity / slab_capacity");
+  }
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g->device);
+  s->grid = cfg->grid_ctas > 0 ? cfg->grid_ctas : 2 * sms;
+
+#define CUS(call)                                                                        \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      fail(GS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+           __LINE__);                                                                    \
+      std::string keep = g_err;                                                          \
+      gs_slicer_destroy(s);                                                              \
+      g_err = keep;                                                                      \
+      return GS_ERR_CUDA;                                                                \
+    }                                                                                    \
+  } while (0)
+
+  if (cfg->owner_host) {
+    std::vector<uint8_t> o8((size_t)N);
+    for (int64_t i = 0; i < N; i++) {
+      const int32_t o = cfg->owner_host[i];
+      if (o < 0 || o >= cfg->num_parts) {
+        gs_slicer_destroy(s);
+        return fail(GS_ERR_INVALID, "owner_host[%lld]=%d outside [0,%d)", (long long)i, o,
+                    cfg->num_parts);
+      }
+      o8[(size_t)i] = (uint8_t)o;
+    }
+    CUS(cudaMalloc((void **)&s->owner, (size_t)N));
+    CUS(cudaMemcpy(s->owner, o8.data(), (size_t)N, cudaMemcpyHostToDevice));
+  }
+  if (cfg->rng_mode == GS_RNG_DRAWS) {
+    CUS(cudaMalloc((void **)&s->draws, (size_t)cfg->n_draws * sizeof(uint32_t)));
+    CUS(cudaMemcpy(s->draws, cfg->draws_host, (size_t)cfg->n_draws * sizeof(uint32_t),
+                   cudaMemcpyHostToDevice));
+  }
+  CUS(cudaMalloc((void **)&s->draw_cursor, sizeof(uint64_t)));
+  CUS(cudaMemset(s->draw_cursor, 0, sizeof(uint64_t)));
+
+  // replay mode consumes one sequential draw stream: keep every slot on one stream
+  const int nstreams =
+      cfg->rng_mode == GS_RNG_DRAWS ? 1 : std::max(1, std::min(cfg->num_streams, cfg->num_slots));
+  s->streams.resize(nstreams);
+  for (int i = 0; i < nstreams; i++) {
+    s->streams[i] = nullptr;
+    CUS(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
+  }
+
+  const int ftiles = (int)((s->Fcap + GS_TILE - 1) / GS_TILE) + 1;
+  const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;
+  s->slots.resize(cfg->num_slots);
+  for (int k = 0; k < cfg->num_slots; k++) {
+    Slot &sl = s->slots[k];
+    GsWs &w = sl.ws;
+    int64_t bytes = 0;
+    w.indptr = g->indptr;
+    w.indices = g->indices;
+    w.owner = s->owner;
+    w.num_nodes = (int32_t)N;
+    w.P = cfg->num_parts;
+    w.L = cfg->num_layers;
+    for (int l = 0; l < GS_MAX_LAYERS; l++) w.fanouts[l] = cfg->fanouts[l];
+    w.rng_mode = cfg->rng_mode;
+    w.seed_lo = (uint32_t)cfg->seed;
+    w.seed_hi = (uint32_t)(cfg->seed >> 32);
+    w.draws = s->draws;
+    w.n_draws = cfg->n_draws;
+    w.draw_cursor = s->draw_cursor;
+    w.slab_cap = s->slab_cap;
+    w.Fcap = (int32_t)s->Fcap;
+    w.Ccap = (int32_t)s->Ccap;
+    w.ftiles_max = ftiles;
+    w.ctiles_max = ctiles;
+#define DA(ptr, n)                                         \
+  do {                                                     \
+    if (dev_alloc(sl, &ptr, (size_t)(n), &bytes) != GS_OK) { \
+      std::string keep = g_err;                            \
+      gs_slicer_destroy(s);                                \
+      g_err = keep;                                        \
+      return GS_ERR_CUDA;                                  \
+    }                                                      \
+  } while (0)
+    DA(w.hdr, 1);
+    DA(w.table, N);
+    DA(w.slab, s->slab_cap + 4);
+    DA(w.rowstart, s->Fcap);
+    DA(w.rowdeg, s->Fcap);
+    DA(w.off, s->Fcap + 1);
+    DA(w.samp_rank, s->Fcap);
+    DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
+    DA(w.cand, s->Ccap);
+    DA(w.cflag, s->Ccap);
+    DA(w.tile_first, ctiles + 1);
+    DA(w.ftile_sum, ftiles);
+    DA(w.ftile_samp, ftiles);
+    DA(w.ftile_pre, 2 * (size_t)ftiles);
+    DA(w.ctile_cnt, (size_t)GS_NC_MAX * ctiles);
+    DA(w.ftile_cnt, (size_t)GS_NF_MAX * ftiles);
+    DA(w.tickets, 8);
+#undef DA
+    s->slot_bytes = bytes;
+    CUS(cudaMemset(w.hdr, 0, sizeof(gs_sample_header)));
+    CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
+    CUS(cudaMemset(w.table, 0xFF, (size_t)N * sizeof(uint2)));
+    CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
+    CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
+                      cudaHostAllocMapped));
+    CUS(cudaHostAlloc((void **)&sl.hdr_host, sizeof(gs_sample_header), cudaHostAllocMapped));
+    memset(sl.hdr_host, 0, sizeof(gs_sample_header));
+    memset(sl.input, 0, sizeof(GsInput));
+    if (cfg->host_output)
+      CUS(cudaHostAlloc((void **)&sl.slab_host, (size_t)(s->slab_cap + 4) * sizeof(int32_t),
+                        cudaHostAllocMapped));
+    void *dp = nullptr;
+    CUS(cudaHostGetDevicePointer(&dp, sl.input, 0));
+    w.input = (const GsInput *)dp;
+    CUS(cudaHostGetDevicePointer(&dp, sl.seeds, 0));
+    w.seeds_in = (const int64_t *)dp;
+    CUS(cudaHostGetDevicePointer(&dp, sl.hdr_host, 0));
+    w.hdr_host = (gs_sample_header *)dp;
+    w.slab_host = nullptr;
+    if (sl.slab_host) {
+      CUS(cudaHostGetDevicePointer(&dp, sl.slab_host, 0));
+      w.slab_host = (int32_t *)dp;
+    }
+    sl.stream = s->streams[k % nstreams];
+    CUS(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    if (cfg->use_graph) {
+      cudaGraph_t graph = nullptr;
+      CUS(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
+      int rc = enqueue_sample(s, sl, sl.stream, nullptr, nullptr);
+      cudaError_t ce = cudaStreamEndCapture(sl.stream, &graph);
+      if (rc != GS_OK || ce != cudaSuccess) {
+        if (rc == GS_OK) fail(GS_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(ce));
+        std::string keep = g_err;
+        gs_slicer_destroy(s);
+        g_err = keep;
+        return GS_ERR_CUDA;
+      }
+      CUS(cudaGraphInstantiate(&sl.exec, graph, 0));
+      cudaGraphDestroy(graph);
+    }
+  }
+  CUS(cudaDeviceSynchronize());
+#undef CUS
+  *out = s;
+  return GS_OK;
+}
+
+int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                     int32_t *slot_out) {
+  if (!s || !slot_out) return fail(GS_ERR_INVALID, "NULL argument");
+  CU(cudaSetDevice(s->g->device));
+  const int ns = (int)s->slots.size();
+  int k = -1;
+  for (int t = 0; t < ns; t++) {
+    const int c = (s->next_slot + t) % ns;
+    if (s->slots[c].state == SLOT_FREE) {
+      k = c;
+      break;
+    }
+  }
+  if (k < 0) return fail(GS_ERR_BUSY, "all %d sample slots are in use; release one", ns);
+  Slot &sl = s->slots[k];
+  int rc = stage_input(s, sl, seeds_host, n, batch_index);
+  if (rc != GS_OK) return rc;
+  if (sl.exec) {
+    CU(cudaGraphLaunch(sl.exec, sl.stream));
+  } else {
+    rc = enqueue_sample(s, sl, sl.stream, nullptr, nullptr);
+    if (rc != GS_OK) return rc;
+  }
+  CU(cudaEventRecord(sl.done, sl.stream));
+  sl.state = SLOT_BUSY;
+  s->next_slot = (k + 1) % ns;
+  *slot_out = k;
+  return GS_OK;
+}
+
+static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out) {
+  sl.state = SLOT_DONE;
+  const int st = sl.hdr_host->status;
+  if (hdr_out) *hdr_out = sl.hdr_host;
+  if (st != 0) {
+    // a sample that stopped half way may have left touched table entries behind
+    cudaMemsetAsync(sl.ws.table, 0xFF, (size_t)s->g->num_nodes * sizeof(uint2), sl.stream);
+    cudaStreamSynchronize(sl.stream);
+    if (st == GS_ERR_OVERFLOW)
+      return fail(GS_ERR_OVERFLOW,
+                  "sample outgrew its workspace (frontier_capacity=%lld cand_capacity=%lld "
+                  "slab_capacity=%lld): raise them in gs_config",
+                  (long long)s->Fcap, (long long)s->Ccap, (long long)s->slab_cap);
+    if (st == GS_ERR_SEED)
+      return fail(GS_ERR_SEED, "seed ids must be distinct and in [0, num_nodes)");
+    return fail(st, "device raised status %d", st);
+  }
+  return GS_OK;
+}
+
+int gs_slicer_wait(gs_slicer *s, int32_t slot, const gs_sample_header **hdr_out) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  Slot &sl = s->slots[slot];
+  if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
+  CU(cudaSetDevice(s->g->device));
+  if (sl.state == SLOT_BUSY) CU(cudaEventSynchronize(sl.done));
+  return finish_wait(s, sl, hdr_out);
+}
+
+int gs_slicer_slab(gs_slicer *s, int32_t slot, const int32_t **device_slab,
+                   const int32_t **host_slab) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  Slot &sl = s->slots[slot];
+  if (sl.state != SLOT_DONE) return fail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (device_slab) *device_slab = sl.ws.slab;
+  if (host_slab) *host_slab = sl.slab_host;
+  return GS_OK;
+}
+
+int gs_slicer_release(gs_slicer *s, int32_t slot) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  Slot &sl = s->slots[slot];
+  if (sl.state == SLOT_BUSY) {
+    CU(cudaSetDevice(s->g->device));
+    CU(cudaEventSynchronize(sl.done));
+    finish_wait(s, sl, nullptr);
+  }
+  sl.state = SLOT_FREE;
+  return GS_OK;
+}
+
+int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                      float *ms, const char **names, int32_t cap, int32_t *n_out) {
+  if (!s || !ms || !names || !n_out) return fail(GS_ERR_INVALID, "NULL argument");
+  CU(cudaSetDevice(s->g->device));
+  Slot &sl = s->slots[0];
+  if (sl.state != SLOT_FREE) return fail(GS_ERR_BUSY, "slot 0 must be free to profile");
+  int rc = stage_input(s, sl, seeds_host, n, batch_index);
+  if (rc != GS_OK) return rc;
+  std::vector<cudaEvent_t> ev;
+  std::vector<const char *> nm;
+  rc = enqueue_sample(s, sl, sl.stream, &ev, &nm);
+  if (rc == GS_OK) {
+    cudaError_t e = cudaStreamSynchronize(sl.stream);
+    if (e != cudaSuccess) rc = fail(GS_ERR_CUDA, "profile run failed: %s", cudaGetErrorString(e));
+  }
+  int cnt = 0;
+  if (rc == GS_OK)
+    for (size_t i = 1; i < ev.size() && cnt < cap; i++, cnt++) {
+      cudaEventElapsedTime(&ms[cnt], ev[i - 1], ev[i]);
+      names[cnt] = nm[i];
+    }
+  for (cudaEvent_t e : ev) cudaEventDestroy(e);
+  *n_out = cnt;
+  if (rc != GS_OK) return rc;
+  sl.state = SLOT_BUSY;  // completed; let wait()/release() run the normal path
+  CU(cudaEventRecord(sl.done, sl.stream));
+  const gs_sample_header *h;
+  rc = finish_wait(s, sl, &h);
+  sl.state = SLOT_FREE;
+  return rc;
+}
+
+int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset) {
+  if (!nodes && n > 0) return fail(GS_ERR_INVALID, "NULL argument");
+  if (reset) srand(1);
+  for (int64_t i = 1; i < n; i++) std::swap(nodes[i], nodes[(int64_t)rand() % (i + 1)]);
+  return GS_OK;
+}
+
+int gs_slicer_launches_per_sample(const gs_slicer *s) { return s ? 2 + 8 * s->cfg.num_layers : 0; }
+int64_t gs_slicer_slot_bytes(const gs_slicer *s) { return s ? s->slot_bytes : 0; }
+
+}  // extern "C"

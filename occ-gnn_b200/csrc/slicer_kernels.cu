@@ -1,0 +1,873 @@
+// slicer_kernels.cu -- hand-written sm_100a kernels of the minibatch slicer.
+//
+// One layer of the reference's sequential slice_layer (slicer.cpp:25-64) +
+// BiPartite::reorder (bipartite.cpp:3-17) becomes eight data-parallel passes.
+// The sequential order the reference's lists are in (first occurrence in a
+// scan over frontier rows and, inside a row, over [self, neighbours...]) is
+// carried by a 32-bit *candidate position*: row i owns positions
+// [off[i], off[i+1]), slot 0 being the self entry.  "First occurrence" = minimum
+// position (atomicMin into a direct-address table), "list order" = ascending
+// position (prefix scans over the candidate stream), so every output list is
+// bit-identical to the sequential algorithm without any sort.
+//
+// All sizes live in device memory (gs_sample_header); every kernel is a
+// fixed-size grid striding over tiles, so a whole minibatch is one static CUDA
+// graph with no host round trip.  Integer / byte work, HBM- and latency-bound:
+// no tensor cores (nothing here is a contraction).
+#include "slicer_internal.cuh"
+
+#define FULL 0xFFFFFFFFu
+
+namespace {
+
+// ------------------------------------------------------------------ helpers
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
+__device__ __forceinline__ uint32_t lt_mask() { return (1u << lane_id()) - 1u; }
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+  const int lane = lane_id();
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t n = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += n;
+  }
+  return v;
+}
+__device__ __forceinline__ unsigned long long warp_incl_scan64(unsigned long long v) {
+  const int lane = lane_id();
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    unsigned long long n = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += n;
+  }
+  return v;
+}
+
+// Exclusive scan of one value per thread over the CTA.  s_w: GS_NW+1 words.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *s_w, uint32_t &total) {
+  const int lane = lane_id(), w = warp_id();
+  uint32_t inc = warp_incl_scan(v);
+  if (lane == 31) s_w[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t x = lane < GS_NW ? s_w[lane] : 0u;
+    uint32_t xi = warp_incl_scan(x);
+    if (lane < GS_NW) s_w[lane] = xi - x;
+    if (lane == GS_NW - 1) s_w[GS_NW] = xi;
+  }
+  __syncthreads();
+  uint32_t res = s_w[w] + inc - v;
+  total = s_w[GS_NW];
+  __syncthreads();
+  return res;
+}
+__device__ __forceinline__ unsigned long long block_excl_scan64(unsigned long long v,
+                                                               unsigned long long *s_w,
+                                                               unsigned long long &total) {
+  const int lane = lane_id(), w = warp_id();
+  unsigned long long inc = warp_incl_scan64(v);
+  if (lane == 31) s_w[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    unsigned long long x = lane < GS_NW ? s_w[lane] : 0ull;
+    unsigned long long xi = warp_incl_scan64(x);
+    if (lane < GS_NW) s_w[lane] = xi - x;
+    if (lane == GS_NW - 1) s_w[GS_NW] = xi;
+  }
+  __syncthreads();
+  unsigned long long res = s_w[w] + inc - v;
+  total = s_w[GS_NW];
+  __syncthreads();
+  return res;
+}
+
+// Last-CTA election: every CTA calls this after its tile results are written.
+// Returns true in exactly one CTA (the last to arrive), with all other CTAs'
+// writes visible to it.  The ticket is re-armed for the next launch.
+__device__ __forceinline__ bool last_block(uint32_t *ticket) {
+  __shared__ uint32_t s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1) ? 1u : 0u;
+    if (s_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0u;
+}
+
+__device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
+  return ws.owner ? (int)__ldg(ws.owner + v) : (int)((uint32_t)v % (uint32_t)ws.P);
+}
+
+// slab bump allocator (single thread).  16-byte aligned spans.
+__device__ __forceinline__ gs_span slab_alloc(gs_sample_header *h, int64_t cap, uint32_t len,
+                                              bool &ok) {
+  gs_span s;
+  int64_t off = h->slab_used;
+  int64_t next = off + (((int64_t)len + 3) & ~3ll);
+  if (next > cap || next > 0x7FFFFFFFll) {
+    ok = false;
+    s.off = 0;
+    s.len = 0;
+    return s;
+  }
+  h->slab_used = next;
+  s.off = (int32_t)off;
+  s.len = (int32_t)len;
+  return s;
+}
+
+// Philox4x32-10 (Salmon et al. SC'11).  Draw for (seed, batch, layer, row's
+// global node id, pick slot): counter-based, so any thread can produce any
+// pick and the result does not depend on the schedule.
+__device__ __forceinline__ uint32_t philox_pick(uint32_t k0, uint32_t k1, uint32_t batch,
+                                                int layer, int32_t node, int slot) {
+  uint32_t c0 = (uint32_t)node, c1 = 0u, c2 = batch,
+           c3 = ((uint32_t)layer << 24) | (uint32_t)(slot >> 2);
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  const int w = slot & 3;
+  return w == 0 ? c0 : (w == 1 ? c1 : (w == 2 ? c2 : c3));
+}
+
+// Two-level exclusive scan of `nc` counter arrays (cnt[c*stride + t], t < n)
+// by one whole CTA, in place; totals[c] receives each array's sum.
+template <int NCMAX>
+__device__ void spine_scan(uint32_t *cnt, int stride, int n, int nc, uint32_t *totals,
+                           uint32_t *s_w) {
+  const int tid = threadIdx.x;
+  const int chunk = (n + GS_TPB - 1) / GS_TPB;
+  const int a = min(n, tid * chunk), b = min(n, a + chunk);
+  uint32_t sum[NCMAX];
+#pragma unroll
+  for (int c = 0; c < NCMAX; c++) {
+    sum[c] = 0u;
+    if (c < nc)
+      for (int t = a; t < b; t++) sum[c] += __ldcg(cnt + (size_t)c * stride + t);
+  }
+#pragma unroll
+  for (int c = 0; c < NCMAX; c++) {
+    if (c < nc) {  // nc is CTA-uniform
+      uint32_t tot;
+      uint32_t pre = block_excl_scan(sum[c], s_w, tot);
+      if (tid == 0) totals[c] = tot;
+      for (int t = a; t < b; t++) {
+        uint32_t v = __ldcg(cnt + (size_t)c * stride + t);
+        cnt[(size_t)c * stride + t] = pre;
+        pre += v;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------ k_begin
+// One CTA.  Resets the sample header, narrows the seed ids (int64, pinned
+// host memory read over PCIe) into the slab as frontier 0.
+__global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
+  gs_sample_header *h = ws.hdr;
+  const int n = ws.input->n_seeds;
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+  gs_span *spans = &h->field[0][0][0];
+  for (int i = threadIdx.x; i < GS_MAX_LAYERS * GS_MAX_PARTS * GS_NUM_FIELDS; i += blockDim.x) {
+    spans[i].off = 0;
+    spans[i].len = 0;
+  }
+  for (int i = threadIdx.x; i <= GS_MAX_LAYERS; i += blockDim.x) {
+    h->frontier_len[i] = 0;
+    h->frontier[i].off = 0;
+    h->frontier[i].len = 0;
+    if (i < GS_MAX_LAYERS) {
+      h->cand_len[i] = 0;
+      h->draw_base[i] = 0;
+    }
+  }
+  bool bad = (n < 0 || n > ws.Fcap || (int64_t)n > ws.slab_cap);
+  if (!bad)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      int64_t v = ws.seeds_in[i];
+      if (v < 0 || v >= (int64_t)ws.num_nodes) s_bad = 1;
+      else ws.slab[i] = (int32_t)v;
+    }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bad = bad || s_bad;
+    h->status = bad ? (int32_t)GS_ERR_SEED : 0;
+    h->num_layers = ws.L;
+    h->num_parts = ws.P;
+    h->n_seeds = n;
+    h->batch_index = ws.input->batch_index;
+    h->draw_cursor = *ws.draw_cursor;
+    h->edges = 0;
+    h->reserved[0] = 0;  // late error raised inside a tiled kernel
+    const int nn = bad ? 0 : n;
+    h->slab_used = ((int64_t)nn + 3) & ~3ll;
+    h->frontier_len[0] = nn;
+    h->frontier[0].off = 0;
+    h->frontier[0].len = nn;
+  }
+}
+
+// ------------------------------------------------------------- k_rows_count
+// Per frontier row: CSR extent and number of candidates c = 1 + (deg < fan or
+// fan < 0 ? deg : fan)  (slicer.cpp:6-22).  Tile sums + last-CTA spine give the
+// candidate offsets' tile prefixes and C_l.
+__global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ unsigned long long s_w64[GS_NW + 1];
+  __shared__ uint32_t s_w[GS_NW + 1];
+  const int F = h->frontier_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int fan = ws.fanouts[layer];
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    unsigned long long csum = 0ull;
+    uint32_t ssum = 0u;
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
+      if (i < F) {
+        const int32_t nd = front[i];
+        const int64_t s = __ldg(ws.indptr + nd), e = __ldg(ws.indptr + nd + 1);
+        const int32_t deg = (int32_t)(e - s);
+        ws.rowstart[i] = s;
+        ws.rowdeg[i] = deg;
+        const bool samp = fan >= 0 && deg >= fan;
+        csum += 1ull + (unsigned long long)(samp ? fan : deg);
+        ssum += samp ? 1u : 0u;
+      }
+    }
+    unsigned long long ctot;
+    uint32_t stot;
+    block_excl_scan64(csum, s_w64, ctot);
+    block_excl_scan(ssum, s_w, stot);
+    if (threadIdx.x == 0) {
+      ws.ftile_sum[t] = ctot;
+      ws.ftile_samp[t] = stot;
+    }
+  }
+  if (!last_block(ws.tickets + 0)) return;
+  // spine: exclusive prefixes over frontier tiles
+  const int chunk = (ntiles + GS_TPB - 1) / GS_TPB;
+  const int a = min(ntiles, (int)threadIdx.x * chunk), b = min(ntiles, a + chunk);
+  unsigned long long cs = 0ull;
+  uint32_t ss = 0u;
+  for (int t = a; t < b; t++) {
+    cs += __ldcg(ws.ftile_sum + t);
+    ss += __ldcg(ws.ftile_samp + t);
+  }
+  unsigned long long ctot;
+  uint32_t stot;
+  unsigned long long cpre = block_excl_scan64(cs, s_w64, ctot);
+  uint32_t spre = block_excl_scan(ss, s_w, stot);
+  const bool ok = ctot <= (unsigned long long)ws.Ccap;
+  if (ok)
+    for (int t = a; t < b; t++) {
+      ws.ftile_pre[t] = (uint32_t)cpre;
+      ws.ftile_pre[ws.ftiles_max + t] = spre;
+      cpre += __ldcg(ws.ftile_sum + t);
+      spre += __ldcg(ws.ftile_samp + t);
+    }
+  if (threadIdx.x == 0) {
+    if (!ok) {
+      h->status = (int32_t)GS_ERR_OVERFLOW;
+      h->cand_len[layer] = 0;
+    } else {
+      h->cand_len[layer] = (int32_t)ctot;
+      ws.off[F] = (uint32_t)ctot;
+      const uint64_t base = *ws.draw_cursor;
+      h->draw_base[layer] = base;
+      if (fan > 0) *ws.draw_cursor = base + (uint64_t)fan * (uint64_t)stot;
+    }
+  }
+}
+
+// -------------------------------------------------------------- k_rows_scan
+// Candidate offset of every row; plants the row's self entry (slot 0) in the
+// candidate stream, (re)initialises the row node's table entry to
+// {no edge-source occurrence yet, self position}, and records which row each
+// candidate tile starts in.
+__global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_w[GS_NW + 1];
+  const int F = h->frontier_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int fan = ws.fanouts[layer];
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    uint32_t base = ws.ftile_pre[t];
+    uint32_t sbase = ws.ftile_pre[ws.ftiles_max + t];
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
+      uint32_t c = 0u, sflag = 0u;
+      int32_t nd = 0;
+      if (i < F) {
+        nd = front[i];
+        const int32_t deg = ws.rowdeg[i];
+        const bool samp = fan >= 0 && deg >= fan;
+        c = 1u + (uint32_t)(samp ? fan : deg);
+        sflag = samp ? 1u : 0u;
+      }
+      uint32_t ctot, stot = 0u;
+      const uint32_t ex = block_excl_scan(c, s_w, ctot);
+      uint32_t sex = 0u;
+      if (replay) sex = block_excl_scan(sflag, s_w, stot);
+      if (i < F) {
+        const uint32_t o = base + ex;
+        ws.off[i] = o;
+        if (replay) ws.samp_rank[i] = sbase + sex;
+        ws.table[nd] = make_uint2(GS_INF, o);
+        ws.cand[o] = i;
+        ws.cflag[o] = (uint8_t)GS_CF_SELF;
+        for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
+          ws.tile_first[tb] = (uint32_t)i;
+      }
+      base += ctot;
+      sbase += stot;
+    }
+  }
+}
+
+// ----------------------------------------------------------------- k_expand
+// Candidate-parallel CSR row expansion (slicer.cpp:6-22).  A tile is GS_TILE
+// consecutive candidate positions, so load is balanced whatever the degree
+// skew; the rows a tile touches are found from tile_first[] and a binary
+// search over their offsets staged in shared memory.  Slots >= 1 of a row are
+// either all its neighbours in CSR order (coalesced reads) or `fan` picks with
+// replacement.  Every real edge source does atomicMin(position) into the
+// direct-address table -- the parallel form of DuplicateRemover's first-
+// occurrence rule (util/duplicate.cpp:14-26).
+__global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_off[GS_TILE + 2];
+  const int F = h->frontier_len[layer];
+  const uint32_t C = (uint32_t)h->cand_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int fan = ws.fanouts[layer];
+  const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
+  const uint32_t batch = (uint32_t)h->batch_index;
+  const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
+  const uint64_t dbase = h->draw_base[layer];
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int i_lo = (int)ws.tile_first[t];
+    const int i_hi = (t + 1 < ntiles) ? (int)ws.tile_first[t + 1] : F - 1;
+    const int cnt = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
+    for (int k = threadIdx.x; k <= cnt; k += GS_TPB) s_off[k] = ws.off[i_lo + k];
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      if (p < C) {
+        int lo = 0, hi = cnt - 1;  // largest k with s_off[k] <= p
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (s_off[mid] <= p) lo = mid; else hi = mid - 1;
+        }
+        const int j = (int)(p - s_off[lo]);
+        if (j > 0) {  // slot 0 (self) was planted by k_rows_scan
+          const int i = i_lo + lo;
+          const int32_t nd1 = front[i];
+          const int64_t rs = ws.rowstart[i];
+          const int32_t deg = ws.rowdeg[i];
+          int32_t pick = j - 1;
+          if (fan >= 0 && deg >= fan) {
+            uint32_t r;
+            if (replay) {
+              const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[i] + (uint32_t)(j - 1);
+              r = di < ws.n_draws ? ws.draws[di] : 0u;
+            } else {
+              r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1, j - 1);
+            }
+            pick = (int32_t)(r % (uint32_t)deg);
+          }
+          const int32_t v = __ldg(ws.indices + rs + pick);
+          ws.cand[p] = v;
+          if (v != nd1) {
+            ws.cflag[p] = 0;
+            atomicMin(&ws.table[v].x, p);
+          } else {
+            ws.cflag[p] = (uint8_t)GS_CF_LOOP;
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------- k_cand_flags
+// With every minimum in place, classify each candidate: first occurrence in
+// the layer (-> next frontier, slicer.cpp:45-49), first occurrence as an edge
+// source (-> in_nodes of the owner's bipartite, bipartite.cpp:4), real edge of
+// part g.  Per-tile counts of the 2P+1 classes, then the last CTA scans them
+// over tiles, fixes F_{l+1}, |in_nodes_g|, E_g and lays the lists out in the slab.
+__global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_cnt[GS_NC_MAX];
+  __shared__ uint32_t s_tot[GS_NC_MAX];
+  __shared__ uint32_t s_w[GS_NW + 1];
+  const int P = ws.P, NC = 2 * P + 1;
+  const int F = h->frontier_len[layer];
+  const uint32_t C = (uint32_t)h->cand_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
+  if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      bool ffirst = false, ifirst = false, edge = false;
+      int g = 0;
+      if (p < C) {
+        uint32_t f = ws.cflag[p];
+        const int32_t c = ws.cand[p];
+        const bool isself = (f & GS_CF_SELF) != 0u;
+        const int32_t v = isself ? front[c] : c;
+        const uint2 e = ws.table[v];
+        if (isself) {
+          ffirst = e.x > p;
+          if (e.y != p) h->reserved[0] = (int32_t)GS_ERR_SEED;  // duplicate seed
+        } else if (!(f & GS_CF_LOOP)) {
+          edge = true;
+          ifirst = e.x == p;
+          ffirst = ifirst && e.y > p;
+          g = owner_of(ws, v);
+        }
+        f = (f & (GS_CF_SELF | GS_CF_LOOP)) | (ffirst ? GS_CF_FFIRST : 0u) |
+            (ifirst ? GS_CF_IFIRST : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
+        ws.cflag[p] = (uint8_t)f;
+      }
+      const uint32_t mf = __ballot_sync(FULL, ffirst);
+      if (lane_id() == 0 && mf) atomicAdd(&s_cnt[0], (uint32_t)__popc(mf));
+      for (int q = 0; q < P; q++) {
+        const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
+        const uint32_t me = __ballot_sync(FULL, edge && g == q);
+        if (lane_id() == 0) {
+          if (mi) atomicAdd(&s_cnt[1 + q], (uint32_t)__popc(mi));
+          if (me) atomicAdd(&s_cnt[1 + P + q], (uint32_t)__popc(me));
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < NC) {
+      ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + t] = s_cnt[threadIdx.x];
+      s_cnt[threadIdx.x] = 0u;
+    }
+    __syncthreads();
+  }
+  if (!last_block(ws.tickets + 1)) return;
+  spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, ntiles, NC, s_tot, s_w);
+  if (threadIdx.x == 0) {
+    bool ok = true;
+    if (h->reserved[0] != 0) {
+      h->status = h->reserved[0];
+      ok = false;
+    }
+    const uint32_t fnext = s_tot[0];
+    if (ok && layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
+    gs_span fs = slab_alloc(h, ws.slab_cap, fnext, ok);
+    int64_t edges = 0;
+    for (int q = 0; q < P && ok; q++) {
+      h->field[layer][q][GS_F_IN_NODES] = slab_alloc(h, ws.slab_cap, s_tot[1 + q], ok);
+      h->field[layer][q][GS_F_CSR_INDICES] = slab_alloc(h, ws.slab_cap, s_tot[1 + P + q], ok);
+      ws.rowscan[(size_t)F * P + q] = s_tot[1 + P + q];
+      edges += s_tot[1 + P + q];
+    }
+    if (ok) {
+      h->frontier[layer + 1] = fs;
+      h->frontier_len[layer + 1] = (int32_t)fnext;
+      h->edges += edges;
+    } else if (h->status == 0) {
+      h->status = (int32_t)GS_ERR_OVERFLOW;
+    }
+  }
+}
+
+// ------------------------------------------------------------- k_cand_apply
+// Second pass over the candidate stream: turn the class flags into ranks
+// (tile prefix from the spine + in-tile ballot ranks, all in position order)
+// and scatter:  next frontier, in_nodes_g, the edge sources of part g in CSR
+// order (ids for now; k_relabel turns them into in_nodes positions), and for
+// every row's self entry the number of part-g edges emitted before the row
+// (rowscan), which is both the CSR row pointer and the row's edge count.
+// First-occurrence winners overwrite their table entry's x with the node's
+// rank in in_nodes_g -- the relabel map (DuplicateRemover::mask, duplicate.cpp:21).
+__global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_wcnt[GS_NW][GS_NC_MAX];
+  __shared__ uint32_t s_wpre[GS_NW][GS_NC_MAX];
+  __shared__ uint32_t s_run[GS_NC_MAX];
+  __shared__ uint32_t s_tot[GS_NC_MAX];
+  __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
+  const int P = ws.P, NC = 2 * P + 1;
+  const uint32_t C = (uint32_t)h->cand_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  int32_t *fnext = ws.slab + h->frontier[layer + 1].off;
+  const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
+  if (threadIdx.x < P) {
+    s_in_off[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
+    s_ix_off[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
+  }
+  const int lane = lane_id(), w = warp_id();
+  const uint32_t ltm = lt_mask();
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x < NC) s_run[threadIdx.x] = ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + t];
+#pragma unroll 1
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      uint32_t f = 0u;
+      int32_t c = 0;
+      bool live = p < C;
+      if (live) {
+        f = ws.cflag[p];
+        c = ws.cand[p];
+      }
+      const bool isself = live && (f & GS_CF_SELF);
+      const bool edge = live && !(f & (GS_CF_SELF | GS_CF_LOOP));
+      const bool ffirst = live && (f & GS_CF_FFIRST);
+      const bool ifirst = live && (f & GS_CF_IFIRST);
+      const int g = (int)(f >> GS_CF_PART_SHIFT);
+      // in-warp ranks
+      const uint32_t mf = __ballot_sync(FULL, ffirst);
+      const uint32_t rf = __popc(mf & ltm);
+      if (lane == 0) s_wcnt[w][0] = __popc(mf);
+      uint32_t ri = 0u, re_own = 0u;
+      uint32_t re[GS_MAX_PARTS];
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++) {
+        re[q] = 0u;
+        if (q < P) {
+          const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
+          const uint32_t me = __ballot_sync(FULL, edge && g == q);
+          if (g == q) ri = __popc(mi & ltm);
+          re[q] = __popc(me & ltm);
+          if (g == q) re_own = re[q];
+          if (lane == 0) {
+            s_wcnt[w][1 + q] = __popc(mi);
+            s_wcnt[w][1 + P + q] = __popc(me);
+          }
+        }
+      }
+      __syncthreads();
+      // exclusive prefix over the CTA's warps, per class
+      if (threadIdx.x < NC * GS_NW) {
+        const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
+        uint32_t a = 0u;
+        for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
+        s_wpre[ww][cc] = a;
+        if (ww == GS_NW - 1) s_tot[cc] = a + s_wcnt[ww][cc];
+      }
+      __syncthreads();
+      if (live) {
+        const int32_t v = isself ? front[c] : c;
+        if (ffirst) fnext[s_run[0] + s_wpre[w][0] + rf] = v;
+        if (ifirst) {
+          const uint32_t r = s_run[1 + g] + s_wpre[w][1 + g] + ri;
+          ws.slab[s_in_off[g] + r] = v;
+          ws.table[v].x = r;
+        }
+        if (edge) ws.slab[s_ix_off[g] + s_run[1 + P + g] + s_wpre[w][1 + P + g] + re_own] = v;
+        if (isself) {
+#pragma unroll
+          for (int q = 0; q < GS_MAX_PARTS; q++)
+            if (q < P)
+              ws.rowscan[(size_t)c * P + q] = s_run[1 + P + q] + s_wpre[w][1 + P + q] + re[q];
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < NC) s_run[threadIdx.x] += s_tot[threadIdx.x];
+      __syncthreads();
+    }
+  }
+}
+
+// ------------------------------------------------------------ k_front_count
+// Row-side classes.  Row i (node nd, owner g0) with has_g = "emitted >= 1 edge
+// into part g":  out_g = has_g (bipartite.h:59-62); owned_g = has_g && g == g0
+// (bipartite.h:56-58); to_g0 = any has_h, h != g0 (slicer.cpp:41);
+// self_g0 = always (slicer.cpp:33-34).  from_g = out_g && g != g0 needs no
+// counter: its rank is rank(out_g) - rank(owned_g).
+__device__ __forceinline__ uint32_t row_has_mask(const GsWs &ws, int i, int P) {
+  uint32_t m = 0u;
+  for (int q = 0; q < P; q++)
+    if (ws.rowscan[(size_t)(i + 1) * P + q] != ws.rowscan[(size_t)i * P + q]) m |= 1u << q;
+  return m;
+}
+
+__global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_cnt[GS_NF_MAX];
+  __shared__ uint32_t s_tot[GS_NF_MAX];
+  __shared__ uint32_t s_w[GS_NW + 1];
+  const int P = ws.P, NF = 4 * P;
+  const int F = h->frontier_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  if (threadIdx.x < GS_NF_MAX) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+#pragma unroll 1
+    for (int it = 0; it < GS_IPT; it++) {
+      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
+      uint32_t has = 0u;
+      int g0 = -1;
+      if (i < F) {
+        g0 = owner_of(ws, front[i]);
+        has = row_has_mask(ws, i, P);
+      }
+      const bool to = g0 >= 0 && (has & ~(1u << g0)) != 0u;
+      for (int q = 0; q < P; q++) {
+        const bool hq = (has >> q) & 1u;
+        const uint32_t m_out = __ballot_sync(FULL, hq);
+        const uint32_t m_own = __ballot_sync(FULL, hq && g0 == q);
+        const uint32_t m_to = __ballot_sync(FULL, to && g0 == q);
+        const uint32_t m_self = __ballot_sync(FULL, g0 == q);
+        if (lane_id() == 0) {
+          if (m_out) atomicAdd(&s_cnt[q], (uint32_t)__popc(m_out));
+          if (m_own) atomicAdd(&s_cnt[P + q], (uint32_t)__popc(m_own));
+          if (m_to) atomicAdd(&s_cnt[2 * P + q], (uint32_t)__popc(m_to));
+          if (m_self) atomicAdd(&s_cnt[3 * P + q], (uint32_t)__popc(m_self));
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < NF) {
+      ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + t] = s_cnt[threadIdx.x];
+      s_cnt[threadIdx.x] = 0u;
+    }
+    __syncthreads();
+  }
+  if (!last_block(ws.tickets + 2)) return;
+  spine_scan<GS_NF_MAX>(ws.ftile_cnt, ws.ftiles_max, ntiles, NF, s_tot, s_w);
+  if (threadIdx.x == 0) {
+    bool ok = true;
+    for (int q = 0; q < P && ok; q++) {
+      const uint32_t n_out = s_tot[q], n_own = s_tot[P + q], n_to = s_tot[2 * P + q],
+                     n_self = s_tot[3 * P + q];
+      gs_span *fl = h->field[layer][q];
+      fl[GS_F_OUT_NODES] = slab_alloc(h, ws.slab_cap, n_out, ok);
+      fl[GS_F_CSR_INDPTR] = slab_alloc(h, ws.slab_cap, n_out + 1u, ok);
+      fl[GS_F_OWNED_OUT] = slab_alloc(h, ws.slab_cap, n_own, ok);
+      fl[GS_F_FROM_IDS] = slab_alloc(h, ws.slab_cap, n_out - n_own, ok);
+      fl[GS_F_TO_IDS] = slab_alloc(h, ws.slab_cap, n_to, ok);
+      fl[GS_F_SELF_IN] = slab_alloc(h, ws.slab_cap, n_self, ok);
+      fl[GS_F_SELF_OUT] = slab_alloc(h, ws.slab_cap, n_self, ok);
+      if (ok) ws.slab[fl[GS_F_CSR_INDPTR].off + n_out] = fl[GS_F_CSR_INDICES].len;
+    }
+    if (!ok) h->status = (int32_t)GS_ERR_OVERFLOW;
+  }
+}
+
+// ------------------------------------------------------------ k_front_apply
+__global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_wcnt[GS_NW][GS_NF_MAX];
+  __shared__ uint32_t s_wpre[GS_NW][GS_NF_MAX];
+  __shared__ uint32_t s_run[GS_NF_MAX];
+  __shared__ uint32_t s_tot[GS_NF_MAX];
+  __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
+  const int P = ws.P, NF = 4 * P;
+  const int F = h->frontier_len[layer];
+  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  if (threadIdx.x < P * GS_NUM_FIELDS)
+    s_off[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
+        h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
+  const int lane = lane_id(), w = warp_id();
+  const uint32_t ltm = lt_mask();
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x < NF) s_run[threadIdx.x] = ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + t];
+#pragma unroll 1
+    for (int it = 0; it < GS_IPT; it++) {
+      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
+      uint32_t has = 0u;
+      int g0 = -1;
+      int32_t nd = 0;
+      if (i < F) {
+        nd = front[i];
+        g0 = owner_of(ws, nd);
+        has = row_has_mask(ws, i, P);
+      }
+      const bool to = g0 >= 0 && (has & ~(1u << g0)) != 0u;
+      uint32_t r_out[GS_MAX_PARTS], r_own[GS_MAX_PARTS];
+      uint32_t r_to = 0u, r_self = 0u;
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++) {
+        r_out[q] = 0u;
+        r_own[q] = 0u;
+        if (q < P) {
+          const bool hq = (has >> q) & 1u;
+          const uint32_t m_out = __ballot_sync(FULL, hq);
+          const uint32_t m_own = __ballot_sync(FULL, hq && g0 == q);
+          const uint32_t m_to = __ballot_sync(FULL, to && g0 == q);
+          const uint32_t m_self = __ballot_sync(FULL, g0 == q);
+          r_out[q] = __popc(m_out & ltm);
+          r_own[q] = __popc(m_own & ltm);
+          if (g0 == q) {
+            r_to = __popc(m_to & ltm);
+            r_self = __popc(m_self & ltm);
+          }
+          if (lane == 0) {
+            s_wcnt[w][q] = __popc(m_out);
+            s_wcnt[w][P + q] = __popc(m_own);
+            s_wcnt[w][2 * P + q] = __popc(m_to);
+            s_wcnt[w][3 * P + q] = __popc(m_self);
+          }
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < NF * GS_NW) {
+        const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
+        uint32_t a = 0u;
+        for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
+        s_wpre[ww][cc] = a;
+        if (ww == GS_NW - 1) s_tot[cc] = a + s_wcnt[ww][cc];
+      }
+      __syncthreads();
+      if (i < F) {
+        int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+#pragma unroll
+        for (int q = 0; q < GS_MAX_PARTS; q++) {
+          if (q < P && ((has >> q) & 1u)) {
+            const uint32_t op = s_run[q] + s_wpre[w][q] + r_out[q];
+            const uint32_t ow = s_run[P + q] + s_wpre[w][P + q] + r_own[q];
+            ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd;
+            ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * P + q];
+            if (q == g0) {
+              ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+              op_own = (int32_t)op;
+            } else {
+              ws.slab[s_off[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+            }
+          }
+        }
+        if (to) ws.slab[s_off[g0][GS_F_TO_IDS] + s_run[2 * P + g0] + s_wpre[w][2 * P + g0] + r_to] = op_own;
+        const uint32_t sp = s_run[3 * P + g0] + s_wpre[w][3 * P + g0] + r_self;
+        const uint32_t x = ws.table[nd].x;  // rank in in_nodes_g0, or INF: never an edge source
+        ws.slab[s_off[g0][GS_F_SELF_IN] + sp] = x == GS_INF ? -1 : (int32_t)x;
+        ws.slab[s_off[g0][GS_F_SELF_OUT] + sp] = op_own;
+      }
+      __syncthreads();
+      if (threadIdx.x < NF) s_run[threadIdx.x] += s_tot[threadIdx.x];
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------- k_relabel
+// csr_indices: edge-source ids -> positions in in_nodes_g through the table
+// (DuplicateRemover::replace, duplicate.cpp:35-39 -- what bipartite.cpp:5
+// would do if `indices` were ever filled).
+__global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  const int P = ws.P;
+  for (int q = 0; q < P; q++) {
+    const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
+    int32_t *ix = ws.slab + sp.off;
+    for (int e = blockIdx.x * GS_TPB + threadIdx.x; e < sp.len; e += gridDim.x * GS_TPB)
+      ix[e] = (int32_t)ws.table[ix[e]].x;
+  }
+}
+
+// ----------------------------------------------------------------- k_finish
+// Sparse reset of the table (DuplicateRemover::clear, duplicate.cpp:28-33: only
+// touched entries -- every node touched in any layer is in the last frontier),
+// then the sample header and, when asked, the used part of the slab are
+// mirrored to pinned host memory with 16-byte stores.
+__global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
+  gs_sample_header *h = ws.hdr;
+  const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
+  if (h->status == 0) {
+    const int L = ws.L;
+    const int32_t *fl = ws.slab + h->frontier[L].off;
+    const int FL = h->frontier_len[L];
+    for (int i = tid; i < FL; i += nth) ws.table[fl[i]] = make_uint2(GS_INF, GS_INF);
+  }
+  {
+    const int nw = (int)(sizeof(gs_sample_header) / 4);
+    const int32_t *src = (const int32_t *)h;
+    int32_t *dst = (int32_t *)ws.hdr_host;
+    for (int i = tid; i < nw; i += nth) dst[i] = src[i];
+  }
+  if (ws.input->want_host && ws.slab_host && h->status == 0) {
+    const int64_t n4 = h->slab_used >> 2;  // spans are 4-element aligned
+    const int4 *src = (const int4 *)ws.slab;
+    int4 *dst = (int4 *)ws.slab_host;
+    for (int64_t i = tid; i < n4; i += nth) dst[i] = src[i];
+  }
+}
+
+__global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+__global__ void k_narrow_ids(const int64_t *src, int32_t *dst, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = (int32_t)src[i];
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- launchers
+void gs_launch_begin(const GsWs &ws, cudaStream_t st) { k_begin<<<1, 1024, 0, st>>>(ws); }
+void gs_launch_rows_count(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_rows_count<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_rows_scan(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_rows_scan<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_expand(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_expand<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_cand_flags(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_cand_flags<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_cand_apply(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_cand_apply<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_front_count(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_front_count<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_front_apply(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_front_apply<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_relabel(const GsWs &ws, int layer, int grid, cudaStream_t st) {
+  k_relabel<<<grid, GS_TPB, 0, st>>>(ws, layer);
+}
+void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st) {
+  k_finish<<<grid, GS_TPB, 0, st>>>(ws);
+}
+void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
+  k_fill_u32<<<1184, 256, 0, st>>>(p, n, v);
+}
+void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st) {
+  k_narrow_ids<<<1184, 256, 0, st>>>(src, dst, n);
+}

@@ -1,0 +1,279 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI
+(cslicer.engine -> libgsplit_slicer.so), against
+  * the golden vectors produced by the unmodified reference (replay of its
+    mt19937 draw stream: bit-exact on every field the reference fills),
+  * the CPU oracle on the same seeded inputs (bit-exact incl. the repaired CSR)
+    across layers / parts / fanouts / owner maps,
+  * size-independent properties at BASELINE.json's full products shape.
+Integer work: the bar is bit-exact everywhere."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import refstream
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+META = json.load(open(os.path.join(GOLD, "golden.json")))
+
+
+def _engine():
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from cslicer import engine
+    return engine
+
+
+def _compare(view, orc):
+    from __graft_entry__ import compare_sample
+    compare_sample(view, orc)
+
+
+@pytest.mark.parametrize("name", sorted(META))
+def test_replay_matches_reference_golden(name):
+    """Same seed-derived edge choices on both sides -> bit-exact Bipartites
+    (north_star).  The draw stream is std::mt19937(5489), state carried over
+    batches exactly as one reference Slicer carries it."""
+    E = _engine()
+    z = np.load(os.path.join(GOLD, f"{name}.npz"))
+    m = META[name]
+    batches = O.cut_batches(z["perm"], m["minibatch"])
+    g = E.Graph(z["indptr"], z["indices"])
+    sl = E.Slicer(g, [10, 10, 10], 4, max_batch=m["minibatch"], num_slots=3, num_streams=3,
+                  draws=O.mt19937_stream(400000))
+    got = []
+    for i, b in enumerate(batches):
+        v = sl.slice(b, i)
+        got.append(refstream.digest_view(v))
+        v.release()
+    assert got == m["sha256"]
+    sl.close()
+    g.close()
+
+
+def test_config1_two_layers_is_prefix_of_reference_three_layers():
+    """BASELINE config 1 (2 layers, fanout [10,10], 4 parts): the reference can
+    only run 3 layers; its first two layers are the 2-layer answer."""
+    E = _engine()
+    z = np.load(os.path.join(GOLD, "mixed.npz"))
+    batches = O.cut_batches(z["perm"], 256)
+    g = E.Graph(z["indptr"], z["indices"])
+    orc = O.OracleSlicer(z["indptr"], z["indices"], [10, 10, 10], 4, O.RNG_PHILOX, seed=9)
+    sl = E.Slicer(g, [10, 10], 4, max_batch=256, num_slots=2, seed=9)
+    for i, b in enumerate(batches[:3]):
+        v = sl.slice(b, i)
+        assert refstream.digest_view(v) == refstream.digest_oracle(orc.slice(b, i), layers=2)
+        v.release()
+    sl.close()
+    g.close()
+
+
+CASES = [
+    # (fanouts, parts, owner, batch, graph)
+    ([10, 10, 10], 4, "mod", 256, "tiny"),
+    ([15, 10, 5], 8, "mod", 512, "small"),
+    ([15, 10, 5], 1, "mod", 300, "small"),
+    ([15, 10, 5], 2, "range", 300, "small"),
+    ([25, 10], 4, "range", 1024, "small"),
+    ([-1, -1], 4, "mod", 128, "small"),
+    ([-1, 5, -1], 3, "random", 64, "tiny"),
+    ([1], 8, "random", 1000, "tiny"),
+    ([3, 3, 3, 3, 3], 5, "mod", 17, "tiny"),
+]
+
+
+@pytest.mark.parametrize("fanouts,P,owner,batch,shape", CASES)
+def test_philox_matches_oracle(fanouts, P, owner, batch, shape):
+    E = _engine()
+    from cslicer.synth import owner_range, synth_graph
+    ip, ix = synth_graph(shape, seed=21)
+    n = ip.size - 1
+    own = None
+    if owner == "range":
+        own = owner_range(n, P)
+    elif owner == "random":
+        own = np.random.default_rng(4).integers(0, P, n).astype(np.int32)
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fanouts, P, max_batch=batch, num_slots=4, num_streams=4, seed=77, owner=own)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX, seed=77, owner=own)
+    rng = np.random.default_rng(8)
+    pending = []
+    for b in range(6):  # keep several minibatches in flight on different streams
+        seeds = rng.permutation(n)[:batch if b != 5 else max(1, batch // 3)]  # ragged last batch
+        pending.append((sl.submit(seeds, b), seeds, b))
+        if len(pending) == 4:
+            slot, s, bi = pending.pop(0)
+            v = sl.wait(slot)
+            _compare(v, orc.slice(s, bi))
+            v.release()
+    for slot, s, bi in pending:
+        v = sl.wait(slot)
+        _compare(v, orc.slice(s, bi))
+        v.release()
+    sl.close()
+    g.close()
+
+
+def test_graph_and_eager_paths_agree_and_device_views_match_host():
+    E = _engine()
+    import torch
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=5)
+    g = E.Graph(ip, ix)
+    a = E.Slicer(g, [15, 10, 5], 4, max_batch=512, num_slots=2, seed=3, use_graph=True)
+    b = E.Slicer(g, [15, 10, 5], 4, max_batch=512, num_slots=2, seed=3, use_graph=False)
+    seeds = np.random.default_rng(0).permutation(ip.size - 1)[:512]
+    va, vb = a.slice(seeds, 0), b.slice(seeds, 0)
+    assert refstream.digest_view(va) == refstream.digest_view(vb)
+    for l in range(3):
+        for p in range(4):
+            for name in ("in_nodes", "csr_indices", "to_ids"):
+                assert np.array_equal(va.tensor(l, p, name).cpu().numpy(), va.numpy(l, p, name))
+    assert torch.equal(va.frontier_tensor(3).cpu(), torch.from_numpy(va.frontier_numpy(3).copy()))
+    prof = b.profile(seeds, 0) if False else None  # slot 0 of b is still held by vb
+    va.release(); vb.release()
+    prof = b.profile(seeds, 0)
+    assert len(prof) == b.launches_per_sample and all(ms >= 0 for _, ms in prof)
+    a.close(); b.close(); g.close()
+
+
+def test_edge_cases_empty_isolated_and_errors():
+    E = _engine()
+    from cslicer import _native as N
+    # 6 nodes: 0->1,2 ; 1->0 ; 2 isolated-out ; 3 self-contained pair with 4 ; 5 isolated
+    ip = np.array([0, 2, 3, 3, 4, 5, 5], np.int64)
+    ix = np.array([1, 2, 0, 4, 3], np.int64)
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, [-1, -1], 2, max_batch=6, num_slots=2)
+    orc = O.OracleSlicer(ip, ix, [-1, -1], 2, O.RNG_PHILOX)
+    for seeds in ([5], [2, 5], [0, 1, 2, 3, 4, 5], [3], []):
+        v = sl.slice(np.array(seeds, np.int64), 0)
+        _compare(v, orc.slice(np.array(seeds, np.int64), 0))
+        v.release()
+    with pytest.raises(N.SlicerError) as e:  # out of range
+        sl.slice(np.array([0, 6], np.int64), 0)
+    assert e.value.code == N.ERR_SEED
+    with pytest.raises(N.SlicerError) as e:  # duplicate seed
+        sl.slice(np.array([1, 1], np.int64), 0)
+    assert e.value.code == N.ERR_SEED
+    with pytest.raises(N.SlicerError) as e:  # batch too large
+        sl.slice(np.arange(6).repeat(2), 0)
+    assert e.value.code == N.ERR_INVALID
+    v = sl.slice(np.array([0, 3], np.int64), 1)  # slicer still healthy after errors
+    _compare(v, orc.slice(np.array([0, 3], np.int64), 1))
+    v.release()
+    s1, s2 = sl.submit([0], 0), sl.submit([1], 1)
+    with pytest.raises(N.SlicerError) as e:
+        sl.submit([2], 2)
+    assert e.value.code == N.ERR_BUSY
+    sl.release(s1); sl.release(s2)
+    # workspace overflow is reported, and the slot recovers
+    ip2, ix2 = __import__("cslicer.synth", fromlist=["x"]).synth_graph("tiny", seed=1)
+    g2 = E.Graph(ip2, ix2)
+    small = E.Slicer(g2, [10, 10], 4, max_batch=64, num_slots=1, cand_capacity=100)
+    with pytest.raises(N.SlicerError) as e:
+        small.slice(np.arange(64), 0)
+    assert e.value.code == N.ERR_OVERFLOW
+    orc2 = O.OracleSlicer(ip2, ix2, [10, 10], 4, O.RNG_PHILOX)
+    v = small.slice(np.arange(3), 0)
+    _compare(v, orc2.slice(np.arange(3), 0))
+    v.release()
+    small.close(); g2.close(); sl.close(); g.close()
+
+
+def test_statistical_equivalence_of_native_sampling():
+    """Philox picks vs the reference's mt19937 picks: both uniform over a row's
+    neighbours with replacement (slicer.cpp:15-20).  Chi-square on a hub row."""
+    E = _engine()
+    deg = 40
+    ip = np.array([0, deg] + [deg] * deg, np.int64)
+    ix = np.arange(1, deg + 1, dtype=np.int64)
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, [10], 1, max_batch=1, num_slots=2, seed=123)
+    counts = np.zeros(deg + 1)
+    trials = 4000
+    for b in range(trials):
+        v = sl.slice([0], b)
+        src = v.numpy(0, 0, "in_nodes")[v.numpy(0, 0, "csr_indices")]
+        assert src.size == 10
+        np.add.at(counts, src, 1)
+        v.release()
+    exp = trials * 10 / deg
+    chi2 = ((counts[1:] - exp) ** 2 / exp).sum()
+    assert counts[0] == 0 and chi2 < 80.0  # 39 dof: p(chi2 > 80) ~ 1e-4
+    sl.close(); g.close()
+
+
+def test_full_size_products_properties():
+    """BASELINE config 2 at full size (2.4 M nodes / ~62 M edges, [15,10,5],
+    batch 4096): properties that need no oracle run, plus an oracle check of one
+    minibatch (the sequential oracle takes a few seconds here)."""
+    E = _engine()
+    import torch
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("products", seed=1234, device="cuda")
+    n = ip.size - 1
+    g = E.Graph(ip, ix)
+    P = 4
+    sl = E.Slicer(g, [15, 10, 5], P, max_batch=4096, num_slots=2, seed=1)
+    seeds = np.random.default_rng(1).permutation(n)[:4096]
+    v = sl.slice(seeds, 0)
+    deg = np.diff(ip)
+    tot = 0
+    for l in range(3):
+        fr, nx = v.frontier_numpy(l), v.frontier_numpy(l + 1)
+        assert np.unique(nx).size == nx.size and set(fr.tolist()) <= set(nx.tolist())
+        fan = [15, 10, 5][l]
+        want_edges = np.minimum(deg[fr], np.where(deg[fr] >= fan, fan, deg[fr])).sum()
+        got = 0
+        union_in = []
+        for p in range(P):
+            ins, outs = v.numpy(l, p, "in_nodes"), v.numpy(l, p, "out_nodes")
+            cp, ci = v.numpy(l, p, "csr_indptr"), v.numpy(l, p, "csr_indices")
+            assert (ins % P == p).all() and np.unique(ins).size == ins.size
+            assert cp[0] == 0 and cp[-1] == ci.size and (np.diff(cp) > 0).all()
+            assert ci.min() >= 0 and ci.max() < ins.size
+            own, frm = v.numpy(l, p, "owned_out_nodes"), v.numpy(l, p, "from_ids")
+            assert (outs[own] % P == p).all() and (outs[frm] % P != p).all()
+            assert own.size + frm.size == outs.size
+            si, so = v.numpy(l, p, "self_ids_in"), v.numpy(l, p, "self_ids_out")
+            assert si.size == (fr % P == p).sum() == so.size
+            ok = so >= 0
+            assert np.array_equal(outs[so[ok]], fr[fr % P == p][ok])
+            got += ci.size
+            union_in.append(ins)
+        assert got == want_edges  # every sampled edge lands in exactly one part
+        assert set(np.concatenate(union_in).tolist()) | set(fr.tolist()) == set(nx.tolist())
+        tot += got
+    assert tot == v.edges
+    orc = O.OracleSlicer(ip, ix, [15, 10, 5], P, O.RNG_PHILOX, seed=1)
+    _compare(v, orc.slice(seeds, 0))
+    v.release()
+    sl.close(); g.close()
+    torch.cuda.empty_cache()
+
+
+def test_reference_facing_module_end_to_end(tmp_path):
+    """cslicer/test_py.py's loop, verbatim in shape, against the golden hashes:
+    the module's own epoch shuffle + replayed draws reproduce the reference's
+    whole sample stream through the reference-named attributes only."""
+    import cslicer as M
+    z = np.load(os.path.join(GOLD, "hubs.npz"))
+    m = META["hubs"]
+    M.write_dataset(str(tmp_path / "hubs"), z["indptr"], z["indices"])
+    csl = M.cslicer("hubs", 16, 32, 1, m["minibatch"], root=str(tmp_path),
+                    draws=O.mt19937_stream(400000))
+    ns = csl.getNoSamples()
+    assert ns == len(m["sha256"])
+    got = []
+    for i in range(ns):
+        s = csl.getSample()
+        got.append(refstream.digest_module_sample(s))
+    assert got == m["sha256"]
+    with pytest.raises(RuntimeError):
+        csl.getSample()
+    csl.close()
