@@ -1,0 +1,424 @@
+#!/usr/bin/env python
+"""bench.py -- sliced minibatches/s of the cslicer hot path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): ogbn-products-shaped synthetic graph
+(2,449,029 nodes, ~61.9 M edges, seed 1234), 3 layers, fanout [15,10,5], batch
+4096, split into `--parts` bipartites per layer (default 4, the reference's
+value).  One step = `--mb-per-step` minibatches pushed through the slicer's slot
+pipeline.  Whole minibatches are the sharding unit: at N > 1 every rank holds a
+replica of the graph topology (0.3 GB of a 180 GB HBM) and slices its own
+minibatches, no collective on the data path -> "scaling": "weak".
+
+own arm      : CUDA slicer through the C ABI (cslicer.engine).
+                 value = results left in HBM (header only to the host);
+                 e2e   = host seeds in, every Bipartite list mirrored to pinned
+                         host memory inside the timed region.
+--impl reference : the reference algorithm on the host cores (multithreaded CPU
+                 restatement, one slicer per thread as WorkerPool.cpp:29-33; the
+                 compiled reference itself cannot express fanout [15,10,5]).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "occ-gnn_b200"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+FANOUTS = [15, 10, 5]
+BATCH = 4096
+SHAPE = "products"
+GRAPH_SEED = 1234
+CACHE = os.path.join(ROOT, ".bench_cache")
+HEADER_BYTES = 4888  # sizeof(gs_sample_header); checked against the library in own_arm
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def load_graph(shape, device):
+    """Seeded synthetic CSR; cached on disk so the two arms share one graph."""
+    from cslicer.synth import synth_graph
+    os.makedirs(CACHE, exist_ok=True)
+    f = os.path.join(CACHE, f"{shape}_{GRAPH_SEED}_{device.split(':')[0]}.npz")
+    if os.path.exists(f):
+        try:
+            z = np.load(f)
+            return z["indptr"], z["indices"]
+        except Exception:
+            pass
+    t = time.time()
+    ip, ix = synth_graph(shape, seed=GRAPH_SEED, device=device)
+    log(f"[bench] generated {shape}: N={ip.size - 1} M={ix.size} in {time.time() - t:.1f}s on {device}")
+    if int(os.environ.get("RANK", "0")) == 0:
+        try:
+            tmp = f + f".tmp{os.getpid()}.npz"
+            np.savez(tmp, indptr=ip, indices=ix)
+            os.replace(tmp, f)
+        except Exception as e:  # cache is best effort
+            log("[bench] cache write failed:", e)
+    return ip, ix
+
+
+def seed_batches(num_nodes, count, rank, world):
+    """Reference behaviour (WorkerPool.cpp:40-49): a fixed permutation of all
+    nodes cut into batches; rank r takes batches r, r+world, ..."""
+    rng = np.random.default_rng(GRAPH_SEED + 1)
+    perm = rng.permutation(num_nodes).astype(np.int64)
+    per_epoch = num_nodes // BATCH
+    out = []
+    for i in range(count):
+        b = (rank + i * world) % per_epoch
+        out.append((b, perm[b * BATCH:(b + 1) * BATCH]))
+    return out
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(gpu_index)], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f:
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def run_pipeline(sl, batches, steps, mb_per_step, torch, timed=True):
+    """Push steps*mb_per_step minibatches through the slot pipeline.
+    -> (device ms between two CUDA events bracketing the region, wall s,
+        total edges, total slab int32 elements)."""
+    n = steps * mb_per_step
+    depth = sl.num_slots
+    inflight = []
+    edges = slab = 0
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(n):
+        if len(inflight) == depth:
+            slot = inflight.pop(0)
+            h = sl.wait_header(slot)
+            edges += h.edges
+            slab += h.slab_used
+            sl.release(slot)
+        bi, seeds = batches[i % len(batches)]
+        inflight.append(sl.submit(seeds, bi))
+    for slot in inflight:
+        h = sl.wait_header(slot)
+        edges += h.edges
+        slab += h.slab_used
+        sl.release(slot)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1), time.perf_counter() - t0, edges, slab
+
+
+def kernel_profile(sl, batches, reps=8):
+    """Eager runs with a CUDA event between launches (outside the timed region)
+    -> {kernel@layer: mean ms}, launch order preserved."""
+    acc, order = {}, []
+    for r in range(reps):
+        bi, seeds = batches[r % len(batches)]
+        layer, seen = -1, {}
+        for name, ms in sl.profile(seeds, bi):
+            if name == "rows_count":
+                layer += 1
+            key = name if name in ("begin", "finish") else f"{name}@{layer}"
+            if r == 0:
+                order.append(key)
+            acc[key] = acc.get(key, 0.0) + ms
+    return [(k, acc[k] / reps) for k in order]
+
+
+def kernel_bytes(view, P):
+    """Compulsory bytes of each kernel launch for one sample (own in/out, w=4)."""
+    out = {}
+    for l in range(view.num_layers):
+        F, Fn, C = view.frontier_len[l], view.frontier_len[l + 1], view.cand_len[l]
+        E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
+        n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
+        n_out = sum(view.field_len(l, g, "out_nodes") for g in range(P))
+        lists = sum(view.field_len(l, g, k) for g in range(P)
+                    for k in ("owned_out_nodes", "from_ids", "to_ids", "self_ids_in", "self_ids_out"))
+        out[f"rows_count@{l}"] = F * (4 + 16) + F * 12
+        out[f"rows_scan@{l}"] = F * 8 + F * (4 + 8 + 4 + 1)
+        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4 + 1 + 4)
+        out[f"cand_flags@{l}"] = C * (4 + 1 + 8) + C * 1
+        out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + n_in * 4 + F * P * 4
+        out[f"front_count@{l}"] = F * (4 + P * 4)
+        out[f"front_apply@{l}"] = F * (4 + P * 4 + 8) + (2 * n_out + lists) * 4
+        out[f"relabel@{l}"] = E * (4 + 8 + 4)
+    return out
+
+
+def own_arm(args):
+    import torch
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    import ctypes
+    from cslicer import _native
+    from cslicer.engine import Graph, Slicer
+    global HEADER_BYTES
+    HEADER_BYTES = ctypes.sizeof(_native.SampleHeader)
+    ip, ix = load_graph(args.shape, f"cuda:{local}")
+    n = ip.size - 1
+    g = Graph(ip, ix, device=local)
+    P, mbs = args.parts, args.mb_per_step
+    batches = seed_batches(n, max(64, mbs), rank, world)
+    kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7)
+    dev = Slicer(g, FANOUTS, host_output=False, **kw)
+    hst = Slicer(g, FANOUTS, host_output=True, **kw)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    # warm-up (>= 3 steps) for both modes
+    W = max(3, args.warmup)
+    run_pipeline(dev, batches, W, mbs, torch)
+    run_pipeline(hst, batches, W, mbs, torch)
+    # one sample for the byte model and sizes
+    v = hst.slice(batches[0][1], batches[0][0])
+    alg_bytes = v.algorithmic_bytes(owner_bytes=0, w=4)
+    kbytes = kernel_bytes(v, P)
+    sizes = dict(frontier=v.frontier_len, candidates=v.cand_len, edges=v.edges,
+                 slab_bytes=v.slab_used * 4)
+    v.release()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    clocks = ClockSampler(local) if rank == 0 else None
+    barrier()
+    ms_dev, wall_dev, edges_dev, _ = run_pipeline(dev, batches, args.steps, mbs, torch)
+    barrier()
+    ms_e2e, wall_e2e, edges_e2e, slab_e2e = run_pipeline(hst, batches, args.steps, mbs, torch)
+    barrier()
+    clk = clocks.stop() if clocks else None
+    if dist is not None:
+        t = torch.tensor([ms_dev, ms_e2e], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = float(t[0]), float(t[1])
+        c = torch.tensor([edges_dev, edges_e2e, slab_e2e], device=f"cuda:{local}", dtype=torch.int64)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        edges_dev, edges_e2e, slab_e2e = int(c[0]), int(c[1]), int(c[2])
+    total_mb = args.steps * mbs * world
+    value = total_mb / (ms_dev * 1e-3)
+    e2e = total_mb / (ms_e2e * 1e-3)
+
+    out = None
+    if rank == 0:
+        prof = kernel_profile(dev, batches)
+        chain_ms = sum(ms for _, ms in prof)
+        top, top_ms = max(prof, key=lambda kv: kv[1])
+        per_gpu_mb_s = value / world
+        achieved = alg_bytes * per_gpu_mb_s / 1e9  # GB/s of compulsory traffic, pipelined steady state
+        roof = {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "what": "algorithmic bytes of one minibatch (SURVEY 8(d), w=4) x minibatches/s per GPU, "
+                        "all 26 kernels of the chain, slots pipelined on streams",
+                "algorithmic_bytes_per_minibatch": int(alg_bytes),
+                "chain_ms_eager_single_stream": round(chain_ms, 4),
+                "chain_gbs_eager_single_stream": round(alg_bytes / (chain_ms * 1e-3) / 1e9, 2),
+                "dominant_kernel": {"name": top, "avg_ms": round(top_ms, 4),
+                                    "share_of_chain": round(top_ms / chain_ms, 3),
+                                    "algorithmic_bytes": int(kbytes.get(top, 0)),
+                                    "achieved_gbs": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9, 2),
+                                    "frac": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9 / peak, 4)},
+                "kernels_ms": {k: round(ms, 4) for k, ms in prof}}
+        out = {"metric": "sliced minibatches/s", "value": round(value, 2), "unit": "minibatches/s",
+               "n_gpus": world, "steps": args.steps, "warmup": W,
+               "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
+               "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+               "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
+                                      f"3-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
+                          "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
+                          "sharding": "whole minibatches per rank, graph topology replicated",
+                          "l2": "inputs larger than L2: graph 0.27 GB + per-slot tables/workspaces "
+                                f"{dev.slot_bytes * args.slots / 1e9:.2f} GB cycled every step",
+                          "sizes_of_one_minibatch": sizes},
+               "sampled_edges_per_s": round(edges_dev / (ms_dev * 1e-3), 1),
+               "e2e": {"value": round(e2e, 2), "unit": "minibatches/s",
+                       "h2d_bytes_per_step": mbs * (BATCH * 8 + 16),
+                       "d2h_bytes_per_step": int(slab_e2e * 4 / (args.steps * world)) + mbs * HEADER_BYTES,
+                       "ms_per_step": round(ms_e2e / args.steps, 4),
+                       "sampled_edges_per_s": round(edges_e2e / (ms_e2e * 1e-3), 1)},
+               "gpu_launches": dev.launches_per_sample * args.steps * mbs,
+               "wall_s": {"value_region": round(wall_dev, 4), "e2e_region": round(wall_e2e, 4)},
+               "clocks": clk, "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(ip, ix, P, batches, args)
+    dev.close()
+    hst.close()
+    g.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_port_rate(ip, ix, P, batches, workers, target_s):
+    """Multithreaded CPU restatement (oracle/, the checker) on a bounded sample:
+    one probe batch sizes the sample to about target_s seconds of work."""
+    from oracle import oracle as O
+    seeds = [b for _, b in batches]
+    t1, _ = O.pool_run(ip, ix, FANOUTS, P, seeds[:1], workers=1, rng_mode=O.RNG_PHILOX, seed=7)
+    nb = int(max(workers, min(len(seeds), target_s / max(t1, 1e-3) * workers * 0.7)))
+    nb = max(workers, (nb // workers) * workers)
+    sample = [seeds[i % len(seeds)] for i in range(nb)]
+    sec, edges = O.pool_run(ip, ix, FANOUTS, P, sample, workers=workers, rng_mode=O.RNG_PHILOX, seed=7)
+    return nb / sec, edges / sec, nb, sec
+
+
+def cpu_baseline(ip, ix, P, batches, args):
+    cores = host_cores()
+    rate, erate, nb, sec = cpu_port_rate(ip, ix, P, batches, cores, args.cpu_seconds)
+    return {"value": round(rate, 3), "unit": "minibatches/s", "cores": cores, "kind": "port",
+            "sample": f"{nb} minibatches of the same workload in {sec:.1f} s, {cores} threads "
+                      "(one restated slicer per thread, WorkerPool.cpp:29-33)",
+            "sampled_edges_per_s": round(erate, 1)}
+
+
+def reference_arm(args):
+    """--impl reference: the reference algorithm on the host cores, same config,
+    metric and unit.  The compiled reference (oracle/_ref) is fixed at 3 layers x
+    fanout 10 x 4 parts, so the exact config is timed with the multithreaded CPU
+    restatement ("port"); rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    dev = "cuda:0" if torch.cuda.is_available() else "cpu"
+    ip, ix = load_graph(args.shape, dev)
+    n = ip.size - 1
+    cores = host_cores()
+    batches = seed_batches(n, 256, 0, 1)
+    from oracle import oracle as O
+    seeds = [b for _, b in batches]
+    t1, _ = O.pool_run(ip, ix, FANOUTS, args.parts, seeds[:1], workers=1, rng_mode=O.RNG_PHILOX, seed=7)
+    # size a step so (steps + warmup) steps end within ~2 minutes
+    total_steps = args.steps + max(1, args.warmup)
+    per_step = int(max(cores, min(4 * cores, 120.0 / total_steps / max(t1, 1e-3) * cores * 0.7)))
+    per_step = max(cores, (per_step // cores) * cores)
+    k = 0
+
+    def step():
+        nonlocal k
+        sample = [seeds[(k + i) % len(seeds)] for i in range(per_step)]
+        k += per_step
+        return O.pool_run(ip, ix, FANOUTS, args.parts, sample, workers=cores,
+                          rng_mode=O.RNG_PHILOX, seed=7)
+    for _ in range(max(1, args.warmup)):
+        step()
+    sec = edges = 0.0
+    for _ in range(args.steps):
+        s_, e_ = step()
+        sec += s_
+        edges += e_
+    value = args.steps * per_step / sec
+    out = {"impl": "reference", "metric": "sliced minibatches/s", "value": round(value, 3),
+           "unit": "minibatches/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+           "steps": args.steps, "warmup": max(1, args.warmup),
+           "ms_per_step": round(sec / args.steps * 1e3, 2), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+           "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
+                                  f"3-layer fanout {FANOUTS}, batch {BATCH}, {args.parts} parts (owner=id%P)",
+                      "minibatches_per_step": per_step},
+           "sampled_edges_per_s": round(edges / sec, 1),
+           "cpu_baseline": {"value": round(value, 3), "unit": "minibatches/s", "cores": cores,
+                            "kind": "port",
+                            "sample": f"{per_step} minibatches per step, {cores} threads, one restated "
+                                      "slicer per thread (WorkerPool.cpp:29-33)"},
+           "e2e": {"value": round(value, 3), "unit": "minibatches/s", "h2d_bytes_per_step": 0,
+                   "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--shape", default=SHAPE)
+    ap.add_argument("--parts", type=int, default=4)
+    ap.add_argument("--mb-per-step", type=int, default=64)
+    ap.add_argument("--slots", type=int, default=8)
+    ap.add_argument("--streams", type=int, default=8)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        own_arm(args)
+
+
+if __name__ == "__main__":
+    main()
