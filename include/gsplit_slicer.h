@@ -101,7 +101,7 @@ typedef struct {
   int64_t frontier_capacity;       /* 0 = derive from fanouts */
   int64_t cand_capacity;           /* 0 = derive */
   int64_t slab_capacity;           /* 0 = derive (int32 elements) */
-  int32_t grid_ctas;               /* 0 = 2 x SM count */
+  int32_t grid_ctas;               /* CTAs per SM of a full-machine launch; 0 = 4 */
   int32_t use_graph;               /* 1 (default via gs_config_default): CUDA-graph replay */
 } gs_config;
 

@@ -61,7 +61,9 @@ struct gs_graph {
 struct gs_slicer {
   gs_graph *g = nullptr;
   gs_config cfg{};
-  int grid = 0;
+  int grid = 0;                       // CTAs of a full-machine launch
+  int grid_rows[GS_MAX_LAYERS] = {0};  // per layer: enough CTAs for the largest possible frontier
+  int grid_cand[GS_MAX_LAYERS] = {0};  // ... and candidate stream (static upper bounds)
   int64_t Fcap = 0, Ccap = 0, slab_cap = 0;
   uint8_t *owner = nullptr;
   uint32_t *draws = nullptr;
@@ -106,21 +108,22 @@ int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEven
   gs_launch_begin(sl.ws, st);
   if ((rc = mark("begin"))) return rc;
   for (int l = 0; l < s->cfg.num_layers; l++) {
-    gs_launch_rows_count(sl.ws, l, s->grid, st);
+    const int gr = s->grid_rows[l], gc = s->grid_cand[l];
+    gs_launch_rows_count(sl.ws, l, gr, st);
     if ((rc = mark(kNames[0]))) return rc;
-    gs_launch_rows_scan(sl.ws, l, s->grid, st);
+    gs_launch_rows_scan(sl.ws, l, gr, st);
     if ((rc = mark(kNames[1]))) return rc;
-    gs_launch_expand(sl.ws, l, s->grid, st);
+    gs_launch_expand(sl.ws, l, gc, st);
     if ((rc = mark(kNames[2]))) return rc;
-    gs_launch_cand_flags(sl.ws, l, s->grid, st);
+    gs_launch_cand_flags(sl.ws, l, gc, st);
     if ((rc = mark(kNames[3]))) return rc;
-    gs_launch_cand_apply(sl.ws, l, s->grid, st);
+    gs_launch_cand_apply(sl.ws, l, gc, st);
     if ((rc = mark(kNames[4]))) return rc;
-    gs_launch_front_count(sl.ws, l, s->grid, st);
+    gs_launch_front_count(sl.ws, l, gr, st);
     if ((rc = mark(kNames[5]))) return rc;
-    gs_launch_front_apply(sl.ws, l, s->grid, st);
+    gs_launch_front_apply(sl.ws, l, gr, st);
     if ((rc = mark(kNames[6]))) return rc;
-    gs_launch_relabel(sl.ws, l, s->grid, st);
+    gs_launch_relabel(sl.ws, l, gc, st);
     if ((rc = mark(kNames[7]))) return rc;
   }
   gs_launch_finish(sl.ws, s->grid, st);
@@ -141,7 +144,7 @@ int stage_input(gs_slicer *s, Slot &sl, const int64_t *seeds, int32_t n, uint64_
 }
 
 void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap, int64_t *Ccap,
-                        int64_t *slab) {
+                        int64_t *slab, int64_t *Fb, int64_t *Cb) {
   int64_t F = c.max_batch, fmax = F, cmax = 0, sl = F + 8;
   const int64_t P = c.num_parts;
   for (int l = 0; l < c.num_layers; l++) {
@@ -151,6 +154,8 @@ void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap,
     const int64_t E = fan >= 0 ? std::min(F * fan, M) : M;
     const int64_t C = F + E;
     cmax = std::max(cmax, C);
+    Fb[l] = F;
+    Cb[l] = C;
     sl += std::min(N, C) + std::min(N, E) + E + 3 * std::min(P * F, E) + P + 4 * F +
           4 * GS_NUM_FIELDS * P + 8;
     F = std::min(N, C);
@@ -285,7 +290,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   s->cfg.owner_host = nullptr;
   s->cfg.draws_host = nullptr;
   const int64_t N = g->num_nodes, M = g->num_edges;
-  compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap);
+  int64_t Fb[GS_MAX_LAYERS] = {0}, Cb[GS_MAX_LAYERS] = {0};
+  compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap, Fb, Cb);
   if (s->Ccap >= (1ll << 31) - 2 * GS_TILE || s->Fcap >= (1ll << 31) - 2 * GS_TILE ||
       s->slab_cap >= (1ll << 31) - 16) {
     delete s;
@@ -294,7 +300,15 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   }
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g->device);
-  s->grid = cfg->grid_ctas > 0 ? cfg->grid_ctas : 2 * sms;
+  // grid_ctas = CTAs per SM of a full-machine launch.  Sizes are only known on
+  // the device, so each launch gets the grid its layer's static upper bound
+  // needs, capped at the full-machine grid (tile loops stride over the rest).
+  s->grid = (cfg->grid_ctas > 0 ? cfg->grid_ctas : 4) * sms;
+  for (int l = 0; l < cfg->num_layers; l++) {
+    const int64_t fb = std::min(Fb[l], s->Fcap), cb = std::min(Cb[l], s->Ccap);
+    s->grid_rows[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (fb + GS_TILE - 1) / GS_TILE));
+    s->grid_cand[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (cb + GS_TILE - 1) / GS_TILE));
+  }
 
 #define CUS(call)                                                                        \
   do {                                                                                   \

@@ -103,21 +103,21 @@ __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
   return ws.owner ? (int)__ldg(ws.owner + v) : (int)((uint32_t)v % (uint32_t)ws.P);
 }
 
-// slab bump allocator (single thread).  16-byte aligned spans.
-__device__ __forceinline__ gs_span slab_alloc(gs_sample_header *h, int64_t cap, uint32_t len,
-                                              bool &ok) {
+// slab bump allocator (single thread).  16-byte aligned spans.  `used` is the
+// caller's register copy of gs_sample_header::slab_used: a layout of ~30 spans
+// must not pay a global round trip per span.
+__device__ __forceinline__ gs_span slab_alloc(int64_t &used, int64_t cap, uint32_t len, bool &ok) {
   gs_span s;
-  int64_t off = h->slab_used;
-  int64_t next = off + (((int64_t)len + 3) & ~3ll);
+  const int64_t next = used + (((int64_t)len + 3) & ~3ll);
   if (next > cap || next > 0x7FFFFFFFll) {
     ok = false;
     s.off = 0;
     s.len = 0;
     return s;
   }
-  h->slab_used = next;
-  s.off = (int32_t)off;
+  s.off = (int32_t)used;
   s.len = (int32_t)len;
+  used = next;
   return s;
 }
 
@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   __shared__ uint32_t s_off[GS_TILE + 2];
   const int F = h->frontier_len[layer];
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const uint32_t batch = (uint32_t)h->batch_index;
@@ -372,40 +372,67 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
     const int cnt = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
     for (int k = threadIdx.x; k <= cnt; k += GS_TPB) s_off[k] = ws.off[i_lo + k];
     __syncthreads();
+    // Three phases over the thread's GS_IPT candidates so that the row lookups,
+    // then the GS_IPT random neighbour gathers, are all in flight together.
+    uint32_t pos[GS_IPT];
+    int row[GS_IPT], slot[GS_IPT];
+    int32_t nd1[GS_IPT], deg[GS_IPT];
+    int64_t rs[GS_IPT];
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      pos[it] = p;
+      slot[it] = 0;
+      row[it] = 0;
       if (p < C) {
         int lo = 0, hi = cnt - 1;  // largest k with s_off[k] <= p
         while (lo < hi) {
           const int mid = (lo + hi + 1) >> 1;
           if (s_off[mid] <= p) lo = mid; else hi = mid - 1;
         }
-        const int j = (int)(p - s_off[lo]);
-        if (j > 0) {  // slot 0 (self) was planted by k_rows_scan
-          const int i = i_lo + lo;
-          const int32_t nd1 = front[i];
-          const int64_t rs = ws.rowstart[i];
-          const int32_t deg = ws.rowdeg[i];
-          int32_t pick = j - 1;
-          if (fan >= 0 && deg >= fan) {
-            uint32_t r;
-            if (replay) {
-              const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[i] + (uint32_t)(j - 1);
-              r = di < ws.n_draws ? ws.draws[di] : 0u;
-            } else {
-              r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1, j - 1);
-            }
-            pick = (int32_t)(r % (uint32_t)deg);
-          }
-          const int32_t v = __ldg(ws.indices + rs + pick);
-          ws.cand[p] = v;
-          if (v != nd1) {
-            ws.cflag[p] = 0;
-            atomicMin(&ws.table[v].x, p);
+        slot[it] = (int)(p - s_off[lo]);  // 0 = self entry, planted by k_rows_scan
+        row[it] = i_lo + lo;
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      if (slot[it] > 0) {
+        nd1[it] = front[row[it]];
+        rs[it] = ws.rowstart[row[it]];
+        deg[it] = ws.rowdeg[row[it]];
+      }
+    }
+    const int32_t *src[GS_IPT];
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      if (slot[it] > 0) {
+        int32_t pick = slot[it] - 1;
+        if (fan >= 0 && deg[it] >= fan) {
+          uint32_t r;
+          if (replay) {
+            const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row[it]] + (uint32_t)(slot[it] - 1);
+            r = di < ws.n_draws ? ws.draws[di] : 0u;
           } else {
-            ws.cflag[p] = (uint8_t)GS_CF_LOOP;
+            r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1[it], slot[it] - 1);
           }
+          pick = (int32_t)(r % (uint32_t)deg[it]);
+        }
+        src[it] = ws.indices + rs[it] + pick;
+      }
+    }
+    int32_t v[GS_IPT];
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++)
+      if (slot[it] > 0) v[it] = __ldg(src[it]);
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      if (slot[it] > 0) {
+        ws.cand[pos[it]] = v[it];
+        if (v[it] != nd1[it]) {
+          ws.cflag[pos[it]] = 0;
+          atomicMin(&ws.table[v[it]].x, pos[it]);
+        } else {
+          ws.cflag[pos[it]] = (uint8_t)GS_CF_LOOP;
         }
       }
     }
@@ -433,25 +460,47 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    // phased so the GS_IPT random table reads of a thread are in flight together
+    uint32_t fl[GS_IPT];
+    int32_t cv[GS_IPT];
+    uint2 te[GS_IPT];
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      fl[it] = 0u;
+      cv[it] = 0;
+      if (p < C) {
+        fl[it] = ws.cflag[p];
+        cv[it] = ws.cand[p];
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      if (p < C && (fl[it] & GS_CF_SELF)) cv[it] = front[cv[it]];
+    }
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
+      te[it] = make_uint2(0u, 0u);
+      if (p < C) te[it] = ws.table[cv[it]];
+    }
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
       bool ffirst = false, ifirst = false, edge = false;
       int g = 0;
       if (p < C) {
-        uint32_t f = ws.cflag[p];
-        const int32_t c = ws.cand[p];
-        const bool isself = (f & GS_CF_SELF) != 0u;
-        const int32_t v = isself ? front[c] : c;
-        const uint2 e = ws.table[v];
-        if (isself) {
+        uint32_t f = fl[it];
+        const uint2 e = te[it];
+        if (f & GS_CF_SELF) {
           ffirst = e.x > p;
           if (e.y != p) h->reserved[0] = (int32_t)GS_ERR_SEED;  // duplicate seed
         } else if (!(f & GS_CF_LOOP)) {
           edge = true;
           ifirst = e.x == p;
           ffirst = ifirst && e.y > p;
-          g = owner_of(ws, v);
+          g = owner_of(ws, cv[it]);
         }
         f = (f & (GS_CF_SELF | GS_CF_LOOP)) | (ffirst ? GS_CF_FFIRST : 0u) |
             (ifirst ? GS_CF_IFIRST : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
@@ -485,15 +534,17 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     }
     const uint32_t fnext = s_tot[0];
     if (ok && layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
-    gs_span fs = slab_alloc(h, ws.slab_cap, fnext, ok);
+    int64_t used = h->slab_used;
+    gs_span fs = slab_alloc(used, ws.slab_cap, fnext, ok);
     int64_t edges = 0;
     for (int q = 0; q < P && ok; q++) {
-      h->field[layer][q][GS_F_IN_NODES] = slab_alloc(h, ws.slab_cap, s_tot[1 + q], ok);
-      h->field[layer][q][GS_F_CSR_INDICES] = slab_alloc(h, ws.slab_cap, s_tot[1 + P + q], ok);
+      h->field[layer][q][GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, s_tot[1 + q], ok);
+      h->field[layer][q][GS_F_CSR_INDICES] = slab_alloc(used, ws.slab_cap, s_tot[1 + P + q], ok);
       ws.rowscan[(size_t)F * P + q] = s_tot[1 + P + q];
       edges += s_tot[1 + P + q];
     }
     if (ok) {
+      h->slab_used = used;
       h->frontier[layer + 1] = fs;
       h->frontier_len[layer + 1] = (int32_t)fnext;
       h->edges += edges;
@@ -516,13 +567,11 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ uint32_t s_wcnt[GS_NW][GS_NC_MAX];
-  __shared__ uint32_t s_wpre[GS_NW][GS_NC_MAX];
-  __shared__ uint32_t s_run[GS_NC_MAX];
-  __shared__ uint32_t s_tot[GS_NC_MAX];
+  __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // tile prefix + earlier warps of the tile
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
   const int P = ws.P, NC = 2 * P + 1;
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
   int32_t *fnext = ws.slab + h->frontier[layer + 1].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   if (threadIdx.x < P) {
@@ -531,74 +580,93 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   }
   const int lane = lane_id(), w = warp_id();
   const uint32_t ltm = lt_mask();
+  // A warp owns GS_IPT*32 consecutive positions of the tile (GS_IPT rounds of
+  // 32), so in-warp order is position order and one cross-warp prefix per tile
+  // is enough.
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     __syncthreads();
-    if (threadIdx.x < NC) s_run[threadIdx.x] = ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + t];
-#pragma unroll 1
-    for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      uint32_t f = 0u;
-      int32_t c = 0;
-      bool live = p < C;
-      if (live) {
-        f = ws.cflag[p];
-        c = ws.cand[p];
-      }
-      const bool isself = live && (f & GS_CF_SELF);
-      const bool edge = live && !(f & (GS_CF_SELF | GS_CF_LOOP));
-      const bool ffirst = live && (f & GS_CF_FFIRST);
-      const bool ifirst = live && (f & GS_CF_IFIRST);
-      const int g = (int)(f >> GS_CF_PART_SHIFT);
-      // in-warp ranks
-      const uint32_t mf = __ballot_sync(FULL, ffirst);
-      const uint32_t rf = __popc(mf & ltm);
-      if (lane == 0) s_wcnt[w][0] = __popc(mf);
-      uint32_t ri = 0u, re_own = 0u;
-      uint32_t re[GS_MAX_PARTS];
+    const uint32_t wbase = (uint32_t)t * GS_TILE + (uint32_t)w * (GS_IPT * 32);
+    uint32_t f[GS_IPT];
+    int32_t ci[GS_IPT], cv[GS_IPT];
 #pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++) {
-        re[q] = 0u;
+    for (int r = 0; r < GS_IPT; r++) {
+      const uint32_t p = wbase + r * 32 + lane;
+      f[r] = GS_CF_LOOP;  // dead lane: neither edge nor first
+      ci[r] = 0;
+      if (p < C) {
+        f[r] = ws.cflag[p];
+        ci[r] = ws.cand[p];
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < GS_IPT; r++) cv[r] = (f[r] & GS_CF_SELF) ? front[ci[r]] : ci[r];
+    // phase 1: per-warp totals of every class
+    {
+      uint32_t nf = 0u, ni[GS_MAX_PARTS], ne[GS_MAX_PARTS];
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++) ni[q] = ne[q] = 0u;
+#pragma unroll
+      for (int r = 0; r < GS_IPT; r++) {
+        const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
+        const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
+        nf += __popc(__ballot_sync(FULL, (f[r] & GS_CF_FFIRST) != 0u));
+#pragma unroll
+        for (int q = 0; q < GS_MAX_PARTS; q++)
+          if (q < P) {
+            ni[q] += __popc(__ballot_sync(FULL, (f[r] & GS_CF_IFIRST) && g == q));
+            ne[q] += __popc(__ballot_sync(FULL, edge && g == q));
+          }
+      }
+      if (lane == 0) {
+        s_wcnt[w][0] = nf;
+#pragma unroll
+        for (int q = 0; q < GS_MAX_PARTS; q++)
+          if (q < P) {
+            s_wcnt[w][1 + q] = ni[q];
+            s_wcnt[w][1 + P + q] = ne[q];
+          }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < NC * GS_NW) {
+      const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
+      uint32_t a = ws.ctile_cnt[(size_t)cc * ws.ctiles_max + t];
+      for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
+      s_base[ww][cc] = a;
+    }
+    __syncthreads();
+    // phase 2: ranks and scatter
+    uint32_t rf = s_base[w][0], ri[GS_MAX_PARTS], re[GS_MAX_PARTS];
+#pragma unroll
+    for (int q = 0; q < GS_MAX_PARTS; q++) {
+      ri[q] = q < P ? s_base[w][1 + q] : 0u;
+      re[q] = q < P ? s_base[w][1 + P + q] : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < GS_IPT; r++) {
+      const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
+      const bool isself = (f[r] & GS_CF_SELF) != 0u;
+      const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
+      const bool ffirst = (f[r] & GS_CF_FFIRST) != 0u, ifirst = (f[r] & GS_CF_IFIRST) != 0u;
+      const uint32_t mf = __ballot_sync(FULL, ffirst);
+      if (ffirst) fnext[rf + __popc(mf & ltm)] = cv[r];
+      rf += __popc(mf);
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++)
         if (q < P) {
           const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
           const uint32_t me = __ballot_sync(FULL, edge && g == q);
-          if (g == q) ri = __popc(mi & ltm);
-          re[q] = __popc(me & ltm);
-          if (g == q) re_own = re[q];
-          if (lane == 0) {
-            s_wcnt[w][1 + q] = __popc(mi);
-            s_wcnt[w][1 + P + q] = __popc(me);
+          const uint32_t ex = re[q] + __popc(me & ltm);  // part-q edges before this position
+          if (ifirst && g == q) {
+            const uint32_t rk = ri[q] + __popc(mi & ltm);
+            ws.slab[s_in_off[q] + rk] = cv[r];
+            ws.table[cv[r]].x = rk;
           }
+          if (edge && g == q) ws.slab[s_ix_off[q] + ex] = cv[r];
+          if (isself) ws.rowscan[(size_t)ci[r] * P + q] = ex;
+          ri[q] += __popc(mi);
+          re[q] += __popc(me);
         }
-      }
-      __syncthreads();
-      // exclusive prefix over the CTA's warps, per class
-      if (threadIdx.x < NC * GS_NW) {
-        const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-        uint32_t a = 0u;
-        for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
-        s_wpre[ww][cc] = a;
-        if (ww == GS_NW - 1) s_tot[cc] = a + s_wcnt[ww][cc];
-      }
-      __syncthreads();
-      if (live) {
-        const int32_t v = isself ? front[c] : c;
-        if (ffirst) fnext[s_run[0] + s_wpre[w][0] + rf] = v;
-        if (ifirst) {
-          const uint32_t r = s_run[1 + g] + s_wpre[w][1 + g] + ri;
-          ws.slab[s_in_off[g] + r] = v;
-          ws.table[v].x = r;
-        }
-        if (edge) ws.slab[s_ix_off[g] + s_run[1 + P + g] + s_wpre[w][1 + P + g] + re_own] = v;
-        if (isself) {
-#pragma unroll
-          for (int q = 0; q < GS_MAX_PARTS; q++)
-            if (q < P)
-              ws.rowscan[(size_t)c * P + q] = s_run[1 + P + q] + s_wpre[w][1 + P + q] + re[q];
-        }
-      }
-      __syncthreads();
-      if (threadIdx.x < NC) s_run[threadIdx.x] += s_tot[threadIdx.x];
-      __syncthreads();
     }
   }
 }
@@ -664,20 +732,24 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
   spine_scan<GS_NF_MAX>(ws.ftile_cnt, ws.ftiles_max, ntiles, NF, s_tot, s_w);
   if (threadIdx.x == 0) {
     bool ok = true;
+    int64_t used = h->slab_used;
     for (int q = 0; q < P && ok; q++) {
       const uint32_t n_out = s_tot[q], n_own = s_tot[P + q], n_to = s_tot[2 * P + q],
                      n_self = s_tot[3 * P + q];
       gs_span *fl = h->field[layer][q];
-      fl[GS_F_OUT_NODES] = slab_alloc(h, ws.slab_cap, n_out, ok);
-      fl[GS_F_CSR_INDPTR] = slab_alloc(h, ws.slab_cap, n_out + 1u, ok);
-      fl[GS_F_OWNED_OUT] = slab_alloc(h, ws.slab_cap, n_own, ok);
-      fl[GS_F_FROM_IDS] = slab_alloc(h, ws.slab_cap, n_out - n_own, ok);
-      fl[GS_F_TO_IDS] = slab_alloc(h, ws.slab_cap, n_to, ok);
-      fl[GS_F_SELF_IN] = slab_alloc(h, ws.slab_cap, n_self, ok);
-      fl[GS_F_SELF_OUT] = slab_alloc(h, ws.slab_cap, n_self, ok);
-      if (ok) ws.slab[fl[GS_F_CSR_INDPTR].off + n_out] = fl[GS_F_CSR_INDICES].len;
+      const gs_span ip = slab_alloc(used, ws.slab_cap, n_out + 1u, ok);
+      fl[GS_F_OUT_NODES] = slab_alloc(used, ws.slab_cap, n_out, ok);
+      fl[GS_F_CSR_INDPTR] = ip;
+      fl[GS_F_OWNED_OUT] = slab_alloc(used, ws.slab_cap, n_own, ok);
+      fl[GS_F_FROM_IDS] = slab_alloc(used, ws.slab_cap, n_out - n_own, ok);
+      fl[GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, n_to, ok);
+      fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, n_self, ok);
+      fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, n_self, ok);
+      // row pointer sentinel = E_g (left in rowscan[F] by k_cand_flags' spine)
+      if (ok) ws.slab[ip.off + n_out] = (int32_t)ws.rowscan[(size_t)F * P + q];
     }
-    if (!ok) h->status = (int32_t)GS_ERR_OVERFLOW;
+    if (ok) h->slab_used = used;
+    else h->status = (int32_t)GS_ERR_OVERFLOW;
   }
 }
 
@@ -686,13 +758,11 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ uint32_t s_wcnt[GS_NW][GS_NF_MAX];
-  __shared__ uint32_t s_wpre[GS_NW][GS_NF_MAX];
-  __shared__ uint32_t s_run[GS_NF_MAX];
-  __shared__ uint32_t s_tot[GS_NF_MAX];
+  __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
   __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
   const int P = ws.P, NF = 4 * P;
   const int F = h->frontier_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   if (threadIdx.x < P * GS_NUM_FIELDS)
     s_off[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
@@ -701,80 +771,109 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   const uint32_t ltm = lt_mask();
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     __syncthreads();
-    if (threadIdx.x < NF) s_run[threadIdx.x] = ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + t];
-#pragma unroll 1
-    for (int it = 0; it < GS_IPT; it++) {
-      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-      uint32_t has = 0u;
-      int g0 = -1;
-      int32_t nd = 0;
-      if (i < F) {
-        nd = front[i];
-        g0 = owner_of(ws, nd);
-        has = row_has_mask(ws, i, P);
-      }
-      const bool to = g0 >= 0 && (has & ~(1u << g0)) != 0u;
-      uint32_t r_out[GS_MAX_PARTS], r_own[GS_MAX_PARTS];
-      uint32_t r_to = 0u, r_self = 0u;
+    const int wbase = t * GS_TILE + w * (GS_IPT * 32);
+    uint32_t has[GS_IPT];
+    int g0[GS_IPT];
+    int32_t nd[GS_IPT];
 #pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++) {
-        r_out[q] = 0u;
-        r_own[q] = 0u;
+    for (int r = 0; r < GS_IPT; r++) {
+      const int i = wbase + r * 32 + lane;
+      has[r] = 0u;
+      g0[r] = -1;
+      nd[r] = 0;
+      if (i < F) {
+        nd[r] = front[i];
+        g0[r] = owner_of(ws, nd[r]);
+        has[r] = row_has_mask(ws, i, P);
+      }
+    }
+    {
+      uint32_t n_out[GS_MAX_PARTS], n_own[GS_MAX_PARTS], n_to[GS_MAX_PARTS], n_self[GS_MAX_PARTS];
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++) n_out[q] = n_own[q] = n_to[q] = n_self[q] = 0u;
+#pragma unroll
+      for (int r = 0; r < GS_IPT; r++) {
+        const bool to = g0[r] >= 0 && (has[r] & ~(1u << g0[r])) != 0u;
+#pragma unroll
+        for (int q = 0; q < GS_MAX_PARTS; q++)
+          if (q < P) {
+            const bool hq = (has[r] >> q) & 1u;
+            n_out[q] += __popc(__ballot_sync(FULL, hq));
+            n_own[q] += __popc(__ballot_sync(FULL, hq && g0[r] == q));
+            n_to[q] += __popc(__ballot_sync(FULL, to && g0[r] == q));
+            n_self[q] += __popc(__ballot_sync(FULL, g0[r] == q));
+          }
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < GS_MAX_PARTS; q++)
+          if (q < P) {
+            s_wcnt[w][q] = n_out[q];
+            s_wcnt[w][P + q] = n_own[q];
+            s_wcnt[w][2 * P + q] = n_to[q];
+            s_wcnt[w][3 * P + q] = n_self[q];
+          }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < NF * GS_NW) {
+      const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
+      uint32_t a = ws.ftile_cnt[(size_t)cc * ws.ftiles_max + t];
+      for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
+      s_base[ww][cc] = a;
+    }
+    __syncthreads();
+    uint32_t b_out[GS_MAX_PARTS], b_own[GS_MAX_PARTS], b_to[GS_MAX_PARTS], b_self[GS_MAX_PARTS];
+#pragma unroll
+    for (int q = 0; q < GS_MAX_PARTS; q++) {
+      b_out[q] = q < P ? s_base[w][q] : 0u;
+      b_own[q] = q < P ? s_base[w][P + q] : 0u;
+      b_to[q] = q < P ? s_base[w][2 * P + q] : 0u;
+      b_self[q] = q < P ? s_base[w][3 * P + q] : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < GS_IPT; r++) {
+      const int i = wbase + r * 32 + lane;
+      const bool live = i < F;
+      const bool to = g0[r] >= 0 && (has[r] & ~(1u << g0[r])) != 0u;
+      int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+      uint32_t p_to = 0u, p_self = 0u;
+#pragma unroll
+      for (int q = 0; q < GS_MAX_PARTS; q++)
         if (q < P) {
-          const bool hq = (has >> q) & 1u;
+          const bool hq = (has[r] >> q) & 1u;
           const uint32_t m_out = __ballot_sync(FULL, hq);
-          const uint32_t m_own = __ballot_sync(FULL, hq && g0 == q);
-          const uint32_t m_to = __ballot_sync(FULL, to && g0 == q);
-          const uint32_t m_self = __ballot_sync(FULL, g0 == q);
-          r_out[q] = __popc(m_out & ltm);
-          r_own[q] = __popc(m_own & ltm);
-          if (g0 == q) {
-            r_to = __popc(m_to & ltm);
-            r_self = __popc(m_self & ltm);
-          }
-          if (lane == 0) {
-            s_wcnt[w][q] = __popc(m_out);
-            s_wcnt[w][P + q] = __popc(m_own);
-            s_wcnt[w][2 * P + q] = __popc(m_to);
-            s_wcnt[w][3 * P + q] = __popc(m_self);
-          }
-        }
-      }
-      __syncthreads();
-      if (threadIdx.x < NF * GS_NW) {
-        const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-        uint32_t a = 0u;
-        for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
-        s_wpre[ww][cc] = a;
-        if (ww == GS_NW - 1) s_tot[cc] = a + s_wcnt[ww][cc];
-      }
-      __syncthreads();
-      if (i < F) {
-        int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
-#pragma unroll
-        for (int q = 0; q < GS_MAX_PARTS; q++) {
-          if (q < P && ((has >> q) & 1u)) {
-            const uint32_t op = s_run[q] + s_wpre[w][q] + r_out[q];
-            const uint32_t ow = s_run[P + q] + s_wpre[w][P + q] + r_own[q];
-            ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd;
+          const uint32_t m_own = __ballot_sync(FULL, hq && g0[r] == q);
+          const uint32_t m_to = __ballot_sync(FULL, to && g0[r] == q);
+          const uint32_t m_self = __ballot_sync(FULL, g0[r] == q);
+          if (hq) {
+            const uint32_t op = b_out[q] + __popc(m_out & ltm);
+            const uint32_t ow = b_own[q] + __popc(m_own & ltm);
+            ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd[r];
             ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * P + q];
-            if (q == g0) {
+            if (q == g0[r]) {
               ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
               op_own = (int32_t)op;
             } else {
               ws.slab[s_off[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
             }
           }
+          if (g0[r] == q) {
+            p_to = b_to[q] + __popc(m_to & ltm);
+            p_self = b_self[q] + __popc(m_self & ltm);
+          }
+          b_out[q] += __popc(m_out);
+          b_own[q] += __popc(m_own);
+          b_to[q] += __popc(m_to);
+          b_self[q] += __popc(m_self);
         }
-        if (to) ws.slab[s_off[g0][GS_F_TO_IDS] + s_run[2 * P + g0] + s_wpre[w][2 * P + g0] + r_to] = op_own;
-        const uint32_t sp = s_run[3 * P + g0] + s_wpre[w][3 * P + g0] + r_self;
-        const uint32_t x = ws.table[nd].x;  // rank in in_nodes_g0, or INF: never an edge source
-        ws.slab[s_off[g0][GS_F_SELF_IN] + sp] = x == GS_INF ? -1 : (int32_t)x;
-        ws.slab[s_off[g0][GS_F_SELF_OUT] + sp] = op_own;
+      if (live) {
+        const int gq = g0[r];
+        if (to) ws.slab[s_off[gq][GS_F_TO_IDS] + p_to] = op_own;
+        const uint32_t x = ws.table[nd[r]].x;  // rank in in_nodes_g0, or INF: never an edge source
+        ws.slab[s_off[gq][GS_F_SELF_IN] + p_self] = x == GS_INF ? -1 : (int32_t)x;
+        ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self] = op_own;
       }
-      __syncthreads();
-      if (threadIdx.x < NF) s_run[threadIdx.x] += s_tot[threadIdx.x];
-      __syncthreads();
     }
   }
 }
@@ -790,8 +889,23 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
   for (int q = 0; q < P; q++) {
     const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
     int32_t *ix = ws.slab + sp.off;
-    for (int e = blockIdx.x * GS_TPB + threadIdx.x; e < sp.len; e += gridDim.x * GS_TPB)
-      ix[e] = (int32_t)ws.table[ix[e]].x;
+    const int stride = gridDim.x * GS_TPB;
+    for (int e0 = blockIdx.x * GS_TPB + threadIdx.x; e0 < sp.len; e0 += GS_IPT * stride) {
+      int32_t v[GS_IPT];
+      uint32_t r[GS_IPT];
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        const int e = e0 + k * stride;
+        v[k] = e < sp.len ? ix[e] : -1;
+      }
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] >= 0 ? ws.table[v[k]].x : 0u;
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        const int e = e0 + k * stride;
+        if (e < sp.len) ix[e] = (int32_t)r[k];
+      }
+    }
   }
 }
 
