@@ -199,6 +199,42 @@ def kernel_bytes(view, P):
     return out
 
 
+def random_accesses(view, P):
+    """Random (data-dependent) 4/8-byte accesses one minibatch makes, by target:
+    CSR (indptr pairs + neighbour picks) and the slot's dedup table."""
+    csr = tab = 0
+    for l in range(view.num_layers):
+        F, C = view.frontier_len[l], view.cand_len[l]
+        E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
+        n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
+        csr += F + (C - F)          # indptr[nd], one neighbour pick per non-self candidate
+        tab += F                    # k_rows_scan: entry (re)initialised with the self position
+        tab += (C - F)              # k_expand: atomicMin
+        tab += C                    # k_cand_flags: read
+        tab += n_in                 # k_cand_apply: rank written back
+        tab += E                    # k_relabel: read
+        tab += F                    # k_front_apply: read (self_ids_in)
+    tab += view.frontier_len[view.num_layers]  # k_finish: sparse reset
+    return csr, tab
+
+
+def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
+    """Random-read ceiling of this GPU for a table of the given footprint
+    (torch.index_select as a tuned gather; a yardstick like the copy peak)."""
+    t = torch.zeros(table_elems, dtype=dtype, device="cuda")
+    idx = torch.randint(0, table_elems, (n,), device="cuda", dtype=torch.int64)
+    for _ in range(2):
+        torch.index_select(t, 0, idx)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        torch.index_select(t, 0, idx)
+    e1.record()
+    torch.cuda.synchronize()
+    return n * 3 / (e0.elapsed_time(e1) * 1e-3)
+
+
 def own_arm(args):
     import torch
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
@@ -219,7 +255,8 @@ def own_arm(args):
     g = Graph(ip, ix, device=local)
     P, mbs = args.parts, args.mb_per_step
     batches = seed_batches(n, max(64, mbs), rank, world)
-    kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7)
+    kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
+              grid_ctas=args.grid_ctas)
     dev = Slicer(g, FANOUTS, host_output=False, **kw)
     hst = Slicer(g, FANOUTS, host_output=True, **kw)
     peaks = {}
@@ -239,6 +276,7 @@ def own_arm(args):
     kbytes = kernel_bytes(v, P)
     sizes = dict(frontier=v.frontier_len, candidates=v.cand_len, edges=v.edges,
                  slab_bytes=v.slab_used * 4)
+    ra_csr, ra_tab = random_accesses(v, P)
     v.release()
 
     def barrier():
@@ -284,6 +322,19 @@ def own_arm(args):
                                     "achieved_gbs": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9, 2),
                                     "frac": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9 / peak, 4)},
                 "kernels_ms": {k: round(ms, 4) for k, ms in prof}}
+        # what the path is really bound by: random sector accesses, not streamed bytes
+        g_csr = gather_yardstick(torch, ix.size, torch.int32)
+        g_tab = gather_yardstick(torch, n * args.slots, torch.int64)
+        floor_s = ra_csr / g_csr + ra_tab / g_tab
+        roof["random_access"] = {
+            "per_minibatch": {"csr_4B": int(ra_csr), "table_8B": int(ra_tab)},
+            "yardstick_gelem_s": {"csr_array": round(g_csr / 1e9, 2),
+                                  "tables_all_slots": round(g_tab / 1e9, 2)},
+            "floor_us_per_minibatch": round(floor_s * 1e6, 1),
+            "achieved_us_per_minibatch": round(1e6 / per_gpu_mb_s, 1),
+            "frac_of_random_access_floor": round(floor_s * per_gpu_mb_s, 3),
+            "note": "each access moves a 32 B sector; yardstick = torch.index_select over arrays of the "
+                    "same footprint, measured in this run"}
         out = {"metric": "sliced minibatches/s", "value": round(value, 2), "unit": "minibatches/s",
                "n_gpus": world, "steps": args.steps, "warmup": W,
                "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
@@ -329,7 +380,7 @@ def cpu_port_rate(ip, ix, P, batches, workers, target_s):
     from oracle import oracle as O
     seeds = [b for _, b in batches]
     t1, _ = O.pool_run(ip, ix, FANOUTS, P, seeds[:1], workers=1, rng_mode=O.RNG_PHILOX, seed=7)
-    nb = int(max(workers, min(len(seeds), target_s / max(t1, 1e-3) * workers * 0.7)))
+    nb = int(max(workers, min(4096, target_s / max(t1, 1e-3) * workers * 0.7)))
     nb = max(workers, (nb // workers) * workers)
     sample = [seeds[i % len(seeds)] for i in range(nb)]
     sec, edges = O.pool_run(ip, ix, FANOUTS, P, sample, workers=workers, rng_mode=O.RNG_PHILOX, seed=7)
@@ -411,6 +462,7 @@ def main():
     ap.add_argument("--mb-per-step", type=int, default=64)
     ap.add_argument("--slots", type=int, default=8)
     ap.add_argument("--streams", type=int, default=8)
+    ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

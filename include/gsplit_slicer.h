@@ -103,6 +103,8 @@ typedef struct {
   int64_t slab_capacity;           /* 0 = derive (int32 elements) */
   int32_t grid_ctas;               /* CTAs per SM of a full-machine launch; 0 = 4 */
   int32_t use_graph;               /* 1 (default via gs_config_default): CUDA-graph replay */
+  int32_t l2_hints;                /* 1 (default): L2 eviction-priority hints, tables kept resident */
+  int32_t reserved0;
 } gs_config;
 
 typedef struct gs_graph gs_graph;

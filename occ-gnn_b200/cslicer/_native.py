@@ -50,7 +50,8 @@ class Config(C.Structure):
                 ("draws_host", C.c_void_p), ("n_draws", C.c_uint64), ("max_batch", C.c_int32),
                 ("num_slots", C.c_int32), ("num_streams", C.c_int32), ("host_output", C.c_int32),
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
-                ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32)]
+                ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32),
+                ("l2_hints", C.c_int32), ("reserved0", C.c_int32)]
 
 
 _lib = None

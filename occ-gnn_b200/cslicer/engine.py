@@ -142,7 +142,7 @@ class Slicer:
 
     def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
                  seed=0, owner=None, draws=None, host_output=True, use_graph=True,
-                 frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0):
+                 frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True):
         L = N.lib()
         self.graph = graph
         cfg = N.Config()
@@ -156,6 +156,7 @@ class Slicer:
         cfg.host_output, cfg.use_graph = int(bool(host_output)), int(bool(use_graph))
         cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)
         cfg.slab_capacity, cfg.grid_ctas = int(slab_capacity), int(grid_ctas)
+        cfg.l2_hints = int(bool(l2_hints))
         keep = []
         if owner is not None:
             o = np.ascontiguousarray(owner, dtype=np.int32)

@@ -184,6 +184,7 @@ void gs_config_default(gs_config *c) {
   c->num_streams = 4;
   c->host_output = 1;
   c->use_graph = 1;
+  c->l2_hints = 1;
 }
 
 int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
@@ -354,8 +355,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
   }
 
-  const int ftiles = (int)((s->Fcap + GS_TILE - 1) / GS_TILE) + 1;
-  const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;
+  const int ftiles = s->grid;  // per-CTA count arrays: one entry per CTA of the largest grid
+  const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;  // tile_first: one per candidate tile
   s->slots.resize(cfg->num_slots);
   for (int k = 0; k < cfg->num_slots; k++) {
     Slot &sl = s->slots[k];
@@ -369,6 +370,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.L = cfg->num_layers;
     for (int l = 0; l < GS_MAX_LAYERS; l++) w.fanouts[l] = cfg->fanouts[l];
     w.rng_mode = cfg->rng_mode;
+    w.l2_hints = cfg->l2_hints;
     w.seed_lo = (uint32_t)cfg->seed;
     w.seed_hi = (uint32_t)(cfg->seed >> 32);
     w.draws = s->draws;
@@ -378,7 +380,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.Fcap = (int32_t)s->Fcap;
     w.Ccap = (int32_t)s->Ccap;
     w.ftiles_max = ftiles;
-    w.ctiles_max = ctiles;
+    w.ctiles_max = s->grid;
 #define DA(ptr, n)                                         \
   do {                                                     \
     if (dev_alloc(sl, &ptr, (size_t)(n), &bytes) != GS_OK) { \
@@ -402,7 +404,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.ftile_sum, ftiles);
     DA(w.ftile_samp, ftiles);
     DA(w.ftile_pre, 2 * (size_t)ftiles);
-    DA(w.ctile_cnt, (size_t)GS_NC_MAX * ctiles);
+    DA(w.ctile_cnt, (size_t)GS_NC_MAX * s->grid);
     DA(w.ftile_cnt, (size_t)GS_NF_MAX * ftiles);
     DA(w.tickets, 8);
 #undef DA

@@ -40,6 +40,7 @@ struct GsWs {
   int32_t fanouts[GS_MAX_LAYERS];
   // rng
   int32_t rng_mode;
+  int32_t l2_hints;      // 1: keep the dedup table in L2 (evict_last), stream the rest (evict_first)
   uint32_t seed_lo, seed_hi;
   const uint32_t *draws;
   uint64_t n_draws;

@@ -99,6 +99,73 @@ __device__ __forceinline__ bool last_block(uint32_t *ticket) {
   return s_last != 0u;
 }
 
+// --------------------------------------------------- L2 residency control
+// The per-slot dedup tables are the only randomly re-read data (4-5 touches per
+// candidate); the CSR gathers and the candidate / slab streams are touched once.
+// With createpolicy hints the tables are kept in B200's 126 MB L2 (evict_last)
+// while the single-use traffic passes through as evict_first.  ws.l2_hints = 0
+// falls back to plain accesses (same results, for A/B measurements).
+__device__ __forceinline__ uint64_t l2_policy_keep() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_stream() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+struct Tbl {  // table access with an optional keep-in-L2 policy
+  uint2 *t;
+  uint64_t pol;
+  bool hint;
+  __device__ __forceinline__ Tbl(const GsWs &ws) : t(ws.table), pol(0), hint(ws.l2_hints != 0) {
+    if (hint) pol = l2_policy_keep();
+  }
+  __device__ __forceinline__ uint2 ld(int32_t v) const {
+    if (!hint) return t[v];
+    uint2 r;
+    asm volatile("ld.global.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;"
+                 : "=r"(r.x), "=r"(r.y) : "l"(t + v), "l"(pol));
+    return r;
+  }
+  __device__ __forceinline__ uint32_t ldx(int32_t v) const {
+    if (!hint) return t[v].x;
+    uint32_t r;
+    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(&t[v].x), "l"(pol));
+    return r;
+  }
+  __device__ __forceinline__ void st(int32_t v, uint2 e) const {
+    if (!hint) { t[v] = e; return; }
+    asm volatile("st.global.L2::cache_hint.v2.u32 [%0], {%1, %2}, %3;"
+                 :: "l"(t + v), "r"(e.x), "r"(e.y), "l"(pol) : "memory");
+  }
+  __device__ __forceinline__ void stx(int32_t v, uint32_t x) const {
+    if (!hint) { t[v].x = x; return; }
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(&t[v].x), "r"(x), "l"(pol) : "memory");
+  }
+  __device__ __forceinline__ void minx(int32_t v, uint32_t p) const {
+    if (!hint) { atomicMin(&t[v].x, p); return; }
+    asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(&t[v].x), "r"(p), "l"(pol) : "memory");
+  }
+};
+__device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, uint64_t pol) {
+  if (!hint) return __ldg(a);
+  int32_t r;
+  asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(a), "l"(pol));
+  return r;
+}
+
+// Tiles are dealt to CTAs in contiguous runs, so a CTA can carry running
+// offsets across its own tiles and the cross-CTA spine only has gridDim.x
+// entries per counter (not one per tile).  Count and apply kernels of a pair
+// are launched with the same grid and therefore see the same runs.
+__device__ __forceinline__ void cta_tiles(int ntiles, int &t0, int &t1) {
+  const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+  t0 = min(ntiles, (int)blockIdx.x * per);
+  t1 = min(ntiles, t0 + per);
+}
+
 __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
   return ws.owner ? (int)__ldg(ws.owner + v) : (int)((uint32_t)v % (uint32_t)ws.P);
 }
@@ -141,33 +208,34 @@ __device__ __forceinline__ uint32_t philox_pick(uint32_t k0, uint32_t k1, uint32
   return w == 0 ? c0 : (w == 1 ? c1 : (w == 2 ? c2 : c3));
 }
 
-// Two-level exclusive scan of `nc` counter arrays (cnt[c*stride + t], t < n)
-// by one whole CTA, in place; totals[c] receives each array's sum.
+// Exclusive scan of `nc` counter arrays (cnt[c*stride + b], b < n = number of
+// CTAs) by one CTA, in place; totals[c] receives each array's sum.  One warp
+// per counter, eight independent coalesced loads in flight per lane, shuffles
+// only -- the spine is on every layer's critical path, so no barrier and no
+// dependent-load chain inside it.
 template <int NCMAX>
 __device__ void spine_scan(uint32_t *cnt, int stride, int n, int nc, uint32_t *totals,
-                           uint32_t *s_w) {
-  const int tid = threadIdx.x;
-  const int chunk = (n + GS_TPB - 1) / GS_TPB;
-  const int a = min(n, tid * chunk), b = min(n, a + chunk);
-  uint32_t sum[NCMAX];
+                           uint32_t * /*unused*/) {
+  const int w = warp_id(), lane = lane_id();
+  for (int c = w; c < nc; c += GS_NW) {
+    uint32_t *a = cnt + (size_t)c * stride;
+    uint32_t carry = 0u;
+    for (int base = 0; base < n; base += 32 * 8) {
+      uint32_t v[8];
 #pragma unroll
-  for (int c = 0; c < NCMAX; c++) {
-    sum[c] = 0u;
-    if (c < nc)
-      for (int t = a; t < b; t++) sum[c] += __ldcg(cnt + (size_t)c * stride + t);
-  }
+      for (int k = 0; k < 8; k++) {
+        const int idx = base + k * 32 + lane;
+        v[k] = idx < n ? __ldcg(a + idx) : 0u;
+      }
 #pragma unroll
-  for (int c = 0; c < NCMAX; c++) {
-    if (c < nc) {  // nc is CTA-uniform
-      uint32_t tot;
-      uint32_t pre = block_excl_scan(sum[c], s_w, tot);
-      if (tid == 0) totals[c] = tot;
-      for (int t = a; t < b; t++) {
-        uint32_t v = __ldcg(cnt + (size_t)c * stride + t);
-        cnt[(size_t)c * stride + t] = pre;
-        pre += v;
+      for (int k = 0; k < 8; k++) {
+        const int idx = base + k * 32 + lane;
+        const uint32_t inc = warp_incl_scan(v[k]);
+        if (idx < n) a[idx] = carry + inc - v[k];
+        carry += __shfl_sync(FULL, inc, 31);
       }
     }
+    if (lane == 0) totals[c] = carry;
   }
   __syncthreads();
 }
@@ -224,7 +292,7 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
 // ------------------------------------------------------------- k_rows_count
 // Per frontier row: CSR extent and number of candidates c = 1 + (deg < fan or
 // fan < 0 ? deg : fan)  (slicer.cpp:6-22).  Tile sums + last-CTA spine give the
-// candidate offsets' tile prefixes and C_l.
+// candidate offsets' per-CTA prefixes and C_l.
 __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -234,21 +302,25 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
   const int32_t *front = ws.slab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  {
     unsigned long long csum = 0ull;
     uint32_t ssum = 0u;
+    for (int t = t0; t < t1; t++) {
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-      if (i < F) {
-        const int32_t nd = front[i];
-        const int64_t s = __ldg(ws.indptr + nd), e = __ldg(ws.indptr + nd + 1);
-        const int32_t deg = (int32_t)(e - s);
-        ws.rowstart[i] = s;
-        ws.rowdeg[i] = deg;
-        const bool samp = fan >= 0 && deg >= fan;
-        csum += 1ull + (unsigned long long)(samp ? fan : deg);
-        ssum += samp ? 1u : 0u;
+      for (int it = 0; it < GS_IPT; it++) {
+        const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
+        if (i < F) {
+          const int32_t nd = front[i];
+          const int64_t s = __ldg(ws.indptr + nd), e = __ldg(ws.indptr + nd + 1);
+          const int32_t deg = (int32_t)(e - s);
+          ws.rowstart[i] = s;
+          ws.rowdeg[i] = deg;
+          const bool samp = fan >= 0 && deg >= fan;
+          csum += 1ull + (unsigned long long)(samp ? fan : deg);
+          ssum += samp ? 1u : 0u;
+        }
       }
     }
     unsigned long long ctot;
@@ -256,14 +328,15 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
     block_excl_scan64(csum, s_w64, ctot);
     block_excl_scan(ssum, s_w, stot);
     if (threadIdx.x == 0) {
-      ws.ftile_sum[t] = ctot;
-      ws.ftile_samp[t] = stot;
+      ws.ftile_sum[blockIdx.x] = ctot;
+      ws.ftile_samp[blockIdx.x] = stot;
     }
   }
   if (!last_block(ws.tickets + 0)) return;
-  // spine: exclusive prefixes over frontier tiles
-  const int chunk = (ntiles + GS_TPB - 1) / GS_TPB;
-  const int a = min(ntiles, (int)threadIdx.x * chunk), b = min(ntiles, a + chunk);
+  // spine: exclusive prefixes over the CTAs' sums
+  const int nb = (int)gridDim.x;
+  const int chunk = (nb + GS_TPB - 1) / GS_TPB;
+  const int a = min(nb, (int)threadIdx.x * chunk), b = min(nb, a + chunk);
   unsigned long long cs = 0ull;
   uint32_t ss = 0u;
   for (int t = a; t < b; t++) {
@@ -304,15 +377,18 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
   __shared__ uint32_t s_w[GS_NW + 1];
   const int F = h->frontier_len[layer];
   const int32_t *front = ws.slab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    uint32_t base = ws.ftile_pre[t];
-    uint32_t sbase = ws.ftile_pre[ws.ftiles_max + t];
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  uint32_t base = ws.ftile_pre[blockIdx.x];  // running over this CTA's run of tiles
+  uint32_t sbase = ws.ftile_pre[ws.ftiles_max + blockIdx.x];
+  for (int t = t0; t < t1; t++) {
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
@@ -333,7 +409,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
         const uint32_t o = base + ex;
         ws.off[i] = o;
         if (replay) ws.samp_rank[i] = sbase + sex;
-        ws.table[nd] = make_uint2(GS_INF, o);
+        tbl.st(nd, make_uint2(GS_INF, o));
         ws.cand[o] = i;
         ws.cflag[o] = (uint8_t)GS_CF_SELF;
         for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
@@ -357,6 +433,8 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
+  const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
   __shared__ uint32_t s_off[GS_TILE + 2];
   const int F = h->frontier_len[layer];
   const uint32_t C = (uint32_t)h->cand_len[layer];
@@ -423,14 +501,14 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
     int32_t v[GS_IPT];
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++)
-      if (slot[it] > 0) v[it] = __ldg(src[it]);
+      if (slot[it] > 0) v[it] = ld_stream_i32(src[it], ws.l2_hints != 0, spol);
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       if (slot[it] > 0) {
         ws.cand[pos[it]] = v[it];
         if (v[it] != nd1[it]) {
           ws.cflag[pos[it]] = 0;
-          atomicMin(&ws.table[v[it]].x, pos[it]);
+          tbl.minx(v[it], pos[it]);
         } else {
           ws.cflag[pos[it]] = (uint8_t)GS_CF_LOOP;
         }
@@ -449,6 +527,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
   __shared__ uint32_t s_cnt[GS_NC_MAX];
   __shared__ uint32_t s_tot[GS_NC_MAX];
   __shared__ uint32_t s_w[GS_NW + 1];
@@ -459,7 +538,9 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  for (int t = t0; t < t1; t++) {
     // phased so the GS_IPT random table reads of a thread are in flight together
     uint32_t fl[GS_IPT];
     int32_t cv[GS_IPT];
@@ -483,7 +564,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     for (int it = 0; it < GS_IPT; it++) {
       const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
       te[it] = make_uint2(0u, 0u);
-      if (p < C) te[it] = ws.table[cv[it]];
+      if (p < C) te[it] = tbl.ld(cv[it]);
     }
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
@@ -517,15 +598,11 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
         }
       }
     }
-    __syncthreads();
-    if (threadIdx.x < NC) {
-      ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + t] = s_cnt[threadIdx.x];
-      s_cnt[threadIdx.x] = 0u;
-    }
-    __syncthreads();
   }
+  __syncthreads();
+  if (threadIdx.x < NC) ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x] = s_cnt[threadIdx.x];
   if (!last_block(ws.tickets + 1)) return;
-  spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, ntiles, NC, s_tot, s_w);
+  spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, (int)gridDim.x, NC, s_tot, s_w);
   if (threadIdx.x == 0) {
     bool ok = true;
     if (h->reserved[0] != 0) {
@@ -566,8 +643,10 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
   __shared__ uint32_t s_wcnt[GS_NW][GS_NC_MAX];
-  __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // tile prefix + earlier warps of the tile
+  __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
+  __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
   const int P = ws.P, NC = 2 * P + 1;
   const uint32_t C = (uint32_t)h->cand_len[layer];
@@ -583,7 +662,10 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   // A warp owns GS_IPT*32 consecutive positions of the tile (GS_IPT rounds of
   // 32), so in-warp order is position order and one cross-warp prefix per tile
   // is enough.
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  if (threadIdx.x < NC) s_run[t0 & 1][threadIdx.x] = ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x];
+  for (int t = t0; t < t1; t++) {
     __syncthreads();
     const uint32_t wbase = (uint32_t)t * GS_TILE + (uint32_t)w * (GS_IPT * 32);
     uint32_t f[GS_IPT];
@@ -630,9 +712,10 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
     __syncthreads();
     if (threadIdx.x < NC * GS_NW) {
       const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-      uint32_t a = ws.ctile_cnt[(size_t)cc * ws.ctiles_max + t];
+      uint32_t a = s_run[t & 1][cc];
       for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
       s_base[ww][cc] = a;
+      if (ww == GS_NW - 1) s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
     }
     __syncthreads();
     // phase 2: ranks and scatter
@@ -660,7 +743,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
           if (ifirst && g == q) {
             const uint32_t rk = ri[q] + __popc(mi & ltm);
             ws.slab[s_in_off[q] + rk] = cv[r];
-            ws.table[cv[r]].x = rk;
+            tbl.stx(cv[r], rk);
           }
           if (edge && g == q) ws.slab[s_ix_off[q] + ex] = cv[r];
           if (isself) ws.rowscan[(size_t)ci[r] * P + q] = ex;
@@ -696,23 +779,30 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   if (threadIdx.x < GS_NF_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-#pragma unroll 1
-    for (int it = 0; it < GS_IPT; it++) {
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  for (int t = t0; t < t1; t++) {
+    uint32_t has[GS_IPT];
+    int g0[GS_IPT];
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {  // all row lookups in flight together
       const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-      uint32_t has = 0u;
-      int g0 = -1;
+      has[it] = 0u;
+      g0[it] = -1;
       if (i < F) {
-        g0 = owner_of(ws, front[i]);
-        has = row_has_mask(ws, i, P);
+        g0[it] = owner_of(ws, front[i]);
+        has[it] = row_has_mask(ws, i, P);
       }
-      const bool to = g0 >= 0 && (has & ~(1u << g0)) != 0u;
+    }
+#pragma unroll
+    for (int it = 0; it < GS_IPT; it++) {
+      const bool to = g0[it] >= 0 && (has[it] & ~(1u << g0[it])) != 0u;
       for (int q = 0; q < P; q++) {
-        const bool hq = (has >> q) & 1u;
+        const bool hq = (has[it] >> q) & 1u;
         const uint32_t m_out = __ballot_sync(FULL, hq);
-        const uint32_t m_own = __ballot_sync(FULL, hq && g0 == q);
-        const uint32_t m_to = __ballot_sync(FULL, to && g0 == q);
-        const uint32_t m_self = __ballot_sync(FULL, g0 == q);
+        const uint32_t m_own = __ballot_sync(FULL, hq && g0[it] == q);
+        const uint32_t m_to = __ballot_sync(FULL, to && g0[it] == q);
+        const uint32_t m_self = __ballot_sync(FULL, g0[it] == q);
         if (lane_id() == 0) {
           if (m_out) atomicAdd(&s_cnt[q], (uint32_t)__popc(m_out));
           if (m_own) atomicAdd(&s_cnt[P + q], (uint32_t)__popc(m_own));
@@ -721,15 +811,11 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
         }
       }
     }
-    __syncthreads();
-    if (threadIdx.x < NF) {
-      ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + t] = s_cnt[threadIdx.x];
-      s_cnt[threadIdx.x] = 0u;
-    }
-    __syncthreads();
   }
+  __syncthreads();
+  if (threadIdx.x < NF) ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x] = s_cnt[threadIdx.x];
   if (!last_block(ws.tickets + 2)) return;
-  spine_scan<GS_NF_MAX>(ws.ftile_cnt, ws.ftiles_max, ntiles, NF, s_tot, s_w);
+  spine_scan<GS_NF_MAX>(ws.ftile_cnt, ws.ftiles_max, (int)gridDim.x, NF, s_tot, s_w);
   if (threadIdx.x == 0) {
     bool ok = true;
     int64_t used = h->slab_used;
@@ -757,8 +843,10 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
   __shared__ uint32_t s_wcnt[GS_NW][GS_NF_MAX];
   __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
+  __shared__ uint32_t s_run[2][GS_NF_MAX];
   __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
   const int P = ws.P, NF = 4 * P;
   const int F = h->frontier_len[layer];
@@ -769,7 +857,10 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
         h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
   const int lane = lane_id(), w = warp_id();
   const uint32_t ltm = lt_mask();
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  if (threadIdx.x < NF) s_run[t0 & 1][threadIdx.x] = ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x];
+  for (int t = t0; t < t1; t++) {
     __syncthreads();
     const int wbase = t * GS_TILE + w * (GS_IPT * 32);
     uint32_t has[GS_IPT];
@@ -818,9 +909,10 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
     __syncthreads();
     if (threadIdx.x < NF * GS_NW) {
       const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-      uint32_t a = ws.ftile_cnt[(size_t)cc * ws.ftiles_max + t];
+      uint32_t a = s_run[t & 1][cc];
       for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
       s_base[ww][cc] = a;
+      if (ww == GS_NW - 1) s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
     }
     __syncthreads();
     uint32_t b_out[GS_MAX_PARTS], b_own[GS_MAX_PARTS], b_to[GS_MAX_PARTS], b_self[GS_MAX_PARTS];
@@ -870,7 +962,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
       if (live) {
         const int gq = g0[r];
         if (to) ws.slab[s_off[gq][GS_F_TO_IDS] + p_to] = op_own;
-        const uint32_t x = ws.table[nd[r]].x;  // rank in in_nodes_g0, or INF: never an edge source
+        const uint32_t x = tbl.ldx(nd[r]);  // rank in in_nodes_g0, or INF: never an edge source
         ws.slab[s_off[gq][GS_F_SELF_IN] + p_self] = x == GS_INF ? -1 : (int32_t)x;
         ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self] = op_own;
       }
@@ -885,6 +977,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  const Tbl tbl(ws);
   const int P = ws.P;
   for (int q = 0; q < P; q++) {
     const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
@@ -899,7 +992,7 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
         v[k] = e < sp.len ? ix[e] : -1;
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] >= 0 ? ws.table[v[k]].x : 0u;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] >= 0 ? tbl.ldx(v[k]) : 0u;
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
@@ -916,12 +1009,13 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
 // mirrored to pinned host memory with 16-byte stores.
 __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
   gs_sample_header *h = ws.hdr;
+  const Tbl tbl(ws);
   const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
   if (h->status == 0) {
     const int L = ws.L;
     const int32_t *fl = ws.slab + h->frontier[L].off;
     const int FL = h->frontier_len[L];
-    for (int i = tid; i < FL; i += nth) ws.table[fl[i]] = make_uint2(GS_INF, GS_INF);
+    for (int i = tid; i < FL; i += nth) tbl.st(fl[i], make_uint2(GS_INF, GS_INF));
   }
   {
     const int nw = (int)(sizeof(gs_sample_header) / 4);

@@ -257,6 +257,41 @@ def test_full_size_products_properties():
     torch.cuda.empty_cache()
 
 
+def _full_size_case(shape, fanouts, P, batch, owner="mod"):
+    E = _engine()
+    import torch
+    from cslicer.synth import owner_range, synth_graph
+    ip, ix = synth_graph(shape, seed=1234, device="cuda")
+    n = ip.size - 1
+    own = owner_range(n, P) if owner == "range" else None
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fanouts, P, max_batch=batch, num_slots=2, num_streams=2, seed=11, owner=own)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX, seed=11, owner=own)
+    rng = np.random.default_rng(3)
+    for b in range(2):
+        seeds = rng.permutation(n)[:batch]
+        v = sl.slice(seeds, b)
+        _compare(v, orc.slice(seeds, b))
+        # idempotence: the same batch index gives the same sample again, on another slot
+        v2 = sl.slice(seeds, b)
+        assert refstream.digest_view(v) == refstream.digest_view(v2)
+        v.release(); v2.release()
+    sl.close(); g.close()
+    torch.cuda.empty_cache()
+
+
+def test_full_size_reddit_shaped_dedup_stress():
+    """BASELINE config 3: 233 K nodes / ~115 M edges (avg degree ~490), 2-layer
+    fanout [25,10] -- every row draws, the frontier saturates towards all nodes."""
+    _full_size_case("reddit", [25, 10], 4, 4096)
+
+
+def test_full_size_full_neighbour_products():
+    """BASELINE config 4's slicing half: fanout -1 on the products shape, 2 layers;
+    bit-exact Bipartites (no rng on either side)."""
+    _full_size_case("products", [-1, -1], 4, 1024, owner="range")
+
+
 def test_reference_facing_module_end_to_end(tmp_path):
     """cslicer/test_py.py's loop, verbatim in shape, against the golden hashes:
     the module's own epoch shuffle + replayed draws reproduce the reference's

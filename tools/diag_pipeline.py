@@ -17,10 +17,12 @@ def rate(sl, nmb=256):
     ms, wall, e, _ = bench.run_pipeline(sl, batches, nmb // 64, 64, torch)
     return nmb / (ms * 1e-3)
 
-for slots, streams, gc in [(1, 1, 4), (2, 2, 4), (4, 4, 4), (8, 8, 4), (16, 16, 4), (32, 32, 4),
-                           (8, 8, 1), (8, 8, 2), (8, 8, 8), (16, 16, 2), (16, 4, 4), (16, 2, 4)]:
+import itertools
+for (slots, streams, gc), hints in itertools.product(
+        [(1, 1, 4), (2, 2, 4), (3, 3, 4), (4, 4, 4), (5, 5, 4), (6, 6, 4), (8, 8, 4), (12, 12, 4), (16, 16, 4),
+         (4, 4, 2), (4, 4, 8), (8, 8, 2)], [False, True]):
     sl = Slicer(g, bench.FANOUTS, 4, max_batch=4096, num_slots=slots, num_streams=streams, seed=7,
-                host_output=False, grid_ctas=gc)
+                host_output=False, grid_ctas=gc, l2_hints=hints)
     r = rate(sl)
     # CPU cost of submit alone: fill all slots without waiting
     torch.cuda.synchronize()
@@ -30,6 +32,6 @@ for slots, streams, gc in [(1, 1, 4), (2, 2, 4), (4, 4, 4), (8, 8, 4), (16, 16, 
     for s_ in ss:
         sl.wait_header(s_); sl.release(s_)
     t2 = time.perf_counter()
-    print(f"slots={slots:2d} streams={streams:2d} ctas/sm={gc}: {r:8.1f} mb/s | submit {1e6*(t1-t0)/slots:6.1f} us/call, "
+    print(f"hints={int(hints)} slots={slots:2d} streams={streams:2d} ctas/sm={gc}: {r:8.1f} mb/s | submit {1e6*(t1-t0)/slots:6.1f} us/call, "
           f"drain {1e6*(t2-t1)/slots:6.1f} us/mb", flush=True)
     sl.close()
