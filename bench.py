@@ -291,13 +291,9 @@ def own_arm(args):
     ms_e2e, wall_e2e, edges_e2e, slab_e2e = run_pipeline(hst, batches, args.steps, mbs, torch)
     barrier()
     clk = clocks.stop() if clocks else None
-    if dist is not None:
-        t = torch.tensor([ms_dev, ms_e2e], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e = float(t[0]), float(t[1])
-        c = torch.tensor([edges_dev, edges_e2e, slab_e2e], device=f"cuda:{local}", dtype=torch.int64)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        edges_dev, edges_e2e, slab_e2e = int(c[0]), int(c[1]), int(c[2])
+    from cslicer.sharding import reduce_job
+    ms_dev, (edges_dev,) = reduce_job(dist, f"cuda:{local}", ms_dev, [edges_dev])
+    ms_e2e, (edges_e2e, slab_e2e) = reduce_job(dist, f"cuda:{local}", ms_e2e, [edges_e2e, slab_e2e])
     total_mb = args.steps * mbs * world
     value = total_mb / (ms_dev * 1e-3)
     e2e = total_mb / (ms_e2e * 1e-3)

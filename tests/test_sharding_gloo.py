@@ -1,0 +1,66 @@
+"""N > 1 host logic on CPU: world_size-2 gloo processes shard an epoch's batches
+with no overlap and no gap, and the whole-job reduction (max time, summed
+counters) is what bench.py reports."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from cslicer.sharding import epoch_batches, rank_batch_ids, reduce_job
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    perm = np.random.default_rng(5).permutation(10_007).astype(np.int64)  # same on every rank
+    mine = epoch_batches(perm, 512, rank, world)
+    ids = torch.tensor([b for b, _ in mine], dtype=torch.int64)
+    seeds = sum(len(s) for _, s in mine)
+    gathered = [torch.zeros(16, dtype=torch.int64) for _ in range(world)]
+    pad = torch.full((16,), -1, dtype=torch.int64)
+    pad[:ids.numel()] = ids
+    dist.all_gather(gathered, pad)
+    ms, (tot_seeds, tot_batches) = reduce_job(dist, "cpu", 10.0 * (rank + 1), [seeds, len(mine)])
+    if rank == 0:
+        allb = sorted(int(x) for g in gathered for x in g.tolist() if x >= 0)
+        out.put((allb, ms, tot_seeds, tot_batches))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_partition_the_epoch_and_reduce():
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    allb, ms, tot_seeds, tot_batches = out.get()
+    nb = (10_007 - 1) // 512 + 1
+    assert allb == list(range(nb))          # disjoint, complete
+    assert tot_batches == nb and tot_seeds == 10_007
+    assert ms == 20.0                        # max over ranks
+
+
+def test_rank_batch_ids_shapes():
+    assert rank_batch_ids(10, 0, 4).tolist() == [0, 4, 8]
+    assert rank_batch_ids(10, 3, 4).tolist() == [3, 7]
+    assert rank_batch_ids(2, 3, 4).tolist() == []
+    got = np.sort(np.concatenate([rank_batch_ids(37, r, 8) for r in range(8)]))
+    assert got.tolist() == list(range(37))
