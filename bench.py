@@ -46,6 +46,30 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# Libraries (NCCL's version banner, ...) write to fd 1; the contract is ONE JSON
+# line on stdout, so fd 1 is pointed at stderr for the run and the line goes to
+# the saved descriptor.
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = json.dumps(obj) + "\n"
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line.encode())
+
+
 def load_graph(shape, device):
     """Seeded synthetic CSR; cached on disk so the two arms share one graph."""
     from cslicer.synth import synth_graph
@@ -353,6 +377,10 @@ def own_arm(args):
                "clocks": clk, "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(ip, ix, P, batches, args)
+            try:
+                out["reference_config"] = reference_config(ip, ix, g, args, torch)
+            except Exception as e:  # context only; never fail the bench line on it
+                out["reference_config"] = {"unavailable": f"{type(e).__name__}: {e}"}
     dev.close()
     hst.close()
     g.close()
@@ -360,7 +388,7 @@ def own_arm(args):
         dist.barrier()
         dist.destroy_process_group()
     if out is not None:
-        print(json.dumps(out), flush=True)
+        emit(out)
 
 
 def host_cores():
@@ -390,6 +418,46 @@ def cpu_baseline(ip, ix, P, batches, args):
             "sample": f"{nb} minibatches of the same workload in {sec:.1f} s, {cores} threads "
                       "(one restated slicer per thread, WorkerPool.cpp:29-33)",
             "sampled_edges_per_s": round(erate, 1)}
+
+
+def reference_config(ip, ix, g, args, torch):
+    """The one configuration the UNMODIFIED reference can run (3 layers x fanout
+    10 with replacement, 4 parts, owner = id % 4): the compiled reference
+    (oracle/_ref, its own Slicer::run threads + ConQueues) on the host cores
+    beside the CUDA path on the same graph and batches."""
+    from cslicer.dataset import write_dataset
+    from cslicer.engine import Slicer
+    from oracle import oracle as O
+    if not O.ref_available():
+        return {"unavailable": "oracle/_ref/libcslicer_ref.so not built (no /root/reference at build time)"}
+    n = ip.size - 1
+    d = os.path.join(CACHE, f"{args.shape}_{GRAPH_SEED}_refdata")
+    if not os.path.exists(os.path.join(d, "meta.txt")):
+        write_dataset(d, ip, ix)
+    cores = host_cores()
+    batches = seed_batches(n, 8 * cores, 0, 1)
+    seeds = [b for _, b in batches]
+    t1 = O.ref_pool_time(d, 1, seeds[:4]) / 4
+    nb = int(max(cores, min(len(seeds), 8.0 / max(t1, 1e-3) * cores * 0.6)))
+    sec = O.ref_pool_time(d, cores, seeds[:nb])
+    sl = Slicer(g, [10, 10, 10], num_parts=4, max_batch=BATCH, num_slots=args.slots,
+                num_streams=args.streams, seed=7, grid_ctas=args.grid_ctas, host_output=False)
+    run_pipeline(sl, batches, 3, args.mb_per_step, torch)
+    ms, _, edges, _ = run_pipeline(sl, batches, 5, args.mb_per_step, torch)
+    sl.close()
+    hs = Slicer(g, [10, 10, 10], num_parts=4, max_batch=BATCH, num_slots=args.slots,
+                num_streams=args.streams, seed=7, grid_ctas=args.grid_ctas, host_output=True)
+    run_pipeline(hs, batches, 2, args.mb_per_step, torch)
+    ms2, _, _, _ = run_pipeline(hs, batches, 3, args.mb_per_step, torch)
+    hs.close()
+    return {"config": "3-layer fanout [10,10,10] with replacement, batch 4096, 4 parts, owner=id%4 "
+                      "(the only configuration the reference supports)",
+            "reference_cpu": {"kind": "reference", "value": round(nb / sec, 3), "unit": "minibatches/s",
+                              "cores": cores, "value_1_worker": round(1.0 / t1, 3),
+                              "sample": f"{nb} minibatches, {cores} reference Slicer threads; stdout silenced"},
+            "cuda_value": round(5 * args.mb_per_step / (ms * 1e-3), 2),
+            "cuda_e2e": round(3 * args.mb_per_step / (ms2 * 1e-3), 2),
+            "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
 
 
 def reference_arm(args):
@@ -444,7 +512,7 @@ def reference_arm(args):
                                       "slicer per thread (WorkerPool.cpp:29-33)"},
            "e2e": {"value": round(value, 3), "unit": "minibatches/s", "h2d_bytes_per_step": 0,
                    "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def main():
@@ -462,6 +530,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    capture_stdout()
     if args.impl == "reference":
         reference_arm(args)
     else:
