@@ -378,6 +378,10 @@ def own_arm(args):
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(ip, ix, P, batches, args)
             try:
+                out["feature_gather"] = feature_gather_line(ip, g, args, torch, batches, peak)
+            except Exception as e:
+                out["feature_gather"] = {"unavailable": f"{type(e).__name__}: {e}"}
+            try:
                 out["reference_config"] = reference_config(ip, ix, g, args, torch)
             except Exception as e:  # context only; never fail the bench line on it
                 out["reference_config"] = {"unavailable": f"{type(e).__name__}: {e}"}
@@ -458,6 +462,40 @@ def reference_config(ip, ix, g, args, torch):
             "cuda_value": round(5 * args.mb_per_step / (ms * 1e-3), 2),
             "cuda_e2e": round(3 * args.mb_per_step / (ms2 * 1e-3), 2),
             "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
+
+
+def feature_gather_line(ip, g, args, torch, batches, peak):
+    """BASELINE config 4's other half: the fused input-feature gather (602-dim
+    fp32, seed 4321) -- rows of the last layer's in_nodes_g, part after part,
+    appended to every sample's CUDA graph.  HBM-bound: whole 2408-byte rows."""
+    from cslicer.engine import Features, Slicer
+    n, dim = ip.size - 1, 602
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(4321)
+    rows = torch.rand((n, dim), generator=gen, device="cuda", dtype=torch.float32).cpu().numpy()
+    F = Features(rows)
+    del rows
+    sl = Slicer(g, FANOUTS, num_parts=args.parts, max_batch=BATCH, num_slots=3, num_streams=3, seed=7,
+                grid_ctas=args.grid_ctas, host_output=False, features=F)
+    run_pipeline(sl, batches, 1, 12, torch)
+    ms, _, edges, _ = run_pipeline(sl, batches, 4, 12, torch)
+    v = sl.slice(batches[0][1], batches[0][0])
+    nrows = v.feature_rows
+    v.release()
+    tk = []
+    for r in range(6):
+        prof = dict(sl.profile(batches[r][1], batches[r][0]))
+        tk.append(prof["gather_features"])
+    k_ms = float(np.mean(tk[1:]))
+    nbytes = 2 * nrows * dim * 4
+    sl.close()
+    F.close()
+    return {"dim": dim, "rows_per_minibatch": int(nrows), "bytes_per_minibatch": int(nbytes),
+            "kernel_ms": round(k_ms, 4), "achieved_gbs": round(nbytes / (k_ms * 1e-3) / 1e9, 1),
+            "frac_of_hbm_peak": round(nbytes / (k_ms * 1e-3) / 1e9 / peak, 4),
+            "minibatches_per_s_with_gather": round(48 / (ms * 1e-3), 2),
+            "note": "algorithmic bytes = one read + one write of every gathered row; slicing + gather "
+                    "pipelined on 3 slots"}
 
 
 def reference_arm(args):

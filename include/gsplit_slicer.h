@@ -81,8 +81,15 @@ typedef struct {
   gs_span frontier[GS_MAX_LAYERS + 1];
   gs_span field[GS_MAX_LAYERS][GS_MAX_PARTS][GS_NUM_FIELDS];
   uint64_t draw_base[GS_MAX_LAYERS];
-  int32_t reserved[6];
+  int32_t late_status;   /* device-internal: error raised inside a tiled kernel */
+  int32_t feature_rows;  /* rows written by the fused feature gather (0 without features) */
+  int32_t feature_part_off[GS_MAX_PARTS + 1]; /* row offset of each part's block in the feature slab */
+  int32_t reserved[3];
 } gs_sample_header;
+
+typedef struct gs_graph gs_graph;
+typedef struct gs_slicer gs_slicer;
+typedef struct gs_features gs_features;
 
 typedef struct {
   int32_t abi_version;             /* GS_ABI_VERSION */
@@ -105,10 +112,10 @@ typedef struct {
   int32_t use_graph;               /* 1 (default via gs_config_default): CUDA-graph replay */
   int32_t l2_hints;                /* 1 (default): L2 eviction-priority hints, tables kept resident */
   int32_t reserved0;
+  gs_features *features;           /* optional: fuse the input-feature gather into every sample */
+  int64_t feature_rows_capacity;   /* 0 = derive (rows of the last layer's in_nodes, all parts) */
 } gs_config;
 
-typedef struct gs_graph gs_graph;
-typedef struct gs_slicer gs_slicer;
 
 const char *gs_last_error(void);
 int gs_abi_version(void);
@@ -123,6 +130,24 @@ int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
 int gs_graph_destroy(gs_graph *g);
 int64_t gs_graph_num_nodes(const gs_graph *g);
 int64_t gs_graph_num_edges(const gs_graph *g);
+
+/* Node features resident in HBM (replaces Dataset::features, dataset.cpp:38-48,
+ * and the gather half of python/utils/memory_manager.py:75-104 /
+ * python/data/bipartite.py:61-67).  rows_host: [num_rows x dim] fp32, row of
+ * node id at index id / id_div (id_div = 1 for a full replica; = num_parts for a
+ * shard that holds only the nodes with id % num_parts == part). */
+int gs_features_create(int device, int64_t num_rows, int32_t dim, int32_t id_div,
+                       const float *rows_host, gs_features **out);
+int gs_features_destroy(gs_features *f);
+/* Standalone gather on device pointers: out[i, :] = rows[ids[i] / id_div, :].
+ * stream: a cudaStream_t (NULL = default stream).  Asynchronous. */
+int gs_features_gather(gs_features *f, const int32_t *ids_device, int64_t n,
+                       float *out_device, void *stream);
+/* Fused gather of a completed slot (gs_config.features set): the feature slab
+ * holds, part after part, the rows of the LAST layer's in_nodes_g -- the input
+ * block each GPU reads.  Offsets are in gs_sample_header.feature_part_off. */
+int gs_slicer_feature_slab(gs_slicer *s, int32_t slot, const float **device_rows,
+                           int32_t *dim);
 
 /* Replaces CSlicer::CSlicer + WorkerPool::WorkerPool + Slicer::Slicer
  * (pyfrontend.cpp:41-70, WorkerPool.cpp:4-35, slicer.h:41-72): allocates the

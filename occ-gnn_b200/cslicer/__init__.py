@@ -22,9 +22,9 @@ import numpy as np
 
 from . import _native
 from .dataset import Dataset, write_dataset  # noqa: F401
-from .engine import Graph, SampleView, Slicer, reference_shuffle  # noqa: F401
+from .engine import Features, Graph, SampleView, Slicer, reference_shuffle  # noqa: F401
 
-__all__ = ["cslicer", "sample", "bipatite", "test_list", "test_pyfront", "Graph", "Slicer",
+__all__ = ["cslicer", "sample", "bipatite", "test_list", "test_pyfront", "Graph", "Slicer", "Features",
            "Dataset", "write_dataset"]
 
 # pyfrontend.cpp:24 hard-codes this root; overridable here by env or keyword.

@@ -24,7 +24,8 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
-           "gs_slicer_slot_bytes", "gs_reference_shuffle"]
+           "gs_slicer_slot_bytes", "gs_reference_shuffle", "gs_features_create",
+           "gs_features_destroy", "gs_features_gather", "gs_slicer_feature_slab"]
 
 
 class Span(C.Structure):
@@ -40,7 +41,9 @@ class SampleHeader(C.Structure):
                 ("frontier", Span * (MAX_LAYERS + 1)),
                 ("field", ((Span * NUM_FIELDS) * MAX_PARTS) * MAX_LAYERS),
                 ("draw_base", C.c_uint64 * MAX_LAYERS),
-                ("reserved", C.c_int32 * 6)]
+                ("late_status", C.c_int32), ("feature_rows", C.c_int32),
+                ("feature_part_off", C.c_int32 * (MAX_PARTS + 1)),
+                ("reserved", C.c_int32 * 3)]
 
 
 class Config(C.Structure):
@@ -51,7 +54,8 @@ class Config(C.Structure):
                 ("num_slots", C.c_int32), ("num_streams", C.c_int32), ("host_output", C.c_int32),
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
                 ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32),
-                ("l2_hints", C.c_int32), ("reserved0", C.c_int32)]
+                ("l2_hints", C.c_int32), ("reserved0", C.c_int32),
+                ("features", C.c_void_p), ("feature_rows_capacity", C.c_int64)]
 
 
 _lib = None
@@ -91,6 +95,12 @@ def lib():
     L.gs_slicer_slot_bytes.restype = C.c_int64
     L.gs_slicer_slot_bytes.argtypes = [C.c_void_p]
     L.gs_reference_shuffle.argtypes = [C.c_void_p, C.c_int64, C.c_int]
+    L.gs_features_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                     C.POINTER(C.c_void_p)]
+    L.gs_features_destroy.argtypes = [C.c_void_p]
+    L.gs_features_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    L.gs_slicer_feature_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                         C.POINTER(C.c_int32)]
     if L.gs_abi_version() != ABI_VERSION:
         raise ImportError("libgsplit_slicer.so ABI version mismatch; rebuild")
     _lib = L

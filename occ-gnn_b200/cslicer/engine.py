@@ -43,6 +43,39 @@ class Graph:
     __del__ = close
 
 
+class Features:
+    """Node features resident in HBM (gs_features).  rows: [num_rows, dim] fp32;
+    node id lives at row id // id_div (id_div=1: full replica; =P: the shard of
+    one part under owner = id % P)."""
+
+    def __init__(self, rows, device=0, id_div=1):
+        r = np.ascontiguousarray(rows, dtype=np.float32)
+        if r.ndim != 2:
+            raise ValueError("features must be [num_rows, dim]")
+        self.num_rows, self.dim, self.device, self.id_div = int(r.shape[0]), int(r.shape[1]), int(device), int(id_div)
+        h = C.c_void_p()
+        N.check(N.lib().gs_features_create(self.device, self.num_rows, self.dim, self.id_div,
+                                           r.ctypes.data, C.byref(h)))
+        self._h = h
+
+    def gather(self, ids):
+        """ids: int32 CUDA tensor -> [len(ids), dim] fp32 CUDA tensor (own kernel,
+        enqueued on torch's current stream)."""
+        import torch
+        ids = ids.to(device=f"cuda:{self.device}", dtype=torch.int32).contiguous()
+        out = torch.empty((ids.numel(), self.dim), dtype=torch.float32, device=ids.device)
+        N.check(N.lib().gs_features_gather(self._h, ids.data_ptr(), ids.numel(), out.data_ptr(),
+                                           torch.cuda.current_stream(ids.device).cuda_stream))
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            N.lib().gs_features_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
 class SampleView:
     """One completed sample in a slot: header + views into the slab."""
 
@@ -59,6 +92,8 @@ class SampleView:
         self._spans = [[[(hdr.field[l][g][f].off, hdr.field[l][g][f].len)
                          for f in range(N.NUM_FIELDS)] for g in range(P)] for l in range(L)]
         self._dev_ptr, self._host_ptr = dev_ptr, host_ptr
+        self.feature_rows = int(hdr.feature_rows)
+        self.feature_part_off = [int(hdr.feature_part_off[g]) for g in range(P + 1)]
         self._host = None
         self._released = False
         if host_ptr:
@@ -97,6 +132,28 @@ class SampleView:
 
     def frontier_tensor(self, l):
         return self._dev(*self._frontier[l])
+
+    def features(self, g):
+        """Fused gather result for part g: rows of the last layer's in_nodes_g,
+        [len(in_nodes_g), dim] fp32 device tensor (zero-copy view of the slot's feature slab)."""
+        import torch
+        if self._released:
+            raise RuntimeError("sample slot already released")
+        ptr, dim = C.c_void_p(), C.c_int32()
+        N.check(N.lib().gs_slicer_feature_slab(self._slicer._h, self.slot, C.byref(ptr), C.byref(dim)))
+        a, b = self.feature_part_off[g], self.feature_part_off[g + 1]
+        dev = f"cuda:{self._slicer.graph.device}"
+        if b == a:
+            return torch.empty((0, dim.value), dtype=torch.float32, device=dev)
+
+        class _F:
+            pass
+        f = _F()
+        f.__cuda_array_interface__ = {"shape": (b - a, dim.value), "typestr": "<f4",
+                                      "data": (ptr.value + 4 * a * dim.value, False), "version": 2,
+                                      "strides": None}
+        f._owner = self
+        return torch.as_tensor(f, device=dev)
 
     def field_len(self, l, g, name):
         return self._span(l, g, name)[1]
@@ -142,7 +199,8 @@ class Slicer:
 
     def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
                  seed=0, owner=None, draws=None, host_output=True, use_graph=True,
-                 frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True):
+                 frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True,
+                 features=None, feature_rows_capacity=0):
         L = N.lib()
         self.graph = graph
         cfg = N.Config()
@@ -157,6 +215,10 @@ class Slicer:
         cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)
         cfg.slab_capacity, cfg.grid_ctas = int(slab_capacity), int(grid_ctas)
         cfg.l2_hints = int(bool(l2_hints))
+        self.features = features
+        if features is not None:
+            cfg.features = features._h
+            cfg.feature_rows_capacity = int(feature_rows_capacity)
         keep = []
         if owner is not None:
             o = np.ascontiguousarray(owner, dtype=np.int32)

@@ -58,8 +58,17 @@ struct gs_graph {
   int32_t *indices = nullptr;
 };
 
+struct gs_features {
+  int device = 0;
+  int64_t num_rows = 0;
+  int32_t dim = 0, id_div = 1;
+  float *rows = nullptr;
+};
+
 struct gs_slicer {
   gs_graph *g = nullptr;
+  gs_features *feat = nullptr;
+  int64_t feat_cap_rows = 0;
   gs_config cfg{};
   int grid = 0;                       // CTAs of a full-machine launch
   int grid_rows[GS_MAX_LAYERS] = {0};  // per layer: enough CTAs for the largest possible frontier
@@ -125,6 +134,10 @@ int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEven
     if ((rc = mark(kNames[6]))) return rc;
     gs_launch_relabel(sl.ws, l, gc, st);
     if ((rc = mark(kNames[7]))) return rc;
+  }
+  if (s->feat) {
+    gs_launch_gather_sample(sl.ws, s->grid, st);
+    if ((rc = mark("gather_features"))) return rc;
   }
   gs_launch_finish(sl.ws, s->grid, st);
   if ((rc = mark("finish"))) return rc;
@@ -290,6 +303,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   s->cfg = *cfg;
   s->cfg.owner_host = nullptr;
   s->cfg.draws_host = nullptr;
+  s->cfg.features = nullptr;
   const int64_t N = g->num_nodes, M = g->num_edges;
   int64_t Fb[GS_MAX_LAYERS] = {0}, Cb[GS_MAX_LAYERS] = {0};
   compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap, Fb, Cb);
@@ -298,6 +312,18 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     delete s;
     return fail(GS_ERR_INVALID, "derived capacities exceed 2^31 positions; lower max_batch or set "
                                 "cand_capacity / slab_capacity");
+  }
+  if (cfg->features) {
+    if (cfg->features->device != g->device) {
+      delete s;
+      return fail(GS_ERR_INVALID, "features live on device %d, graph on %d", cfg->features->device,
+                  g->device);
+    }
+    s->feat = cfg->features;
+    const int last = cfg->num_layers - 1;
+    const int64_t e_last = Cb[last] - Fb[last];
+    s->feat_cap_rows = cfg->feature_rows_capacity > 0 ? cfg->feature_rows_capacity
+                                                      : std::max<int64_t>(1, std::min(N, e_last));
   }
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g->device);
@@ -407,6 +433,14 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.ctile_cnt, (size_t)GS_NC_MAX * s->grid);
     DA(w.ftile_cnt, (size_t)GS_NF_MAX * ftiles);
     DA(w.tickets, 8);
+    if (s->feat) {
+      w.feat = s->feat->rows;
+      w.feat_dim = s->feat->dim;
+      w.feat_div = s->feat->id_div;
+      w.feat_rows = s->feat->num_rows;
+      w.feat_cap_rows = s->feat_cap_rows;
+      DA(w.feat_out, (size_t)s->feat_cap_rows * s->feat->dim);
+    }
 #undef DA
     s->slot_bytes = bytes;
     CUS(cudaMemset(w.hdr, 0, sizeof(gs_sample_header)));
@@ -489,7 +523,7 @@ int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_
 
 static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out) {
   sl.state = SLOT_DONE;
-  const int st = sl.hdr_host->status;
+  const int st = sl.hdr_host->status ? sl.hdr_host->status : sl.hdr_host->late_status;
   if (hdr_out) *hdr_out = sl.hdr_host;
   if (st != 0) {
     // a sample that stopped half way may have left touched table entries behind
@@ -498,8 +532,9 @@ static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out)
     if (st == GS_ERR_OVERFLOW)
       return fail(GS_ERR_OVERFLOW,
                   "sample outgrew its workspace (frontier_capacity=%lld cand_capacity=%lld "
-                  "slab_capacity=%lld): raise them in gs_config",
-                  (long long)s->Fcap, (long long)s->Ccap, (long long)s->slab_cap);
+                  "slab_capacity=%lld feature_rows_capacity=%lld): raise them in gs_config",
+                  (long long)s->Fcap, (long long)s->Ccap, (long long)s->slab_cap,
+                  (long long)s->feat_cap_rows);
     if (st == GS_ERR_SEED)
       return fail(GS_ERR_SEED, "seed ids must be distinct and in [0, num_nodes)");
     return fail(st, "device raised status %d", st);
@@ -570,6 +605,66 @@ int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64
   return rc;
 }
 
+int gs_features_create(int device, int64_t num_rows, int32_t dim, int32_t id_div,
+                       const float *rows_host, gs_features **out) {
+  if (!out || !rows_host) return fail(GS_ERR_INVALID, "NULL argument");
+  if (num_rows < 1 || dim < 1 || id_div < 1) return fail(GS_ERR_INVALID, "num_rows, dim, id_div must be >= 1");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(GS_ERR_CUDA, "no CUDA device (%s): this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  CU(cudaSetDevice(device));
+  gs_features *f = new (std::nothrow) gs_features();
+  if (!f) return fail(GS_ERR_INVALID, "out of host memory");
+  f->device = device;
+  f->num_rows = num_rows;
+  f->dim = dim;
+  f->id_div = id_div;
+  const size_t bytes = (size_t)num_rows * dim * sizeof(float);
+  cudaError_t ce = cudaMalloc((void **)&f->rows, bytes);
+  if (ce == cudaSuccess) ce = cudaMemcpy(f->rows, rows_host, bytes, cudaMemcpyHostToDevice);
+  if (ce != cudaSuccess) {
+    cudaFree(f->rows);
+    delete f;
+    return fail(GS_ERR_CUDA, "feature upload failed: %s", cudaGetErrorString(ce));
+  }
+  *out = f;
+  return GS_OK;
+}
+
+int gs_features_destroy(gs_features *f) {
+  if (!f) return GS_OK;
+  cudaSetDevice(f->device);
+  cudaFree(f->rows);
+  delete f;
+  return GS_OK;
+}
+
+int gs_features_gather(gs_features *f, const int32_t *ids_device, int64_t n, float *out_device,
+                       void *stream) {
+  if (!f || (n > 0 && (!ids_device || !out_device))) return fail(GS_ERR_INVALID, "NULL argument");
+  if (n <= 0) return GS_OK;
+  CU(cudaSetDevice(f->device));
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, f->device);
+  const int grid = (int)std::min<int64_t>((n + GS_NW - 1) / GS_NW, (int64_t)sms * 8);
+  gs_launch_gather_ids(f->rows, f->dim, f->id_div, f->num_rows, ids_device, n, out_device, grid,
+                       (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  return GS_OK;
+}
+
+int gs_slicer_feature_slab(gs_slicer *s, int32_t slot, const float **device_rows, int32_t *dim) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  if (!s->feat) return fail(GS_ERR_STATE, "slicer was created without gs_config.features");
+  Slot &sl = s->slots[slot];
+  if (sl.state != SLOT_DONE) return fail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (device_rows) *device_rows = sl.ws.feat_out;
+  if (dim) *dim = s->feat->dim;
+  return GS_OK;
+}
+
 int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset) {
   if (!nodes && n > 0) return fail(GS_ERR_INVALID, "NULL argument");
   if (reset) srand(1);
@@ -577,7 +672,9 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset) {
   return GS_OK;
 }
 
-int gs_slicer_launches_per_sample(const gs_slicer *s) { return s ? 2 + 8 * s->cfg.num_layers : 0; }
+int gs_slicer_launches_per_sample(const gs_slicer *s) {
+  return s ? 2 + 8 * s->cfg.num_layers + (s->feat ? 1 : 0) : 0;
+}
 int64_t gs_slicer_slot_bytes(const gs_slicer *s) { return s ? s->slot_bytes : 0; }
 
 }  // extern "C"

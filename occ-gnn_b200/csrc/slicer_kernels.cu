@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
     h->batch_index = ws.input->batch_index;
     h->draw_cursor = *ws.draw_cursor;
     h->edges = 0;
-    h->reserved[0] = 0;  // late error raised inside a tiled kernel
+    h->late_status = 0;  // late error raised inside a tiled kernel
     const int nn = bad ? 0 : n;
     h->slab_used = ((int64_t)nn + 3) & ~3ll;
     h->frontier_len[0] = nn;
@@ -576,7 +576,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
         const uint2 e = te[it];
         if (f & GS_CF_SELF) {
           ffirst = e.x > p;
-          if (e.y != p) h->reserved[0] = (int32_t)GS_ERR_SEED;  // duplicate seed
+          if (e.y != p) h->late_status = (int32_t)GS_ERR_SEED;  // duplicate seed
         } else if (!(f & GS_CF_LOOP)) {
           edge = true;
           ifirst = e.x == p;
@@ -605,8 +605,8 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, (int)gridDim.x, NC, s_tot, s_w);
   if (threadIdx.x == 0) {
     bool ok = true;
-    if (h->reserved[0] != 0) {
-      h->status = h->reserved[0];
+    if (h->late_status != 0) {
+      h->status = h->late_status;
       ok = false;
     }
     const uint32_t fnext = s_tot[0];
@@ -1031,6 +1031,76 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
   }
 }
 
+// ------------------------------------------------------------ feature gather
+// One warp per row: out[r, :] = rows[id / div, :].  602 fp32 = 2408 B rows are
+// 8-byte but not 16-byte multiples, so the vector width is chosen from dim
+// (float4 / float2 / float); rows are contiguous, so unlike the id work above this
+// kernel streams whole lines and is bounded by plain HBM bandwidth.
+template <typename V>
+__device__ __forceinline__ void copy_row(const float *__restrict__ src, float *__restrict__ dst,
+                                         int nvec, int lane) {
+  const V *s = reinterpret_cast<const V *>(src);
+  V *d = reinterpret_cast<V *>(dst);
+  int k = lane;
+  for (; k + 96 < nvec; k += 128) {  // four independent loads in flight per lane
+    const V a = __ldg(s + k), b = __ldg(s + k + 32), c = __ldg(s + k + 64), e = __ldg(s + k + 96);
+    d[k] = a; d[k + 32] = b; d[k + 64] = c; d[k + 96] = e;
+  }
+  for (; k < nvec; k += 32) d[k] = __ldg(s + k);
+}
+__device__ __forceinline__ void gather_row(const float *feat, int dim, int64_t src_row, float *out,
+                                           int64_t dst_row, int lane) {
+  const float *src = feat + src_row * dim;
+  float *dst = out + dst_row * dim;
+  if ((dim & 3) == 0) copy_row<float4>(src, dst, dim >> 2, lane);
+  else if ((dim & 1) == 0) copy_row<float2>(src, dst, dim >> 1, lane);
+  else copy_row<float>(src, dst, dim, lane);
+}
+
+// Fused into every sample's graph: the rows of the last layer's in_nodes_g, part
+// after part -- the block of input features GPU g reads for this minibatch
+// (python/data/bipartite.py:61-67 gather, memory_manager.py:75-104 refresh).
+__global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ int32_t s_off[GS_MAX_PARTS], s_start[GS_MAX_PARTS + 1];
+  const int P = ws.P, l = ws.L - 1;
+  if (threadIdx.x == 0) {
+    int32_t acc = 0;
+    for (int q = 0; q < P; q++) {
+      s_off[q] = h->field[l][q][GS_F_IN_NODES].off;
+      s_start[q] = acc;
+      acc += h->field[l][q][GS_F_IN_NODES].len;
+    }
+    s_start[P] = acc;
+    if (blockIdx.x == 0) {
+      const bool fits = (int64_t)acc <= ws.feat_cap_rows;
+      h->feature_rows = fits ? acc : 0;
+      for (int q = 0; q <= P; q++) h->feature_part_off[q] = q <= P ? s_start[q] : 0;
+      if (!fits) h->late_status = (int32_t)GS_ERR_OVERFLOW;  // folded into status by k_finish
+    }
+  }
+  __syncthreads();
+  const int R = s_start[P];
+  if ((int64_t)R > ws.feat_cap_rows) return;
+  const int lane = lane_id();
+  const int nwarps = gridDim.x * GS_NW;
+  for (int r = blockIdx.x * GS_NW + warp_id(); r < R; r += nwarps) {
+    int q = 0;
+    while (q + 1 < P && r >= s_start[q + 1]) q++;
+    const int32_t id = ws.slab[s_off[q] + (r - s_start[q])];
+    gather_row(ws.feat, ws.feat_dim, (int64_t)(id / ws.feat_div), ws.feat_out, r, lane);
+  }
+}
+
+__global__ void __launch_bounds__(GS_TPB) k_gather_ids(const float *feat, int dim, int div,
+                                                       const int32_t *ids, int64_t n, float *out) {
+  const int lane = lane_id();
+  const int64_t nwarps = (int64_t)gridDim.x * GS_NW;
+  for (int64_t r = (int64_t)blockIdx.x * GS_NW + warp_id(); r < n; r += nwarps)
+    gather_row(feat, dim, (int64_t)(ids[r] / div), out, r, lane);
+}
+
 __global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x)
@@ -1072,6 +1142,14 @@ void gs_launch_relabel(const GsWs &ws, int layer, int grid, cudaStream_t st) {
 }
 void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st) {
   k_finish<<<grid, GS_TPB, 0, st>>>(ws);
+}
+void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st) {
+  k_gather_sample<<<grid, GS_TPB, 0, st>>>(ws);
+}
+void gs_launch_gather_ids(const float *feat, int dim, int div, int64_t rows, const int32_t *ids,
+                          int64_t n, float *out, int grid, cudaStream_t st) {
+  (void)rows;
+  k_gather_ids<<<grid, GS_TPB, 0, st>>>(feat, dim, div, ids, n, out);
 }
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
   k_fill_u32<<<1184, 256, 0, st>>>(p, n, v);

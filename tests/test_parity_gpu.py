@@ -292,6 +292,46 @@ def test_full_size_full_neighbour_products():
     _full_size_case("products", [-1, -1], 4, 1024, owner="range")
 
 
+@pytest.mark.parametrize("dim,P,fanouts", [(602, 4, [-1, -1]), (128, 8, [15, 10, 5]), (7, 3, [5, 5])])
+def test_fused_feature_gather_matches_numpy(dim, P, fanouts):
+    """BASELINE config 4's gather half: rows of the last layer's in_nodes_g, fused
+    into the sample's graph; fp32 copy, so equality is exact (tolerance 0)."""
+    E = _engine()
+    import torch
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=12)
+    n = ip.size - 1
+    feat = np.random.default_rng(4321).random((n, dim), dtype=np.float32)
+    g = E.Graph(ip, ix)
+    F = E.Features(feat)
+    sl = E.Slicer(g, fanouts, P, max_batch=256, num_slots=2, seed=5, features=F)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX, seed=5)
+    seeds = np.random.default_rng(2).permutation(n)[:256]
+    v = sl.slice(seeds, 0)
+    r = orc.slice(seeds, 0)
+    _compare(v, r)
+    tot = 0
+    for p in range(P):
+        want = feat[r["layers"][-1][p]["in_nodes"]]
+        got = v.features(p).cpu().numpy()
+        assert got.shape == want.shape and np.array_equal(got, want)
+        tot += want.shape[0]
+    assert v.feature_rows == tot
+    # standalone gather on arbitrary ids, and a sharded store (owner = id % P: row id // P)
+    ids = torch.from_numpy(np.random.default_rng(1).integers(0, n, 5000).astype(np.int32)).cuda()
+    assert np.array_equal(F.gather(ids).cpu().numpy(), feat[ids.cpu().numpy()])
+    shard = E.Features(feat[1::P], id_div=P)  # nodes with id % P == 1
+    mine = ids[ids % P == 1]
+    assert np.array_equal(shard.gather(mine).cpu().numpy(), feat[mine.cpu().numpy()])
+    v.release()
+    small = E.Slicer(g, fanouts, P, max_batch=256, num_slots=1, seed=5, features=F, feature_rows_capacity=8)
+    from cslicer import _native as N
+    with pytest.raises(N.SlicerError) as e:
+        small.slice(seeds, 0)
+    assert e.value.code == N.ERR_OVERFLOW
+    small.close(); sl.close(); shard.close(); F.close(); g.close()
+
+
 def test_reference_facing_module_end_to_end(tmp_path):
     """cslicer/test_py.py's loop, verbatim in shape, against the golden hashes:
     the module's own epoch shuffle + replayed draws reproduce the reference's
