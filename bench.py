@@ -236,7 +236,7 @@ def random_accesses(view, P):
         tab += (C - F)              # k_expand: atomicMin
         tab += C                    # k_cand_flags: read
         tab += n_in                 # k_cand_apply: rank written back
-        tab += E                    # k_relabel: read
+        tab += E - n_in             # k_relabel: read, only for edges that are not a first occurrence
         tab += F                    # k_front_apply: read (self_ids_in)
     tab += view.frontier_len[view.num_layers]  # k_finish: sparse reset
     return csr, tab

@@ -71,6 +71,7 @@ struct gs_slicer {
   int64_t feat_cap_rows = 0;
   gs_config cfg{};
   int grid = 0;                       // CTAs of a full-machine launch
+  int grid_full = 0;                  // 8 CTAs per SM: full occupancy for the streaming gather
   int grid_rows[GS_MAX_LAYERS] = {0};  // per layer: enough CTAs for the largest possible frontier
   int grid_cand[GS_MAX_LAYERS] = {0};  // ... and candidate stream (static upper bounds)
   int64_t Fcap = 0, Ccap = 0, slab_cap = 0;
@@ -136,7 +137,7 @@ int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEven
     if ((rc = mark(kNames[7]))) return rc;
   }
   if (s->feat) {
-    gs_launch_gather_sample(sl.ws, s->grid, st);
+    gs_launch_gather_sample(sl.ws, s->grid_full, st);  // streaming kernel: wants every warp slot
     if ((rc = mark("gather_features"))) return rc;
   }
   gs_launch_finish(sl.ws, s->grid, st);
@@ -331,6 +332,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   // the device, so each launch gets the grid its layer's static upper bound
   // needs, capped at the full-machine grid (tile loops stride over the rest).
   s->grid = (cfg->grid_ctas > 0 ? cfg->grid_ctas : 4) * sms;
+  s->grid_full = 8 * sms;
   for (int l = 0; l < cfg->num_layers; l++) {
     const int64_t fb = std::min(Fb[l], s->Fcap), cb = std::min(Cb[l], s->Ccap);
     s->grid_rows[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (fb + GS_TILE - 1) / GS_TILE));

@@ -740,12 +740,17 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
           const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
           const uint32_t me = __ballot_sync(FULL, edge && g == q);
           const uint32_t ex = re[q] + __popc(me & ltm);  // part-q edges before this position
+          // An edge whose source occurs here for the first time knows its own
+          // rank: it writes the final csr_indices value.  Every other edge
+          // leaves ~id (negative) for k_relabel, which then only looks up those.
+          int32_t ixv = ~cv[r];
           if (ifirst && g == q) {
             const uint32_t rk = ri[q] + __popc(mi & ltm);
             ws.slab[s_in_off[q] + rk] = cv[r];
             tbl.stx(cv[r], rk);
+            ixv = (int32_t)rk;
           }
-          if (edge && g == q) ws.slab[s_ix_off[q] + ex] = cv[r];
+          if (edge && g == q) ws.slab[s_ix_off[q] + ex] = ixv;
           if (isself) ws.rowscan[(size_t)ci[r] * P + q] = ex;
           ri[q] += __popc(mi);
           re[q] += __popc(me);
@@ -989,14 +994,14 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        v[k] = e < sp.len ? ix[e] : -1;
+        v[k] = e < sp.len ? ix[e] : 0;  // >= 0: already final (written by the first occurrence)
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] >= 0 ? tbl.ldx(v[k]) : 0u;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? tbl.ldx(~v[k]) : 0u;
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        if (e < sp.len) ix[e] = (int32_t)r[k];
+        if (v[k] < 0) ix[e] = (int32_t)r[k];
       }
     }
   }
