@@ -35,7 +35,8 @@ typedef enum {
   GS_ERR_BUSY = 3,     /* no free sample slot: release one first */
   GS_ERR_OVERFLOW = 4, /* a sample outgrew its workspace: raise the capacities */
   GS_ERR_SEED = 5,     /* seed id out of range */
-  GS_ERR_STATE = 6     /* slot not in the state the call needs */
+  GS_ERR_STATE = 6,    /* slot not in the state the call needs */
+  GS_ERR_PEER = 7      /* partitioned mode: a peer rank failed or never reached a barrier */
 } gs_status;
 
 typedef enum { GS_RNG_PHILOX = 0, GS_RNG_DRAWS = 1 } gs_rng_mode;
@@ -194,6 +195,82 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
 int gs_slicer_launches_per_sample(const gs_slicer *s);
 /* Device bytes held by one slot / by the slicer. */
 int64_t gs_slicer_slot_bytes(const gs_slicer *s);
+
+/* ------------------------------------------------------------------------
+ * Partitioned mode: one rank per GPU, rank g of num_parts holds
+ * only the CSR rows (and a dedup table) of the nodes it owns and produces
+ * B[layer][g] -- what GPU g of the reference's 4-GPU layout consumes
+ * (slicer.cpp:36-43 routes an edge to the bipartite of the source's owner).
+ * Ranks exchange sampled edges and new frontier nodes with their own stores /
+ * reductions into peer memory over NVLink (arenas mapped with CUDA IPC, or
+ * directly when several ranks share a process); no host round trip and no
+ * library collective sits on the data path.  Every rank must be given the same
+ * batches in the same order.  The reference has no counterpart (one process,
+ * whole graph in host memory, dataset.cpp:18-36); outputs are bit-identical to
+ * part g of the single-GPU slicer above and of the oracle.
+ * ------------------------------------------------------------------------ */
+typedef enum { GS_OWNER_MOD = 0, GS_OWNER_RANGE = 1 } gs_owner_mode;
+
+typedef struct gs_pslicer gs_pslicer;
+
+typedef struct {
+  int32_t abi_version;
+  int32_t num_layers;
+  int32_t fanouts[GS_MAX_LAYERS];
+  int32_t num_parts;                       /* = number of ranks */
+  int32_t rank;
+  int32_t owner_mode;                      /* gs_owner_mode */
+  int32_t range_bounds[GS_MAX_PARTS + 1];  /* GS_OWNER_RANGE: part q owns [b[q], b[q+1]) */
+  uint64_t seed;                           /* philox key (same on every rank) */
+  int32_t max_batch;
+  int32_t num_slots;                       /* samples that may be held unreleased */
+  int32_t host_output;
+  int32_t grid_ctas;                       /* 0 = 4 CTAs per SM */
+  int32_t timeout_ms;                      /* barrier timeout; 0 = 5000 */
+  int32_t use_graph;                       /* 1: one CUDA graph per slot (gs_pslicer_submit) */
+  int64_t frontier_capacity;               /* 0 = derive; must agree on all ranks */
+  int64_t cand_capacity;
+  int64_t slab_capacity;
+  int64_t num_edges_global;                /* bounds fanout -1 layers; 0 = unknown */
+  void *stream;                            /* cudaStream_t to run on; NULL = own stream */
+} gs_pconfig;
+
+void gs_pconfig_default(gs_pconfig *cfg);
+
+/* indptr_local_host: [n_local + 1] row offsets of the nodes this rank owns, in
+ * local-index order (GS_OWNER_MOD: id / num_parts; GS_OWNER_RANGE: id - b[rank]);
+ * indices_local_host: their neighbour lists, GLOBAL ids. */
+int gs_pslicer_create(int device, int64_t num_nodes_global, int64_t n_local, int64_t m_local,
+                      const int64_t *indptr_local_host, const int64_t *indices_local_host,
+                      const gs_pconfig *cfg, gs_pslicer **out);
+int gs_pslicer_destroy(gs_pslicer *s);
+/* 64-byte cudaIpcMemHandle_t of this rank's arena, to be sent to every peer. */
+int gs_pslicer_ipc_handle(gs_pslicer *s, void *handle64);
+int gs_pslicer_connect_ipc(gs_pslicer *s, int32_t peer_rank, const void *handle64);
+/* Peer living in the same process (tests / single-GPU emulation of P ranks). */
+int gs_pslicer_connect_local(gs_pslicer *s, int32_t peer_rank, gs_pslicer *peer);
+/* All peers connected: freeze the launch sequence (captures the CUDA graphs). */
+int gs_pslicer_ready(gs_pslicer *s);
+
+/* One minibatch = gs_pslicer_num_segments() launch segments separated by the
+ * inter-rank barriers.  gs_pslicer_submit = stage + every segment + commit (one
+ * process per rank).  stage / enqueue / commit expose the segments so that
+ * several ranks sharing ONE stream can be interleaved segment by segment. */
+int gs_pslicer_num_segments(const gs_pslicer *s);
+int gs_pslicer_submit(gs_pslicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                      int32_t *slot_out);
+int gs_pslicer_stage(gs_pslicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                     int32_t *slot_out);
+int gs_pslicer_enqueue(gs_pslicer *s, int32_t slot, int32_t seg_lo, int32_t seg_hi);
+int gs_pslicer_commit(gs_pslicer *s, int32_t slot);
+int gs_pslicer_wait(gs_pslicer *s, int32_t slot, const gs_sample_header **hdr_out);
+int gs_pslicer_slab(gs_pslicer *s, int32_t slot, const int32_t **device_slab,
+                    const int32_t **host_slab);
+int gs_pslicer_release(gs_pslicer *s, int32_t slot);
+/* After any error: every rank calls this (all streams idle) before the next submit. */
+int gs_pslicer_reset(gs_pslicer *s);
+int gs_pslicer_launches_per_sample(const gs_pslicer *s);
+int64_t gs_pslicer_device_bytes(const gs_pslicer *s);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,8 @@ LIB_PATH = os.path.join(HERE, "libgsplit_slicer.so")
 
 MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 1
 RNG_PHILOX, RNG_DRAWS = 0, 1
-OK, ERR_INVALID, ERR_CUDA, ERR_BUSY, ERR_OVERFLOW, ERR_SEED, ERR_STATE = range(7)
+OK, ERR_INVALID, ERR_CUDA, ERR_BUSY, ERR_OVERFLOW, ERR_SEED, ERR_STATE, ERR_PEER = range(8)
+OWNER_MOD, OWNER_RANGE = 0, 1
 FIELDS = ["in_nodes", "out_nodes", "owned_out_nodes", "from_ids", "to_ids", "self_ids_in",
           "self_ids_out", "csr_indptr", "csr_indices"]
 NUM_FIELDS = len(FIELDS)
@@ -25,7 +26,14 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_reference_shuffle", "gs_features_create",
-           "gs_features_destroy", "gs_features_gather", "gs_slicer_feature_slab"]
+           "gs_features_destroy", "gs_features_gather", "gs_slicer_feature_slab",
+           # partitioned mode (one rank per GPU)
+           "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
+           "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
+           "gs_pslicer_num_segments", "gs_pslicer_submit", "gs_pslicer_stage",
+           "gs_pslicer_enqueue", "gs_pslicer_commit", "gs_pslicer_wait", "gs_pslicer_slab",
+           "gs_pslicer_release", "gs_pslicer_reset", "gs_pslicer_launches_per_sample",
+           "gs_pslicer_device_bytes"]
 
 
 class Span(C.Structure):
@@ -56,6 +64,18 @@ class Config(C.Structure):
                 ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32),
                 ("l2_hints", C.c_int32), ("reserved0", C.c_int32),
                 ("features", C.c_void_p), ("feature_rows_capacity", C.c_int64)]
+
+
+class PConfig(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("num_layers", C.c_int32),
+                ("fanouts", C.c_int32 * MAX_LAYERS), ("num_parts", C.c_int32),
+                ("rank", C.c_int32), ("owner_mode", C.c_int32),
+                ("range_bounds", C.c_int32 * (MAX_PARTS + 1)), ("seed", C.c_uint64),
+                ("max_batch", C.c_int32), ("num_slots", C.c_int32), ("host_output", C.c_int32),
+                ("grid_ctas", C.c_int32), ("timeout_ms", C.c_int32), ("use_graph", C.c_int32),
+                ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
+                ("slab_capacity", C.c_int64), ("num_edges_global", C.c_int64),
+                ("stream", C.c_void_p)]
 
 
 _lib = None
@@ -101,6 +121,26 @@ def lib():
     L.gs_features_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     L.gs_slicer_feature_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                          C.POINTER(C.c_int32)]
+    L.gs_pconfig_default.argtypes = [C.POINTER(PConfig)]
+    L.gs_pslicer_create.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                    C.POINTER(PConfig), C.POINTER(C.c_void_p)]
+    L.gs_pslicer_destroy.argtypes = [C.c_void_p]
+    L.gs_pslicer_ipc_handle.argtypes = [C.c_void_p, C.c_void_p]
+    L.gs_pslicer_connect_ipc.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.gs_pslicer_connect_local.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.gs_pslicer_ready.argtypes = [C.c_void_p]
+    L.gs_pslicer_num_segments.argtypes = [C.c_void_p]
+    L.gs_pslicer_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64, C.POINTER(C.c_int32)]
+    L.gs_pslicer_stage.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64, C.POINTER(C.c_int32)]
+    L.gs_pslicer_enqueue.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+    L.gs_pslicer_commit.argtypes = [C.c_void_p, C.c_int32]
+    L.gs_pslicer_wait.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.POINTER(SampleHeader))]
+    L.gs_pslicer_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    L.gs_pslicer_release.argtypes = [C.c_void_p, C.c_int32]
+    L.gs_pslicer_reset.argtypes = [C.c_void_p]
+    L.gs_pslicer_launches_per_sample.argtypes = [C.c_void_p]
+    L.gs_pslicer_device_bytes.restype = C.c_int64
+    L.gs_pslicer_device_bytes.argtypes = [C.c_void_p]
     if L.gs_abi_version() != ABI_VERSION:
         raise ImportError("libgsplit_slicer.so ABI version mismatch; rebuild")
     _lib = L

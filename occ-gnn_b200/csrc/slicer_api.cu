@@ -26,6 +26,14 @@ int fail(int code, const char *fmt, ...) {
   return code;
 }
 
+}  // namespace
+// shared with pslicer_api.cu
+int gs_set_error(int code, const char *msg) {
+  g_err = msg;
+  return code;
+}
+namespace {
+
 #define CU(call)                                                                       \
   do {                                                                                 \
     cudaError_t e_ = (call);                                                           \

@@ -1,0 +1,169 @@
+// slicer_device.cuh -- device helpers shared by the replicated slicer
+// (slicer_kernels.cu) and the partitioned slicer (pslicer_kernels.cu).
+#pragma once
+#include "slicer_internal.cuh"
+
+#define FULL 0xFFFFFFFFu
+
+namespace {
+
+// ------------------------------------------------------------------ helpers
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
+__device__ __forceinline__ uint32_t lt_mask() { return (1u << lane_id()) - 1u; }
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+  const int lane = lane_id();
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t n = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += n;
+  }
+  return v;
+}
+__device__ __forceinline__ unsigned long long warp_incl_scan64(unsigned long long v) {
+  const int lane = lane_id();
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    unsigned long long n = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += n;
+  }
+  return v;
+}
+
+// Exclusive scan of one value per thread over the CTA.  s_w: GS_NW+1 words.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *s_w, uint32_t &total) {
+  const int lane = lane_id(), w = warp_id();
+  uint32_t inc = warp_incl_scan(v);
+  if (lane == 31) s_w[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t x = lane < GS_NW ? s_w[lane] : 0u;
+    uint32_t xi = warp_incl_scan(x);
+    if (lane < GS_NW) s_w[lane] = xi - x;
+    if (lane == GS_NW - 1) s_w[GS_NW] = xi;
+  }
+  __syncthreads();
+  uint32_t res = s_w[w] + inc - v;
+  total = s_w[GS_NW];
+  __syncthreads();
+  return res;
+}
+__device__ __forceinline__ unsigned long long block_excl_scan64(unsigned long long v,
+                                                               unsigned long long *s_w,
+                                                               unsigned long long &total) {
+  const int lane = lane_id(), w = warp_id();
+  unsigned long long inc = warp_incl_scan64(v);
+  if (lane == 31) s_w[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    unsigned long long x = lane < GS_NW ? s_w[lane] : 0ull;
+    unsigned long long xi = warp_incl_scan64(x);
+    if (lane < GS_NW) s_w[lane] = xi - x;
+    if (lane == GS_NW - 1) s_w[GS_NW] = xi;
+  }
+  __syncthreads();
+  unsigned long long res = s_w[w] + inc - v;
+  total = s_w[GS_NW];
+  __syncthreads();
+  return res;
+}
+
+// Last-CTA election: every CTA calls this after its tile results are written.
+// Returns true in exactly one CTA (the last to arrive), with all other CTAs'
+// writes visible to it.  The ticket is re-armed for the next launch.
+__device__ __forceinline__ bool last_block(uint32_t *ticket) {
+  __shared__ uint32_t s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1) ? 1u : 0u;
+    if (s_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0u;
+}
+
+// Tiles are dealt to CTAs in contiguous runs, so a CTA can carry running
+// offsets across its own tiles and the cross-CTA spine only has gridDim.x
+// entries per counter (not one per tile).  Count and apply kernels of a pair
+// are launched with the same grid and therefore see the same runs.
+__device__ __forceinline__ void cta_tiles(int ntiles, int &t0, int &t1) {
+  const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+  t0 = min(ntiles, (int)blockIdx.x * per);
+  t1 = min(ntiles, t0 + per);
+}
+
+// slab bump allocator (single thread).  16-byte aligned spans.  `used` is the
+// caller's register copy of gs_sample_header::slab_used: a layout of ~30 spans
+// must not pay a global round trip per span.
+__device__ __forceinline__ gs_span slab_alloc(int64_t &used, int64_t cap, uint32_t len, bool &ok) {
+  gs_span s;
+  const int64_t next = used + (((int64_t)len + 3) & ~3ll);
+  if (next > cap || next > 0x7FFFFFFFll) {
+    ok = false;
+    s.off = 0;
+    s.len = 0;
+    return s;
+  }
+  s.off = (int32_t)used;
+  s.len = (int32_t)len;
+  used = next;
+  return s;
+}
+
+// Philox4x32-10 (Salmon et al. SC'11).  Draw for (seed, batch, layer, row's
+// global node id, pick slot): counter-based, so any thread can produce any
+// pick and the result does not depend on the schedule.
+__device__ __forceinline__ uint32_t philox_pick(uint32_t k0, uint32_t k1, uint32_t batch,
+                                                int layer, int32_t node, int slot) {
+  uint32_t c0 = (uint32_t)node, c1 = 0u, c2 = batch,
+           c3 = ((uint32_t)layer << 24) | (uint32_t)(slot >> 2);
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  const int w = slot & 3;
+  return w == 0 ? c0 : (w == 1 ? c1 : (w == 2 ? c2 : c3));
+}
+
+// Exclusive scan of `nc` counter arrays (cnt[c*stride + b], b < n = number of
+// CTAs) by one CTA, in place; totals[c] receives each array's sum.  One warp
+// per counter, eight independent coalesced loads in flight per lane, shuffles
+// only -- the spine is on every layer's critical path, so no barrier and no
+// dependent-load chain inside it.
+template <int NCMAX>
+__device__ void spine_scan(uint32_t *cnt, int stride, int n, int nc, uint32_t *totals,
+                           uint32_t * /*unused*/) {
+  const int w = warp_id(), lane = lane_id();
+  for (int c = w; c < nc; c += GS_NW) {
+    uint32_t *a = cnt + (size_t)c * stride;
+    uint32_t carry = 0u;
+    for (int base = 0; base < n; base += 32 * 8) {
+      uint32_t v[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const int idx = base + k * 32 + lane;
+        v[k] = idx < n ? __ldcg(a + idx) : 0u;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const int idx = base + k * 32 + lane;
+        const uint32_t inc = warp_incl_scan(v[k]);
+        if (idx < n) a[idx] = carry + inc - v[k];
+        carry += __shfl_sync(FULL, inc, 31);
+      }
+    }
+    if (lane == 0) totals[c] = carry;
+  }
+  __syncthreads();
+}
+
+}  // namespace

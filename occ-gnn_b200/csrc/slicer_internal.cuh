@@ -77,6 +77,9 @@ struct GsWs {
   int32_t *slab_host;
 };
 
+// error string of the calling thread (slicer_api.cu); returns `code`
+int gs_set_error(int code, const char *msg);
+
 // launchers (slicer_kernels.cu); every one enqueues exactly one kernel on `st`
 void gs_launch_begin(const GsWs &ws, cudaStream_t st);
 void gs_launch_rows_count(const GsWs &ws, int layer, int grid, cudaStream_t st);

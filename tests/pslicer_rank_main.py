@@ -1,0 +1,47 @@
+"""One rank of the one-process-per-GPU partitioned slicer (launched by
+tests/test_partitioned.py::test_one_process_per_gpu_ipc and usable by hand:
+torchrun --nproc-per-node N tests/pslicer_rank_main.py)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "occ-gnn_b200"), ROOT, os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from cslicer.partitioned import PartitionedSlicer, connect_process_group, partition_csr
+    from cslicer.synth import synth_graph
+    from oracle import oracle as O
+    from test_partitioned import _compare_rank
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("gloo")  # carries 64-byte handles once; data moves over NVLink
+    ip, ix = synth_graph("small", seed=21)
+    n = ip.size - 1
+    fan = [15, 10, 5]
+    lip, lix = partition_csr(ip, ix, world)[rank]
+    ps = PartitionedSlicer(lip, lix, n, rank, world, fan, device=local, max_batch=512, num_slots=2,
+                           seed=77, num_edges_global=ix.size)
+    connect_process_group(ps, dist)
+    orc = O.OracleSlicer(ip, ix, fan, world, O.RNG_PHILOX, seed=77)
+    rng = np.random.default_rng(8)
+    for bi in range(6):
+        seeds = rng.permutation(n)[:512 if bi != 5 else 100]
+        v = ps.slice(seeds, bi)
+        _compare_rank(v, orc.slice(seeds, bi), rank)
+        v.release()
+    dist.barrier()
+    ps.close()
+    print(f"rank {rank} ok", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,173 @@
+"""Partitioned mode: rank g of P holds the CSR rows of the nodes it
+owns and must produce part g of every layer bit-identically to the oracle (and
+so to the single-GPU slicer), plus the replicated frontiers.
+
+CPU part: host-side sharding helpers.  GPU part: P ranks emulated in one process
+on one device (`LocalGroup`: same kernels, arenas and barriers as one process
+per GPU), and -- when the box has >= 2 GPUs -- real one-process-per-GPU ranks
+wired with CUDA IPC through torch.distributed."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def test_partition_csr_round_trip():
+    from cslicer.partitioned import owner_of, partition_csr, range_bounds
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    n = ip.size - 1
+    for mode in ("mod", "range"):
+        for P in (1, 2, 3, 8):
+            b = range_bounds(n, P)
+            shards = partition_csr(ip, ix, P, mode, b)
+            own = owner_of(np.arange(n), n, P, mode, b)
+            assert sum(s[0].size - 1 for s in shards) == n
+            assert sum(s[1].size for s in shards) == ix.size
+            for v in list(range(0, n, max(1, n // 50))) + [n - 1]:
+                g = int(own[v])
+                li = v // P if mode == "mod" else v - b[g]
+                lip, lix = shards[g]
+                assert np.array_equal(lix[lip[li]:lip[li + 1]], ix[ip[v]:ip[v + 1]])
+
+
+def _compare_rank(view, orc, g, check_frontiers=True):
+    from cslicer import _native
+    L = view.num_layers
+    if check_frontiers:
+        for l in range(L + 1):
+            a, b = view.frontier_numpy(l), orc["frontiers"][l]
+            assert a.shape == b.shape and np.array_equal(a, b), f"rank {g}: frontier {l} differs"
+    for l in range(L):
+        for name in _native.FIELDS:
+            a, b = view.numpy(l, g, name), orc["layers"][l][g][name]
+            assert a.shape == b.shape and np.array_equal(a, b), \
+                f"rank {g} layer {l} field {name} differs: {a[:8]} vs {b[:8]} (len {a.size}/{b.size})"
+        for q in range(view.num_parts):
+            if q != g:
+                assert all(view.field_len(l, q, nm) == 0 for nm in _native.FIELDS)
+    assert view.edges == sum(orc["layers"][l][g]["csr_indices"].size for l in range(L))
+
+
+CASES = [
+    # (fanouts, parts, owner, batch, graph)
+    ([10, 10, 10], 4, "mod", 256, "tiny"),
+    ([15, 10, 5], 8, "mod", 512, "small"),
+    ([15, 10, 5], 2, "range", 300, "small"),
+    ([25, 10], 4, "range", 1024, "small"),
+    ([-1, -1], 4, "mod", 128, "small"),
+    ([-1, 5, -1], 3, "range", 64, "tiny"),
+    ([5, 5], 1, "mod", 100, "tiny"),
+    ([3, 3, 3, 3, 3], 5, "mod", 17, "tiny"),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fanouts,P,owner,batch,shape", CASES)
+def test_local_group_matches_oracle(fanouts, P, owner, batch, shape):
+    import torch
+    assert torch.cuda.is_available()
+    from cslicer.partitioned import LocalGroup, owner_of, range_bounds
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph(shape, seed=21)
+    n = ip.size - 1
+    b = range_bounds(n, P)
+    own = None if owner == "mod" else owner_of(np.arange(n), n, P, "range", b)
+    grp = LocalGroup(ip, ix, P, fanouts, owner_mode=owner, bounds=b, max_batch=batch, num_slots=2,
+                     seed=77)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX, seed=77, owner=own)
+    rng = np.random.default_rng(8)
+    for bi in range(5):
+        seeds = rng.permutation(n)[:batch if bi != 4 else max(1, batch // 3)]
+        views = grp.slice(seeds, bi)
+        want = orc.slice(seeds, bi)
+        for g, v in enumerate(views):
+            _compare_rank(v, want, g)
+            v.release()
+    grp.close()
+
+
+@pytest.mark.gpu
+def test_local_group_pipelined_slots_and_duplicate_seed():
+    """Two minibatches in flight per rank (slots), then a bad batch: every rank
+    reports the error, reset() brings the group back."""
+    from cslicer import _native
+    from cslicer.partitioned import LocalGroup
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=5)
+    n = ip.size - 1
+    grp = LocalGroup(ip, ix, 4, [10, 10], max_batch=128, num_slots=3, seed=1)
+    orc = O.OracleSlicer(ip, ix, [10, 10], 4, O.RNG_PHILOX, seed=1)
+    rng = np.random.default_rng(0)
+    batches = [rng.permutation(n)[:128] for _ in range(3)]
+    pend = [grp.submit(s, i) for i, s in enumerate(batches)]
+    for i, slots in enumerate(pend):
+        want = orc.slice(batches[i], i)
+        for g, v in enumerate(grp.wait(slots)):
+            _compare_rank(v, want, g)
+            v.release()
+    bad = batches[0].copy()
+    bad[5] = bad[9]
+    slots = grp.submit(bad, 7)
+    for r, s in zip(grp.ranks, slots):
+        with pytest.raises(_native.SlicerError):
+            r.wait(s)
+    for r in grp.ranks:
+        r.reset()
+    views = grp.slice(batches[1], 1)
+    want = orc.slice(batches[1], 1)
+    for g, v in enumerate(views):
+        _compare_rank(v, want, g)
+        v.release()
+    grp.close()
+
+
+@pytest.mark.gpu
+def test_products_shape_partitioned_equals_replicated():
+    """BASELINE config 2 at full size, 8 parts: every rank's part equals the
+    single-GPU slicer's part (itself pinned to the oracle at small sizes)."""
+    from cslicer import _native, engine
+    from cslicer.partitioned import LocalGroup
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("products", seed=1234)
+    n = ip.size - 1
+    P, fan = 8, [15, 10, 5]
+    g = engine.Graph(ip, ix)
+    sl = engine.Slicer(g, fan, P, max_batch=4096, num_slots=1, num_streams=1, seed=3)
+    grp = LocalGroup(ip, ix, P, fan, max_batch=4096, num_slots=1, seed=3)
+    seeds = np.random.default_rng(1).permutation(n)[:4096]
+    ref = sl.slice(seeds, 11)
+    views = grp.slice(seeds, 11)
+    for q, v in enumerate(views):
+        for l in range(4):
+            assert np.array_equal(v.frontier_numpy(l), ref.frontier_numpy(l))
+        for l in range(3):
+            for name in _native.FIELDS:
+                assert np.array_equal(v.numpy(l, q, name), ref.numpy(l, q, name)), (q, l, name)
+        v.release()
+    ref.release()
+    grp.close()
+    sl.close()
+    g.close()
+
+
+@pytest.mark.gpu
+def test_one_process_per_gpu_ipc():
+    """Real ranks: torchrun-style spawn of 2 processes, arenas wired with CUDA
+    IPC, parity of each rank's part against the oracle."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29541")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                        "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port", "29541",
+                        os.path.join(HERE, "pslicer_rank_main.py")], env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
