@@ -388,11 +388,83 @@ def own_arm(args):
     dev.close()
     hst.close()
     g.close()
+    if dist is not None and not args.no_partitioned:
+        try:
+            pl = partitioned_line(args, torch, dist, ip, ix, local, rank, world)
+        except Exception as e:  # context only; never fail the bench line on it
+            pl = {"unavailable": f"{type(e).__name__}: {e}"}
+        if out is not None:
+            out["partitioned"] = pl
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     if out is not None:
         emit(out)
+
+
+def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32):
+    """SURVEY 8(e) layout at N > 1: graph rows sharded by owner (rank g holds
+    N/P of the CSR and of the dedup table), all ranks cooperate on EVERY
+    minibatch and rank g produces part g; edges and new frontier nodes move by
+    the kernels' own stores / red.min into peer memory over NVLink.  Capacity
+    mode (papers100M-scale graphs, sharded features); the replicated mode above
+    is the throughput mode.  -> dict for the bench line (rank 0), None elsewhere."""
+    from cslicer.partitioned import PartitionedSlicer, connect_process_group, partition_csr
+    from cslicer.sharding import reduce_job
+    n = ip.size - 1
+    lip, lix = partition_csr(ip, ix, world)[rank]
+    ps = PartitionedSlicer(lip, lix, n, rank, world, FANOUTS, device=local, max_batch=BATCH,
+                           num_slots=2, seed=7, host_output=False, num_edges_global=ix.size,
+                           grid_ctas=args.grid_ctas)
+    connect_process_group(ps, dist)
+    batches = seed_batches(n, 64, 0, 1)  # every rank is given the same batches
+
+    def run(k):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        inflight, edges = [], 0
+        e0.record()
+        for i in range(k):
+            if len(inflight) == 2:
+                slot = inflight.pop(0)
+                edges += ps.wait_header(slot).edges
+                ps.release(slot)
+            bi, seeds = batches[i % len(batches)]
+            inflight.append(ps.submit(seeds, bi))
+        for slot in inflight:
+            edges += ps.wait_header(slot).edges
+            ps.release(slot)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1), edges
+    run(3 * mbs)
+    dist.barrier()
+    torch.cuda.synchronize()
+    ms, edges = run(steps * mbs)
+    dist.barrier()
+    ms, (edges,) = reduce_job(dist, f"cuda:{local}", ms, [edges])
+    v = ps.slice(batches[0][1], batches[0][0])
+    fr = list(v.frontier_len)
+    v.release()
+    out = None
+    if rank == 0:
+        per_mb = ms / (steps * mbs)
+        e_mb = edges / (steps * mbs)
+        xbytes = e_mb * (world - 1) / world * 9 + sum(fr[1:]) * 8 * (world - 1) + BATCH * 4
+        out = {"value": round(1e3 / per_mb, 2), "unit": "minibatches/s (whole job, every rank works on every minibatch)",
+               "ms_per_minibatch": round(per_mb, 4), "sampled_edges_per_s": round(edges / (ms * 1e-3), 1),
+               "ranks": world, "parts": world, "launches_per_minibatch_per_rank": ps.launches_per_sample,
+               "barriers_per_minibatch": 3 * len(FANOUTS) + 1,
+               "device_bytes_per_rank": int(ps.device_bytes),
+               "graph_shard_bytes_per_rank": int(lip.size * 8 + lix.size * 4),
+               "nvlink_bytes_per_minibatch_est": int(xbytes),
+               "nvlink_gbs_est": round(xbytes / (per_mb * 1e-3) / 1e9, 2),
+               "note": "exchange = 9 B per remote edge (id, flag, red.min) + 8 B per new frontier node per "
+                       "peer; NVLink 5 peak 900 GB/s per direction per GPU: the exchange is latency-, not "
+                       "bandwidth-bound"}
+    dist.barrier()
+    ps.close()
+    return out
 
 
 def host_cores():
@@ -567,6 +639,8 @@ def main():
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-partitioned", action="store_true",
+                    help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")
     args = ap.parse_args()
     capture_stdout()
     if args.impl == "reference":
