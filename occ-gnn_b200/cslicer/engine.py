@@ -36,7 +36,7 @@ class Graph:
         self._h = h
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and N is not None and N.lib is not None:
             N.lib().gs_graph_destroy(self._h)
             self._h = None
 

@@ -847,8 +847,9 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
 }
 
 // ----------------------------------------------------------------- k_finish
-// Sparse reset of the table (DuplicateRemover::clear, duplicate.cpp:28-33: only
-// touched entries -- every node touched in any layer is in the last frontier),
+// Reset of the table (DuplicateRemover::clear, duplicate.cpp:28-33: only touched
+// entries -- every node touched in any layer is in the last frontier; dense
+// fill instead when the touched set covers most of the table's sectors),
 // then the sample header and, when asked, the used part of the slab are
 // mirrored to pinned host memory with 16-byte stores.
 __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
@@ -859,7 +860,17 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
     const int L = ws.L;
     const int32_t *fl = ws.slab + h->frontier[L].off;
     const int FL = h->frontier_len[L];
-    for (int i = tid; i < FL; i += nth) tbl.st(fl[i], make_uint2(GS_INF, GS_INF));
+    if ((int64_t)FL * 8 > (int64_t)ws.num_nodes) {
+      // most 32-byte sectors of the table hold a touched entry: a streaming
+      // fill of the whole table moves fewer sectors than FL scattered stores
+      uint4 *t4 = (uint4 *)ws.table;
+      const int64_t n4 = (int64_t)ws.num_nodes >> 1;
+      const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
+      for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
+      if ((ws.num_nodes & 1) && tid == 0) ws.table[ws.num_nodes - 1] = make_uint2(GS_INF, GS_INF);
+    } else {
+      for (int i = tid; i < FL; i += nth) tbl.st(fl[i], make_uint2(GS_INF, GS_INF));
+    }
   }
   {
     const int nw = (int)(sizeof(gs_sample_header) / 4);
