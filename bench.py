@@ -84,7 +84,7 @@ def load_graph(shape, device):
     t = time.time()
     ip, ix = synth_graph(shape, seed=GRAPH_SEED, device=device)
     log(f"[bench] generated {shape}: N={ip.size - 1} M={ix.size} in {time.time() - t:.1f}s on {device}")
-    if int(os.environ.get("RANK", "0")) == 0:
+    if int(os.environ.get("RANK", "0")) == 0 and ix.size < 200_000_000:
         try:
             tmp = f + f".tmp{os.getpid()}.npz"
             np.savez(tmp, indptr=ip, indices=ix)
@@ -360,7 +360,7 @@ def own_arm(args):
                "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
-                                      f"3-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
+                                      f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
                           "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
                           "sharding": "whole minibatches per rank, graph topology replicated",
                           "l2": "inputs larger than L2: graph 0.27 GB + per-slot tables/workspaces "
@@ -613,7 +613,7 @@ def reference_arm(args):
            "ms_per_step": round(sec / args.steps * 1e3, 2), "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
            "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
-                                  f"3-layer fanout {FANOUTS}, batch {BATCH}, {args.parts} parts (owner=id%P)",
+                                  f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {args.parts} parts (owner=id%P)",
                       "minibatches_per_step": per_step},
            "sampled_edges_per_s": round(edges / sec, 1),
            "cpu_baseline": {"value": round(value, 3), "unit": "minibatches/s", "cores": cores,
@@ -626,6 +626,7 @@ def reference_arm(args):
 
 
 def main():
+    global BATCH, FANOUTS
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -633,6 +634,8 @@ def main():
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--shape", default=SHAPE)
     ap.add_argument("--parts", type=int, default=4)
+    ap.add_argument("--batch", type=int, default=BATCH, help="seeds per minibatch (config 5: 8192)")
+    ap.add_argument("--fanouts", default=",".join(map(str, FANOUTS)))
     ap.add_argument("--mb-per-step", type=int, default=64)
     ap.add_argument("--slots", type=int, default=8)
     ap.add_argument("--streams", type=int, default=8)
@@ -642,6 +645,8 @@ def main():
     ap.add_argument("--no-partitioned", action="store_true",
                     help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")
     args = ap.parse_args()
+    BATCH = args.batch
+    FANOUTS = [int(x) for x in args.fanouts.split(",")]
     capture_stdout()
     if args.impl == "reference":
         reference_arm(args)
