@@ -436,6 +436,9 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
     DA(w.cand, s->Ccap);
     DA(w.cflag, s->Ccap);
+    DA(w.kill, s->Ccap);
+    DA(w.irank, s->Ccap);
+    DA(w.rowa, s->Fcap);
     DA(w.tile_first, ctiles + 1);
     DA(w.ftile_sum, ftiles);
     DA(w.ftile_samp, ftiles);
@@ -455,7 +458,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     s->slot_bytes = bytes;
     CUS(cudaMemset(w.hdr, 0, sizeof(gs_sample_header)));
     CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
-    CUS(cudaMemset(w.table, 0xFF, (size_t)N * sizeof(uint2)));
+    CUS(cudaMemset(w.table, 0xFF, (size_t)N * sizeof(uint32_t)));
+    CUS(cudaMemset(w.kill, 0, (size_t)s->Ccap));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
                       cudaHostAllocMapped));
@@ -537,7 +541,8 @@ static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out)
   if (hdr_out) *hdr_out = sl.hdr_host;
   if (st != 0) {
     // a sample that stopped half way may have left touched table entries behind
-    cudaMemsetAsync(sl.ws.table, 0xFF, (size_t)s->g->num_nodes * sizeof(uint2), sl.stream);
+    cudaMemsetAsync(sl.ws.table, 0xFF, (size_t)s->g->num_nodes * sizeof(uint32_t), sl.stream);
+    cudaMemsetAsync(sl.ws.kill, 0, (size_t)s->Ccap, sl.stream);
     cudaStreamSynchronize(sl.stream);
     if (st == GS_ERR_OVERFLOW)
       return fail(GS_ERR_OVERFLOW,

@@ -47,7 +47,7 @@ struct GsWs {
   uint64_t *draw_cursor; // shared by all slots (GS_RNG_DRAWS runs on one stream)
   // per-slot state
   gs_sample_header *hdr; // device
-  uint2 *table;          // [N] {x: min edge-source position | in_nodes rank, y: self position}
+  uint32_t *table;       // [N] minimum edge-source position of the node in the current layer (GS_INF: none)
   int32_t *slab;         // sample slab: frontiers + every bipartite list
   int64_t slab_cap;
   int64_t *rowstart;     // [Fcap]   indptr[front[i]]
@@ -57,6 +57,9 @@ struct GsWs {
   uint32_t *rowscan;     // [(Fcap+1)*P] edges of part g emitted before row i
   int32_t *cand;         // [Ccap]   candidate stream (slot 0 of a row holds the row index)
   uint8_t *cflag;        // [Ccap]
+  uint8_t *kill;         // [Ccap] 1: the edge candidate here is NOT a frontier first (its node's self entry came earlier); zero between layers
+  uint32_t *irank;       // [Ccap] rank in in_nodes_g of the first edge occurrence at this position
+  uint32_t *rowa;        // [Fcap] table value (min edge-source position) of every row's node
   uint32_t *tile_first;  // [ctiles_max+1] row containing candidate t*GS_TILE
   unsigned long long *ftile_sum; // [ftiles_max] candidates per frontier tile
   uint32_t *ftile_samp;  // [ftiles_max] drawing rows per frontier tile

@@ -35,37 +35,25 @@ __device__ __forceinline__ uint64_t l2_policy_stream() {
   return p;
 }
 struct Tbl {  // table access with an optional keep-in-L2 policy
-  uint2 *t;
+  uint32_t *t;
   uint64_t pol;
   bool hint;
   __device__ __forceinline__ Tbl(const GsWs &ws) : t(ws.table), pol(0), hint(ws.l2_hints != 0) {
     if (hint) pol = l2_policy_keep();
   }
-  __device__ __forceinline__ uint2 ld(int32_t v) const {
-    if (!hint) return t[v];
-    uint2 r;
-    asm volatile("ld.global.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;"
-                 : "=r"(r.x), "=r"(r.y) : "l"(t + v), "l"(pol));
-    return r;
-  }
-  __device__ __forceinline__ uint32_t ldx(int32_t v) const {
-    if (!hint) return t[v].x;
+  __device__ __forceinline__ uint32_t ld(int32_t v) const {
+    if (!hint) return __ldcg(t + v);
     uint32_t r;
-    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(&t[v].x), "l"(pol));
+    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(t + v), "l"(pol));
     return r;
   }
-  __device__ __forceinline__ void st(int32_t v, uint2 e) const {
-    if (!hint) { t[v] = e; return; }
-    asm volatile("st.global.L2::cache_hint.v2.u32 [%0], {%1, %2}, %3;"
-                 :: "l"(t + v), "r"(e.x), "r"(e.y), "l"(pol) : "memory");
+  __device__ __forceinline__ void st(int32_t v, uint32_t x) const {
+    if (!hint) { t[v] = x; return; }
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(t + v), "r"(x), "l"(pol) : "memory");
   }
-  __device__ __forceinline__ void stx(int32_t v, uint32_t x) const {
-    if (!hint) { t[v].x = x; return; }
-    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(&t[v].x), "r"(x), "l"(pol) : "memory");
-  }
-  __device__ __forceinline__ void minx(int32_t v, uint32_t p) const {
-    if (!hint) { atomicMin(&t[v].x, p); return; }
-    asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(&t[v].x), "r"(p), "l"(pol) : "memory");
+  __device__ __forceinline__ void min(int32_t v, uint32_t p) const {
+    if (!hint) { atomicMin(t + v, p); return; }
+    asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(t + v), "r"(p), "l"(pol) : "memory");
   }
 };
 __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, uint64_t pol) {
@@ -106,8 +94,14 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
   if (!bad)
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
       int64_t v = ws.seeds_in[i];
-      if (v < 0 || v >= (int64_t)ws.num_nodes) s_bad = 1;
-      else ws.slab[i] = (int32_t)v;
+      if (v < 0 || v >= (int64_t)ws.num_nodes) {
+        s_bad = 1;
+      } else {
+        ws.slab[i] = (int32_t)v;
+        // the table is all-INF between minibatches: a second claim of the same
+        // entry is a duplicate seed (k_rows_scan resets the claimed entries)
+        if (atomicCAS(ws.table + v, GS_INF, (uint32_t)i) != GS_INF) s_bad = 1;
+      }
     }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -210,9 +204,10 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
 
 // -------------------------------------------------------------- k_rows_scan
 // Candidate offset of every row; plants the row's self entry (slot 0) in the
-// candidate stream, (re)initialises the row node's table entry to
-// {no edge-source occurrence yet, self position}, and records which row each
-// candidate tile starts in.
+// candidate stream, resets the row node's table entry to "no edge-source
+// occurrence yet" (entries touched in earlier layers all belong to frontier
+// nodes), records which row each candidate tile starts in, and zeroes the
+// frontier-first counters k_cand_flags accumulates into with atomics.
 __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -225,6 +220,8 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
+  for (int k = blockIdx.x * GS_TPB + threadIdx.x; k < ws.ctiles_max; k += gridDim.x * GS_TPB)
+    ws.ctile_cnt[k] = 0u;
   uint32_t base = ws.ftile_pre[blockIdx.x];  // running over this CTA's run of tiles
   uint32_t sbase = ws.ftile_pre[ws.ftiles_max + blockIdx.x];
   for (int t = t0; t < t1; t++) {
@@ -248,7 +245,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
         const uint32_t o = base + ex;
         ws.off[i] = o;
         if (replay) ws.samp_rank[i] = sbase + sex;
-        tbl.st(nd, make_uint2(GS_INF, o));
+        tbl.st(nd, GS_INF);
         ws.cand[o] = i;
         ws.cflag[o] = (uint8_t)GS_CF_SELF;
         for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
@@ -347,7 +344,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
         ws.cand[pos[it]] = v[it];
         if (v[it] != nd1[it]) {
           ws.cflag[pos[it]] = 0;
-          tbl.minx(v[it], pos[it]);
+          tbl.min(v[it], pos[it]);
         } else {
           ws.cflag[pos[it]] = (uint8_t)GS_CF_LOOP;
         }
@@ -358,11 +355,17 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
 }
 
 // ------------------------------------------------------------- k_cand_flags
-// With every minimum in place, classify each candidate: first occurrence in
-// the layer (-> next frontier, slicer.cpp:45-49), first occurrence as an edge
-// source (-> in_nodes of the owner's bipartite, bipartite.cpp:4), real edge of
-// part g.  Per-tile counts of the 2P+1 classes, then the last CTA scans them
-// over tiles, fixes F_{l+1}, |in_nodes_g|, E_g and lays the lists out in the slab.
+// With every minimum in place, classify each candidate.  An edge candidate is
+// the first occurrence of its source as an edge source (-> in_nodes of the
+// owner's bipartite, bipartite.cpp:4) when the table holds its own position;
+// it then also claims the node's slot in the next frontier (slicer.cpp:45-49).
+// A frontier row's self entry at s sees the node's minimum edge position a: the
+// node's frontier slot is at min(a, s), so when s < a the self entry takes the
+// slot and revokes the edge candidate's claim (kill[a] = 1, one less first in
+// the CTA that owns position a).  Every other edge candidate replaces its node
+// id by the position of the first occurrence: that is all k_cand_apply and
+// k_relabel need to relabel it.  Per-CTA counts of the 2P+1 classes, then the
+// last CTA scans them, fixes F_{l+1}, |in_nodes_g|, E_g and lays the lists out.
 __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -375,56 +378,54 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int32_t *front = ws.slab + h->frontier[layer].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
+  const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles per CTA (cta_tiles)
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
   for (int t = t0; t < t1; t++) {
     // phased so the GS_IPT random table reads of a thread are in flight together
-    uint32_t fl[GS_IPT];
-    int32_t cv[GS_IPT];
-    uint2 te[GS_IPT];
+    uint32_t fl[GS_IPT], te[GS_IPT];
+    int32_t ci[GS_IPT], cv[GS_IPT];
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      fl[it] = 0u;
-      cv[it] = 0;
+      fl[it] = GS_CF_LOOP;  // dead lane
+      ci[it] = 0;
       if (p < C) {
         fl[it] = ws.cflag[p];
-        cv[it] = ws.cand[p];
+        ci[it] = ws.cand[p];
       }
     }
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      if (p < C && (fl[it] & GS_CF_SELF)) cv[it] = front[cv[it]];
-    }
+    for (int it = 0; it < GS_IPT; it++) cv[it] = (fl[it] & GS_CF_SELF) ? front[ci[it]] : ci[it];
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      te[it] = make_uint2(0u, 0u);
-      if (p < C) te[it] = tbl.ld(cv[it]);
+      te[it] = 0u;
+      if (!(fl[it] & GS_CF_LOOP)) te[it] = tbl.ld(cv[it]);
     }
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
       bool ffirst = false, ifirst = false, edge = false;
       int g = 0;
-      if (p < C) {
-        uint32_t f = fl[it];
-        const uint2 e = te[it];
-        if (f & GS_CF_SELF) {
-          ffirst = e.x > p;
-          if (e.y != p) h->late_status = (int32_t)GS_ERR_SEED;  // duplicate seed
-        } else if (!(f & GS_CF_LOOP)) {
-          edge = true;
-          ifirst = e.x == p;
-          ffirst = ifirst && e.y > p;
-          g = owner_of(ws, cv[it]);
+      uint32_t f = fl[it];
+      if (f & GS_CF_SELF) {
+        const uint32_t a = te[it];
+        ws.rowa[ci[it]] = a;
+        ffirst = a > p;
+        if (ffirst && a != GS_INF) {  // revoke the claim of the edge candidate at a
+          ws.kill[a] = 1;
+          atomicSub(&ws.ctile_cnt[min((int)(a / GS_TILE) / per, (int)gridDim.x - 1)], 1u);
         }
-        f = (f & (GS_CF_SELF | GS_CF_LOOP)) | (ffirst ? GS_CF_FFIRST : 0u) |
-            (ifirst ? GS_CF_IFIRST : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
-        ws.cflag[p] = (uint8_t)f;
+        ws.cflag[p] = (uint8_t)(GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u));
+      } else if (!(f & GS_CF_LOOP)) {
+        edge = true;
+        ifirst = te[it] == p;
+        ffirst = ifirst;  // unless revoked
+        g = owner_of(ws, cv[it]);
+        if (!ifirst) ws.cand[p] = (int32_t)te[it];
+        ws.cflag[p] = (uint8_t)((ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT));
       }
       const uint32_t mf = __ballot_sync(FULL, ffirst);
       if (lane_id() == 0 && mf) atomicAdd(&s_cnt[0], (uint32_t)__popc(mf));
@@ -439,17 +440,14 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     }
   }
   __syncthreads();
-  if (threadIdx.x < NC) ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x] = s_cnt[threadIdx.x];
+  if (threadIdx.x == 0) atomicAdd(&ws.ctile_cnt[blockIdx.x], s_cnt[0]);  // zeroed by k_rows_scan; peers subtract
+  else if (threadIdx.x < NC) ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x] = s_cnt[threadIdx.x];
   if (!last_block(ws.tickets + 1)) return;
   spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, (int)gridDim.x, NC, s_tot, s_w);
   if (threadIdx.x == 0) {
     bool ok = true;
-    if (h->late_status != 0) {
-      h->status = h->late_status;
-      ok = false;
-    }
     const uint32_t fnext = s_tot[0];
-    if (ok && layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
+    if (layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
     int64_t used = h->slab_used;
     gs_span fs = slab_alloc(used, ws.slab_cap, fnext, ok);
     int64_t edges = 0;
@@ -477,12 +475,13 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
 // order (ids for now; k_relabel turns them into in_nodes positions), and for
 // every row's self entry the number of part-g edges emitted before the row
 // (rowscan), which is both the CSR row pointer and the row's edge count.
-// First-occurrence winners overwrite their table entry's x with the node's
-// rank in in_nodes_g -- the relabel map (DuplicateRemover::mask, duplicate.cpp:21).
+// First-occurrence winners record the node's rank in in_nodes_g at their own
+// position (irank) -- the relabel map (DuplicateRemover::mask, duplicate.cpp:21)
+// indexed by position of first occurrence instead of by node, so that it is a
+// C-sized, L2-resident array and this kernel never touches the N-sized table.
 __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  const Tbl tbl(ws);
   __shared__ uint32_t s_wcnt[GS_NW][GS_NC_MAX];
   __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
   __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
@@ -517,6 +516,12 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
       if (p < C) {
         f[r] = ws.cflag[p];
         ci[r] = ws.cand[p];
+        // an edge candidate's claim on the frontier slot may have been revoked
+        // by the node's earlier self entry (k_cand_flags); leave kill[] zeroed
+        if ((f[r] & (GS_CF_FFIRST | GS_CF_SELF)) == GS_CF_FFIRST && ws.kill[p]) {
+          f[r] &= ~GS_CF_FFIRST;
+          ws.kill[p] = 0;
+        }
       }
     }
 #pragma unroll
@@ -580,13 +585,14 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
           const uint32_t me = __ballot_sync(FULL, edge && g == q);
           const uint32_t ex = re[q] + __popc(me & ltm);  // part-q edges before this position
           // An edge whose source occurs here for the first time knows its own
-          // rank: it writes the final csr_indices value.  Every other edge
-          // leaves ~id (negative) for k_relabel, which then only looks up those.
+          // rank: it writes the final csr_indices value and records the rank at
+          // its position (irank).  Every other edge carries the position m of
+          // that first occurrence and leaves ~m (negative) for k_relabel.
           int32_t ixv = ~cv[r];
           if (ifirst && g == q) {
             const uint32_t rk = ri[q] + __popc(mi & ltm);
             ws.slab[s_in_off[q] + rk] = cv[r];
-            tbl.stx(cv[r], rk);
+            ws.irank[wbase + r * 32 + lane] = rk;
             ixv = (int32_t)rk;
           }
           if (edge && g == q) ws.slab[s_ix_off[q] + ex] = ixv;
@@ -687,7 +693,6 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  const Tbl tbl(ws);
   __shared__ uint32_t s_wcnt[GS_NW][GS_NF_MAX];
   __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
   __shared__ uint32_t s_run[2][GS_NF_MAX];
@@ -806,8 +811,8 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
       if (live) {
         const int gq = g0[r];
         if (to) ws.slab[s_off[gq][GS_F_TO_IDS] + p_to] = op_own;
-        const uint32_t x = tbl.ldx(nd[r]);  // rank in in_nodes_g0, or INF: never an edge source
-        ws.slab[s_off[gq][GS_F_SELF_IN] + p_self] = x == GS_INF ? -1 : (int32_t)x;
+        const uint32_t a = ws.rowa[i];  // position of the node's first edge occurrence, or INF: never an edge source
+        ws.slab[s_off[gq][GS_F_SELF_IN] + p_self] = a == GS_INF ? -1 : (int32_t)__ldcg(ws.irank + a);
         ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self] = op_own;
       }
     }
@@ -821,7 +826,6 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  const Tbl tbl(ws);
   const int P = ws.P;
   for (int q = 0; q < P; q++) {
     const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
@@ -836,7 +840,7 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
         v[k] = e < sp.len ? ix[e] : 0;  // >= 0: already final (written by the first occurrence)
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? tbl.ldx(~v[k]) : 0u;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(ws.irank + (uint32_t)~v[k]) : 0u;
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
@@ -864,12 +868,12 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
       // most 32-byte sectors of the table hold a touched entry: a streaming
       // fill of the whole table moves fewer sectors than FL scattered stores
       uint4 *t4 = (uint4 *)ws.table;
-      const int64_t n4 = (int64_t)ws.num_nodes >> 1;
+      const int64_t n4 = (int64_t)ws.num_nodes >> 2;
       const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
       for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
-      if ((ws.num_nodes & 1) && tid == 0) ws.table[ws.num_nodes - 1] = make_uint2(GS_INF, GS_INF);
+      if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
     } else {
-      for (int i = tid; i < FL; i += nth) tbl.st(fl[i], make_uint2(GS_INF, GS_INF));
+      for (int i = tid; i < FL; i += nth) tbl.st(fl[i], GS_INF);
     }
   }
   {
