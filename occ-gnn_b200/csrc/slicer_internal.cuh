@@ -54,7 +54,7 @@ struct GsWs {
   int32_t *rowdeg;       // [Fcap]
   uint32_t *off;         // [Fcap+1] first candidate position of row i
   uint32_t *samp_rank;   // [Fcap]   # earlier rows that draw (replay mode)
-  uint32_t *rowscan;     // [(Fcap+1)*P] edges of part g emitted before row i
+  uint32_t *rowscan;     // [P][Fcap+1] edges of part g emitted before row i
   int32_t *cand;         // [Ccap]   candidate stream (slot 0 of a row holds the row index)
   uint8_t *cflag;        // [Ccap]
   uint8_t *kill;         // [Ccap] 1: the edge candidate here is NOT a frontier first (its node's self entry came earlier); zero between layers

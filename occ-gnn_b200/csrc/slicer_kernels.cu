@@ -63,6 +63,9 @@ __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, ui
   return r;
 }
 
+// rowscan is stored part-major ([q][Fcap+1]) so that consecutive rows are contiguous
+__device__ __forceinline__ size_t rs_at(const GsWs &ws, int q, int i) { return (size_t)q * ((size_t)ws.Fcap + 1) + (size_t)i; }
+
 __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
   return ws.owner ? (int)__ldg(ws.owner + v) : (int)((uint32_t)v % (uint32_t)ws.P);
 }
@@ -203,8 +206,8 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
 }
 
 // -------------------------------------------------------------- k_rows_scan
-// Candidate offset of every row; plants the row's self entry (slot 0) in the
-// candidate stream, resets the row node's table entry to "no edge-source
+// Candidate offset of every row (k_expand writes the stream, self entries
+// included); resets the row node's table entry to "no edge-source
 // occurrence yet" (entries touched in earlier layers all belong to frontier
 // nodes), records which row each candidate tile starts in, and zeroes the
 // frontier-first counters k_cand_flags accumulates into with atomics.
@@ -246,8 +249,6 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
         ws.off[i] = o;
         if (replay) ws.samp_rank[i] = sbase + sex;
         tbl.st(nd, GS_INF);
-        ws.cand[o] = i;
-        ws.cflag[o] = (uint8_t)GS_CF_SELF;
         for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
           ws.tile_first[tb] = (uint32_t)i;
       }
@@ -338,16 +339,20 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++)
       if (slot[it] > 0) v[it] = ld_stream_i32(src[it], ws.l2_hints != 0, spol);
+    // every position of the tile is written, self entries (slot 0: row index)
+    // included, so the candidate stream goes out in full coalesced lines
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
-      if (slot[it] > 0) {
-        ws.cand[pos[it]] = v[it];
-        if (v[it] != nd1[it]) {
-          ws.cflag[pos[it]] = 0;
-          tbl.min(v[it], pos[it]);
-        } else {
-          ws.cflag[pos[it]] = (uint8_t)GS_CF_LOOP;
+      if (pos[it] < C) {
+        int32_t cvv = row[it];
+        uint32_t cf = GS_CF_SELF;
+        if (slot[it] > 0) {
+          cvv = v[it];
+          cf = v[it] != nd1[it] ? 0u : GS_CF_LOOP;
+          if (cf == 0u) tbl.min(v[it], pos[it]);
         }
+        ws.cand[pos[it]] = cvv;
+        ws.cflag[pos[it]] = (uint8_t)cf;
       }
     }
     __syncthreads();
@@ -418,14 +423,18 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
           ws.kill[a] = 1;
           atomicSub(&ws.ctile_cnt[min((int)(a / GS_TILE) / per, (int)gridDim.x - 1)], 1u);
         }
-        ws.cflag[p] = (uint8_t)(GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u));
+        f = GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u);
       } else if (!(f & GS_CF_LOOP)) {
         edge = true;
         ifirst = te[it] == p;
         ffirst = ifirst;  // unless revoked
         g = owner_of(ws, cv[it]);
-        if (!ifirst) ws.cand[p] = (int32_t)te[it];
-        ws.cflag[p] = (uint8_t)((ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT));
+        if (!ifirst) ci[it] = (int32_t)te[it];
+        f = (ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
+      }
+      if (p < C) {  // whole lines go back, not scattered words
+        ws.cand[p] = ci[it];
+        ws.cflag[p] = (uint8_t)f;
       }
       const uint32_t mf = __ballot_sync(FULL, ffirst);
       if (lane_id() == 0 && mf) atomicAdd(&s_cnt[0], (uint32_t)__popc(mf));
@@ -454,7 +463,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     for (int q = 0; q < P && ok; q++) {
       h->field[layer][q][GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, s_tot[1 + q], ok);
       h->field[layer][q][GS_F_CSR_INDICES] = slab_alloc(used, ws.slab_cap, s_tot[1 + P + q], ok);
-      ws.rowscan[(size_t)F * P + q] = s_tot[1 + P + q];
+      ws.rowscan[rs_at(ws, q, F)] = s_tot[1 + P + q];
       edges += s_tot[1 + P + q];
     }
     if (ok) {
@@ -486,6 +495,14 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
   __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
+  // Output staging: inside a tile every list's ranks are consecutive, so the
+  // tile's share of fnext / in_nodes_q / csr_indices_q is assembled here
+  // (in_nodes and csr_indices segmented by part) and copied out in whole lines
+  // instead of 4-byte scatters -- the pipeline is bound by L2 sector operations.
+  __shared__ int32_t s_stage[3][GS_TILE];
+  __shared__ uint32_t s_tcnt[GS_NC_MAX];   // class counts of the current tile
+  __shared__ uint32_t s_gd[GS_NC_MAX];     // global rank - stage index, per class
+  __shared__ uint32_t s_send[2][GS_MAX_PARTS];  // segment ends inside stage 1 / 2
   const int P = ws.P, NC = 2 * P + 1;
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
@@ -559,10 +576,26 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
       uint32_t a = s_run[t & 1][cc];
       for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
       s_base[ww][cc] = a;
-      if (ww == GS_NW - 1) s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
+      if (ww == GS_NW - 1) {
+        s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
+        s_tcnt[cc] = a + s_wcnt[ww][cc] - s_run[t & 1][cc];
+      }
     }
     __syncthreads();
-    // phase 2: ranks and scatter
+    if (threadIdx.x == 0) {
+      s_gd[0] = s_run[t & 1][0];
+      uint32_t si = 0u, se = 0u;
+      for (int q = 0; q < P; q++) {
+        s_gd[1 + q] = s_run[t & 1][1 + q] - si;
+        s_gd[1 + P + q] = s_run[t & 1][1 + P + q] - se;
+        si += s_tcnt[1 + q];
+        se += s_tcnt[1 + P + q];
+        s_send[0][q] = si;
+        s_send[1][q] = se;
+      }
+    }
+    __syncthreads();
+    // phase 2: ranks, outputs into the stage
     uint32_t rf = s_base[w][0], ri[GS_MAX_PARTS], re[GS_MAX_PARTS];
 #pragma unroll
     for (int q = 0; q < GS_MAX_PARTS; q++) {
@@ -576,8 +609,9 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
       const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
       const bool ffirst = (f[r] & GS_CF_FFIRST) != 0u, ifirst = (f[r] & GS_CF_IFIRST) != 0u;
       const uint32_t mf = __ballot_sync(FULL, ffirst);
-      if (ffirst) fnext[rf + __popc(mf & ltm)] = cv[r];
+      if (ffirst) s_stage[0][rf + __popc(mf & ltm) - s_gd[0]] = cv[r];
       rf += __popc(mf);
+      uint32_t myrank = 0u;  // irank goes out for every position: one full line per warp round
 #pragma unroll
       for (int q = 0; q < GS_MAX_PARTS; q++)
         if (q < P) {
@@ -591,15 +625,32 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
           int32_t ixv = ~cv[r];
           if (ifirst && g == q) {
             const uint32_t rk = ri[q] + __popc(mi & ltm);
-            ws.slab[s_in_off[q] + rk] = cv[r];
-            ws.irank[wbase + r * 32 + lane] = rk;
+            s_stage[1][rk - s_gd[1 + q]] = cv[r];
+            myrank = rk;
             ixv = (int32_t)rk;
           }
-          if (edge && g == q) ws.slab[s_ix_off[q] + ex] = ixv;
-          if (isself) ws.rowscan[(size_t)ci[r] * P + q] = ex;
+          if (edge && g == q) s_stage[2][ex - s_gd[1 + P + q]] = ixv;
+          if (isself) ws.rowscan[rs_at(ws, q, ci[r])] = ex;
           ri[q] += __popc(mi);
           re[q] += __popc(me);
         }
+      if (wbase + r * 32 + lane < C) ws.irank[wbase + r * 32 + lane] = myrank;
+    }
+    __syncthreads();
+    // copy-out: whole runs, consecutive threads -> consecutive addresses
+    for (uint32_t j = threadIdx.x; j < s_tcnt[0]; j += GS_TPB) fnext[s_gd[0] + j] = s_stage[0][j];
+    {
+      const uint32_t n_in = s_send[0][P - 1], n_ix = s_send[1][P - 1];
+      for (uint32_t j = threadIdx.x; j < n_in; j += GS_TPB) {
+        int q = 0;
+        while (j >= s_send[0][q]) q++;
+        ws.slab[s_in_off[q] + (j + s_gd[1 + q])] = s_stage[1][j];
+      }
+      for (uint32_t j = threadIdx.x; j < n_ix; j += GS_TPB) {
+        int q = 0;
+        while (j >= s_send[1][q]) q++;
+        ws.slab[s_ix_off[q] + (j + s_gd[1 + P + q])] = s_stage[2][j];
+      }
     }
   }
 }
@@ -613,7 +664,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
 __device__ __forceinline__ uint32_t row_has_mask(const GsWs &ws, int i, int P) {
   uint32_t m = 0u;
   for (int q = 0; q < P; q++)
-    if (ws.rowscan[(size_t)(i + 1) * P + q] != ws.rowscan[(size_t)i * P + q]) m |= 1u << q;
+    if (ws.rowscan[rs_at(ws, q, i + 1)] != ws.rowscan[rs_at(ws, q, i)]) m |= 1u << q;
   return m;
 }
 
@@ -682,7 +733,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
       fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, n_self, ok);
       fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, n_self, ok);
       // row pointer sentinel = E_g (left in rowscan[F] by k_cand_flags' spine)
-      if (ok) ws.slab[ip.off + n_out] = (int32_t)ws.rowscan[(size_t)F * P + q];
+      if (ok) ws.slab[ip.off + n_out] = (int32_t)ws.rowscan[rs_at(ws, q, F)];
     }
     if (ok) h->slab_used = used;
     else h->status = (int32_t)GS_ERR_OVERFLOW;
@@ -791,7 +842,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
             const uint32_t op = b_out[q] + __popc(m_out & ltm);
             const uint32_t ow = b_own[q] + __popc(m_own & ltm);
             ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd[r];
-            ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * P + q];
+            ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[rs_at(ws, q, i)];
             if (q == g0[r]) {
               ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
               op_own = (int32_t)op;
