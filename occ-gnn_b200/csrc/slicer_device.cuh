@@ -166,4 +166,25 @@ __device__ void spine_scan(uint32_t *cnt, int stride, int n, int nc, uint32_t *t
   __syncthreads();
 }
 
+// Per-part counters packed one byte per part (P <= 8) in a 64-bit word: a lane
+// that contributes an item of part g adds pk_one(g).  One packed scan / reduce
+// over the warp replaces P ballot+popc pairs; a byte holds at most 32 * GS_IPT
+// = 128 < 256 items.
+__device__ __forceinline__ unsigned long long pk_one(int g) { return 1ull << (8 * g); }
+__device__ __forceinline__ uint32_t pk_get(unsigned long long v, int g) { return (uint32_t)(v >> (8 * g)) & 0xFFu; }
+__device__ __forceinline__ unsigned long long pk_warp_sum(unsigned long long v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+  return v;
+}
+__device__ __forceinline__ unsigned long long pk_warp_incl(unsigned long long v) {
+  const int lane = lane_id();
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long n = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += n;
+  }
+  return v;
+}
+
 }  // namespace

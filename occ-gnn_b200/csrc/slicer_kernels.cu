@@ -390,6 +390,8 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   cta_tiles(ntiles, t0, t1);
   for (int t = t0; t < t1; t++) {
     // phased so the GS_IPT random table reads of a thread are in flight together
+    unsigned long long pk_i = 0ull, pk_e = 0ull;  // this lane's firsts / edges per part
+    uint32_t n_ff = 0u;
     uint32_t fl[GS_IPT], te[GS_IPT];
     int32_t ci[GS_IPT], cv[GS_IPT];
 #pragma unroll
@@ -436,15 +438,21 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
         ws.cand[p] = ci[it];
         ws.cflag[p] = (uint8_t)f;
       }
-      const uint32_t mf = __ballot_sync(FULL, ffirst);
-      if (lane_id() == 0 && mf) atomicAdd(&s_cnt[0], (uint32_t)__popc(mf));
+      n_ff += ffirst ? 1u : 0u;
+      if (edge) pk_e += pk_one(g);
+      if (ifirst) pk_i += pk_one(g);
+    }
+    // one packed reduction per tile instead of 2P+1 ballots per round
+    pk_i = pk_warp_sum(pk_i);
+    pk_e = pk_warp_sum(pk_e);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) n_ff += __shfl_xor_sync(FULL, n_ff, d);
+    if (lane_id() == 0) {
+      if (n_ff) atomicAdd(&s_cnt[0], n_ff);
       for (int q = 0; q < P; q++) {
-        const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
-        const uint32_t me = __ballot_sync(FULL, edge && g == q);
-        if (lane_id() == 0) {
-          if (mi) atomicAdd(&s_cnt[1 + q], (uint32_t)__popc(mi));
-          if (me) atomicAdd(&s_cnt[1 + P + q], (uint32_t)__popc(me));
-        }
+        const uint32_t a = pk_get(pk_i, q), b = pk_get(pk_e, q);
+        if (a) atomicAdd(&s_cnt[1 + q], a);
+        if (b) atomicAdd(&s_cnt[1 + P + q], b);
       }
     }
   }
@@ -491,18 +499,14 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  __shared__ uint32_t s_wcnt[GS_NW][GS_NC_MAX];
+  // The kernels of this pipeline are bound by instruction issue, not by memory:
+  // per-part ranks come from two packed warp scans (one byte per part) instead
+  // of 2P ballot/popc pairs per round.
+  __shared__ unsigned long long s_wi[GS_NW], s_we[GS_NW];  // per-warp packed class totals of the tile
+  __shared__ uint32_t s_wf[GS_NW];
   __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
   __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
-  // Output staging: inside a tile every list's ranks are consecutive, so the
-  // tile's share of fnext / in_nodes_q / csr_indices_q is assembled here
-  // (in_nodes and csr_indices segmented by part) and copied out in whole lines
-  // instead of 4-byte scatters -- the pipeline is bound by L2 sector operations.
-  __shared__ int32_t s_stage[3][GS_TILE];
-  __shared__ uint32_t s_tcnt[GS_NC_MAX];   // class counts of the current tile
-  __shared__ uint32_t s_gd[GS_NC_MAX];     // global rank - stage index, per class
-  __shared__ uint32_t s_send[2][GS_MAX_PARTS];  // segment ends inside stage 1 / 2
   const int P = ws.P, NC = 2 * P + 1;
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
@@ -545,112 +549,76 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
     for (int r = 0; r < GS_IPT; r++) cv[r] = (f[r] & GS_CF_SELF) ? front[ci[r]] : ci[r];
     // phase 1: per-warp totals of every class
     {
-      uint32_t nf = 0u, ni[GS_MAX_PARTS], ne[GS_MAX_PARTS];
-#pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++) ni[q] = ne[q] = 0u;
+      unsigned long long pi = 0ull, pe = 0ull;
+      uint32_t nf = 0u;
 #pragma unroll
       for (int r = 0; r < GS_IPT; r++) {
         const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
-        const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
-        nf += __popc(__ballot_sync(FULL, (f[r] & GS_CF_FFIRST) != 0u));
-#pragma unroll
-        for (int q = 0; q < GS_MAX_PARTS; q++)
-          if (q < P) {
-            ni[q] += __popc(__ballot_sync(FULL, (f[r] & GS_CF_IFIRST) && g == q));
-            ne[q] += __popc(__ballot_sync(FULL, edge && g == q));
-          }
+        if (!(f[r] & (GS_CF_SELF | GS_CF_LOOP))) pe += pk_one(g);
+        if (f[r] & GS_CF_IFIRST) pi += pk_one(g);
+        nf += (f[r] & GS_CF_FFIRST) ? 1u : 0u;
       }
+      pi = pk_warp_sum(pi);
+      pe = pk_warp_sum(pe);
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) nf += __shfl_xor_sync(FULL, nf, d);
       if (lane == 0) {
-        s_wcnt[w][0] = nf;
-#pragma unroll
-        for (int q = 0; q < GS_MAX_PARTS; q++)
-          if (q < P) {
-            s_wcnt[w][1 + q] = ni[q];
-            s_wcnt[w][1 + P + q] = ne[q];
-          }
+        s_wi[w] = pi;
+        s_we[w] = pe;
+        s_wf[w] = nf;
       }
     }
     __syncthreads();
-    if (threadIdx.x < NC * GS_NW) {
-      const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-      uint32_t a = s_run[t & 1][cc];
-      for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
-      s_base[ww][cc] = a;
-      if (ww == GS_NW - 1) {
-        s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
-        s_tcnt[cc] = a + s_wcnt[ww][cc] - s_run[t & 1][cc];
+    if (lane < NC) {  // lane = class: this warp's base, and (warp 0) the next tile's running counts
+      const int cc = lane;
+      uint32_t a = s_run[t & 1][cc], all = 0u;
+      for (int k = 0; k < GS_NW; k++) {
+        const uint32_t c = cc == 0 ? s_wf[k] : (cc <= P ? pk_get(s_wi[k], cc - 1) : pk_get(s_we[k], cc - 1 - P));
+        if (k < w) a += c;
+        all += c;
       }
+      s_base[w][cc] = a;
+      if (w == 0) s_run[(t + 1) & 1][cc] = s_run[t & 1][cc] + all;
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      s_gd[0] = s_run[t & 1][0];
-      uint32_t si = 0u, se = 0u;
-      for (int q = 0; q < P; q++) {
-        s_gd[1 + q] = s_run[t & 1][1 + q] - si;
-        s_gd[1 + P + q] = s_run[t & 1][1 + P + q] - se;
-        si += s_tcnt[1 + q];
-        se += s_tcnt[1 + P + q];
-        s_send[0][q] = si;
-        s_send[1][q] = se;
-      }
-    }
-    __syncthreads();
-    // phase 2: ranks, outputs into the stage
-    uint32_t rf = s_base[w][0], ri[GS_MAX_PARTS], re[GS_MAX_PARTS];
-#pragma unroll
-    for (int q = 0; q < GS_MAX_PARTS; q++) {
-      ri[q] = q < P ? s_base[w][1 + q] : 0u;
-      re[q] = q < P ? s_base[w][1 + P + q] : 0u;
-    }
+    __syncwarp();
+    // phase 2: ranks and scatter
+    uint32_t rf = s_base[w][0];
+    unsigned long long run_i = 0ull, run_e = 0ull;  // packed totals of this warp's earlier rounds
 #pragma unroll
     for (int r = 0; r < GS_IPT; r++) {
+      const uint32_t p = wbase + r * 32 + lane;
       const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
       const bool isself = (f[r] & GS_CF_SELF) != 0u;
       const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
       const bool ffirst = (f[r] & GS_CF_FFIRST) != 0u, ifirst = (f[r] & GS_CF_IFIRST) != 0u;
       const uint32_t mf = __ballot_sync(FULL, ffirst);
-      if (ffirst) s_stage[0][rf + __popc(mf & ltm) - s_gd[0]] = cv[r];
+      if (ffirst) fnext[rf + __popc(mf & ltm)] = cv[r];
       rf += __popc(mf);
-      uint32_t myrank = 0u;  // irank goes out for every position: one full line per warp round
-#pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++)
-        if (q < P) {
-          const uint32_t mi = __ballot_sync(FULL, ifirst && g == q);
-          const uint32_t me = __ballot_sync(FULL, edge && g == q);
-          const uint32_t ex = re[q] + __popc(me & ltm);  // part-q edges before this position
-          // An edge whose source occurs here for the first time knows its own
-          // rank: it writes the final csr_indices value and records the rank at
-          // its position (irank).  Every other edge carries the position m of
-          // that first occurrence and leaves ~m (negative) for k_relabel.
-          int32_t ixv = ~cv[r];
-          if (ifirst && g == q) {
-            const uint32_t rk = ri[q] + __popc(mi & ltm);
-            s_stage[1][rk - s_gd[1 + q]] = cv[r];
-            myrank = rk;
-            ixv = (int32_t)rk;
-          }
-          if (edge && g == q) s_stage[2][ex - s_gd[1 + P + q]] = ixv;
-          if (isself) ws.rowscan[rs_at(ws, q, ci[r])] = ex;
-          ri[q] += __popc(mi);
-          re[q] += __popc(me);
+      const unsigned long long one_e = edge ? pk_one(g) : 0ull, one_i = ifirst ? pk_one(g) : 0ull;
+      const unsigned long long inc_e = pk_warp_incl(one_e), inc_i = pk_warp_incl(one_i);
+      const unsigned long long before_e = run_e + inc_e - one_e;  // part-q edges of this warp before this position
+      uint32_t myrank = 0u;
+      if (edge) {
+        const uint32_t ex = s_base[w][1 + P + g] + pk_get(before_e, g);
+        // An edge whose source occurs here for the first time knows its own
+        // rank: it writes the final csr_indices value and records the rank at
+        // its position (irank).  Every other edge carries the position m of
+        // that first occurrence and leaves ~m (negative) for k_relabel.
+        int32_t ixv = ~cv[r];
+        if (ifirst) {
+          const uint32_t rk = s_base[w][1 + g] + pk_get(run_i + inc_i - one_i, g);
+          ws.slab[s_in_off[g] + rk] = cv[r];
+          myrank = rk;
+          ixv = (int32_t)rk;
         }
-      if (wbase + r * 32 + lane < C) ws.irank[wbase + r * 32 + lane] = myrank;
-    }
-    __syncthreads();
-    // copy-out: whole runs, consecutive threads -> consecutive addresses
-    for (uint32_t j = threadIdx.x; j < s_tcnt[0]; j += GS_TPB) fnext[s_gd[0] + j] = s_stage[0][j];
-    {
-      const uint32_t n_in = s_send[0][P - 1], n_ix = s_send[1][P - 1];
-      for (uint32_t j = threadIdx.x; j < n_in; j += GS_TPB) {
-        int q = 0;
-        while (j >= s_send[0][q]) q++;
-        ws.slab[s_in_off[q] + (j + s_gd[1 + q])] = s_stage[1][j];
+        ws.slab[s_ix_off[g] + ex] = ixv;
       }
-      for (uint32_t j = threadIdx.x; j < n_ix; j += GS_TPB) {
-        int q = 0;
-        while (j >= s_send[1][q]) q++;
-        ws.slab[s_ix_off[q] + (j + s_gd[1 + P + q])] = s_stage[2][j];
-      }
+      if (isself)
+        for (int q = 0; q < P; q++)
+          ws.rowscan[rs_at(ws, q, ci[r])] = s_base[w][1 + P + q] + pk_get(before_e, q);
+      if (p < C) ws.irank[p] = myrank;  // every position: one full line per warp round
+      run_e += __shfl_sync(FULL, inc_e, 31);
+      run_i += __shfl_sync(FULL, inc_i, 31);
     }
   }
 }
