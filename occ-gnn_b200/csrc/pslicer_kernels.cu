@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(1024) pk_begin(PsWs ws) {
     h->draw_cursor = 0;
     h->edges = 0;
     h->late_status = 0;
+    h->reserved[0] = ws.input->want_host;  // kept on the device: k_finish must not poll host memory from every thread
     h->feature_rows = 0;
     const int nn = bad ? 0 : n;
     h->slab_used = ((int64_t)nn + 3) & ~3ll;
@@ -717,7 +718,7 @@ __global__ void __launch_bounds__(GS_TPB) pk_finish(PsWs ws) {
     int32_t *dst = (int32_t *)ws.hdr_host;
     for (int i = tid; i < nw; i += nth) dst[i] = src[i];
   }
-  if (ws.input->want_host && ws.slab_host && h->status == 0) {
+  if (h->reserved[0] && ws.slab_host && h->status == 0) {
     const int64_t n4 = h->slab_used >> 2;
     const int4 *src = (const int4 *)ws.slab;
     int4 *dst = (int4 *)ws.slab_host;

@@ -117,6 +117,24 @@ __device__ __forceinline__ gs_span slab_alloc(int64_t &used, int64_t cap, uint32
 // Philox4x32-10 (Salmon et al. SC'11).  Draw for (seed, batch, layer, row's
 // global node id, pick slot): counter-based, so any thread can produce any
 // pick and the result does not depend on the schedule.
+// One Philox block = four draws: picks 4*blk .. 4*blk+3 of (seed, batch, layer, node).
+__device__ __forceinline__ uint4 philox_block(uint32_t k0, uint32_t k1, uint32_t batch, int layer,
+                                              int32_t node, int blk) {
+  uint32_t c0 = (uint32_t)node, c1 = 0u, c2 = batch, c3 = ((uint32_t)layer << 24) | (uint32_t)blk;
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ uint32_t philox_word(const uint4 &b, int w) {
+  return w == 0 ? b.x : (w == 1 ? b.y : (w == 2 ? b.z : b.w));
+}
 __device__ __forceinline__ uint32_t philox_pick(uint32_t k0, uint32_t k1, uint32_t batch,
                                                 int layer, int32_t node, int slot) {
   uint32_t c0 = (uint32_t)node, c1 = 0u, c2 = batch,

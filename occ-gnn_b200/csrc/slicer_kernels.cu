@@ -116,7 +116,8 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
     h->batch_index = ws.input->batch_index;
     h->draw_cursor = *ws.draw_cursor;
     h->edges = 0;
-    h->late_status = 0;  // late error raised inside a tiled kernel
+    h->late_status = 0;
+    h->reserved[0] = ws.input->want_host;  // kept on the device: k_finish must not poll host memory from every thread  // late error raised inside a tiled kernel
     const int nn = bad ? 0 : n;
     h->slab_used = ((int64_t)nn + 3) & ~3ll;
     h->frontier_len[0] = nn;
@@ -287,73 +288,93 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
     const int cnt = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
     for (int k = threadIdx.x; k <= cnt; k += GS_TPB) s_off[k] = ws.off[i_lo + k];
     __syncthreads();
-    // Three phases over the thread's GS_IPT candidates so that the row lookups,
-    // then the GS_IPT random neighbour gathers, are all in flight together.
-    uint32_t pos[GS_IPT];
+    // A thread owns GS_IPT CONSECUTIVE positions (the kernel is bound by
+    // instruction issue): one binary search, then a walk; one Philox block serves
+    // up to four picks of a row; the stream goes out as 16-byte / 4-byte vectors.
+    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     int row[GS_IPT], slot[GS_IPT];
     int32_t nd1[GS_IPT], deg[GS_IPT];
     int64_t rs[GS_IPT];
-#pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      pos[it] = p;
-      slot[it] = 0;
-      row[it] = 0;
-      if (p < C) {
-        int lo = 0, hi = cnt - 1;  // largest k with s_off[k] <= p
-        while (lo < hi) {
-          const int mid = (lo + hi + 1) >> 1;
-          if (s_off[mid] <= p) lo = mid; else hi = mid - 1;
-        }
-        slot[it] = (int)(p - s_off[lo]);  // 0 = self entry, planted by k_rows_scan
-        row[it] = i_lo + lo;
+    int lo = 0;
+    if (p0 < C) {
+      int hi = cnt - 1;  // largest k with s_off[k] <= p0
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (s_off[mid] <= p0) lo = mid; else hi = mid - 1;
       }
     }
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      if (slot[it] > 0) {
-        nd1[it] = front[row[it]];
-        rs[it] = ws.rowstart[row[it]];
-        deg[it] = ws.rowdeg[row[it]];
+    for (int k = 0; k < GS_IPT; k++) {
+      const uint32_t p = p0 + k;
+      if (k > 0 && p < C && p >= s_off[lo + 1]) lo++;  // every row has >= 1 candidate: one step is enough
+      row[k] = i_lo + lo;
+      slot[k] = p < C ? (int)(p - s_off[lo]) : 0;  // 0 = self entry (or dead position)
+    }
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      if (k > 0 && row[k] == row[k - 1]) {
+        nd1[k] = nd1[k - 1];
+        rs[k] = rs[k - 1];
+        deg[k] = deg[k - 1];
+      } else {
+        nd1[k] = front[row[k]];
+        rs[k] = ws.rowstart[row[k]];
+        deg[k] = ws.rowdeg[row[k]];
       }
     }
     const int32_t *src[GS_IPT];
+    uint4 blk = make_uint4(0u, 0u, 0u, 0u);
+    int blk_row = -1, blk_id = -1;
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      if (slot[it] > 0) {
-        int32_t pick = slot[it] - 1;
-        if (fan >= 0 && deg[it] >= fan) {
+    for (int k = 0; k < GS_IPT; k++) {
+      src[k] = nullptr;
+      if (slot[k] > 0) {
+        int32_t pick = slot[k] - 1;
+        if (fan >= 0 && deg[k] >= fan) {
           uint32_t r;
           if (replay) {
-            const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row[it]] + (uint32_t)(slot[it] - 1);
+            const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row[k]] + (uint32_t)pick;
             r = di < ws.n_draws ? ws.draws[di] : 0u;
           } else {
-            r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1[it], slot[it] - 1);
+            if (blk_row != row[k] || blk_id != (pick >> 2)) {
+              blk_row = row[k];
+              blk_id = pick >> 2;
+              blk = philox_block(ws.seed_lo, ws.seed_hi, batch, layer, nd1[k], blk_id);
+            }
+            r = philox_word(blk, pick & 3);
           }
-          pick = (int32_t)(r % (uint32_t)deg[it]);
+          pick = (int32_t)(r % (uint32_t)deg[k]);
         }
-        src[it] = ws.indices + rs[it] + pick;
+        src[k] = ws.indices + rs[k] + pick;
       }
     }
     int32_t v[GS_IPT];
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++)
-      if (slot[it] > 0) v[it] = ld_stream_i32(src[it], ws.l2_hints != 0, spol);
-    // every position of the tile is written, self entries (slot 0: row index)
-    // included, so the candidate stream goes out in full coalesced lines
+    for (int k = 0; k < GS_IPT; k++)
+      if (src[k]) v[k] = ld_stream_i32(src[k], ws.l2_hints != 0, spol);
+    int32_t cvv[GS_IPT];
+    uint32_t cf[GS_IPT];
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      if (pos[it] < C) {
-        int32_t cvv = row[it];
-        uint32_t cf = GS_CF_SELF;
-        if (slot[it] > 0) {
-          cvv = v[it];
-          cf = v[it] != nd1[it] ? 0u : GS_CF_LOOP;
-          if (cf == 0u) tbl.min(v[it], pos[it]);
-        }
-        ws.cand[pos[it]] = cvv;
-        ws.cflag[pos[it]] = (uint8_t)cf;
+    for (int k = 0; k < GS_IPT; k++) {
+      cvv[k] = row[k];  // self entry: the row index
+      cf[k] = GS_CF_SELF;
+      if (src[k]) {
+        cvv[k] = v[k];
+        cf[k] = v[k] != nd1[k] ? 0u : GS_CF_LOOP;
+        if (cf[k] == 0u) tbl.min(v[k], p0 + k);
       }
+    }
+    if (p0 + GS_IPT <= C) {
+      *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(cvv[0], cvv[1], cvv[2], cvv[3]);
+      *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
+          make_uchar4((unsigned char)cf[0], (unsigned char)cf[1], (unsigned char)cf[2], (unsigned char)cf[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++)
+        if (p0 + k < C) {
+          ws.cand[p0 + k] = cvv[k];
+          ws.cflag[p0 + k] = (uint8_t)cf[k];
+        }
     }
     __syncthreads();
   }
@@ -389,58 +410,76 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
   for (int t = t0; t < t1; t++) {
-    // phased so the GS_IPT random table reads of a thread are in flight together
+    // A thread owns GS_IPT consecutive positions: vector loads / stores of the
+    // stream, its GS_IPT random table reads in flight together, lane-local
+    // packed counts and one warp reduction per tile.
     unsigned long long pk_i = 0ull, pk_e = 0ull;  // this lane's firsts / edges per part
     uint32_t n_ff = 0u;
     uint32_t fl[GS_IPT], te[GS_IPT];
     int32_t ci[GS_IPT], cv[GS_IPT];
+    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
+    const bool full = p0 + GS_IPT <= C;
+    if (full) {
+      const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+      const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
+      ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
+      fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
+    } else {
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      fl[it] = GS_CF_LOOP;  // dead lane
-      ci[it] = 0;
-      if (p < C) {
-        fl[it] = ws.cflag[p];
-        ci[it] = ws.cand[p];
+      for (int k = 0; k < GS_IPT; k++) {
+        fl[k] = GS_CF_LOOP;  // dead position
+        ci[k] = 0;
+        if (p0 + k < C) {
+          fl[k] = ws.cflag[p0 + k];
+          ci[k] = ws.cand[p0 + k];
+        }
       }
     }
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) cv[it] = (fl[it] & GS_CF_SELF) ? front[ci[it]] : ci[it];
+    for (int k = 0; k < GS_IPT; k++) cv[k] = (fl[k] & GS_CF_SELF) ? front[ci[k]] : ci[k];
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      te[it] = 0u;
-      if (!(fl[it] & GS_CF_LOOP)) te[it] = tbl.ld(cv[it]);
+    for (int k = 0; k < GS_IPT; k++) {
+      te[k] = 0u;
+      if (!(fl[k] & GS_CF_LOOP)) te[k] = tbl.ld(cv[k]);
     }
 #pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const uint32_t p = (uint32_t)t * GS_TILE + it * GS_TPB + threadIdx.x;
-      bool ffirst = false, ifirst = false, edge = false;
-      int g = 0;
-      uint32_t f = fl[it];
+    for (int k = 0; k < GS_IPT; k++) {
+      const uint32_t p = p0 + k;
+      const uint32_t f = fl[k];
       if (f & GS_CF_SELF) {
-        const uint32_t a = te[it];
-        ws.rowa[ci[it]] = a;
-        ffirst = a > p;
+        const uint32_t a = te[k];
+        ws.rowa[ci[k]] = a;
+        const bool ffirst = a > p;
         if (ffirst && a != GS_INF) {  // revoke the claim of the edge candidate at a
           ws.kill[a] = 1;
           atomicSub(&ws.ctile_cnt[min((int)(a / GS_TILE) / per, (int)gridDim.x - 1)], 1u);
         }
-        f = GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u);
+        n_ff += ffirst ? 1u : 0u;
+        fl[k] = GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u);
       } else if (!(f & GS_CF_LOOP)) {
-        edge = true;
-        ifirst = te[it] == p;
-        ffirst = ifirst;  // unless revoked
-        g = owner_of(ws, cv[it]);
-        if (!ifirst) ci[it] = (int32_t)te[it];
-        f = (ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
+        const bool ifirst = te[k] == p;  // also claims the frontier slot, unless revoked
+        const int g = owner_of(ws, cv[k]);
+        pk_e += pk_one(g);
+        if (ifirst) {
+          pk_i += pk_one(g);
+          n_ff++;
+        } else {
+          ci[k] = (int32_t)te[k];
+        }
+        fl[k] = (ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
       }
-      if (p < C) {  // whole lines go back, not scattered words
-        ws.cand[p] = ci[it];
-        ws.cflag[p] = (uint8_t)f;
-      }
-      n_ff += ffirst ? 1u : 0u;
-      if (edge) pk_e += pk_one(g);
-      if (ifirst) pk_i += pk_one(g);
+    }
+    if (full) {
+      *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
+          make_uchar4((unsigned char)fl[0], (unsigned char)fl[1], (unsigned char)fl[2], (unsigned char)fl[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++)
+        if (p0 + k < C) {
+          ws.cand[p0 + k] = ci[k];
+          ws.cflag[p0 + k] = (uint8_t)fl[k];
+        }
     }
     // one packed reduction per tile instead of 2P+1 ballots per round
     pk_i = pk_warp_sum(pk_i);
@@ -526,47 +565,52 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   if (threadIdx.x < NC) s_run[t0 & 1][threadIdx.x] = ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x];
   for (int t = t0; t < t1; t++) {
     __syncthreads();
-    const uint32_t wbase = (uint32_t)t * GS_TILE + (uint32_t)w * (GS_IPT * 32);
+    // A lane owns GS_IPT consecutive positions, a warp 32 * GS_IPT: in-warp order
+    // is position order, ONE packed scan per warp and tile gives every lane the
+    // per-part counts before its first position; it then ranks its own items.
+    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
+    const bool full = p0 + GS_IPT <= C;
     uint32_t f[GS_IPT];
     int32_t ci[GS_IPT], cv[GS_IPT];
+    if (full) {
+      const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+      const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
+      ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
+      f[0] = f4.x; f[1] = f4.y; f[2] = f4.z; f[3] = f4.w;
+    } else {
 #pragma unroll
-    for (int r = 0; r < GS_IPT; r++) {
-      const uint32_t p = wbase + r * 32 + lane;
-      f[r] = GS_CF_LOOP;  // dead lane: neither edge nor first
-      ci[r] = 0;
-      if (p < C) {
-        f[r] = ws.cflag[p];
-        ci[r] = ws.cand[p];
-        // an edge candidate's claim on the frontier slot may have been revoked
-        // by the node's earlier self entry (k_cand_flags); leave kill[] zeroed
-        if ((f[r] & (GS_CF_FFIRST | GS_CF_SELF)) == GS_CF_FFIRST && ws.kill[p]) {
-          f[r] &= ~GS_CF_FFIRST;
-          ws.kill[p] = 0;
+      for (int k = 0; k < GS_IPT; k++) {
+        f[k] = GS_CF_LOOP;  // dead position: neither edge nor first
+        ci[k] = 0;
+        if (p0 + k < C) {
+          f[k] = ws.cflag[p0 + k];
+          ci[k] = ws.cand[p0 + k];
         }
       }
     }
+    unsigned long long pi = 0ull, pe = 0ull;
+    uint32_t nf = 0u;
 #pragma unroll
-    for (int r = 0; r < GS_IPT; r++) cv[r] = (f[r] & GS_CF_SELF) ? front[ci[r]] : ci[r];
-    // phase 1: per-warp totals of every class
-    {
-      unsigned long long pi = 0ull, pe = 0ull;
-      uint32_t nf = 0u;
-#pragma unroll
-      for (int r = 0; r < GS_IPT; r++) {
-        const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
-        if (!(f[r] & (GS_CF_SELF | GS_CF_LOOP))) pe += pk_one(g);
-        if (f[r] & GS_CF_IFIRST) pi += pk_one(g);
-        nf += (f[r] & GS_CF_FFIRST) ? 1u : 0u;
+    for (int k = 0; k < GS_IPT; k++) {
+      // an edge candidate's claim on the frontier slot may have been revoked by
+      // the node's earlier self entry (k_cand_flags); leave kill[] zeroed
+      if ((f[k] & (GS_CF_FFIRST | GS_CF_SELF)) == GS_CF_FFIRST && ws.kill[p0 + k]) {
+        f[k] &= ~GS_CF_FFIRST;
+        ws.kill[p0 + k] = 0;
       }
-      pi = pk_warp_sum(pi);
-      pe = pk_warp_sum(pe);
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) nf += __shfl_xor_sync(FULL, nf, d);
-      if (lane == 0) {
-        s_wi[w] = pi;
-        s_we[w] = pe;
-        s_wf[w] = nf;
-      }
+      cv[k] = (f[k] & GS_CF_SELF) ? front[ci[k]] : ci[k];
+      const int g = (int)(f[k] >> GS_CF_PART_SHIFT);
+      if (!(f[k] & (GS_CF_SELF | GS_CF_LOOP))) pe += pk_one(g);
+      if (f[k] & GS_CF_IFIRST) pi += pk_one(g);
+      nf += (f[k] & GS_CF_FFIRST) ? 1u : 0u;
+    }
+    // exclusive packed prefixes over the warp's lanes; lane 31 publishes the totals
+    const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe);
+    const uint32_t inc_f = warp_incl_scan(nf);
+    if (lane == 31) {
+      s_wi[w] = inc_i;
+      s_we[w] = inc_e;
+      s_wf[w] = inc_f;
     }
     __syncthreads();
     if (lane < NC) {  // lane = class: this warp's base, and (warp 0) the next tile's running counts
@@ -581,44 +625,41 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
       if (w == 0) s_run[(t + 1) & 1][cc] = s_run[t & 1][cc] + all;
     }
     __syncwarp();
-    // phase 2: ranks and scatter
-    uint32_t rf = s_base[w][0];
-    unsigned long long run_i = 0ull, run_e = 0ull;  // packed totals of this warp's earlier rounds
+    uint32_t rf = s_base[w][0] + inc_f - nf;
+    unsigned long long ri = inc_i - pi, re = inc_e - pe;  // packed counts of this warp before the lane's item
+    uint32_t myrank[GS_IPT];
 #pragma unroll
-    for (int r = 0; r < GS_IPT; r++) {
-      const uint32_t p = wbase + r * 32 + lane;
-      const int g = (int)(f[r] >> GS_CF_PART_SHIFT);
-      const bool isself = (f[r] & GS_CF_SELF) != 0u;
-      const bool edge = !(f[r] & (GS_CF_SELF | GS_CF_LOOP));
-      const bool ffirst = (f[r] & GS_CF_FFIRST) != 0u, ifirst = (f[r] & GS_CF_IFIRST) != 0u;
-      const uint32_t mf = __ballot_sync(FULL, ffirst);
-      if (ffirst) fnext[rf + __popc(mf & ltm)] = cv[r];
-      rf += __popc(mf);
-      const unsigned long long one_e = edge ? pk_one(g) : 0ull, one_i = ifirst ? pk_one(g) : 0ull;
-      const unsigned long long inc_e = pk_warp_incl(one_e), inc_i = pk_warp_incl(one_i);
-      const unsigned long long before_e = run_e + inc_e - one_e;  // part-q edges of this warp before this position
-      uint32_t myrank = 0u;
-      if (edge) {
-        const uint32_t ex = s_base[w][1 + P + g] + pk_get(before_e, g);
+    for (int k = 0; k < GS_IPT; k++) {
+      const int g = (int)(f[k] >> GS_CF_PART_SHIFT);
+      myrank[k] = 0u;
+      if (f[k] & GS_CF_FFIRST) fnext[rf++] = cv[k];
+      if (f[k] & GS_CF_SELF) {
+        uint32_t *rsp = ws.rowscan + ci[k];
+        for (int q = 0; q < P; q++, rsp += (size_t)ws.Fcap + 1) *rsp = s_base[w][1 + P + q] + pk_get(re, q);
+      } else if (!(f[k] & GS_CF_LOOP)) {
+        const uint32_t ex = s_base[w][1 + P + g] + pk_get(re, g);
         // An edge whose source occurs here for the first time knows its own
         // rank: it writes the final csr_indices value and records the rank at
         // its position (irank).  Every other edge carries the position m of
         // that first occurrence and leaves ~m (negative) for k_relabel.
-        int32_t ixv = ~cv[r];
-        if (ifirst) {
-          const uint32_t rk = s_base[w][1 + g] + pk_get(run_i + inc_i - one_i, g);
-          ws.slab[s_in_off[g] + rk] = cv[r];
-          myrank = rk;
+        int32_t ixv = ~cv[k];
+        if (f[k] & GS_CF_IFIRST) {
+          const uint32_t rk = s_base[w][1 + g] + pk_get(ri, g);
+          ws.slab[s_in_off[g] + rk] = cv[k];
+          myrank[k] = rk;
           ixv = (int32_t)rk;
+          ri += pk_one(g);
         }
         ws.slab[s_ix_off[g] + ex] = ixv;
+        re += pk_one(g);
       }
-      if (isself)
-        for (int q = 0; q < P; q++)
-          ws.rowscan[rs_at(ws, q, ci[r])] = s_base[w][1 + P + q] + pk_get(before_e, q);
-      if (p < C) ws.irank[p] = myrank;  // every position: one full line per warp round
-      run_e += __shfl_sync(FULL, inc_e, 31);
-      run_i += __shfl_sync(FULL, inc_i, 31);
+    }
+    if (full) {
+      *reinterpret_cast<uint4 *>(ws.irank + p0) = make_uint4(myrank[0], myrank[1], myrank[2], myrank[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++)
+        if (p0 + k < C) ws.irank[p0 + k] = myrank[k];
     }
   }
 }
@@ -901,7 +942,7 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
     int32_t *dst = (int32_t *)ws.hdr_host;
     for (int i = tid; i < nw; i += nth) dst[i] = src[i];
   }
-  if (ws.input->want_host && ws.slab_host && h->status == 0) {
+  if (h->reserved[0] && ws.slab_host && h->status == 0) {
     const int64_t n4 = h->slab_used >> 2;  // spans are 4-element aligned
     const int4 *src = (const int4 *)ws.slab;
     int4 *dst = (int4 *)ws.slab_host;
