@@ -439,6 +439,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.kill, s->Ccap);
     DA(w.irank, s->Ccap);
     DA(w.rowa, s->Fcap);
+    DA(w.rowhas, s->Fcap + 4);
     DA(w.tile_first, ctiles + 1);
     DA(w.ftile_sum, ftiles);
     DA(w.ftile_samp, ftiles);

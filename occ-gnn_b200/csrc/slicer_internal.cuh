@@ -59,6 +59,7 @@ struct GsWs {
   uint8_t *cflag;        // [Ccap]
   uint8_t *kill;         // [Ccap] 1: the edge candidate here is NOT a frontier first (its node's self entry came earlier); zero between layers
   uint32_t *irank;       // [Ccap] rank in in_nodes_g of the first edge occurrence at this position
+  uint8_t *rowhas;       // [Fcap] bit q: row emitted >= 1 edge into part q (k_front_count -> k_front_apply)
   uint32_t *rowa;        // [Fcap] table value (min edge-source position) of every row's node
   uint32_t *tile_first;  // [ctiles_max+1] row containing candidate t*GS_TILE
   unsigned long long *ftile_sum; // [ftiles_max] candidates per frontier tile

@@ -670,11 +670,11 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
 // (bipartite.h:56-58); to_g0 = any has_h, h != g0 (slicer.cpp:41);
 // self_g0 = always (slicer.cpp:33-34).  from_g = out_g && g != g0 needs no
 // counter: its rank is rank(out_g) - rank(owned_g).
-__device__ __forceinline__ uint32_t row_has_mask(const GsWs &ws, int i, int P) {
-  uint32_t m = 0u;
-  for (int q = 0; q < P; q++)
-    if (ws.rowscan[rs_at(ws, q, i + 1)] != ws.rowscan[rs_at(ws, q, i)]) m |= 1u << q;
-  return m;
+// bit q of a mask -> byte q of a packed counter word
+__device__ __forceinline__ unsigned long long pk_spread(uint32_t mask, int P) {
+  unsigned long long v = 0ull;
+  for (int q = 0; q < P; q++) v |= (unsigned long long)((mask >> q) & 1u) << (8 * q);
+  return v;
 }
 
 __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
@@ -692,35 +692,55 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
   for (int t = t0; t < t1; t++) {
-    uint32_t has[GS_IPT];
-    int g0[GS_IPT];
-#pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {  // all row lookups in flight together
-      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-      has[it] = 0u;
-      g0[it] = -1;
-      if (i < F) {
-        g0[it] = owner_of(ws, front[i]);
-        has[it] = row_has_mask(ws, i, P);
-      }
-    }
-#pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const bool to = g0[it] >= 0 && (has[it] & ~(1u << g0[it])) != 0u;
+    // a thread owns GS_IPT consecutive rows: per part, GS_IPT + 1 consecutive
+    // rowscan values give the rows' edge counts; classes are counted in packed
+    // words (one byte per part) and reduced once per warp and tile
+    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u};
+    if (i0 < F) {
+      const int nk = min(GS_IPT, F - i0);
       for (int q = 0; q < P; q++) {
-        const bool hq = (has[it] >> q) & 1u;
-        const uint32_t m_out = __ballot_sync(FULL, hq);
-        const uint32_t m_own = __ballot_sync(FULL, hq && g0[it] == q);
-        const uint32_t m_to = __ballot_sync(FULL, to && g0[it] == q);
-        const uint32_t m_self = __ballot_sync(FULL, g0[it] == q);
-        if (lane_id() == 0) {
-          if (m_out) atomicAdd(&s_cnt[q], (uint32_t)__popc(m_out));
-          if (m_own) atomicAdd(&s_cnt[P + q], (uint32_t)__popc(m_own));
-          if (m_to) atomicAdd(&s_cnt[2 * P + q], (uint32_t)__popc(m_to));
-          if (m_self) atomicAdd(&s_cnt[3 * P + q], (uint32_t)__popc(m_self));
-        }
+        const uint32_t *rs = ws.rowscan + rs_at(ws, q, i0);
+        uint32_t prev = rs[0];
+#pragma unroll
+        for (int k = 0; k < GS_IPT; k++)
+          if (k < nk) {
+            const uint32_t nx = rs[k + 1];
+            if (nx != prev) has[k] |= 1u << q;
+            prev = nx;
+          }
       }
     }
+    unsigned long long p_out = 0ull, p_own = 0ull, p_to = 0ull, p_self = 0ull;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++)
+      if (i0 + k < F) {
+        const int g0 = owner_of(ws, front[i0 + k]);
+        p_out += pk_spread(has[k], P);
+        p_self += pk_one(g0);
+        if ((has[k] >> g0) & 1u) p_own += pk_one(g0);
+        if (has[k] & ~(1u << g0)) p_to += pk_one(g0);
+      }
+    if (i0 + GS_IPT <= F) {
+      *reinterpret_cast<uchar4 *>(ws.rowhas + i0) =
+          make_uchar4((unsigned char)has[0], (unsigned char)has[1], (unsigned char)has[2], (unsigned char)has[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++)
+        if (i0 + k < F) ws.rowhas[i0 + k] = (uint8_t)has[k];
+    }
+    p_out = pk_warp_sum(p_out);
+    p_own = pk_warp_sum(p_own);
+    p_to = pk_warp_sum(p_to);
+    p_self = pk_warp_sum(p_self);
+    if (lane_id() == 0)
+      for (int q = 0; q < P; q++) {
+        const uint32_t a = pk_get(p_out, q), b = pk_get(p_own, q), c = pk_get(p_to, q), d = pk_get(p_self, q);
+        if (a) atomicAdd(&s_cnt[q], a);
+        if (b) atomicAdd(&s_cnt[P + q], b);
+        if (c) atomicAdd(&s_cnt[2 * P + q], c);
+        if (d) atomicAdd(&s_cnt[3 * P + q], d);
+      }
   }
   __syncthreads();
   if (threadIdx.x < NF) ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x] = s_cnt[threadIdx.x];
@@ -753,7 +773,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  __shared__ uint32_t s_wcnt[GS_NW][GS_NF_MAX];
+  __shared__ unsigned long long s_wp[GS_NW][4];  // per-warp packed totals: out, own, to, self
   __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
   __shared__ uint32_t s_run[2][GS_NF_MAX];
   __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
@@ -765,116 +785,94 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
     s_off[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
         h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
   const int lane = lane_id(), w = warp_id();
-  const uint32_t ltm = lt_mask();
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
   if (threadIdx.x < NF) s_run[t0 & 1][threadIdx.x] = ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x];
   for (int t = t0; t < t1; t++) {
     __syncthreads();
-    const int wbase = t * GS_TILE + w * (GS_IPT * 32);
-    uint32_t has[GS_IPT];
+    // a lane owns GS_IPT consecutive rows (row order = list order); four packed
+    // scans per warp and tile give it the per-part ranks before its first row
+    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u};
     int g0[GS_IPT];
-    int32_t nd[GS_IPT];
+    int32_t nd[GS_IPT] = {0, 0, 0, 0};
+    if (i0 + GS_IPT <= F) {
+      const uchar4 h4 = *reinterpret_cast<const uchar4 *>(ws.rowhas + i0);
+      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
+      has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
+      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
+    } else {
 #pragma unroll
-    for (int r = 0; r < GS_IPT; r++) {
-      const int i = wbase + r * 32 + lane;
-      has[r] = 0u;
-      g0[r] = -1;
-      nd[r] = 0;
-      if (i < F) {
-        nd[r] = front[i];
-        g0[r] = owner_of(ws, nd[r]);
-        has[r] = row_has_mask(ws, i, P);
-      }
-    }
-    {
-      uint32_t n_out[GS_MAX_PARTS], n_own[GS_MAX_PARTS], n_to[GS_MAX_PARTS], n_self[GS_MAX_PARTS];
-#pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++) n_out[q] = n_own[q] = n_to[q] = n_self[q] = 0u;
-#pragma unroll
-      for (int r = 0; r < GS_IPT; r++) {
-        const bool to = g0[r] >= 0 && (has[r] & ~(1u << g0[r])) != 0u;
-#pragma unroll
-        for (int q = 0; q < GS_MAX_PARTS; q++)
-          if (q < P) {
-            const bool hq = (has[r] >> q) & 1u;
-            n_out[q] += __popc(__ballot_sync(FULL, hq));
-            n_own[q] += __popc(__ballot_sync(FULL, hq && g0[r] == q));
-            n_to[q] += __popc(__ballot_sync(FULL, to && g0[r] == q));
-            n_self[q] += __popc(__ballot_sync(FULL, g0[r] == q));
-          }
-      }
-      if (lane == 0) {
-#pragma unroll
-        for (int q = 0; q < GS_MAX_PARTS; q++)
-          if (q < P) {
-            s_wcnt[w][q] = n_out[q];
-            s_wcnt[w][P + q] = n_own[q];
-            s_wcnt[w][2 * P + q] = n_to[q];
-            s_wcnt[w][3 * P + q] = n_self[q];
-          }
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x < NF * GS_NW) {
-      const int cc = threadIdx.x / GS_NW, ww = threadIdx.x % GS_NW;
-      uint32_t a = s_run[t & 1][cc];
-      for (int k = 0; k < ww; k++) a += s_wcnt[k][cc];
-      s_base[ww][cc] = a;
-      if (ww == GS_NW - 1) s_run[(t + 1) & 1][cc] = a + s_wcnt[ww][cc];
-    }
-    __syncthreads();
-    uint32_t b_out[GS_MAX_PARTS], b_own[GS_MAX_PARTS], b_to[GS_MAX_PARTS], b_self[GS_MAX_PARTS];
-#pragma unroll
-    for (int q = 0; q < GS_MAX_PARTS; q++) {
-      b_out[q] = q < P ? s_base[w][q] : 0u;
-      b_own[q] = q < P ? s_base[w][P + q] : 0u;
-      b_to[q] = q < P ? s_base[w][2 * P + q] : 0u;
-      b_self[q] = q < P ? s_base[w][3 * P + q] : 0u;
-    }
-#pragma unroll
-    for (int r = 0; r < GS_IPT; r++) {
-      const int i = wbase + r * 32 + lane;
-      const bool live = i < F;
-      const bool to = g0[r] >= 0 && (has[r] & ~(1u << g0[r])) != 0u;
-      int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
-      uint32_t p_to = 0u, p_self = 0u;
-#pragma unroll
-      for (int q = 0; q < GS_MAX_PARTS; q++)
-        if (q < P) {
-          const bool hq = (has[r] >> q) & 1u;
-          const uint32_t m_out = __ballot_sync(FULL, hq);
-          const uint32_t m_own = __ballot_sync(FULL, hq && g0[r] == q);
-          const uint32_t m_to = __ballot_sync(FULL, to && g0[r] == q);
-          const uint32_t m_self = __ballot_sync(FULL, g0[r] == q);
-          if (hq) {
-            const uint32_t op = b_out[q] + __popc(m_out & ltm);
-            const uint32_t ow = b_own[q] + __popc(m_own & ltm);
-            ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd[r];
-            ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[rs_at(ws, q, i)];
-            if (q == g0[r]) {
-              ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
-              op_own = (int32_t)op;
-            } else {
-              ws.slab[s_off[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
-            }
-          }
-          if (g0[r] == q) {
-            p_to = b_to[q] + __popc(m_to & ltm);
-            p_self = b_self[q] + __popc(m_self & ltm);
-          }
-          b_out[q] += __popc(m_out);
-          b_own[q] += __popc(m_own);
-          b_to[q] += __popc(m_to);
-          b_self[q] += __popc(m_self);
+      for (int k = 0; k < GS_IPT; k++)
+        if (i0 + k < F) {
+          has[k] = ws.rowhas[i0 + k];
+          nd[k] = front[i0 + k];
         }
-      if (live) {
-        const int gq = g0[r];
-        if (to) ws.slab[s_off[gq][GS_F_TO_IDS] + p_to] = op_own;
-        const uint32_t a = ws.rowa[i];  // position of the node's first edge occurrence, or INF: never an edge source
-        ws.slab[s_off[gq][GS_F_SELF_IN] + p_self] = a == GS_INF ? -1 : (int32_t)__ldcg(ws.irank + a);
-        ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self] = op_own;
+    }
+    unsigned long long p_out = 0ull, p_own = 0ull, p_to = 0ull, p_self = 0ull;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      g0[k] = -1;
+      if (i0 + k < F) {
+        g0[k] = owner_of(ws, nd[k]);
+        p_out += pk_spread(has[k], P);
+        p_self += pk_one(g0[k]);
+        if ((has[k] >> g0[k]) & 1u) p_own += pk_one(g0[k]);
+        if (has[k] & ~(1u << g0[k])) p_to += pk_one(g0[k]);
       }
+    }
+    const unsigned long long i_out = pk_warp_incl(p_out), i_own = pk_warp_incl(p_own),
+                             i_to = pk_warp_incl(p_to), i_self = pk_warp_incl(p_self);
+    if (lane == 31) {
+      s_wp[w][0] = i_out;
+      s_wp[w][1] = i_own;
+      s_wp[w][2] = i_to;
+      s_wp[w][3] = i_self;
+    }
+    __syncthreads();
+    if (lane < NF) {  // lane = class (kind * P + part): this warp's base, warp 0 also the next tile's start
+      const int kind = lane / P, q = lane % P;
+      uint32_t a = s_run[t & 1][lane], all = 0u;
+      for (int k = 0; k < GS_NW; k++) {
+        const uint32_t c = pk_get(s_wp[k][kind], q);
+        if (k < w) a += c;
+        all += c;
+      }
+      s_base[w][lane] = a;
+      if (w == 0) s_run[(t + 1) & 1][lane] = s_run[t & 1][lane] + all;
+    }
+    __syncwarp();
+    unsigned long long r_out = i_out - p_out, r_own = i_own - p_own, r_to = i_to - p_to, r_self = i_self - p_self;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      const int i = i0 + k;
+      if (i >= F) break;
+      const int gq = g0[k];
+      int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+      for (int q = 0; q < P; q++)
+        if ((has[k] >> q) & 1u) {
+          const uint32_t op = s_base[w][q] + pk_get(r_out, q);
+          const uint32_t ow = s_base[w][P + q] + pk_get(r_own, q);
+          ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd[k];
+          ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[rs_at(ws, q, i)];
+          if (q == gq) {
+            ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+            op_own = (int32_t)op;
+          } else {
+            ws.slab[s_off[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+          }
+        }
+      if (has[k] & ~(1u << gq)) {
+        ws.slab[s_off[gq][GS_F_TO_IDS] + s_base[w][2 * P + gq] + pk_get(r_to, gq)] = op_own;
+        r_to += pk_one(gq);
+      }
+      const uint32_t p_self_rank = s_base[w][3 * P + gq] + pk_get(r_self, gq);
+      const uint32_t a = ws.rowa[i];  // position of the node's first edge occurrence, or INF: never an edge source
+      ws.slab[s_off[gq][GS_F_SELF_IN] + p_self_rank] = a == GS_INF ? -1 : (int32_t)__ldcg(ws.irank + a);
+      ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self_rank] = op_own;
+      r_out += pk_spread(has[k], P);
+      r_self += pk_one(gq);
+      if ((has[k] >> gq) & 1u) r_own += pk_one(gq);
     }
   }
 }
