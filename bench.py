@@ -213,33 +213,32 @@ def kernel_bytes(view, P):
         lists = sum(view.field_len(l, g, k) for g in range(P)
                     for k in ("owned_out_nodes", "from_ids", "to_ids", "self_ids_in", "self_ids_out"))
         out[f"rows_count@{l}"] = F * (4 + 16) + F * 12
-        out[f"rows_scan@{l}"] = F * 8 + F * (4 + 8 + 4 + 1)
-        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4 + 1 + 4)
-        out[f"cand_flags@{l}"] = C * (4 + 1 + 8) + C * 1
-        out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + n_in * 4 + F * P * 4
-        out[f"front_count@{l}"] = F * (4 + P * 4)
-        out[f"front_apply@{l}"] = F * (4 + P * 4 + 8) + (2 * n_out + lists) * 4
-        out[f"relabel@{l}"] = E * (4 + 8 + 4)
+        out[f"rows_scan@{l}"] = F * 8 + F * (4 + 4)                       # counts in, off + table reset out
+        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5            # pick + red.min per edge, stream out
+        out[f"cand_flags@{l}"] = C * 5 + C * 4 + C * 5 + F * 4             # stream in, table read, stream out, rowa
+        out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + C * 4 + F * P * 4   # stream in, lists, irank, rowscan
+        out[f"front_count@{l}"] = F * (4 + P * 4 + 1)
+        out[f"front_apply@{l}"] = F * (4 + 1 + 4 + 4) + n_out * 4 + (2 * n_out + lists) * 4
+        out[f"relabel@{l}"] = E * (4 + 4) + (E - n_in) * 4
     return out
 
 
 def random_accesses(view, P):
-    """Random (data-dependent) 4/8-byte accesses one minibatch makes, by target:
-    CSR (indptr pairs + neighbour picks) and the slot's dedup table."""
-    csr = tab = 0
+    """Random (data-dependent) 4-byte accesses one minibatch makes, by target:
+    CSR (indptr pairs + neighbour picks), the slot's N-sized dedup table, and the
+    C-sized position-indexed rank array."""
+    csr = tab = pos = 0
     for l in range(view.num_layers):
         F, C = view.frontier_len[l], view.cand_len[l]
         E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
         n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
         csr += F + (C - F)          # indptr[nd], one neighbour pick per non-self candidate
-        tab += F                    # k_rows_scan: entry (re)initialised with the self position
-        tab += (C - F)              # k_expand: atomicMin
+        tab += F                    # k_rows_scan: entry reset
+        tab += (C - F)              # k_expand: red.min
         tab += C                    # k_cand_flags: read
-        tab += n_in                 # k_cand_apply: rank written back
-        tab += E - n_in             # k_relabel: read, only for edges that are not a first occurrence
-        tab += F                    # k_front_apply: read (self_ids_in)
-    tab += view.frontier_len[view.num_layers]  # k_finish: sparse reset
-    return csr, tab
+        pos += E - n_in             # k_relabel: rank of the first occurrence, by position
+        pos += F                    # k_front_apply: self_ids_in
+    return csr, tab, pos
 
 
 def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
@@ -300,7 +299,7 @@ def own_arm(args):
     kbytes = kernel_bytes(v, P)
     sizes = dict(frontier=v.frontier_len, candidates=v.cand_len, edges=v.edges,
                  slab_bytes=v.slab_used * 4)
-    ra_csr, ra_tab = random_accesses(v, P)
+    ra_csr, ra_tab, ra_pos = random_accesses(v, P)
     v.release()
 
     def barrier():
@@ -332,7 +331,7 @@ def own_arm(args):
         roof = {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
                 "what": "algorithmic bytes of one minibatch (SURVEY 8(d), w=4) x minibatches/s per GPU, "
-                        "all 26 kernels of the chain, slots pipelined on streams",
+                        f"all {dev.launches_per_sample} kernels of the chain, slots pipelined on streams",
                 "algorithmic_bytes_per_minibatch": int(alg_bytes),
                 "chain_ms_eager_single_stream": round(chain_ms, 4),
                 "chain_gbs_eager_single_stream": round(alg_bytes / (chain_ms * 1e-3) / 1e9, 2),
@@ -344,10 +343,10 @@ def own_arm(args):
                 "kernels_ms": {k: round(ms, 4) for k, ms in prof}}
         # what the path is really bound by: random sector accesses, not streamed bytes
         g_csr = gather_yardstick(torch, ix.size, torch.int32)
-        g_tab = gather_yardstick(torch, n * args.slots, torch.int64)
-        floor_s = ra_csr / g_csr + ra_tab / g_tab
+        g_tab = gather_yardstick(torch, n * args.slots, torch.int32)
+        floor_s = ra_csr / g_csr + (ra_tab + ra_pos) / g_tab
         roof["random_access"] = {
-            "per_minibatch": {"csr_4B": int(ra_csr), "table_8B": int(ra_tab)},
+            "per_minibatch": {"csr_4B": int(ra_csr), "table_4B": int(ra_tab), "rank_by_position_4B": int(ra_pos)},
             "yardstick_gelem_s": {"csr_array": round(g_csr / 1e9, 2),
                                   "tables_all_slots": round(g_tab / 1e9, 2)},
             "floor_us_per_minibatch": round(floor_s * 1e6, 1),
