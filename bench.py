@@ -408,14 +408,14 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     the kernels' own stores / red.min into peer memory over NVLink.  Capacity
     mode (papers100M-scale graphs, sharded features); the replicated mode above
     is the throughput mode.  -> dict for the bench line (rank 0), None elsewhere."""
-    from cslicer.partitioned import PartitionedSlicer, connect_process_group, partition_csr
+    from cslicer.partitioned import PartitionedPipeline, partition_csr
     from cslicer.sharding import reduce_job
     n = ip.size - 1
     lip, lix = partition_csr(ip, ix, world)[rank]
-    ps = PartitionedSlicer(lip, lix, n, rank, world, FANOUTS, device=local, max_batch=BATCH,
-                           num_slots=2, seed=7, host_output=False, num_edges_global=ix.size,
-                           grid_ctas=args.grid_ctas)
-    connect_process_group(ps, dist)
+    lanes, depth = args.lanes, 2 * args.lanes
+    ps = PartitionedPipeline(lip, lix, n, rank, world, FANOUTS, dist, lanes=lanes, device=local,
+                             max_batch=BATCH, num_slots=2, seed=7, host_output=False,
+                             num_edges_global=ix.size, grid_ctas=args.grid_ctas)
     batches = seed_batches(n, 64, 0, 1)  # every rank is given the same batches
 
     def run(k):
@@ -424,15 +424,15 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
         inflight, edges = [], 0
         e0.record()
         for i in range(k):
-            if len(inflight) == 2:
-                slot = inflight.pop(0)
-                edges += ps.wait_header(slot).edges
-                ps.release(slot)
+            if len(inflight) == depth:
+                tk = inflight.pop(0)
+                edges += ps.wait_header(tk).edges
+                ps.release(tk)
             bi, seeds = batches[i % len(batches)]
             inflight.append(ps.submit(seeds, bi))
-        for slot in inflight:
-            edges += ps.wait_header(slot).edges
-            ps.release(slot)
+        for tk in inflight:
+            edges += ps.wait_header(tk).edges
+            ps.release(tk)
         e1.record()
         torch.cuda.synchronize()
         return e0.elapsed_time(e1), edges
@@ -452,7 +452,7 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
         xbytes = e_mb * (world - 1) / world * 9 + sum(fr[1:]) * 8 * (world - 1) + BATCH * 4
         out = {"value": round(1e3 / per_mb, 2), "unit": "minibatches/s (whole job, every rank works on every minibatch)",
                "ms_per_minibatch": round(per_mb, 4), "sampled_edges_per_s": round(edges / (ms * 1e-3), 1),
-               "ranks": world, "parts": world, "launches_per_minibatch_per_rank": ps.launches_per_sample,
+               "ranks": world, "parts": world, "lanes_per_rank": lanes, "launches_per_minibatch_per_rank": ps.launches_per_sample,
                "barriers_per_minibatch": 3 * len(FANOUTS) + 1,
                "device_bytes_per_rank": int(ps.device_bytes),
                "graph_shard_bytes_per_rank": int(lip.size * 8 + lix.size * 4),
@@ -641,6 +641,7 @@ def main():
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
     ap.add_argument("--no-partitioned", action="store_true",
                     help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")
     args = ap.parse_args()

@@ -197,6 +197,47 @@ def connect_process_group(ps, dist):
     return ps
 
 
+class PartitionedPipeline:
+    """Several minibatches in flight per rank: `lanes` independent partitioned
+    slicers (own arena, workspaces, stream and barrier flags each), minibatch b
+    runs on lane b % lanes on every rank.  A lane's 3L+1 barriers then overlap
+    with the kernels of the other lanes.  Collective constructor (one process
+    per GPU): every rank builds the same lanes in the same order."""
+
+    def __init__(self, indptr_local, indices_local, num_nodes, rank, num_parts, fanouts, dist, *,
+                 lanes=4, **kw):
+        self.lanes = [PartitionedSlicer(indptr_local, indices_local, num_nodes, rank, num_parts,
+                                        fanouts, **kw) for _ in range(int(lanes))]
+        for ps in self.lanes:
+            connect_process_group(ps, dist)
+        self.rank, self.num_parts = int(rank), int(num_parts)
+        self.launches_per_sample = self.lanes[0].launches_per_sample
+        self.device_bytes = sum(ps.device_bytes for ps in self.lanes)
+        self._next = 0
+
+    def submit(self, seeds, batch_index=0):
+        """-> ticket (lane, slot)"""
+        k = self._next
+        self._next = (k + 1) % len(self.lanes)
+        return k, self.lanes[k].submit(seeds, batch_index)
+
+    def wait(self, ticket):
+        return self.lanes[ticket[0]].wait(ticket[1])
+
+    def wait_header(self, ticket):
+        return self.lanes[ticket[0]].wait_header(ticket[1])
+
+    def release(self, ticket):
+        self.lanes[ticket[0]].release(ticket[1])
+
+    def slice(self, seeds, batch_index=0):
+        return self.wait(self.submit(seeds, batch_index))
+
+    def close(self):
+        for ps in self.lanes:
+            ps.close()
+
+
 class LocalGroup:
     """P ranks in one process on one device, sharing one stream: the segments of
     a minibatch are enqueued rank after rank, so every barrier wait finds its

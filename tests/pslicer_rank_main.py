@@ -15,7 +15,8 @@ for p in (os.path.join(ROOT, "occ-gnn_b200"), ROOT, os.path.dirname(os.path.absp
 def main():
     import torch
     import torch.distributed as dist
-    from cslicer.partitioned import PartitionedSlicer, connect_process_group, partition_csr
+    from cslicer.partitioned import (PartitionedPipeline, PartitionedSlicer, connect_process_group,
+                                     partition_csr)
     from cslicer.synth import synth_graph
     from oracle import oracle as O
     from test_partitioned import _compare_rank
@@ -39,6 +40,19 @@ def main():
         v.release()
     dist.barrier()
     ps.close()
+    # several minibatches in flight per rank: independent lanes, barriers overlap
+    pp = PartitionedPipeline(lip, lix, n, rank, world, fan, dist, lanes=3, device=local, max_batch=512,
+                             num_slots=2, seed=77, num_edges_global=ix.size)
+    batches = [rng.permutation(n)[:512] for _ in range(9)]
+    tickets = [pp.submit(b, 100 + i) for i, b in enumerate(batches[:6])]
+    for i, b in enumerate(batches):
+        v = pp.wait(tickets[i])
+        _compare_rank(v, orc.slice(b, 100 + i), rank)
+        v.release()
+        if i + 6 < len(batches):
+            tickets.append(pp.submit(batches[i + 6], 100 + i + 6))
+    dist.barrier()
+    pp.close()
     print(f"rank {rank} ok", flush=True)
     dist.destroy_process_group()
 
