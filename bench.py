@@ -27,6 +27,8 @@ import sys
 import tempfile
 import time
 
+# partitioned mode runs several lanes (streams) whose barrier kernels must be co-resident
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (os.path.join(ROOT, "occ-gnn_b200"), ROOT):
     if p not in sys.path:
@@ -415,7 +417,7 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     lanes, depth = args.lanes, 2 * args.lanes
     ps = PartitionedPipeline(lip, lix, n, rank, world, FANOUTS, dist, lanes=lanes, device=local,
                              max_batch=BATCH, num_slots=2, seed=7, host_output=False,
-                             num_edges_global=ix.size, grid_ctas=args.grid_ctas)
+                             num_edges_global=ix.size, grid_ctas=args.grid_ctas, timeout_ms=2000)
     batches = seed_batches(n, 64, 0, 1)  # every rank is given the same batches
 
     def run(k):

@@ -390,9 +390,9 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   PA(w.ftile_pre, s->grid);
   PA(w.ctr, (size_t)PS_NCTR * s->grid);
   PA(w.tickets, 8);
-  PA(w.epoch, 1);
+  PA(w.epoch, 2);
   CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
-  CUS(cudaMemset(w.epoch, 0, sizeof(uint32_t)));
+  CUS(cudaMemset(w.epoch, 0, 2 * sizeof(uint32_t)));
   CUS(cudaMemset(w.rowrem, 0, (size_t)s->Fcap));
   s->slots.resize(cfg->num_slots);
   for (PSlot &sl : s->slots) {
@@ -595,6 +595,7 @@ int gs_pslicer_reset(gs_pslicer *s) {
   CU(cudaMemsetAsync(s->me.nf, 0, (size_t)s->Ccap * sizeof(uint2), s->stream));
   CU(cudaMemsetAsync(s->me.err, 0, sizeof(int32_t), s->stream));
   CU(cudaMemsetAsync(s->base.tickets, 0, 8 * sizeof(uint32_t), s->stream));
+  CU(cudaMemsetAsync(s->base.epoch + 1, 0, sizeof(uint32_t), s->stream));
   CU(cudaStreamSynchronize(s->stream));
   for (PSlot &sl : s->slots) sl.state = PSLOT_FREE;
   return GS_OK;

@@ -65,7 +65,7 @@ struct PsWs {
   uint32_t *ftile_pre; // [grid]
   uint32_t *ctr;       // [PS_NCTR][grid] per-CTA counters of the current spine kernel
   uint32_t *tickets;   // [8]
-  uint32_t *epoch;     // [1] barriers executed so far
+  uint32_t *epoch;     // [2] barriers executed so far; [1] != 0: a barrier timed out (group broken until reset)
   int32_t Fcap, Ccap, grid_max, timeout_ms;
   // per-slot
   gs_sample_header *hdr;

@@ -69,7 +69,10 @@ __global__ void pk_wait(PsWs ws) {
   const int q = threadIdx.x;
   const uint32_t e = *ws.epoch;
   bool timed_out = false;
-  if (q < ws.P) {
+  // epoch[1] != 0: an earlier barrier of this rank timed out; the group is broken
+  // until gs_pslicer_reset(), so do not spend timeout_ms on every later barrier
+  const bool broken = ws.epoch[1] != 0u;
+  if (q < ws.P && !broken) {
     const unsigned long long t0 = globaltimer_ns();
     const unsigned long long lim = (unsigned long long)ws.timeout_ms * 1000000ull;
     while ((int32_t)(ld_acquire_sys(ws.me.flags + q) - e) < 0) {
@@ -83,8 +86,9 @@ __global__ void pk_wait(PsWs ws) {
   const int any_to = __syncthreads_or(timed_out ? 1 : 0);
   if (threadIdx.x == 0) {
     const int32_t pe = *(volatile int32_t *)ws.me.err;
+    if (any_to) ws.epoch[1] = 1u;
     if (ws.hdr->status == 0) {
-      if (any_to) ws.hdr->status = (int32_t)GS_ERR_PEER;
+      if (any_to || broken) ws.hdr->status = (int32_t)GS_ERR_PEER;
       else if (pe != 0) ws.hdr->status = pe;
     }
   }
