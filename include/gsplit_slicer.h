@@ -233,6 +233,10 @@ typedef struct {
   int64_t slab_capacity;
   int64_t num_edges_global;                /* bounds fanout -1 layers; 0 = unknown */
   void *stream;                            /* cudaStream_t to run on; NULL = own stream */
+  const float *features_local_host;        /* optional [n_local x feature_dim] fp32: rows of the owned nodes, local order */
+  int32_t feature_dim;
+  int32_t reserved0;
+  int64_t feature_rows_capacity;           /* 0 = derive */
 } gs_pconfig;
 
 void gs_pconfig_default(gs_pconfig *cfg);
@@ -267,6 +271,11 @@ int gs_pslicer_wait(gs_pslicer *s, int32_t slot, const gs_sample_header **hdr_ou
 int gs_pslicer_slab(gs_pslicer *s, int32_t slot, const int32_t **device_slab,
                     const int32_t **host_slab);
 int gs_pslicer_release(gs_pslicer *s, int32_t slot);
+/* Fused input-feature gather (features_local_host set): rows of the LAST layer's
+ * in_nodes of this rank's part -- all owned by this rank, so the gather is local
+ * (python/data/bipartite.py:61-67, memory_manager.py:75-104). */
+int gs_pslicer_feature_slab(gs_pslicer *s, int32_t slot, const float **device_rows, int32_t *dim,
+                            int32_t *rows);
 /* After any error: every rank calls this (all streams idle) before the next submit. */
 int gs_pslicer_reset(gs_pslicer *s);
 int gs_pslicer_launches_per_sample(const gs_pslicer *s);

@@ -32,7 +32,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
            "gs_pslicer_num_segments", "gs_pslicer_submit", "gs_pslicer_stage",
            "gs_pslicer_enqueue", "gs_pslicer_commit", "gs_pslicer_wait", "gs_pslicer_slab",
-           "gs_pslicer_release", "gs_pslicer_reset", "gs_pslicer_launches_per_sample",
+           "gs_pslicer_release", "gs_pslicer_feature_slab", "gs_pslicer_reset", "gs_pslicer_launches_per_sample",
            "gs_pslicer_device_bytes"]
 
 
@@ -75,7 +75,9 @@ class PConfig(C.Structure):
                 ("grid_ctas", C.c_int32), ("timeout_ms", C.c_int32), ("use_graph", C.c_int32),
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
                 ("slab_capacity", C.c_int64), ("num_edges_global", C.c_int64),
-                ("stream", C.c_void_p)]
+                ("stream", C.c_void_p), ("features_local_host", C.c_void_p),
+                ("feature_dim", C.c_int32), ("reserved0", C.c_int32),
+                ("feature_rows_capacity", C.c_int64)]
 
 
 _lib = None
@@ -137,6 +139,8 @@ def lib():
     L.gs_pslicer_wait.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.POINTER(SampleHeader))]
     L.gs_pslicer_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
     L.gs_pslicer_release.argtypes = [C.c_void_p, C.c_int32]
+    L.gs_pslicer_feature_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                          C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.gs_pslicer_reset.argtypes = [C.c_void_p]
     L.gs_pslicer_launches_per_sample.argtypes = [C.c_void_p]
     L.gs_pslicer_device_bytes.restype = C.c_int64

@@ -139,18 +139,17 @@ class SampleView:
         import torch
         if self._released:
             raise RuntimeError("sample slot already released")
-        ptr, dim = C.c_void_p(), C.c_int32()
-        N.check(N.lib().gs_slicer_feature_slab(self._slicer._h, self.slot, C.byref(ptr), C.byref(dim)))
+        ptr, dim = self._slicer._feature_slab(self.slot)
         a, b = self.feature_part_off[g], self.feature_part_off[g + 1]
         dev = f"cuda:{self._slicer.graph.device}"
         if b == a:
-            return torch.empty((0, dim.value), dtype=torch.float32, device=dev)
+            return torch.empty((0, dim), dtype=torch.float32, device=dev)
 
         class _F:
             pass
         f = _F()
-        f.__cuda_array_interface__ = {"shape": (b - a, dim.value), "typestr": "<f4",
-                                      "data": (ptr.value + 4 * a * dim.value, False), "version": 2,
+        f.__cuda_array_interface__ = {"shape": (b - a, dim), "typestr": "<f4",
+                                      "data": (ptr + 4 * a * dim, False), "version": 2,
                                       "strides": None}
         f._owner = self
         return torch.as_tensor(f, device=dev)
@@ -264,6 +263,11 @@ class Slicer:
     def _release(self, slot):
         if getattr(self, "_h", None):
             N.lib().gs_slicer_release(self._h, slot)
+
+    def _feature_slab(self, slot):
+        ptr, dim = C.c_void_p(), C.c_int32()
+        N.check(N.lib().gs_slicer_feature_slab(self._h, slot, C.byref(ptr), C.byref(dim)))
+        return ptr.value, dim.value
 
     release = _release
 

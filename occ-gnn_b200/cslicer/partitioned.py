@@ -77,7 +77,7 @@ class PartitionedSlicer:
                  owner_mode="mod", bounds=None, device=0, max_batch=4096, num_slots=2, seed=0,
                  host_output=True, use_graph=True, stream=None, num_edges_global=0,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0,
-                 timeout_ms=5000):
+                 timeout_ms=5000, features_local=None, feature_rows_capacity=0):
         L = N.lib()
         ip = np.ascontiguousarray(indptr_local, dtype=np.int64)
         ix = np.ascontiguousarray(indices_local, dtype=np.int64)
@@ -99,6 +99,13 @@ class PartitionedSlicer:
         cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)
         cfg.slab_capacity, cfg.num_edges_global = int(slab_capacity), int(num_edges_global)
         cfg.stream = stream
+        feat = None
+        if features_local is not None:  # [n_local, dim] fp32 rows of the owned nodes, local order
+            feat = np.ascontiguousarray(features_local, dtype=np.float32)
+            if feat.ndim != 2 or feat.shape[0] != ip.size - 1:
+                raise ValueError("features_local must be [n_local, dim]")
+            cfg.features_local_host, cfg.feature_dim = feat.ctypes.data, int(feat.shape[1])
+            cfg.feature_rows_capacity = int(feature_rows_capacity)
         h = C.c_void_p()
         N.check(L.gs_pslicer_create(int(device), int(num_nodes), ip.size - 1, ix.size,
                                     ip.ctypes.data, ix.ctypes.data, C.byref(cfg), C.byref(h)))
@@ -163,6 +170,11 @@ class PartitionedSlicer:
     def _release(self, slot):
         if getattr(self, "_h", None):
             N.lib().gs_pslicer_release(self._h, slot)
+
+    def _feature_slab(self, slot):
+        ptr, dim, rows = C.c_void_p(), C.c_int32(), C.c_int32()
+        N.check(N.lib().gs_pslicer_feature_slab(self._h, slot, C.byref(ptr), C.byref(dim), C.byref(rows)))
+        return ptr.value, dim.value
 
     release = _release
 
@@ -252,7 +264,10 @@ class LocalGroup:
         n = len(indptr) - 1
         self._stream = torch.cuda.Stream(device=device)
         shards = partition_csr(indptr, indices, num_parts, owner_mode, bounds)
+        feats = kw.pop("features", None)  # [N, dim] -> every rank is given the rows it owns
+        own = owner_of(np.arange(n), n, num_parts, owner_mode, bounds) if feats is not None else None
         self.ranks = [PartitionedSlicer(ip, ix, n, g, num_parts, fanouts, owner_mode=owner_mode,
+                                        features_local=None if feats is None else feats[own == g],
                                         bounds=bounds, device=device, max_batch=max_batch,
                                         num_slots=num_slots, seed=seed, host_output=host_output,
                                         stream=self._stream.cuda_stream,

@@ -41,6 +41,7 @@ struct PSlot {
   int64_t *seeds = nullptr;
   gs_sample_header *hdr_host = nullptr;
   int32_t *slab_host = nullptr;
+  float *feat_out = nullptr;        // device
   cudaGraphExec_t exec = nullptr;
   cudaEvent_t done = nullptr;
   int state = PSLOT_FREE;
@@ -76,6 +77,8 @@ struct gs_pslicer {
   int64_t Fcap = 0, Ccap = 0, slab_cap = 0;
   int64_t *indptr = nullptr;
   int32_t *indices = nullptr;
+  float *feat = nullptr;  // [n_local][feat_dim]
+  int64_t feat_cap_rows = 0;
   char *arena = nullptr;
   size_t arena_bytes = 0;
   PsArena me{};
@@ -131,6 +134,7 @@ int enqueue_segment(gs_pslicer *s, PSlot &sl, int seg) {
         ps_launch_rows_scan(ws, l, s->grid_rows[l], st);
         ps_launch_signal(ws, st);
       } else {
+        if (s->feat) ps_launch_gather(ws, 8 * (s->grid / std::max(1, s->cfg.grid_ctas > 0 ? s->cfg.grid_ctas : 4)), st);
         ps_launch_finish(ws, s->grid, st);
       }
     } else if (k == 1) {
@@ -201,6 +205,7 @@ int gs_pslicer_destroy(gs_pslicer *s) {
     if (sl.done) cudaEventDestroy(sl.done);
     cudaFree(sl.hdr);
     cudaFree(sl.slab);
+    cudaFree(sl.feat_out);
     if (sl.input) cudaFreeHost(sl.input);
     if (sl.seeds) cudaFreeHost(sl.seeds);
     if (sl.hdr_host) cudaFreeHost(sl.hdr_host);
@@ -210,6 +215,7 @@ int gs_pslicer_destroy(gs_pslicer *s) {
     if (s->ipc_base[q]) cudaIpcCloseMemHandle(s->ipc_base[q]);
   for (void *p : s->dev) cudaFree(p);
   cudaFree(s->arena);
+  cudaFree(s->feat);
   cudaFree(s->indptr);
   cudaFree(s->indices);
   if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
@@ -264,6 +270,7 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   if (!s) return pfail(GS_ERR_INVALID, "out of host memory");
   s->device = device;
   s->cfg = *cfg;
+  s->cfg.features_local_host = nullptr;
   if (s->cfg.timeout_ms <= 0) s->cfg.timeout_ms = 5000;
   s->N = N;
   s->n_local = n_local;
@@ -357,6 +364,21 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
     CUS(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     s->own_stream = true;
   }
+  if (cfg->features_local_host) {
+    if (cfg->feature_dim < 1) {
+      gs_pslicer_destroy(s);
+      return pfail(GS_ERR_INVALID, "feature_dim must be >= 1");
+    }
+    const size_t fb = (size_t)std::max<int64_t>(n_local, 1) * cfg->feature_dim * sizeof(float);
+    CUS(cudaMalloc((void **)&s->feat, fb));
+    CUS(cudaMemcpy(s->feat, cfg->features_local_host, (size_t)n_local * cfg->feature_dim * sizeof(float),
+                   cudaMemcpyHostToDevice));
+    s->bytes += (int64_t)fb;
+    const int last = L - 1;
+    s->feat_cap_rows = cfg->feature_rows_capacity > 0
+                           ? cfg->feature_rows_capacity
+                           : std::max<int64_t>(1, std::min(n_local, Cb[last] - Fb[last]));
+  }
   // private workspaces
   PsWs &w = s->base;
   w.indptr = s->indptr;
@@ -377,6 +399,9 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   w.grid_max = s->grid;
   w.timeout_ms = s->cfg.timeout_ms;
   w.slab_cap = s->slab_cap;
+  w.feat = s->feat;
+  w.feat_dim = cfg->feature_dim;
+  w.feat_cap_rows = s->feat_cap_rows;
   const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;
   PA(w.rowstart, s->Fcap);
   PA(w.rowdeg, s->Fcap);
@@ -408,6 +433,10 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
     if (cfg->host_output)
       CUS(cudaHostAlloc((void **)&sl.slab_host, (size_t)(s->slab_cap + 4) * sizeof(int32_t), cudaHostAllocMapped));
     CUS(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    if (s->feat) {
+      CUS(cudaMalloc((void **)&sl.feat_out, (size_t)s->feat_cap_rows * cfg->feature_dim * sizeof(float)));
+      s->bytes += (int64_t)(s->feat_cap_rows * cfg->feature_dim * sizeof(float));
+    }
   }
   CUS(cudaDeviceSynchronize());
 #undef PA
@@ -472,6 +501,7 @@ int gs_pslicer_ready(gs_pslicer *s) {
     sl.ws = s->base;
     sl.ws.hdr = sl.hdr;
     sl.ws.slab = sl.slab;
+    sl.ws.feat_out = sl.feat_out;
     void *dp = nullptr;
     CU(cudaHostGetDevicePointer(&dp, sl.input, 0));
     sl.ws.input = (const GsInput *)dp;
@@ -575,6 +605,18 @@ int gs_pslicer_slab(gs_pslicer *s, int32_t slot, const int32_t **device_slab, co
   return GS_OK;
 }
 
+int gs_pslicer_feature_slab(gs_pslicer *s, int32_t slot, const float **device_rows, int32_t *dim,
+                            int32_t *rows) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return pfail(GS_ERR_INVALID, "bad slot");
+  if (!s->feat) return pfail(GS_ERR_STATE, "slicer was created without features_local_host");
+  PSlot &sl = s->slots[slot];
+  if (sl.state != PSLOT_DONE) return pfail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (device_rows) *device_rows = sl.feat_out;
+  if (dim) *dim = s->cfg.feature_dim;
+  if (rows) *rows = sl.hdr_host->feature_rows;
+  return GS_OK;
+}
+
 int gs_pslicer_release(gs_pslicer *s, int32_t slot) {
   if (!s || slot < 0 || slot >= (int)s->slots.size()) return pfail(GS_ERR_INVALID, "bad slot");
   PSlot &sl = s->slots[slot];
@@ -605,7 +647,7 @@ int gs_pslicer_launches_per_sample(const gs_pslicer *s) {
   if (!s) return 0;
   const int L = s->cfg.num_layers;
   // begin + finish, 7 kernels per layer, 3L+1 barriers of two launches each
-  return 2 + 7 * L + 2 * (3 * L + 1);
+  return 2 + 7 * L + 2 * (3 * L + 1) + (s->feat ? 1 : 0);
 }
 int64_t gs_pslicer_device_bytes(const gs_pslicer *s) { return s ? s->bytes : 0; }
 

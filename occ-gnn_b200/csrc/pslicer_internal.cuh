@@ -67,7 +67,11 @@ struct PsWs {
   uint32_t *tickets;   // [8]
   uint32_t *epoch;     // [2] barriers executed so far; [1] != 0: a barrier timed out (group broken until reset)
   int32_t Fcap, Ccap, grid_max, timeout_ms;
+  const float *feat;   // [n_local][feat_dim] rows of the owned nodes (optional)
+  int32_t feat_dim;
+  int64_t feat_cap_rows;
   // per-slot
+  float *feat_out;     // [feat_cap_rows][feat_dim]
   gs_sample_header *hdr;
   int32_t *slab;
   int64_t slab_cap;
@@ -88,4 +92,5 @@ void ps_launch_cand_apply(const PsWs &ws, int layer, int grid, cudaStream_t st);
 void ps_launch_front_count(const PsWs &ws, int layer, int grid, cudaStream_t st);
 void ps_launch_front_apply(const PsWs &ws, int layer, int grid, cudaStream_t st);
 void ps_launch_relabel(const PsWs &ws, int layer, int grid, cudaStream_t st);
+void ps_launch_gather(const PsWs &ws, int grid, cudaStream_t st);
 void ps_launch_finish(const PsWs &ws, int grid, cudaStream_t st);

@@ -702,6 +702,28 @@ __global__ void __launch_bounds__(GS_TPB) pk_relabel(PsWs ws, int layer) {
   }
 }
 
+// ----------------------------------------------------------------- pk_gather
+// Fused input-feature gather: in_nodes of this rank's part are nodes it owns, so
+// their rows are in the local shard.  One warp per 2408-byte row: streaming.
+__global__ void __launch_bounds__(GS_TPB) pk_gather(PsWs ws) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  const gs_span sp = h->field[ws.L - 1][ws.rank][GS_F_IN_NODES];
+  const int R = sp.len;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const bool fits = (int64_t)R <= ws.feat_cap_rows;
+    h->feature_rows = fits ? R : 0;
+    for (int q = 0; q <= ws.P; q++) h->feature_part_off[q] = (fits && q > ws.rank) ? R : 0;
+    if (!fits) h->late_status = (int32_t)GS_ERR_OVERFLOW;
+  }
+  if ((int64_t)R > ws.feat_cap_rows) return;
+  const int32_t *ids = ws.slab + sp.off;
+  const int lane = lane_id();
+  const int nwarps = gridDim.x * GS_NW;
+  for (int r = blockIdx.x * GS_NW + warp_id(); r < R; r += nwarps)
+    gather_row(ws.feat, ws.feat_dim, (int64_t)ps_local(ws, ids[r], ws.rank), ws.feat_out, r, lane);
+}
+
 // ----------------------------------------------------------------- pk_finish
 // Sparse reset of this rank's table (every node touched is in the last
 // frontier; this rank resets the ones it owns), header and slab -> pinned host.
@@ -759,4 +781,5 @@ void ps_launch_front_apply(const PsWs &ws, int layer, int grid, cudaStream_t st)
 void ps_launch_relabel(const PsWs &ws, int layer, int grid, cudaStream_t st) {
   pk_relabel<<<grid, GS_TPB, 0, st>>>(ws, layer);
 }
+void ps_launch_gather(const PsWs &ws, int grid, cudaStream_t st) { pk_gather<<<grid, GS_TPB, 0, st>>>(ws); }
 void ps_launch_finish(const PsWs &ws, int grid, cudaStream_t st) { pk_finish<<<grid, GS_TPB, 0, st>>>(ws); }

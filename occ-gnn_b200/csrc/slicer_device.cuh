@@ -205,4 +205,27 @@ __device__ __forceinline__ unsigned long long pk_warp_incl(unsigned long long v)
   return v;
 }
 
+// One warp copies one feature row; vector width chosen from dim (float4 / float2 / float).
+template <typename V>
+__device__ __forceinline__ void copy_row(const float *__restrict__ src, float *__restrict__ dst,
+                                         int nvec, int lane) {
+  const V *s = reinterpret_cast<const V *>(src);
+  V *d = reinterpret_cast<V *>(dst);
+  int k = lane;
+  for (; k + 96 < nvec; k += 128) {  // four independent loads in flight per lane
+    const V a = __ldg(s + k), b = __ldg(s + k + 32), c = __ldg(s + k + 64), e = __ldg(s + k + 96);
+    d[k] = a; d[k + 32] = b; d[k + 64] = c; d[k + 96] = e;
+  }
+  for (; k < nvec; k += 32) d[k] = __ldg(s + k);
+}
+__device__ __forceinline__ void gather_row(const float *feat, int dim, int64_t src_row, float *out,
+                                           int64_t dst_row, int lane) {
+  const float *src = feat + src_row * dim;
+  float *dst = out + dst_row * dim;
+  if ((dim & 3) == 0) copy_row<float4>(src, dst, dim >> 2, lane);
+  else if ((dim & 1) == 0) copy_row<float2>(src, dst, dim >> 1, lane);
+  else copy_row<float>(src, dst, dim, lane);
+}
+
+
 }  // namespace

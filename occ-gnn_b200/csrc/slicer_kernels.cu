@@ -953,27 +953,6 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
 // 8-byte but not 16-byte multiples, so the vector width is chosen from dim
 // (float4 / float2 / float); rows are contiguous, so unlike the id work above this
 // kernel streams whole lines and is bounded by plain HBM bandwidth.
-template <typename V>
-__device__ __forceinline__ void copy_row(const float *__restrict__ src, float *__restrict__ dst,
-                                         int nvec, int lane) {
-  const V *s = reinterpret_cast<const V *>(src);
-  V *d = reinterpret_cast<V *>(dst);
-  int k = lane;
-  for (; k + 96 < nvec; k += 128) {  // four independent loads in flight per lane
-    const V a = __ldg(s + k), b = __ldg(s + k + 32), c = __ldg(s + k + 64), e = __ldg(s + k + 96);
-    d[k] = a; d[k + 32] = b; d[k + 64] = c; d[k + 96] = e;
-  }
-  for (; k < nvec; k += 32) d[k] = __ldg(s + k);
-}
-__device__ __forceinline__ void gather_row(const float *feat, int dim, int64_t src_row, float *out,
-                                           int64_t dst_row, int lane) {
-  const float *src = feat + src_row * dim;
-  float *dst = out + dst_row * dim;
-  if ((dim & 3) == 0) copy_row<float4>(src, dst, dim >> 2, lane);
-  else if ((dim & 1) == 0) copy_row<float2>(src, dst, dim >> 1, lane);
-  else copy_row<float>(src, dst, dim, lane);
-}
-
 // Fused into every sample's graph: the rows of the last layer's in_nodes_g, part
 // after part -- the block of input features GPU g reads for this minibatch
 // (python/data/bipartite.py:61-67 gather, memory_manager.py:75-104 refresh).

@@ -171,3 +171,34 @@ def test_one_process_per_gpu_ipc():
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("owner,P,dim", [("mod", 4, 602), ("range", 3, 64)])
+def test_partitioned_fused_feature_gather(owner, P, dim):
+    """Config 4 in the partitioned layout: rank g holds only the feature rows of the
+    nodes it owns; in_nodes of its part are owned by it, so the fused gather is
+    local.  fp32 copy: equality is exact (tolerance 0)."""
+    from cslicer.partitioned import LocalGroup, owner_of, range_bounds
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=12)
+    n = ip.size - 1
+    b = range_bounds(n, P)
+    own = None if owner == "mod" else owner_of(np.arange(n), n, P, "range", b)
+    feat = np.random.default_rng(4321).random((n, dim), dtype=np.float32)
+    fan = [-1, 5]
+    grp = LocalGroup(ip, ix, P, fan, owner_mode=owner, bounds=b, max_batch=256, num_slots=2, seed=5,
+                     features=feat)
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=5, owner=own)
+    rng = np.random.default_rng(2)
+    for bi in range(3):
+        seeds = rng.permutation(n)[:256]
+        want = orc.slice(seeds, bi)
+        for g, v in enumerate(grp.slice(seeds, bi)):
+            _compare_rank(v, want, g)
+            rows = feat[want["layers"][-1][g]["in_nodes"]]
+            got = v.features(g).cpu().numpy()
+            assert got.shape == rows.shape and np.array_equal(got, rows)
+            assert v.feature_rows == rows.shape[0]
+            v.release()
+    grp.close()
