@@ -418,7 +418,7 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   PA(w.epoch, 2);
   CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
   CUS(cudaMemset(w.epoch, 0, 2 * sizeof(uint32_t)));
-  CUS(cudaMemset(w.rowrem, 0, (size_t)s->Fcap));
+  CUS(cudaMemset(w.rowrem, 0, (size_t)s->Fcap * sizeof(uint32_t)));
   s->slots.resize(cfg->num_slots);
   for (PSlot &sl : s->slots) {
     CUS(cudaMalloc((void **)&sl.hdr, sizeof(gs_sample_header)));

@@ -25,7 +25,7 @@
 #define PS_CF_IFIRST 0x08u
 #define PS_CF_EDGE 0x10u   // edge whose source this rank owns (cand = source id)
 
-#define PS_NCTR 8          // per-kernel counter arrays (max used: 5)
+#define PS_NCTR (5 + 2 * GS_MAX_PARTS)  // per-kernel counter arrays: 5 + per-peer from / to lists
 
 // What a peer may touch of a rank's memory: one cudaMalloc arena, exported
 // with cudaIpcGetMemHandle; identical layout on every rank.
@@ -59,7 +59,7 @@ struct PsWs {
   uint32_t *cnt[2];    // [Fcap] candidate count of every frontier row (replicated), ping-pong by layer
   uint32_t *off;       // [Fcap+1]
   uint32_t *rowscan;   // [Fcap+1] edges of MY part emitted before row i
-  uint8_t *rowrem;     // [Fcap] owned row sampled a source owned by another rank
+  uint32_t *rowrem;    // [Fcap] owned row: bit q = it sampled a source owned by rank q != this rank
   uint32_t *tile_first;// [ctiles+1]
   unsigned long long *ftile_sum; // [grid]
   uint32_t *ftile_pre; // [grid]

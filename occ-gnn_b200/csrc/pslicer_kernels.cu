@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(GS_TPB) pk_expand(PsWs ws, int layer) {
         pa.cand[pos[it]] = v[it];
         pa.cflag[pos[it]] = (uint8_t)PS_CF_EDGE;
         atomicMin(&pa.table[ps_local(ws, v[it], q)].x, pos[it]);
-        if (q != ws.rank) ws.rowrem[row[it]] = 1;
+        if (q != ws.rank && !(ws.rowrem[row[it]] & (1u << q))) atomicOr(&ws.rowrem[row[it]], 1u << q);
       }
     }
     __syncthreads();
@@ -528,15 +528,32 @@ __global__ void __launch_bounds__(GS_TPB) pk_cand_apply(PsWs ws, int layer) {
 // of all ranks -> F_{l+1}; (2) the row-side classes of B[layer][rank]
 // (bipartite.h:33-66): out = row has an edge in my part; owned = out and I own
 // the row; to = I own the row and it sampled a remote source; self = I own it.
+// Per-peer counters, 16 bits per rank in two 64-bit words (ranks 0-3 / 4-7): a
+// CTA-wide scan of one word ranks a round of GS_TPB rows for four peers at once.
+struct Pk16 {
+  unsigned long long w[2];
+};
+__device__ __forceinline__ void pk16_add(Pk16 &v, int q) { v.w[q >> 2] += 1ull << (16 * (q & 3)); }
+__device__ __forceinline__ uint32_t pk16_get(const Pk16 &v, int q) { return (uint32_t)(v.w[q >> 2] >> (16 * (q & 3))) & 0xFFFFu; }
+
+// Row classes of B[layer][rank] (bipartite.h:33-66).  fromq: the rank that owns the
+// row when this rank holds a partial aggregate for it (-1 otherwise); tomask: ranks
+// that hold partial aggregates for a row this rank owns.
 __device__ __forceinline__ void ps_row_class(const PsWs &ws, const int32_t *front, int i, int F,
-                                             bool &out, bool &own, bool &to, bool &self) {
+                                             bool &out, bool &own, bool &to, bool &self, int &fromq,
+                                             uint32_t &tomask) {
   out = own = to = self = false;
+  fromq = -1;
+  tomask = 0u;
   if (i < F) {
-    const bool mine = ps_owner(ws, front[i]) == ws.rank;
+    const int q0 = ps_owner(ws, front[i]);
+    const bool mine = q0 == ws.rank;
     out = ws.rowscan[i + 1] != ws.rowscan[i];
     own = out && mine;
     self = mine;
-    to = mine && ws.rowrem[i] != 0;
+    if (mine) tomask = ws.rowrem[i];
+    to = tomask != 0u;
+    if (out && !mine) fromq = q0;
   }
 }
 
@@ -561,12 +578,18 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_count(PsWs ws, int layer) {
     }
   cta_tiles((F + GS_TILE - 1) / GS_TILE, t0, t1);
   uint32_t n_out = 0u, n_own = 0u, n_to = 0u, n_self = 0u;
+  Pk16 pf = {{0ull, 0ull}}, pt = {{0ull, 0ull}};  // per-peer from / to rows
   for (int t = t0; t < t1; t++)
 #pragma unroll
     for (int it = 0; it < GS_IPT; it++) {
       bool o, w, to, sf;
-      ps_row_class(ws, front, t * GS_TILE + it * GS_TPB + threadIdx.x, F, o, w, to, sf);
+      int fq;
+      uint32_t tm;
+      ps_row_class(ws, front, t * GS_TILE + it * GS_TPB + threadIdx.x, F, o, w, to, sf, fq, tm);
       n_out += o; n_own += w; n_to += to; n_self += sf;
+      if (fq >= 0) pk16_add(pf, fq);
+      for (int q = 0; q < ws.P; q++)
+        if ((tm >> q) & 1u) pk16_add(pt, q);
     }
   const uint32_t v[5] = {nf, n_out, n_own, n_to, n_self};
 #pragma unroll
@@ -576,10 +599,23 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_count(PsWs ws, int layer) {
     for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
     if (lane_id() == 0 && x) atomicAdd(&s_cnt[c], x);
   }
+  for (int q = 0; q < ws.P; q++) {  // per-thread fields stay far below 2^16; sum them unpacked
+    uint32_t a = pk16_get(pf, q), b = pk16_get(pt, q);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      a += __shfl_xor_sync(FULL, a, d);
+      b += __shfl_xor_sync(FULL, b, d);
+    }
+    if (lane_id() == 0) {
+      if (a) atomicAdd(&s_cnt[5 + q], a);
+      if (b) atomicAdd(&s_cnt[5 + ws.P + q], b);
+    }
+  }
   __syncthreads();
-  if (threadIdx.x < 5) ws.ctr[(size_t)threadIdx.x * ws.grid_max + blockIdx.x] = s_cnt[threadIdx.x];
+  const int NCT = 5 + 2 * ws.P;
+  if (threadIdx.x < NCT) ws.ctr[(size_t)threadIdx.x * ws.grid_max + blockIdx.x] = s_cnt[threadIdx.x];
   if (!last_block(ws.tickets + 2)) return;
-  spine_scan<PS_NCTR>(ws.ctr, ws.grid_max, (int)gridDim.x, 5, s_tot, nullptr);
+  spine_scan<PS_NCTR>(ws.ctr, ws.grid_max, (int)gridDim.x, NCT, s_tot, nullptr);
   if (threadIdx.x == 0) {
     bool ok = true;
     const uint32_t fnext = s_tot[0];
@@ -596,6 +632,15 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_count(PsWs ws, int layer) {
     fl[GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, nt, ok);
     fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, ns, ok);
     fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, ns, ok);
+    // per-peer split, in the slots [q != rank] the reference leaves empty (bipartite.h:19-21):
+    // FROM_IDS[q] = my out positions of rows rank q owns; TO_IDS[q] = my out position (or -1)
+    // of rows I own that rank q holds a partial aggregate for.  Entry k of one pairs with
+    // entry k of the other on rank q.
+    for (int q = 0; q < ws.P; q++)
+      if (q != ws.rank) {
+        h->field[layer][q][GS_F_FROM_IDS] = slab_alloc(used, ws.slab_cap, s_tot[5 + q], ok);
+        h->field[layer][q][GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, s_tot[5 + ws.P + q], ok);
+      }
     if (ok) {
       ws.slab[ip.off + no] = (int32_t)ws.rowscan[F];
       h->slab_used = used;
@@ -647,16 +692,40 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_apply(PsWs ws, int layer) {
   cta_tiles((F + GS_TILE - 1) / GS_TILE, t0, t1);
   uint32_t b_out = ws.ctr[(size_t)1 * ws.grid_max + blockIdx.x], b_own = ws.ctr[(size_t)2 * ws.grid_max + blockIdx.x];
   uint32_t b_to = ws.ctr[(size_t)3 * ws.grid_max + blockIdx.x], b_self = ws.ctr[(size_t)4 * ws.grid_max + blockIdx.x];
+  __shared__ unsigned long long s_w64[GS_NW + 1];
+  __shared__ uint32_t s_bf[GS_MAX_PARTS], s_bt[GS_MAX_PARTS];  // running per-peer bases of this CTA
+  __shared__ int32_t s_fo[GS_MAX_PARTS], s_to[GS_MAX_PARTS];   // slab offsets of the per-peer lists
+  if (threadIdx.x < ws.P) {
+    const int q = threadIdx.x;
+    s_bf[q] = ws.ctr[(size_t)(5 + q) * ws.grid_max + blockIdx.x];
+    s_bt[q] = ws.ctr[(size_t)(5 + ws.P + q) * ws.grid_max + blockIdx.x];
+    s_fo[q] = h->field[layer][q][GS_F_FROM_IDS].off;
+    s_to[q] = h->field[layer][q][GS_F_TO_IDS].off;
+  }
+  __syncthreads();
   for (int t = t0; t < t1; t++)
     for (int it = 0; it < GS_IPT; it++) {
       const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
       bool o, w, to, sf;
-      ps_row_class(ws, front, i, F, o, w, to, sf);
+      int fq;
+      uint32_t tm;
+      ps_row_class(ws, front, i, F, o, w, to, sf, fq, tm);
       uint32_t t_out, t_own, t_to, t_self;
       const uint32_t op = b_out + block_excl_scan(o ? 1u : 0u, s_w, t_out);
       const uint32_t ow = b_own + block_excl_scan(w ? 1u : 0u, s_w, t_own);
       const uint32_t pt = b_to + block_excl_scan(to ? 1u : 0u, s_w, t_to);
       const uint32_t ps = b_self + block_excl_scan(sf ? 1u : 0u, s_w, t_self);
+      // per-peer ranks: 16-bit fields, four peers per CTA-wide scan
+      Pk16 vf = {{0ull, 0ull}}, vt = {{0ull, 0ull}}, ef, et, tf, tt;
+      if (fq >= 0) pk16_add(vf, fq);
+      for (int q = 0; q < ws.P; q++)
+        if ((tm >> q) & 1u) pk16_add(vt, q);
+      const int nwords = ws.P > 4 ? 2 : 1;
+      ef.w[1] = et.w[1] = tf.w[1] = tt.w[1] = 0ull;
+      for (int k = 0; k < nwords; k++) {
+        ef.w[k] = block_excl_scan64(vf.w[k], s_w64, tf.w[k]);
+        et.w[k] = block_excl_scan64(vt.w[k], s_w64, tt.w[k]);
+      }
       if (i < F) {
         const int32_t nd = front[i];
         if (o) {
@@ -666,6 +735,9 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_apply(PsWs ws, int layer) {
           else from[op - ow] = (int32_t)op;
         }
         const int32_t op_own = w ? (int32_t)op : -1;
+        if (fq >= 0) ws.slab[s_fo[fq] + s_bf[fq] + pk16_get(ef, fq)] = (int32_t)op;
+        for (int q = 0; q < ws.P; q++)
+          if ((tm >> q) & 1u) ws.slab[s_to[q] + s_bt[q] + pk16_get(et, q)] = op_own;
         if (to) to_ids[pt] = op_own;
         if (sf) {
           const uint32_t x = ws.me.table[ps_local(ws, nd, g)].x;
@@ -674,6 +746,12 @@ __global__ void __launch_bounds__(GS_TPB) pk_front_apply(PsWs ws, int layer) {
         }
       }
       b_out += t_out; b_own += t_own; b_to += t_to; b_self += t_self;
+      __syncthreads();  // everyone has read the per-peer bases of this round
+      if (threadIdx.x < ws.P) {
+        s_bf[threadIdx.x] += pk16_get(tf, threadIdx.x);
+        s_bt[threadIdx.x] += pk16_get(tt, threadIdx.x);
+      }
+      __syncthreads();
     }
 }
 

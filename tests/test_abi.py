@@ -36,14 +36,17 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_the_header(tmp_path):
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "gsplit_slicer.h"\n'
-                   'int main(){printf("%zu %zu %zu %zu %zu\\n", sizeof(gs_sample_header),'
+                   'int main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(gs_sample_header),'
                    'sizeof(gs_config), offsetof(gs_sample_header, field),'
-                   'offsetof(gs_config, max_batch), offsetof(gs_sample_header, draw_base));return 0;}')
+                   'offsetof(gs_config, max_batch), offsetof(gs_sample_header, draw_base),'
+                   'sizeof(gs_pconfig), offsetof(gs_pconfig, stream), offsetof(gs_pconfig, feature_rows_capacity));'
+                   'return 0;}')
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     assert got == [C.sizeof(N.SampleHeader), C.sizeof(N.Config), N.SampleHeader.field.offset,
-                   N.Config.max_batch.offset, N.SampleHeader.draw_base.offset]
+                   N.Config.max_batch.offset, N.SampleHeader.draw_base.offset,
+                   C.sizeof(N.PConfig), N.PConfig.stream.offset, N.PConfig.feature_rows_capacity.offset]
 
 
 def test_config_default_is_the_reference_configuration():

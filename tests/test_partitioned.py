@@ -37,9 +37,13 @@ def test_partition_csr_round_trip():
                 assert np.array_equal(lix[lip[li]:lip[li + 1]], ix[ip[v]:ip[v + 1]])
 
 
-def _compare_rank(view, orc, g, check_frontiers=True):
+def _compare_rank(view, orc, g, check_frontiers=True, owner=None):
+    """Rank g's sample against part g of the oracle's; the slots [q != g] of
+    from_ids / to_ids (empty in the reference, bipartite.h:19-21) carry the per-peer
+    split, whose expectation follows from the oracle's node lists: the rows rank q
+    owns that appear in out_nodes_g, in frontier order."""
     from cslicer import _native
-    L = view.num_layers
+    L, P = view.num_layers, view.num_parts
     if check_frontiers:
         for l in range(L + 1):
             a, b = view.frontier_numpy(l), orc["frontiers"][l]
@@ -49,9 +53,19 @@ def _compare_rank(view, orc, g, check_frontiers=True):
             a, b = view.numpy(l, g, name), orc["layers"][l][g][name]
             assert a.shape == b.shape and np.array_equal(a, b), \
                 f"rank {g} layer {l} field {name} differs: {a[:8]} vs {b[:8]} (len {a.size}/{b.size})"
-        for q in range(view.num_parts):
-            if q != g:
-                assert all(view.field_len(l, q, nm) == 0 for nm in _native.FIELDS)
+        fr = orc["frontiers"][l]
+        own = (fr % P) if owner is None else np.asarray(owner)[fr]
+        pos = [{int(v): i for i, v in enumerate(orc["layers"][l][q]["out_nodes"])} for q in range(P)]
+        for q in range(P):
+            if q == g:
+                continue
+            for nm in _native.FIELDS:
+                if nm not in ("from_ids", "to_ids"):
+                    assert view.field_len(l, q, nm) == 0
+            want_from = [pos[g][int(v)] for v, o in zip(fr, own) if o == q and int(v) in pos[g]]
+            want_to = [pos[g].get(int(v), -1) for v, o in zip(fr, own) if o == g and int(v) in pos[q]]
+            assert view.numpy(l, q, "from_ids").tolist() == want_from, (l, g, q, "from")
+            assert view.numpy(l, q, "to_ids").tolist() == want_to, (l, g, q, "to")
     assert view.edges == sum(orc["layers"][l][g]["csr_indices"].size for l in range(L))
 
 
@@ -88,7 +102,7 @@ def test_local_group_matches_oracle(fanouts, P, owner, batch, shape):
         views = grp.slice(seeds, bi)
         want = orc.slice(seeds, bi)
         for g, v in enumerate(views):
-            _compare_rank(v, want, g)
+            _compare_rank(v, want, g, owner=own)
             v.release()
     grp.close()
 
@@ -195,7 +209,7 @@ def test_partitioned_fused_feature_gather(owner, P, dim):
         seeds = rng.permutation(n)[:256]
         want = orc.slice(seeds, bi)
         for g, v in enumerate(grp.slice(seeds, bi)):
-            _compare_rank(v, want, g)
+            _compare_rank(v, want, g, owner=own)
             rows = feat[want["layers"][-1][g]["in_nodes"]]
             got = v.features(g).cpu().numpy()
             assert got.shape == rows.shape and np.array_equal(got, rows)
