@@ -237,6 +237,9 @@ typedef struct {
   int32_t feature_dim;
   int32_t reserved0;
   int64_t feature_rows_capacity;           /* 0 = derive */
+  int64_t shuffle_rows_capacity;           /* rows one rank may send to one peer per shuffle; 0 = no shuffle */
+  int32_t shuffle_max_dim;                 /* widest row a shuffle may carry */
+  int32_t reserved1;
 } gs_pconfig;
 
 void gs_pconfig_default(gs_pconfig *cfg);
@@ -276,6 +279,21 @@ int gs_pslicer_release(gs_pslicer *s, int32_t slot);
  * (python/data/bipartite.py:61-67, memory_manager.py:75-104). */
 int gs_pslicer_feature_slab(gs_pslicer *s, int32_t slot, const float **device_rows, int32_t *dim,
                             int32_t *rows);
+/* Split-parallel shuffle of one layer (replaces the 12 peer copies + mergeKernel per
+ * layer of src/gnn/dist_sage.cu:120-160,193-199 and pull_for_remotes / push_from_remotes
+ * of python/data/bipartite.py:88-99): rows_device is this rank's [len(out_nodes) x dim]
+ * fp32 block of partial aggregates of the slot's sample.
+ *   forward  (backward = 0): row FROM_IDS[q][k] goes to rank q, which adds it to its row
+ *                            TO_IDS[me][k] (skipped when -1), peers merged in rank order;
+ *   backward (backward = 1): the transpose -- row TO_IDS[q][k] of the owner (zeros when -1)
+ *                            overwrites row FROM_IDS[owner][k] of the contributor.
+ * The rows move by the kernel's own stores into the peers' staging arenas over NVLink.
+ * Collective over the ranks (same slot order on every rank), asynchronous on the slicer's
+ * stream; gs_pslicer_sync() waits for it.  phase -1 = whole shuffle; 0 / 1 / 2 = push +
+ * signal / wait + merge + signal / wait, for ranks that share one stream. */
+int gs_pslicer_shuffle(gs_pslicer *s, int32_t slot, int32_t layer, float *rows_device, int32_t dim,
+                       int32_t backward, int32_t phase);
+int gs_pslicer_sync(gs_pslicer *s);
 /* After any error: every rank calls this (all streams idle) before the next submit. */
 int gs_pslicer_reset(gs_pslicer *s);
 int gs_pslicer_launches_per_sample(const gs_pslicer *s);

@@ -32,7 +32,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
            "gs_pslicer_num_segments", "gs_pslicer_submit", "gs_pslicer_stage",
            "gs_pslicer_enqueue", "gs_pslicer_commit", "gs_pslicer_wait", "gs_pslicer_slab",
-           "gs_pslicer_release", "gs_pslicer_feature_slab", "gs_pslicer_reset", "gs_pslicer_launches_per_sample",
+           "gs_pslicer_release", "gs_pslicer_feature_slab", "gs_pslicer_shuffle", "gs_pslicer_sync", "gs_pslicer_reset", "gs_pslicer_launches_per_sample",
            "gs_pslicer_device_bytes"]
 
 
@@ -77,7 +77,8 @@ class PConfig(C.Structure):
                 ("slab_capacity", C.c_int64), ("num_edges_global", C.c_int64),
                 ("stream", C.c_void_p), ("features_local_host", C.c_void_p),
                 ("feature_dim", C.c_int32), ("reserved0", C.c_int32),
-                ("feature_rows_capacity", C.c_int64)]
+                ("feature_rows_capacity", C.c_int64), ("shuffle_rows_capacity", C.c_int64),
+                ("shuffle_max_dim", C.c_int32), ("reserved1", C.c_int32)]
 
 
 _lib = None
@@ -141,6 +142,9 @@ def lib():
     L.gs_pslicer_release.argtypes = [C.c_void_p, C.c_int32]
     L.gs_pslicer_feature_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                           C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.gs_pslicer_shuffle.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+                                     C.c_int32]
+    L.gs_pslicer_sync.argtypes = [C.c_void_p]
     L.gs_pslicer_reset.argtypes = [C.c_void_p]
     L.gs_pslicer_launches_per_sample.argtypes = [C.c_void_p]
     L.gs_pslicer_device_bytes.restype = C.c_int64

@@ -77,7 +77,8 @@ class PartitionedSlicer:
                  owner_mode="mod", bounds=None, device=0, max_batch=4096, num_slots=2, seed=0,
                  host_output=True, use_graph=True, stream=None, num_edges_global=0,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0,
-                 timeout_ms=5000, features_local=None, feature_rows_capacity=0):
+                 timeout_ms=5000, features_local=None, feature_rows_capacity=0,
+                 shuffle_rows_capacity=0, shuffle_max_dim=0):
         L = N.lib()
         ip = np.ascontiguousarray(indptr_local, dtype=np.int64)
         ix = np.ascontiguousarray(indices_local, dtype=np.int64)
@@ -106,6 +107,7 @@ class PartitionedSlicer:
                 raise ValueError("features_local must be [n_local, dim]")
             cfg.features_local_host, cfg.feature_dim = feat.ctypes.data, int(feat.shape[1])
             cfg.feature_rows_capacity = int(feature_rows_capacity)
+        cfg.shuffle_rows_capacity, cfg.shuffle_max_dim = int(shuffle_rows_capacity), int(shuffle_max_dim)
         h = C.c_void_p()
         N.check(L.gs_pslicer_create(int(device), int(num_nodes), ip.size - 1, ix.size,
                                     ip.ctypes.data, ix.ctypes.data, C.byref(cfg), C.byref(h)))
@@ -180,6 +182,25 @@ class PartitionedSlicer:
 
     def slice(self, seeds, batch_index=0):
         return self.wait(self.submit(seeds, batch_index))
+
+    def shuffle(self, view, layer, rows, backward=False, phase=-1):
+        """Split-parallel shuffle of `rows` ([len(out_nodes), dim] fp32 CUDA tensor, the
+        partial aggregates of layer `layer` of `view`), in place: forward adds the
+        peers' partial rows into the rows this rank owns, backward hands the owners'
+        rows back to the contributors.  Collective: every rank calls it for the same
+        minibatch, in the same order.  Blocks until done when phase == -1."""
+        import torch
+        assert rows.is_cuda and rows.dtype == torch.float32 and rows.is_contiguous() and rows.dim() == 2
+        if phase in (-1, 0):
+            torch.cuda.current_stream(rows.device).synchronize()  # rows were produced on torch's stream
+        N.check(N.lib().gs_pslicer_shuffle(self._h, view.slot, int(layer), rows.data_ptr(),
+                                           int(rows.shape[1]), int(bool(backward)), int(phase)))
+        if phase in (-1, 2):
+            self.sync()
+        return rows
+
+    def sync(self):
+        N.check(N.lib().gs_pslicer_sync(self._h))
 
     def reset(self):
         N.check(N.lib().gs_pslicer_reset(self._h))
@@ -296,6 +317,13 @@ class LocalGroup:
     def slice(self, seeds, batch_index=0):
         """-> [SampleView of rank 0, ..., rank P-1]"""
         return self.wait(self.submit(seeds, batch_index))
+
+    def shuffle(self, views, layer, rows, backward=False):
+        """rows[g]: rank g's [len(out_nodes_g), dim] tensor; all ranks, phase by phase."""
+        for phase in (0, 1, 2):
+            for r, v, x in zip(self.ranks, views, rows):
+                r.shuffle(v, layer, x, backward, phase)
+        return rows
 
     def close(self):
         for r in self.ranks:

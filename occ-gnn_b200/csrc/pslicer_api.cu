@@ -50,7 +50,8 @@ struct PSlot {
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 // Peer-visible arena: one allocation, same layout on every rank.
-size_t arena_layout(char *base, int64_t table_cap, int64_t Ccap, int64_t max_batch, PsArena *a) {
+size_t arena_layout(char *base, int64_t table_cap, int64_t Ccap, int64_t max_batch, int64_t stage_floats,
+                    PsArena *a) {
   size_t o = 0;
   auto take = [&](size_t bytes) {
     char *p = base ? base + o : nullptr;
@@ -63,6 +64,7 @@ size_t arena_layout(char *base, int64_t table_cap, int64_t Ccap, int64_t max_bat
   a->nf = (uint2 *)take((size_t)Ccap * sizeof(uint2));
   a->cnt0 = (uint32_t *)take((size_t)max_batch * sizeof(uint32_t));
   a->rowrem = nullptr;
+  a->stage = (float *)take((size_t)stage_floats * sizeof(float));
   a->flags = (uint32_t *)take(GS_MAX_PARTS * sizeof(uint32_t));
   a->err = (int32_t *)take(sizeof(int32_t));
   return o;
@@ -78,6 +80,7 @@ struct gs_pslicer {
   int64_t *indptr = nullptr;
   int32_t *indices = nullptr;
   float *feat = nullptr;  // [n_local][feat_dim]
+  int64_t stage_floats = 0;
   int64_t feat_cap_rows = 0;
   char *arena = nullptr;
   size_t arena_bytes = 0;
@@ -349,11 +352,17 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
     cudaFree(tmp);
   }
   // arena
+  if (cfg->shuffle_rows_capacity < 0 || cfg->shuffle_max_dim < 0) {
+    gs_pslicer_destroy(s);
+    return pfail(GS_ERR_INVALID, "negative shuffle capacity");
+  }
+  const int64_t stage_dim = ((int64_t)cfg->shuffle_max_dim + 3) & ~3ll;  // 16-byte aligned peer blocks and rows
+  s->stage_floats = (int64_t)P * cfg->shuffle_rows_capacity * stage_dim;
   PsArena dummy;
-  s->arena_bytes = arena_layout(nullptr, table_cap, s->Ccap, cfg->max_batch, &dummy);
+  s->arena_bytes = arena_layout(nullptr, table_cap, s->Ccap, cfg->max_batch, s->stage_floats, &dummy);
   CUS(cudaMalloc((void **)&s->arena, s->arena_bytes));
   s->bytes += (int64_t)s->arena_bytes;
-  arena_layout(s->arena, table_cap, s->Ccap, cfg->max_batch, &s->me);
+  arena_layout(s->arena, table_cap, s->Ccap, cfg->max_batch, s->stage_floats, &s->me);
   CUS(cudaMemset(s->arena, 0, s->arena_bytes));
   CUS(cudaMemset(s->me.table, 0xFF, (size_t)table_cap * sizeof(uint2)));
   s->peer[cfg->rank] = s->me;
@@ -399,6 +408,8 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   w.grid_max = s->grid;
   w.timeout_ms = s->cfg.timeout_ms;
   w.slab_cap = s->slab_cap;
+  w.stage_rows = cfg->shuffle_rows_capacity;
+  w.stage_dim = (int32_t)(((int64_t)cfg->shuffle_max_dim + 3) & ~3ll);
   w.feat = s->feat;
   w.feat_dim = cfg->feature_dim;
   w.feat_cap_rows = s->feat_cap_rows;
@@ -465,7 +476,7 @@ int gs_pslicer_connect_ipc(gs_pslicer *s, int32_t q, const void *handle64) {
   void *base = nullptr;
   CU(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
   s->ipc_base[q] = base;
-  arena_layout((char *)base, s->table_cap, s->Ccap, s->cfg.max_batch, &s->peer[q]);
+  arena_layout((char *)base, s->table_cap, s->Ccap, s->cfg.max_batch, s->stage_floats, &s->peer[q]);
   s->connected[q] = true;
   return GS_OK;
 }
@@ -475,7 +486,8 @@ int gs_pslicer_connect_local(gs_pslicer *s, int32_t q, gs_pslicer *peer) {
   if (q < 0 || q >= s->cfg.num_parts || q == s->cfg.rank) return pfail(GS_ERR_INVALID, "bad peer rank %d", q);
   if (s->ready) return pfail(GS_ERR_STATE, "already frozen by gs_pslicer_ready()");
   if (peer->cfg.rank != q || peer->cfg.num_parts != s->cfg.num_parts || peer->Ccap != s->Ccap ||
-      peer->table_cap != s->table_cap || peer->cfg.max_batch != s->cfg.max_batch)
+      peer->table_cap != s->table_cap || peer->cfg.max_batch != s->cfg.max_batch ||
+      peer->stage_floats != s->stage_floats)
     return pfail(GS_ERR_INVALID, "peer %d was created with a different configuration", q);
   if (peer->device != s->device) {
     CU(cudaSetDevice(s->device));
@@ -625,6 +637,47 @@ int gs_pslicer_release(gs_pslicer *s, int32_t slot) {
     CU(cudaEventSynchronize(sl.done));
   }
   sl.state = PSLOT_FREE;
+  return GS_OK;
+}
+
+int gs_pslicer_shuffle(gs_pslicer *s, int32_t slot, int32_t layer, float *rows, int32_t dim,
+                       int32_t backward, int32_t phase) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return pfail(GS_ERR_INVALID, "bad slot");
+  PSlot &sl = s->slots[slot];
+  if (sl.state != PSLOT_DONE) return pfail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (layer < 0 || layer >= s->cfg.num_layers) return pfail(GS_ERR_INVALID, "bad layer");
+  if (!rows || dim < 1 || dim > s->cfg.shuffle_max_dim)
+    return pfail(GS_ERR_INVALID, "rows NULL or dim %d outside [1, shuffle_max_dim=%d]", dim,
+                 s->cfg.shuffle_max_dim);
+  if (phase < -1 || phase > 2) return pfail(GS_ERR_INVALID, "phase must be -1, 0, 1 or 2");
+  const gs_sample_header *h = sl.hdr_host;
+  for (int q = 0; q < s->cfg.num_parts; q++)
+    if (q != s->cfg.rank && (h->field[layer][q][GS_F_FROM_IDS].len > s->cfg.shuffle_rows_capacity ||
+                             h->field[layer][q][GS_F_TO_IDS].len > s->cfg.shuffle_rows_capacity))
+      return pfail(GS_ERR_OVERFLOW, "shuffle of layer %d needs more than shuffle_rows_capacity=%lld rows per peer",
+                   layer, (long long)s->cfg.shuffle_rows_capacity);
+  CU(cudaSetDevice(s->device));
+  const PsWs &ws = sl.ws;
+  cudaStream_t st = s->stream;
+  if (phase == -1 || phase == 0) {
+    ps_launch_shuffle_push(ws, layer, rows, dim, backward, s->grid, st);
+    ps_launch_signal(ws, st);
+  }
+  if (phase == -1 || phase == 1) {
+    ps_launch_wait(ws, st);
+    for (int q = 0; q < s->cfg.num_parts; q++)
+      if (q != s->cfg.rank) ps_launch_shuffle_merge(ws, layer, rows, dim, backward, q, s->grid, st);
+    ps_launch_signal(ws, st);  // peers may reuse my staging arena only after I merged
+  }
+  if (phase == -1 || phase == 2) ps_launch_wait(ws, st);
+  CU(cudaGetLastError());
+  return GS_OK;
+}
+
+int gs_pslicer_sync(gs_pslicer *s) {
+  if (!s) return pfail(GS_ERR_INVALID, "NULL argument");
+  CU(cudaSetDevice(s->device));
+  CU(cudaStreamSynchronize(s->stream));
   return GS_OK;
 }
 

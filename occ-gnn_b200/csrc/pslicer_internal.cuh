@@ -36,6 +36,7 @@ struct PsArena {
   uint2 *nf;         // [Ccap] new frontier node at position p: {id, candidates it will own next layer}; y == 0: none
   uint32_t *cnt0;    // [max_batch] candidate counts of the seeds
   uint8_t *rowrem;   // unused by peers (kept here so the arena is one allocation)
+  float *stage;      // [P][shuffle_rows][shuffle_dim] rows received from every peer in a shuffle
   uint32_t *flags;   // [GS_MAX_PARTS] barrier: flags[q] = last epoch rank q signalled
   int32_t *err;      // [1] status raised by any peer
 };
@@ -67,6 +68,8 @@ struct PsWs {
   uint32_t *tickets;   // [8]
   uint32_t *epoch;     // [2] barriers executed so far; [1] != 0: a barrier timed out (group broken until reset)
   int32_t Fcap, Ccap, grid_max, timeout_ms;
+  int64_t stage_rows;  // shuffle capacity: rows per peer
+  int32_t stage_dim;
   const float *feat;   // [n_local][feat_dim] rows of the owned nodes (optional)
   int32_t feat_dim;
   int64_t feat_cap_rows;
@@ -93,4 +96,6 @@ void ps_launch_front_count(const PsWs &ws, int layer, int grid, cudaStream_t st)
 void ps_launch_front_apply(const PsWs &ws, int layer, int grid, cudaStream_t st);
 void ps_launch_relabel(const PsWs &ws, int layer, int grid, cudaStream_t st);
 void ps_launch_gather(const PsWs &ws, int grid, cudaStream_t st);
+void ps_launch_shuffle_push(const PsWs &ws, int layer, float *rows, int dim, int backward, int grid, cudaStream_t st);
+void ps_launch_shuffle_merge(const PsWs &ws, int layer, float *rows, int dim, int backward, int peer, int grid, cudaStream_t st);
 void ps_launch_finish(const PsWs &ws, int grid, cudaStream_t st);

@@ -802,6 +802,59 @@ __global__ void __launch_bounds__(GS_TPB) pk_gather(PsWs ws) {
     gather_row(ws.feat, ws.feat_dim, (int64_t)ps_local(ws, ids[r], ws.rank), ws.feat_out, r, lane);
 }
 
+// ---------------------------------------------------------------- pk_shuffle
+// Split-parallel shuffle of one layer's partial aggregates (dist_sage.cu:120-160,
+// 193-199; bipartite.py:88-99).  push: one warp per row, straight into the
+// owner's staging arena over NVLink (slot [sender][k]).  merge: after the
+// barrier, the receiver folds one peer's rows in; the host launches the peers in
+// rank order, and inside a peer every destination row is distinct, so the sums
+// are deterministic.  backward is the transpose with copy instead of add.
+__global__ void __launch_bounds__(GS_TPB) pk_shuffle_push(PsWs ws, int layer, const float *rows, int dim,
+                                                          int backward) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  const int lane = lane_id();
+  const int gw = blockIdx.x * GS_NW + warp_id(), nw = gridDim.x * GS_NW;
+  for (int q = 0; q < ws.P; q++) {
+    if (q == ws.rank) continue;
+    const gs_span sp = h->field[layer][q][backward ? GS_F_TO_IDS : GS_F_FROM_IDS];
+    const int32_t *list = ws.slab + sp.off;
+    float *dst = ws.peer[q].stage + (size_t)ws.rank * ws.stage_rows * ws.stage_dim;
+    for (int k = gw; k < sp.len; k += nw) {
+      const int32_t r = list[k];
+      float *d = dst + (size_t)k * dim;
+      if (r >= 0) {
+        gather_row(rows, dim, (int64_t)r, d, 0, lane);
+      } else {  // backward: the owner has no row for this node (reference semantics: -1)
+        for (int c = lane; c < dim; c += 32) d[c] = 0.0f;
+      }
+    }
+  }
+  __threadfence_system();
+}
+
+__global__ void __launch_bounds__(GS_TPB) pk_shuffle_merge(PsWs ws, int layer, float *rows, int dim,
+                                                           int backward, int q) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  const int lane = lane_id();
+  const int gw = blockIdx.x * GS_NW + warp_id(), nw = gridDim.x * GS_NW;
+  const gs_span sp = h->field[layer][q][backward ? GS_F_FROM_IDS : GS_F_TO_IDS];
+  const int32_t *list = ws.slab + sp.off;
+  const float *src = ws.me.stage + (size_t)q * ws.stage_rows * ws.stage_dim;
+  for (int k = gw; k < sp.len; k += nw) {
+    const int32_t r = list[k];
+    if (r < 0) continue;
+    const float *sr = src + (size_t)k * dim;
+    float *d = rows + (size_t)r * dim;
+    if (backward) {
+      for (int c = lane; c < dim; c += 32) d[c] = __ldcg(sr + c);
+    } else {
+      for (int c = lane; c < dim; c += 32) d[c] += __ldcg(sr + c);
+    }
+  }
+}
+
 // ----------------------------------------------------------------- pk_finish
 // Sparse reset of this rank's table (every node touched is in the last
 // frontier; this rank resets the ones it owns), header and slab -> pinned host.
@@ -860,4 +913,12 @@ void ps_launch_relabel(const PsWs &ws, int layer, int grid, cudaStream_t st) {
   pk_relabel<<<grid, GS_TPB, 0, st>>>(ws, layer);
 }
 void ps_launch_gather(const PsWs &ws, int grid, cudaStream_t st) { pk_gather<<<grid, GS_TPB, 0, st>>>(ws); }
+void ps_launch_shuffle_push(const PsWs &ws, int layer, float *rows, int dim, int backward, int grid,
+                            cudaStream_t st) {
+  pk_shuffle_push<<<grid, GS_TPB, 0, st>>>(ws, layer, rows, dim, backward);
+}
+void ps_launch_shuffle_merge(const PsWs &ws, int layer, float *rows, int dim, int backward, int peer,
+                             int grid, cudaStream_t st) {
+  pk_shuffle_merge<<<grid, GS_TPB, 0, st>>>(ws, layer, rows, dim, backward, peer);
+}
 void ps_launch_finish(const PsWs &ws, int grid, cudaStream_t st) { pk_finish<<<grid, GS_TPB, 0, st>>>(ws); }

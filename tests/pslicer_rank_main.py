@@ -19,7 +19,7 @@ def main():
                                      partition_csr)
     from cslicer.synth import synth_graph
     from oracle import oracle as O
-    from test_partitioned import _compare_rank
+    from test_partitioned import _compare_rank, _shuffle_reference
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
@@ -29,7 +29,8 @@ def main():
     fan = [15, 10, 5]
     lip, lix = partition_csr(ip, ix, world)[rank]
     ps = PartitionedSlicer(lip, lix, n, rank, world, fan, device=local, max_batch=512, num_slots=2,
-                           seed=77, num_edges_global=ix.size)
+                           seed=77, num_edges_global=ix.size, shuffle_rows_capacity=1 << 16,
+                           shuffle_max_dim=32)
     connect_process_group(ps, dist)
     orc = O.OracleSlicer(ip, ix, fan, world, O.RNG_PHILOX, seed=77)
     rng = np.random.default_rng(8)
@@ -38,6 +39,19 @@ def main():
         v = ps.slice(seeds, bi)
         _compare_rank(v, orc.slice(seeds, bi), rank)
         v.release()
+    # split-parallel shuffle over NVLink: every rank can restate all ranks' rows from the seed
+    seeds = rng.permutation(n)[:512]
+    v = ps.slice(seeds, 50)
+    want = orc.slice(seeds, 50)
+    for l in range(len(fan)):
+        for backward in (False, True):
+            parts = [np.random.default_rng(1000 + 10 * l + g).random(
+                (want["layers"][l][g]["out_nodes"].size, 32), dtype=np.float32) for g in range(world)]
+            rows = torch.from_numpy(parts[rank]).cuda()
+            ps.shuffle(v, l, rows, backward)
+            ref = _shuffle_reference(want, l, world, lambda x: x % world, parts, backward)
+            assert np.array_equal(rows.cpu().numpy(), ref[rank]), (l, backward)
+    v.release()
     dist.barrier()
     ps.close()
     # several minibatches in flight per rank: independent lanes, barriers overlap

@@ -216,3 +216,58 @@ def test_partitioned_fused_feature_gather(owner, P, dim):
             assert v.feature_rows == rows.shape[0]
             v.release()
     grp.close()
+
+
+def _shuffle_reference(want, l, P, own_of, parts, backward):
+    """numpy statement of the shuffle on the oracle's lists: node nd owned by q with
+    a partial row on g != q (nd in out_nodes_g).  forward: owner row += partial rows
+    in rank order (when the owner has a row at all); backward: contributor row =
+    owner row, or zeros."""
+    pos = [{int(v): i for i, v in enumerate(want["layers"][l][q]["out_nodes"])} for q in range(P)]
+    out = [x.copy() for x in parts]
+    for q in range(P):          # owner
+        for g in range(P):      # contributor, rank order
+            if g == q:
+                continue
+            for nd in want["frontiers"][l]:
+                nd = int(nd)
+                if own_of(nd) != q or nd not in pos[g]:
+                    continue
+                if not backward:
+                    if nd in pos[q]:
+                        out[q][pos[q][nd]] = out[q][pos[q][nd]] + parts[g][pos[g][nd]]
+                else:
+                    out[g][pos[g][nd]] = parts[q][pos[q][nd]] if nd in pos[q] else 0.0
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,dim", [(4, 64), (3, 50)])
+def test_split_parallel_shuffle_forward_and_backward(P, dim):
+    """Consumer of from_ids/to_ids: partial aggregates of the rows a
+    rank does not own travel to the owner and are summed there in rank order; the
+    backward pass is the transpose.  fp32 adds in a fixed order: tolerance 0."""
+    import torch
+    from cslicer.partitioned import LocalGroup
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=31)
+    n = ip.size - 1
+    fan = [5, 5]
+    grp = LocalGroup(ip, ix, P, fan, max_batch=200, num_slots=2, seed=3, shuffle_rows_capacity=4096,
+                     shuffle_max_dim=dim)
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=3)
+    seeds = np.random.default_rng(5).permutation(n)[:200]
+    views = grp.slice(seeds, 0)
+    want = orc.slice(seeds, 0)
+    rng = np.random.default_rng(9)
+    for l in range(2):
+        for backward in (False, True):
+            parts = [rng.random((views[g].field_len(l, g, "out_nodes"), dim), dtype=np.float32) for g in range(P)]
+            rows = [torch.from_numpy(x).cuda() for x in parts]
+            grp.shuffle(views, l, rows, backward)
+            ref = _shuffle_reference(want, l, P, lambda v: v % P, parts, backward)
+            for g in range(P):
+                assert np.array_equal(rows[g].cpu().numpy(), ref[g]), (l, backward, g)
+    for v in views:
+        v.release()
+    grp.close()
