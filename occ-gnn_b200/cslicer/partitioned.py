@@ -213,6 +213,18 @@ class PartitionedSlicer:
     __del__ = close
 
 
+def exchange_handles(dist, handle):
+    """All-gather one 64-byte handle per rank through torch.distributed (any backend,
+    gloo included: no GPU involved) -> list indexed by rank."""
+    if len(handle) != 64:
+        raise ValueError("a CUDA IPC memory handle is 64 bytes")
+    out = [None] * dist.get_world_size()
+    dist.all_gather_object(out, bytes(handle))
+    if any(h is None or len(h) != 64 for h in out):
+        raise RuntimeError("handle exchange failed")
+    return out
+
+
 def connect_process_group(ps, dist):
     """One process per GPU: all-gather the ranks' 64-byte CUDA IPC handles over
     torch.distributed (any backend), map every peer arena, freeze.  Collective:
@@ -220,8 +232,7 @@ def connect_process_group(ps, dist):
     world, rank = dist.get_world_size(), dist.get_rank()
     if world != ps.num_parts or rank != ps.rank:
         raise ValueError("process group does not match the slicer's (rank, num_parts)")
-    handles = [None] * world
-    dist.all_gather_object(handles, ps.ipc_handle())
+    handles = exchange_handles(dist, ps.ipc_handle())
     for q in range(world):
         if q != rank:
             ps.connect_ipc(q, handles[q])

@@ -64,3 +64,43 @@ def test_rank_batch_ids_shapes():
     assert rank_batch_ids(2, 3, 4).tolist() == []
     got = np.sort(np.concatenate([rank_batch_ids(37, r, 8) for r in range(8)]))
     assert got.tolist() == list(range(37))
+
+
+def _pworker(rank, world, port, out):
+    """Partitioned mode, host side only (no GPU): every rank shards the same CSR,
+    keeps its own part, and the ranks exchange their 64-byte arena handles."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from cslicer.partitioned import exchange_handles, owner_of, partition_csr
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    n = ip.size - 1
+    lip, lix = partition_csr(ip, ix, world)[rank]
+    handle = bytes([rank]) * 64                      # stands in for cudaIpcMemHandle_t
+    got = exchange_handles(dist, handle)
+    ok = got == [bytes([r]) * 64 for r in range(world)]
+    # shard sizes add up to the graph and rows keep their neighbour lists
+    sizes = torch.tensor([lip.size - 1, lix.size], dtype=torch.int64)
+    dist.all_reduce(sizes)
+    mine = np.flatnonzero(owner_of(np.arange(n), n, world) == rank)
+    rows_ok = all(np.array_equal(lix[lip[k]:lip[k + 1]], ix[ip[v]:ip[v + 1]]) for k, v in enumerate(mine))
+    if rank == 0:
+        out.put((ok, rows_ok, sizes.tolist(), n, int(ix.size)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_shard_the_graph_and_exchange_handles():
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pworker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    ok, rows_ok, sizes, n, m = out.get()
+    assert ok and rows_ok and sizes == [n, m]
