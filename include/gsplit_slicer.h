@@ -85,7 +85,8 @@ typedef struct {
   int32_t late_status;   /* device-internal: error raised inside a tiled kernel */
   int32_t feature_rows;  /* rows written by the fused feature gather (0 without features) */
   int32_t feature_part_off[GS_MAX_PARTS + 1]; /* row offset of each part's block in the feature slab */
-  int32_t reserved[3];
+  int32_t reserved[3];   /* [0] host mirror wanted, [1] frontier slab elements in use, [2] 1: `frontier`
+                          * spans index the frontier slab (gs_slicer_frontiers), 0: the sample slab */
 } gs_sample_header;
 
 typedef struct gs_graph gs_graph;
@@ -172,6 +173,12 @@ int gs_slicer_wait(gs_slicer *s, int32_t slot, const gs_sample_header **hdr_out)
  * host_slab is NULL unless host_output was set. */
 int gs_slicer_slab(gs_slicer *s, int32_t slot, const int32_t **device_slab,
                    const int32_t **host_slab);
+
+/* Frontiers 0..L of a completed slot (gs_sample_header.frontier spans index this
+ * device array).  They are by-products, not part of a reference Sample, so they are
+ * not mirrored to the host; gs_slicer_read_frontier copies one out on demand. */
+int gs_slicer_frontiers(gs_slicer *s, int32_t slot, const int32_t **device_frontiers);
+int gs_slicer_read_frontier(gs_slicer *s, int32_t slot, int32_t layer, int32_t *host_out);
 
 /* Replaces PySample's destructor (pybipartite.cpp:68-76). */
 int gs_slicer_release(gs_slicer *s, int32_t slot);

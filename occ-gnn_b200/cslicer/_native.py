@@ -27,6 +27,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_reference_shuffle", "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_slicer_feature_slab",
+           "gs_slicer_frontiers", "gs_slicer_read_frontier",
            # partitioned mode (one rank per GPU)
            "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
            "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
@@ -111,6 +112,8 @@ def lib():
     L.gs_slicer_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                  C.POINTER(C.c_void_p)]
     L.gs_slicer_release.argtypes = [C.c_void_p, C.c_int32]
+    L.gs_slicer_frontiers.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]
+    L.gs_slicer_read_frontier.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     L.gs_slicer_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64,
                                     C.POINTER(C.c_float), C.POINTER(C.c_char_p), C.c_int32,
                                     C.POINTER(C.c_int32)]

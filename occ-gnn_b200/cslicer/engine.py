@@ -96,6 +96,9 @@ class SampleView:
         self.feature_part_off = [int(hdr.feature_part_off[g]) for g in range(P + 1)]
         self._host = None
         self._released = False
+        self._frontier_on_device = bool(hdr.reserved[2])
+        self._fcache = {}
+        self._fdev_ptr = slicer._frontier_base(slot) if self._frontier_on_device else dev_ptr
         if host_ptr:
             n = max(self.slab_used, 1)
             self._host = np.ctypeslib.as_array(
@@ -112,26 +115,37 @@ class SampleView:
         return self._host[off:off + ln]
 
     def frontier_numpy(self, l):
+        """Frontier l as a host array.  Frontiers are by-products (not part of a
+        reference Sample): the single-GPU slicer keeps them on the device only and
+        this copies one out on demand."""
+        off, ln = self._frontier[l]
+        if self._frontier_on_device:
+            if l not in self._fcache:
+                if self._released:
+                    raise RuntimeError("sample slot already released")
+                out = np.empty(ln, dtype=np.int32)
+                N.check(N.lib().gs_slicer_read_frontier(self._slicer._h, self.slot, int(l), out.ctypes.data))
+                self._fcache[l] = out
+            return self._fcache[l]
         if self._host is None:
             raise RuntimeError("slicer was created with host_output=0: use .frontier_tensor()")
-        off, ln = self._frontier[l]
         return self._host[off:off + ln]
 
     # ---- device views (torch is plumbing here: it only wraps the pointer)
-    def _dev(self, off, ln):
+    def _dev(self, off, ln, base=None):
         import torch
         if self._released:
             raise RuntimeError("sample slot already released")
         if ln == 0:
             return torch.empty(0, dtype=torch.int32, device=f"cuda:{self._slicer.graph.device}")
-        return torch.as_tensor(_DevSpan(self._dev_ptr + 4 * off, ln, self),
+        return torch.as_tensor(_DevSpan((self._dev_ptr if base is None else base) + 4 * off, ln, self),
                                device=f"cuda:{self._slicer.graph.device}")
 
     def tensor(self, l, g, name):
         return self._dev(*self._span(l, g, name))
 
     def frontier_tensor(self, l):
-        return self._dev(*self._frontier[l])
+        return self._dev(*self._frontier[l], base=self._fdev_ptr)
 
     def features(self, g):
         """Fused gather result for part g: rows of the last layer's in_nodes_g,
@@ -162,6 +176,9 @@ class SampleView:
         if not self._released:
             if self._host is not None:
                 self._host = self._host.copy()
+            if self._frontier_on_device:
+                for l in range(self.num_layers + 1):
+                    self.frontier_numpy(l)
             self.release()
 
     def release(self):
@@ -268,6 +285,11 @@ class Slicer:
         ptr, dim = C.c_void_p(), C.c_int32()
         N.check(N.lib().gs_slicer_feature_slab(self._h, slot, C.byref(ptr), C.byref(dim)))
         return ptr.value, dim.value
+
+    def _frontier_base(self, slot):
+        ptr = C.c_void_p()
+        N.check(N.lib().gs_slicer_frontiers(self._h, slot, C.byref(ptr)))
+        return ptr.value or 0
 
     release = _release
 

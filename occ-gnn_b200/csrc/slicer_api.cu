@@ -82,7 +82,7 @@ struct gs_slicer {
   int grid_full = 0;                  // 8 CTAs per SM: full occupancy for the streaming gather
   int grid_rows[GS_MAX_LAYERS] = {0};  // per layer: enough CTAs for the largest possible frontier
   int grid_cand[GS_MAX_LAYERS] = {0};  // ... and candidate stream (static upper bounds)
-  int64_t Fcap = 0, Ccap = 0, slab_cap = 0;
+  int64_t Fcap = 0, Ccap = 0, slab_cap = 0, fslab_cap = 0;
   uint8_t *owner = nullptr;
   uint32_t *draws = nullptr;
   uint64_t *draw_cursor = nullptr;
@@ -166,8 +166,8 @@ int stage_input(gs_slicer *s, Slot &sl, const int64_t *seeds, int32_t n, uint64_
 }
 
 void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap, int64_t *Ccap,
-                        int64_t *slab, int64_t *Fb, int64_t *Cb) {
-  int64_t F = c.max_batch, fmax = F, cmax = 0, sl = F + 8;
+                        int64_t *slab, int64_t *fslab, int64_t *Fb, int64_t *Cb) {
+  int64_t F = c.max_batch, fmax = F, cmax = 0, sl = 8, fs = F + 8;
   const int64_t P = c.num_parts;
   for (int l = 0; l < c.num_layers; l++) {
     F = std::min(F, N);
@@ -178,13 +178,14 @@ void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap,
     cmax = std::max(cmax, C);
     Fb[l] = F;
     Cb[l] = C;
-    sl += std::min(N, C) + std::min(N, E) + E + 3 * std::min(P * F, E) + P + 4 * F +
-          4 * GS_NUM_FIELDS * P + 8;
+    sl += std::min(N, E) + E + 3 * std::min(P * F, E) + P + 4 * F + 4 * GS_NUM_FIELDS * P + 8;
+    fs += std::min(N, C) + 8;
     F = std::min(N, C);
   }
   *Fcap = c.frontier_capacity > 0 ? c.frontier_capacity : fmax;
   *Ccap = c.cand_capacity > 0 ? c.cand_capacity : cmax;
   *slab = c.slab_capacity > 0 ? c.slab_capacity : sl;
+  *fslab = fs;
 }
 
 }  // namespace
@@ -315,7 +316,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   s->cfg.features = nullptr;
   const int64_t N = g->num_nodes, M = g->num_edges;
   int64_t Fb[GS_MAX_LAYERS] = {0}, Cb[GS_MAX_LAYERS] = {0};
-  compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap, Fb, Cb);
+  compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap, &s->fslab_cap, Fb, Cb);
   if (s->Ccap >= (1ll << 31) - 2 * GS_TILE || s->Fcap >= (1ll << 31) - 2 * GS_TILE ||
       s->slab_cap >= (1ll << 31) - 16) {
     delete s;
@@ -413,6 +414,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.n_draws = cfg->n_draws;
     w.draw_cursor = s->draw_cursor;
     w.slab_cap = s->slab_cap;
+    w.fslab_cap = s->fslab_cap;
     w.Fcap = (int32_t)s->Fcap;
     w.Ccap = (int32_t)s->Ccap;
     w.ftiles_max = ftiles;
@@ -429,6 +431,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.hdr, 1);
     DA(w.table, N);
     DA(w.slab, s->slab_cap + 4);
+    DA(w.fslab, s->fslab_cap + 4);
     DA(w.rowstart, s->Fcap);
     DA(w.rowdeg, s->Fcap);
     DA(w.off, s->Fcap + 1);
@@ -574,6 +577,27 @@ int gs_slicer_slab(gs_slicer *s, int32_t slot, const int32_t **device_slab,
   if (sl.state != SLOT_DONE) return fail(GS_ERR_STATE, "slot %d not waited on", slot);
   if (device_slab) *device_slab = sl.ws.slab;
   if (host_slab) *host_slab = sl.slab_host;
+  return GS_OK;
+}
+
+int gs_slicer_frontiers(gs_slicer *s, int32_t slot, const int32_t **device_frontiers) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  Slot &sl = s->slots[slot];
+  if (sl.state != SLOT_DONE) return fail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (device_frontiers) *device_frontiers = sl.ws.fslab;
+  return GS_OK;
+}
+
+int gs_slicer_read_frontier(gs_slicer *s, int32_t slot, int32_t layer, int32_t *host_out) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  Slot &sl = s->slots[slot];
+  if (sl.state != SLOT_DONE) return fail(GS_ERR_STATE, "slot %d not waited on", slot);
+  if (layer < 0 || layer > s->cfg.num_layers) return fail(GS_ERR_INVALID, "bad layer");
+  const gs_span sp = sl.hdr_host->frontier[layer];
+  if (sp.len == 0) return GS_OK;
+  if (!host_out) return fail(GS_ERR_INVALID, "NULL argument");
+  CU(cudaSetDevice(s->g->device));
+  CU(cudaMemcpy(host_out, sl.ws.fslab + sp.off, (size_t)sp.len * sizeof(int32_t), cudaMemcpyDeviceToHost));
   return GS_OK;
 }
 

@@ -48,8 +48,10 @@ struct GsWs {
   // per-slot state
   gs_sample_header *hdr; // device
   uint32_t *table;       // [N] minimum edge-source position of the node in the current layer (GS_INF: none)
-  int32_t *slab;         // sample slab: frontiers + every bipartite list
+  int32_t *slab;         // sample slab: every bipartite list (mirrored to the host in e2e mode)
   int64_t slab_cap;
+  int32_t *fslab;        // frontier slab: frontiers 0..L (device only; read back on demand)
+  int64_t fslab_cap;
   int64_t *rowstart;     // [Fcap]   indptr[front[i]]
   int32_t *rowdeg;       // [Fcap]
   uint32_t *off;         // [Fcap+1] first candidate position of row i

@@ -93,14 +93,14 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
       h->draw_base[i] = 0;
     }
   }
-  bool bad = (n < 0 || n > ws.Fcap || (int64_t)n > ws.slab_cap);
+  bool bad = (n < 0 || n > ws.Fcap || (int64_t)n > ws.fslab_cap);
   if (!bad)
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
       int64_t v = ws.seeds_in[i];
       if (v < 0 || v >= (int64_t)ws.num_nodes) {
         s_bad = 1;
       } else {
-        ws.slab[i] = (int32_t)v;
+        ws.fslab[i] = (int32_t)v;
         // the table is all-INF between minibatches: a second claim of the same
         // entry is a duplicate seed (k_rows_scan resets the claimed entries)
         if (atomicCAS(ws.table + v, GS_INF, (uint32_t)i) != GS_INF) s_bad = 1;
@@ -119,7 +119,9 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
     h->late_status = 0;
     h->reserved[0] = ws.input->want_host;  // kept on the device: k_finish must not poll host memory from every thread  // late error raised inside a tiled kernel
     const int nn = bad ? 0 : n;
-    h->slab_used = ((int64_t)nn + 3) & ~3ll;
+    h->slab_used = 0;
+    h->reserved[1] = (nn + 3) & ~3;  // frontier slab in use (int32 elements)
+    h->reserved[2] = 1;              // frontier spans index the frontier slab, not the sample slab
     h->frontier_len[0] = nn;
     h->frontier[0].off = 0;
     h->frontier[0].len = nn;
@@ -136,7 +138,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
   __shared__ unsigned long long s_w64[GS_NW + 1];
   __shared__ uint32_t s_w[GS_NW + 1];
   const int F = h->frontier_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   int t0, t1;
@@ -218,7 +220,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
   const Tbl tbl(ws);
   __shared__ uint32_t s_w[GS_NW + 1];
   const int F = h->frontier_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
@@ -276,7 +278,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   __shared__ uint32_t s_off[GS_TILE + 2];
   const int F = h->frontier_len[layer];
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const uint32_t batch = (uint32_t)h->batch_index;
@@ -402,7 +404,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   const int P = ws.P, NC = 2 * P + 1;
   const int F = h->frontier_len[layer];
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles per CTA (cta_tiles)
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
@@ -504,8 +506,8 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     bool ok = true;
     const uint32_t fnext = s_tot[0];
     if (layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
-    int64_t used = h->slab_used;
-    gs_span fs = slab_alloc(used, ws.slab_cap, fnext, ok);
+    int64_t used = h->slab_used, fused = h->reserved[1];
+    gs_span fs = slab_alloc(fused, ws.fslab_cap, fnext, ok);
     int64_t edges = 0;
     for (int q = 0; q < P && ok; q++) {
       h->field[layer][q][GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, s_tot[1 + q], ok);
@@ -515,6 +517,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     }
     if (ok) {
       h->slab_used = used;
+      h->reserved[1] = (int32_t)fused;
       h->frontier[layer + 1] = fs;
       h->frontier_len[layer + 1] = (int32_t)fnext;
       h->edges += edges;
@@ -548,8 +551,8 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
   const int P = ws.P, NC = 2 * P + 1;
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
-  int32_t *fnext = ws.slab + h->frontier[layer + 1].off;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
+  int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   if (threadIdx.x < P) {
     s_in_off[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
@@ -685,7 +688,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
   __shared__ uint32_t s_w[GS_NW + 1];
   const int P = ws.P, NF = 4 * P;
   const int F = h->frontier_len[layer];
-  const int32_t *front = ws.slab + h->frontier[layer].off;
+  const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   if (threadIdx.x < GS_NF_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
@@ -779,7 +782,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
   const int P = ws.P, NF = 4 * P;
   const int F = h->frontier_len[layer];
-  const int32_t *__restrict__ front = ws.slab + h->frontier[layer].off;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   if (threadIdx.x < P * GS_NUM_FIELDS)
     s_off[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
@@ -920,7 +923,7 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
   const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
   if (h->status == 0) {
     const int L = ws.L;
-    const int32_t *fl = ws.slab + h->frontier[L].off;
+    const int32_t *fl = ws.fslab + h->frontier[L].off;
     const int FL = h->frontier_len[L];
     if ((int64_t)FL * 8 > (int64_t)ws.num_nodes) {
       // most 32-byte sectors of the table hold a touched entry: a streaming
