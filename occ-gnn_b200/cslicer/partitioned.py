@@ -65,6 +65,32 @@ def partition_csr(indptr, indices, num_parts, owner_mode="mod", bounds=None):
     return out
 
 
+def renumber_by_owner(indptr, indices, owner, num_parts):
+    """Arbitrary owner map (e.g. METIS `partition_map_opt.bin`, metis.py:70-71) ->
+    contiguous owner ranges, the form the partitioned slicer addresses arithmetically
+    (SURVEY 8(f) N4).  Nodes are renumbered part after part, keeping their relative
+    order inside a part.  -> (indptr', indices', bounds, new_of_old, old_of_new):
+    row new_of_old[v] of the new CSR is row v of the old one with neighbour ids
+    mapped; part q owns [bounds[q], bounds[q+1])."""
+    ip = np.asarray(indptr, dtype=np.int64)
+    ix = np.asarray(indices, dtype=np.int64)
+    own = np.asarray(owner, dtype=np.int64)
+    n = ip.size - 1
+    if own.size != n or own.min(initial=0) < 0 or own.max(initial=0) >= num_parts:
+        raise ValueError("owner map must have num_nodes entries in [0, num_parts)")
+    old_of_new = np.argsort(own, kind="stable").astype(np.int64)
+    new_of_old = np.empty(n, dtype=np.int64)
+    new_of_old[old_of_new] = np.arange(n, dtype=np.int64)
+    counts = np.bincount(own, minlength=num_parts)
+    bounds = [0] + np.cumsum(counts).tolist()
+    deg = np.diff(ip)[old_of_new]
+    nip = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(deg, out=nip[1:])
+    src = np.repeat(ip[old_of_new] - nip[:-1], deg) + np.arange(nip[-1], dtype=np.int64)
+    nix = new_of_old[ix[src]]
+    return nip, nix, bounds, new_of_old, old_of_new
+
+
 class _Dev:
     def __init__(self, device):
         self.device = int(device)

@@ -37,6 +37,24 @@ def test_partition_csr_round_trip():
                 assert np.array_equal(lix[lip[li]:lip[li + 1]], ix[ip[v]:ip[v + 1]])
 
 
+def test_renumber_by_owner_makes_contiguous_ranges():
+    from cslicer.partitioned import renumber_by_owner
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    n = ip.size - 1
+    P = 4
+    own = np.random.default_rng(1).integers(0, P, n)
+    nip, nix, b, new_of_old, old_of_new = renumber_by_owner(ip, ix, own, P)
+    assert b[0] == 0 and b[-1] == n and nip[-1] == ix.size
+    for q in range(P):
+        assert np.all(own[old_of_new[b[q]:b[q + 1]]] == q)
+        assert np.all(np.diff(old_of_new[b[q]:b[q + 1]]) > 0)      # relative order kept
+    for v in range(0, n, 37):
+        w = new_of_old[v]
+        assert np.array_equal(nix[nip[w]:nip[w + 1]], new_of_old[ix[ip[v]:ip[v + 1]]])
+    assert np.array_equal(old_of_new[new_of_old], np.arange(n))
+
+
 def _compare_rank(view, orc, g, check_frontiers=True, owner=None):
     """Rank g's sample against part g of the oracle's; the slots [q != g] of
     from_ids / to_ids (empty in the reference, bipartite.h:19-21) carry the per-peer
