@@ -39,7 +39,13 @@ typedef enum {
   GS_ERR_PEER = 7      /* partitioned mode: a peer rank failed or never reached a barrier */
 } gs_status;
 
-typedef enum { GS_RNG_PHILOX = 0, GS_RNG_DRAWS = 1 } gs_rng_mode;
+/* GS_RNG_PHILOX: picks WITH replacement (slicer.cpp:14-18), counter-based draws.
+ * GS_RNG_DRAWS: the same rule fed from an explicit draw stream (mt19937 replay).
+ * GS_RNG_PHILOX_NOREPLACE: the `fanout` picks of a row are distinct -- the rule
+ * of the Python sibling's sampler (dgl sample_neighbors, replace=False,
+ * python/utils/sampler.py:187); SURVEY 8(f) N1.  Parity with DGL's generator is
+ * unpinned (DGL absent); the oracle restates this library's own permutation. */
+typedef enum { GS_RNG_PHILOX = 0, GS_RNG_DRAWS = 1, GS_RNG_PHILOX_NOREPLACE = 2 } gs_rng_mode;
 
 /* Per-bipartite lists.  The first seven are the reference's fields
  * (bipartite.h:9-24, exposed at pyfrontend.cpp:128-138); for from_ids/to_ids the
@@ -242,7 +248,7 @@ typedef struct {
   void *stream;                            /* cudaStream_t to run on; NULL = own stream */
   const float *features_local_host;        /* optional [n_local x feature_dim] fp32: rows of the owned nodes, local order */
   int32_t feature_dim;
-  int32_t reserved0;
+  int32_t rng_mode;                        /* GS_RNG_PHILOX (default) or GS_RNG_PHILOX_NOREPLACE */
   int64_t feature_rows_capacity;           /* 0 = derive */
   int64_t shuffle_rows_capacity;           /* rows one rank may send to one peer per shuffle; 0 = no shuffle */
   int32_t shuffle_max_dim;                 /* widest row a shuffle may carry */

@@ -118,14 +118,15 @@ class cslicer:
     streams (each slot is one pre-captured CUDA graph).  Keyword extensions:
     root, dataset, fanouts, num_parts, owner_map ('mod' | 'range' | 'metis' | array),
     seed, device, draws (explicit 32-bit draw stream: replay mode), compat,
-    shuffle ('reference' | 'none'), host_output, capacities.
+    shuffle ('reference' | 'none'), host_output, capacities, replace (False = distinct
+    picks per row, the Python sibling's DGL rule, python/utils/sampler.py:187).
     """
 
     def __init__(self, name, queue_size, no_worker_threads, number_of_epochs, minibatch_size, *,
                  root=None, dataset=None, fanouts=None, num_layers=None, num_parts=REF_PARTS,
                  owner_map="mod", seed=0, device=0, draws=None, compat=True, shuffle="reference",
                  host_output=True, use_graph=True, frontier_capacity=0, cand_capacity=0,
-                 slab_capacity=0):
+                 slab_capacity=0, replace=True):
         if dataset is None:
             root = root or os.environ.get("GSPLIT_DATA_ROOT", DEFAULT_ROOT)
             dataset = Dataset(os.path.join(root, name), load_node_data=(owner_map == "metis"))
@@ -154,7 +155,8 @@ class cslicer:
                              num_slots=slots, num_streams=max(1, int(no_worker_threads)),
                              seed=seed, owner=owner, draws=draws, host_output=host_output,
                              use_graph=use_graph, frontier_capacity=frontier_capacity,
-                             cand_capacity=cand_capacity, slab_capacity=slab_capacity)
+                             cand_capacity=cand_capacity, slab_capacity=slab_capacity,
+                             replace=replace)
         self._shuffle = shuffle
         self._nodes = np.arange(self.num_nodes, dtype=np.int64)  # WorkerPool.cpp:13-16
         self._per_epoch = (self.num_nodes - 1) // self.minibatch_size + 1

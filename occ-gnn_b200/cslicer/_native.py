@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgsplit_slicer.so")
 
 MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 1
-RNG_PHILOX, RNG_DRAWS = 0, 1
+RNG_PHILOX, RNG_DRAWS, RNG_PHILOX_NOREPLACE = 0, 1, 2
 OK, ERR_INVALID, ERR_CUDA, ERR_BUSY, ERR_OVERFLOW, ERR_SEED, ERR_STATE, ERR_PEER = range(8)
 OWNER_MOD, OWNER_RANGE = 0, 1
 FIELDS = ["in_nodes", "out_nodes", "owned_out_nodes", "from_ids", "to_ids", "self_ids_in",
@@ -77,7 +77,7 @@ class PConfig(C.Structure):
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
                 ("slab_capacity", C.c_int64), ("num_edges_global", C.c_int64),
                 ("stream", C.c_void_p), ("features_local_host", C.c_void_p),
-                ("feature_dim", C.c_int32), ("reserved0", C.c_int32),
+                ("feature_dim", C.c_int32), ("rng_mode", C.c_int32),
                 ("feature_rows_capacity", C.c_int64), ("shuffle_rows_capacity", C.c_int64),
                 ("shuffle_max_dim", C.c_int32), ("reserved1", C.c_int32)]
 

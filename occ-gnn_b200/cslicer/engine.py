@@ -216,7 +216,9 @@ class Slicer:
     def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
                  seed=0, owner=None, draws=None, host_output=True, use_graph=True,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True,
-                 features=None, feature_rows_capacity=0):
+                 features=None, feature_rows_capacity=0, replace=True):
+        """replace=False: the picks of a row are distinct (GS_RNG_PHILOX_NOREPLACE,
+        the Python sibling's DGL sampling rule, python/utils/sampler.py:187)."""
         L = N.lib()
         self.graph = graph
         cfg = N.Config()
@@ -226,6 +228,10 @@ class Slicer:
             cfg.fanouts[i] = int(f)
         cfg.num_parts = int(num_parts)
         cfg.seed = int(seed)
+        if not replace:
+            if draws is not None:
+                raise ValueError("replace=False cannot be combined with an explicit draw stream")
+            cfg.rng_mode = N.RNG_PHILOX_NOREPLACE
         cfg.max_batch, cfg.num_slots, cfg.num_streams = int(max_batch), int(num_slots), int(num_streams)
         cfg.host_output, cfg.use_graph = int(bool(host_output)), int(bool(use_graph))
         cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)

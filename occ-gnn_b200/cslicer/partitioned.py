@@ -104,7 +104,7 @@ class PartitionedSlicer:
                  host_output=True, use_graph=True, stream=None, num_edges_global=0,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0,
                  timeout_ms=5000, features_local=None, feature_rows_capacity=0,
-                 shuffle_rows_capacity=0, shuffle_max_dim=0):
+                 shuffle_rows_capacity=0, shuffle_max_dim=0, replace=True):
         L = N.lib()
         ip = np.ascontiguousarray(indptr_local, dtype=np.int64)
         ix = np.ascontiguousarray(indices_local, dtype=np.int64)
@@ -120,6 +120,7 @@ class PartitionedSlicer:
             for q in range(num_parts + 1):
                 cfg.range_bounds[q] = int(b[q])
         cfg.seed = int(seed)
+        cfg.rng_mode = N.RNG_PHILOX if replace else N.RNG_PHILOX_NOREPLACE
         cfg.max_batch, cfg.num_slots = int(max_batch), int(num_slots)
         cfg.host_output, cfg.use_graph = int(bool(host_output)), int(bool(use_graph))
         cfg.grid_ctas, cfg.timeout_ms = int(grid_ctas), int(timeout_ms)

@@ -258,6 +258,8 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   } else {
     return pfail(GS_ERR_INVALID, "unknown owner_mode %d", cfg->owner_mode);
   }
+  if (cfg->rng_mode != GS_RNG_PHILOX && cfg->rng_mode != GS_RNG_PHILOX_NOREPLACE)
+    return pfail(GS_ERR_INVALID, "partitioned slicer: rng_mode must be GS_RNG_PHILOX or GS_RNG_PHILOX_NOREPLACE");
   if (n_local != want_local)
     return pfail(GS_ERR_INVALID, "rank %d owns %lld nodes under this owner map, shard has %lld",
                  cfg->rank, (long long)want_local, (long long)n_local);
@@ -402,6 +404,7 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   for (int l = 0; l < GS_MAX_LAYERS; l++) w.fanouts[l] = cfg->fanouts[l];
   w.seed_lo = (uint32_t)cfg->seed;
   w.seed_hi = (uint32_t)(cfg->seed >> 32);
+  w.rng_mode = cfg->rng_mode;
   w.me = s->me;
   w.Fcap = (int32_t)s->Fcap;
   w.Ccap = (int32_t)s->Ccap;

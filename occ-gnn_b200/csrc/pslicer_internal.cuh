@@ -52,6 +52,7 @@ struct PsWs {
   int32_t bounds[GS_MAX_PARTS + 1];  // PS_OWNER_RANGE
   int32_t fanouts[GS_MAX_LAYERS];
   uint32_t seed_lo, seed_hi;
+  int32_t rng_mode;       // GS_RNG_PHILOX or GS_RNG_PHILOX_NOREPLACE
   PsArena me;
   PsArena peer[GS_MAX_PARTS];  // peer[rank] == me
   // private workspaces (one set: minibatches run one after another on one stream)

@@ -308,8 +308,13 @@ __global__ void __launch_bounds__(GS_TPB) pk_expand(PsWs ws, int layer) {
         const int32_t deg = ws.rowdeg[row[it]];
         int32_t pick = slot[it] - 1;
         if (fan >= 0 && deg >= fan) {
-          const uint32_t r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1[it], slot[it] - 1);
-          pick = (int32_t)(r % (uint32_t)deg);
+          if (ws.rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) {
+            const uint4 key = philox_block(ws.seed_lo, ws.seed_hi, batch, layer, nd1[it], GS_NR_KEY_BLOCK);
+            pick = (int32_t)nr_pick(key, (uint32_t)pick, (uint32_t)deg);
+          } else {
+            const uint32_t r = philox_pick(ws.seed_lo, ws.seed_hi, batch, layer, nd1[it], slot[it] - 1);
+            pick = (int32_t)(r % (uint32_t)deg);
+          }
         }
         src[it] = ws.indices + rs + pick;
       }

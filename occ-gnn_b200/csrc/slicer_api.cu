@@ -301,7 +301,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   if (cfg->max_batch < 1) return fail(GS_ERR_INVALID, "max_batch must be >= 1");
   if (cfg->num_slots < 1 || cfg->num_slots > 256)
     return fail(GS_ERR_INVALID, "num_slots must be in [1,256]");
-  if (cfg->rng_mode != GS_RNG_PHILOX && cfg->rng_mode != GS_RNG_DRAWS)
+  if (cfg->rng_mode != GS_RNG_PHILOX && cfg->rng_mode != GS_RNG_DRAWS &&
+      cfg->rng_mode != GS_RNG_PHILOX_NOREPLACE)
     return fail(GS_ERR_INVALID, "unknown rng_mode %d", cfg->rng_mode);
   if (cfg->rng_mode == GS_RNG_DRAWS && (!cfg->draws_host || cfg->n_draws == 0))
     return fail(GS_ERR_INVALID, "GS_RNG_DRAWS needs draws_host / n_draws");

@@ -152,6 +152,51 @@ __device__ __forceinline__ uint32_t philox_pick(uint32_t k0, uint32_t k1, uint32
   return w == 0 ? c0 : (w == 1 ? c1 : (w == 2 ? c2 : c3));
 }
 
+// GS_RNG_PHILOX_NOREPLACE: pick j of a row is perm(j), perm a keyed bijection of
+// [0, deg) -- so the `fan` picks of a row are distinct (a uniform fan-subset,
+// what dgl.sampling.sample_neighbors(replace=False) draws at
+// python/utils/sampler.py:187) while every position still computes its own pick
+// in O(1), without reading the row.  Keys: the Philox block with block id
+// GS_NR_KEY_BLOCK of (seed, batch, layer, node).
+//   deg <= 16: Fisher-Yates over sixteen 4-bit entries packed in one register,
+//              run up to step j (exactly uniform up to 2^-28 draw bias);
+//   deg  > 16: unbalanced Feistel network over ceil(log2 deg) bits (12 rounds on
+//              5-bit domains, 8 above: pair/triple statistics measured uniform),
+//              cycle-walked back into [0, deg) (domain < 2*deg: < 2 walks expected).
+#define GS_NR_KEY_BLOCK 0x00FFFFFF
+__device__ __forceinline__ uint32_t nr_mix(uint32_t r, uint32_t key) {
+  uint32_t f = r * 0x9E3779B1u + key;
+  f ^= f >> 16; f *= 0x85EBCA6Bu;
+  f ^= f >> 13; f *= 0xC2B2AE35u;
+  return f ^ (f >> 16);
+}
+__device__ __forceinline__ uint32_t nr_pick(const uint4 &key, uint32_t j, uint32_t deg) {
+  if (deg <= 1u) return 0u;
+  if (deg <= 16u) {
+    unsigned long long perm = 0xFEDCBA9876543210ull;
+    for (uint32_t i = 0; i <= j; i++) {
+      const uint32_t t = i + __umulhi(nr_mix(i, philox_word(key, i & 3)), deg - i);
+      const unsigned long long d = ((perm >> (4 * i)) ^ (perm >> (4 * t))) & 15ull;
+      perm ^= (d << (4 * i)) ^ (d << (4 * t));
+    }
+    return (uint32_t)(perm >> (4 * j)) & 15u;
+  }
+  const int bits = 32 - __clz((int)(deg - 1u));
+  const int rounds = bits <= 5 ? 12 : 8;
+  uint32_t x = j;
+  do {
+    int wl = bits >> 1, wr = bits - wl;
+    for (int r = 0; r < rounds; r++) {
+      const uint32_t left = x >> wr, right = x & ((1u << wr) - 1u);
+      const uint32_t rk = philox_word(key, r & 3) + (uint32_t)(r >> 2) * 0x632BE5ABu;
+      const uint32_t f = nr_mix(right, rk) & ((1u << wl) - 1u);
+      x = (right << wl) | (left ^ f);
+      const int t = wl; wl = wr; wr = t;
+    }
+  } while (x >= deg);
+  return x;
+}
+
 // Exclusive scan of `nc` counter arrays (cnt[c*stride + b], b < n = number of
 // CTAs) by one CTA, in place; totals[c] receives each array's sum.  One warp
 // per counter, eight independent coalesced loads in flight per lane, shuffles

@@ -283,6 +283,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const uint32_t batch = (uint32_t)h->batch_index;
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
+  const bool norepl = ws.rng_mode == (int)GS_RNG_PHILOX_NOREPLACE;
   const uint64_t dbase = h->draw_base[layer];
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int i_lo = (int)ws.tile_first[t];
@@ -338,12 +339,13 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
             const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row[k]] + (uint32_t)pick;
             r = di < ws.n_draws ? ws.draws[di] : 0u;
           } else {
-            if (blk_row != row[k] || blk_id != (pick >> 2)) {
+            const int want = norepl ? GS_NR_KEY_BLOCK : (pick >> 2);
+            if (blk_row != row[k] || blk_id != want) {
               blk_row = row[k];
-              blk_id = pick >> 2;
+              blk_id = want;
               blk = philox_block(ws.seed_lo, ws.seed_hi, batch, layer, nd1[k], blk_id);
             }
-            r = philox_word(blk, pick & 3);
+            r = norepl ? nr_pick(blk, (uint32_t)pick, (uint32_t)deg[k]) : philox_word(blk, pick & 3);
           }
           pick = (int32_t)(r % (uint32_t)deg[k]);
         }

@@ -102,6 +102,63 @@ uint32_t orc_philox_pick(uint64_t seed, uint64_t batch_index, int layer,
   return out[slot & 3];
 }
 
+/* Without-replacement picks: pick j of a row = perm(j), perm a keyed bijection
+ * of [0, deg); semantics follow python/utils/sampler.py:187 (distinct
+ * neighbours per destination).  Keys: the Philox block of (seed, batch, layer,
+ * node) whose block id is 0xFFFFFF (pick blocks use ids slot/4, far below).
+ *   deg <= 16: the first j+1 steps of a Fisher-Yates shuffle of 0..15 (step i
+ *              swaps entry i with entry i + floor(draw_i * (deg-i) / 2^32));
+ *   deg  > 16: an unbalanced Feistel network over ceil(log2 deg) bits (12 rounds
+ *              when that is 5 bits, else 8), re-applied until the value < deg. */
+static uint32_t nr_mix(uint32_t right, uint32_t key) {
+  uint32_t f = right * 0x9E3779B1u + key;
+  f ^= f >> 16;
+  f *= 0x85EBCA6Bu;
+  f ^= f >> 13;
+  f *= 0xC2B2AE35u;
+  f ^= f >> 16;
+  return f;
+}
+
+uint32_t orc_noreplace_pick(uint64_t seed, uint64_t batch_index, int layer, int64_t node,
+                            uint32_t j, uint32_t deg) {
+  if (deg <= 1u) return 0u;
+  uint32_t ctr[4], key[2], rk[4];
+  ctr[0] = (uint32_t)(uint64_t)node;
+  ctr[1] = (uint32_t)((uint64_t)node >> 32);
+  ctr[2] = (uint32_t)batch_index;
+  ctr[3] = ((uint32_t)layer << 24) | 0x00FFFFFFu;
+  key[0] = (uint32_t)seed;
+  key[1] = (uint32_t)(seed >> 32);
+  orc_philox4x32_10(ctr, key, rk);
+  if (deg <= 16u) {
+    uint8_t a[16];
+    for (int i = 0; i < 16; i++) a[i] = (uint8_t)i;
+    for (uint32_t i = 0; i <= j; i++) {
+      uint32_t draw = nr_mix(i, rk[i % 4]);
+      uint32_t t = i + (uint32_t)(((uint64_t)draw * (deg - i)) >> 32);
+      uint8_t tmp = a[i]; a[i] = a[t]; a[t] = tmp;
+    }
+    return a[j];
+  }
+  int bits = 0;
+  while (((uint64_t)1 << bits) < deg) bits++; /* smallest bits with 2^bits >= deg */
+  const int rounds = bits <= 5 ? 12 : 8;
+  uint32_t x = j;
+  for (;;) {
+    int wl = bits / 2, wr = bits - wl;
+    for (int r = 0; r < rounds; r++) {
+      uint32_t left = x >> wr;
+      uint32_t right = x & (uint32_t)(((uint64_t)1 << wr) - 1);
+      uint32_t k = rk[r % 4] + (uint32_t)(r / 4) * 0x632BE5ABu;
+      uint32_t f = nr_mix(right, k) & (uint32_t)(((uint64_t)1 << wl) - 1);
+      x = (right << wl) | (left ^ f);
+      int t = wl; wl = wr; wr = t;
+    }
+    if (x < deg) return x;
+  }
+}
+
 /* ------------------------------------------------------ duplicate remover */
 /* util/duplicate.cpp:8-45: dense int mask over all nodes + touched list. */
 typedef struct {
@@ -289,7 +346,13 @@ static void orc_neighbour_sample(orc_slicer *s, int layer, int64_t nd1, vec *out
     for (int64_t i = 0; i < deg; i++) vec_push(out, s->indices[off + i]);
   } else {
     for (int i = 0; i < fan; i++) {
-      int64_t r = (int64_t)(orc_draw(s, layer, nd1, i) % (uint64_t)deg);
+      int64_t r;
+      if (s->cfg.rng_mode == ORC_RNG_PHILOX_NOREPLACE) {
+        r = (int64_t)orc_noreplace_pick(s->cfg.seed, s->batch_index, layer, nd1, (uint32_t)i, (uint32_t)deg);
+        s->draws_used++;
+      } else {
+        r = (int64_t)(orc_draw(s, layer, nd1, i) % (uint64_t)deg);
+      }
       vec_push(out, s->indices[off + r]);
     }
   }

@@ -33,7 +33,11 @@ extern "C" {
 #define ORC_MAX_LAYERS 8
 #define ORC_MAX_PARTS 16
 
-enum { ORC_RNG_MT19937 = 0, ORC_RNG_PHILOX = 1, ORC_RNG_DRAWS = 2 };
+/* ORC_RNG_PHILOX_NOREPLACE: distinct picks per row (the product's
+ * GS_RNG_PHILOX_NOREPLACE; semantics of python/utils/sampler.py:187,
+ * dgl sample_neighbors replace=False).  DGL's own generator is not available
+ * here: this mode restates the product's permutation -- parity unpinned. */
+enum { ORC_RNG_MT19937 = 0, ORC_RNG_PHILOX = 1, ORC_RNG_DRAWS = 2, ORC_RNG_PHILOX_NOREPLACE = 3 };
 
 enum {
   ORC_F_IN_NODES = 0,
@@ -72,6 +76,9 @@ int orc_slice(orc_slicer *s, const int64_t *seeds, int64_t n_seeds,
 
 /* Field access on the last sliced sample (pointers valid until next orc_slice). */
 int64_t orc_field_len(const orc_slicer *s, int layer, int part, int field);
+/* pick j (0-based) of a row of degree deg under ORC_RNG_PHILOX_NOREPLACE */
+uint32_t orc_noreplace_pick(uint64_t seed, uint64_t batch_index, int layer, int64_t node,
+                            uint32_t j, uint32_t deg);
 const int64_t *orc_field_ptr(const orc_slicer *s, int layer, int part, int field);
 int64_t orc_frontier_len(const orc_slicer *s, int layer); /* layer in [0, L] */
 const int64_t *orc_frontier_ptr(const orc_slicer *s, int layer);

@@ -20,7 +20,7 @@ LIB = os.path.join(HERE, "liborc.so")
 REF_LIB = os.path.join(HERE, "_ref", "libcslicer_ref.so")
 
 MAX_LAYERS, MAX_PARTS = 8, 16
-RNG_MT19937, RNG_PHILOX, RNG_DRAWS = 0, 1, 2
+RNG_MT19937, RNG_PHILOX, RNG_DRAWS, RNG_PHILOX_NOREPLACE = 0, 1, 2, 3
 FIELDS = ["in_nodes", "out_nodes", "owned_out_nodes", "from_ids", "to_ids",
           "self_ids_in", "self_ids_out", "indptr_compat", "csr_indptr", "csr_indices"]
 
@@ -71,6 +71,8 @@ def lib():
         L.orc_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_philox_pick.restype = C.c_uint32
         L.orc_philox_pick.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_int64, C.c_int]
+        L.orc_noreplace_pick.restype = C.c_uint32
+        L.orc_noreplace_pick.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_int64, C.c_uint32, C.c_uint32]
         L.orc_mt19937_stream.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
         _lib = L
     return _lib
@@ -193,6 +195,10 @@ def philox4x32_10(ctr, key):
 
 def philox_pick(seed, batch_index, layer, node, slot):
     return int(lib().orc_philox_pick(seed, batch_index, layer, node, slot))
+
+
+def noreplace_pick(seed, batch_index, layer, node, j, deg):
+    return int(lib().orc_noreplace_pick(seed, batch_index, layer, node, j, deg))
 
 
 def mt19937_stream(n, seed=5489):

@@ -70,6 +70,54 @@ def test_philox_known_answers():
         assert list(O.philox4x32_10(ctr, key)) == want
 
 
+def test_noreplace_pick_is_a_keyed_permutation():
+    """ORC_RNG_PHILOX_NOREPLACE (python/utils/sampler.py:187): over
+    j = 0..deg-1 the picks of a row are a permutation of its neighbours, so any
+    `fanout` of them are distinct; different nodes / batches / layers permute
+    differently; every neighbour is equally likely to be pick 0."""
+    for deg in [1, 2, 3, 4, 5, 7, 8, 9, 16, 17, 31, 33, 100, 1000, 1025]:
+        picks = [O.noreplace_pick(5, 2, 1, 40 + deg, j, deg) for j in range(deg)]
+        assert sorted(picks) == list(range(deg))
+    a = [O.noreplace_pick(5, 2, 1, 7, j, 50) for j in range(50)]
+    assert a != [O.noreplace_pick(5, 2, 1, 8, j, 50) for j in range(50)]
+    assert a != [O.noreplace_pick(5, 3, 1, 7, j, 50) for j in range(50)]
+    assert a != [O.noreplace_pick(5, 2, 0, 7, j, 50) for j in range(50)]
+    assert a != [O.noreplace_pick(6, 2, 1, 7, j, 50) for j in range(50)]
+    # first pick uniform, (pick 0, pick 1) uniform over ordered pairs: Fisher-Yates
+    # branch (deg <= 16), 12-round and 8-round Feistel branches
+    for deg, n, lim1, lim2 in [(13, 26000, 40.0, 240.0), (20, 30000, 52.0, 500.0), (40, 40000, 82.0, 1800.0)]:
+        p0 = np.array([O.noreplace_pick(1, 0, 0, v, 0, deg) for v in range(n)])
+        p1 = np.array([O.noreplace_pick(1, 0, 0, v, 1, deg) for v in range(n)])
+        first = np.bincount(p0, minlength=deg)
+        pair = np.bincount(p0 * deg + p1, minlength=deg * deg).reshape(deg, deg)
+        exp = n / deg
+        assert ((first - exp) ** 2 / exp).sum() < lim1      # chi-square, deg-1 dof, p ~ 1e-4
+        assert pair.trace() == 0
+        off = pair[~np.eye(deg, dtype=bool)]
+        expp = n / (deg * (deg - 1))
+        assert ((off - expp) ** 2 / expp).sum() < lim2      # deg*(deg-1)-1 dof, p < 1e-4
+
+
+def test_noreplace_oracle_samples_distinct_neighbours():
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    fan = [10, 5]
+    orc = O.OracleSlicer(ip, ix, fan, 1, O.RNG_PHILOX_NOREPLACE, seed=4)
+    seeds = np.random.default_rng(2).permutation(ip.size - 1)[:200]
+    r = orc.slice(seeds, 0)
+    d = r["layers"][0][0]
+    # P = 1: out_nodes = the frontier, in_nodes[csr_indices] = self + sampled sources per row
+    src = d["in_nodes"][d["csr_indices"]]
+    for i, nd in enumerate(d["out_nodes"]):
+        row = src[d["csr_indptr"][i]:d["csr_indptr"][i + 1]]
+        nb = ix[ip[nd]:ip[nd + 1]]
+        assert set(row.tolist()) <= set(nb.tolist())
+        if nb.size >= fan[0]:  # sampled row: exactly `fanout` picks, all distinct (no duplicate edges in the graph)
+            assert len(row) == fan[0] and len(set(row.tolist())) == fan[0]
+        else:
+            assert np.array_equal(row, nb)
+
+
 def test_mt19937_matches_numpy_legacy_seeding():
     m = np.random.MT19937()
     m._legacy_seeding(5489)

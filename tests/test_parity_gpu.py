@@ -118,6 +118,41 @@ def test_philox_matches_oracle(fanouts, P, owner, batch, shape):
     g.close()
 
 
+@pytest.mark.parametrize("fanouts,P,shape,batch", [([15, 10, 5], 4, "small", 512), ([10, 10, 10], 8, "tiny", 256),
+                                                   ([1, 2, 40], 2, "small", 100), ([-1, 7], 3, "tiny", 64)])
+def test_without_replacement_matches_oracle(fanouts, P, shape, batch):
+    """GS_RNG_PHILOX_NOREPLACE (python/utils/sampler.py:187 samples
+    distinct neighbours): bit-exact against the oracle's restatement of the keyed
+    permutation, and the picks of every sampled row are distinct."""
+    E = _engine()
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph(shape, seed=21)
+    n = ip.size - 1
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fanouts, P, max_batch=batch, num_slots=2, num_streams=2, seed=3, replace=False)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX_NOREPLACE, seed=3)
+    rng = np.random.default_rng(8)
+    for b in range(4):
+        seeds = rng.permutation(n)[:batch]
+        v = sl.slice(seeds, b)
+        _compare(v, orc.slice(seeds, b))
+        # distinct picks: per destination, the sources over all parts have no repeats
+        for l in range(len(fanouts)):
+            pairs = []
+            for q in range(P):
+                ind, idx = v.numpy(l, q, "csr_indptr"), v.numpy(l, q, "csr_indices")
+                src = v.numpy(l, q, "in_nodes")[idx]
+                dst = np.repeat(v.numpy(l, q, "out_nodes"), np.diff(ind))
+                pairs.append(np.stack([dst, src], 1))
+            pairs = np.concatenate(pairs)
+            assert np.unique(pairs, axis=0).shape[0] == pairs.shape[0]
+        v.release()
+    sl.close()
+    g.close()
+    with pytest.raises(ValueError):
+        E.Slicer(E.Graph(ip, ix), fanouts, P, draws=np.zeros(4, np.uint32), replace=False)
+
+
 def test_graph_and_eager_paths_agree_and_device_views_match_host():
     E = _engine()
     import torch

@@ -126,6 +126,31 @@ def test_local_group_matches_oracle(fanouts, P, owner, batch, shape):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fanouts,P,owner", [([15, 10, 5], 4, "mod"), ([3, 20], 3, "range")])
+def test_local_group_without_replacement_matches_oracle(fanouts, P, owner):
+    """replace=False: every rank draws the same keyed permutation
+    for the rows it owns as the sequential oracle."""
+    from cslicer.partitioned import LocalGroup, owner_of, range_bounds
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=21)
+    n = ip.size - 1
+    b = range_bounds(n, P)
+    own = None if owner == "mod" else owner_of(np.arange(n), n, P, "range", b)
+    grp = LocalGroup(ip, ix, P, fanouts, owner_mode=owner, bounds=b, max_batch=300, num_slots=2,
+                     seed=5, replace=False)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX_NOREPLACE, seed=5, owner=own)
+    rng = np.random.default_rng(9)
+    for bi in range(3):
+        seeds = rng.permutation(n)[:300]
+        views = grp.slice(seeds, bi)
+        want = orc.slice(seeds, bi)
+        for g, v in enumerate(views):
+            _compare_rank(v, want, g, owner=own)
+            v.release()
+    grp.close()
+
+
+@pytest.mark.gpu
 def test_local_group_pipelined_slots_and_duplicate_seed():
     """Two minibatches in flight per rank (slots), then a bad batch: every rank
     reports the error, reset() brings the group back."""
