@@ -146,6 +146,17 @@ int64_t gs_graph_num_edges(const gs_graph *g);
  * shard that holds only the nodes with id % num_parts == part). */
 int gs_features_create(int device, int64_t num_rows, int32_t dim, int32_t id_div,
                        const float *rows_host, gs_features **out);
+/* The same store with the table left in HOST memory and an HBM cache in front
+ * (replaces MemoryManager.initialize + refresh_cache,
+ * python/utils/memory_manager.py:40-104).  rows_host is page-locked and mapped
+ * in place (no copy; it must stay valid and unchanged until gs_features_destroy);
+ * cached_rows: n_cached distinct row indices (id / id_div) whose rows are copied
+ * to HBM.  Gathers read cached rows from HBM and every other row straight from
+ * host memory over PCIe inside the same kernel -- no per-minibatch refresh. */
+int gs_features_create_cached(int device, int64_t num_rows, int32_t dim, int32_t id_div,
+                              const float *rows_host, const int64_t *cached_rows, int64_t n_cached,
+                              gs_features **out);
+int gs_features_info(const gs_features *f, int64_t *num_rows, int32_t *dim, int64_t *rows_in_hbm);
 int gs_features_destroy(gs_features *f);
 /* Standalone gather on device pointers: out[i, :] = rows[ids[i] / id_div, :].
  * stream: a cudaStream_t (NULL = default stream).  Asynchronous. */

@@ -26,7 +26,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_reference_shuffle", "gs_features_create",
-           "gs_features_destroy", "gs_features_gather", "gs_slicer_feature_slab",
+           "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
            "gs_slicer_frontiers", "gs_slicer_read_frontier",
            # partitioned mode (one rank per GPU)
            "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
@@ -124,6 +124,10 @@ def lib():
     L.gs_features_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                      C.POINTER(C.c_void_p)]
     L.gs_features_destroy.argtypes = [C.c_void_p]
+    L.gs_features_create_cached.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                            C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+    L.gs_features_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32),
+                                   C.POINTER(C.c_int64)]
     L.gs_features_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     L.gs_slicer_feature_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                          C.POINTER(C.c_int32)]

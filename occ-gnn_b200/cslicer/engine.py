@@ -44,18 +44,37 @@ class Graph:
 
 
 class Features:
-    """Node features resident in HBM (gs_features).  rows: [num_rows, dim] fp32;
-    node id lives at row id // id_div (id_div=1: full replica; =P: the shard of
-    one part under owner = id % P)."""
+    """Node features (gs_features).  rows: [num_rows, dim] fp32; node id lives at
+    row id // id_div (id_div=1: full replica; =P: the shard of one part under
+    owner = id % P).
 
-    def __init__(self, rows, device=0, id_div=1):
-        r = np.ascontiguousarray(rows, dtype=np.float32)
+    cache_rows=None: the whole table is copied to HBM.  cache_rows=<row indices>:
+    the table stays in host memory (page-locked in place -- `rows` must then be a
+    C-contiguous float32 array, which this object keeps alive) and only those rows
+    are held in HBM; gathers serve every other row from host memory inside the
+    same kernel (python/utils/memory_manager.py:40-104 without the refresh step)."""
+
+    def __init__(self, rows, device=0, id_div=1, cache_rows=None):
+        h = C.c_void_p()
+        if cache_rows is None:
+            r = np.ascontiguousarray(rows, dtype=np.float32)
+        else:
+            r = rows
+            if not (isinstance(r, np.ndarray) and r.dtype == np.float32 and r.flags.c_contiguous):
+                raise ValueError("a cached store maps `rows` in place: pass a C-contiguous float32 ndarray")
         if r.ndim != 2:
             raise ValueError("features must be [num_rows, dim]")
         self.num_rows, self.dim, self.device, self.id_div = int(r.shape[0]), int(r.shape[1]), int(device), int(id_div)
-        h = C.c_void_p()
-        N.check(N.lib().gs_features_create(self.device, self.num_rows, self.dim, self.id_div,
-                                           r.ctypes.data, C.byref(h)))
+        if cache_rows is None:
+            N.check(N.lib().gs_features_create(self.device, self.num_rows, self.dim, self.id_div,
+                                               r.ctypes.data, C.byref(h)))
+            self.rows_in_hbm = self.num_rows
+        else:
+            c = np.ascontiguousarray(cache_rows, dtype=np.int64)
+            self._host_rows = r  # mapped in place by the library
+            N.check(N.lib().gs_features_create_cached(self.device, self.num_rows, self.dim, self.id_div,
+                                                      r.ctypes.data, c.ctypes.data, c.size, C.byref(h)))
+            self.rows_in_hbm = int(c.size)
         self._h = h
 
     def gather(self, ids):

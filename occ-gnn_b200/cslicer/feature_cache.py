@@ -1,0 +1,44 @@
+"""Which feature rows a GPU keeps in HBM.
+
+Host-side restatement of MemoryManager.initialize's policy
+(/root/reference python/utils/memory_manager.py:40-74): with a cache fraction c
+of all N nodes per GPU,
+  * c <= 1/P : the c*N highest-degree nodes of the GPU's own partition;
+  * c  > 1/P : the whole partition, then the highest-degree nodes of the rest
+               until c*N rows are held.
+The reference orders by `torch.sort(descending=True)`, which leaves the order of
+equal degrees unspecified; here ties go to the smaller node id (a stable sort),
+so the choice is deterministic.  The rows chosen feed
+`engine.Features(rows, cache_rows=...)`; nothing else of MemoryManager is needed:
+a miss is read from host memory by the gather kernel, so there is no
+refresh_cache / clean_up cycle (memory_manager.py:75-104).
+"""
+import numpy as np
+
+
+def degree_ordered_cache(indptr, fraction, owner=None, part=0, num_parts=4):
+    """-> int64 array of node ids to cache on GPU `part`, cached order = slot order.
+    owner: int array [N] (None: id % num_parts, pyfrontend.cpp:57)."""
+    if not 0.0 < fraction <= 1.0:
+        raise ValueError("cache fraction must be in (0, 1]")  # memory_manager.py:28
+    ip = np.asarray(indptr, dtype=np.int64)
+    n = ip.size - 1
+    deg = np.diff(ip)
+    own = (np.arange(n) % num_parts) if owner is None else np.asarray(owner)
+    n_cached = int(fraction * n)                      # memory_manager.py:42
+    mine = np.nonzero(own == part)[0]
+    if fraction <= 1.0 / num_parts:                   # memory_manager.py:52-56 (reference: <= .25, P = 4)
+        order = np.argsort(-deg[mine], kind="stable")
+        return mine[order[:n_cached]].astype(np.int64)
+    rest = np.nonzero(own != part)[0]                 # memory_manager.py:58-66
+    order = np.argsort(-deg[rest], kind="stable")
+    extra = rest[order[:max(0, n_cached - mine.size)]]
+    return np.concatenate([mine, extra]).astype(np.int64)
+
+
+def hit_rate(cache_ids, ids, num_nodes):
+    """Fraction of `ids` served from HBM."""
+    m = np.zeros(num_nodes, dtype=bool)
+    m[np.asarray(cache_ids, dtype=np.int64)] = True
+    ids = np.asarray(ids, dtype=np.int64)
+    return float(m[ids].mean()) if ids.size else 1.0

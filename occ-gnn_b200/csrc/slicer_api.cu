@@ -70,7 +70,11 @@ struct gs_features {
   int device = 0;
   int64_t num_rows = 0;
   int32_t dim = 0, id_div = 1;
-  float *rows = nullptr;
+  float *rows = nullptr;          // HBM: every row, or the cached rows
+  int32_t *slot_of = nullptr;     // cached store: [num_rows] slot in `rows` or -1
+  const float *host_dev = nullptr;// cached store: device alias of the caller's host table
+  void *host_reg = nullptr;       // ... the range this library page-locked (NULL: was already pinned)
+  int64_t n_cached = 0;
 };
 
 struct gs_slicer {
@@ -453,6 +457,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.tickets, 8);
     if (s->feat) {
       w.feat = s->feat->rows;
+      w.feat_slot = s->feat->slot_of;
+      w.feat_host = s->feat->host_dev;
       w.feat_dim = s->feat->dim;
       w.feat_div = s->feat->id_div;
       w.feat_rows = s->feat->num_rows;
@@ -674,10 +680,89 @@ int gs_features_create(int device, int64_t num_rows, int32_t dim, int32_t id_div
   return GS_OK;
 }
 
+// Cached store: the table stays where the caller has it, in
+// host memory, page-locked and mapped here; the rows named in cached_rows are
+// copied to HBM.  Replaces MemoryManager.initialize + refresh_cache
+// (python/utils/memory_manager.py:40-104): a miss is served by the gather
+// kernel itself over PCIe, so nothing is refreshed or undone per minibatch.
+int gs_features_create_cached(int device, int64_t num_rows, int32_t dim, int32_t id_div,
+                              const float *rows_host, const int64_t *cached_rows, int64_t n_cached,
+                              gs_features **out) {
+  if (!out || !rows_host || (n_cached > 0 && !cached_rows)) return fail(GS_ERR_INVALID, "NULL argument");
+  if (num_rows < 1 || dim < 1 || id_div < 1) return fail(GS_ERR_INVALID, "num_rows, dim, id_div must be >= 1");
+  if (n_cached < 0 || n_cached > num_rows || num_rows >= (1ll << 31))
+    return fail(GS_ERR_INVALID, "n_cached must be in [0, num_rows], num_rows < 2^31");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(GS_ERR_CUDA, "no CUDA device (%s): this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  std::vector<int32_t> slot((size_t)num_rows, -1);
+  for (int64_t k = 0; k < n_cached; k++) {
+    const int64_t r = cached_rows[k];
+    if (r < 0 || r >= num_rows) return fail(GS_ERR_INVALID, "cached_rows[%lld]=%lld outside [0,num_rows)", (long long)k, (long long)r);
+    if (slot[(size_t)r] >= 0) return fail(GS_ERR_INVALID, "cached_rows lists row %lld twice", (long long)r);
+    slot[(size_t)r] = (int32_t)k;
+  }
+  CU(cudaSetDevice(device));
+  gs_features *f = new (std::nothrow) gs_features();
+  if (!f) return fail(GS_ERR_INVALID, "out of host memory");
+  f->device = device;
+  f->num_rows = num_rows;
+  f->dim = dim;
+  f->id_div = id_div;
+  f->n_cached = n_cached;
+  const size_t row_bytes = (size_t)dim * sizeof(float);
+  auto bail = [&](cudaError_t ce, const char *what) {
+    cudaGetLastError();
+    gs_features_destroy(f);
+    return fail(GS_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(ce));
+  };
+  // page-lock + map the caller's table in place (no copy); already-pinned memory is used as it is
+  cudaError_t ce = cudaHostRegister((void *)rows_host, (size_t)num_rows * row_bytes,
+                                    cudaHostRegisterMapped | cudaHostRegisterPortable);
+  if (ce == cudaSuccess) f->host_reg = (void *)rows_host;
+  else if (ce == cudaErrorHostMemoryAlreadyRegistered) cudaGetLastError();
+  else return bail(ce, "cudaHostRegister of the feature table");
+  void *alias = nullptr;
+  if ((ce = cudaHostGetDevicePointer(&alias, (void *)rows_host, 0)) != cudaSuccess)
+    return bail(ce, "cudaHostGetDevicePointer");
+  f->host_dev = (const float *)alias;
+  if ((ce = cudaMalloc((void **)&f->slot_of, (size_t)num_rows * sizeof(int32_t))) != cudaSuccess)
+    return bail(ce, "cudaMalloc(slot map)");
+  if ((ce = cudaMemcpy(f->slot_of, slot.data(), (size_t)num_rows * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess)
+    return bail(ce, "slot map upload");
+  if ((ce = cudaMalloc((void **)&f->rows, std::max<size_t>(1, (size_t)n_cached * row_bytes))) != cudaSuccess)
+    return bail(ce, "cudaMalloc(cache rows)");
+  // upload the cached rows in runs of consecutive source rows (a degree-ordered
+  // cache of a degree-sorted graph is one run; an arbitrary set degrades to row copies)
+  for (int64_t k = 0; k < n_cached;) {
+    int64_t k1 = k + 1;
+    while (k1 < n_cached && cached_rows[k1] == cached_rows[k1 - 1] + 1) k1++;
+    ce = cudaMemcpyAsync(f->rows + (size_t)k * dim, rows_host + (size_t)cached_rows[k] * dim,
+                         (size_t)(k1 - k) * row_bytes, cudaMemcpyHostToDevice, 0);
+    if (ce != cudaSuccess) return bail(ce, "cache row upload");
+    k = k1;
+  }
+  if ((ce = cudaStreamSynchronize(0)) != cudaSuccess) return bail(ce, "cache row upload");
+  *out = f;
+  return GS_OK;
+}
+
+int gs_features_info(const gs_features *f, int64_t *num_rows, int32_t *dim, int64_t *rows_in_hbm) {
+  if (!f) return fail(GS_ERR_INVALID, "NULL argument");
+  if (num_rows) *num_rows = f->num_rows;
+  if (dim) *dim = f->dim;
+  if (rows_in_hbm) *rows_in_hbm = f->slot_of ? f->n_cached : f->num_rows;
+  return GS_OK;
+}
+
 int gs_features_destroy(gs_features *f) {
   if (!f) return GS_OK;
   cudaSetDevice(f->device);
   cudaFree(f->rows);
+  cudaFree(f->slot_of);
+  if (f->host_reg) cudaHostUnregister(f->host_reg);
   delete f;
   return GS_OK;
 }
@@ -690,8 +775,8 @@ int gs_features_gather(gs_features *f, const int32_t *ids_device, int64_t n, flo
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, f->device);
   const int grid = (int)std::min<int64_t>((n + GS_NW - 1) / GS_NW, (int64_t)sms * 8);
-  gs_launch_gather_ids(f->rows, f->dim, f->id_div, f->num_rows, ids_device, n, out_device, grid,
-                       (cudaStream_t)stream);
+  gs_launch_gather_ids(f->rows, f->slot_of, f->host_dev, f->dim, f->id_div, f->num_rows, ids_device,
+                       n, out_device, grid, (cudaStream_t)stream);
   CU(cudaGetLastError());
   return GS_OK;
 }

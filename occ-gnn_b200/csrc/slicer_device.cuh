@@ -263,6 +263,29 @@ __device__ __forceinline__ void copy_row(const float *__restrict__ src, float *_
   }
   for (; k < nvec; k += 32) d[k] = __ldg(s + k);
 }
+// Feature store with an HBM cache in front of a host-resident table (SURVEY
+// 8(f) N2; python/utils/memory_manager.py:40-104): slot_of[row] >= 0 -> the row
+// sits in HBM at that slot, else it is read in place from pinned, mapped host
+// memory over PCIe by the same warp.  slot_of == NULL: every row is in HBM.
+struct FeatSrc {
+  const float *rows;       // HBM rows (all of them, or the cached ones)
+  const int32_t *slot_of;  // [num_rows] or NULL
+  const float *host_rows;  // device alias of the host table (cached stores only)
+  __device__ __forceinline__ const float *row(int64_t r, int dim) const {
+    if (slot_of) {
+      const int32_t s = __ldg(slot_of + r);
+      return s >= 0 ? rows + (int64_t)s * dim : host_rows + r * dim;
+    }
+    return rows + r * dim;
+  }
+};
+__device__ __forceinline__ void gather_row_from(const float *src, int dim, float *out, int64_t dst_row,
+                                                int lane) {
+  float *dst = out + dst_row * dim;
+  if ((dim & 3) == 0) copy_row<float4>(src, dst, dim >> 2, lane);
+  else if ((dim & 1) == 0) copy_row<float2>(src, dst, dim >> 1, lane);
+  else copy_row<float>(src, dst, dim, lane);
+}
 __device__ __forceinline__ void gather_row(const float *feat, int dim, int64_t src_row, float *out,
                                            int64_t dst_row, int lane) {
   const float *src = feat + src_row * dim;

@@ -72,7 +72,9 @@ struct GsWs {
   uint32_t *tickets;     // [8] last-block tickets, one per spine kernel
   int32_t Fcap, Ccap, ftiles_max, ctiles_max;
   // fused input-feature gather (optional)
-  const float *feat;     // [rows][feat_dim] fp32
+  const float *feat;     // [rows][feat_dim] fp32 (cached store: the cached rows)
+  const int32_t *feat_slot; // cached store: [feat_rows] slot of every row or -1; else NULL
+  const float *feat_host;   // cached store: device alias of the host-resident table
   float *feat_out;       // per-slot feature slab [feat_cap_rows][feat_dim]
   int32_t feat_dim, feat_div;
   int64_t feat_rows, feat_cap_rows;
@@ -98,7 +100,8 @@ void gs_launch_front_apply(const GsWs &ws, int layer, int grid, cudaStream_t st)
 void gs_launch_relabel(const GsWs &ws, int layer, int grid, cudaStream_t st);
 void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st);
 void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st);
-void gs_launch_gather_ids(const float *feat, int dim, int div, int64_t rows, const int32_t *ids,
-                          int64_t n, float *out, int grid, cudaStream_t st);
+void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
+                          int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
+                          cudaStream_t st);
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st);
 void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st);

@@ -961,6 +961,9 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
 // Fused into every sample's graph: the rows of the last layer's in_nodes_g, part
 // after part -- the block of input features GPU g reads for this minibatch
 // (python/data/bipartite.py:61-67 gather, memory_manager.py:75-104 refresh).
+// With a cached store (FeatSrc) rows outside the HBM cache are read in place from
+// host memory by the same warp, so there is no per-batch refresh step and no
+// global_to_local table to patch and undo (memory_manager.py:77-104).
 __global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -986,20 +989,21 @@ __global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
   if ((int64_t)R > ws.feat_cap_rows) return;
   const int lane = lane_id();
   const int nwarps = gridDim.x * GS_NW;
+  const FeatSrc fs{ws.feat, ws.feat_slot, ws.feat_host};
   for (int r = blockIdx.x * GS_NW + warp_id(); r < R; r += nwarps) {
     int q = 0;
     while (q + 1 < P && r >= s_start[q + 1]) q++;
     const int32_t id = ws.slab[s_off[q] + (r - s_start[q])];
-    gather_row(ws.feat, ws.feat_dim, (int64_t)(id / ws.feat_div), ws.feat_out, r, lane);
+    gather_row_from(fs.row((int64_t)(id / ws.feat_div), ws.feat_dim), ws.feat_dim, ws.feat_out, r, lane);
   }
 }
 
-__global__ void __launch_bounds__(GS_TPB) k_gather_ids(const float *feat, int dim, int div,
+__global__ void __launch_bounds__(GS_TPB) k_gather_ids(FeatSrc fs, int dim, int div,
                                                        const int32_t *ids, int64_t n, float *out) {
   const int lane = lane_id();
   const int64_t nwarps = (int64_t)gridDim.x * GS_NW;
   for (int64_t r = (int64_t)blockIdx.x * GS_NW + warp_id(); r < n; r += nwarps)
-    gather_row(feat, dim, (int64_t)(ids[r] / div), out, r, lane);
+    gather_row_from(fs.row((int64_t)(ids[r] / div), dim), dim, out, r, lane);
 }
 
 __global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
@@ -1047,10 +1051,11 @@ void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st) {
 void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st) {
   k_gather_sample<<<grid, GS_TPB, 0, st>>>(ws);
 }
-void gs_launch_gather_ids(const float *feat, int dim, int div, int64_t rows, const int32_t *ids,
-                          int64_t n, float *out, int grid, cudaStream_t st) {
+void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
+                          int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
+                          cudaStream_t st) {
   (void)rows;
-  k_gather_ids<<<grid, GS_TPB, 0, st>>>(feat, dim, div, ids, n, out);
+  k_gather_ids<<<grid, GS_TPB, 0, st>>>(FeatSrc{feat, slot_of, host_rows}, dim, div, ids, n, out);
 }
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
   k_fill_u32<<<1184, 256, 0, st>>>(p, n, v);

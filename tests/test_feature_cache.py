@@ -1,0 +1,48 @@
+"""Host-side cache policy (python/utils/memory_manager.py:40-74).
+The reference's MemoryManager needs DGL and four GPUs to construct, so these are
+hand-computed expectations of its rule -- parity unpinned (see the module docstring)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "occ-gnn_b200"))
+
+from cslicer.feature_cache import degree_ordered_cache, hit_rate  # noqa: E402
+
+
+def _graph(deg):
+    return np.concatenate([[0], np.cumsum(deg)]).astype(np.int64)
+
+
+def test_small_fraction_takes_top_degree_nodes_of_own_partition():
+    deg = np.array([5, 1, 9, 3, 7, 2, 8, 4, 6, 0, 11, 10])  # N = 12, P = 4: part 2 owns 2, 6, 10
+    ip = _graph(deg)
+    got = degree_ordered_cache(ip, 2 / 12, part=2, num_parts=4)
+    assert got.tolist() == [10, 2]           # degrees 11, 9 (then 8)
+    got = degree_ordered_cache(ip, 0.25, part=2, num_parts=4)
+    assert got.tolist() == [10, 2, 6]        # exactly the partition, by degree
+    owner = np.array([0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3])
+    got = degree_ordered_cache(ip, 0.25, owner=owner, part=1, num_parts=4)
+    assert got.tolist() == [4, 3, 5]
+
+
+def test_large_fraction_is_partition_plus_top_degree_of_the_rest():
+    deg = np.array([5, 1, 9, 3, 7, 2, 8, 4, 6, 0, 11, 10])
+    ip = _graph(deg)
+    got = degree_ordered_cache(ip, 0.5, part=0, num_parts=4)  # 6 rows: own {0,4,8} + 3 best others
+    assert got.tolist() == [0, 4, 8, 10, 11, 2]
+    full = degree_ordered_cache(ip, 1.0, part=3, num_parts=4)
+    assert sorted(full.tolist()) == list(range(12))
+
+
+def test_ties_go_to_the_smaller_id_and_fraction_is_validated():
+    ip = _graph(np.full(8, 3))
+    assert degree_ordered_cache(ip, 0.25, part=1, num_parts=2).tolist() == [1, 3]
+    for bad in (0.0, -0.1, 1.5):
+        with pytest.raises(ValueError):
+            degree_ordered_cache(ip, bad)
+    assert hit_rate([1, 3], [1, 1, 2, 3], 8) == 0.75
+    assert hit_rate([], [], 8) == 1.0

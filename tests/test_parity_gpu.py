@@ -367,6 +367,53 @@ def test_fused_feature_gather_matches_numpy(dim, P, fanouts):
     small.close(); sl.close(); shard.close(); F.close(); g.close()
 
 
+@pytest.mark.parametrize("fraction,dim", [(0.1, 602), (0.4, 128), (1.0, 7)])
+def test_cached_feature_store_matches_numpy(fraction, dim):
+    """table in host memory, degree-ordered HBM cache in front
+    (python/utils/memory_manager.py:40-104).  A gather returns the same rows
+    whether a row is served from HBM or from host memory: exact equality."""
+    E = _engine()
+    import torch
+    from cslicer import _native as N
+    from cslicer.feature_cache import degree_ordered_cache, hit_rate
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=12)
+    n, P, fanouts = ip.size - 1, 4, [10, 5]
+    feat = np.random.default_rng(4321).random((n, dim), dtype=np.float32)
+    cache = degree_ordered_cache(ip, fraction, part=1, num_parts=P)
+    assert cache.size == int(fraction * n) and np.unique(cache).size == cache.size
+    F = E.Features(feat, cache_rows=cache)
+    assert F.rows_in_hbm == cache.size
+    ids = np.random.default_rng(1).integers(0, n, 20000).astype(np.int32)
+    assert np.array_equal(F.gather(torch.from_numpy(ids).cuda()).cpu().numpy(), feat[ids])
+    hr = hit_rate(cache, ids, n)
+    assert (hr == 1.0) if fraction == 1.0 else (0.0 < hr < 1.0)
+    # fused into the slicer: the block every part reads
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fanouts, P, max_batch=256, num_slots=2, seed=5, features=F)
+    orc = O.OracleSlicer(ip, ix, fanouts, P, O.RNG_PHILOX, seed=5)
+    for b in range(2):
+        seeds = np.random.default_rng(b).permutation(n)[:256]
+        v = sl.slice(seeds, b)
+        r = orc.slice(seeds, b)
+        _compare(v, r)
+        for p in range(P):
+            assert np.array_equal(v.features(p).cpu().numpy(), feat[r["layers"][-1][p]["in_nodes"]])
+        v.release()
+    sl.close()
+    # nothing cached: every row comes from host memory
+    F0 = E.Features(feat, cache_rows=np.zeros(0, np.int64))
+    assert np.array_equal(F0.gather(torch.from_numpy(ids[:3000]).cuda()).cpu().numpy(), feat[ids[:3000]])
+    F0.close()
+    for bad in ([0, 0], [n], [-1]):
+        with pytest.raises(N.SlicerError) as e:
+            E.Features(feat, cache_rows=np.array(bad))
+        assert e.value.code == N.ERR_INVALID
+    with pytest.raises(ValueError):
+        E.Features(feat.astype(np.float64), cache_rows=cache)
+    F.close(); g.close()
+
+
 def test_reference_facing_module_end_to_end(tmp_path):
     """cslicer/test_py.py's loop, verbatim in shape, against the golden hashes:
     the module's own epoch shuffle + replayed draws reproduce the reference's
