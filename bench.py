@@ -379,7 +379,7 @@ def own_arm(args):
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(ip, ix, P, batches, args)
             try:
-                out["feature_gather"] = feature_gather_line(ip, g, args, torch, batches, peak)
+                out["feature_gather"] = feature_gather_line(ip, ix, g, args, torch, batches, peak)
             except Exception as e:
                 out["feature_gather"] = {"unavailable": f"{type(e).__name__}: {e}"}
             try:
@@ -537,7 +537,7 @@ def reference_config(ip, ix, g, args, torch):
             "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
 
 
-def feature_gather_line(ip, g, args, torch, batches, peak):
+def feature_gather_line(ip, ix, g, args, torch, batches, peak):
     """BASELINE config 4's other half: the fused input-feature gather (602-dim
     fp32, seed 4321) -- rows of the last layer's in_nodes_g, part after part,
     appended to every sample's CUDA graph.  HBM-bound: whole 2408-byte rows."""
@@ -562,7 +562,7 @@ def feature_gather_line(ip, g, args, torch, batches, peak):
     nbytes = 2 * nrows * dim * 4
     sl.close()
     F.close()
-    cached = cached_gather(ip, g, args, rows, batches)
+    cached = cached_gather(ip, ix, g, args, rows, batches)
     del rows
     return {"dim": dim, "cached_store": cached, "rows_per_minibatch": int(nrows), "bytes_per_minibatch": int(nbytes),
             "kernel_ms": round(k_ms, 4), "achieved_gbs": round(nbytes / (k_ms * 1e-3) / 1e9, 1),
@@ -572,14 +572,14 @@ def feature_gather_line(ip, g, args, torch, batches, peak):
                     "pipelined on 3 slots"}
 
 
-def cached_gather(ip, g, args, rows, batches, fraction=0.25):
+def cached_gather(ip, ix, g, args, rows, batches, fraction=0.25):
     """the same fused gather with the table left in host memory and
     the `fraction` highest-degree nodes cached in HBM (memory_manager.py:40-74); a
     miss is read from pinned host memory by the gather warp itself (PCIe-bound)."""
     from cslicer.engine import Features, Slicer
     from cslicer.feature_cache import degree_ordered_cache, hit_rate
     try:
-        cache = degree_ordered_cache(ip, fraction, part=0, num_parts=1)
+        cache = degree_ordered_cache(ip, fraction, part=0, num_parts=1, indices=ix)
         F = Features(rows, cache_rows=cache)
         sl = Slicer(g, FANOUTS, num_parts=args.parts, max_batch=BATCH, num_slots=2, num_streams=2, seed=7,
                     grid_ctas=args.grid_ctas, host_output=False, features=F)
@@ -593,7 +593,7 @@ def cached_gather(ip, g, args, rows, batches, fraction=0.25):
         miss_bytes = (1.0 - hr) * ids.size * rows.shape[1] * 4
         sl.close()
         F.close()
-        return {"cache_fraction": fraction, "policy": "highest degree first", "rows_in_hbm": int(cache.size),
+        return {"cache_fraction": fraction, "policy": "highest source degree first (synthetic sources are uniform: weak skew)", "rows_in_hbm": int(cache.size),
                 "hit_rate": round(hr, 4), "kernel_ms": round(k_ms, 3),
                 "host_read_gbs": round(miss_bytes / (k_ms * 1e-3) / 1e9, 1),
                 "note": "misses are zero-copy reads of pinned host rows inside the gather kernel"}

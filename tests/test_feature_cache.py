@@ -46,3 +46,10 @@ def test_ties_go_to_the_smaller_id_and_fraction_is_validated():
             degree_ordered_cache(ip, bad)
     assert hit_rate([1, 3], [1, 1, 2, 3], 8) == 0.75
     assert hit_rate([], [], 8) == 1.0
+
+
+def test_source_degree_ranking_uses_the_neighbour_array():
+    ip = _graph(np.array([2, 2, 2, 0]))
+    ix = np.array([3, 3, 3, 0, 3, 1])          # node 3 is the most frequent source, then 0 / 1
+    got = degree_ordered_cache(ip, 0.5, part=0, num_parts=1, indices=ix)
+    assert got.tolist() == [3, 0]
