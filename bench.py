@@ -267,7 +267,10 @@ def own_arm(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dist = None
+    bound = None
     if world > 1:
+        from cslicer.sharding import bind_to_gpu_cpus
+        bound = bind_to_gpu_cpus(local)  # pinned sample mirrors land on the GPU's NUMA node
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     import ctypes
@@ -283,7 +286,7 @@ def own_arm(args):
     kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
               grid_ctas=args.grid_ctas)
     dev = Slicer(g, FANOUTS, host_output=False, **kw)
-    hst = Slicer(g, FANOUTS, host_output=True, **kw)
+    hst = Slicer(g, FANOUTS, host_output=True, host_copy_engine=not args.host_stores, **kw)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -364,6 +367,7 @@ def own_arm(args):
                                       f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
                           "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
                           "sharding": "whole minibatches per rank, graph topology replicated",
+                          "cpu_binding": (f"rank 0 on {len(bound)} cores next to its GPU" if bound else "none"),
                           "l2": "inputs larger than L2: graph 0.27 GB + per-slot tables/workspaces "
                                 f"{dev.slot_bytes * args.slots / 1e9:.2f} GB cycled every step",
                           "sizes_of_one_minibatch": sizes},
@@ -673,6 +677,8 @@ def main():
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--host-stores", action="store_true",
+                    help="e2e: mirror samples with stores from the last kernel instead of the copy engine")
     ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
     ap.add_argument("--no-partitioned", action="store_true",
                     help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")

@@ -63,7 +63,7 @@ class Config(C.Structure):
                 ("num_slots", C.c_int32), ("num_streams", C.c_int32), ("host_output", C.c_int32),
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
                 ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32),
-                ("l2_hints", C.c_int32), ("reserved0", C.c_int32),
+                ("l2_hints", C.c_int32), ("host_copy_engine", C.c_int32),
                 ("features", C.c_void_p), ("feature_rows_capacity", C.c_int64)]
 
 

@@ -235,7 +235,7 @@ class Slicer:
     def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
                  seed=0, owner=None, draws=None, host_output=True, use_graph=True,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True,
-                 features=None, feature_rows_capacity=0, replace=True):
+                 features=None, feature_rows_capacity=0, replace=True, host_copy_engine=True):
         """replace=False: the picks of a row are distinct (GS_RNG_PHILOX_NOREPLACE,
         the Python sibling's DGL sampling rule, python/utils/sampler.py:187)."""
         L = N.lib()
@@ -256,6 +256,7 @@ class Slicer:
         cfg.frontier_capacity, cfg.cand_capacity = int(frontier_capacity), int(cand_capacity)
         cfg.slab_capacity, cfg.grid_ctas = int(slab_capacity), int(grid_ctas)
         cfg.l2_hints = int(bool(l2_hints))
+        cfg.host_copy_engine = int(bool(host_copy_engine))
         self.features = features
         if features is not None:
             cfg.features = features._h

@@ -32,3 +32,33 @@ def reduce_job(dist, device, elapsed_ms, counters):
     c = torch.tensor([int(x) for x in counters], dtype=torch.int64, device=device)
     dist.all_reduce(c, op=dist.ReduceOp.SUM)
     return float(t[0]), [int(x) for x in c.tolist()]
+
+
+def bind_to_gpu_cpus(device):
+    """Pin this process to the CPU cores next to GPU `device` (NVML's ideal-CPU
+    mask) so the pinned sample mirrors it allocates afterwards -- first-touch
+    pages -- land on the NUMA node the GPU's PCIe root hangs off.  With one
+    process per GPU every rank writes 40-55 GB/s into host memory; without this
+    all eight ranks share one node's memory controllers.  Returns the CPU list,
+    or None when NVML / affinity is unavailable (never fatal)."""
+    import os
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        # honour CUDA_VISIBLE_DEVICES: look the device up by PCI bus id, not by index
+        bus = torch.cuda.get_device_properties(device).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(device), "pci_domain_id", 0)
+        dev_id = getattr(torch.cuda.get_device_properties(device), "pci_device_id", 0)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(f"{dom:08x}:{bus:02x}:{dev_id:02x}.0".encode())
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None

@@ -169,8 +169,18 @@ def test_graph_and_eager_paths_agree_and_device_views_match_host():
             for name in ("in_nodes", "csr_indices", "to_ids"):
                 assert np.array_equal(va.tensor(l, p, name).cpu().numpy(), va.numpy(l, p, name))
     assert torch.equal(va.frontier_tensor(3).cpu(), torch.from_numpy(va.frontier_numpy(3).copy()))
-    prof = b.profile(seeds, 0) if False else None  # slot 0 of b is still held by vb
     va.release(); vb.release()
+    # host mirror: copy engine (default; size estimated from earlier samples, remainder topped
+    # up in wait) against stores from the last kernel -- growing, shrinking and growing batches
+    c = E.Slicer(g, [15, 10, 5], 4, max_batch=512, num_slots=3, seed=3, host_copy_engine=False)
+    for bi, nb in enumerate([64, 512, 8, 300, 512, 1]):
+        sb = np.random.default_rng(bi).permutation(ip.size - 1)[:nb]
+        v1, v2 = a.slice(sb, bi), c.slice(sb, bi)
+        assert refstream.digest_view(v1) == refstream.digest_view(v2)
+        for name in ("out_nodes", "csr_indices", "self_ids_in"):
+            assert np.array_equal(v1.tensor(2, 3, name).cpu().numpy(), v1.numpy(2, 3, name))
+        v1.release(); v2.release()
+    c.close()
     prof = b.profile(seeds, 0)
     assert len(prof) == b.launches_per_sample and all(ms >= 0 for _, ms in prof)
     a.close(); b.close(); g.close()
