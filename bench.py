@@ -260,6 +260,13 @@ def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
     return n * 3 / (e0.elapsed_time(e1) * 1e-3)
 
 
+# One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.96 MB read +
+# 2.85 MB written to DRAM (cold L2; the 12 MB candidate stream it writes stays in L2) against
+# 35.9 MB algorithmic -- the excess is 32-byte sectors moved for 4-byte neighbour picks.
+NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "expand@2", "bytes": 88812800,
+               "source": "profiles/r1_ncu_expand_full_raw.csv (ncu --set full, tools/capture_evidence.sh)"}
+
+
 def own_arm(args):
     import torch
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
@@ -346,6 +353,11 @@ def own_arm(args):
                                     "achieved_gbs": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9, 2),
                                     "frac": round(kbytes.get(top, 0) / (top_ms * 1e-3) / 1e9 / peak, 4)},
                 "kernels_ms": {k: round(ms, 4) for k, ms in prof}}
+        # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, one launch, from the
+        # committed `ncu --set full` capture (valid for the default workload only)
+        if (args.shape, FANOUTS, BATCH, P) == NCU_TRAFFIC["workload"] and top == NCU_TRAFFIC["kernel"]:
+            roof["traffic"] = NCU_TRAFFIC["bytes"]
+            roof["traffic_source"] = NCU_TRAFFIC["source"]
         # what the path is really bound by: random sector accesses, not streamed bytes
         g_csr = gather_yardstick(torch, ix.size, torch.int32)
         g_tab = gather_yardstick(torch, n * args.slots, torch.int32)
