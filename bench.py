@@ -419,7 +419,7 @@ def own_arm(args):
         emit(out)
 
 
-def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32):
+def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32, shard=None):
     """SURVEY 8(e) layout at N > 1: graph rows sharded by owner (rank g holds
     N/P of the CSR and of the dedup table), all ranks cooperate on EVERY
     minibatch and rank g produces part g; edges and new frontier nodes move by
@@ -428,12 +428,17 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     is the throughput mode.  -> dict for the bench line (rank 0), None elsewhere."""
     from cslicer.partitioned import PartitionedPipeline, partition_csr
     from cslicer.sharding import reduce_job
-    n = ip.size - 1
-    lip, lix = partition_csr(ip, ix, world)[rank]
+    okw = {}
+    if shard is None:
+        n, m_global = ip.size - 1, ix.size
+        lip, lix = partition_csr(ip, ix, world)[rank]
+    else:  # this rank's rows only (contiguous-range owner map); the full graph is nowhere on the host
+        lip, lix, n, m_global, bounds = shard
+        okw = dict(owner_mode="range", bounds=bounds)
     lanes, depth = args.lanes, 2 * args.lanes
     ps = PartitionedPipeline(lip, lix, n, rank, world, FANOUTS, dist, lanes=lanes, device=local,
                              max_batch=BATCH, num_slots=2, seed=7, host_output=False,
-                             num_edges_global=ix.size, grid_ctas=args.grid_ctas, timeout_ms=2000)
+                             num_edges_global=m_global, grid_ctas=args.grid_ctas, timeout_ms=2000, **okw)
     batches = seed_batches(n, 64, 0, 1)  # every rank is given the same batches
 
     def run(k):
@@ -463,6 +468,12 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     v = ps.slice(batches[0][1], batches[0][0])
     fr = list(v.frontier_len)
     v.release()
+    # every rank must hold the same replicated frontier sizes (a cheap cross-rank invariant)
+    t = torch.tensor(fr, dtype=torch.int64, device=f"cuda:{local}")
+    tmax, tmin = t.clone(), t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+    assert torch.equal(tmax, tmin), "ranks disagree on the frontier sizes"
     out = None
     if rank == 0:
         per_mb = ms / (steps * mbs)
@@ -472,6 +483,8 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
                "ms_per_minibatch": round(per_mb, 4), "sampled_edges_per_s": round(edges / (ms * 1e-3), 1),
                "ranks": world, "parts": world, "lanes_per_rank": lanes, "launches_per_minibatch_per_rank": ps.launches_per_sample,
                "barriers_per_minibatch": 3 * len(FANOUTS) + 1,
+               "owner_map": "contiguous ranges" if shard is not None else "id % ranks",
+               "frontier_sizes": [int(x) for x in fr],
                "device_bytes_per_rank": int(ps.device_bytes),
                "graph_shard_bytes_per_rank": int(lip.size * 8 + lix.size * 4),
                "nvlink_bytes_per_minibatch_est": int(xbytes),
@@ -482,6 +495,41 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     dist.barrier()
     ps.close()
     return out
+
+
+def partitioned_shards_arm(args):
+    """`--partitioned-shards` (N > 1 only): the partitioned slicer on a graph that is
+    generated shard by shard -- every rank replays the seeded generator on its GPU
+    and keeps only the rows it owns, so a papers100M-shaped graph (BASELINE config 5,
+    8 parts) never exists whole on the host.  Prints one JSON line (evidence for
+    SURVEY 8(e); not the contract line)."""
+    import torch
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world > 1, "--partitioned-shards needs torchrun with N > 1"
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    from cslicer.partitioned import range_bounds
+    from cslicer.synth import SHAPES, synth_graph
+    n = SHAPES[args.shape][0]
+    bounds = range_bounds(n, world)
+    t = time.time()
+    lip, lix, n, m = synth_graph(args.shape, seed=GRAPH_SEED, device=f"cuda:{local}",
+                                 rows=(int(bounds[rank]), int(bounds[rank + 1])))
+    torch.cuda.empty_cache()
+    log(f"[bench] rank {rank}: rows {bounds[rank]}..{bounds[rank + 1]} of {args.shape} "
+        f"(N={n} M={m}; local edges {lix.size}) in {time.time() - t:.1f}s")
+    out = partitioned_line(args, torch, dist, None, None, local, rank, world,
+                           shard=(lip, lix, n, m, bounds))
+    if rank == 0:
+        out = {"metric": "sliced minibatches/s (partitioned mode)", "n_gpus": world, "data": "synthetic",
+               "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={m} seed {GRAPH_SEED}; "
+                                      f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {world} parts = ranks"},
+               **out}
+        print(json.dumps(out), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
 
 
 def host_cores():
@@ -692,6 +740,8 @@ def main():
     ap.add_argument("--host-stores", action="store_true",
                     help="e2e: mirror samples with stores from the last kernel instead of the copy engine")
     ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
+    ap.add_argument("--partitioned-shards", action="store_true",
+                    help="N > 1: only the partitioned slicer, graph generated shard by shard (config 5 at scale)")
     ap.add_argument("--no-partitioned", action="store_true",
                     help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")
     args = ap.parse_args()
@@ -700,6 +750,8 @@ def main():
     capture_stdout()
     if args.impl == "reference":
         reference_arm(args)
+    elif args.partitioned_shards:
+        partitioned_shards_arm(args)
     else:
         own_arm(args)
 

@@ -32,8 +32,13 @@ def power_law_degrees(num_nodes, mean_degree, alpha, gen, device, cap=None):
 
 
 def synth_graph(shape="tiny", seed=1234, device="cpu", num_nodes=None, num_edges=None,
-                alpha=None, max_degree=None, chunk=1 << 27):
-    """-> (indptr int64[N+1], indices int64[M]) as numpy arrays on the host."""
+                alpha=None, max_degree=None, chunk=1 << 27, rows=None):
+    """-> (indptr int64[N+1], indices int64[M]) as numpy arrays on the host.
+
+    rows=(lo, hi): keep only the rows lo <= r < hi of the SAME graph (the generator
+    is replayed in full on `device`, only that shard reaches the host) ->
+    (indptr_local int64[hi-lo+1], indices_local int64[m_local], num_nodes, num_edges_global);
+    the shard a rank of the partitioned slicer holds under a contiguous-range owner map."""
     if isinstance(shape, str):
         n0, m0, a0 = SHAPES[shape]
     else:
@@ -49,6 +54,7 @@ def synth_graph(shape="tiny", seed=1234, device="cpu", num_nodes=None, num_edges
     row_end = torch.cumsum(deg, 0)
     out_deg = torch.zeros(n, dtype=torch.int64, device=dev)
     pieces = []
+    shard = None if rows is None else (int(rows[0]), int(rows[1]))
     r0 = 0
     while r0 < n:
         base = int(row_end[r0 - 1]) if r0 else 0
@@ -61,9 +67,19 @@ def synth_graph(shape="tiny", seed=1234, device="cpu", num_nodes=None, num_edges
         key = (rows[keep] * n + dst[keep]).unique()  # sorted by (row, dst), duplicates dropped
         rows_u = torch.div(key, n, rounding_mode="floor")
         out_deg[r0:r1] = torch.bincount(rows_u - r0, minlength=r1 - r0)
-        pieces.append((key - rows_u * n).cpu())
-        del rows, dst, keep, key, rows_u
+        nbr = key - rows_u * n
+        if shard is not None:
+            nbr = nbr[(rows_u >= shard[0]) & (rows_u < shard[1])]
+        if nbr.numel() or shard is None:
+            pieces.append(nbr.cpu())
+        del rows, dst, keep, key, rows_u, nbr
         r0 = r1
+    if shard is not None:
+        lo, hi = shard
+        ip = torch.zeros(hi - lo + 1, dtype=torch.int64)
+        ip[1:] = torch.cumsum(out_deg[lo:hi].cpu(), 0)
+        ix = torch.cat(pieces) if pieces else torch.zeros(0, dtype=torch.int64)
+        return ip.numpy(), ix.numpy(), n, int(out_deg.sum())
     indptr = torch.zeros(n + 1, dtype=torch.int64)
     indptr[1:] = torch.cumsum(out_deg.cpu(), 0)
     indices = torch.cat(pieces) if len(pieces) > 1 else pieces[0]

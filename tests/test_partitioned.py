@@ -87,6 +87,21 @@ def _compare_rank(view, orc, g, check_frontiers=True, owner=None):
     assert view.edges == sum(orc["layers"][l][g]["csr_indices"].size for l in range(L))
 
 
+def test_shard_generation_equals_rows_of_the_whole_graph():
+    """synth_graph(rows=...) replays the generator and keeps one rank's rows: the
+    shards of a contiguous-range owner map concatenate to the whole graph."""
+    from cslicer.partitioned import partition_csr, range_bounds
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=3, chunk=50000)
+    n, P = ip.size - 1, 3
+    b = range_bounds(n, P)
+    whole = partition_csr(ip, ix, P, "range", b)
+    for g in range(P):
+        lip, lix, nn, m = synth_graph("small", seed=3, chunk=50000, rows=(b[g], b[g + 1]))
+        assert (nn, m) == (n, ix.size)
+        assert np.array_equal(lip, whole[g][0]) and np.array_equal(lix, whole[g][1])
+
+
 CASES = [
     # (fanouts, parts, owner, batch, graph)
     ([10, 10, 10], 4, "mod", 256, "tiny"),
