@@ -258,7 +258,7 @@ typedef struct {
   int64_t frontier_capacity;               /* 0 = derive; must agree on all ranks */
   int64_t cand_capacity;
   int64_t slab_capacity;
-  int64_t num_edges_global;                /* bounds fanout -1 layers; 0 = unknown */
+  int64_t num_edges_global;                /* upper bound of the edge count: bounds fanout -1 layers; 0 = unknown */
   void *stream;                            /* cudaStream_t to run on; NULL = own stream */
   const float *features_local_host;        /* optional [n_local x feature_dim] fp32: rows of the owned nodes, local order */
   int32_t feature_dim;

@@ -330,7 +330,7 @@ class LocalGroup:
                                         bounds=bounds, device=device, max_batch=max_batch,
                                         num_slots=num_slots, seed=seed, host_output=host_output,
                                         stream=self._stream.cuda_stream,
-                                        num_edges_global=len(indices), **kw)
+                                        num_edges_global=max(1, len(indices)), **kw)
                       for g, (ip, ix) in enumerate(shards)]
         for a in self.ranks:
             for b in self.ranks:
