@@ -114,3 +114,33 @@ def test_partitioned_slicer_random_case(case):
             _compare_rank(v, want, q, owner=own)
             v.release()
     grp.close()
+
+
+def test_limits_eight_layers_eight_parts_and_widest_fanout():
+    """GS_MAX_LAYERS = 8 layers x GS_MAX_PARTS = 8 parts, and the widest accepted fanout
+    (1023) on rows both shorter and longer than it, with and without replacement."""
+    from cslicer import engine as E
+    from cslicer import _native as N
+    from __graft_entry__ import compare_sample
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=2, max_degree=3000)
+    n = ip.size - 1
+    assert int(np.diff(ip).max()) > 1023
+    g = E.Graph(ip, ix)
+    for fan, P, batch, replace in [([2] * 8, 8, 64, True), ([1023], 8, 256, True),
+                                   ([1023, 2], 3, 128, False)]:
+        sl = E.Slicer(g, fan, P, max_batch=batch, num_slots=2, seed=11, replace=replace)
+        orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX if replace else O.RNG_PHILOX_NOREPLACE, seed=11)
+        hubs = np.argsort(-np.diff(ip))[:batch // 2]          # the longest rows are in the batch
+        rest = np.setdiff1d(np.random.default_rng(3).permutation(n)[:batch], hubs)[:batch - hubs.size]
+        seeds = np.concatenate([hubs, rest])
+        v = sl.slice(seeds, 0)
+        compare_sample(v, orc.slice(seeds, 0))
+        v.release()
+        sl.close()
+    for bad in ([1024], [0], [-2], [2] * 9):
+        with pytest.raises((N.SlicerError, ValueError, IndexError)):
+            E.Slicer(g, bad, 4, max_batch=8)
+    with pytest.raises(N.SlicerError):
+        E.Slicer(g, [2], 9, max_batch=8)
+    g.close()
