@@ -380,7 +380,7 @@ def own_arm(args):
                           "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
                           "sharding": "whole minibatches per rank, graph topology replicated",
                           "cpu_binding": (f"rank 0 on {len(bound)} cores next to its GPU" if bound else "none"),
-                          "l2": "inputs larger than L2: graph 0.27 GB + per-slot tables/workspaces "
+                          "l2": f"inputs larger than L2: graph {(ip.size * 8 + ix.size * 4) / 1e9:.2f} GB + per-slot tables/workspaces "
                                 f"{dev.slot_bytes * args.slots / 1e9:.2f} GB cycled every step",
                           "sizes_of_one_minibatch": sizes},
                "sampled_edges_per_s": round(edges_dev / (ms_dev * 1e-3), 1),
