@@ -405,6 +405,10 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
   w.seed_lo = (uint32_t)cfg->seed;
   w.seed_hi = (uint32_t)(cfg->seed >> 32);
   w.rng_mode = cfg->rng_mode;
+  w.pmask = (P & (P - 1)) == 0 ? P - 1 : -1;
+  w.pshift = 0;
+  while ((1 << w.pshift) < P) w.pshift++;
+  w.pmagic = (uint32_t)((0x100000000ull + (uint64_t)P - 1) / (uint64_t)P);
   w.me = s->me;
   w.Fcap = (int32_t)s->Fcap;
   w.Ccap = (int32_t)s->Ccap;

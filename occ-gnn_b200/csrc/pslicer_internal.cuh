@@ -49,6 +49,8 @@ struct PsWs {
   int32_t n_local;
   int32_t P, L, rank;
   int32_t owner_mode;
+  int32_t pmask, pshift;  // PS_OWNER_MOD, P a power of two: id & pmask, id >> pshift (else pmask = -1)
+  uint32_t pmagic;        // ceil(2^32 / P): id / P by multiply-high + one correction step
   int32_t bounds[GS_MAX_PARTS + 1];  // PS_OWNER_RANGE
   int32_t fanouts[GS_MAX_LAYERS];
   uint32_t seed_lo, seed_hi;

@@ -12,15 +12,40 @@
 
 namespace {
 
+// id / P and id % P without integer division on the hot path: shift / mask when
+// P is a power of two, else multiply-high by ceil(2^32/P) (quotient exact or one
+// too large for any 31-bit id) and one correction step.
+__device__ __forceinline__ void ps_divmod(const PsWs &ws, int32_t v, int32_t &q, int32_t &r) {
+  if (ws.pmask >= 0) {
+    q = v >> ws.pshift;
+    r = v & ws.pmask;
+    return;
+  }
+  q = (int32_t)__umulhi((uint32_t)v, ws.pmagic);
+  r = v - q * ws.P;
+  if (r < 0) {
+    r += ws.P;
+    q--;
+  }
+}
 __device__ __forceinline__ int ps_owner(const PsWs &ws, int32_t v) {
-  if (ws.owner_mode == PS_OWNER_MOD) return (int)((uint32_t)v % (uint32_t)ws.P);
+  if (ws.owner_mode == PS_OWNER_MOD) {
+    int32_t q, r;
+    ps_divmod(ws, v, q, r);
+    return r;
+  }
   int q = 0;
   while (q + 1 < ws.P && v >= ws.bounds[q + 1]) q++;
   return q;
 }
 // index of node v in its owner's local arrays (CSR shard rows, dedup table)
 __device__ __forceinline__ int32_t ps_local(const PsWs &ws, int32_t v, int q) {
-  return ws.owner_mode == PS_OWNER_MOD ? (int32_t)((uint32_t)v / (uint32_t)ws.P) : v - ws.bounds[q];
+  if (ws.owner_mode == PS_OWNER_MOD) {
+    int32_t d, r;
+    ps_divmod(ws, v, d, r);
+    return d;
+  }
+  return v - ws.bounds[q];
 }
 // candidates row `nd` (owned by this rank) contributes under fanout `fan`:
 // 1 + (deg < fan or fan < 0 ? deg : fan)   (slicer.cpp:6-22)

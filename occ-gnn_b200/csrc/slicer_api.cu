@@ -419,6 +419,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.owner = s->owner;
     w.num_nodes = (int32_t)N;
     w.P = cfg->num_parts;
+    w.pmask = (cfg->num_parts & (cfg->num_parts - 1)) == 0 ? cfg->num_parts - 1 : -1;
+    w.pmagic = (uint32_t)((0x100000000ull + (uint64_t)cfg->num_parts - 1) / (uint64_t)cfg->num_parts);
     w.L = cfg->num_layers;
     for (int l = 0; l < GS_MAX_LAYERS; l++) w.fanouts[l] = cfg->fanouts[l];
     w.rng_mode = cfg->rng_mode;

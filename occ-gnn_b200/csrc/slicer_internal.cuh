@@ -37,6 +37,8 @@ struct GsWs {
   const uint8_t *owner;   // [N] or nullptr -> id % P
   int32_t num_nodes;
   int32_t P, L;
+  int32_t pmask;     // P - 1 when P is a power of two, else -1
+  uint32_t pmagic;   // ceil(2^32 / P): id / P by multiply-high (+ one correction step)
   int32_t fanouts[GS_MAX_LAYERS];
   // rng
   int32_t rng_mode;

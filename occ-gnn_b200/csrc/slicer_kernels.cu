@@ -66,8 +66,14 @@ __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, ui
 // rowscan is stored part-major ([q][Fcap+1]) so that consecutive rows are contiguous
 __device__ __forceinline__ size_t rs_at(const GsWs &ws, int q, int i) { return (size_t)q * ((size_t)ws.Fcap + 1) + (size_t)i; }
 
+// owner = id % P (pyfrontend.cpp:57) without a hardware-unsupported modulo on the
+// hot path: a mask when P is a power of two, else multiply-high by ceil(2^32/P)
+// (quotient exact or one too large for any 31-bit id) and one correction.
 __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
-  return ws.owner ? (int)__ldg(ws.owner + v) : (int)((uint32_t)v % (uint32_t)ws.P);
+  if (ws.owner) return (int)__ldg(ws.owner + v);
+  if (ws.pmask >= 0) return (int)(v & ws.pmask);
+  int32_t r = v - (int32_t)(__umulhi((uint32_t)v, ws.pmagic) * (uint32_t)ws.P);
+  return r < 0 ? r + ws.P : r;
 }
 
 // ------------------------------------------------------------------ k_begin
@@ -409,6 +415,11 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
   const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles per CTA (cta_tiles)
+  // tile / per by multiply-high: exact while tile * per < 2^32 (ntiles <= 65536)
+  const bool per_inv_ok = per > 1 && ntiles <= 65536;
+  const uint32_t per_inv = per_inv_ok ? (uint32_t)((0x100000000ull + (uint32_t)per - 1) / (uint32_t)per) : 0u;
+  // running class counts of this warp over the CTA's tiles: lane q < P keeps part q
+  uint32_t acc_i = 0u, acc_e = 0u, acc_f = 0u;
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
   int t0, t1;
@@ -456,7 +467,9 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
         const bool ffirst = a > p;
         if (ffirst && a != GS_INF) {  // revoke the claim of the edge candidate at a
           ws.kill[a] = 1;
-          atomicSub(&ws.ctile_cnt[min((int)(a / GS_TILE) / per, (int)gridDim.x - 1)], 1u);
+          const uint32_t ta = a / GS_TILE;
+          const int cta = per == 1 ? (int)ta : (per_inv_ok ? (int)__umulhi(ta, per_inv) : (int)ta / per);
+          atomicSub(&ws.ctile_cnt[min(cta, (int)gridDim.x - 1)], 1u);
         }
         n_ff += ffirst ? 1u : 0u;
         fl[k] = GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u);
@@ -490,15 +503,16 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
     pk_e = pk_warp_sum(pk_e);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) n_ff += __shfl_xor_sync(FULL, n_ff, d);
-    if (lane_id() == 0) {
-      if (n_ff) atomicAdd(&s_cnt[0], n_ff);
-      for (int q = 0; q < P; q++) {
-        const uint32_t a = pk_get(pk_i, q), b = pk_get(pk_e, q);
-        if (a) atomicAdd(&s_cnt[1 + q], a);
-        if (b) atomicAdd(&s_cnt[1 + P + q], b);
-      }
-    }
+    // every lane holds the warp totals: lane q keeps the running count of part q
+    acc_i += pk_get(pk_i, lane_id() & 7);
+    acc_e += pk_get(pk_e, lane_id() & 7);
+    acc_f += n_ff;
   }
+  if (lane_id() < P) {
+    if (acc_i) atomicAdd(&s_cnt[1 + lane_id()], acc_i);
+    if (acc_e) atomicAdd(&s_cnt[1 + P + lane_id()], acc_e);
+  }
+  if (lane_id() == 0 && acc_f) atomicAdd(&s_cnt[0], acc_f);
   __syncthreads();
   if (threadIdx.x == 0) atomicAdd(&ws.ctile_cnt[blockIdx.x], s_cnt[0]);  // zeroed by k_rows_scan; peers subtract
   else if (threadIdx.x < NC) ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x] = s_cnt[threadIdx.x];
@@ -546,8 +560,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
   // The kernels of this pipeline are bound by instruction issue, not by memory:
   // per-part ranks come from two packed warp scans (one byte per part) instead
   // of 2P ballot/popc pairs per round.
-  __shared__ unsigned long long s_wi[GS_NW], s_we[GS_NW];  // per-warp packed class totals of the tile
-  __shared__ uint32_t s_wf[GS_NW];
+  __shared__ uint32_t s_wc[GS_NW][GS_NC_MAX];  // per-warp class totals of the tile
   __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
   __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
   __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
@@ -612,22 +625,25 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
     // exclusive packed prefixes over the warp's lanes; lane 31 publishes the totals
     const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe);
     const uint32_t inc_f = warp_incl_scan(nf);
-    if (lane == 31) {
-      s_wi[w] = inc_i;
-      s_we[w] = inc_e;
-      s_wf[w] = inc_f;
+    {  // lane = class: unpack this warp's totals (held by lane 31) once, one word per class
+      const unsigned long long tot_i = __shfl_sync(FULL, inc_i, 31), tot_e = __shfl_sync(FULL, inc_e, 31);
+      const uint32_t tot_f = __shfl_sync(FULL, inc_f, 31);
+      if (lane < NC)
+        s_wc[w][lane] = lane == 0 ? tot_f : (lane <= P ? pk_get(tot_i, lane - 1) : pk_get(tot_e, lane - 1 - P));
     }
     __syncthreads();
-    if (lane < NC) {  // lane = class: this warp's base, and (warp 0) the next tile's running counts
+    if (lane < NC) {  // this warp's base = running counts + earlier warps; warp 0 also advances the running counts
       const int cc = lane;
-      uint32_t a = s_run[t & 1][cc], all = 0u;
-      for (int k = 0; k < GS_NW; k++) {
-        const uint32_t c = cc == 0 ? s_wf[k] : (cc <= P ? pk_get(s_wi[k], cc - 1) : pk_get(s_we[k], cc - 1 - P));
-        if (k < w) a += c;
-        all += c;
+      uint32_t a = s_run[t & 1][cc];
+      if (w == 0) {
+        uint32_t all = 0u;
+#pragma unroll
+        for (int k = 0; k < GS_NW; k++) all += s_wc[k][cc];
+        s_run[(t + 1) & 1][cc] = a + all;
+      } else {
+        for (int k = 0; k < w; k++) a += s_wc[k][cc];
       }
       s_base[w][cc] = a;
-      if (w == 0) s_run[(t + 1) & 1][cc] = s_run[t & 1][cc] + all;
     }
     __syncwarp();
     uint32_t rf = s_base[w][0] + inc_f - nf;
