@@ -692,10 +692,11 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
 // self_g0 = always (slicer.cpp:33-34).  from_g = out_g && g != g0 needs no
 // counter: its rank is rank(out_g) - rank(owned_g).
 // bit q of a mask -> byte q of a packed counter word
-__device__ __forceinline__ unsigned long long pk_spread(uint32_t mask, int P) {
-  unsigned long long v = 0ull;
-  for (int q = 0; q < P; q++) v |= (unsigned long long)((mask >> q) & 1u) << (8 * q);
-  return v;
+// (multiply replicates the mask byte into all eight bytes, the AND keeps bit q in
+// byte q, + 0x7F carries any kept bit into bit 7 of its byte)
+__device__ __forceinline__ unsigned long long pk_spread(uint32_t mask, int /*P*/) {
+  const unsigned long long v = ((unsigned long long)(mask & 0xFFu) * 0x0101010101010101ull) & 0x8040201008040201ull;
+  return ((v + 0x7F7F7F7F7F7F7F7Full) >> 7) & 0x0101010101010101ull;
 }
 
 __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
@@ -710,6 +711,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
   if (threadIdx.x < GS_NF_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
+  uint32_t acc_out = 0u, acc_own = 0u, acc_to = 0u, acc_self = 0u;  // lane q < P: this warp's counts of part q
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
   for (int t = t0; t < t1; t++) {
@@ -754,14 +756,19 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
     p_own = pk_warp_sum(p_own);
     p_to = pk_warp_sum(p_to);
     p_self = pk_warp_sum(p_self);
-    if (lane_id() == 0)
-      for (int q = 0; q < P; q++) {
-        const uint32_t a = pk_get(p_out, q), b = pk_get(p_own, q), c = pk_get(p_to, q), d = pk_get(p_self, q);
-        if (a) atomicAdd(&s_cnt[q], a);
-        if (b) atomicAdd(&s_cnt[P + q], b);
-        if (c) atomicAdd(&s_cnt[2 * P + q], c);
-        if (d) atomicAdd(&s_cnt[3 * P + q], d);
-      }
+    // every lane holds the warp totals: lane q keeps the running counts of part q
+    const int lq = lane_id() & 7;
+    acc_out += pk_get(p_out, lq);
+    acc_own += pk_get(p_own, lq);
+    acc_to += pk_get(p_to, lq);
+    acc_self += pk_get(p_self, lq);
+  }
+  if (lane_id() < P) {
+    const int q = lane_id();
+    if (acc_out) atomicAdd(&s_cnt[q], acc_out);
+    if (acc_own) atomicAdd(&s_cnt[P + q], acc_own);
+    if (acc_to) atomicAdd(&s_cnt[2 * P + q], acc_to);
+    if (acc_self) atomicAdd(&s_cnt[3 * P + q], acc_self);
   }
   __syncthreads();
   if (threadIdx.x < NF) ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x] = s_cnt[threadIdx.x];
@@ -794,7 +801,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
 __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  __shared__ unsigned long long s_wp[GS_NW][4];  // per-warp packed totals: out, own, to, self
+  __shared__ uint32_t s_wc[GS_NW][GS_NF_MAX];  // per-warp class totals of the tile (kind * P + part)
   __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
   __shared__ uint32_t s_run[2][GS_NF_MAX];
   __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
@@ -844,23 +851,28 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
     }
     const unsigned long long i_out = pk_warp_incl(p_out), i_own = pk_warp_incl(p_own),
                              i_to = pk_warp_incl(p_to), i_self = pk_warp_incl(p_self);
-    if (lane == 31) {
-      s_wp[w][0] = i_out;
-      s_wp[w][1] = i_own;
-      s_wp[w][2] = i_to;
-      s_wp[w][3] = i_self;
+    {  // lanes 0..7 unpack the part counts of the four kinds from lane 31's totals: one word per class
+      const unsigned long long t_out = __shfl_sync(FULL, i_out, 31), t_own = __shfl_sync(FULL, i_own, 31),
+                               t_to = __shfl_sync(FULL, i_to, 31), t_self = __shfl_sync(FULL, i_self, 31);
+      if (lane < P) {
+        s_wc[w][lane] = pk_get(t_out, lane);
+        s_wc[w][P + lane] = pk_get(t_own, lane);
+        s_wc[w][2 * P + lane] = pk_get(t_to, lane);
+        s_wc[w][3 * P + lane] = pk_get(t_self, lane);
+      }
     }
     __syncthreads();
     if (lane < NF) {  // lane = class (kind * P + part): this warp's base, warp 0 also the next tile's start
-      const int kind = lane / P, q = lane % P;
-      uint32_t a = s_run[t & 1][lane], all = 0u;
-      for (int k = 0; k < GS_NW; k++) {
-        const uint32_t c = pk_get(s_wp[k][kind], q);
-        if (k < w) a += c;
-        all += c;
+      uint32_t a = s_run[t & 1][lane];
+      if (w == 0) {
+        uint32_t all = 0u;
+#pragma unroll
+        for (int k = 0; k < GS_NW; k++) all += s_wc[k][lane];
+        s_run[(t + 1) & 1][lane] = a + all;
+      } else {
+        for (int k = 0; k < w; k++) a += s_wc[k][lane];
       }
       s_base[w][lane] = a;
-      if (w == 0) s_run[(t + 1) & 1][lane] = s_run[t & 1][lane] + all;
     }
     __syncwarp();
     unsigned long long r_out = i_out - p_out, r_own = i_own - p_own, r_to = i_to - p_to, r_self = i_self - p_self;
