@@ -276,6 +276,9 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
 // replacement.  Every real edge source does atomicMin(position) into the
 // direct-address table -- the parallel form of DuplicateRemover's first-
 // occurrence rule (util/duplicate.cpp:14-26).
+// RNG (gs_rng_mode) is a template parameter: the pick path of the other two
+// modes costs instructions in a kernel bound by issue.
+template <int RNG>
 __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -288,8 +291,8 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
   const int fan = ws.fanouts[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const uint32_t batch = (uint32_t)h->batch_index;
-  const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
-  const bool norepl = ws.rng_mode == (int)GS_RNG_PHILOX_NOREPLACE;
+  constexpr bool replay = RNG == (int)GS_RNG_DRAWS;
+  constexpr bool norepl = RNG == (int)GS_RNG_PHILOX_NOREPLACE;
   const uint64_t dbase = h->draw_base[layer];
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int i_lo = (int)ws.tile_first[t];
@@ -333,7 +336,8 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
     }
     const int32_t *src[GS_IPT];
     uint4 blk = make_uint4(0u, 0u, 0u, 0u);
-    int blk_row = -1, blk_id = -1;
+    int blk_row = -1, blk_id = -1, mg_row = -1;
+    uint32_t mg = 0u;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
       src[k] = nullptr;
@@ -353,7 +357,11 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
             }
             r = norepl ? nr_pick(blk, (uint32_t)pick, (uint32_t)deg[k]) : philox_word(blk, pick & 3);
           }
-          pick = (int32_t)(r % (uint32_t)deg[k]);
+          if (norepl) {
+            pick = (int32_t)r;  // already a member of [0, deg)
+          } else {
+            pick = (int32_t)(r % (uint32_t)deg[k]);
+          }
         }
         src[k] = ws.indices + rs[k] + pick;
       }
@@ -1056,7 +1064,9 @@ void gs_launch_rows_scan(const GsWs &ws, int layer, int grid, cudaStream_t st) {
   k_rows_scan<<<grid, GS_TPB, 0, st>>>(ws, layer);
 }
 void gs_launch_expand(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_expand<<<grid, GS_TPB, 0, st>>>(ws, layer);
+  if (ws.rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS><<<grid, GS_TPB, 0, st>>>(ws, layer);
+  else if (ws.rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE><<<grid, GS_TPB, 0, st>>>(ws, layer);
+  else k_expand<(int)GS_RNG_PHILOX><<<grid, GS_TPB, 0, st>>>(ws, layer);
 }
 void gs_launch_cand_flags(const GsWs &ws, int layer, int grid, cudaStream_t st) {
   k_cand_flags<<<grid, GS_TPB, 0, st>>>(ws, layer);
