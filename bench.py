@@ -260,10 +260,10 @@ def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
     return n * 3 / (e0.elapsed_time(e1) * 1e-3)
 
 
-# One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.96 MB read +
-# 2.85 MB written to DRAM (cold L2; the 12 MB candidate stream it writes stays in L2) against
+# One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.97 MB read +
+# 2.70 MB written to DRAM (cold L2; the 12 MB candidate stream it writes stays in L2) against
 # 35.9 MB algorithmic -- the excess is 32-byte sectors moved for 4-byte neighbour picks.
-NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "expand@2", "bytes": 88812800,
+NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "expand@2", "bytes": 88668928,
                "source": "profiles/r1_ncu_expand_full_raw.csv (ncu --set full, tools/capture_evidence.sh)"}
 
 
