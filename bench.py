@@ -291,7 +291,7 @@ def own_arm(args):
     P, mbs = args.parts, args.mb_per_step
     batches = seed_batches(n, max(64, mbs), rank, world)
     kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
-              grid_ctas=args.grid_ctas)
+              grid_ctas=args.grid_ctas, l2_hints=not args.no_l2_hints)
     dev = Slicer(g, FANOUTS, host_output=False, **kw)
     hst = Slicer(g, FANOUTS, host_output=True, host_copy_engine=not args.host_stores, **kw)
     peaks = {}
@@ -737,6 +737,7 @@ def main():
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-l2-hints", action="store_true", help="A/B: plain loads/stores/reds on the dedup table")
     ap.add_argument("--host-stores", action="store_true",
                     help="e2e: mirror samples with stores from the last kernel instead of the copy engine")
     ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
