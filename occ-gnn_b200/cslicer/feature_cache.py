@@ -8,7 +8,9 @@ of all N nodes per GPU,
                until c*N rows are held.
 The reference orders by `torch.sort(descending=True)`, which leaves the order of
 equal degrees unspecified; here ties go to the smaller node id (a stable sort),
-so the choice is deterministic.  The rows chosen feed
+so the choice is deterministic.  Pinned against the reference's own code:
+tests/golden/cache_policy.npz holds `MemoryManager.local_to_global_id` as the
+unmodified module computes it (tests/golden/make_cache_policy_golden.py).  The rows chosen feed
 `engine.Features(rows, cache_rows=...)`; nothing else of MemoryManager is needed:
 a miss is read from host memory by the gather kernel, so there is no
 refresh_cache / clean_up cycle (memory_manager.py:75-104).
@@ -16,19 +18,24 @@ refresh_cache / clean_up cycle (memory_manager.py:75-104).
 import numpy as np
 
 
-def degree_ordered_cache(indptr, fraction, owner=None, part=0, num_parts=4, indices=None):
+def degree_ordered_cache(indptr, fraction, owner=None, part=0, num_parts=4, indices=None, degrees=None):
     """-> int64 array of node ids to cache on GPU `part`, cached order = slot order.
     owner: int array [N] (None: id % num_parts, pyfrontend.cpp:57).
     indices: the CSR's neighbour array.  Given, nodes are ranked by how often they
     occur in it -- their out-degree as a message SOURCE, which is what
     `graph.out_degree` is at memory_manager.py:54,61 and what decides how often
     sampling reaches a node.  Omitted, the row length is used (the same number
-    on a symmetric graph such as the reference's datasets)."""
+    on a symmetric graph such as the reference's datasets).  degrees: an explicit
+    per-node degree array (then indptr may be None)."""
     if not 0.0 < fraction <= 1.0:
         raise ValueError("cache fraction must be in (0, 1]")  # memory_manager.py:28
-    ip = np.asarray(indptr, dtype=np.int64)
-    n = ip.size - 1
-    deg = np.diff(ip) if indices is None else np.bincount(np.asarray(indices), minlength=n)
+    if degrees is not None:
+        deg = np.asarray(degrees, dtype=np.int64)
+        n = deg.size
+    else:
+        ip = np.asarray(indptr, dtype=np.int64)
+        n = ip.size - 1
+        deg = np.diff(ip) if indices is None else np.bincount(np.asarray(indices), minlength=n)
     own = (np.arange(n) % num_parts) if owner is None else np.asarray(owner)
     n_cached = int(fraction * n)                      # memory_manager.py:42
     mine = np.nonzero(own == part)[0]

@@ -1,6 +1,6 @@
-"""Host-side cache policy (python/utils/memory_manager.py:40-74).
-The reference's MemoryManager needs DGL and four GPUs to construct, so these are
-hand-computed expectations of its rule -- parity unpinned (see the module docstring)."""
+"""Host-side cache policy (python/utils/memory_manager.py:40-74):
+hand-computed expectations of the rule, and golden vectors produced by the
+reference's own MemoryManager (tests/golden/make_cache_policy_golden.py)."""
 import os
 import sys
 
@@ -53,3 +53,24 @@ def test_source_degree_ranking_uses_the_neighbour_array():
     ix = np.array([3, 3, 3, 0, 3, 1])          # node 3 is the most frequent source, then 0 / 1
     got = degree_ordered_cache(ip, 0.5, part=0, num_parts=1, indices=ix)
     assert got.tolist() == [3, 0]
+
+
+def test_policy_matches_the_reference_memory_manager_golden():
+    """tests/golden/cache_policy.npz = MemoryManager.local_to_global_id[g] computed by the
+    UNMODIFIED reference module (distinct degrees, so sort ties cannot matter): same
+    nodes in the same slot order for fractions below, at and above 1/4; and what its
+    refresh_cache appends per batch is exactly the set this design reads from host."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "cache_policy.npz"))
+    deg, part = z["out_degree"], z["partition_map"]
+    for frac in (0.05, 0.25, 0.5, 1.0):
+        for g in range(4):
+            got = degree_ordered_cache(None, frac, owner=part, part=g, num_parts=4, degrees=deg)
+            assert np.array_equal(got, z[f"cached_{frac}_{g}"]), (frac, g)
+    for frac in (0.05, 0.25):
+        last = z[f"last_layer_{frac}"]
+        for g in range(4):
+            cached = z[f"cached_{frac}_{g}"]
+            mine = last[part[last] == g]
+            missing = mine[~np.isin(mine, cached)]          # served from host memory by the gather kernel
+            assert np.array_equal(z[f"refreshed_{frac}_{g}"], np.concatenate([cached, missing]))
+            assert abs(hit_rate(cached, mine, deg.size) - (1.0 - missing.size / max(1, mine.size))) < 1e-12
