@@ -72,5 +72,8 @@ def test_policy_matches_the_reference_memory_manager_golden():
             cached = z[f"cached_{frac}_{g}"]
             mine = last[part[last] == g]
             missing = mine[~np.isin(mine, cached)]          # served from host memory by the gather kernel
+            if frac >= 0.25:  # memory_manager.py:76-78: no refresh at >= 1/4, even where the partition is larger than the cache
+                assert np.array_equal(z[f"refreshed_{frac}_{g}"], cached)
+                continue
             assert np.array_equal(z[f"refreshed_{frac}_{g}"], np.concatenate([cached, missing]))
             assert abs(hit_rate(cached, mine, deg.size) - (1.0 - missing.size / max(1, mine.size))) < 1e-12
