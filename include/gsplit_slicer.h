@@ -321,7 +321,10 @@ int gs_pslicer_feature_slab(gs_pslicer *s, int32_t slot, const float **device_ro
 int gs_pslicer_shuffle(gs_pslicer *s, int32_t slot, int32_t layer, float *rows_device, int32_t dim,
                        int32_t backward, int32_t phase);
 int gs_pslicer_sync(gs_pslicer *s);
-/* After any error: every rank calls this (all streams idle) before the next submit. */
+/* After any error: COLLECTIVE -- every rank calls this with its streams idle, and no rank
+ * submits again before all ranks have returned (a host-side barrier, e.g. dist.barrier()).
+ * Clears the dedup table, the dense marks, the error word, the "group broken" latch and the
+ * barrier state (epoch and flags restart at 0: after a peer timeout the epochs differ). */
 int gs_pslicer_reset(gs_pslicer *s);
 int gs_pslicer_launches_per_sample(const gs_pslicer *s);
 int64_t gs_pslicer_device_bytes(const gs_pslicer *s);

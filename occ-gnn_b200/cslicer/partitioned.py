@@ -282,6 +282,7 @@ class PartitionedPipeline:
         for ps in self.lanes:
             connect_process_group(ps, dist)
         self.rank, self.num_parts = int(rank), int(num_parts)
+        self._dist = dist
         self.launches_per_sample = self.lanes[0].launches_per_sample
         self.device_bytes = sum(ps.device_bytes for ps in self.lanes)
         self._next = 0
@@ -304,9 +305,29 @@ class PartitionedPipeline:
     def slice(self, seeds, batch_index=0):
         return self.wait(self.submit(seeds, batch_index))
 
+    def reset(self):
+        """After any error (a GS_ERR_PEER timeout included): collective -- every rank
+        calls it; nobody submits again before all ranks have reset (gs_pslicer_reset)."""
+        for ps in self.lanes:
+            ps.sync()
+        self._dist.barrier()   # every rank has stopped writing into its peers' arenas
+        for ps in self.lanes:
+            ps.reset()
+        self._dist.barrier()   # nobody signals before every arena is clean
+        self._next = 0
+
     def close(self):
         for ps in self.lanes:
             ps.close()
+
+
+def reset_process_group(ps, dist):
+    """Collective recovery of one PartitionedSlicer per rank after an error:
+    gs_pslicer_reset on every rank, then a host barrier before anyone submits."""
+    ps.sync()
+    dist.barrier()   # every rank has stopped writing into its peers' arenas
+    ps.reset()
+    dist.barrier()   # nobody signals before every arena is clean
 
 
 class LocalGroup:

@@ -697,7 +697,10 @@ int gs_pslicer_reset(gs_pslicer *s) {
   CU(cudaMemsetAsync(s->me.nf, 0, (size_t)s->Ccap * sizeof(uint2), s->stream));
   CU(cudaMemsetAsync(s->me.err, 0, sizeof(int32_t), s->stream));
   CU(cudaMemsetAsync(s->base.tickets, 0, 8 * sizeof(uint32_t), s->stream));
-  CU(cudaMemsetAsync(s->base.epoch + 1, 0, sizeof(uint32_t), s->stream));
+  // barrier state: after a peer timeout the ranks' epochs differ (the rank that ran alone
+  // signalled, the others did not), so a reset starts every rank from epoch 0 with clean flags
+  CU(cudaMemsetAsync(s->base.epoch, 0, 2 * sizeof(uint32_t), s->stream));
+  CU(cudaMemsetAsync(s->me.flags, 0, GS_MAX_PARTS * sizeof(uint32_t), s->stream));
   CU(cudaStreamSynchronize(s->stream));
   for (PSlot &sl : s->slots) sl.state = PSLOT_FREE;
   return GS_OK;

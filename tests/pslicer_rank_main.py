@@ -30,7 +30,7 @@ def main():
     lip, lix = partition_csr(ip, ix, world)[rank]
     ps = PartitionedSlicer(lip, lix, n, rank, world, fan, device=local, max_batch=512, num_slots=2,
                            seed=77, num_edges_global=ix.size, shuffle_rows_capacity=1 << 16,
-                           shuffle_max_dim=32)
+                           shuffle_max_dim=32, timeout_ms=1500)
     connect_process_group(ps, dist)
     orc = O.OracleSlicer(ip, ix, fan, world, O.RNG_PHILOX, seed=77)
     rng = np.random.default_rng(8)
@@ -52,6 +52,24 @@ def main():
             ref = _shuffle_reference(want, l, world, lambda x: x % world, parts, backward)
             assert np.array_equal(rows.cpu().numpy(), ref[rank]), (l, backward)
     v.release()
+    dist.barrier()
+    # failure detection over real peers: the last rank sits one minibatch out; the others
+    # time out with GS_ERR_PEER instead of hanging, then the whole group resets and goes on
+    from cslicer import _native as N
+    from cslicer.partitioned import reset_process_group
+    seeds = rng.permutation(n)[:256]
+    if rank != world - 1:
+        try:
+            ps.slice(seeds, 60)
+            raise AssertionError("a minibatch without one of its ranks must fail")
+        except N.SlicerError as e:
+            assert e.code == N.ERR_PEER, e
+    reset_process_group(ps, dist)
+    for bi in (61, 62):
+        seeds = rng.permutation(n)[:256]
+        v = ps.slice(seeds, bi)
+        _compare_rank(v, orc.slice(seeds, bi), rank)
+        v.release()
     dist.barrier()
     ps.close()
     # several minibatches in flight per rank: independent lanes, barriers overlap

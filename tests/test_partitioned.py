@@ -329,3 +329,41 @@ def test_split_parallel_shuffle_forward_and_backward(P, dim):
     for v in views:
         v.release()
     grp.close()
+
+
+@pytest.mark.gpu
+def test_missing_peer_times_out_with_err_peer_and_the_group_recovers():
+    """Failure detection: a rank whose peer never arrives does not hang -- the device-side
+    barrier gives up after timeout_ms, the sample fails with GS_ERR_PEER, later barriers
+    of the broken group return at once, and gs_pslicer_reset brings both ranks back.
+    (Two ranks emulated on one device and one stream, as in LocalGroup: the minibatch of
+    rank 0 is enqueued alone, so its barriers can never be met.)"""
+    import time
+    import torch
+    assert torch.cuda.is_available()
+    from cslicer import _native as N
+    from cslicer.partitioned import LocalGroup
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=5)
+    n, P, fan = ip.size - 1, 2, [5, 5]
+    grp = LocalGroup(ip, ix, P, fan, max_batch=64, num_slots=2, seed=3, timeout_ms=60)
+    seeds = np.random.default_rng(1).permutation(n)[:64]
+    r0 = grp.ranks[0]
+    t0 = time.time()
+    slot = r0.stage(seeds, 0)
+    r0.enqueue(slot, 0, grp.num_segments)      # rank 1 never enqueues this minibatch
+    r0.commit(slot)
+    with pytest.raises(N.SlicerError) as e:
+        r0.wait(slot)
+    assert e.value.code == N.ERR_PEER
+    assert time.time() - t0 < 5.0              # one timeout, not one per barrier
+    for r in grp.ranks:
+        r.reset()
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=3)
+    for bi in range(2):
+        views = grp.slice(seeds, bi)
+        want = orc.slice(seeds, bi)
+        for g, v in enumerate(views):
+            _compare_rank(v, want, g)
+            v.release()
+    grp.close()
