@@ -581,6 +581,7 @@ int gs_pslicer_commit(gs_pslicer *s, int32_t slot) {
 
 int gs_pslicer_submit(gs_pslicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
                       int32_t *slot_out) {
+  const GsRange trace("gs_pslicer_submit");
   int rc = stage(s, seeds_host, n, batch_index, slot_out);
   if (rc != GS_OK) return rc;
   PSlot &sl = s->slots[*slot_out];
@@ -599,6 +600,7 @@ int gs_pslicer_wait(gs_pslicer *s, int32_t slot, const gs_sample_header **hdr_ou
   PSlot &sl = s->slots[slot];
   if (sl.state == PSLOT_FREE || sl.state == PSLOT_STAGED)
     return pfail(GS_ERR_STATE, "slot %d holds no submitted sample", slot);
+  const GsRange trace("gs_pslicer_wait");
   CU(cudaSetDevice(s->device));
   if (sl.state == PSLOT_BUSY) CU(cudaEventSynchronize(sl.done));
   sl.state = PSLOT_DONE;
@@ -652,6 +654,7 @@ int gs_pslicer_shuffle(gs_pslicer *s, int32_t slot, int32_t layer, float *rows, 
   if (!s || slot < 0 || slot >= (int)s->slots.size()) return pfail(GS_ERR_INVALID, "bad slot");
   PSlot &sl = s->slots[slot];
   if (sl.state != PSLOT_DONE) return pfail(GS_ERR_STATE, "slot %d not waited on", slot);
+  const GsRange trace(backward ? "gs_pslicer_shuffle(backward)" : "gs_pslicer_shuffle(forward)");
   if (layer < 0 || layer >= s->cfg.num_layers) return pfail(GS_ERR_INVALID, "bad layer");
   if (!rows || dim < 1 || dim > s->cfg.shuffle_max_dim)
     return pfail(GS_ERR_INVALID, "rows NULL or dim %d outside [1, shuffle_max_dim=%d]", dim,

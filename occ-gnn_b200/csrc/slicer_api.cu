@@ -10,6 +10,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "slicer_internal.cuh"
 
 namespace {
@@ -31,6 +33,20 @@ int fail(int code, const char *fmt, ...) {
 int gs_set_error(int code, const char *msg) {
   g_err = msg;
   return code;
+}
+
+static bool gs_nvtx_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("GSPLIT_NVTX");
+    return e && *e && *e != '0';
+  }();
+  return on;
+}
+GsRange::GsRange(const char *name) : on(gs_nvtx_enabled()) {
+  if (on) nvtxRangePushA(name);
+}
+GsRange::~GsRange() {
+  if (on) nvtxRangePop();
 }
 namespace {
 
@@ -532,6 +548,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
 int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
                      int32_t *slot_out) {
   if (!s || !slot_out) return fail(GS_ERR_INVALID, "NULL argument");
+  const GsRange trace("gs_slicer_submit");
   CU(cudaSetDevice(s->g->device));
   const int ns = (int)s->slots.size();
   int k = -1;
@@ -610,6 +627,7 @@ int gs_slicer_wait(gs_slicer *s, int32_t slot, const gs_sample_header **hdr_out)
   if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
   Slot &sl = s->slots[slot];
   if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
+  const GsRange trace("gs_slicer_wait");
   CU(cudaSetDevice(s->g->device));
   if (sl.state == SLOT_BUSY) CU(cudaEventSynchronize(sl.done));
   return finish_wait(s, sl, hdr_out);

@@ -90,6 +90,16 @@ struct GsWs {
 // error string of the calling thread (slicer_api.cu); returns `code`
 int gs_set_error(int code, const char *msg);
 
+// Tracing (the reference marks its phases with NVTX ranges,
+// src/samplers/neigh_sample.h:98, python/train.py:68).  GSPLIT_NVTX=1 in the
+// environment turns on one range per submit / wait / shuffle of the C ABI; off
+// (the default) it costs one predictable branch.  Header-only NVTX v3.
+struct GsRange {
+  bool on;
+  explicit GsRange(const char *name);
+  ~GsRange();
+};
+
 // launchers (slicer_kernels.cu); every one enqueues exactly one kernel on `st`
 void gs_launch_begin(const GsWs &ws, cudaStream_t st);
 void gs_launch_rows_count(const GsWs &ws, int layer, int grid, cudaStream_t st);

@@ -444,3 +444,16 @@ def test_reference_facing_module_end_to_end(tmp_path):
     with pytest.raises(RuntimeError):
         csl.getSample()
     csl.close()
+
+
+def test_nvtx_ranges_can_be_switched_on():
+    """GSPLIT_NVTX=1 (tracing): the C ABI wraps submit / wait in NVTX
+    ranges; results and exit status are unchanged (run in a child: the switch is read once)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GSPLIT_NVTX="1")
+    r = subprocess.run([sys.executable, "-c", "import __graft_entry__ as g; g.smoke()"], cwd=root, env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "smoke ok" in r.stdout
