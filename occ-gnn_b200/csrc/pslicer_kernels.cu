@@ -826,10 +826,13 @@ __global__ void __launch_bounds__(GS_TPB) pk_gather(PsWs ws) {
   }
   if ((int64_t)R > ws.feat_cap_rows) return;
   const int32_t *ids = ws.slab + sp.off;
-  const int lane = lane_id();
-  const int nwarps = gridDim.x * GS_NW;
-  for (int r = blockIdx.x * GS_NW + warp_id(); r < R; r += nwarps)
-    gather_row(ws.feat, ws.feat_dim, (int64_t)ps_local(ws, ids[r], ws.rank), ws.feat_out, r, lane);
+  const float *feat = ws.feat;
+  const int dim = ws.feat_dim;
+  auto src_of_row = [&](int64_t r) -> const float * {
+    return feat + (int64_t)ps_local(ws, __ldg(ids + r), ws.rank) * dim;
+  };
+  gather_block(dim, (int64_t)R, ws.feat_out, src_of_row, (int64_t)blockIdx.x * GS_NW + warp_id(),
+               (int64_t)gridDim.x * GS_NW, lane_id());
 }
 
 // ---------------------------------------------------------------- pk_shuffle

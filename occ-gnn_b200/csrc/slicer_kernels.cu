@@ -336,8 +336,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
     }
     const int32_t *src[GS_IPT];
     uint4 blk = make_uint4(0u, 0u, 0u, 0u);
-    int blk_row = -1, blk_id = -1, mg_row = -1;
-    uint32_t mg = 0u;
+    int blk_row = -1, blk_id = -1;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
       src[k] = nullptr;
@@ -1023,23 +1022,24 @@ __global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
   __syncthreads();
   const int R = s_start[P];
   if ((int64_t)R > ws.feat_cap_rows) return;
-  const int lane = lane_id();
-  const int nwarps = gridDim.x * GS_NW;
   const FeatSrc fs{ws.feat, ws.feat_slot, ws.feat_host};
-  for (int r = blockIdx.x * GS_NW + warp_id(); r < R; r += nwarps) {
+  const int dim = ws.feat_dim, div = ws.feat_div;
+  const int32_t *slab = ws.slab;
+  auto src_of_row = [&](int64_t r) -> const float * {
     int q = 0;
     while (q + 1 < P && r >= s_start[q + 1]) q++;
-    const int32_t id = ws.slab[s_off[q] + (r - s_start[q])];
-    gather_row_from(fs.row((int64_t)(id / ws.feat_div), ws.feat_dim), ws.feat_dim, ws.feat_out, r, lane);
-  }
+    const int32_t id = slab[s_off[q] + ((int)r - s_start[q])];
+    return fs.row((int64_t)(id / div), dim);
+  };
+  gather_block(dim, (int64_t)R, ws.feat_out, src_of_row, (int64_t)blockIdx.x * GS_NW + warp_id(),
+               (int64_t)gridDim.x * GS_NW, lane_id());
 }
 
 __global__ void __launch_bounds__(GS_TPB) k_gather_ids(FeatSrc fs, int dim, int div,
                                                        const int32_t *ids, int64_t n, float *out) {
-  const int lane = lane_id();
-  const int64_t nwarps = (int64_t)gridDim.x * GS_NW;
-  for (int64_t r = (int64_t)blockIdx.x * GS_NW + warp_id(); r < n; r += nwarps)
-    gather_row_from(fs.row((int64_t)(ids[r] / div), dim), dim, out, r, lane);
+  auto src_of_row = [&](int64_t r) -> const float * { return fs.row((int64_t)(__ldg(ids + r) / div), dim); };
+  gather_block(dim, n, out, src_of_row, (int64_t)blockIdx.x * GS_NW + warp_id(), (int64_t)gridDim.x * GS_NW,
+               lane_id());
 }
 
 __global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
