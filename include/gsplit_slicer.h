@@ -203,6 +203,26 @@ int gs_slicer_read_frontier(gs_slicer *s, int32_t slot, int32_t layer, int32_t *
 /* Replaces PySample's destructor (pybipartite.cpp:68-76). */
 int gs_slicer_release(gs_slicer *s, int32_t slot);
 
+/* Split-parallel hand-over (the consumer of Sample.layers[l][g] is GPU g,
+ * python/train.py:120-160, python/data/bipartite.py:20-58): every list of part g of
+ * the slot's sample is packed into one self-describing block of `block_words`
+ * int32 at dst_device + g * block_words, so that the P blocks can leave in ONE
+ * all-to-all over NVLink (block g -> rank g) while every rank keeps slicing whole
+ * minibatches on a replicated topology.  Block layout (int32 words):
+ *   [0] GS_PART_MAGIC  [1] status (0, or GS_ERR_OVERFLOW: block_words too small)
+ *   [2] part  [3] num_layers  [4] num_parts  [5] n_seeds  [6,7] batch_index (lo, hi)
+ *   [8] words in use  [9] edges of this part  [10..15] 0
+ *   [16 + 2*(l*GS_NUM_FIELDS + f)], [.. + 1] = offset (words from the block start,
+ *   16-byte aligned) and length of field f of layer l;  data from word
+ *   GS_PART_HEADER_WORDS on.
+ * The slot must hold a submitted sample (waiting for it is not required: the pack
+ * runs on the slot's stream, after the sample's kernels).  consumer_stream (a
+ * cudaStream_t; NULL = the default stream) is made to wait for the pack.  block_words % 4 == 0. */
+#define GS_PART_MAGIC 0x31505347
+#define GS_PART_HEADER_WORDS (16 + 2 * GS_MAX_LAYERS * GS_NUM_FIELDS)
+int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_t block_words,
+                         void *consumer_stream);
+
 /* Diagnostics: run one minibatch eagerly (no graph) on slot 0 with a CUDA event
  * between kernels; ms[i] receives the duration of launch i, names[i] a static
  * string.  Returns the number of launches through *n_out (<= cap). */
@@ -222,6 +242,9 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
 int gs_slicer_launches_per_sample(const gs_slicer *s);
 /* Device bytes held by one slot / by the slicer. */
 int64_t gs_slicer_slot_bytes(const gs_slicer *s);
+/* int32 elements one slot's sample slab can hold (gs_config.slab_capacity, or the
+ * bound derived from max_batch and the fanouts): an upper bound for any part block. */
+int64_t gs_slicer_slab_capacity(const gs_slicer *s);
 
 /* ------------------------------------------------------------------------
  * Partitioned mode: one rank per GPU, rank g of num_parts holds

@@ -10,7 +10,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgsplit_slicer.so")
+# GSPLIT_SLICER_LIB: another build of the same library (A/B of compile-time variants)
+LIB_PATH = os.environ.get("GSPLIT_SLICER_LIB") or os.path.join(HERE, "libgsplit_slicer.so")
 
 MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 1
 RNG_PHILOX, RNG_DRAWS, RNG_PHILOX_NOREPLACE = 0, 1, 2
@@ -25,9 +26,9 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
-           "gs_slicer_slot_bytes", "gs_reference_shuffle", "gs_features_create",
+           "gs_slicer_slot_bytes", "gs_slicer_slab_capacity", "gs_reference_shuffle", "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
-           "gs_slicer_frontiers", "gs_slicer_read_frontier",
+           "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts",
            # partitioned mode (one rank per GPU)
            "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
            "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
@@ -120,6 +121,9 @@ def lib():
     L.gs_slicer_launches_per_sample.argtypes = [C.c_void_p]
     L.gs_slicer_slot_bytes.restype = C.c_int64
     L.gs_slicer_slot_bytes.argtypes = [C.c_void_p]
+    L.gs_slicer_slab_capacity.restype = C.c_int64
+    L.gs_slicer_slab_capacity.argtypes = [C.c_void_p]
+    L.gs_slicer_pack_parts.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
     L.gs_reference_shuffle.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     L.gs_features_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                      C.POINTER(C.c_void_p)]

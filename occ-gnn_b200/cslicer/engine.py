@@ -279,6 +279,10 @@ class Slicer:
         self.launches_per_sample = L.gs_slicer_launches_per_sample(h)
         self.slot_bytes = L.gs_slicer_slot_bytes(h)
 
+    def slab_capacity_words(self):
+        """int32 elements a slot's slab can hold: an upper bound for a hand-over block."""
+        return int(N.lib().gs_slicer_slab_capacity(self._h))
+
     def submit(self, seeds, batch_index=0):
         s = np.ascontiguousarray(seeds, dtype=np.int64)
         slot = C.c_int32(-1)

@@ -1,0 +1,148 @@
+"""Split-parallel hand-over: slice whole minibatches anywhere, deliver part g to GPU g.
+
+The consumer of `sample.layers[l][g]` is GPU g (python/train.py:120-160 moves
+bipartite g of every layer to device g; python/data/bipartite.py:20-58 builds its
+tensors there).  The partitioned slicer (partitioned.py) produces part g ON rank g
+but makes all ranks walk every minibatch together.  This is the throughput form of
+the same contract on a machine where the topology fits every GPU (DESIGN.md
+section 6.4): rank r slices its own minibatches b = r, r + R, ... with the
+replicated slicer, `gs_slicer_pack_parts` (own kernel) packs the R parts of a sample
+into R self-describing blocks, and ONE all-to-all over NVLink moves block g to rank
+g.  After round k rank g holds part g of minibatches kR .. kR + R - 1, bit-identical
+to what the single-GPU slicer (and the oracle) emit for those minibatches.
+
+Block layout: include/gsplit_slicer.h (gs_slicer_pack_parts).  `pack_block_numpy`
+restates it on the host for the CPU tests; `PartBlock` parses either.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+MAGIC = 0x31505347
+HEADER_WORDS = 16 + 2 * N.MAX_LAYERS * N.NUM_FIELDS
+
+
+def _pad4(n):
+    return (int(n) + 3) & ~3
+
+
+def part_words(fields_by_layer):
+    """int32 words a block needs for `fields_by_layer[l][name] -> array`."""
+    return HEADER_WORDS + sum(_pad4(len(fl[name])) for fl in fields_by_layer for name in N.FIELDS)
+
+
+def pack_block_numpy(fields_by_layer, part, num_parts, n_seeds, batch_index, block_words):
+    """Host restatement of k_pack_parts (slicer_kernels.cu) for one part."""
+    L = len(fields_by_layer)
+    blk = np.zeros(block_words, dtype=np.int32)
+    need = part_words(fields_by_layer)
+    blk[0] = MAGIC
+    blk[1] = 0 if need <= block_words else N.ERR_OVERFLOW
+    blk[2], blk[3], blk[4], blk[5] = part, L, num_parts, n_seeds
+    blk[6] = np.uint32(batch_index & 0xFFFFFFFF).astype(np.int32)
+    blk[7] = np.uint32(batch_index >> 32).astype(np.int32)
+    blk[8] = min(need, 0x7FFFFFFF)
+    blk[9] = sum(len(fl["csr_indices"]) for fl in fields_by_layer)
+    at = HEADER_WORDS
+    for l, fl in enumerate(fields_by_layer):
+        for f, name in enumerate(N.FIELDS):
+            a = np.asarray(fl[name], dtype=np.int32)
+            k = 16 + 2 * (l * N.NUM_FIELDS + f)
+            blk[k], blk[k + 1] = at, a.size
+            if need <= block_words:
+                blk[at:at + a.size] = a
+            at += _pad4(a.size)
+    return blk
+
+
+class PartBlock:
+    """One received block: part `part` of minibatch `batch_index`, every list a
+    zero-copy slice of the buffer it arrived in (numpy array or torch tensor)."""
+
+    def __init__(self, buf, header=None):
+        h = np.asarray(header if header is not None else buf[:HEADER_WORDS]).astype(np.int64)
+        if int(h[0]) != MAGIC:
+            raise RuntimeError("not a part block (bad magic)")
+        self.status = int(h[1])
+        if self.status == N.ERR_OVERFLOW:
+            raise RuntimeError(f"part block overflow: the part needs {int(h[8])} words; raise block_words")
+        if self.status != 0:
+            raise RuntimeError(f"source rank raised status {self.status} for this minibatch")
+        self.part, self.num_layers, self.num_parts, self.n_seeds = int(h[2]), int(h[3]), int(h[4]), int(h[5])
+        self.batch_index = (int(h[6]) & 0xFFFFFFFF) | ((int(h[7]) & 0xFFFFFFFF) << 32)
+        self.words, self.edges = int(h[8]), int(h[9])
+        self._spans = [[(int(h[16 + 2 * (l * N.NUM_FIELDS + f)]), int(h[17 + 2 * (l * N.NUM_FIELDS + f)]))
+                        for f in range(N.NUM_FIELDS)] for l in range(self.num_layers)]
+        self._buf = buf
+
+    def field(self, l, name):
+        off, ln = self._spans[l][N.FIELDS.index(name)]
+        return self._buf[off:off + ln]
+
+    def field_len(self, l, name):
+        return self._spans[l][N.FIELDS.index(name)][1]
+
+
+def pack_parts(slicer, slot, dst, consumer_stream=None):
+    """gs_slicer_pack_parts: dst = int32 CUDA tensor [num_parts, block_words] (torch is
+    plumbing: it owns the buffer the collective sends)."""
+    if dst.dim() != 2 or dst.shape[0] != slicer.num_parts or not dst.is_contiguous():
+        raise ValueError("dst must be a contiguous [num_parts, block_words] int32 tensor")
+    N.check(N.lib().gs_slicer_pack_parts(slicer._h, int(slot), C.c_void_p(dst.data_ptr()), int(dst.shape[1]),
+                                         C.c_void_p(consumer_stream or 0)))
+
+
+class PartScatter:
+    """Collective hand-over for R = num_parts ranks, `depth` rounds in flight.
+
+        k = ps.post(slot)        # pack the slot's sample + all-to-all (async; every rank calls it)
+        blocks = ps.collect(k)   # [PartBlock of source rank 0, 1, ...]: part `rank` of R minibatches
+
+    The exchange runs on its own stream, so the slicer keeps working on the next
+    minibatches while blocks are in flight."""
+
+    def __init__(self, slicer, dist, block_words, depth=2, group=None):
+        import torch
+        self.slicer, self.dist, self.group = slicer, dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if slicer.num_parts != self.world:
+            raise ValueError(f"hand-over needs num_parts == world size ({slicer.num_parts} != {self.world})")
+        self.block_words = _pad4(block_words)
+        if self.block_words < HEADER_WORDS:
+            raise ValueError("block_words smaller than a block header")
+        dev = torch.device("cuda", slicer.graph.device)
+        self.depth = int(depth)
+        self.send = [torch.empty((self.world, self.block_words), dtype=torch.int32, device=dev)
+                     for _ in range(self.depth)]
+        self.recv = [torch.empty((self.world, self.block_words), dtype=torch.int32, device=dev)
+                     for _ in range(self.depth)]
+        self.stream = torch.cuda.Stream(device=dev)
+        self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self._posted = 0
+        self._torch = torch
+
+    def post(self, slot):
+        torch = self._torch
+        k = self._posted % self.depth
+        if self._posted >= self.depth:
+            self.done[k].synchronize()  # the round that used these buffers has been delivered
+        pack_parts(self.slicer, slot, self.send[k], self.stream.cuda_stream)
+        with torch.cuda.stream(self.stream):
+            self.dist.all_to_all_single(self.recv[k], self.send[k], group=self.group)
+            self.done[k].record(self.stream)
+        self._posted += 1
+        return self._posted - 1
+
+    def collect(self, ticket, parse=True):
+        k = ticket % self.depth
+        self.done[k].synchronize()
+        if not parse:
+            return self.recv[k]
+        hdr = self.recv[k][:, :HEADER_WORDS].cpu().numpy()
+        return [PartBlock(self.recv[k][r], hdr[r]) for r in range(self.world)]
+
+    def nvlink_bytes_per_round(self):
+        """bytes this rank sends to peers per round (the local block does not travel)"""
+        return 4 * self.block_words * (self.world - 1)

@@ -70,6 +70,7 @@ struct Slot {
   cudaGraphExec_t exec = nullptr;
   cudaEvent_t done = nullptr;
   cudaEvent_t chain_done = nullptr;  // copy-engine mirror: kernels of the sample finished
+  cudaEvent_t pack_done = nullptr;   // gs_slicer_pack_parts: the part blocks are written
   int64_t copied = 0;                // ... int32 elements of the slab the DMA of this sample moved
   cudaStream_t stream = nullptr;
   int state = SLOT_FREE;
@@ -299,6 +300,7 @@ int gs_slicer_destroy(gs_slicer *s) {
     if (sl.exec) cudaGraphExecDestroy(sl.exec);
     if (sl.done) cudaEventDestroy(sl.done);
     if (sl.chain_done) cudaEventDestroy(sl.chain_done);
+    if (sl.pack_done) cudaEventDestroy(sl.pack_done);
     for (void *p : sl.dev) cudaFree(p);
     if (sl.input) cudaFreeHost(sl.input);
     if (sl.seeds) cudaFreeHost(sl.seeds);
@@ -523,6 +525,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     sl.stream = s->streams[k % nstreams];
     CUS(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     CUS(cudaEventCreateWithFlags(&sl.chain_done, cudaEventDisableTiming));
+    CUS(cudaEventCreateWithFlags(&sl.pack_done, cudaEventDisableTiming));
     if (cfg->use_graph) {
       cudaGraph_t graph = nullptr;
       CUS(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
@@ -673,6 +676,26 @@ int gs_slicer_release(gs_slicer *s, int32_t slot) {
     finish_wait(s, sl, nullptr);
   }
   sl.state = SLOT_FREE;
+  return GS_OK;
+}
+
+int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_t block_words,
+                         void *consumer_stream) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  if (!dst_device || block_words < GS_PART_HEADER_WORDS || (block_words & 3) ||
+      ((uintptr_t)dst_device & 15))
+    return fail(GS_ERR_INVALID, "pack_parts: dst must be 16-byte aligned, block_words a multiple of 4 and >= %d",
+                (int)GS_PART_HEADER_WORDS);
+  Slot &sl = s->slots[slot];
+  if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
+  const GsRange trace("gs_slicer_pack_parts");
+  CU(cudaSetDevice(s->g->device));
+  // on the slot's own stream: after the sample's kernels, before the slot's next sample
+  gs_launch_pack_parts(sl.ws, dst_device, block_words, std::max(1, s->grid_full / std::max(1, s->cfg.num_parts)),
+                       sl.stream);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(sl.pack_done, sl.stream));
+  CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, sl.pack_done, 0));  // NULL: the default stream waits
   return GS_OK;
 }
 
@@ -858,5 +881,6 @@ int gs_slicer_launches_per_sample(const gs_slicer *s) {
   return s ? 2 + 8 * s->cfg.num_layers + (s->feat ? 1 : 0) : 0;
 }
 int64_t gs_slicer_slot_bytes(const gs_slicer *s) { return s ? s->slot_bytes : 0; }
+int64_t gs_slicer_slab_capacity(const gs_slicer *s) { return s ? s->slab_cap : 0; }
 
 }  // extern "C"

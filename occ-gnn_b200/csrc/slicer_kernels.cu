@@ -16,6 +16,20 @@
 // no tensor cores (nothing here is a contraction).
 #include "slicer_device.cuh"
 
+// Resident CTAs per SM the tiled kernels are compiled for (0: ptxas' choice,
+// 46-55 registers -> 4-5 CTAs; n: register cap 65536 / (GS_TPB * n)).  Several
+// minibatches run concurrently on their own streams, so what counts is how many
+// warps of ALL of them fit an SM.  Measured (tools/build_variants.sh): 6 (40
+// registers, few spills) = 0 within 0.3 %, 8 (32 registers, spills) -7 %.
+#ifndef GS_MINB
+#define GS_MINB 0
+#endif
+#if GS_MINB > 0
+#define GS_BOUNDS __launch_bounds__(GS_TPB, GS_MINB)
+#else
+#define GS_BOUNDS __launch_bounds__(GS_TPB)
+#endif
+
 namespace {
 
 // --------------------------------------------------- L2 residency control
@@ -138,7 +152,7 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
 // Per frontier row: CSR extent and number of candidates c = 1 + (deg < fan or
 // fan < 0 ? deg : fan)  (slicer.cpp:6-22).  Tile sums + last-CTA spine give the
 // candidate offsets' per-CTA prefixes and C_l.
-__global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_rows_count(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ unsigned long long s_w64[GS_NW + 1];
@@ -220,7 +234,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_count(GsWs ws, int layer) {
 // occurrence yet" (entries touched in earlier layers all belong to frontier
 // nodes), records which row each candidate tile starts in, and zeroes the
 // frontier-first counters k_cand_flags accumulates into with atomics.
-__global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_rows_scan(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const Tbl tbl(ws);
@@ -279,7 +293,7 @@ __global__ void __launch_bounds__(GS_TPB) k_rows_scan(GsWs ws, int layer) {
 // RNG (gs_rng_mode) is a template parameter: the pick path of the other two
 // modes costs instructions in a kernel bound by issue.
 template <int RNG>
-__global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const Tbl tbl(ws);
@@ -409,7 +423,7 @@ __global__ void __launch_bounds__(GS_TPB) k_expand(GsWs ws, int layer) {
 // id by the position of the first occurrence: that is all k_cand_apply and
 // k_relabel need to relabel it.  Per-CTA counts of the 2P+1 classes, then the
 // last CTA scans them, fixes F_{l+1}, |in_nodes_g|, E_g and lays the lists out.
-__global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const Tbl tbl(ws);
@@ -561,7 +575,7 @@ __global__ void __launch_bounds__(GS_TPB) k_cand_flags(GsWs ws, int layer) {
 // position (irank) -- the relabel map (DuplicateRemover::mask, duplicate.cpp:21)
 // indexed by position of first occurrence instead of by node, so that it is a
 // C-sized, L2-resident array and this kernel never touches the N-sized table.
-__global__ void __launch_bounds__(GS_TPB) k_cand_apply(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_cand_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   // The kernels of this pipeline are bound by instruction issue, not by memory:
@@ -706,7 +720,7 @@ __device__ __forceinline__ unsigned long long pk_spread(uint32_t mask, int /*P*/
   return ((v + 0x7F7F7F7F7F7F7F7Full) >> 7) & 0x0101010101010101ull;
 }
 
-__global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_front_count(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ uint32_t s_cnt[GS_NF_MAX];
@@ -805,7 +819,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_count(GsWs ws, int layer) {
 }
 
 // ------------------------------------------------------------ k_front_apply
-__global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_front_apply(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ uint32_t s_wc[GS_NW][GS_NF_MAX];  // per-warp class totals of the tile (kind * P + part)
@@ -921,7 +935,7 @@ __global__ void __launch_bounds__(GS_TPB) k_front_apply(GsWs ws, int layer) {
 // csr_indices: edge-source ids -> positions in in_nodes_g through the table
 // (DuplicateRemover::replace, duplicate.cpp:35-39 -- what bipartite.cpp:5
 // would do if `indices` were ever filled).
-__global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
+__global__ void GS_BOUNDS k_relabel(GsWs ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const int P = ws.P;
@@ -954,7 +968,7 @@ __global__ void __launch_bounds__(GS_TPB) k_relabel(GsWs ws, int layer) {
 // fill instead when the touched set covers most of the table's sectors),
 // then the sample header and, when asked, the used part of the slab are
 // mirrored to pinned host memory with 16-byte stores.
-__global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
+__global__ void GS_BOUNDS k_finish(GsWs ws) {
   gs_sample_header *h = ws.hdr;
   const Tbl tbl(ws);
   const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
@@ -999,7 +1013,7 @@ __global__ void __launch_bounds__(GS_TPB) k_finish(GsWs ws) {
 // With a cached store (FeatSrc) rows outside the HBM cache are read in place from
 // host memory by the same warp, so there is no per-batch refresh step and no
 // global_to_local table to patch and undo (memory_manager.py:77-104).
-__global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
+__global__ void GS_BOUNDS k_gather_sample(GsWs ws) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ int32_t s_off[GS_MAX_PARTS], s_start[GS_MAX_PARTS + 1];
@@ -1035,11 +1049,72 @@ __global__ void __launch_bounds__(GS_TPB) k_gather_sample(GsWs ws) {
                (int64_t)gridDim.x * GS_NW, lane_id());
 }
 
-__global__ void __launch_bounds__(GS_TPB) k_gather_ids(FeatSrc fs, int dim, int div,
+__global__ void GS_BOUNDS k_gather_ids(FeatSrc fs, int dim, int div,
                                                        const int32_t *ids, int64_t n, float *out) {
   auto src_of_row = [&](int64_t r) -> const float * { return fs.row((int64_t)(__ldg(ids + r) / div), dim); };
   gather_block(dim, n, out, src_of_row, (int64_t)blockIdx.x * GS_NW + warp_id(), (int64_t)gridDim.x * GS_NW,
                lane_id());
+}
+
+// ------------------------------------------------------------- k_pack_parts
+// Split-parallel hand-over: blockIdx.y = part g.  Every list of part g (all
+// layers, the nine fields) is copied into block g of `dst` behind a span table,
+// 16-byte vectors, consecutive threads on consecutive addresses (slab spans and
+// block offsets are both 16-byte aligned).  The P blocks then travel in one
+// all-to-all (block g -> rank g).  Streams 2 x 4 bytes per list element.
+__global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, int32_t *dst, int64_t block_words) {
+  const gs_sample_header *h = ws.hdr;
+  __shared__ int32_t s_src[GS_MAX_LAYERS * GS_NUM_FIELDS], s_len[GS_MAX_LAYERS * GS_NUM_FIELDS],
+      s_dst[GS_MAX_LAYERS * GS_NUM_FIELDS];
+  __shared__ int64_t s_total;
+  __shared__ int32_t s_edges;
+  const int g = blockIdx.y, L = ws.L, ns = L * GS_NUM_FIELDS;
+  int32_t *blk = dst + (int64_t)g * block_words;
+  const int status = h->status ? h->status : h->late_status;
+  if (threadIdx.x == 0) {
+    int64_t at = GS_PART_HEADER_WORDS;
+    int32_t edges = 0;
+    for (int k = 0; k < ns; k++) {
+      const gs_span sp = status == 0 ? h->field[k / GS_NUM_FIELDS][g][k % GS_NUM_FIELDS] : gs_span{0, 0};
+      s_src[k] = sp.off;
+      s_len[k] = sp.len;
+      s_dst[k] = (int32_t)min(at, (int64_t)0x7FFFFFF0);
+      at += ((int64_t)sp.len + 3) & ~3ll;
+      if (k % GS_NUM_FIELDS == GS_F_CSR_INDICES) edges += sp.len;
+    }
+    s_total = at;
+    s_edges = edges;
+  }
+  __syncthreads();
+  const bool fits = s_total <= block_words;
+  if (blockIdx.x == 0) {
+    for (int k = threadIdx.x; k < GS_PART_HEADER_WORDS; k += GS_TPB) {
+      int32_t v = 0;
+      if (k == 0) v = (int32_t)GS_PART_MAGIC;
+      else if (k == 1) v = status != 0 ? status : (fits ? 0 : (int32_t)GS_ERR_OVERFLOW);
+      else if (k == 2) v = g;
+      else if (k == 3) v = L;
+      else if (k == 4) v = ws.P;
+      else if (k == 5) v = h->n_seeds;
+      else if (k == 6) v = (int32_t)(uint32_t)(h->batch_index & 0xFFFFFFFFull);
+      else if (k == 7) v = (int32_t)(uint32_t)(h->batch_index >> 32);
+      else if (k == 8) v = (int32_t)min(s_total, (int64_t)0x7FFFFFFF);
+      else if (k == 9) v = s_edges;
+      else if (k >= 16 && k < 16 + 2 * ns) {
+        const int j = (k - 16) >> 1;
+        v = ((k - 16) & 1) ? s_len[j] : s_dst[j];
+      }
+      blk[k] = v;
+    }
+  }
+  if (!fits || status != 0) return;
+  const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
+  for (int k = 0; k < ns; k++) {
+    const int n4 = (s_len[k] + 3) >> 2;  // the padding words of a span belong to it in both layouts
+    const int4 *src = reinterpret_cast<const int4 *>(ws.slab + s_src[k]);
+    int4 *out = reinterpret_cast<int4 *>(blk + s_dst[k]);
+    for (int i = tid; i < n4; i += nth) out[i] = src[i];
+  }
 }
 
 __global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
@@ -1094,6 +1169,9 @@ void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float
                           cudaStream_t st) {
   (void)rows;
   k_gather_ids<<<grid, GS_TPB, 0, st>>>(FeatSrc{feat, slot_of, host_rows}, dim, div, ids, n, out);
+}
+void gs_launch_pack_parts(const GsWs &ws, int32_t *dst, int64_t block_words, int grid_x, cudaStream_t st) {
+  k_pack_parts<<<dim3(grid_x, ws.P), GS_TPB, 0, st>>>(ws, dst, block_words);
 }
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
   k_fill_u32<<<1184, 256, 0, st>>>(p, n, v);

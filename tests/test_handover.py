@@ -1,0 +1,174 @@
+"""Split-parallel hand-over (cslicer/handover.py): every rank slices whole
+minibatches, part g of each sample travels to rank g in one all-to-all.
+
+CPU: the block format against its host restatement, and a world_size-2 gloo run
+in which the parts come from the oracle.  GPU: `gs_slicer_pack_parts` (own kernel)
+against the sample it packs, on one device and -- with >= 2 GPUs -- over NCCL."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FAN = [15, 10, 5]
+
+
+def _oracle_parts(orc_sample, g):
+    return [{k: v for k, v in layer[g].items()} for layer in orc_sample["layers"]]
+
+
+def test_block_format_round_trip_and_overflow():
+    from cslicer import _native as N
+    from cslicer.handover import HEADER_WORDS, PartBlock, pack_block_numpy, part_words
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    orc = O.OracleSlicer(ip, ix, FAN, 4, O.RNG_PHILOX, seed=9)
+    seeds = np.random.default_rng(1).permutation(ip.size - 1)[:128]
+    want = orc.slice(seeds, (5 << 32) | 7)
+    for g in range(4):
+        fl = _oracle_parts(want, g)
+        need = part_words(fl)
+        assert need >= HEADER_WORDS and need % 4 == 0
+        b = PartBlock(pack_block_numpy(fl, g, 4, seeds.size, (5 << 32) | 7, need + 64))
+        assert (b.part, b.num_layers, b.num_parts, b.n_seeds) == (g, 3, 4, 128)
+        assert b.batch_index == (5 << 32) | 7 and b.words == need
+        assert b.edges == sum(len(x["csr_indices"]) for x in fl)
+        for l in range(3):
+            for name in N.FIELDS:
+                assert np.array_equal(b.field(l, name), fl[l][name]), (g, l, name)
+        with pytest.raises(RuntimeError, match="overflow"):
+            PartBlock(pack_block_numpy(fl, g, 4, seeds.size, 0, need - 4))
+    with pytest.raises(RuntimeError, match="magic"):
+        PartBlock(np.zeros(HEADER_WORDS, dtype=np.int32))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _gloo_worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from cslicer import _native as N
+    from cslicer.handover import PartBlock, pack_block_numpy, part_words
+    from cslicer.sharding import rank_batch_ids
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=3)
+    n = ip.size - 1
+    orc = O.OracleSlicer(ip, ix, FAN, world, O.RNG_PHILOX, seed=11)
+    perm = np.random.default_rng(2).permutation(n)
+    batches = [perm[i * 96:(i + 1) * 96] for i in range(2 * world)]
+    ok = True
+    for k in range(2):                                   # round k: rank r slices batch k*world + r
+        b = int(rank_batch_ids(2 * world, rank, world)[k])
+        mine = orc.slice(batches[b], b)
+        words = 4 * ((max(part_words(_oracle_parts(mine, g)) for g in range(world)) * 3 // 2 + 3) // 4)
+        w = torch.tensor([words])
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)         # equal splits: one block size for the round
+        words = int(w[0])
+        send = torch.from_numpy(np.stack([pack_block_numpy(_oracle_parts(mine, g), g, world, 96, b, words)
+                                          for g in range(world)]))
+        recv = torch.empty_like(send)
+        dist.all_to_all_single(recv, send)
+        for src in range(world):
+            blk = PartBlock(recv[src].numpy())
+            want = orc.slice(batches[k * world + src], k * world + src)
+            ok &= blk.part == rank and blk.batch_index == k * world + src
+            for l in range(len(FAN)):
+                for name in N.FIELDS:
+                    ok &= bool(np.array_equal(blk.field(l, name), want["layers"][l][rank][name]))
+    out.put((rank, ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_gloo_ranks_receive_their_part_of_every_minibatch():
+    import torch.multiprocessing as mp
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+        assert p.exitcode == 0
+    got = dict(out.get() for _ in range(world))
+    assert got == {0: True, 1: True}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,fan,batch", [(4, [15, 10, 5], 512), (8, [10, 10], 256), (3, [-1, 5], 128), (1, [5], 64)])
+def test_pack_parts_matches_the_sample_and_the_oracle(P, fan, batch):
+    import torch
+    from cslicer import _native as N
+    from cslicer.engine import Graph, Slicer
+    from cslicer.handover import HEADER_WORDS, PartBlock, pack_parts
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=4)
+    n = ip.size - 1
+    g = Graph(ip, ix)
+    sl = Slicer(g, fan, P, max_batch=batch, num_slots=2, num_streams=2, seed=31)
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=31)
+    rng = np.random.default_rng(6)
+    for bi in (0, 1, (3 << 32) | 9):
+        seeds = rng.permutation(n)[:batch]
+        slot = sl.submit(seeds, bi)
+        words = 4 * (sl.slab_capacity_words() // 4 + HEADER_WORDS)
+        dst = torch.empty((P, words), dtype=torch.int32, device="cuda:0")
+        pack_parts(sl, slot, dst, torch.cuda.current_stream().cuda_stream)   # before wait: ordered on the slot's stream
+        host = dst.cpu().numpy()
+        v = sl.wait(slot)
+        want = orc.slice(seeds, bi)
+        for q in range(P):
+            b = PartBlock(host[q])
+            assert (b.part, b.num_layers, b.num_parts, b.n_seeds, b.batch_index) == (q, len(fan), P, batch, bi)
+            for l in range(len(fan)):
+                for name in N.FIELDS:
+                    a = b.field(l, name)
+                    assert np.array_equal(a, v.numpy(l, q, name)), (q, l, name)
+                    assert np.array_equal(a, want["layers"][l][q][name]), (q, l, name)
+            assert b.edges == sum(v.field_len(l, q, "csr_indices") for l in range(len(fan)))
+        # a block that is too small says so instead of writing past its end
+        small = torch.full((P, HEADER_WORDS + 8), -7, dtype=torch.int32, device="cuda:0")
+        guard = small.clone()
+        pack_parts(sl, slot, small, torch.cuda.current_stream().cuda_stream)
+        sh = small.cpu().numpy()
+        if max(PartBlock(host[q]).words for q in range(P)) > HEADER_WORDS + 8:
+            q = int(np.argmax([PartBlock(host[q]).words for q in range(P)]))
+            assert sh[q][1] == N.ERR_OVERFLOW
+            assert np.array_equal(sh[q][HEADER_WORDS:], guard.cpu().numpy()[q][HEADER_WORDS:])
+            with pytest.raises(RuntimeError, match="overflow"):
+                PartBlock(sh[q])
+        v.release()
+    with pytest.raises(N.SlicerError):
+        pack_parts(sl, 0, torch.empty((P, HEADER_WORDS + 2), dtype=torch.int32, device="cuda:0"))
+    sl.close()
+    g.close()
+
+
+@pytest.mark.gpu
+def test_hand_over_between_real_ranks_nccl():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29547")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                        "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port", "29547",
+                        os.path.join(HERE, "handover_rank_main.py")], env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
