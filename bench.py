@@ -404,6 +404,13 @@ def own_arm(args):
                 out["reference_config"] = {"unavailable": f"{type(e).__name__}: {e}"}
     dev.close()
     hst.close()
+    if dist is not None and not args.no_hand_over:
+        try:
+            ho = hand_over_line(args, torch, dist, g, n, local, rank, world)
+        except Exception as e:  # context only; never fail the bench line on it
+            ho = {"unavailable": f"{type(e).__name__}: {e}"}
+        if out is not None:
+            out["hand_over"] = ho
     g.close()
     if dist is not None and not args.no_partitioned:
         try:
@@ -417,6 +424,85 @@ def own_arm(args):
         dist.destroy_process_group()
     if out is not None:
         emit(out)
+
+
+def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=64):
+    """Split-parallel hand-over at N > 1: every rank slices its own
+    minibatches with `world` parts on the replicated topology, packs the parts
+    (gs_slicer_pack_parts) and ONE all-to-all over NVLink per round delivers part g
+    of `world` minibatches to rank g -- what the split-parallel training step
+    consumes (python/train.py:120-160), at the throughput of the replicated
+    slicer.  -> dict for the bench line (rank 0), None elsewhere."""
+    from cslicer import _native as N
+    from cslicer.engine import Slicer
+    from cslicer.handover import HEADER_WORDS, PartBlock, PartScatter
+    from cslicer.sharding import reduce_job
+    sl = Slicer(g, FANOUTS, num_parts=world, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams,
+                seed=7, grid_ctas=args.grid_ctas, host_output=False)
+    batches = seed_batches(n, 64, rank, world)  # rank r slices batches r, r + world, ...
+    # one block size for the job: the largest part of a probe minibatch on any rank + 25 %
+    slot = sl.submit(batches[0][1], batches[0][0])
+    h = sl.wait_header(slot)
+    need = max(HEADER_WORDS + sum((h.field[l][q][f].len + 3) & ~3 for l in range(len(FANOUTS))
+                                  for f in range(N.NUM_FIELDS)) for q in range(world))
+    slab_words = int(h.slab_used)
+    sl.release(slot)
+    t = torch.tensor([need], dtype=torch.int64, device=f"cuda:{local}")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    block_words = (int(t[0]) * 5 // 4 + 3) & ~3
+    depth = args.slots
+    ps = PartScatter(sl, dist, block_words, depth=depth)
+
+    def run(k):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        inflight, last = [], None
+        e0.record()
+        for i in range(k):
+            if len(inflight) == depth:
+                slot, tk = inflight.pop(0)
+                sl.wait_header(slot)
+                sl.release(slot)
+                ps.collect(tk, parse=False)
+            bi, seeds = batches[i % len(batches)]
+            slot = sl.submit(seeds, bi)
+            inflight.append((slot, ps.post(slot)))
+        for slot, tk in inflight:
+            sl.wait_header(slot)
+            sl.release(slot)
+            last = ps.collect(tk, parse=False)
+        e1.record(ps.stream)
+        e1.synchronize()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1), last
+    run(2 * rounds)
+    dist.barrier()
+    torch.cuda.synchronize()
+    ms, last = run(steps * rounds)
+    dist.barrier()
+    ms, _ = reduce_job(dist, f"cuda:{local}", ms, [0])
+    # what arrived last: part `rank` of the last round's minibatch of every source rank
+    hdr = last[:, :HEADER_WORDS].cpu().numpy()
+    k_last = (steps * rounds - 1) % len(batches)
+    for src in range(world):
+        b = PartBlock(last[src], hdr[src])
+        want = seed_batches(n, 64, src, world)[k_last][0]
+        assert b.part == rank and b.batch_index == want, (b.part, b.batch_index, want)
+    out = None
+    if rank == 0:
+        total = steps * rounds * world
+        sent = ps.nvlink_bytes_per_round()
+        out = {"value": round(total / (ms * 1e-3), 2),
+               "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
+               "ranks": world, "parts": world, "rounds_in_flight": depth,
+               "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
+               "nvlink_bytes_sent_per_rank_per_round": int(sent),
+               "nvlink_gbs_per_rank": round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
+               "exchange": "gs_slicer_pack_parts (own kernel, slot stream) + all_to_all_single of equal, "
+                           "self-describing blocks (NCCL, own stream, overlapped with slicing)"}
+    ps = None
+    sl.close()
+    return out
 
 
 def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32, shard=None):
@@ -743,6 +829,8 @@ def main():
     ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
     ap.add_argument("--partitioned-shards", action="store_true",
                     help="N > 1: only the partitioned slicer, graph generated shard by shard (config 5 at scale)")
+    ap.add_argument("--no-hand-over", action="store_true",
+                    help="N > 1: skip the split-parallel hand-over (slice anywhere, part g -> rank g) measurement")
     ap.add_argument("--no-partitioned", action="store_true",
                     help="N > 1: skip the extra partitioned-mode (graph sharded by owner) measurement")
     args = ap.parse_args()
