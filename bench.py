@@ -451,7 +451,39 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     block_words = (int(t[0]) * 5 // 4 + 3) & ~3
     depth = args.slots
-    ps = PartScatter(sl, dist, block_words, depth=depth)
+    from cslicer.handover import PeerScatter
+    results = {}
+    for kind in ("peer_stores", "nccl_all_to_all"):
+        ps = (PeerScatter if kind == "peer_stores" else PartScatter)(sl, dist, block_words, depth=depth)
+        results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n)
+        sent = ps.nvlink_bytes_per_round()
+        if hasattr(ps, "close"):
+            ps.close()
+        ps = None
+    out = None
+    if rank == 0:
+        total = steps * rounds * world
+        ms = results["peer_stores"]
+        out = {"value": round(total / (ms * 1e-3), 2),
+               "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
+               "ranks": world, "parts": world, "rounds_in_flight": depth,
+               "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
+               "nvlink_bytes_sent_per_rank_per_round": int(sent),
+               "nvlink_gbs_per_rank": round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
+               "exchange": "gs_slicer_scatter_parts: the packing kernel's own 16-byte stores into the owner "
+                           "ranks' receive buffers (CUDA IPC over NVLink), one 4-byte all-reduce per round as "
+                           "the barrier; overlapped with slicing",
+               "same_with_nccl_all_to_all": {
+                   "value": round(total / (results["nccl_all_to_all"] * 1e-3), 2),
+                   "exchange": "gs_slicer_pack_parts into a send buffer + all_to_all_single of equal blocks"}}
+    sl.close()
+    return out
+
+
+def _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n):
+    from cslicer.handover import HEADER_WORDS, PartBlock
+    from cslicer.sharding import reduce_job
+    release = getattr(ps, "release", lambda tk: None)
 
     def run(k):
         torch.cuda.synchronize()
@@ -464,13 +496,15 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
                 sl.wait_header(slot)
                 sl.release(slot)
                 ps.collect(tk, parse=False)
+                release(tk)
             bi, seeds = batches[i % len(batches)]
             slot = sl.submit(seeds, bi)
             inflight.append((slot, ps.post(slot)))
         for slot, tk in inflight:
             sl.wait_header(slot)
             sl.release(slot)
-            last = ps.collect(tk, parse=False)
+            last = ps.collect(tk, parse=False).clone()
+            release(tk)
         e1.record(ps.stream)
         e1.synchronize()
         torch.cuda.synchronize()
@@ -488,21 +522,7 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
         b = PartBlock(last[src], hdr[src])
         want = seed_batches(n, 64, src, world)[k_last][0]
         assert b.part == rank and b.batch_index == want, (b.part, b.batch_index, want)
-    out = None
-    if rank == 0:
-        total = steps * rounds * world
-        sent = ps.nvlink_bytes_per_round()
-        out = {"value": round(total / (ms * 1e-3), 2),
-               "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
-               "ranks": world, "parts": world, "rounds_in_flight": depth,
-               "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
-               "nvlink_bytes_sent_per_rank_per_round": int(sent),
-               "nvlink_gbs_per_rank": round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
-               "exchange": "gs_slicer_pack_parts (own kernel, slot stream) + all_to_all_single of equal, "
-                           "self-describing blocks (NCCL, own stream, overlapped with slicing)"}
-    ps = None
-    sl.close()
-    return out
+    return ms
 
 
 def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32, shard=None):

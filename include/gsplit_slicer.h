@@ -223,6 +223,23 @@ int gs_slicer_release(gs_slicer *s, int32_t slot);
 int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_t block_words,
                          void *consumer_stream);
 
+/* Fused form of the hand-over: block g is written STRAIGHT into dst_blocks[g] -- a
+ * device pointer that may be PEER memory (a buffer of rank g mapped with
+ * gs_ipc_open), so the parts cross NVLink inside the packing kernel's own 16-byte
+ * stores and no send buffer or library collective touches the payload.
+ * dst_blocks: host array of num_parts device pointers (16-byte aligned).
+ * after_stream (cudaStream_t, may be NULL = none): the pack first waits for the work
+ * queued on it so far (the barrier of the round that last used these buffers). */
+int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks,
+                            int64_t block_words, void *after_stream, void *consumer_stream);
+
+/* Device buffers another process can map (cudaIpcGetMemHandle / OpenMemHandle):
+ * handle = 64 bytes.  gs_ipc_open enables peer access to the owner's GPU. */
+int gs_ipc_alloc(int device, int64_t bytes, void **dev_ptr, void *handle_out);
+int gs_ipc_open(int device, const void *handle, void **dev_ptr);
+int gs_ipc_close(int device, void *dev_ptr);
+int gs_ipc_free(int device, void *dev_ptr);
+
 /* Diagnostics: run one minibatch eagerly (no graph) on slot 0 with a CUDA event
  * between kernels; ms[i] receives the duration of launch i, names[i] a static
  * string.  Returns the number of launches through *n_out (<= cap). */

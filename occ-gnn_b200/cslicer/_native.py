@@ -28,7 +28,8 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_slicer_slab_capacity", "gs_reference_shuffle", "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
-           "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts",
+           "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts", "gs_slicer_scatter_parts",
+           "gs_ipc_alloc", "gs_ipc_open", "gs_ipc_close", "gs_ipc_free",
            # partitioned mode (one rank per GPU)
            "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
            "gs_pslicer_connect_ipc", "gs_pslicer_connect_local", "gs_pslicer_ready",
@@ -124,6 +125,12 @@ def lib():
     L.gs_slicer_slab_capacity.restype = C.c_int64
     L.gs_slicer_slab_capacity.argtypes = [C.c_void_p]
     L.gs_slicer_pack_parts.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
+    L.gs_slicer_scatter_parts.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.c_int64,
+                                          C.c_void_p, C.c_void_p]
+    L.gs_ipc_alloc.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
+    L.gs_ipc_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.gs_ipc_close.argtypes = [C.c_int, C.c_void_p]
+    L.gs_ipc_free.argtypes = [C.c_int, C.c_void_p]
     L.gs_reference_shuffle.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     L.gs_features_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                      C.POINTER(C.c_void_p)]

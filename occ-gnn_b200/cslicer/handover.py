@@ -146,3 +146,123 @@ class PartScatter:
     def nvlink_bytes_per_round(self):
         """bytes this rank sends to peers per round (the local block does not travel)"""
         return 4 * self.block_words * (self.world - 1)
+
+
+class _DevWords:
+    """__cuda_array_interface__ carrier for an int32 device buffer this module owns."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": "<i4",
+                                         "data": (int(ptr), False), "version": 2, "strides": None}
+
+
+class PeerScatter:
+    """The hand-over with the exchange fused into the packing kernel: every rank's
+    receive buffers are mapped into every other rank (CUDA IPC, handles all-gathered
+    once through torch.distributed), and `gs_slicer_scatter_parts` writes block g of
+    a sample straight into rank g's buffer -- the parts cross NVLink inside the
+    kernel's own 16-byte stores; no send buffer, no library collective on the
+    payload.  What is left for the library is a 4-byte all-reduce per round, used as
+    the barrier that tells a rank all of its blocks have landed.
+
+        k = ps.post(slot)        # scatter the slot's sample + barrier (async; every rank calls it)
+        blocks = ps.collect(k)   # [PartBlock of source rank 0, 1, ...]
+        ps.release(k)            # the blocks of round k may be overwritten
+
+    `depth` rounds may be un-released when `post` is called.  Ordering, all on the
+    device: round X lands in buffer X % (depth + 1); a rank's pack for round X waits
+    (stream wait) for its barrier X - 1, whose completion means every rank has
+    queued barrier X - 1 -- behind the releases it had made by then, i.e. of every
+    round <= X - 1 - depth, which includes the round this buffer held."""
+
+    def __init__(self, slicer, dist, block_words, depth=2, group=None):
+        import torch
+        self.slicer, self.dist, self.group = slicer, dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if slicer.num_parts != self.world:
+            raise ValueError(f"hand-over needs num_parts == world size ({slicer.num_parts} != {self.world})")
+        self.block_words = _pad4(block_words)
+        if self.block_words < HEADER_WORDS:
+            raise ValueError("block_words smaller than a block header")
+        self.device = slicer.graph.device
+        dev = torch.device("cuda", self.device)
+        self.depth, self.nbuf = int(depth), int(depth) + 1
+        nbytes = 4 * self.nbuf * self.world * self.block_words
+        base, handle = C.c_void_p(), (C.c_char * 64)()
+        N.check(N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle))
+        self._base = base.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self._peer = []
+        for q in range(self.world):
+            if q == self.rank:
+                self._peer.append(self._base)
+            else:
+                p = C.c_void_p()
+                N.check(N.lib().gs_ipc_open(self.device, handles[q], C.byref(p)))
+                self._peer.append(p.value)
+        # my block of round-buffer k lands in [k][rank] of every peer's arena
+        self._dst = []
+        for k in range(self.nbuf):
+            arr = (C.c_void_p * self.world)()
+            for q in range(self.world):
+                arr[q] = self._peer[q] + 4 * (k * self.world + self.rank) * self.block_words
+            self._dst.append(arr)
+        self.recv = torch.as_tensor(_DevWords(self._base, (self.nbuf, self.world, self.block_words)), device=dev)
+        self.stream = torch.cuda.Stream(device=dev)
+        self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._posted = 0
+        self._released = set()
+        self._torch = torch
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group)  # every arena is mapped everywhere before the first store
+
+    def post(self, slot):
+        torch = self._torch
+        r = self._posted
+        if r - self.depth >= 0 and (r - self.depth) not in self._released:
+            raise RuntimeError(f"round {r - self.depth} must be released before round {r} is posted "
+                               f"(depth={self.depth})")
+        self._released.discard(r - self.depth - 1)
+        k = r % self.nbuf
+        st = self.stream.cuda_stream
+        N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
+                                                C.c_void_p(st), C.c_void_p(st)))
+        with torch.cuda.stream(self.stream):
+            self.dist.all_reduce(self._flag, group=self.group)  # barrier: 4 bytes; the payload went by stores
+            self.done[k].record(self.stream)
+        self._posted += 1
+        return r
+
+    def collect(self, ticket, parse=True):
+        k = ticket % self.nbuf
+        self.done[k].synchronize()
+        if not parse:
+            return self.recv[k]
+        hdr = self.recv[k][:, :HEADER_WORDS].cpu().numpy()
+        return [PartBlock(self.recv[k][r], hdr[r]) for r in range(self.world)]
+
+    def release(self, ticket):
+        """The consumer is done with round `ticket` (work queued so far on torch's
+        current stream included): its buffer may be overwritten."""
+        torch = self._torch
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.recv.device))
+        self.stream.wait_event(ev)  # this rank's next barrier carries the release to the writers
+        self._released.add(ticket)
+
+    def nvlink_bytes_per_round(self):
+        return 4 * self.block_words * (self.world - 1)
+
+    def close(self):
+        if getattr(self, "_base", None):
+            self._torch.cuda.synchronize(self.recv.device)
+            self.dist.barrier(group=self.group)  # nobody is still storing into a buffer about to go
+            for q, p in enumerate(self._peer):
+                if q != self.rank:
+                    N.lib().gs_ipc_close(self.device, C.c_void_p(p))
+            self.recv = None
+            self.dist.barrier(group=self.group)
+            N.lib().gs_ipc_free(self.device, C.c_void_p(self._base))
+            self._base = None

@@ -71,6 +71,7 @@ struct Slot {
   cudaEvent_t done = nullptr;
   cudaEvent_t chain_done = nullptr;  // copy-engine mirror: kernels of the sample finished
   cudaEvent_t pack_done = nullptr;   // gs_slicer_pack_parts: the part blocks are written
+  cudaEvent_t pack_after = nullptr;  // gs_slicer_scatter_parts: what the pack has to wait for
   int64_t copied = 0;                // ... int32 elements of the slab the DMA of this sample moved
   cudaStream_t stream = nullptr;
   int state = SLOT_FREE;
@@ -301,6 +302,7 @@ int gs_slicer_destroy(gs_slicer *s) {
     if (sl.done) cudaEventDestroy(sl.done);
     if (sl.chain_done) cudaEventDestroy(sl.chain_done);
     if (sl.pack_done) cudaEventDestroy(sl.pack_done);
+    if (sl.pack_after) cudaEventDestroy(sl.pack_after);
     for (void *p : sl.dev) cudaFree(p);
     if (sl.input) cudaFreeHost(sl.input);
     if (sl.seeds) cudaFreeHost(sl.seeds);
@@ -526,6 +528,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     CUS(cudaEventCreateWithFlags(&sl.chain_done, cudaEventDisableTiming));
     CUS(cudaEventCreateWithFlags(&sl.pack_done, cudaEventDisableTiming));
+    CUS(cudaEventCreateWithFlags(&sl.pack_after, cudaEventDisableTiming));
     if (cfg->use_graph) {
       cudaGraph_t graph = nullptr;
       CUS(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
@@ -679,6 +682,25 @@ int gs_slicer_release(gs_slicer *s, int32_t slot) {
   return GS_OK;
 }
 
+static int scatter_parts(gs_slicer *s, int32_t slot, const GsPartDst &dst, int64_t block_words,
+                         void *after_stream, void *consumer_stream) {
+  Slot &sl = s->slots[slot];
+  if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
+  const GsRange trace("gs_slicer_pack_parts");
+  CU(cudaSetDevice(s->g->device));
+  if (after_stream) {
+    CU(cudaEventRecord(sl.pack_after, (cudaStream_t)after_stream));
+    CU(cudaStreamWaitEvent(sl.stream, sl.pack_after, 0));
+  }
+  // on the slot's own stream: after the sample's kernels, before the slot's next sample
+  gs_launch_pack_parts(sl.ws, dst, block_words, std::max(1, s->grid_full / std::max(1, s->cfg.num_parts)),
+                       sl.stream);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(sl.pack_done, sl.stream));
+  CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, sl.pack_done, 0));  // NULL: the default stream waits
+  return GS_OK;
+}
+
 int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_t block_words,
                          void *consumer_stream) {
   if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
@@ -686,16 +708,60 @@ int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_
       ((uintptr_t)dst_device & 15))
     return fail(GS_ERR_INVALID, "pack_parts: dst must be 16-byte aligned, block_words a multiple of 4 and >= %d",
                 (int)GS_PART_HEADER_WORDS);
-  Slot &sl = s->slots[slot];
-  if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
-  const GsRange trace("gs_slicer_pack_parts");
-  CU(cudaSetDevice(s->g->device));
-  // on the slot's own stream: after the sample's kernels, before the slot's next sample
-  gs_launch_pack_parts(sl.ws, dst_device, block_words, std::max(1, s->grid_full / std::max(1, s->cfg.num_parts)),
-                       sl.stream);
-  CU(cudaGetLastError());
-  CU(cudaEventRecord(sl.pack_done, sl.stream));
-  CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, sl.pack_done, 0));  // NULL: the default stream waits
+  GsPartDst dst{};
+  for (int g = 0; g < s->cfg.num_parts; g++) dst.blk[g] = dst_device + (int64_t)g * block_words;
+  return scatter_parts(s, slot, dst, block_words, nullptr, consumer_stream);
+}
+
+int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks, int64_t block_words,
+                            void *after_stream, void *consumer_stream) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
+  if (!dst_blocks || block_words < GS_PART_HEADER_WORDS || (block_words & 3))
+    return fail(GS_ERR_INVALID, "scatter_parts: block_words must be a multiple of 4 and >= %d",
+                (int)GS_PART_HEADER_WORDS);
+  GsPartDst dst{};
+  for (int g = 0; g < s->cfg.num_parts; g++) {
+    if (!dst_blocks[g] || ((uintptr_t)dst_blocks[g] & 15))
+      return fail(GS_ERR_INVALID, "scatter_parts: dst_blocks[%d] must be a 16-byte aligned device pointer", g);
+    dst.blk[g] = dst_blocks[g];
+  }
+  return scatter_parts(s, slot, dst, block_words, after_stream, consumer_stream);
+}
+
+int gs_ipc_alloc(int device, int64_t bytes, void **dev_ptr, void *handle_out) {
+  if (!dev_ptr || !handle_out || bytes <= 0) return fail(GS_ERR_INVALID, "gs_ipc_alloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  CU(cudaSetDevice(device));
+  void *p = nullptr;
+  CU(cudaMalloc(&p, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(GS_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  }
+  memcpy(handle_out, &h, 64);
+  *dev_ptr = p;
+  return GS_OK;
+}
+int gs_ipc_open(int device, const void *handle, void **dev_ptr) {
+  if (!dev_ptr || !handle) return fail(GS_ERR_INVALID, "gs_ipc_open: bad argument");
+  CU(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  CU(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return GS_OK;
+}
+int gs_ipc_close(int device, void *dev_ptr) {
+  if (!dev_ptr) return GS_OK;
+  CU(cudaSetDevice(device));
+  CU(cudaIpcCloseMemHandle(dev_ptr));
+  return GS_OK;
+}
+int gs_ipc_free(int device, void *dev_ptr) {
+  if (!dev_ptr) return GS_OK;
+  CU(cudaSetDevice(device));
+  CU(cudaFree(dev_ptr));
   return GS_OK;
 }
 

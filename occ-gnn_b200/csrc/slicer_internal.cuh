@@ -115,6 +115,7 @@ void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st);
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
                           cudaStream_t st);
-void gs_launch_pack_parts(const GsWs &ws, int32_t *dst, int64_t block_words, int grid_x, cudaStream_t st);
+struct GsPartDst { int32_t *blk[GS_MAX_PARTS]; };  // block g of a hand-over (local or peer memory)
+void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, cudaStream_t st);
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st);
 void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st);

@@ -1060,16 +1060,18 @@ __global__ void GS_BOUNDS k_gather_ids(FeatSrc fs, int dim, int div,
 // Split-parallel hand-over: blockIdx.y = part g.  Every list of part g (all
 // layers, the nine fields) is copied into block g of `dst` behind a span table,
 // 16-byte vectors, consecutive threads on consecutive addresses (slab spans and
-// block offsets are both 16-byte aligned).  The P blocks then travel in one
-// all-to-all (block g -> rank g).  Streams 2 x 4 bytes per list element.
-__global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, int32_t *dst, int64_t block_words) {
+// block offsets are both 16-byte aligned).  Block g is either a piece of a local
+// send buffer (the P blocks then travel in one all-to-all) or rank g's receive
+// buffer itself, mapped over CUDA IPC: then this kernel's stores ARE the
+// exchange.  Streams 2 x 4 bytes per list element.
+__global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, GsPartDst dst, int64_t block_words) {
   const gs_sample_header *h = ws.hdr;
   __shared__ int32_t s_src[GS_MAX_LAYERS * GS_NUM_FIELDS], s_len[GS_MAX_LAYERS * GS_NUM_FIELDS],
       s_dst[GS_MAX_LAYERS * GS_NUM_FIELDS];
   __shared__ int64_t s_total;
   __shared__ int32_t s_edges;
   const int g = blockIdx.y, L = ws.L, ns = L * GS_NUM_FIELDS;
-  int32_t *blk = dst + (int64_t)g * block_words;
+  int32_t *blk = dst.blk[g];  // may be peer memory: the stores below then travel over NVLink
   const int status = h->status ? h->status : h->late_status;
   if (threadIdx.x == 0) {
     int64_t at = GS_PART_HEADER_WORDS;
@@ -1170,7 +1172,7 @@ void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float
   (void)rows;
   k_gather_ids<<<grid, GS_TPB, 0, st>>>(FeatSrc{feat, slot_of, host_rows}, dim, div, ids, n, out);
 }
-void gs_launch_pack_parts(const GsWs &ws, int32_t *dst, int64_t block_words, int grid_x, cudaStream_t st) {
+void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, cudaStream_t st) {
   k_pack_parts<<<dim3(grid_x, ws.P), GS_TPB, 0, st>>>(ws, dst, block_words);
 }
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {

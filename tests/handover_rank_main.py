@@ -32,17 +32,33 @@ def main():
     orc = O.OracleSlicer(ip, ix, fan, world, O.RNG_PHILOX, seed=77)   # the checker: any rank can restate any minibatch
     perm = np.random.default_rng(8).permutation(n)
     batches = [perm[(i * batch) % (n - batch):][:batch] for i in range(rounds * world)]
-    ps = PartScatter(sl, dist, block_words=sl.slab_capacity_words() // world + HEADER_WORDS, depth=2)
-    tickets = []
-    for k in range(rounds):                      # two rounds in flight
-        b = k * world + rank
-        slot = sl.submit(batches[b], b)
-        tickets.append(ps.post(slot))
-        sl.release(slot)
-        if k >= 1:
-            _check(ps, tickets[k - 1], k - 1, world, rank, orc, batches, fan, N)
-    _check(ps, tickets[-1], rounds - 1, world, rank, orc, batches, fan, N)
-    dist.barrier()
+    words = sl.slab_capacity_words() // world + HEADER_WORDS
+    for kind in ("nccl all-to-all", "peer stores"):
+        if kind == "peer stores":
+            from cslicer.handover import PeerScatter
+            ps = PeerScatter(sl, dist, block_words=words, depth=2)
+        else:
+            ps = PartScatter(sl, dist, block_words=words, depth=2)
+        tickets = []
+        for k in range(rounds):                      # two rounds in flight
+            b = k * world + rank
+            slot = sl.submit(batches[b], b)
+            tickets.append(ps.post(slot))
+            sl.release(slot)
+            if k >= 1:
+                _check(ps, tickets[k - 1], k - 1, world, rank, orc, batches, fan, N)
+        _check(ps, tickets[-1], rounds - 1, world, rank, orc, batches, fan, N)
+        if kind == "peer stores":
+            try:                                     # discipline: an un-released round blocks the buffer ring
+                for k in range(4):
+                    slot = sl.submit(batches[0], 0)
+                    ps.post(slot)
+                    sl.release(slot)
+                raise AssertionError("post did not refuse to overwrite an un-released round")
+            except RuntimeError:
+                pass
+            ps.close()
+        dist.barrier()
     print(f"rank {rank} ok", flush=True)
     sl.close()
     g.close()
@@ -60,6 +76,8 @@ def _check(ps, ticket, k, world, rank, orc, batches, fan, N):
             for name in N.FIELDS:
                 got = blk.field(l, name).cpu().numpy()
                 assert np.array_equal(got, want["layers"][l][rank][name]), (k, src, l, name)
+    if hasattr(ps, "release"):
+        ps.release(ticket)
 
 
 if __name__ == "__main__":
