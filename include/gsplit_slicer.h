@@ -228,10 +228,10 @@ int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_
  * gs_ipc_open), so the parts cross NVLink inside the packing kernel's own 16-byte
  * stores and no send buffer or library collective touches the payload.
  * dst_blocks: host array of num_parts device pointers (16-byte aligned).
- * after_stream (cudaStream_t, may be NULL = none): the pack first waits for the work
- * queued on it so far (the barrier of the round that last used these buffers). */
+ * after_event (a recorded cudaEvent_t, may be NULL = none): the pack first waits for
+ * it (the barrier after which the owners are done with these buffers). */
 int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks,
-                            int64_t block_words, void *after_stream, void *consumer_stream);
+                            int64_t block_words, void *after_event, void *consumer_stream);
 
 /* Device buffers another process can map (cudaIpcGetMemHandle / OpenMemHandle):
  * handle = 64 bytes.  gs_ipc_open enables peer access to the owner's GPU. */

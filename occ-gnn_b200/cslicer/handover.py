@@ -170,12 +170,14 @@ class PeerScatter:
         ps.release(k)            # the blocks of round k may be overwritten
 
     `depth` rounds may be un-released when `post` is called.  Ordering, all on the
-    device: round X lands in buffer X % (depth + 1); a rank's pack for round X waits
-    (stream wait) for its barrier X - 1, whose completion means every rank has
-    queued barrier X - 1 -- behind the releases it had made by then, i.e. of every
-    round <= X - 1 - depth, which includes the round this buffer held."""
+    device: round X lands in buffer X % nbuf, nbuf = depth + 1 + slack; a rank's pack
+    for round X waits (event wait on the slot's stream) for its own barrier
+    X - 1 - slack, whose completion means every rank has queued that barrier --
+    behind the releases it had made by then, i.e. of every round
+    <= X - 1 - slack - depth = X - nbuf, the round this buffer held.  With slack > 0
+    that barrier is several rounds old, so packs do not queue up behind barriers."""
 
-    def __init__(self, slicer, dist, block_words, depth=2, group=None):
+    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3):
         import torch
         self.slicer, self.dist, self.group = slicer, dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
@@ -186,7 +188,8 @@ class PeerScatter:
             raise ValueError("block_words smaller than a block header")
         self.device = slicer.graph.device
         dev = torch.device("cuda", self.device)
-        self.depth, self.nbuf = int(depth), int(depth) + 1
+        self.depth, self.slack = int(depth), int(slack)
+        self.nbuf = self.depth + 1 + self.slack
         nbytes = 4 * self.nbuf * self.world * self.block_words
         base, handle = C.c_void_p(), (C.c_char * 64)()
         N.check(N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle))
@@ -226,9 +229,10 @@ class PeerScatter:
                                f"(depth={self.depth})")
         self._released.discard(r - self.depth - 1)
         k = r % self.nbuf
-        st = self.stream.cuda_stream
+        after = r - 1 - self.slack  # the barrier behind which every owner released round r - nbuf
+        ev = self.done[after % self.nbuf].cuda_event if after >= 0 and r >= self.nbuf else 0
         N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
-                                                C.c_void_p(st), C.c_void_p(st)))
+                                                C.c_void_p(ev), C.c_void_p(self.stream.cuda_stream)))
         with torch.cuda.stream(self.stream):
             self.dist.all_reduce(self._flag, group=self.group)  # barrier: 4 bytes; the payload went by stores
             self.done[k].record(self.stream)

@@ -1115,7 +1115,16 @@ __global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, GsPartDst dst, i
     const int n4 = (s_len[k] + 3) >> 2;  // the padding words of a span belong to it in both layouts
     const int4 *src = reinterpret_cast<const int4 *>(ws.slab + s_src[k]);
     int4 *out = reinterpret_cast<int4 *>(blk + s_dst[k]);
-    for (int i = tid; i < n4; i += nth) out[i] = src[i];
+    // four independent 16-byte loads in flight per thread before the (possibly remote) stores
+    int i = tid;
+    for (; i + 3 * nth < n4; i += 4 * nth) {
+      const int4 a = src[i], b = src[i + nth], c = src[i + 2 * nth], d = src[i + 3 * nth];
+      out[i] = a;
+      out[i + nth] = b;
+      out[i + 2 * nth] = c;
+      out[i + 3 * nth] = d;
+    }
+    for (; i < n4; i += nth) out[i] = src[i];
   }
 }
 
