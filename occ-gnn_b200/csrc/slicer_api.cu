@@ -58,6 +58,9 @@ namespace {
                   __FILE__, __LINE__);                                                 \
   } while (0)
 
+// tagged dedup table: tag indices start at 1 (index 0 is the fill pattern's tag)
+const uint32_t kEpochStart[2] = {1u, 1u};
+
 enum SlotState { SLOT_FREE = 0, SLOT_BUSY = 1, SLOT_DONE = 2 };
 
 struct Slot {
@@ -452,6 +455,12 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.fslab_cap = s->fslab_cap;
     w.Fcap = (int32_t)s->Fcap;
     w.Ccap = (int32_t)s->Ccap;
+    {  // tagged table when positions leave room for >= 4 samples' worth of tags in a 32-bit entry
+      int S = 1;
+      while (S < 32 && (1ll << S) <= std::max<int64_t>(s->Ccap, cfg->max_batch)) S++;
+      const int64_t ntags = S < 32 ? (1ll << (32 - S)) : 1;
+      w.tag_shift = (GS_TABLE_TAGS && ntags >= 4 * (int64_t)(cfg->num_layers + 1)) ? S : 0;
+    }
     w.ftiles_max = ftiles;
     w.ctiles_max = s->grid;
 #define DA(ptr, n)                                         \
@@ -485,6 +494,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.ctile_cnt, (size_t)GS_NC_MAX * s->grid);
     DA(w.ftile_cnt, (size_t)GS_NF_MAX * ftiles);
     DA(w.tickets, 8);
+    DA(w.epoch, 2);
     if (s->feat) {
       w.feat = s->feat->rows;
       w.feat_slot = s->feat->slot_of;
@@ -500,6 +510,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaMemset(w.hdr, 0, sizeof(gs_sample_header)));
     CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
     CUS(cudaMemset(w.table, 0xFF, (size_t)N * sizeof(uint32_t)));
+    CUS(cudaMemcpy(w.epoch, kEpochStart, sizeof(kEpochStart), cudaMemcpyHostToDevice));
     CUS(cudaMemset(w.kill, 0, (size_t)s->Ccap));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
@@ -599,6 +610,7 @@ static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out)
   if (st != 0) {
     // a sample that stopped half way may have left touched table entries behind
     cudaMemsetAsync(sl.ws.table, 0xFF, (size_t)s->g->num_nodes * sizeof(uint32_t), sl.stream);
+    cudaMemcpyAsync(sl.ws.epoch, kEpochStart, sizeof(kEpochStart), cudaMemcpyHostToDevice, sl.stream);
     cudaMemsetAsync(sl.ws.kill, 0, (size_t)s->Ccap, sl.stream);
     cudaStreamSynchronize(sl.stream);
     if (st == GS_ERR_OVERFLOW)

@@ -22,6 +22,11 @@
 #define GS_CF_PART_SHIFT 4
 
 // Inputs of one minibatch, in pinned mapped host memory (read by k_begin over PCIe).
+// Tagged dedup table (no per-layer / per-sample resets); A/B with -DGS_TABLE_TAGS=0
+#ifndef GS_TABLE_TAGS
+#define GS_TABLE_TAGS 1
+#endif
+
 struct GsInput {
   int32_t n_seeds;
   int32_t want_host;
@@ -50,6 +55,10 @@ struct GsWs {
   // per-slot state
   gs_sample_header *hdr; // device
   uint32_t *table;       // [N] minimum edge-source position of the node in the current layer (GS_INF: none)
+  uint32_t *epoch;       // [2] tagged table: [0] next free tag index, [1] first tag index of the current sample
+  int32_t tag_shift;     // S > 0: table value = (tag << S) | position, newer layers use SMALLER tags, so a
+                         // stale entry loses every red.min and reads as "none": no per-layer / per-sample
+                         // resets, one dense fill every 2^(32-S) / (L+1) samples.  0: untagged (reset each time)
   int32_t *slab;         // sample slab: every bipartite list (mirrored to the host in e2e mode)
   int64_t slab_cap;
   int32_t *fslab;        // frontier slab: frontiers 0..L (device only; read back on demand)

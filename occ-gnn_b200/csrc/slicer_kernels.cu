@@ -90,6 +90,17 @@ __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
   return r < 0 ? r + ws.P : r;
 }
 
+// Tagged dedup table (ws.tag_shift = S > 0).  A sample draws L + 1 consecutive tag
+// indices e (seed claim, then one per layer); the stored tag is ntags - 1 - e, so
+// values written later are SMALLER: red.min overwrites anything left by earlier
+// layers or samples, and a reader that finds another tag sees "no occurrence".
+// Index 0 is never used (its tag is the all-ones fill pattern).
+__device__ __forceinline__ uint32_t table_tag(const GsWs &ws, int use) {
+  if (!ws.tag_shift) return 0u;
+  const uint32_t e = __ldcg(ws.epoch + 1) + (uint32_t)use;
+  return ((1u << (32 - ws.tag_shift)) - 1u - e) << ws.tag_shift;
+}
+
 // ------------------------------------------------------------------ k_begin
 // One CTA.  Resets the sample header, narrows the seed ids (int64, pinned
 // host memory read over PCIe) into the slab as frontier 0.
@@ -97,7 +108,19 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
   gs_sample_header *h = ws.hdr;
   const int n = ws.input->n_seeds;
   __shared__ int s_bad;
-  if (threadIdx.x == 0) s_bad = 0;
+  __shared__ uint32_t s_tag;
+  if (threadIdx.x == 0) {
+    s_bad = 0;
+    s_tag = 0u;
+    if (ws.tag_shift) {
+      const uint32_t ntags = 1u << (32 - ws.tag_shift);
+      uint32_t e0 = ws.epoch[0];
+      if (e0 + (uint32_t)ws.L + 1u > ntags) e0 = 1u;  // out of tags: the previous k_finish refilled the table
+      ws.epoch[1] = e0;
+      ws.epoch[0] = e0 + (uint32_t)ws.L + 1u;
+      s_tag = (ntags - 1u - e0) << ws.tag_shift;
+    }
+  }
   __syncthreads();
   gs_span *spans = &h->field[0][0][0];
   for (int i = threadIdx.x; i < GS_MAX_LAYERS * GS_MAX_PARTS * GS_NUM_FIELDS; i += blockDim.x) {
@@ -123,7 +146,14 @@ __global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
         ws.fslab[i] = (int32_t)v;
         // the table is all-INF between minibatches: a second claim of the same
         // entry is a duplicate seed (k_rows_scan resets the claimed entries)
-        if (atomicCAS(ws.table + v, GS_INF, (uint32_t)i) != GS_INF) s_bad = 1;
+        if (ws.tag_shift) {
+          // every other entry carries a larger tag (or the fill pattern): the min always
+          // takes the claim, and an old value with OUR tag is an earlier claim of this sample
+          const uint32_t old = atomicMin(ws.table + v, s_tag | (uint32_t)i);
+          if (((old ^ s_tag) >> ws.tag_shift) == 0u) s_bad = 1;
+        } else if (atomicCAS(ws.table + v, GS_INF, (uint32_t)i) != GS_INF) {
+          s_bad = 1;
+        }
       }
     }
   __syncthreads();
@@ -271,7 +301,7 @@ __global__ void GS_BOUNDS k_rows_scan(GsWs ws, int layer) {
         const uint32_t o = base + ex;
         ws.off[i] = o;
         if (replay) ws.samp_rank[i] = sbase + sex;
-        tbl.st(nd, GS_INF);
+        if (!ws.tag_shift) tbl.st(nd, GS_INF);  // tagged table: entries of earlier layers are stale by their tag
         for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
           ws.tile_first[tb] = (uint32_t)i;
       }
@@ -308,6 +338,7 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
   constexpr bool replay = RNG == (int)GS_RNG_DRAWS;
   constexpr bool norepl = RNG == (int)GS_RNG_PHILOX_NOREPLACE;
   const uint64_t dbase = h->draw_base[layer];
+  const uint32_t tg = table_tag(ws, 1 + layer);
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int i_lo = (int)ws.tile_first[t];
     const int i_hi = (t + 1 < ntiles) ? (int)ws.tile_first[t + 1] : F - 1;
@@ -392,7 +423,7 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
       if (src[k]) {
         cvv[k] = v[k];
         cf[k] = v[k] != nd1[k] ? 0u : GS_CF_LOOP;
-        if (cf[k] == 0u) tbl.min(v[k], p0 + k);
+        if (cf[k] == 0u) tbl.min(v[k], tg | (p0 + k));
       }
     }
     if (p0 + GS_IPT <= C) {
@@ -441,6 +472,8 @@ __global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
   const uint32_t per_inv = per_inv_ok ? (uint32_t)((0x100000000ull + (uint32_t)per - 1) / (uint32_t)per) : 0u;
   // running class counts of this warp over the CTA's tiles: lane q < P keeps part q
   uint32_t acc_i = 0u, acc_e = 0u, acc_f = 0u;
+  const uint32_t tg = table_tag(ws, 1 + layer);
+  const int tsh = ws.tag_shift;
   if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
   int t0, t1;
@@ -477,6 +510,10 @@ __global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
     for (int k = 0; k < GS_IPT; k++) {
       te[k] = 0u;
       if (!(fl[k] & GS_CF_LOOP)) te[k] = tbl.ld(cv[k]);
+    }
+    if (tsh) {  // this layer's tag -> the position; any other tag -> no occurrence
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) te[k] = ((te[k] ^ tg) >> tsh) == 0u ? (te[k] ^ tg) : GS_INF;
     }
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
@@ -972,7 +1009,17 @@ __global__ void GS_BOUNDS k_finish(GsWs ws) {
   gs_sample_header *h = ws.hdr;
   const Tbl tbl(ws);
   const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
-  if (h->status == 0) {
+  if (h->status == 0 && ws.tag_shift) {
+    // tagged table: nothing to reset, unless the NEXT sample would run out of tags
+    // (k_begin applies the same test and restarts the tag sequence)
+    if (__ldcg(ws.epoch) + (uint32_t)ws.L + 1u > (1u << (32 - ws.tag_shift))) {
+      uint4 *t4 = (uint4 *)ws.table;
+      const int64_t n4 = (int64_t)ws.num_nodes >> 2;
+      const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
+      for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
+      if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
+    }
+  } else if (h->status == 0) {
     const int L = ws.L;
     const int32_t *fl = ws.fslab + h->frontier[L].off;
     const int FL = h->frontier_len[L];

@@ -118,6 +118,39 @@ def test_philox_matches_oracle(fanouts, P, owner, batch, shape):
     g.close()
 
 
+@pytest.mark.parametrize("cand_capacity,what", [(1 << 26, "32 tags: the sequence wraps every 8 samples"),
+                                                (1 << 28, "8 tags < 4 (L + 1): untagged table, reset every sample"),
+                                                (0, "default capacity")])
+def test_tagged_dedup_table_wraps_and_matches_oracle(cand_capacity, what):
+    """The dedup table keeps (tag, position) per node: later layers / samples use smaller
+    tags, so nothing is reset between them and the table is refilled only when a slot runs
+    out of tags.  40 samples on ONE slot cross several refills; duplicate seeds (an error
+    that leaves claims behind) in the middle must not leak into the next sample."""
+    E = _engine()
+    from cslicer import _native as N
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("tiny", seed=13)
+    n = ip.size - 1
+    fan = [10, 5, 5]
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fan, 4, max_batch=128, num_slots=1, num_streams=1, seed=3, cand_capacity=cand_capacity)
+    orc = O.OracleSlicer(ip, ix, fan, 4, O.RNG_PHILOX, seed=3)
+    rng = np.random.default_rng(17)
+    for b in range(40):
+        seeds = rng.permutation(n)[:128 if b % 7 else 33]
+        if b in (11, 30):
+            bad = seeds.copy()
+            bad[5] = bad[50 % bad.size]
+            with pytest.raises(N.SlicerError):
+                sl.slice(bad, b)
+        v = sl.slice(seeds, b)
+        _compare(v, orc.slice(seeds, b))
+        v.release()
+    sl.close()
+    g.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("fanouts,P,shape,batch", [([15, 10, 5], 4, "small", 512), ([10, 10, 10], 8, "tiny", 256),
                                                    ([1, 2, 40], 2, "small", 100), ([-1, 7], 3, "tiny", 64)])
 def test_without_replacement_matches_oracle(fanouts, P, shape, batch):
