@@ -838,8 +838,8 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH, help="seeds per minibatch (config 5: 8192)")
     ap.add_argument("--fanouts", default=",".join(map(str, FANOUTS)))
     ap.add_argument("--mb-per-step", type=int, default=64)
-    ap.add_argument("--slots", type=int, default=8)
-    ap.add_argument("--streams", type=int, default=8)
+    ap.add_argument("--slots", type=int, default=12)
+    ap.add_argument("--streams", type=int, default=12)
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
