@@ -215,7 +215,7 @@ def kernel_bytes(view, P):
         lists = sum(view.field_len(l, g, k) for g in range(P)
                     for k in ("owned_out_nodes", "from_ids", "to_ids", "self_ids_in", "self_ids_out"))
         out[f"rows_count@{l}"] = F * (4 + 16) + F * 12
-        out[f"rows_scan@{l}"] = F * 8 + F * (4 + 4)                       # counts in, off + table reset out
+        out[f"rows_scan@{l}"] = F * 8 + F * 4                             # counts in, off out (tagged table: no reset)
         out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5            # pick + red.min per edge, stream out
         out[f"cand_flags@{l}"] = C * 5 + C * 4 + C * 5 + F * 4             # stream in, table read, stream out, rowa
         out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + C * 4 + F * P * 4   # stream in, lists, irank, rowscan
@@ -235,7 +235,7 @@ def random_accesses(view, P):
         E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
         n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
         csr += F + (C - F)          # indptr[nd], one neighbour pick per non-self candidate
-        tab += F                    # k_rows_scan: entry reset
+        # (no per-row entry reset any more: the table is tagged)
         tab += (C - F)              # k_expand: red.min
         tab += C                    # k_cand_flags: read
         pos += E - n_in             # k_relabel: rank of the first occurrence, by position
