@@ -101,7 +101,8 @@ class PartScatter:
         blocks = ps.collect(k)   # [PartBlock of source rank 0, 1, ...]: part `rank` of R minibatches
 
     The exchange runs on its own stream, so the slicer keeps working on the next
-    minibatches while blocks are in flight."""
+    minibatches while blocks are in flight.  The blocks of a round stay valid until
+    `depth` further rounds have been posted (their buffers are then reused)."""
 
     def __init__(self, slicer, dist, block_words, depth=2, group=None):
         import torch
@@ -168,6 +169,7 @@ class PeerScatter:
         k = ps.post(slot)        # scatter the slot's sample + barrier (async; every rank calls it)
         blocks = ps.collect(k)   # [PartBlock of source rank 0, 1, ...]
         ps.release(k)            # the blocks of round k may be overwritten
+        ps.close()               # collective: unmap the peers' rings, free this rank's
 
     `depth` rounds may be un-released when `post` is called.  Ordering, all on the
     device: round X lands in buffer X % nbuf, nbuf = depth + 1 + slack; a rank's pack
