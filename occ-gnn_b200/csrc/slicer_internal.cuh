@@ -27,6 +27,11 @@
 #define GS_TABLE_TAGS 1
 #endif
 
+// hand-over copy through the bulk-copy engine (cp.async.bulk); A/B with -DGS_PACK_TMA=0
+#ifndef GS_PACK_TMA
+#define GS_PACK_TMA 1
+#endif
+
 struct GsInput {
   int32_t n_seeds;
   int32_t want_host;
@@ -125,6 +130,7 @@ void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
                           cudaStream_t st);
 struct GsPartDst { int32_t *blk[GS_MAX_PARTS]; };  // block g of a hand-over (local or peer memory)
-void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, cudaStream_t st);
+void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, bool tma,
+                          cudaStream_t st);
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st);
 void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st);

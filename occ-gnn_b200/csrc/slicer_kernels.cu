@@ -1111,6 +1111,14 @@ __global__ void GS_BOUNDS k_gather_ids(FeatSrc fs, int dim, int div,
 // send buffer (the P blocks then travel in one all-to-all) or rank g's receive
 // buffer itself, mapped over CUDA IPC: then this kernel's stores ARE the
 // exchange.  Streams 2 x 4 bytes per list element.
+// TMA: a CTA stages 16 KB pieces of the lists in shared memory (coalesced 16-byte
+// loads, four in flight per thread) and ONE thread hands each piece to the bulk-copy
+// engine (cp.async.bulk shared -> global, double-buffered).  The NVLink round trip
+// of a remote store is then the copy engine's business: no warp waits on it, and a
+// grid of one CTA per SM is enough to keep 4.7 MB in flight, so the samples being
+// sliced on the other streams keep their SM slots.
+#define GS_PK_CHUNK 4096  // int32 words per piece
+template <bool TMA>
 __global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, GsPartDst dst, int64_t block_words) {
   const gs_sample_header *h = ws.hdr;
   __shared__ int32_t s_src[GS_MAX_LAYERS * GS_NUM_FIELDS], s_len[GS_MAX_LAYERS * GS_NUM_FIELDS],
@@ -1157,6 +1165,36 @@ __global__ void __launch_bounds__(GS_TPB) k_pack_parts(GsWs ws, GsPartDst dst, i
     }
   }
   if (!fits || status != 0) return;
+  if (TMA) {
+    __shared__ __align__(128) int32_t s_buf[TMA ? 2 : 1][TMA ? GS_PK_CHUNK : 4];
+    const int G = (int)gridDim.x;
+    int it = 0, cbase = 0;  // pieces are dealt round-robin over the part's CTAs
+    for (int k = 0; k < ns; k++) {
+      const int words = (s_len[k] + 3) & ~3;  // the padding words of a span belong to it in both layouts
+      const int nch = (words + GS_PK_CHUNK - 1) / GS_PK_CHUNK;
+      for (int j = ((int)blockIdx.x - cbase % G + G) % G; j < nch; j += G, it++) {
+        const int w0 = j * GS_PK_CHUNK, nw = min(GS_PK_CHUNK, words - w0);
+        int32_t *sb = s_buf[it & 1];
+        // the bulk store that read this buffer two pieces ago must be done reading it
+        if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncthreads();
+        const int4 *src = reinterpret_cast<const int4 *>(ws.slab + s_src[k] + w0);
+        for (int i = threadIdx.x; i < (nw >> 2); i += GS_TPB) reinterpret_cast<int4 *>(sb)[i] = src[i];
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          const uint32_t sa = (uint32_t)__cvta_generic_to_shared(sb);
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                       :: "l"(blk + s_dst[k] + w0), "r"(sa), "r"(nw * 4) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      cbase += nch;
+    }
+    // the block is complete only when every bulk store has been performed
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    return;
+  }
   const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
   for (int k = 0; k < ns; k++) {
     const int n4 = (s_len[k] + 3) >> 2;  // the padding words of a span belong to it in both layouts
@@ -1228,8 +1266,10 @@ void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float
   (void)rows;
   k_gather_ids<<<grid, GS_TPB, 0, st>>>(FeatSrc{feat, slot_of, host_rows}, dim, div, ids, n, out);
 }
-void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, cudaStream_t st) {
-  k_pack_parts<<<dim3(grid_x, ws.P), GS_TPB, 0, st>>>(ws, dst, block_words);
+void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_words, int grid_x, bool tma,
+                          cudaStream_t st) {
+  if (tma) k_pack_parts<true><<<dim3(grid_x, ws.P), GS_TPB, 0, st>>>(ws, dst, block_words);
+  else k_pack_parts<false><<<dim3(grid_x, ws.P), GS_TPB, 0, st>>>(ws, dst, block_words);
 }
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
   k_fill_u32<<<1184, 256, 0, st>>>(p, n, v);
