@@ -157,6 +157,38 @@ class _DevWords:
                                          "data": (int(ptr), False), "version": 2, "strides": None}
 
 
+class RingSchedule:
+    """Host-side bookkeeping of PeerScatter's receive ring (no GPU involved, so the
+    CPU tests can run the protocol against a model of streams and barriers).
+
+    Round X lands in buffer X % nbuf, nbuf = depth + 1 + slack.  `next_post` -> (X,
+    buffer, index of the barrier the pack has to wait for, or None while the ring is
+    still fresh); it refuses to go on while round X - depth is un-released, which is
+    what makes barrier X - 1 - slack carry the release of round X - nbuf."""
+
+    def __init__(self, depth, slack):
+        if depth < 1 or slack < 0:
+            raise ValueError("depth >= 1 and slack >= 0")
+        self.depth, self.slack, self.nbuf = int(depth), int(slack), int(depth) + 1 + int(slack)
+        self.posted = 0
+        self.released = set()
+
+    def next_post(self):
+        r = self.posted
+        if r - self.depth >= 0 and (r - self.depth) not in self.released:
+            raise RuntimeError(f"round {r - self.depth} must be released before round {r} is posted "
+                               f"(depth={self.depth})")
+        self.released.discard(r - self.depth - 1)
+        after = r - 1 - self.slack
+        self.posted += 1
+        return r, r % self.nbuf, (after if r >= self.nbuf else None)
+
+    def release(self, ticket):
+        if not (0 <= ticket < self.posted):
+            raise ValueError("unknown round")
+        self.released.add(ticket)
+
+
 class PeerScatter:
     """The hand-over with the exchange fused into the packing kernel: every rank's
     receive buffers are mapped into every other rank (CUDA IPC, handles all-gathered
@@ -190,8 +222,8 @@ class PeerScatter:
             raise ValueError("block_words smaller than a block header")
         self.device = slicer.graph.device
         dev = torch.device("cuda", self.device)
-        self.depth, self.slack = int(depth), int(slack)
-        self.nbuf = self.depth + 1 + self.slack
+        self.ring = RingSchedule(depth, slack)
+        self.depth, self.slack, self.nbuf = self.ring.depth, self.ring.slack, self.ring.nbuf
         nbytes = 4 * self.nbuf * self.world * self.block_words
         base, handle = C.c_void_p(), (C.c_char * 64)()
         N.check(N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle))
@@ -217,28 +249,19 @@ class PeerScatter:
         self.stream = torch.cuda.Stream(device=dev)
         self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
-        self._posted = 0
-        self._released = set()
         self._torch = torch
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # every arena is mapped everywhere before the first store
 
     def post(self, slot):
         torch = self._torch
-        r = self._posted
-        if r - self.depth >= 0 and (r - self.depth) not in self._released:
-            raise RuntimeError(f"round {r - self.depth} must be released before round {r} is posted "
-                               f"(depth={self.depth})")
-        self._released.discard(r - self.depth - 1)
-        k = r % self.nbuf
-        after = r - 1 - self.slack  # the barrier behind which every owner released round r - nbuf
-        ev = self.done[after % self.nbuf].cuda_event if after >= 0 and r >= self.nbuf else 0
+        r, k, after = self.ring.next_post()  # after: the barrier behind which every owner released round r - nbuf
+        ev = self.done[after % self.nbuf].cuda_event if after is not None else 0
         N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
                                                 C.c_void_p(ev), C.c_void_p(self.stream.cuda_stream)))
         with torch.cuda.stream(self.stream):
             self.dist.all_reduce(self._flag, group=self.group)  # barrier: 4 bytes; the payload went by stores
             self.done[k].record(self.stream)
-        self._posted += 1
         return r
 
     def collect(self, ticket, parse=True):
@@ -256,7 +279,7 @@ class PeerScatter:
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.recv.device))
         self.stream.wait_event(ev)  # this rank's next barrier carries the release to the writers
-        self._released.add(ticket)
+        self.ring.release(ticket)
 
     def nvlink_bytes_per_round(self):
         return 4 * self.block_words * (self.world - 1)

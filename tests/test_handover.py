@@ -172,3 +172,76 @@ def test_hand_over_between_real_ranks_nccl():
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
+
+
+@pytest.mark.parametrize("world,depth,slack", [(2, 1, 0), (2, 2, 3), (4, 3, 1), (8, 2, 0), (3, 4, 2)])
+def test_ring_protocol_never_overwrites_an_unreleased_round(world, depth, slack):
+    """Model of PeerScatter's device-side ordering, run against the real RingSchedule.
+    Every rank has a comm stream (FIFO of release marks and barriers) and packs that
+    wait for one of the rank's own barriers; a barrier completes when it is at the head
+    of EVERY rank's comm stream and the rank's pack of that round is done.  Ranks post,
+    consume and release in random interleavings; whenever a pack runs, the buffer it
+    writes must have been released by every owner -- and the protocol must not stall."""
+    from cslicer.handover import RingSchedule
+    rng = np.random.default_rng(100 * world + 10 * depth + slack)
+    rounds = 60
+    rings = [RingSchedule(depth, slack) for _ in range(world)]
+    nbuf = rings[0].nbuf
+    comm = [[] for _ in range(world)]            # per rank: ("release", X) | ("barrier", X)
+    packs = [dict() for _ in range(world)]       # per rank: round -> barrier index to wait for (or None)
+    pack_done = [set() for _ in range(world)]
+    barrier_done = set()
+    released_on_device = [set() for _ in range(world)]   # release marks the comm stream has passed
+    collected = [0] * world                      # rounds consumed so far (in order)
+    holds = [dict() for _ in range(world)]       # per owner: buffer -> (round, source) payload check
+    for _ in range(200000):
+        progressed = False
+        i = int(rng.integers(world))
+        act = int(rng.integers(4))
+        ring = rings[i]
+        if act == 0 and ring.posted < rounds:    # host: post the next round if the discipline allows
+            if ring.posted - depth < 0 or (ring.posted - depth) in ring.released:
+                r, k, after = ring.next_post()
+                assert k == r % nbuf
+                packs[i][r] = after
+                comm[i].append(("barrier", r))
+                progressed = True
+        elif act == 1:                           # device: run a pack whose barrier has completed
+            ready = [r for r, after in packs[i].items()
+                     if r not in pack_done[i] and (after is None or after in barrier_done)]
+            if ready:                            # packs sit on different slot streams: any order
+                r = int(rng.choice(ready))
+                for g in range(world):           # the store into owner g's buffer r % nbuf
+                    prev = r - nbuf
+                    assert prev < 0 or prev in released_on_device[g], (i, g, r, prev)
+                    holds[g][(r % nbuf, i)] = r
+                pack_done[i].add(r)
+                progressed = True
+        elif act == 2:                           # device: comm streams advance
+            while comm[i] and comm[i][0][0] == "release":
+                released_on_device[i].add(comm[i].pop(0)[1])
+                progressed = True
+            heads = [c[0] if c else None for c in comm]
+            if heads[i] and heads[i][0] == "barrier":
+                r = heads[i][1]
+                if all(h == ("barrier", r) for h in heads) and all(r in pack_done[g] for g in range(world)):
+                    for c in comm:
+                        c.pop(0)
+                    barrier_done.add(r)
+                    progressed = True
+        else:                                    # host: consume + release the oldest delivered round
+            r = collected[i]
+            if r in barrier_done:
+                for src in range(world):         # what the consumer reads is that round's payload
+                    assert holds[i][(r % nbuf, src)] == r, (i, src, r, holds[i][(r % nbuf, src)])
+                comm[i].append(("release", r))
+                ring.release(r)
+                collected[i] += 1
+                progressed = True
+        if all(c == rounds for c in collected):
+            break
+    assert all(c == rounds for c in collected), f"protocol stalled: {collected}"
+    with pytest.raises(RuntimeError):            # discipline: `depth` un-released rounds at most
+        ring = RingSchedule(depth, slack)
+        for _ in range(depth + 1):
+            ring.next_post()
