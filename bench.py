@@ -398,6 +398,17 @@ def own_arm(args):
                 out["feature_gather"] = feature_gather_line(ip, ix, g, args, torch, batches, peak)
             except Exception as e:
                 out["feature_gather"] = {"unavailable": f"{type(e).__name__}: {e}"}
+            try:  # the contiguous-range owner map next to id % P (owner read from a byte table)
+                from cslicer.synth import owner_range
+                rsl = Slicer(g, FANOUTS, host_output=False, owner=owner_range(n, P), **kw)
+                run_pipeline(rsl, batches, 3, mbs, torch)
+                ms_r, _, edges_r, _ = run_pipeline(rsl, batches, 3, mbs, torch)
+                rsl.close()
+                out["owner_range"] = {"value": round(3 * mbs / (ms_r * 1e-3), 2), "unit": "minibatches/s",
+                                      "sampled_edges_per_s": round(edges_r / (ms_r * 1e-3), 1),
+                                      "note": "same workload, owner = id*P//N from a uint8[N] table, samples left in HBM"}
+            except Exception as e:
+                out["owner_range"] = {"unavailable": f"{type(e).__name__}: {e}"}
             try:
                 out["reference_config"] = reference_config(ip, ix, g, args, torch)
             except Exception as e:  # context only; never fail the bench line on it
