@@ -464,10 +464,15 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
     depth = args.slots
     from cslicer.handover import PeerScatter
     results = {}
+    sent = 4 * block_words * (world - 1)
     for kind in ("peer_stores", "nccl_all_to_all"):
-        ps = (PeerScatter if kind == "peer_stores" else PartScatter)(sl, dist, block_words, depth=depth)
+        try:  # constructor failures are collective (raised on every rank): the other arm still runs
+            ps = (PeerScatter if kind == "peer_stores" else PartScatter)(sl, dist, block_words, depth=depth)
+        except RuntimeError as e:
+            log(f"[bench] hand-over arm {kind} unavailable: {e}")
+            results[kind] = float("nan")
+            continue
         results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n)
-        sent = ps.nvlink_bytes_per_round()
         if hasattr(ps, "close"):
             ps.close()
         ps = None
@@ -475,17 +480,23 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
     if rank == 0:
         total = steps * rounds * world
         ms = results["peer_stores"]
-        out = {"value": round(total / (ms * 1e-3), 2),
+
+        def rate(t):  # NaN (arm unavailable or its delivery check failed) -> null: the line stays strict JSON
+            return None if t != t else round(total / (t * 1e-3), 2)
+        out = {"value": rate(ms),
                "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
+               "verified": "every rank received part `rank` of the expected minibatch from every source "
+                           "(a mismatch or an unavailable arm turns its value into null)",
                "ranks": world, "parts": world, "rounds_in_flight": depth,
                "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
                "nvlink_bytes_sent_per_rank_per_round": int(sent),
-               "nvlink_gbs_per_rank": round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
-               "exchange": "gs_slicer_scatter_parts: the packing kernel's own 16-byte stores into the owner "
-                           "ranks' receive buffers (CUDA IPC over NVLink), one 4-byte all-reduce per round as "
-                           "the barrier; overlapped with slicing",
+               "nvlink_gbs_per_rank": None if ms != ms else round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
+               "exchange": "gs_slicer_scatter_parts: the packing kernel writes every block straight into its "
+                           "owner rank's receive buffer (CUDA IPC over NVLink; cp.async.bulk pieces from 4 parts "
+                           "up, 16-byte stores below), one 4-byte all-reduce per round as the barrier; "
+                           "overlapped with slicing",
                "same_with_nccl_all_to_all": {
-                   "value": round(total / (results["nccl_all_to_all"] * 1e-3), 2),
+                   "value": rate(results["nccl_all_to_all"]),
                    "exchange": "gs_slicer_pack_parts into a send buffer + all_to_all_single of equal blocks"}}
     sl.close()
     return out
@@ -529,11 +540,18 @@ def _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, ra
     # what arrived last: part `rank` of the last round's minibatch of every source rank
     hdr = last[:, :HEADER_WORDS].cpu().numpy()
     k_last = (steps * rounds - 1) % len(batches)
+    ok = 1
     for src in range(world):
-        b = PartBlock(last[src], hdr[src])
-        want = seed_batches(n, 64, src, world)[k_last][0]
-        assert b.part == rank and b.batch_index == want, (b.part, b.batch_index, want)
-    return ms
+        try:
+            b = PartBlock(last[src], hdr[src])
+            want = seed_batches(n, 64, src, world)[k_last][0]
+            ok &= int(b.part == rank and b.batch_index == want)
+        except Exception:
+            ok = 0
+    # collective verdict: a rank must not leave the sequence of collectives on its own
+    t = torch.tensor([ok], dtype=torch.int32, device=f"cuda:{local}")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return ms if int(t[0]) == 1 else float("nan")
 
 
 def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32, shard=None):

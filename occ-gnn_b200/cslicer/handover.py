@@ -226,18 +226,40 @@ class PeerScatter:
         self.depth, self.slack, self.nbuf = self.ring.depth, self.ring.slack, self.ring.nbuf
         nbytes = 4 * self.nbuf * self.world * self.block_words
         base, handle = C.c_void_p(), (C.c_char * 64)()
-        N.check(N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle))
-        self._base = base.value
+        rc = N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle)
+        self._base = base.value if rc == N.OK else None
         handles = [None] * self.world
-        dist.all_gather_object(handles, bytes(handle.raw), group=group)
-        self._peer = []
+        dist.all_gather_object(handles, bytes(handle.raw) if rc == N.OK else b"", group=group)
+        if any(len(h) != 64 for h in handles):  # collective verdict: every rank raises, none is left waiting
+            if self._base:
+                N.lib().gs_ipc_free(self.device, C.c_void_p(self._base))
+                self._base = None
+            raise RuntimeError(f"receive ring of {nbytes} bytes could not be allocated / exported on rank(s) "
+                               f"{[q for q, h in enumerate(handles) if len(h) != 64]}")
+        self._peer, err = [], None
         for q in range(self.world):
             if q == self.rank:
                 self._peer.append(self._base)
-            else:
-                p = C.c_void_p()
+                continue
+            p = C.c_void_p()
+            try:
                 N.check(N.lib().gs_ipc_open(self.device, handles[q], C.byref(p)))
-                self._peer.append(p.value)
+            except N.SlicerError as e:  # keep going: the verdict below is collective
+                err = err or e
+            self._peer.append(p.value)
+        # every rank learns whether ALL mappings succeeded, so that a failure raises on every
+        # rank instead of leaving the others inside the next collective
+        ok = torch.tensor([0 if err else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok[0]) == 0:
+            for q, p in enumerate(self._peer):
+                if q != self.rank and p:
+                    N.lib().gs_ipc_close(self.device, C.c_void_p(p))
+            dist.barrier(group=group)
+            N.lib().gs_ipc_free(self.device, C.c_void_p(self._base))
+            self._base = None
+            raise RuntimeError(f"peer mapping of the receive rings failed on some rank ({err or 'a peer'}): "
+                               "use PartScatter (NCCL all-to-all) on this machine")
         # my block of round-buffer k lands in [k][rank] of every peer's arena
         self._dst = []
         for k in range(self.nbuf):
