@@ -1,5 +1,8 @@
 #!/bin/bash
 # GPU call: A/B of register-cap variants + what the pipelined chain saturates (range replay).
+# Build the variants first, in the build container (nvcc cross-compiles, the .so files travel):
+#   bash tools/build_variants.sh base:"" minb6:"-DGS_MINB=6" minb8:"-DGS_MINB=8"
+# Other A/B switches: -DGS_TABLE_TAGS=0 (untagged dedup table), -DGS_PACK_TMA=0 (hand-over by plain stores).
 set -u
 out=gpurun_out/c1; mkdir -p $out
 V=occ-gnn_b200/cslicer/variants
