@@ -194,8 +194,8 @@ class PeerScatter:
     receive buffers are mapped into every other rank (CUDA IPC, handles all-gathered
     once through torch.distributed), and `gs_slicer_scatter_parts` writes block g of
     a sample straight into rank g's buffer -- the parts cross NVLink inside the
-    kernel's own 16-byte stores; no send buffer, no library collective on the
-    payload.  What is left for the library is a 4-byte all-reduce per round, used as
+    kernel itself (16-byte stores, or cp.async.bulk pieces from 4 parts up); no send
+    buffer, no library collective on the payload.  What is left for the library is a 4-byte all-reduce per round, used as
     the barrier that tells a rank all of its blocks have landed.
 
         k = ps.post(slot)        # scatter the slot's sample + barrier (async; every rank calls it)

@@ -702,7 +702,9 @@ static int scatter_parts(gs_slicer *s, int32_t slot, const GsPartDst &dst, int64
   // >= 4 parts (most stores remote): bulk-copy engine, one CTA per SM over all parts keeps
   // ~4.7 MB in flight (4 B200: 25.2 K minibatches/s against 24.7 K with plain stores);
   // fewer parts: plain 16-byte stores, 8 CTAs per SM (2 B200: 14.2 K against 13.2 K)
-  const bool tma = GS_PACK_TMA && s->cfg.num_parts >= 4;
+  // GSPLIT_PACK_TMA=0/1 in the environment overrides the choice (tests force both paths on 2 ranks)
+  const char *ov = getenv("GSPLIT_PACK_TMA");
+  const bool tma = GS_PACK_TMA && (ov ? atoi(ov) != 0 : s->cfg.num_parts >= 4);
   const int pack_ctas = tma ? std::max(2, s->grid_full / 8) : s->grid_full;
   gs_launch_pack_parts(sl.ws, dst, block_words, std::max(1, pack_ctas / std::max(1, s->cfg.num_parts)), tma,
                        sl.stream);

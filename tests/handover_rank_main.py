@@ -33,8 +33,10 @@ def main():
     perm = np.random.default_rng(8).permutation(n)
     batches = [perm[(i * batch) % (n - batch):][:batch] for i in range(rounds * world)]
     words = sl.slab_capacity_words() // world + HEADER_WORDS
-    for kind in ("nccl all-to-all", "peer stores"):
-        if kind == "peer stores":
+    for kind in ("nccl all-to-all", "peer stores", "peer stores, bulk-copy engine"):
+        # 2 ranks would use plain stores: force the cp.async.bulk path over NVLink as well
+        os.environ["GSPLIT_PACK_TMA"] = "1" if kind.endswith("engine") else "0"
+        if kind.startswith("peer stores"):
             from cslicer.handover import PeerScatter
             ps = PeerScatter(sl, dist, block_words=words, depth=2)
         else:
@@ -48,7 +50,7 @@ def main():
             if k >= 1:
                 _check(ps, tickets[k - 1], k - 1, world, rank, orc, batches, fan, N)
         _check(ps, tickets[-1], rounds - 1, world, rank, orc, batches, fan, N)
-        if kind == "peer stores":
+        if kind.startswith("peer stores"):
             try:                                     # discipline: an un-released round blocks the buffer ring
                 for k in range(4):
                     slot = sl.submit(batches[0], 0)
@@ -59,6 +61,7 @@ def main():
                 pass
             ps.close()
         dist.barrier()
+    os.environ.pop("GSPLIT_PACK_TMA", None)
     print(f"rank {rank} ok", flush=True)
     sl.close()
     g.close()
