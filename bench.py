@@ -188,16 +188,16 @@ def run_pipeline(sl, batches, steps, mb_per_step, torch, timed=True):
 
 
 def kernel_profile(sl, batches, reps=8):
-    """Eager runs with a CUDA event between launches (outside the timed region)
-    -> {kernel@layer: mean ms}, launch order preserved."""
+    """Eager runs of ONE minibatch with a CUDA event between launches (outside the
+    timed region) -> [(kernel@layer, mean ms)], launch order preserved."""
     acc, order = {}, []
     for r in range(reps):
         bi, seeds = batches[r % len(batches)]
-        layer, seen = -1, {}
+        layer = -1
         for name, ms in sl.profile(seeds, bi):
-            if name == "rows_count":
+            if name.startswith("rows"):
                 layer += 1
-            key = name if name in ("begin", "finish") else f"{name}@{layer}"
+            key = name if "finish" in name else f"{name}@{layer}"
             if r == 0:
                 order.append(key)
             acc[key] = acc.get(key, 0.0) + ms
@@ -205,23 +205,25 @@ def kernel_profile(sl, batches, reps=8):
 
 
 def kernel_bytes(view, P):
-    """Compulsory bytes of each kernel launch for one sample (own in/out, w=4)."""
+    """Bytes each launch of one sample must move (its own inputs and outputs, w=4;
+    DESIGN section 5) -- the per-kernel roofline numerator."""
     out = {}
-    for l in range(view.num_layers):
+    L = view.num_layers
+    rel = {}
+    for l in range(L):
         F, Fn, C = view.frontier_len[l], view.frontier_len[l + 1], view.cand_len[l]
         E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
         n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
         n_out = sum(view.field_len(l, g, "out_nodes") for g in range(P))
         lists = sum(view.field_len(l, g, k) for g in range(P)
                     for k in ("owned_out_nodes", "from_ids", "to_ids", "self_ids_in", "self_ids_out"))
-        out[f"rows_count@{l}"] = F * (4 + 16) + F * 12
-        out[f"rows_scan@{l}"] = F * 8 + F * 4                             # counts in, off out (tagged table: no reset)
-        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5            # pick + red.min per edge, stream out
-        out[f"cand_flags@{l}"] = C * 5 + C * 4 + C * 5 + F * 4             # stream in, table read, stream out, rowa
-        out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + C * 4 + F * P * 4   # stream in, lists, irank, rowscan
-        out[f"front_count@{l}"] = F * (4 + P * 4 + 1)
-        out[f"front_apply@{l}"] = F * (4 + 1 + 4 + 4) + n_out * 4 + (2 * n_out + lists) * 4
-        out[f"relabel@{l}"] = E * (4 + 4) + (E - n_in) * 4
+        rel[l] = E * (4 + 4) + (E - n_in) * 4                             # csr_indices in/out + rank lookups
+        rows = F * (4 + 16) + F * (16 + 4 + 4 + 4 + 4 + 4)                 # frontier + indptr pair in; rowinfo, off, selfrank, ea, rowhas, table mark out
+        out[f"rows@{l}" if l == 0 else f"rows+relabel@{l}"] = rows + (rel[l - 1] if l else 0)
+        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5            # rowinfo + off, pick + atom.min per edge, stream out
+        out[f"cand@{l}"] = (C * 5 + C * 4 + F * 12                        # stream in, table / ea read, rowhas + selfrank + frontier
+                            + (Fn + n_in + E + 2 * n_out + lists) * 4)    # every list of the layer out
+    out["relabel+finish"] = rel[L - 1]
     return out
 
 
@@ -236,10 +238,9 @@ def random_accesses(view, P):
         n_in = sum(view.field_len(l, g, "in_nodes") for g in range(P))
         csr += F + (C - F)          # indptr[nd], one neighbour pick per non-self candidate
         # (no per-row entry reset any more: the table is tagged)
-        tab += (C - F)              # k_expand: red.min
-        tab += C                    # k_cand_flags: read
-        pos += E - n_in             # k_relabel: rank of the first occurrence, by position
-        pos += F                    # k_front_apply: self_ids_in
+        tab += (C - F)              # k_expand: atom.min
+        tab += C                    # k_cand: read (table, or the row-indexed minimum)
+        pos += E - n_in             # relabel: rank of the first occurrence, by position
     return csr, tab, pos
 
 
@@ -263,7 +264,7 @@ def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
 # One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.97 MB read +
 # 2.70 MB written to DRAM (cold L2; the 12 MB candidate stream it writes stays in L2) against
 # 35.9 MB algorithmic -- the excess is 32-byte sectors moved for 4-byte neighbour picks.
-NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "expand@2", "bytes": 89627904,
+NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "r1:expand@2", "bytes": 89627904,
                "source": "profiles/r1_ncu_expand_full_raw.csv (ncu --set full, tools/capture_evidence.sh)"}
 
 
@@ -291,7 +292,7 @@ def own_arm(args):
     P, mbs = args.parts, args.mb_per_step
     batches = seed_batches(n, max(64, mbs), rank, world)
     kw = dict(num_parts=P, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
-              grid_ctas=args.grid_ctas, l2_hints=not args.no_l2_hints)
+              grid_ctas=args.grid_ctas, l2_hints=not args.no_l2_hints, group_size=args.group)
     dev = Slicer(g, FANOUTS, host_output=False, **kw)
     hst = Slicer(g, FANOUTS, host_output=True, host_copy_engine=not args.host_stores, **kw)
     peaks = {}
@@ -378,6 +379,7 @@ def own_arm(args):
                "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
                                       f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
                           "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
+                          "minibatches_per_launch": args.group,
                           "sharding": "whole minibatches per rank, graph topology replicated",
                           "cpu_binding": (f"rank 0 on {len(bound)} cores next to its GPU" if bound else "none"),
                           "l2": f"inputs larger than L2: graph {(ip.size * 8 + ix.size * 4) / 1e9:.2f} GB + per-slot tables/workspaces "
@@ -389,7 +391,8 @@ def own_arm(args):
                        "d2h_bytes_per_step": int(slab_e2e * 4 / (args.steps * world)) + mbs * HEADER_BYTES,
                        "ms_per_step": round(ms_e2e / args.steps, 4),
                        "sampled_edges_per_s": round(edges_e2e / (ms_e2e * 1e-3), 1)},
-               "gpu_launches": dev.launches_per_sample * args.steps * mbs,
+               "gpu_launches": dev.launches_per_sample * args.steps * mbs // args.group,
+               "launches_per_minibatch": round(dev.launches_per_sample / args.group, 2),
                "wall_s": {"value_region": round(wall_dev, 4), "e2e_region": round(wall_e2e, 4)},
                "clocks": clk, "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
@@ -736,6 +739,20 @@ def reference_config(ip, ix, g, args, torch):
             "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
 
 
+def _time_gather(F, ids, torch, reps=5):
+    """The gather kernel alone on the ids of one sample's input block (the fused
+    gather shares its launch with the last relabel, so it is timed standalone)."""
+    F.gather(ids)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        F.gather(ids)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
 def feature_gather_line(ip, ix, g, args, torch, batches, peak):
     """BASELINE config 4's other half: the fused input-feature gather (602-dim
     fp32, seed 4321) -- rows of the last layer's in_nodes_g, part after part,
@@ -752,12 +769,9 @@ def feature_gather_line(ip, ix, g, args, torch, batches, peak):
     ms, _, edges, _ = run_pipeline(sl, batches, 4, 12, torch)
     v = sl.slice(batches[0][1], batches[0][0])
     nrows = v.feature_rows
+    ids = torch.cat([v.tensor(v.num_layers - 1, q, "in_nodes") for q in range(args.parts)]).clone()
     v.release()
-    tk = []
-    for r in range(6):
-        prof = dict(sl.profile(batches[r][1], batches[r][0]))
-        tk.append(prof["gather_features"])
-    k_ms = float(np.mean(tk[1:]))
+    k_ms = _time_gather(F, ids, torch)
     nbytes = 2 * nrows * dim * 4
     sl.close()
     F.close()
@@ -786,8 +800,8 @@ def cached_gather(ip, ix, g, args, rows, batches, fraction=0.25):
         ids = np.concatenate([v.tensor(v.num_layers - 1, q, "in_nodes").cpu().numpy()
                               for q in range(args.parts)])
         v.release()
-        tk = [dict(sl.profile(batches[r][1], batches[r][0]))["gather_features"] for r in range(4)]
-        k_ms = float(np.mean(tk[1:]))
+        import torch
+        k_ms = _time_gather(F, torch.from_numpy(ids).cuda(), torch, reps=3)
         hr = hit_rate(cache, ids, ip.size - 1)
         miss_bytes = (1.0 - hr) * ids.size * rows.shape[1] * 4
         sl.close()
@@ -869,6 +883,8 @@ def main():
     ap.add_argument("--mb-per-step", type=int, default=64)
     ap.add_argument("--slots", type=int, default=12)
     ap.add_argument("--streams", type=int, default=12)
+    ap.add_argument("--group", type=int, default=1,
+                    help="minibatches per launch sequence (gs_config.group_size); must divide --slots")
     ap.add_argument("--grid-ctas", type=int, default=2, help="CTAs per SM of a full-machine launch")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -10,12 +10,15 @@
  * gs_last_error() describes the last failure on the calling thread.
  *
  * Execution model: a slicer owns `num_slots` sample slots (the reference's
- * bounded queue, WorkerPool.cpp:23-24).  gs_slicer_submit() enqueues one
- * minibatch on a slot's CUDA stream as a single pre-captured CUDA graph
- * (seed upload, every kernel, result download) and returns at once;
- * gs_slicer_wait() blocks until that slot's sample is complete;
- * gs_slicer_release() hands the slot back.  There is no CPU fallback: without a
- * CUDA device gs_graph_create() fails with GS_ERR_CUDA.
+ * bounded queue, WorkerPool.cpp:23-24), in groups of `group_size` consecutive
+ * slots.  gs_slicer_submit() stages one minibatch in the next slot of the group
+ * being filled; the submit that fills the group launches it -- ONE pre-captured
+ * CUDA graph of 3 L + 1 kernels for all `group_size` minibatches (blockIdx.y =
+ * member) on the group's stream -- and returns at once.  gs_slicer_wait() blocks
+ * until that slot's sample is complete (launching a partly filled group first);
+ * gs_slicer_release() hands the slot back.  group_size = 1 is the reference's
+ * one-batch-at-a-time behaviour.  There is no CPU fallback: without a CUDA
+ * device gs_graph_create() fails with GS_ERR_CUDA.
  */
 #ifndef GSPLIT_SLICER_H
 #define GSPLIT_SLICER_H
@@ -26,7 +29,7 @@ extern "C" {
 
 #define GS_MAX_LAYERS 8
 #define GS_MAX_PARTS 8
-#define GS_ABI_VERSION 1
+#define GS_ABI_VERSION 2
 
 typedef enum {
   GS_OK = 0,
@@ -119,12 +122,15 @@ typedef struct {
   int32_t grid_ctas;               /* CTAs per SM of a full-machine launch; 0 = 4 */
   int32_t use_graph;               /* 1 (default via gs_config_default): CUDA-graph replay */
   int32_t l2_hints;                /* 1 (default): L2 eviction-priority hints, tables kept resident */
-  int32_t host_copy_engine;        /* host_output mirror: 1 (default) = one DMA per sample on a dedicated copy
-                                    * stream, sized from the running maximum of slab_used (the rare remainder is
-                                    * topped up in gs_slicer_wait); 0 = 16-byte stores from the last kernel.
-                                    * Measured D2H ceilings on this box: copy engine 57.0 GB/s, SM or TMA stores 52.3 */
+  int32_t host_copy_engine;        /* kept for ABI stability; the host_output mirror is always one DMA per sample on
+                                    * a dedicated copy stream, sized from the running maximum of slab_used (the rare
+                                    * remainder is topped up in gs_slicer_wait).  Measured D2H ceilings on this box:
+                                    * copy engine 57.0 GB/s, stores issued by SMs or TMA 52.3 (the round-1 alternative) */
   gs_features *features;           /* optional: fuse the input-feature gather into every sample */
   int64_t feature_rows_capacity;   /* 0 = derive (rows of the last layer's in_nodes, all parts) */
+  int32_t group_size;              /* minibatches per launch sequence (1..16, must divide num_slots; GS_RNG_DRAWS
+                                    * forces 1): the kernels of `group_size` consecutive slots run as ONE grid each */
+  int32_t reserved0;
 } gs_config;
 
 
@@ -180,9 +186,15 @@ int gs_slicer_destroy(gs_slicer *s);
 
 /* Replaces WorkerPool::run's push of one batch (WorkerPool.cpp:41-49) and the
  * Slicer::run iteration that consumes it (slicer.cpp:120-139).  seeds_host:
- * n int64 node ids, distinct.  Returns GS_ERR_BUSY when every slot is in use. */
+ * n int64 node ids, distinct.  Returns GS_ERR_BUSY when no group can take the
+ * batch: every slot in use, or -- group_size > 1 -- the next member slot of the
+ * group being filled is still held (groups are refilled in slot order). */
 int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n,
                      uint64_t batch_index, int32_t *slot_out);
+/* Launch the group being filled now, with the members staged so far (the stop
+ * sentinel of WorkerPool.cpp:52-55: no more batches will come).  gs_slicer_wait
+ * / release / pack_parts on a staged slot do this implicitly. */
+int gs_slicer_flush(gs_slicer *s);
 
 /* Replaces CSlicer::getSample / ConQueue::pop_object (pyfrontend.cpp:73-78,
  * conqueue.h:42-60) for one slot: blocks until the sample is complete, then
@@ -255,7 +267,8 @@ int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n,
  * times with reset only on the first call.  Host-only; no device work. */
 int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
 
-/* Number of kernel launches one submitted minibatch performs. */
+/* Number of kernel launches one launch sequence performs (3 L + 1), shared by the
+ * group_size minibatches of a group. */
 int gs_slicer_launches_per_sample(const gs_slicer *s);
 /* Device bytes held by one slot / by the slicer. */
 int64_t gs_slicer_slot_bytes(const gs_slicer *s);

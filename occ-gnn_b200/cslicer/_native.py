@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 # GSPLIT_SLICER_LIB: another build of the same library (A/B of compile-time variants)
 LIB_PATH = os.environ.get("GSPLIT_SLICER_LIB") or os.path.join(HERE, "libgsplit_slicer.so")
 
-MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 1
+MAX_LAYERS, MAX_PARTS, ABI_VERSION = 8, 8, 2
 RNG_PHILOX, RNG_DRAWS, RNG_PHILOX_NOREPLACE = 0, 1, 2
 OK, ERR_INVALID, ERR_CUDA, ERR_BUSY, ERR_OVERFLOW, ERR_SEED, ERR_STATE, ERR_PEER = range(8)
 OWNER_MOD, OWNER_RANGE = 0, 1
@@ -24,7 +24,7 @@ NUM_FIELDS = len(FIELDS)
 # every symbol include/gsplit_slicer.h declares (tests check the export table)
 SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_create",
            "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
-           "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_wait", "gs_slicer_slab",
+           "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_flush", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_slicer_slab_capacity", "gs_reference_shuffle", "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
@@ -66,7 +66,8 @@ class Config(C.Structure):
                 ("frontier_capacity", C.c_int64), ("cand_capacity", C.c_int64),
                 ("slab_capacity", C.c_int64), ("grid_ctas", C.c_int32), ("use_graph", C.c_int32),
                 ("l2_hints", C.c_int32), ("host_copy_engine", C.c_int32),
-                ("features", C.c_void_p), ("feature_rows_capacity", C.c_int64)]
+                ("features", C.c_void_p), ("feature_rows_capacity", C.c_int64),
+                ("group_size", C.c_int32), ("reserved0", C.c_int32)]
 
 
 class PConfig(C.Structure):
@@ -110,6 +111,7 @@ def lib():
     L.gs_slicer_destroy.argtypes = [C.c_void_p]
     L.gs_slicer_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64,
                                    C.POINTER(C.c_int32)]
+    L.gs_slicer_flush.argtypes = [C.c_void_p]
     L.gs_slicer_wait.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.POINTER(SampleHeader))]
     L.gs_slicer_slab.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                  C.POINTER(C.c_void_p)]

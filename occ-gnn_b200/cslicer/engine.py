@@ -235,9 +235,12 @@ class Slicer:
     def __init__(self, graph, fanouts, num_parts=4, max_batch=4096, num_slots=4, num_streams=4,
                  seed=0, owner=None, draws=None, host_output=True, use_graph=True,
                  frontier_capacity=0, cand_capacity=0, slab_capacity=0, grid_ctas=0, l2_hints=True,
-                 features=None, feature_rows_capacity=0, replace=True, host_copy_engine=True):
+                 features=None, feature_rows_capacity=0, replace=True, host_copy_engine=True, group_size=1):
         """replace=False: the picks of a row are distinct (GS_RNG_PHILOX_NOREPLACE,
-        the Python sibling's DGL sampling rule, python/utils/sampler.py:187)."""
+        the Python sibling's DGL sampling rule, python/utils/sampler.py:187).
+        group_size: minibatches per launch sequence (must divide num_slots): submit()
+        stages, the submit that fills a group launches it; wait() on a staged slot
+        launches the partly filled group.  A replayed draw stream forces 1."""
         L = N.lib()
         self.graph = graph
         cfg = N.Config()
@@ -257,6 +260,8 @@ class Slicer:
         cfg.slab_capacity, cfg.grid_ctas = int(slab_capacity), int(grid_ctas)
         cfg.l2_hints = int(bool(l2_hints))
         cfg.host_copy_engine = int(bool(host_copy_engine))
+        cfg.group_size = 1 if draws is not None else int(group_size)
+        self.group_size = cfg.group_size
         self.features = features
         if features is not None:
             cfg.features = features._h
@@ -289,6 +294,10 @@ class Slicer:
         N.check(N.lib().gs_slicer_submit(self._h, s.ctypes.data, s.size, int(batch_index),
                                          C.byref(slot)))
         return slot.value
+
+    def flush(self):
+        """Launch the group being filled with the minibatches staged so far."""
+        N.check(N.lib().gs_slicer_flush(self._h))
 
     def wait(self, slot):
         hp = C.POINTER(N.SampleHeader)()
@@ -329,7 +338,7 @@ class Slicer:
     def profile(self, seeds, batch_index=0):
         """-> list of (kernel name, ms) for one eager run with events between launches."""
         s = np.ascontiguousarray(seeds, dtype=np.int64)
-        cap = 4 + 8 * N.MAX_LAYERS
+        cap = 4 + 3 * N.MAX_LAYERS
         ms = (C.c_float * cap)()
         names = (C.c_char_p * cap)()
         n = C.c_int32(0)

@@ -58,10 +58,10 @@ namespace {
                   __FILE__, __LINE__);                                                 \
   } while (0)
 
-// tagged dedup table: tag indices start at 1 (index 0 is the fill pattern's tag)
-const uint32_t kEpochStart[2] = {1u, 1u};
+// per-slot state at creation / after a reset: first tag index, first scan epoch
+const GsState kStateStart = {1u, 1u, {0u, 0u}};
 
-enum SlotState { SLOT_FREE = 0, SLOT_BUSY = 1, SLOT_DONE = 2 };
+enum SlotState { SLOT_FREE = 0, SLOT_STAGED = 1, SLOT_BUSY = 2, SLOT_DONE = 3 };
 
 struct Slot {
   GsWs ws{};
@@ -70,13 +70,23 @@ struct Slot {
   int64_t *seeds = nullptr; // pinned, mapped
   gs_sample_header *hdr_host = nullptr;
   int32_t *slab_host = nullptr;
-  cudaGraphExec_t exec = nullptr;
   cudaEvent_t done = nullptr;
-  cudaEvent_t chain_done = nullptr;  // copy-engine mirror: kernels of the sample finished
   cudaEvent_t pack_done = nullptr;   // gs_slicer_pack_parts: the part blocks are written
   int64_t copied = 0;                // ... int32 elements of the slab the DMA of this sample moved
-  cudaStream_t stream = nullptr;
+  int group = 0;
   int state = SLOT_FREE;
+};
+
+// `members` consecutive slots share ONE launch sequence (grid.y = member): the
+// kernels of small layers then fill the machine, and a minibatch costs
+// (3 L + 1) / members launches.
+struct Group {
+  int first = 0, members = 0;        // slots [first, first + members)
+  GsWs *wsv = nullptr;               // device copy of the members' GsWs
+  cudaStream_t stream = nullptr;
+  cudaGraphExec_t exec = nullptr;    // the full group
+  cudaEvent_t chain_done = nullptr;  // kernels of the group's last launch finished
+  int staged = 0;                    // members staged for the next launch
 };
 
 }  // namespace
@@ -99,15 +109,18 @@ struct gs_features {
   int64_t n_cached = 0;
 };
 
+
 struct gs_slicer {
   gs_graph *g = nullptr;
   gs_features *feat = nullptr;
   int64_t feat_cap_rows = 0;
   gs_config cfg{};
-  int grid = 0;                       // CTAs of a full-machine launch
-  int grid_full = 0;                  // 8 CTAs per SM: full occupancy for the streaming gather
-  int grid_rows[GS_MAX_LAYERS] = {0};  // per layer: enough CTAs for the largest possible frontier
-  int grid_cand[GS_MAX_LAYERS] = {0};  // ... and candidate stream (static upper bounds)
+  int group_size = 1;
+  int grid = 0;                          // CTAs per member of a full-machine launch
+  int grid_gather = 0;                   // feature gather role of the last launch (streaming: wants every warp slot)
+  int grid_rows[GS_MAX_LAYERS] = {0};    // per layer: enough CTAs for the largest possible frontier
+  int grid_cand[GS_MAX_LAYERS] = {0};    // ... candidate stream
+  int grid_relabel[GS_MAX_LAYERS] = {0}; // ... edge list (static upper bounds)
   int64_t Fcap = 0, Ccap = 0, slab_cap = 0, fslab_cap = 0;
   uint8_t *owner = nullptr;
   uint32_t *draws = nullptr;
@@ -117,7 +130,9 @@ struct gs_slicer {
                                        // DMAs lose ~12 % of the link: 50 vs 57 GB/s measured)
   int64_t mirror_est = 0;              // running estimate of slab_used (int32 elements) + margin
   std::vector<Slot> slots;
-  int next_slot = 0;
+  std::vector<Group> groups;
+  int cur_group = -1;                  // group being filled by gs_slicer_submit (-1: none)
+  int next_group = 0;
   int64_t slot_bytes = 0;
 };
 
@@ -134,12 +149,11 @@ int dev_alloc(Slot &sl, T **p, size_t n, int64_t *bytes) {
   return GS_OK;
 }
 
-// The static launch sequence of one minibatch.  `ev` (optional) receives one
-// event after every launch, for gs_slicer_profile.
-int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEvent_t> *ev,
-                   std::vector<const char *> *names) {
-  static const char *kNames[] = {"rows_count", "rows_scan",   "expand",      "cand_flags",
-                                 "cand_apply", "front_count", "front_apply", "relabel"};
+// The static launch sequence of `members` minibatches of one group (grid.y =
+// member): 3 launches per layer + 1.  `ev` (optional) receives one event after
+// every launch, for gs_slicer_profile.
+int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::vector<cudaEvent_t> *ev,
+                  std::vector<const char *> *names) {
   auto mark = [&](const char *nm) -> int {
     if (ev) {
       cudaEvent_t e;
@@ -151,34 +165,18 @@ int enqueue_sample(gs_slicer *s, Slot &sl, cudaStream_t st, std::vector<cudaEven
     return GS_OK;
   };
   int rc;
+  const int L = s->cfg.num_layers;
   if ((rc = mark("start"))) return rc;
-  gs_launch_begin(sl.ws, st);
-  if ((rc = mark("begin"))) return rc;
-  for (int l = 0; l < s->cfg.num_layers; l++) {
-    const int gr = s->grid_rows[l], gc = s->grid_cand[l];
-    gs_launch_rows_count(sl.ws, l, gr, st);
-    if ((rc = mark(kNames[0]))) return rc;
-    gs_launch_rows_scan(sl.ws, l, gr, st);
-    if ((rc = mark(kNames[1]))) return rc;
-    gs_launch_expand(sl.ws, l, gc, st);
-    if ((rc = mark(kNames[2]))) return rc;
-    gs_launch_cand_flags(sl.ws, l, gc, st);
-    if ((rc = mark(kNames[3]))) return rc;
-    gs_launch_cand_apply(sl.ws, l, gc, st);
-    if ((rc = mark(kNames[4]))) return rc;
-    gs_launch_front_count(sl.ws, l, gr, st);
-    if ((rc = mark(kNames[5]))) return rc;
-    gs_launch_front_apply(sl.ws, l, gr, st);
-    if ((rc = mark(kNames[6]))) return rc;
-    gs_launch_relabel(sl.ws, l, gc, st);
-    if ((rc = mark(kNames[7]))) return rc;
+  for (int l = 0; l < L; l++) {
+    gs_launch_rows(gr.wsv, members, l, s->grid_rows[l], l > 0 ? s->grid_relabel[l - 1] : 0, st);
+    if ((rc = mark(l == 0 ? "rows" : "rows+relabel"))) return rc;
+    gs_launch_expand(gr.wsv, members, s->cfg.rng_mode, l, s->grid_cand[l], st);
+    if ((rc = mark("expand"))) return rc;
+    gs_launch_cand(gr.wsv, members, l, s->grid_cand[l], st);
+    if ((rc = mark("cand"))) return rc;
   }
-  if (s->feat) {
-    gs_launch_gather_sample(sl.ws, s->grid_full, st);  // streaming kernel: wants every warp slot
-    if ((rc = mark("gather_features"))) return rc;
-  }
-  gs_launch_finish(sl.ws, s->grid, st);
-  if ((rc = mark("finish"))) return rc;
+  gs_launch_tail(gr.wsv, members, s->grid_relabel[L - 1], s->feat ? s->grid_gather : 0, st);
+  if ((rc = mark(s->feat ? "relabel+gather_features+finish" : "relabel+finish"))) return rc;
   CU(cudaGetLastError());
   return GS_OK;
 }
@@ -217,6 +215,50 @@ void compute_capacities(const gs_config &c, int64_t N, int64_t M, int64_t *Fcap,
   *fslab = fs;
 }
 
+// Launch the group being filled with the members staged so far.  A full group
+// replays its CUDA graph; a partial one (gs_slicer_flush, or a wait on a staged
+// slot) is launched eagerly with grid.y = staged, so members that are not part
+// of the launch -- and whatever their slots still hold -- are not touched.
+int launch_group(gs_slicer *s, Group &gr) {
+  const int m = gr.staged;
+  if (m <= 0) return GS_OK;
+  if (gr.exec && m == gr.members) {
+    CU(cudaGraphLaunch(gr.exec, gr.stream));
+  } else {
+    int rc = enqueue_group(s, gr, m, gr.stream, nullptr, nullptr);
+    if (rc != GS_OK) return rc;
+  }
+  const bool mirror = s->copy_stream != nullptr;
+  if (mirror) {
+    CU(cudaEventRecord(gr.chain_done, gr.stream));
+    CU(cudaStreamWaitEvent(s->copy_stream, gr.chain_done, 0));
+  }
+  for (int j = 0; j < m; j++) {
+    Slot &sl = s->slots[gr.first + j];
+    sl.copied = 0;
+    if (mirror && sl.slab_host) {
+      // mirror with the copy engine: its size must be known now, so move the running
+      // maximum of slab_used (+2 %); gs_slicer_wait tops up the rare remainder
+      sl.copied = std::min<int64_t>(s->slab_cap, s->mirror_est);
+      if (sl.copied > 0)
+        CU(cudaMemcpyAsync(sl.slab_host, sl.ws.slab, (size_t)sl.copied * sizeof(int32_t),
+                           cudaMemcpyDeviceToHost, s->copy_stream));
+      CU(cudaEventRecord(sl.done, s->copy_stream));
+    } else {
+      CU(cudaEventRecord(sl.done, gr.stream));
+    }
+    sl.state = SLOT_BUSY;
+  }
+  gr.staged = 0;
+  s->cur_group = -1;
+  return GS_OK;
+}
+
+int flush_if_staged(gs_slicer *s, Slot &sl) {
+  if (sl.state != SLOT_STAGED) return GS_OK;
+  return launch_group(s, s->groups[sl.group]);
+}
+
 }  // namespace
 
 extern "C" {
@@ -238,6 +280,7 @@ void gs_config_default(gs_config *c) {
   c->use_graph = 1;
   c->l2_hints = 1;
   c->host_copy_engine = 1;
+  c->group_size = 1;
 }
 
 int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
@@ -259,23 +302,56 @@ int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
   g->device = device;
   g->num_nodes = num_nodes;
   g->num_edges = num_edges;
-  CU(cudaMalloc((void **)&g->indptr, (size_t)(num_nodes + 1) * sizeof(int64_t)));
-  CU(cudaMemcpy(g->indptr, indptr_host, (size_t)(num_nodes + 1) * sizeof(int64_t),
-                cudaMemcpyHostToDevice));
-  CU(cudaMalloc((void **)&g->indices, (size_t)std::max<int64_t>(num_edges, 1) * sizeof(int32_t)));
+  // The kernels index indptr[] and the dedup table with the ids they read from
+  // `indices`: a malformed CSR is rejected here, by one device pass over each
+  // array BEFORE the ids are narrowed to int32 (Dataset's checksums compare sums
+  // only, dataset.cpp:27,35).
+  unsigned long long *err = nullptr;
+  int64_t *tmp = nullptr;
+  auto bail = [&](int code) {
+    cudaFree(err);
+    cudaFree(tmp);
+    std::string keep = g_err;
+    gs_graph_destroy(g);
+    g_err = keep;
+    return code;
+  };
+#define CUG(call)                                                                          \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess)                                                                 \
+      return bail(fail(GS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                       __FILE__, __LINE__));                                               \
+  } while (0)
+  CUG(cudaMalloc((void **)&err, 2 * sizeof(unsigned long long)));
+  CUG(cudaMemset(err, 0xFF, 2 * sizeof(unsigned long long)));
+  CUG(cudaMalloc((void **)&g->indptr, (size_t)(num_nodes + 1) * sizeof(int64_t)));
+  CUG(cudaMemcpy(g->indptr, indptr_host, (size_t)(num_nodes + 1) * sizeof(int64_t),
+                 cudaMemcpyHostToDevice));
+  gs_launch_check_indptr(g->indptr, num_nodes, num_edges, err, 0);
+  CUG(cudaGetLastError());
+  CUG(cudaMalloc((void **)&g->indices, (size_t)std::max<int64_t>(num_edges, 1) * sizeof(int32_t)));
   // narrow int64 -> int32 on the device, in bounded chunks
   const int64_t chunk = 1ll << 26;
-  int64_t *tmp = nullptr;
-  CU(cudaMalloc((void **)&tmp, (size_t)std::min(chunk, std::max<int64_t>(num_edges, 1)) *
-                                   sizeof(int64_t)));
+  CUG(cudaMalloc((void **)&tmp, (size_t)std::min(chunk, std::max<int64_t>(num_edges, 1)) *
+                                    sizeof(int64_t)));
   for (int64_t o = 0; o < num_edges; o += chunk) {
     const int64_t n = std::min(chunk, num_edges - o);
-    CU(cudaMemcpy(tmp, indices_host + o, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice));
+    CUG(cudaMemcpy(tmp, indices_host + o, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice));
+    gs_launch_check_ids(tmp, (size_t)n, o, num_nodes, err, 0);
     gs_launch_narrow_ids(tmp, g->indices + o, (size_t)n, 0);
-    CU(cudaGetLastError());
+    CUG(cudaGetLastError());
   }
-  CU(cudaDeviceSynchronize());
-  CU(cudaFree(tmp));
+  unsigned long long bad[2] = {0, 0};
+  CUG(cudaMemcpy(bad, err, sizeof bad, cudaMemcpyDeviceToHost));  // synchronises the default stream
+#undef CUG
+  if (bad[0] != ~0ull)
+    return bail(fail(GS_ERR_INVALID, "indptr is not a non-decreasing sequence inside [0, num_edges]: first bad row %llu",
+                     bad[0] - 1ull));
+  if (bad[1] != ~0ull)
+    return bail(fail(GS_ERR_INVALID, "indices[%llu] lies outside [0, num_nodes)", bad[1] - 1ull));
+  cudaFree(err);
+  cudaFree(tmp);
   *out = g;
   return GS_OK;
 }
@@ -291,18 +367,17 @@ int gs_graph_destroy(gs_graph *g) {
 int64_t gs_graph_num_nodes(const gs_graph *g) { return g ? g->num_nodes : 0; }
 int64_t gs_graph_num_edges(const gs_graph *g) { return g ? g->num_edges : 0; }
 
-}  // extern "C"
-
-extern "C" {
-
 int gs_slicer_destroy(gs_slicer *s) {
   if (!s) return GS_OK;
   cudaSetDevice(s->g->device);
   cudaDeviceSynchronize();
+  for (Group &gr : s->groups) {
+    if (gr.exec) cudaGraphExecDestroy(gr.exec);
+    if (gr.chain_done) cudaEventDestroy(gr.chain_done);
+    cudaFree(gr.wsv);
+  }
   for (Slot &sl : s->slots) {
-    if (sl.exec) cudaGraphExecDestroy(sl.exec);
     if (sl.done) cudaEventDestroy(sl.done);
-    if (sl.chain_done) cudaEventDestroy(sl.chain_done);
     if (sl.pack_done) cudaEventDestroy(sl.pack_done);
     for (void *p : sl.dev) cudaFree(p);
     if (sl.input) cudaFreeHost(sl.input);
@@ -339,6 +414,10 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     return fail(GS_ERR_INVALID, "unknown rng_mode %d", cfg->rng_mode);
   if (cfg->rng_mode == GS_RNG_DRAWS && (!cfg->draws_host || cfg->n_draws == 0))
     return fail(GS_ERR_INVALID, "GS_RNG_DRAWS needs draws_host / n_draws");
+  // replay mode consumes one sequential draw stream: one minibatch at a time, on one stream
+  const int gsz = cfg->rng_mode == GS_RNG_DRAWS ? 1 : std::max(1, cfg->group_size);
+  if (gsz > 16 || cfg->num_slots % gsz != 0)
+    return fail(GS_ERR_INVALID, "group_size=%d must be in [1,16] and divide num_slots=%d", gsz, cfg->num_slots);
   CU(cudaSetDevice(g->device));
 
   gs_slicer *s = new (std::nothrow) gs_slicer();
@@ -348,13 +427,16 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   s->cfg.owner_host = nullptr;
   s->cfg.draws_host = nullptr;
   s->cfg.features = nullptr;
+  s->group_size = gsz;
   const int64_t N = g->num_nodes, M = g->num_edges;
   int64_t Fb[GS_MAX_LAYERS] = {0}, Cb[GS_MAX_LAYERS] = {0};
   compute_capacities(*cfg, N, M, &s->Fcap, &s->Ccap, &s->slab_cap, &s->fslab_cap, Fb, Cb);
-  if (s->Ccap >= (1ll << 31) - 2 * GS_TILE || s->Fcap >= (1ll << 31) - 2 * GS_TILE ||
+  // table entries are (tag | kind | payload): positions and row indices need a payload of
+  // <= 30 bits, which leaves at least one tag
+  if (s->Ccap >= (1ll << 30) - 2 * GS_TILE || s->Fcap >= (1ll << 30) - 2 * GS_TILE ||
       s->slab_cap >= (1ll << 31) - 16) {
     delete s;
-    return fail(GS_ERR_INVALID, "derived capacities exceed 2^31 positions; lower max_batch or set "
+    return fail(GS_ERR_INVALID, "derived capacities exceed 2^30 positions; lower max_batch or set "
                                 "cand_capacity / slab_capacity");
   }
   if (cfg->features) {
@@ -371,15 +453,17 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   }
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g->device);
-  // grid_ctas = CTAs per SM of a full-machine launch.  Sizes are only known on
-  // the device, so each launch gets the grid its layer's static upper bound
-  // needs, capped at the full-machine grid (tile loops stride over the rest).
+  // grid_ctas = CTAs per SM and member of a full-machine launch.  Sizes are only
+  // known on the device, so each launch gets the grid its layer's static upper
+  // bound needs, capped at the full-machine grid (tile loops run over the rest).
   s->grid = (cfg->grid_ctas > 0 ? cfg->grid_ctas : 4) * sms;
-  s->grid_full = 8 * sms;
+  s->grid_gather = std::max(1, 8 * sms / gsz);
   for (int l = 0; l < cfg->num_layers; l++) {
     const int64_t fb = std::min(Fb[l], s->Fcap), cb = std::min(Cb[l], s->Ccap);
+    const int64_t eb = std::max<int64_t>(1, cb - fb);
     s->grid_rows[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (fb + GS_TILE - 1) / GS_TILE));
     s->grid_cand[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (cb + GS_TILE - 1) / GS_TILE));
+    s->grid_relabel[l] = (int)std::max<int64_t>(1, std::min<int64_t>(s->grid, (eb + GS_TILE - 1) / GS_TILE));
   }
 
 #define CUS(call)                                                                        \
@@ -417,24 +501,27 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   CUS(cudaMalloc((void **)&s->draw_cursor, sizeof(uint64_t)));
   CUS(cudaMemset(s->draw_cursor, 0, sizeof(uint64_t)));
 
-  // replay mode consumes one sequential draw stream: keep every slot on one stream
+  const int ngroups = cfg->num_slots / gsz;
   const int nstreams =
-      cfg->rng_mode == GS_RNG_DRAWS ? 1 : std::max(1, std::min(cfg->num_streams, cfg->num_slots));
+      cfg->rng_mode == GS_RNG_DRAWS ? 1 : std::max(1, std::min(cfg->num_streams, ngroups));
   s->streams.resize(nstreams);
   for (int i = 0; i < nstreams; i++) {
     s->streams[i] = nullptr;
     CUS(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
   }
-  if (cfg->host_output && cfg->host_copy_engine)
-    CUS(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+  if (cfg->host_output) CUS(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
 
-  const int ftiles = s->grid;  // per-CTA count arrays: one entry per CTA of the largest grid
-  const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;  // tile_first: one per candidate tile
+  const int ftiles = (int)((s->Fcap + GS_TILE - 1) / GS_TILE) + 1;
+  const int ctiles = (int)((s->Ccap + GS_TILE - 1) / GS_TILE) + 1;
+  int pos_bits = 1;
+  while (pos_bits < 30 && (1ll << pos_bits) <= std::max<int64_t>(std::max(s->Ccap, s->Fcap), cfg->max_batch)) pos_bits++;
   s->slots.resize(cfg->num_slots);
+  s->groups.resize(ngroups);
   for (int k = 0; k < cfg->num_slots; k++) {
     Slot &sl = s->slots[k];
     GsWs &w = sl.ws;
     int64_t bytes = 0;
+    sl.group = k / gsz;
     w.indptr = g->indptr;
     w.indices = g->indices;
     w.owner = s->owner;
@@ -455,14 +542,9 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.fslab_cap = s->fslab_cap;
     w.Fcap = (int32_t)s->Fcap;
     w.Ccap = (int32_t)s->Ccap;
-    {  // tagged table when positions leave room for >= 4 samples' worth of tags in a 32-bit entry
-      int S = 1;
-      while (S < 32 && (1ll << S) <= std::max<int64_t>(s->Ccap, cfg->max_batch)) S++;
-      const int64_t ntags = S < 32 ? (1ll << (32 - S)) : 1;
-      w.tag_shift = (GS_TABLE_TAGS && ntags >= 4 * (int64_t)(cfg->num_layers + 1)) ? S : 0;
-    }
-    w.ftiles_max = ftiles;
-    w.ctiles_max = s->grid;
+    w.pos_bits = pos_bits;
+    w.ftiles_cap = ftiles;
+    w.ctiles_cap = ctiles;
 #define DA(ptr, n)                                         \
   do {                                                     \
     if (dev_alloc(sl, &ptr, (size_t)(n), &bytes) != GS_OK) { \
@@ -472,29 +554,27 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
       return GS_ERR_CUDA;                                  \
     }                                                      \
   } while (0)
+    const int L = cfg->num_layers;
     DA(w.hdr, 1);
+    DA(w.state, 1);
     DA(w.table, N);
     DA(w.slab, s->slab_cap + 4);
     DA(w.fslab, s->fslab_cap + 4);
-    DA(w.rowstart, s->Fcap);
-    DA(w.rowdeg, s->Fcap);
+    DA(w.rowinfo, s->Fcap);
     DA(w.off, s->Fcap + 1);
     DA(w.samp_rank, s->Fcap);
-    DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
-    DA(w.cand, s->Ccap);
-    DA(w.cflag, s->Ccap);
-    DA(w.kill, s->Ccap);
-    DA(w.irank, s->Ccap);
-    DA(w.rowa, s->Fcap);
-    DA(w.rowhas, s->Fcap + 4);
+    DA(w.selfrank, s->Fcap);
+    DA(w.ea, s->Fcap);
+    DA(w.rowhas, s->Fcap);
+    DA(w.cand, s->Ccap + 4);
+    DA(w.cflag, s->Ccap + 4);
     DA(w.tile_first, ctiles + 1);
-    DA(w.ftile_sum, ftiles);
-    DA(w.ftile_samp, ftiles);
-    DA(w.ftile_pre, 2 * (size_t)ftiles);
-    DA(w.ctile_cnt, (size_t)GS_NC_MAX * s->grid);
-    DA(w.ftile_cnt, (size_t)GS_NF_MAX * ftiles);
-    DA(w.tickets, 8);
-    DA(w.epoch, 2);
+    DA(w.cnt, (size_t)L * GS_CNT_STRIDE);
+    DA(w.tickets, (size_t)(L + 1) * GS_TICKETS);
+    DA(w.rs_status, ftiles);
+    DA(w.rs_val, 2 * (size_t)ftiles * GS_RS_NC);
+    DA(w.cs_status, ctiles);
+    DA(w.cs_val, 2 * (size_t)ctiles * GS_CS_NC);
     if (s->feat) {
       w.feat = s->feat->rows;
       w.feat_slot = s->feat->slot_of;
@@ -508,10 +588,12 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
 #undef DA
     s->slot_bytes = bytes;
     CUS(cudaMemset(w.hdr, 0, sizeof(gs_sample_header)));
-    CUS(cudaMemset(w.tickets, 0, 8 * sizeof(uint32_t)));
+    CUS(cudaMemcpy(w.state, &kStateStart, sizeof(GsState), cudaMemcpyHostToDevice));
     CUS(cudaMemset(w.table, 0xFF, (size_t)N * sizeof(uint32_t)));
-    CUS(cudaMemcpy(w.epoch, kEpochStart, sizeof(kEpochStart), cudaMemcpyHostToDevice));
-    CUS(cudaMemset(w.kill, 0, (size_t)s->Ccap));
+    CUS(cudaMemset(w.cnt, 0, (size_t)L * GS_CNT_STRIDE * sizeof(uint32_t)));
+    CUS(cudaMemset(w.tickets, 0, (size_t)(L + 1) * GS_TICKETS * sizeof(uint32_t)));
+    CUS(cudaMemset(w.rs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
+    CUS(cudaMemset(w.cs_status, 0, (size_t)ctiles * sizeof(uint32_t)));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
                       cudaHostAllocMapped));
@@ -528,20 +610,23 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     w.seeds_in = (const int64_t *)dp;
     CUS(cudaHostGetDevicePointer(&dp, sl.hdr_host, 0));
     w.hdr_host = (gs_sample_header *)dp;
-    w.slab_host = nullptr;
-    if (sl.slab_host && !cfg->host_copy_engine) {  // mirrored by k_finish's own stores
-      CUS(cudaHostGetDevicePointer(&dp, sl.slab_host, 0));
-      w.slab_host = (int32_t *)dp;
-    }
-    sl.stream = s->streams[k % nstreams];
     CUS(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
-    CUS(cudaEventCreateWithFlags(&sl.chain_done, cudaEventDisableTiming));
     CUS(cudaEventCreateWithFlags(&sl.pack_done, cudaEventDisableTiming));
+  }
+  for (int j = 0; j < ngroups; j++) {
+    Group &gr = s->groups[j];
+    gr.first = j * gsz;
+    gr.members = gsz;
+    gr.stream = s->streams[j % nstreams];
+    CUS(cudaMalloc((void **)&gr.wsv, (size_t)gsz * sizeof(GsWs)));
+    for (int m = 0; m < gsz; m++)
+      CUS(cudaMemcpy(gr.wsv + m, &s->slots[gr.first + m].ws, sizeof(GsWs), cudaMemcpyHostToDevice));
+    CUS(cudaEventCreateWithFlags(&gr.chain_done, cudaEventDisableTiming));
     if (cfg->use_graph) {
       cudaGraph_t graph = nullptr;
-      CUS(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
-      int rc = enqueue_sample(s, sl, sl.stream, nullptr, nullptr);
-      cudaError_t ce = cudaStreamEndCapture(sl.stream, &graph);
+      CUS(cudaStreamBeginCapture(gr.stream, cudaStreamCaptureModeThreadLocal));
+      int rc = enqueue_group(s, gr, gsz, gr.stream, nullptr, nullptr);
+      cudaError_t ce = cudaStreamEndCapture(gr.stream, &graph);
       if (rc != GS_OK || ce != cudaSuccess) {
         if (rc == GS_OK) fail(GS_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(ce));
         std::string keep = g_err;
@@ -549,7 +634,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
         g_err = keep;
         return GS_ERR_CUDA;
       }
-      CUS(cudaGraphInstantiate(&sl.exec, graph, 0));
+      CUS(cudaGraphInstantiate(&gr.exec, graph, 0));
       cudaGraphDestroy(graph);
     }
   }
@@ -564,43 +649,46 @@ int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_
   if (!s || !slot_out) return fail(GS_ERR_INVALID, "NULL argument");
   const GsRange trace("gs_slicer_submit");
   CU(cudaSetDevice(s->g->device));
-  const int ns = (int)s->slots.size();
-  int k = -1;
-  for (int t = 0; t < ns; t++) {
-    const int c = (s->next_slot + t) % ns;
-    if (s->slots[c].state == SLOT_FREE) {
-      k = c;
-      break;
+  const int ng = (int)s->groups.size();
+  if (s->cur_group < 0) {
+    // the next group in ring order, as soon as its first slot is free again (a
+    // released slot implies that the group's last launch has completed)
+    int pick = -1;
+    for (int t = 0; t < ng && pick < 0; t++) {
+      const Group &cand = s->groups[(s->next_group + t) % ng];
+      bool idle = true;
+      for (int j = 0; j < cand.members; j++) {
+        const int st = s->slots[cand.first + j].state;
+        if (st == SLOT_BUSY || st == SLOT_STAGED || (j == 0 && st != SLOT_FREE)) idle = false;
+      }
+      if (idle) pick = (s->next_group + t) % ng;
     }
+    if (pick < 0)
+      return fail(GS_ERR_BUSY, "all %d sample slots are in use; release one", (int)s->slots.size());
+    s->cur_group = pick;
+    s->next_group = (pick + 1) % ng;
+    s->groups[pick].staged = 0;
   }
-  if (k < 0) return fail(GS_ERR_BUSY, "all %d sample slots are in use; release one", ns);
+  Group &gr = s->groups[s->cur_group];
+  const int k = gr.first + gr.staged;
   Slot &sl = s->slots[k];
+  if (sl.state != SLOT_FREE)
+    return fail(GS_ERR_BUSY, "slot %d (member %d of the group being filled) is still held; release it", k,
+                gr.staged);
   int rc = stage_input(s, sl, seeds_host, n, batch_index);
   if (rc != GS_OK) return rc;
-  if (sl.exec) {
-    CU(cudaGraphLaunch(sl.exec, sl.stream));
-  } else {
-    rc = enqueue_sample(s, sl, sl.stream, nullptr, nullptr);
-    if (rc != GS_OK) return rc;
-  }
-  sl.copied = 0;
-  if (s->copy_stream && sl.slab_host) {
-    // mirror with the copy engine: its size must be known now, so move the running
-    // maximum of slab_used (+2 %); gs_slicer_wait tops up the rare remainder
-    CU(cudaEventRecord(sl.chain_done, sl.stream));
-    CU(cudaStreamWaitEvent(s->copy_stream, sl.chain_done, 0));
-    sl.copied = std::min<int64_t>(s->slab_cap, s->mirror_est);
-    if (sl.copied > 0)
-      CU(cudaMemcpyAsync(sl.slab_host, sl.ws.slab, (size_t)sl.copied * sizeof(int32_t),
-                         cudaMemcpyDeviceToHost, s->copy_stream));
-    CU(cudaEventRecord(sl.done, s->copy_stream));
-  } else {
-    CU(cudaEventRecord(sl.done, sl.stream));
-  }
-  sl.state = SLOT_BUSY;
-  s->next_slot = (k + 1) % ns;
+  sl.state = SLOT_STAGED;
+  gr.staged++;
   *slot_out = k;
+  if (gr.staged == gr.members) return launch_group(s, gr);
   return GS_OK;
+}
+
+int gs_slicer_flush(gs_slicer *s) {
+  if (!s) return fail(GS_ERR_INVALID, "NULL argument");
+  if (s->cur_group < 0) return GS_OK;
+  CU(cudaSetDevice(s->g->device));
+  return launch_group(s, s->groups[s->cur_group]);
 }
 
 static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out) {
@@ -608,11 +696,8 @@ static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out)
   const int st = sl.hdr_host->status ? sl.hdr_host->status : sl.hdr_host->late_status;
   if (hdr_out) *hdr_out = sl.hdr_host;
   if (st != 0) {
-    // a sample that stopped half way may have left touched table entries behind
-    cudaMemsetAsync(sl.ws.table, 0xFF, (size_t)s->g->num_nodes * sizeof(uint32_t), sl.stream);
-    cudaMemcpyAsync(sl.ws.epoch, kEpochStart, sizeof(kEpochStart), cudaMemcpyHostToDevice, sl.stream);
-    cudaMemsetAsync(sl.ws.kill, 0, (size_t)s->Ccap, sl.stream);
-    cudaStreamSynchronize(sl.stream);
+    // nothing to repair: a sample's tag, scan epochs and tickets are retired by its own
+    // last launch, whatever it left in the table reads as stale from the next sample on
     if (st == GS_ERR_OVERFLOW)
       return fail(GS_ERR_OVERFLOW,
                   "sample outgrew its workspace (frontier_capacity=%lld cand_capacity=%lld "
@@ -626,10 +711,10 @@ static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out)
   if (s->copy_stream && sl.slab_host) {
     const int64_t used = sl.hdr_host->slab_used;
     if (used > sl.copied) {  // first samples, or a sample larger than any before it
-      cudaError_t e = cudaMemcpyAsync(sl.slab_host + sl.copied, sl.ws.slab + sl.copied,
-                                      (size_t)(used - sl.copied) * sizeof(int32_t), cudaMemcpyDeviceToHost,
-                                      s->copy_stream);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(s->copy_stream);
+      // blocking copy on the legacy stream's behalf of THIS slot only: it must not queue
+      // behind the mirrors of samples submitted later (those sit on copy_stream)
+      cudaError_t e = cudaMemcpy(sl.slab_host + sl.copied, sl.ws.slab + sl.copied,
+                                 (size_t)(used - sl.copied) * sizeof(int32_t), cudaMemcpyDeviceToHost);
       if (e != cudaSuccess) return fail(GS_ERR_CUDA, "host mirror failed: %s", cudaGetErrorString(e));
       sl.copied = used;
     }
@@ -644,6 +729,8 @@ int gs_slicer_wait(gs_slicer *s, int32_t slot, const gs_sample_header **hdr_out)
   if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
   const GsRange trace("gs_slicer_wait");
   CU(cudaSetDevice(s->g->device));
+  int rc = flush_if_staged(s, sl);
+  if (rc != GS_OK) return rc;
   if (sl.state == SLOT_BUSY) CU(cudaEventSynchronize(sl.done));
   return finish_wait(s, sl, hdr_out);
 }
@@ -682,8 +769,10 @@ int gs_slicer_read_frontier(gs_slicer *s, int32_t slot, int32_t layer, int32_t *
 int gs_slicer_release(gs_slicer *s, int32_t slot) {
   if (!s || slot < 0 || slot >= (int)s->slots.size()) return fail(GS_ERR_INVALID, "bad slot");
   Slot &sl = s->slots[slot];
-  if (sl.state == SLOT_BUSY) {
+  if (sl.state == SLOT_STAGED || sl.state == SLOT_BUSY) {
     CU(cudaSetDevice(s->g->device));
+    int rc = flush_if_staged(s, sl);
+    if (rc != GS_OK) return rc;
     CU(cudaEventSynchronize(sl.done));
     finish_wait(s, sl, nullptr);
   }
@@ -697,19 +786,23 @@ static int scatter_parts(gs_slicer *s, int32_t slot, const GsPartDst &dst, int64
   if (sl.state == SLOT_FREE) return fail(GS_ERR_STATE, "slot %d holds no sample", slot);
   const GsRange trace("gs_slicer_pack_parts");
   CU(cudaSetDevice(s->g->device));
-  if (after_event) CU(cudaStreamWaitEvent(sl.stream, (cudaEvent_t)after_event, 0));
-  // on the slot's own stream: after the sample's kernels, before the slot's next sample.
+  int rc = flush_if_staged(s, sl);
+  if (rc != GS_OK) return rc;
+  cudaStream_t st = s->groups[sl.group].stream;
+  if (after_event) CU(cudaStreamWaitEvent(st, (cudaEvent_t)after_event, 0));
+  // on the group's own stream: after the sample's kernels, before the group's next launch.
   // >= 4 parts (most stores remote): bulk-copy engine, one CTA per SM over all parts keeps
   // ~4.7 MB in flight (4 B200: 25.2 K minibatches/s against 24.7 K with plain stores);
   // fewer parts: plain 16-byte stores, 8 CTAs per SM (2 B200: 14.2 K against 13.2 K)
   // GSPLIT_PACK_TMA=0/1 in the environment overrides the choice (tests force both paths on 2 ranks)
   const char *ov = getenv("GSPLIT_PACK_TMA");
   const bool tma = GS_PACK_TMA && (ov ? atoi(ov) != 0 : s->cfg.num_parts >= 4);
-  const int pack_ctas = tma ? std::max(2, s->grid_full / 8) : s->grid_full;
-  gs_launch_pack_parts(sl.ws, dst, block_words, std::max(1, pack_ctas / std::max(1, s->cfg.num_parts)), tma,
-                       sl.stream);
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->g->device);
+  const int pack_ctas = tma ? std::max(2, sms) : 8 * sms;
+  gs_launch_pack_parts(sl.ws, dst, block_words, std::max(1, pack_ctas / std::max(1, s->cfg.num_parts)), tma, st);
   CU(cudaGetLastError());
-  CU(cudaEventRecord(sl.pack_done, sl.stream));
+  CU(cudaEventRecord(sl.pack_done, st));
   CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, sl.pack_done, 0));  // NULL: the default stream waits
   return GS_OK;
 }
@@ -778,19 +871,23 @@ int gs_ipc_free(int device, void *dev_ptr) {
   return GS_OK;
 }
 
+
 int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
                       float *ms, const char **names, int32_t cap, int32_t *n_out) {
   if (!s || !ms || !names || !n_out) return fail(GS_ERR_INVALID, "NULL argument");
   CU(cudaSetDevice(s->g->device));
-  Slot &sl = s->slots[0];
-  if (sl.state != SLOT_FREE) return fail(GS_ERR_BUSY, "slot 0 must be free to profile");
+  Group &gr = s->groups[0];
+  for (int j = 0; j < gr.members; j++)
+    if (s->slots[gr.first + j].state != SLOT_FREE)
+      return fail(GS_ERR_BUSY, "the slots of group 0 must be free to profile");
+  Slot &sl = s->slots[gr.first];
   int rc = stage_input(s, sl, seeds_host, n, batch_index);
   if (rc != GS_OK) return rc;
   std::vector<cudaEvent_t> ev;
   std::vector<const char *> nm;
-  rc = enqueue_sample(s, sl, sl.stream, &ev, &nm);
+  rc = enqueue_group(s, gr, 1, gr.stream, &ev, &nm);
   if (rc == GS_OK) {
-    cudaError_t e = cudaStreamSynchronize(sl.stream);
+    cudaError_t e = cudaStreamSynchronize(gr.stream);
     if (e != cudaSuccess) rc = fail(GS_ERR_CUDA, "profile run failed: %s", cudaGetErrorString(e));
   }
   int cnt = 0;
@@ -802,8 +899,9 @@ int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64
   for (cudaEvent_t e : ev) cudaEventDestroy(e);
   *n_out = cnt;
   if (rc != GS_OK) return rc;
-  sl.state = SLOT_BUSY;  // completed; let wait()/release() run the normal path
-  CU(cudaEventRecord(sl.done, sl.stream));
+  sl.state = SLOT_BUSY;  // completed; run the normal completion path
+  CU(cudaEventRecord(sl.done, gr.stream));
+  sl.copied = 0;
   const gs_sample_header *h;
   rc = finish_wait(s, sl, &h);
   sl.state = SLOT_FREE;
@@ -957,7 +1055,7 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset) {
 }
 
 int gs_slicer_launches_per_sample(const gs_slicer *s) {
-  return s ? 2 + 8 * s->cfg.num_layers + (s->feat ? 1 : 0) : 0;
+  return s ? 3 * s->cfg.num_layers + 1 : 0;
 }
 int64_t gs_slicer_slot_bytes(const gs_slicer *s) { return s ? s->slot_bytes : 0; }
 int64_t gs_slicer_slab_capacity(const gs_slicer *s) { return s ? s->slab_cap : 0; }

@@ -8,38 +8,58 @@
 
 #define GS_TPB 256          // threads per CTA in every tiled kernel
 #define GS_NW (GS_TPB / 32) // warps per CTA
-#define GS_IPT 4            // sub-iterations (items per thread) per tile
+#define GS_IPT 4            // consecutive items per thread and tile
 #define GS_TILE (GS_TPB * GS_IPT)
 #define GS_INF 0xFFFFFFFFu
-#define GS_NC_MAX (2 * GS_MAX_PARTS + 1) // candidate-side counters
-#define GS_NF_MAX (4 * GS_MAX_PARTS)     // frontier-side counters
 
-// candidate flag byte
-#define GS_CF_SELF 0x01u   // slot 0 of a row: the destination itself (slicer.cpp:7)
-#define GS_CF_LOOP 0x02u   // sampled neighbour equal to the destination (treated as self, slicer.cpp:33)
-#define GS_CF_FFIRST 0x04u // first occurrence in the layer's candidate stream -> next frontier
-#define GS_CF_IFIRST 0x08u // first occurrence as an edge source -> in_nodes of its owner
+// candidate flag byte: kind in bits 0-1, part in bits 4-6 (edge: owner of the
+// source; self entry: owner of the row's node)
+#define GS_CK_EDGE 0u  // cand = source id; its table entry holds the minimum position
+#define GS_CK_SELF 1u  // slot 0 of a row: the destination itself (slicer.cpp:7); cand = row index
+#define GS_CK_DEAD 2u  // sampled neighbour equal to the destination (slicer.cpp:33), or past the end
+#define GS_CK_FHIT 3u  // edge whose source is a node of the CURRENT frontier; cand = its row index
+#define GS_CK_MASK 3u
 #define GS_CF_PART_SHIFT 4
 
-// Inputs of one minibatch, in pinned mapped host memory (read by k_begin over PCIe).
-// Tagged dedup table (no per-layer / per-sample resets); A/B with -DGS_TABLE_TAGS=0
-#ifndef GS_TABLE_TAGS
-#define GS_TABLE_TAGS 1
-#endif
+// per-layer totals, exact once k_expand has run (index into GsWs::cnt[layer])
+#define GS_CNT_STRIDE 64
+#define GS_CNT_NEW 0                      // nodes new to the frontier
+#define GS_CNT_IN(P, q) (1 + (q))         // |in_nodes_q|
+#define GS_CNT_E(P, q) (1 + (P) + (q))    // edges of part q
+#define GS_CNT_OUT(P, q) (1 + 2 * (P) + (q))
+#define GS_CNT_OWN(P, q) (1 + 3 * (P) + (q))
+#define GS_CNT_TO(P, q) (1 + 4 * (P) + (q))
+#define GS_CNT_SELF(P, q) (1 + 5 * (P) + (q))  // rows owned by q (k_rows)
+#define GS_TICKETS 4                      // per layer: [0] k_rows tiles, [1] k_expand done, [2] k_cand tiles
+
+// decoupled look-back descriptors
+#define GS_RS_NC 16   // k_rows scan: candidates, drawing rows, rows per owner (uint64 each; 2 + P used)
+#define GS_CS_NC 64   // k_cand scan: 1 + 5 P counters (uint32; <= 41 used), padded to two lane rounds
+#define GS_SKIPPED 1000  // header status of a group member that holds no minibatch
 
 // hand-over copy through the bulk-copy engine (cp.async.bulk); A/B with -DGS_PACK_TMA=0
 #ifndef GS_PACK_TMA
 #define GS_PACK_TMA 1
 #endif
 
+// Inputs of one minibatch, in pinned mapped host memory (read by k_rows<FIRST> over PCIe).
 struct GsInput {
-  int32_t n_seeds;
+  int32_t n_seeds;   // < 0: this member of the group holds no minibatch
   int32_t want_host;
   uint64_t batch_index;
 };
 
-// Everything a kernel needs; passed by value, constant for the life of a slot,
-// so a slot's whole minibatch is one replayable CUDA graph.
+// Per-slot state carried from sample to sample; prepared for sample k + 1 by the
+// last CTA of sample k's k_tail, so no kernel of a sample ever has to reset anything.
+struct GsState {
+  uint32_t tag_idx;     // tag index of the current sample; stored tag = ntags - 1 - tag_idx (index 0 = fill pattern)
+  uint32_t scan_epoch;  // scan descriptors of layer l: epoch scan_epoch + 2 l (k_rows), + 2 l + 1 (k_cand)
+  uint32_t pad[2];
+};
+
+// Everything a kernel needs about one slot.  The kernels receive an ARRAY of
+// these (one per minibatch of a group, blockIdx.y selects) and stage their own
+// in shared memory.
 struct GsWs {
   // graph (shared by all slots)
   const int64_t *indptr;  // [N+1]
@@ -52,41 +72,37 @@ struct GsWs {
   int32_t fanouts[GS_MAX_LAYERS];
   // rng
   int32_t rng_mode;
-  int32_t l2_hints;      // 1: keep the dedup table in L2 (evict_last), stream the rest (evict_first)
+  int32_t l2_hints;      // 1: keep the dedup table in L2 (evict_last), stream the picks (evict_first)
   uint32_t seed_lo, seed_hi;
   const uint32_t *draws;
   uint64_t n_draws;
-  uint64_t *draw_cursor; // shared by all slots (GS_RNG_DRAWS runs on one stream)
+  uint64_t *draw_cursor; // shared by all slots (GS_RNG_DRAWS runs on one stream, groups of one)
   // per-slot state
   gs_sample_header *hdr; // device
-  uint32_t *table;       // [N] minimum edge-source position of the node in the current layer (GS_INF: none)
-  uint32_t *epoch;       // [2] tagged table: [0] next free tag index, [1] first tag index of the current sample
-  int32_t tag_shift;     // S > 0: table value = (tag << S) | position, newer layers use SMALLER tags, so a
-                         // stale entry loses every red.min and reads as "none": no per-layer / per-sample
-                         // resets, one dense fill every 2^(32-S) / (L+1) samples.  0: untagged (reset each time)
+  GsState *state;
+  uint32_t *table;       // [N] (tag | kind | payload): kind 0 = node of the current frontier, payload = its row;
+                         //     kind 1 = minimum edge-source position of a node new to this layer
+  int32_t pos_bits;      // S: payload bits; the kind bit is 1 << S, the tag sits above it
   int32_t *slab;         // sample slab: every bipartite list (mirrored to the host in e2e mode)
   int64_t slab_cap;
   int32_t *fslab;        // frontier slab: frontiers 0..L (device only; read back on demand)
   int64_t fslab_cap;
-  int64_t *rowstart;     // [Fcap]   indptr[front[i]]
-  int32_t *rowdeg;       // [Fcap]
+  int4 *rowinfo;         // [Fcap] {indptr lo, indptr hi, degree, node id} of every frontier row
   uint32_t *off;         // [Fcap+1] first candidate position of row i
   uint32_t *samp_rank;   // [Fcap]   # earlier rows that draw (replay mode)
-  uint32_t *rowscan;     // [P][Fcap+1] edges of part g emitted before row i
-  int32_t *cand;         // [Ccap]   candidate stream (slot 0 of a row holds the row index)
+  uint32_t *selfrank;    // [Fcap]   # earlier rows with the same owner = rank in self_ids_* of that part
+  uint32_t *ea;          // [Fcap]   minimum edge-source position of the row's node in this layer (GS_INF: none)
+  uint32_t *rowhas;      // [Fcap]   bit q: the row emitted >= 1 edge into part q
+  int32_t *cand;         // [Ccap]   candidate stream; after k_cand: in_nodes rank at first-occurrence positions
   uint8_t *cflag;        // [Ccap]
-  uint8_t *kill;         // [Ccap] 1: the edge candidate here is NOT a frontier first (its node's self entry came earlier); zero between layers
-  uint32_t *irank;       // [Ccap] rank in in_nodes_g of the first edge occurrence at this position
-  uint8_t *rowhas;       // [Fcap] bit q: row emitted >= 1 edge into part q (k_front_count -> k_front_apply)
-  uint32_t *rowa;        // [Fcap] table value (min edge-source position) of every row's node
-  uint32_t *tile_first;  // [ctiles_max+1] row containing candidate t*GS_TILE
-  unsigned long long *ftile_sum; // [ftiles_max] candidates per frontier tile
-  uint32_t *ftile_samp;  // [ftiles_max] drawing rows per frontier tile
-  uint32_t *ftile_pre;   // [2][ftiles_max] exclusive prefixes of the two above
-  uint32_t *ctile_cnt;   // [GS_NC_MAX][ctiles_max]
-  uint32_t *ftile_cnt;   // [GS_NF_MAX][ftiles_max]
-  uint32_t *tickets;     // [8] last-block tickets, one per spine kernel
-  int32_t Fcap, Ccap, ftiles_max, ctiles_max;
+  uint32_t *tile_first;  // [ctiles_cap] row containing candidate t*GS_TILE
+  uint32_t *cnt;         // [L][GS_CNT_STRIDE] per-layer totals
+  uint32_t *tickets;     // [L][GS_TICKETS] + [GS_TICKETS] (tail)
+  uint32_t *rs_status;   // [ftiles_cap]
+  unsigned long long *rs_val;  // [2][ftiles_cap][GS_RS_NC]  aggregates, inclusive prefixes
+  uint32_t *cs_status;   // [ctiles_cap]
+  uint32_t *cs_val;      // [2][ctiles_cap][GS_CS_NC]
+  int32_t Fcap, Ccap, ftiles_cap, ctiles_cap;
   // fused input-feature gather (optional)
   const float *feat;     // [rows][feat_dim] fp32 (cached store: the cached rows)
   const int32_t *feat_slot; // cached store: [feat_rows] slot of every row or -1; else NULL
@@ -98,7 +114,6 @@ struct GsWs {
   const int64_t *seeds_in;
   const GsInput *input;
   gs_sample_header *hdr_host;
-  int32_t *slab_host;
 };
 
 // error string of the calling thread (slicer_api.cu); returns `code`
@@ -114,18 +129,15 @@ struct GsRange {
   ~GsRange();
 };
 
-// launchers (slicer_kernels.cu); every one enqueues exactly one kernel on `st`
-void gs_launch_begin(const GsWs &ws, cudaStream_t st);
-void gs_launch_rows_count(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_rows_scan(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_expand(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_cand_flags(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_cand_apply(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_front_count(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_front_apply(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_relabel(const GsWs &ws, int layer, int grid, cudaStream_t st);
-void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st);
-void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st);
+// launchers (slicer_kernels.cu); every one enqueues exactly one kernel on `st`.
+// wsv: device array of `members` GsWs (one group); grid.y = members.
+struct GsGrids {
+  int rows, cand, relabel;  // CTAs of the three roles for one layer (static upper bounds)
+};
+void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, int grid_relabel, cudaStream_t st);
+void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int grid, cudaStream_t st);
+void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st);
+void gs_launch_tail(const GsWs *wsv, int members, int grid_relabel, int grid_gather, cudaStream_t st);
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
                           cudaStream_t st);
@@ -134,3 +146,10 @@ void gs_launch_pack_parts(const GsWs &ws, const GsPartDst &dst, int64_t block_wo
                           cudaStream_t st);
 void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st);
 void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st);
+// CSR validation on the device (gs_graph_create): err[0] = first offending index + 1 (0: none), by kind
+void gs_launch_check_indptr(const int64_t *indptr, int64_t n, int64_t m, unsigned long long *err, cudaStream_t st);
+void gs_launch_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t num_nodes, unsigned long long *err,
+                         cudaStream_t st);
+// random-sector yardstick (bench): n reads of one 4-byte word each from a table of `elems` words
+void gs_launch_sector_probe(const uint32_t *table, uint64_t elems, uint64_t n, uint32_t seed, uint32_t *sink,
+                            int grid, cudaStream_t st);

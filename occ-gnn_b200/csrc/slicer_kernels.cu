@@ -1,26 +1,37 @@
 // slicer_kernels.cu -- hand-written sm_100a kernels of the minibatch slicer.
 //
 // One layer of the reference's sequential slice_layer (slicer.cpp:25-64) +
-// BiPartite::reorder (bipartite.cpp:3-17) becomes eight data-parallel passes.
-// The sequential order the reference's lists are in (first occurrence in a
-// scan over frontier rows and, inside a row, over [self, neighbours...]) is
-// carried by a 32-bit *candidate position*: row i owns positions
-// [off[i], off[i+1]), slot 0 being the self entry.  "First occurrence" = minimum
-// position (atomicMin into a direct-address table), "list order" = ascending
-// position (prefix scans over the candidate stream), so every output list is
-// bit-identical to the sequential algorithm without any sort.
+// BiPartite::reorder (bipartite.cpp:3-17) becomes THREE data-parallel launches,
+// each a single pass over its stream:
 //
-// All sizes live in device memory (gs_sample_header); every kernel is a
-// fixed-size grid striding over tiles, so a whole minibatch is one static CUDA
-// graph with no host round trip.  Integer / byte work, HBM- and latency-bound:
-// no tensor cores (nothing here is a contraction).
+//   k_rows    frontier rows: CSR extents, candidate offsets (decoupled look-back
+//             scan), the rows' rank among the rows of their owner, and the mark
+//             "node v is row i of the current frontier" in the dedup table
+//             (+ in the same launch: the relabel of the PREVIOUS layer's edges);
+//   k_expand  candidate-parallel CSR expansion + Philox picks; one returning
+//             atom.min per edge source finds out whether the source is new to the
+//             layer or already a frontier row, and that answer makes every list
+//             length of the layer exact BEFORE any list is written: the last CTA
+//             lays the whole layer out in the sample slab;
+//   k_cand    one pass over the candidate stream with a decoupled look-back scan of
+//             1 + 5 P counters: next frontier, in_nodes, csr_indices, out_nodes,
+//             csr_indptr, owned / from / to / self lists -- every list of every part.
+//
+// The sequential order the reference's lists are in (first occurrence in a scan
+// over frontier rows and, inside a row, over [self, neighbours...]) is carried by
+// a 32-bit *candidate position*: row i owns positions [off[i], off[i+1]), slot 0
+// being the self entry.  "First occurrence" = minimum position (atom.min into a
+// direct-address table), "list order" = ascending position (prefix scans over the
+// candidate stream), so every output list is bit-identical to the sequential
+// algorithm without any sort.
+//
+// All sizes live in device memory (gs_sample_header); tiles are handed out by
+// tickets, so a whole minibatch -- or a group of them, blockIdx.y -- is one
+// static CUDA graph of 3 L + 1 launches with no host round trip.  Integer / byte
+// work, HBM- and latency-bound: no tensor cores (nothing here is a contraction).
 #include "slicer_device.cuh"
 
-// Resident CTAs per SM the tiled kernels are compiled for (0: ptxas' choice,
-// 46-55 registers -> 4-5 CTAs; n: register cap 65536 / (GS_TPB * n)).  Several
-// minibatches run concurrently on their own streams, so what counts is how many
-// warps of ALL of them fit an SM.  Measured (tools/build_variants.sh): 6 (40
-// registers, few spills) = 0 within 0.3 %, 8 (32 registers, spills) -7 %.
+// Resident CTAs per SM the tiled kernels are compiled for (0: ptxas' choice).
 #ifndef GS_MINB
 #define GS_MINB 0
 #endif
@@ -33,10 +44,9 @@
 namespace {
 
 // --------------------------------------------------- L2 residency control
-// The per-slot dedup tables are the only randomly re-read data (4-5 touches per
-// candidate); the CSR gathers and the candidate / slab streams are touched once.
-// With createpolicy hints the tables are kept in B200's 126 MB L2 (evict_last)
-// while the single-use traffic passes through as evict_first.  ws.l2_hints = 0
+// The per-slot dedup tables are the only randomly re-read data; the CSR gathers
+// are touched once.  With createpolicy hints the tables are kept in B200's 126 MB
+// L2 (evict_last) while the picks pass through as evict_first.  ws.l2_hints = 0
 // falls back to plain accesses (same results, for A/B measurements).
 __device__ __forceinline__ uint64_t l2_policy_keep() {
   uint64_t p;
@@ -65,9 +75,13 @@ struct Tbl {  // table access with an optional keep-in-L2 policy
     if (!hint) { t[v] = x; return; }
     asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(t + v), "r"(x), "l"(pol) : "memory");
   }
-  __device__ __forceinline__ void min(int32_t v, uint32_t p) const {
-    if (!hint) { atomicMin(t + v, p); return; }
-    asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(t + v), "r"(p), "l"(pol) : "memory");
+  // returning minimum: the old value tells the caller what the node was before
+  __device__ __forceinline__ uint32_t atom_min(int32_t v, uint32_t p) const {
+    if (!hint) return atomicMin(t + v, p);
+    uint32_t r;
+    asm volatile("atom.global.min.L2::cache_hint.u32 %0, [%1], %2, %3;"
+                 : "=r"(r) : "l"(t + v), "r"(p), "l"(pol) : "memory");
+    return r;
   }
 };
 __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, uint64_t pol) {
@@ -76,9 +90,14 @@ __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, ui
   asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(a), "l"(pol));
   return r;
 }
-
-// rowscan is stored part-major ([q][Fcap+1]) so that consecutive rows are contiguous
-__device__ __forceinline__ size_t rs_at(const GsWs &ws, int q, int i) { return (size_t)q * ((size_t)ws.Fcap + 1) + (size_t)i; }
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
 
 // owner = id % P (pyfrontend.cpp:57) without a hardware-unsupported modulo on the
 // hot path: a mask when P is a power of two, else multiply-high by ceil(2^32/P)
@@ -90,271 +109,447 @@ __device__ __forceinline__ int owner_of(const GsWs &ws, int32_t v) {
   return r < 0 ? r + ws.P : r;
 }
 
-// Tagged dedup table (ws.tag_shift = S > 0).  A sample draws L + 1 consecutive tag
-// indices e (seed claim, then one per layer); the stored tag is ntags - 1 - e, so
-// values written later are SMALLER: red.min overwrites anything left by earlier
-// layers or samples, and a reader that finds another tag sees "no occurrence".
-// Index 0 is never used (its tag is the all-ones fill pattern).
-__device__ __forceinline__ uint32_t table_tag(const GsWs &ws, int use) {
-  if (!ws.tag_shift) return 0u;
-  const uint32_t e = __ldcg(ws.epoch + 1) + (uint32_t)use;
-  return ((1u << (32 - ws.tag_shift)) - 1u - e) << ws.tag_shift;
+// Dedup-table entries are (tag | kind | payload), S = ws.pos_bits payload bits.
+// A sample uses ONE tag; tags count DOWN from sample to sample, so whatever an
+// earlier sample left behind is larger than anything this sample writes: it
+// loses every atom.min and reads as "never seen".  Nothing is reset between
+// layers or samples (DuplicateRemover::clear, duplicate.cpp:28-33, has no
+// counterpart); k_tail refills the table when a slot runs out of tags.  Within
+// a sample kind 0 (frontier row) < kind 1 (edge position): an atom.min of an
+// edge position never displaces the row mark, and returns it.
+struct Tag {
+  uint32_t tg;    // this sample's tag, in place
+  uint32_t kind;  // 1 << S
+  uint32_t pmask; // payload mask
+  int tsh;        // S + 1
+  __device__ __forceinline__ Tag(const GsWs &ws, const GsState &st) {
+    const int S = ws.pos_bits;
+    tsh = S + 1;
+    kind = 1u << S;
+    pmask = kind - 1u;
+    tg = ((1u << (31 - S)) - 1u - st.tag_idx) << tsh;
+  }
+  __device__ __forceinline__ bool mine(uint32_t e) const { return ((e ^ tg) >> tsh) == 0u; }
+};
+
+// bit q of a mask -> byte q of a packed counter word
+// (multiply replicates the mask byte into all eight bytes, the AND keeps bit q in
+// byte q, + 0x7F carries any kept bit into bit 7 of its byte)
+__device__ __forceinline__ unsigned long long pk_spread(uint32_t mask) {
+  const unsigned long long v = ((unsigned long long)(mask & 0xFFu) * 0x0101010101010101ull) & 0x8040201008040201ull;
+  return ((v + 0x7F7F7F7F7F7F7F7Full) >> 7) & 0x0101010101010101ull;
+}
+// warp sum of a packed word whose bytes are <= 7 per lane: two redux instructions
+__device__ __forceinline__ unsigned long long pk_redux(unsigned long long v) {
+  const uint32_t lo = __reduce_add_sync(FULL, (uint32_t)v), hi = __reduce_add_sync(FULL, (uint32_t)(v >> 32));
+  return ((unsigned long long)hi << 32) | lo;
 }
 
-// ------------------------------------------------------------------ k_begin
-// One CTA.  Resets the sample header, narrows the seed ids (int64, pinned
-// host memory read over PCIe) into the slab as frontier 0.
-__global__ void __launch_bounds__(1024) k_begin(GsWs ws) {
-  gs_sample_header *h = ws.hdr;
-  const int n = ws.input->n_seeds;
-  __shared__ int s_bad;
-  __shared__ uint32_t s_tag;
-  if (threadIdx.x == 0) {
-    s_bad = 0;
-    s_tag = 0u;
-    if (ws.tag_shift) {
-      const uint32_t ntags = 1u << (32 - ws.tag_shift);
-      uint32_t e0 = ws.epoch[0];
-      if (e0 + (uint32_t)ws.L + 1u > ntags) e0 = 1u;  // out of tags: the previous k_finish refilled the table
-      ws.epoch[1] = e0;
-      ws.epoch[0] = e0 + (uint32_t)ws.L + 1u;
-      s_tag = (ntags - 1u - e0) << ws.tag_shift;
-    }
-  }
+__device__ __forceinline__ void stage_ws(GsWs &dst, const GsWs *__restrict__ src) {
+  const uint32_t *s = reinterpret_cast<const uint32_t *>(src);
+  uint32_t *d = reinterpret_cast<uint32_t *>(&dst);
+  for (int i = threadIdx.x; i < (int)(sizeof(GsWs) / 4); i += blockDim.x) d[i] = __ldg(s + i);
   __syncthreads();
-  gs_span *spans = &h->field[0][0][0];
-  for (int i = threadIdx.x; i < GS_MAX_LAYERS * GS_MAX_PARTS * GS_NUM_FIELDS; i += blockDim.x) {
-    spans[i].off = 0;
-    spans[i].len = 0;
-  }
-  for (int i = threadIdx.x; i <= GS_MAX_LAYERS; i += blockDim.x) {
-    h->frontier_len[i] = 0;
-    h->frontier[i].off = 0;
-    h->frontier[i].len = 0;
-    if (i < GS_MAX_LAYERS) {
-      h->cand_len[i] = 0;
-      h->draw_base[i] = 0;
-    }
-  }
-  bool bad = (n < 0 || n > ws.Fcap || (int64_t)n > ws.fslab_cap);
-  if (!bad)
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      int64_t v = ws.seeds_in[i];
-      if (v < 0 || v >= (int64_t)ws.num_nodes) {
-        s_bad = 1;
-      } else {
-        ws.fslab[i] = (int32_t)v;
-        // the table is all-INF between minibatches: a second claim of the same
-        // entry is a duplicate seed (k_rows_scan resets the claimed entries)
-        if (ws.tag_shift) {
-          // every other entry carries a larger tag (or the fill pattern): the min always
-          // takes the claim, and an old value with OUR tag is an earlier claim of this sample
-          const uint32_t old = atomicMin(ws.table + v, s_tag | (uint32_t)i);
-          if (((old ^ s_tag) >> ws.tag_shift) == 0u) s_bad = 1;
-        } else if (atomicCAS(ws.table + v, GS_INF, (uint32_t)i) != GS_INF) {
-          s_bad = 1;
-        }
-      }
-    }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    bad = bad || s_bad;
-    h->status = bad ? (int32_t)GS_ERR_SEED : 0;
-    h->num_layers = ws.L;
-    h->num_parts = ws.P;
-    h->n_seeds = n;
-    h->batch_index = ws.input->batch_index;
-    h->draw_cursor = *ws.draw_cursor;
-    h->edges = 0;
-    h->late_status = 0;
-    h->reserved[0] = ws.input->want_host;  // kept on the device: k_finish must not poll host memory from every thread  // late error raised inside a tiled kernel
-    const int nn = bad ? 0 : n;
-    h->slab_used = 0;
-    h->reserved[1] = (nn + 3) & ~3;  // frontier slab in use (int32 elements)
-    h->reserved[2] = 1;              // frontier spans index the frontier slab, not the sample slab
-    h->frontier_len[0] = nn;
-    h->frontier[0].off = 0;
-    h->frontier[0].len = nn;
-  }
 }
 
-// ------------------------------------------------------------- k_rows_count
-// Per frontier row: CSR extent and number of candidates c = 1 + (deg < fan or
-// fan < 0 ? deg : fan)  (slicer.cpp:6-22).  Tile sums + last-CTA spine give the
-// candidate offsets' per-CTA prefixes and C_l.
-__global__ void GS_BOUNDS k_rows_count(GsWs ws, int layer) {
-  gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
-  __shared__ unsigned long long s_w64[GS_NW + 1];
-  __shared__ uint32_t s_w[GS_NW + 1];
-  const int F = h->frontier_len[layer];
-  const int32_t *front = ws.fslab + h->frontier[layer].off;
-  const int fan = ws.fanouts[layer];
-  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
+// ------------------------------------------------------ decoupled look-back
+// Single-pass prefix over tiles handed out by a ticket (Merrill & Garland): a
+// tile publishes its aggregate, walks back over its predecessors' aggregates
+// until it meets a published inclusive prefix, then publishes its own.  Every
+// predecessor of a tile was drawn by a CTA that is already running, so the spin
+// always ends, whatever else shares the machine.  Executed by warp 0; counter c
+// lives in lane c % 32, round c / 32.  Status words carry the sample's scan
+// epoch, so descriptors are never reset (k_tail zeroes them once per 2^30 uses).
+template <typename T, int NPL, int NCPAD>
+__device__ __forceinline__ void tile_lookback(uint32_t *status, T *agg, T *inc, int tile, uint32_t ep,
+                                              const T (&mine)[NPL], T (&excl)[NPL]) {
+  const int lane = lane_id();
   {
-    unsigned long long csum = 0ull;
-    uint32_t ssum = 0u;
-    for (int t = t0; t < t1; t++) {
+    T *pub = (tile == 0 ? inc : agg) + (size_t)tile * NCPAD;
 #pragma unroll
-      for (int it = 0; it < GS_IPT; it++) {
-        const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-        if (i < F) {
-          const int32_t nd = front[i];
-          const int64_t s = __ldg(ws.indptr + nd), e = __ldg(ws.indptr + nd + 1);
-          const int32_t deg = (int32_t)(e - s);
-          ws.rowstart[i] = s;
-          ws.rowdeg[i] = deg;
-          const bool samp = fan >= 0 && deg >= fan;
-          csum += 1ull + (unsigned long long)(samp ? fan : deg);
-          ssum += samp ? 1u : 0u;
-        }
+    for (int j = 0; j < NPL; j++)
+      if (lane + 32 * j < NCPAD) pub[lane + 32 * j] = mine[j];
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      st_release(status + tile, (ep << 2) | (tile == 0 ? 2u : 1u));
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NPL; j++) excl[j] = (T)0;
+  if (tile == 0) return;
+  int t = tile - 1;
+  for (;;) {
+    const int tl = t - lane;
+    uint32_t pm, rm, need;
+    for (;;) {
+      const uint32_t st = tl >= 0 ? ld_acquire(status + tl) : ((ep << 2) | 2u);  // before tile 0: prefix 0
+      const bool ready = (st >> 2) == ep && (st & 3u) != 0u;
+      pm = __ballot_sync(FULL, ready && (st & 3u) == 2u);
+      rm = __ballot_sync(FULL, ready);
+      need = pm ? (((pm & (0u - pm)) << 1) - 1u) : FULL;  // lanes up to the nearest inclusive prefix
+      if ((rm & need) == need) break;
+      __nanosleep(32);
+    }
+    __syncwarp();
+    const int np = pm ? (__ffs((int)pm) - 1) : 32;  // tiles t .. t-np+1 give aggregates, tile t-np its prefix
+    for (int j = 0; j < np; j++) {
+      const T *a = agg + (size_t)(t - j) * NCPAD;
+#pragma unroll
+      for (int jj = 0; jj < NPL; jj++)
+        if (lane + 32 * jj < NCPAD) excl[jj] += __ldcg(a + lane + 32 * jj);
+    }
+    if (pm) {
+      const int tp = t - np;
+      if (tp >= 0) {
+        const T *a = inc + (size_t)tp * NCPAD;
+#pragma unroll
+        for (int jj = 0; jj < NPL; jj++)
+          if (lane + 32 * jj < NCPAD) excl[jj] += __ldcg(a + lane + 32 * jj);
       }
+      break;
     }
-    unsigned long long ctot;
-    uint32_t stot;
-    block_excl_scan64(csum, s_w64, ctot);
-    block_excl_scan(ssum, s_w, stot);
-    if (threadIdx.x == 0) {
-      ws.ftile_sum[blockIdx.x] = ctot;
-      ws.ftile_samp[blockIdx.x] = stot;
-    }
+    t -= 32;
   }
-  if (!last_block(ws.tickets + 0)) return;
-  // spine: exclusive prefixes over the CTAs' sums
-  const int nb = (int)gridDim.x;
-  const int chunk = (nb + GS_TPB - 1) / GS_TPB;
-  const int a = min(nb, (int)threadIdx.x * chunk), b = min(nb, a + chunk);
-  unsigned long long cs = 0ull;
-  uint32_t ss = 0u;
-  for (int t = a; t < b; t++) {
-    cs += __ldcg(ws.ftile_sum + t);
-    ss += __ldcg(ws.ftile_samp + t);
-  }
-  unsigned long long ctot;
-  uint32_t stot;
-  unsigned long long cpre = block_excl_scan64(cs, s_w64, ctot);
-  uint32_t spre = block_excl_scan(ss, s_w, stot);
-  const bool ok = ctot <= (unsigned long long)ws.Ccap;
-  if (ok)
-    for (int t = a; t < b; t++) {
-      ws.ftile_pre[t] = (uint32_t)cpre;
-      ws.ftile_pre[ws.ftiles_max + t] = spre;
-      cpre += __ldcg(ws.ftile_sum + t);
-      spre += __ldcg(ws.ftile_samp + t);
-    }
-  if (threadIdx.x == 0) {
-    if (!ok) {
-      h->status = (int32_t)GS_ERR_OVERFLOW;
-      h->cand_len[layer] = 0;
-    } else {
-      h->cand_len[layer] = (int32_t)ctot;
-      ws.off[F] = (uint32_t)ctot;
-      const uint64_t base = *ws.draw_cursor;
-      h->draw_base[layer] = base;
-      if (fan > 0) *ws.draw_cursor = base + (uint64_t)fan * (uint64_t)stot;
+  {
+    T *pub = inc + (size_t)tile * NCPAD;
+#pragma unroll
+    for (int j = 0; j < NPL; j++)
+      if (lane + 32 * j < NCPAD) pub[lane + 32 * j] = excl[j] + mine[j];
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      st_release(status + tile, (ep << 2) | 2u);
     }
   }
 }
 
-// -------------------------------------------------------------- k_rows_scan
-// Candidate offset of every row (k_expand writes the stream, self entries
-// included); resets the row node's table entry to "no edge-source
-// occurrence yet" (entries touched in earlier layers all belong to frontier
-// nodes), records which row each candidate tile starts in, and zeroes the
-// frontier-first counters k_cand_flags accumulates into with atomics.
-__global__ void GS_BOUNDS k_rows_scan(GsWs ws, int layer) {
+// ------------------------------------------------------------------- k_rows
+// Sample header at the start of a sample (the CTA that draws tile 0 of layer 0
+// runs this BEFORE it publishes its tile; every other CTA reports errors only
+// after its look-back, which orders it behind that publication).
+__device__ void init_header(const GsWs &ws, int n, int status) {
   gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
-  const Tbl tbl(ws);
-  __shared__ uint32_t s_w[GS_NW + 1];
-  const int F = h->frontier_len[layer];
-  const int32_t *front = ws.fslab + h->frontier[layer].off;
-  const int fan = ws.fanouts[layer];
-  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
-  for (int k = blockIdx.x * GS_TPB + threadIdx.x; k < ws.ctiles_max; k += gridDim.x * GS_TPB)
-    ws.ctile_cnt[k] = 0u;
-  uint32_t base = ws.ftile_pre[blockIdx.x];  // running over this CTA's run of tiles
-  uint32_t sbase = ws.ftile_pre[ws.ftiles_max + blockIdx.x];
-  for (int t = t0; t < t1; t++) {
-#pragma unroll
-    for (int it = 0; it < GS_IPT; it++) {
-      const int i = t * GS_TILE + it * GS_TPB + threadIdx.x;
-      uint32_t c = 0u, sflag = 0u;
-      int32_t nd = 0;
-      if (i < F) {
-        nd = front[i];
-        const int32_t deg = ws.rowdeg[i];
-        const bool samp = fan >= 0 && deg >= fan;
-        c = 1u + (uint32_t)(samp ? fan : deg);
-        sflag = samp ? 1u : 0u;
-      }
-      uint32_t ctot, stot = 0u;
-      const uint32_t ex = block_excl_scan(c, s_w, ctot);
-      uint32_t sex = 0u;
-      if (replay) sex = block_excl_scan(sflag, s_w, stot);
-      if (i < F) {
-        const uint32_t o = base + ex;
-        ws.off[i] = o;
-        if (replay) ws.samp_rank[i] = sbase + sex;
-        if (!ws.tag_shift) tbl.st(nd, GS_INF);  // tagged table: entries of earlier layers are stale by their tag
-        for (uint32_t tb = (o + GS_TILE - 1) / GS_TILE; (uint64_t)tb * GS_TILE < (uint64_t)o + c; tb++)
-          ws.tile_first[tb] = (uint32_t)i;
-      }
-      base += ctot;
-      sbase += stot;
+  h->status = status;
+  h->num_layers = ws.L;
+  h->num_parts = ws.P;
+  h->n_seeds = n;
+  h->batch_index = ws.input->batch_index;
+  h->draw_cursor = *ws.draw_cursor;
+  h->edges = 0;
+  h->late_status = 0;
+  h->feature_rows = 0;
+  h->reserved[0] = ws.input->want_host;
+  h->slab_used = 0;
+  h->reserved[1] = (n + 3) & ~3;  // frontier slab in use (int32 elements)
+  h->reserved[2] = 1;             // frontier spans index the frontier slab, not the sample slab
+  for (int l = 0; l <= GS_MAX_LAYERS; l++) {
+    h->frontier_len[l] = l == 0 ? n : 0;
+    h->frontier[l].off = 0;
+    h->frontier[l].len = l == 0 ? n : 0;
+    if (l < GS_MAX_LAYERS) h->cand_len[l] = 0;
+  }
+}
+
+// Per frontier row: CSR extent and number of candidates c = 1 + (deg < fan or
+// fan < 0 ? deg : fan) (slicer.cpp:6-22), exclusive scan -> first candidate
+// position; rank of the row among the rows of its owner (= its slot in
+// self_ids_in / self_ids_out, slicer.cpp:33-34); the row's mark in the dedup
+// table.  FIRST: the rows are the seeds, read as int64 from pinned host memory,
+// checked and narrowed; claiming their table entries with atom.min doubles as
+// the duplicate-seed check.
+template <bool FIRST>
+__device__ void rows_role(const GsWs &ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  __shared__ unsigned long long s_wc[GS_NW][GS_RS_NC];
+  __shared__ unsigned long long s_base[GS_NW][GS_RS_NC];
+  __shared__ unsigned long long s_agg[GS_RS_NC], s_pre[GS_RS_NC];
+  __shared__ int s_tile;
+  if (!FIRST && h->status != 0) return;
+  const int P = ws.P, NC = 2 + P;
+  const int lane = lane_id(), w = warp_id();
+  int F;
+  const int32_t *front = nullptr;
+  int first_status = 0;
+  if (FIRST) {
+    F = ws.input->n_seeds;
+    if (F < 0) {
+      first_status = GS_SKIPPED;
+      F = 0;
+    } else if (F > ws.Fcap || (int64_t)F > ws.fslab_cap) {
+      first_status = (int)GS_ERR_SEED;
+      F = 0;
     }
+  } else {
+    F = h->frontier_len[layer];
+    front = ws.fslab + h->frontier[layer].off;
+  }
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
+  uint32_t *tick = ws.tickets + layer * GS_TICKETS;
+  if (ntiles == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      if (FIRST) init_header(ws, 0, first_status);
+      h->cand_len[layer] = 0;
+      ws.off[0] = 0u;
+      h->draw_base[layer] = *ws.draw_cursor;
+    }
+    return;
+  }
+  const int fan = ws.fanouts[layer];
+  const GsState stt = *ws.state;
+  const uint32_t ep = stt.scan_epoch + 2u * (uint32_t)layer;
+  const Tag tag(ws, stt);
+  const Tbl tbl(ws);
+  const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
+  unsigned long long *rs_agg = ws.rs_val, *rs_inc = ws.rs_val + (size_t)ws.ftiles_cap * GS_RS_NC;
+  bool bad = false;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick + 0, 1u);
+  __syncthreads();
+  int t = s_tile;
+  while (t < ntiles) {
+    if (FIRST && t == 0 && threadIdx.x == 0) init_header(ws, F, 0);
+    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    int32_t nd[GS_IPT];
+    int64_t rs[GS_IPT];
+    int32_t deg[GS_IPT];
+    int g0[GS_IPT];
+    if (FIRST) {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        nd[k] = 0;
+        if (i0 + k < F) {
+          const int64_t v = ws.seeds_in[i0 + k];
+          if (v < 0 || v >= (int64_t)ws.num_nodes) bad = true;
+          else nd[k] = (int32_t)v;
+        }
+      }
+    } else if (i0 + GS_IPT <= F) {
+      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
+      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) nd[k] = i0 + k < F ? front[i0 + k] : 0;
+    }
+    int64_t e_[GS_IPT];
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      rs[k] = 0; e_[k] = 0;
+      if (i0 + k < F) {
+        rs[k] = __ldg(ws.indptr + nd[k]);
+        e_[k] = __ldg(ws.indptr + nd[k] + 1);
+      }
+    }
+    unsigned long long c4 = 0ull, pk4 = 0ull;
+    uint32_t s4 = 0u;
+    uint32_t c[GS_IPT];
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      deg[k] = (int32_t)(e_[k] - rs[k]);
+      c[k] = 0u;
+      g0[k] = 0;
+      if (i0 + k < F) {
+        const bool samp = fan >= 0 && deg[k] >= fan;
+        c[k] = 1u + (uint32_t)(samp ? fan : deg[k]);
+        s4 += samp ? 1u : 0u;
+        g0[k] = owner_of(ws, nd[k]);
+        pk4 += pk_one(g0[k]);
+        c4 += c[k];
+      }
+    }
+    const unsigned long long inc_c = warp_incl_scan64(c4), inc_pk = pk_warp_incl(pk4);
+    const uint32_t inc_s = warp_incl_scan(s4);
+    {
+      const unsigned long long tot_pk = __shfl_sync(FULL, inc_pk, 31);
+      if (lane == 31) {
+        s_wc[w][0] = inc_c;
+        s_wc[w][1] = inc_s;
+      }
+      if (lane < P) s_wc[w][2 + lane] = pk_get(tot_pk, lane);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick + 0, 1u);  // next tile of this CTA (read after the barrier below)
+    if (lane < NC) {
+      unsigned long long a = 0ull, all = 0ull;
+#pragma unroll
+      for (int k = 0; k < GS_NW; k++) {
+        const unsigned long long x = s_wc[k][lane];
+        if (k < w) a += x;
+        all += x;
+      }
+      s_base[w][lane] = a;
+      if (w == 0) s_agg[lane] = all;
+    }
+    if (w == 0) {
+      __syncwarp();
+      unsigned long long mine[1], excl[1];
+      mine[0] = lane < NC ? s_agg[lane] : 0ull;
+      tile_lookback<unsigned long long, 1, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, mine, excl);
+      if (lane < GS_RS_NC) s_pre[lane] = excl[0];
+    }
+    __syncthreads();
+    if (FIRST && bad) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);
+    unsigned long long base_c = s_pre[0] + s_base[w][0] + inc_c - c4;
+    uint32_t base_s = (uint32_t)(s_pre[1] + s_base[w][1]) + inc_s - s4;
+    unsigned long long r_pk = inc_pk - pk4;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      const int i = i0 + k;
+      if (i < F) {
+        const uint32_t o = (uint32_t)base_c;
+        ws.off[i] = o;
+        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k], (int)(uint32_t)((uint64_t)rs[k] >> 32), deg[k], nd[k]);
+        ws.selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
+        ws.ea[i] = GS_INF;
+        ws.rowhas[i] = 0u;
+        if (replay) ws.samp_rank[i] = base_s;
+        if (FIRST) {
+          ws.fslab[i] = nd[k];
+          // a second claim of the same entry under this sample's tag is a duplicate seed
+          if (!bad || nd[k] != 0 || ws.seeds_in[i] == 0) {
+            const uint32_t old = atomicMin(ws.table + nd[k], tag.tg | (uint32_t)i);
+            if (tag.mine(old)) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);
+          }
+        } else {
+          tbl.st(nd[k], tag.tg | (uint32_t)i);
+        }
+        // candidate tiles that start inside this row
+        const unsigned long long end = base_c + c[k];
+        for (unsigned long long tb = (base_c + GS_TILE - 1) / GS_TILE;
+             tb * GS_TILE < end && tb < (unsigned long long)ws.ctiles_cap; tb++)
+          ws.tile_first[tb] = (uint32_t)i;
+        base_c = end;
+        const bool samp = fan >= 0 && deg[k] >= fan;
+        base_s += samp ? 1u : 0u;
+        r_pk += pk_one(g0[k]);
+      }
+    }
+    if (t == ntiles - 1 && threadIdx.x == 0) {
+      const unsigned long long ctot = s_pre[0] + s_agg[0];
+      const unsigned long long stot = s_pre[1] + s_agg[1];
+      if (ctot > (unsigned long long)ws.Ccap) {
+        atomicCAS(&h->status, 0, (int)GS_ERR_OVERFLOW);
+        h->cand_len[layer] = 0;
+      } else {
+        h->cand_len[layer] = (int32_t)ctot;
+        ws.off[F] = (uint32_t)ctot;
+        const uint64_t base = *ws.draw_cursor;
+        h->draw_base[layer] = base;
+        if (fan > 0) *ws.draw_cursor = base + (uint64_t)fan * (uint64_t)stot;
+      }
+      for (int q = 0; q < P; q++) cnt[GS_CNT_SELF(P, q)] = (uint32_t)(s_pre[2 + q] + s_agg[2 + q]);
+    }
+    __syncthreads();
+    t = s_tile;
   }
 }
 
 // ----------------------------------------------------------------- k_expand
+// Lays out every list of the layer.  Runs in the last CTA of k_expand: by then
+// the per-layer totals are exact (see expand_role), so k_cand writes each list
+// once, at its final place; a part's nine lists are contiguous.
+__device__ void layer_alloc(const GsWs &ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  const int P = ws.P;
+  const uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
+  const int F = h->frontier_len[layer];
+  bool ok = true;
+  const unsigned long long fnext = (unsigned long long)F + __ldcg(cnt + GS_CNT_NEW);
+  if (layer + 1 < ws.L && fnext > (unsigned long long)ws.Fcap) ok = false;
+  int64_t used = h->slab_used, fused = h->reserved[1];
+  const gs_span fs = slab_alloc(fused, ws.fslab_cap, (uint32_t)fnext, ok);
+  int64_t edges = 0;
+  for (int q = 0; q < P && ok; q++) {
+    const uint32_t n_in = __ldcg(cnt + GS_CNT_IN(P, q)), n_e = __ldcg(cnt + GS_CNT_E(P, q)),
+                   n_out = __ldcg(cnt + GS_CNT_OUT(P, q)), n_own = __ldcg(cnt + GS_CNT_OWN(P, q)),
+                   n_to = __ldcg(cnt + GS_CNT_TO(P, q)), n_self = __ldcg(cnt + GS_CNT_SELF(P, q));
+    gs_span *fl = h->field[layer][q];
+    fl[GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, n_in, ok);
+    fl[GS_F_OUT_NODES] = slab_alloc(used, ws.slab_cap, n_out, ok);
+    fl[GS_F_OWNED_OUT] = slab_alloc(used, ws.slab_cap, n_own, ok);
+    fl[GS_F_FROM_IDS] = slab_alloc(used, ws.slab_cap, n_out - n_own, ok);
+    fl[GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, n_to, ok);
+    fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, n_self, ok);
+    fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, n_self, ok);
+    const gs_span ip = slab_alloc(used, ws.slab_cap, n_out + 1u, ok);
+    fl[GS_F_CSR_INDPTR] = ip;
+    fl[GS_F_CSR_INDICES] = slab_alloc(used, ws.slab_cap, n_e, ok);
+    if (ok) ws.slab[ip.off + n_out] = (int32_t)n_e;  // row pointer sentinel
+    edges += n_e;
+  }
+  if (ok) {
+    h->slab_used = used;
+    h->reserved[1] = (int32_t)fused;
+    h->frontier[layer + 1] = fs;
+    h->frontier_len[layer + 1] = (int32_t)fnext;
+    h->edges += edges;
+  } else {
+    atomicCAS(&h->status, 0, (int)GS_ERR_OVERFLOW);
+  }
+}
+
 // Candidate-parallel CSR row expansion (slicer.cpp:6-22).  A tile is GS_TILE
 // consecutive candidate positions, so load is balanced whatever the degree
 // skew; the rows a tile touches are found from tile_first[] and a binary
 // search over their offsets staged in shared memory.  Slots >= 1 of a row are
 // either all its neighbours in CSR order (coalesced reads) or `fan` picks with
-// replacement.  Every real edge source does atomicMin(position) into the
-// direct-address table -- the parallel form of DuplicateRemover's first-
-// occurrence rule (util/duplicate.cpp:14-26).
+// replacement.  Every real edge source v does ONE returning atom.min(position)
+// on its table entry -- the parallel form of DuplicateRemover's first-occurrence
+// rule (util/duplicate.cpp:14-26).  The value it returns is
+//   * stale (another sample's tag): v is new to the frontier and this is the
+//     first arrival for v        -> one more next-frontier node, one more in_node;
+//   * a frontier-row mark (kind 0): v is row idx of the current frontier; its
+//     minimum edge position is kept per ROW (ea[idx], an F-sized array) and the
+//     candidate carries idx instead of v, so k_cand never needs v's self position
+//     from an N-sized table;
+//   * an edge position of this layer: nothing to count.
+// One atomicOr per (thread, row) on rowhas[] finds the first edge of a row into
+// each part: out_nodes / owned / to list lengths.  With the per-part edge counts
+// these are ALL the list lengths of the layer, exact, before k_cand starts.
 // RNG (gs_rng_mode) is a template parameter: the pick path of the other two
 // modes costs instructions in a kernel bound by issue.
 template <int RNG>
-__global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
+__device__ void expand_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const Tbl tbl(ws);
   const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
   __shared__ uint32_t s_off[GS_TILE + 2];
+  __shared__ uint32_t s_cnt[GS_CNT_STRIDE];
+  const int P = ws.P;
   const int F = h->frontier_len[layer];
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   const int fan = ws.fanouts[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   const uint32_t batch = (uint32_t)h->batch_index;
   constexpr bool replay = RNG == (int)GS_RNG_DRAWS;
   constexpr bool norepl = RNG == (int)GS_RNG_PHILOX_NOREPLACE;
   const uint64_t dbase = h->draw_base[layer];
-  const uint32_t tg = table_tag(ws, 1 + layer);
+  const GsState stt = *ws.state;
+  const Tag tag(ws, stt);
+  const uint32_t tge = tag.tg | tag.kind;
+  uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
+  const int lane = lane_id();
+  if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int i_lo = (int)ws.tile_first[t];
     const int i_hi = (t + 1 < ntiles) ? (int)ws.tile_first[t + 1] : F - 1;
-    const int cnt = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
-    for (int k = threadIdx.x; k <= cnt; k += GS_TPB) s_off[k] = ws.off[i_lo + k];
+    const int cntr = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
+    for (int k = threadIdx.x; k <= cntr; k += GS_TPB) s_off[k] = ws.off[i_lo + k];
     __syncthreads();
-    // A thread owns GS_IPT CONSECUTIVE positions (the kernel is bound by
-    // instruction issue): one binary search, then a walk; one Philox block serves
-    // up to four picks of a row; the stream goes out as 16-byte / 4-byte vectors.
+    // A thread owns GS_IPT CONSECUTIVE positions: one binary search, then a walk;
+    // one Philox block serves up to four picks of a row; the stream goes out as
+    // 16-byte / 4-byte vectors.
     const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     int row[GS_IPT], slot[GS_IPT];
     int32_t nd1[GS_IPT], deg[GS_IPT];
     int64_t rs[GS_IPT];
     int lo = 0;
     if (p0 < C) {
-      int hi = cnt - 1;  // largest k with s_off[k] <= p0
+      int hi = cntr - 1;  // largest k with s_off[k] <= p0
       while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;
         if (s_off[mid] <= p0) lo = mid; else hi = mid - 1;
@@ -365,7 +560,7 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
       const uint32_t p = p0 + k;
       if (k > 0 && p < C && p >= s_off[lo + 1]) lo++;  // every row has >= 1 candidate: one step is enough
       row[k] = i_lo + lo;
-      slot[k] = p < C ? (int)(p - s_off[lo]) : 0;  // 0 = self entry (or dead position)
+      slot[k] = p < C ? (int)(p - s_off[lo]) : -1;  // 0 = self entry, -1 = past the end
     }
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
@@ -374,9 +569,10 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
         rs[k] = rs[k - 1];
         deg[k] = deg[k - 1];
       } else {
-        nd1[k] = front[row[k]];
-        rs[k] = ws.rowstart[row[k]];
-        deg[k] = ws.rowdeg[row[k]];
+        const int4 ri = ws.rowinfo[row[k]];
+        rs[k] = (int64_t)(((uint64_t)(uint32_t)ri.y << 32) | (uint32_t)ri.x);
+        deg[k] = ri.z;
+        nd1[k] = ri.w;
       }
     }
     const int32_t *src[GS_IPT];
@@ -414,18 +610,69 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++)
       if (src[k]) v[k] = ld_stream_i32(src[k], ws.l2_hints != 0, spol);
-    int32_t cvv[GS_IPT];
-    uint32_t cf[GS_IPT];
+    // one returning atom.min per real edge source, all four in flight
+    int g[GS_IPT];
+    uint32_t old[GS_IPT];
+    bool edge[GS_IPT];
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      cvv[k] = row[k];  // self entry: the row index
-      cf[k] = GS_CF_SELF;
-      if (src[k]) {
-        cvv[k] = v[k];
-        cf[k] = v[k] != nd1[k] ? 0u : GS_CF_LOOP;
-        if (cf[k] == 0u) tbl.min(v[k], tg | (p0 + k));
+      edge[k] = src[k] != nullptr && v[k] != nd1[k];
+      g[k] = 0;
+      old[k] = 0u;
+      if (edge[k]) {
+        g[k] = owner_of(ws, v[k]);
+        old[k] = tbl.atom_min(v[k], tge | (p0 + k));
       }
     }
+    int32_t cvv[GS_IPT];
+    uint32_t cf[GS_IPT], rbits[GS_IPT];
+    unsigned long long pk_in = 0ull, pk_e = 0ull, pk_out = 0ull, pk_own = 0ull, pk_to = 0ull;
+    uint32_t n_new = 0u;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      rbits[k] = 0u;
+      if (slot[k] == 0) {
+        cvv[k] = row[k];  // self entry: the row index; part = owner of the row's node
+        cf[k] = GS_CK_SELF | ((uint32_t)owner_of(ws, nd1[k]) << GS_CF_PART_SHIFT);
+      } else if (!edge[k]) {
+        cvv[k] = 0;
+        cf[k] = GS_CK_DEAD;
+      } else {
+        cvv[k] = v[k];
+        cf[k] = GS_CK_EDGE | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
+        pk_e += pk_one(g[k]);
+        rbits[k] = 1u << g[k];
+        if (!tag.mine(old[k])) {  // first arrival for a node that is new to the frontier
+          n_new++;
+          pk_in += pk_one(g[k]);
+        } else if (!(old[k] & tag.kind)) {  // a row of the current frontier
+          const uint32_t idx = old[k] & tag.pmask;
+          if (atomicMin(ws.ea + idx, p0 + k) == GS_INF) pk_in += pk_one(g[k]);
+          cvv[k] = (int32_t)idx;
+          cf[k] = GS_CK_FHIT | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
+        }
+      }
+    }
+    // first edge of a row into each part: one atomicOr per run of equal rows
+#pragma unroll
+    for (int k = 0; k + 1 < GS_IPT; k++)
+      if (row[k + 1] == row[k]) {
+        rbits[k + 1] |= rbits[k];
+        rbits[k] = 0u;
+      }
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++)
+      if (rbits[k]) {
+        const uint32_t was = atomicOr(ws.rowhas + row[k], rbits[k]);
+        const uint32_t nb = rbits[k] & ~was;
+        if (nb) {
+          const int g0 = owner_of(ws, nd1[k]);
+          const uint32_t own = 1u << g0;
+          pk_out += pk_spread(nb);
+          if (nb & own) pk_own += pk_one(g0);
+          if ((nb & ~own) && !(was & ~own)) pk_to += pk_one(g0);
+        }
+      }
     if (p0 + GS_IPT <= C) {
       *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(cvv[0], cvv[1], cvv[2], cvv[3]);
       *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
@@ -438,56 +685,86 @@ __global__ void GS_BOUNDS k_expand(GsWs ws, int layer) {
           ws.cflag[p0 + k] = (uint8_t)cf[k];
         }
     }
+    // per-tile totals: a lane adds at most GS_IPT to a byte, a warp at most 128
+    pk_in = pk_redux(pk_in);
+    pk_e = pk_redux(pk_e);
+    pk_out = pk_redux(pk_out);
+    pk_own = pk_redux(pk_own);
+    pk_to = pk_redux(pk_to);
+    n_new = __reduce_add_sync(FULL, n_new);
+    if (lane < P) {
+      uint32_t x;
+      if ((x = pk_get(pk_in, lane))) atomicAdd(&s_cnt[GS_CNT_IN(P, lane)], x);
+      if ((x = pk_get(pk_e, lane))) atomicAdd(&s_cnt[GS_CNT_E(P, lane)], x);
+      if ((x = pk_get(pk_out, lane))) atomicAdd(&s_cnt[GS_CNT_OUT(P, lane)], x);
+      if ((x = pk_get(pk_own, lane))) atomicAdd(&s_cnt[GS_CNT_OWN(P, lane)], x);
+      if ((x = pk_get(pk_to, lane))) atomicAdd(&s_cnt[GS_CNT_TO(P, lane)], x);
+    }
+    if (lane == 31 && n_new) atomicAdd(&s_cnt[GS_CNT_NEW], n_new);
     __syncthreads();
   }
+  __syncthreads();
+  if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);
+  if (!last_block(ws.tickets + layer * GS_TICKETS + 1)) return;
+  if (threadIdx.x == 0) layer_alloc(ws, layer);
 }
 
-// ------------------------------------------------------------- k_cand_flags
-// With every minimum in place, classify each candidate.  An edge candidate is
-// the first occurrence of its source as an edge source (-> in_nodes of the
-// owner's bipartite, bipartite.cpp:4) when the table holds its own position;
-// it then also claims the node's slot in the next frontier (slicer.cpp:45-49).
-// A frontier row's self entry at s sees the node's minimum edge position a: the
-// node's frontier slot is at min(a, s), so when s < a the self entry takes the
-// slot and revokes the edge candidate's claim (kill[a] = 1, one less first in
-// the CTA that owns position a).  Every other edge candidate replaces its node
-// id by the position of the first occurrence: that is all k_cand_apply and
-// k_relabel need to relabel it.  Per-CTA counts of the 2P+1 classes, then the
-// last CTA scans them, fixes F_{l+1}, |in_nodes_g|, E_g and lays the lists out.
-__global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
+// ------------------------------------------------------------------- k_cand
+// The one pass over the candidate stream.  With every minimum in place:
+//   edge of a NEW node v at p:   first occurrence iff table[v] holds p  -> in_nodes of its
+//                                owner's part (bipartite.cpp:4) and the next frontier (slicer.cpp:45-49);
+//   edge of frontier ROW idx:    first edge occurrence iff ea[idx] == p -> in_nodes; it is the node's
+//                                frontier slot only if it precedes the row's self entry (p < off[idx]);
+//   self entry of row i at s:    frontier slot iff no edge of the node came earlier (ea[i] > s); it also
+//                                closes the ROW side: has = rowhas[i] says which parts the row has
+//                                edges in: out_g (bipartite.h:59-62), owned_g (:56-58), to_g0
+//                                (slicer.cpp:41), self_g0 (slicer.cpp:33-34), from_g = out_g minus
+//                                owned_g, csr_indptr = edges of part g before s.
+// Ranks = exclusive prefix over positions of 1 + 5 P counters: per-thread packed
+// counts (one byte per part), one packed warp scan per kind, cross-warp bases in
+// shared memory, tile prefix by decoupled look-back.  A first occurrence records
+// its in_nodes rank at its own position in the (now dead) candidate word: that is
+// the relabel map (DuplicateRemover::mask, duplicate.cpp:21) indexed by position,
+// which relabel_role reads for every later occurrence.
+#define CS_NF 0
+#define CS_IN(q) (1 + (q))
+#define CS_E(q) (9 + (q))
+#define CS_OUT(q) (17 + (q))
+#define CS_OWN(q) (25 + (q))
+#define CS_TO(q) (33 + (q))
+#define CS_USED 41
+__device__ void cand_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  __shared__ uint32_t s_wc[GS_NW][GS_CS_NC];    // per-warp totals of the tile
+  __shared__ uint32_t s_base[GS_NW][GS_CS_NC];  // earlier warps of the tile (+ tile prefix, added below)
+  __shared__ uint32_t s_pre[GS_CS_NC];
+  __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
+  __shared__ int s_tile;
   const Tbl tbl(ws);
-  __shared__ uint32_t s_cnt[GS_NC_MAX];
-  __shared__ uint32_t s_tot[GS_NC_MAX];
-  __shared__ uint32_t s_w[GS_NW + 1];
-  const int P = ws.P, NC = 2 * P + 1;
-  const int F = h->frontier_len[layer];
+  const int P = ws.P;
   const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *front = ws.fslab + h->frontier[layer].off;
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
-  const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles per CTA (cta_tiles)
-  // tile / per by multiply-high: exact while tile * per < 2^32 (ntiles <= 65536)
-  const bool per_inv_ok = per > 1 && ntiles <= 65536;
-  const uint32_t per_inv = per_inv_ok ? (uint32_t)((0x100000000ull + (uint32_t)per - 1) / (uint32_t)per) : 0u;
-  // running class counts of this warp over the CTA's tiles: lane q < P keeps part q
-  uint32_t acc_i = 0u, acc_e = 0u, acc_f = 0u;
-  const uint32_t tg = table_tag(ws, 1 + layer);
-  const int tsh = ws.tag_shift;
-  if (threadIdx.x < GS_NC_MAX) s_cnt[threadIdx.x] = 0u;
+  if (ntiles == 0) return;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
+  int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
+  const GsState stt = *ws.state;
+  const uint32_t ep = stt.scan_epoch + 2u * (uint32_t)layer + 1u;
+  const Tag tag(ws, stt);
+  uint32_t *cs_agg = ws.cs_val, *cs_inc = ws.cs_val + (size_t)ws.ctiles_cap * GS_CS_NC;
+  uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
+  const int lane = lane_id(), w = warp_id();
+  if (threadIdx.x < P * GS_NUM_FIELDS)
+    s_fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
+        h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);
   __syncthreads();
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
-  for (int t = t0; t < t1; t++) {
-    // A thread owns GS_IPT consecutive positions: vector loads / stores of the
-    // stream, its GS_IPT random table reads in flight together, lane-local
-    // packed counts and one warp reduction per tile.
-    unsigned long long pk_i = 0ull, pk_e = 0ull;  // this lane's firsts / edges per part
-    uint32_t n_ff = 0u;
-    uint32_t fl[GS_IPT], te[GS_IPT];
-    int32_t ci[GS_IPT], cv[GS_IPT];
+  int t = s_tile;
+  while (t < ntiles) {
     const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     const bool full = p0 + GS_IPT <= C;
+    uint32_t fl[GS_IPT];
+    int32_t ci[GS_IPT];
     if (full) {
       const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
       const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
@@ -496,7 +773,7 @@ __global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
     } else {
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
-        fl[k] = GS_CF_LOOP;  // dead position
+        fl[k] = GS_CK_DEAD;
         ci[k] = 0;
         if (p0 + k < C) {
           fl[k] = ws.cflag[p0 + k];
@@ -504,548 +781,192 @@ __global__ void GS_BOUNDS k_cand_flags(GsWs ws, int layer) {
         }
       }
     }
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) cv[k] = (fl[k] & GS_CF_SELF) ? front[ci[k]] : ci[k];
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      te[k] = 0u;
-      if (!(fl[k] & GS_CF_LOOP)) te[k] = tbl.ld(cv[k]);
-    }
-    if (tsh) {  // this layer's tag -> the position; any other tag -> no occurrence
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++) te[k] = ((te[k] ^ tg) >> tsh) == 0u ? (te[k] ^ tg) : GS_INF;
-    }
+    // x: minimum position (edge: of its source; self: of the row's node as an edge source)
+    // y: self: rowhas; frontier-row edge: the row's self position
+    // z: self / frontier-row edge: the node id
+    uint32_t x[GS_IPT], y[GS_IPT];
+    int32_t z[GS_IPT];
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      const uint32_t p = p0 + k;
-      const uint32_t f = fl[k];
-      if (f & GS_CF_SELF) {
-        const uint32_t a = te[k];
-        ws.rowa[ci[k]] = a;
-        const bool ffirst = a > p;
-        if (ffirst && a != GS_INF) {  // revoke the claim of the edge candidate at a
-          ws.kill[a] = 1;
-          const uint32_t ta = a / GS_TILE;
-          const int cta = per == 1 ? (int)ta : (per_inv_ok ? (int)__umulhi(ta, per_inv) : (int)ta / per);
-          atomicSub(&ws.ctile_cnt[min(cta, (int)gridDim.x - 1)], 1u);
-        }
-        n_ff += ffirst ? 1u : 0u;
-        fl[k] = GS_CF_SELF | (ffirst ? GS_CF_FFIRST : 0u);
-      } else if (!(f & GS_CF_LOOP)) {
-        const bool ifirst = te[k] == p;  // also claims the frontier slot, unless revoked
-        const int g = owner_of(ws, cv[k]);
-        pk_e += pk_one(g);
-        if (ifirst) {
-          pk_i += pk_one(g);
-          n_ff++;
-        } else {
-          ci[k] = (int32_t)te[k];
-        }
-        fl[k] = (ifirst ? (GS_CF_FFIRST | GS_CF_IFIRST) : 0u) | ((uint32_t)g << GS_CF_PART_SHIFT);
+      const uint32_t kind = fl[k] & GS_CK_MASK;
+      x[k] = GS_INF; y[k] = 0u; z[k] = ci[k];
+      if (kind == GS_CK_EDGE) {
+        x[k] = tbl.ld(ci[k]) & tag.pmask;
+      } else if (kind != GS_CK_DEAD) {
+        x[k] = __ldcg(ws.ea + ci[k]);
+        y[k] = kind == GS_CK_SELF ? __ldcg(ws.rowhas + ci[k]) : __ldcg(ws.off + ci[k]);
+        z[k] = front[ci[k]];
       }
     }
-    if (full) {
-      *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
-      *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
-          make_uchar4((unsigned char)fl[0], (unsigned char)fl[1], (unsigned char)fl[2], (unsigned char)fl[3]);
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++)
-        if (p0 + k < C) {
-          ws.cand[p0 + k] = ci[k];
-          ws.cflag[p0 + k] = (uint8_t)fl[k];
-        }
-    }
-    // one packed reduction per tile instead of 2P+1 ballots per round
-    pk_i = pk_warp_sum(pk_i);
-    pk_e = pk_warp_sum(pk_e);
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) n_ff += __shfl_xor_sync(FULL, n_ff, d);
-    // every lane holds the warp totals: lane q keeps the running count of part q
-    acc_i += pk_get(pk_i, lane_id() & 7);
-    acc_e += pk_get(pk_e, lane_id() & 7);
-    acc_f += n_ff;
-  }
-  if (lane_id() < P) {
-    if (acc_i) atomicAdd(&s_cnt[1 + lane_id()], acc_i);
-    if (acc_e) atomicAdd(&s_cnt[1 + P + lane_id()], acc_e);
-  }
-  if (lane_id() == 0 && acc_f) atomicAdd(&s_cnt[0], acc_f);
-  __syncthreads();
-  if (threadIdx.x == 0) atomicAdd(&ws.ctile_cnt[blockIdx.x], s_cnt[0]);  // zeroed by k_rows_scan; peers subtract
-  else if (threadIdx.x < NC) ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x] = s_cnt[threadIdx.x];
-  if (!last_block(ws.tickets + 1)) return;
-  spine_scan<GS_NC_MAX>(ws.ctile_cnt, ws.ctiles_max, (int)gridDim.x, NC, s_tot, s_w);
-  if (threadIdx.x == 0) {
-    bool ok = true;
-    const uint32_t fnext = s_tot[0];
-    if (layer + 1 < ws.L && fnext > (uint32_t)ws.Fcap) ok = false;
-    int64_t used = h->slab_used, fused = h->reserved[1];
-    gs_span fs = slab_alloc(fused, ws.fslab_cap, fnext, ok);
-    int64_t edges = 0;
-    for (int q = 0; q < P && ok; q++) {
-      h->field[layer][q][GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, s_tot[1 + q], ok);
-      h->field[layer][q][GS_F_CSR_INDICES] = slab_alloc(used, ws.slab_cap, s_tot[1 + P + q], ok);
-      ws.rowscan[rs_at(ws, q, F)] = s_tot[1 + P + q];
-      edges += s_tot[1 + P + q];
-    }
-    if (ok) {
-      h->slab_used = used;
-      h->reserved[1] = (int32_t)fused;
-      h->frontier[layer + 1] = fs;
-      h->frontier_len[layer + 1] = (int32_t)fnext;
-      h->edges += edges;
-    } else if (h->status == 0) {
-      h->status = (int32_t)GS_ERR_OVERFLOW;
-    }
-  }
-}
-
-// ------------------------------------------------------------- k_cand_apply
-// Second pass over the candidate stream: turn the class flags into ranks
-// (tile prefix from the spine + in-tile ballot ranks, all in position order)
-// and scatter:  next frontier, in_nodes_g, the edge sources of part g in CSR
-// order (ids for now; k_relabel turns them into in_nodes positions), and for
-// every row's self entry the number of part-g edges emitted before the row
-// (rowscan), which is both the CSR row pointer and the row's edge count.
-// First-occurrence winners record the node's rank in in_nodes_g at their own
-// position (irank) -- the relabel map (DuplicateRemover::mask, duplicate.cpp:21)
-// indexed by position of first occurrence instead of by node, so that it is a
-// C-sized, L2-resident array and this kernel never touches the N-sized table.
-__global__ void GS_BOUNDS k_cand_apply(GsWs ws, int layer) {
-  gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
-  // The kernels of this pipeline are bound by instruction issue, not by memory:
-  // per-part ranks come from two packed warp scans (one byte per part) instead
-  // of 2P ballot/popc pairs per round.
-  __shared__ uint32_t s_wc[GS_NW][GS_NC_MAX];  // per-warp class totals of the tile
-  __shared__ uint32_t s_base[GS_NW][GS_NC_MAX];  // CTA prefix + earlier tiles + earlier warps of the tile
-  __shared__ uint32_t s_run[2][GS_NC_MAX];       // running class counts at the start of a tile (ping-pong)
-  __shared__ int32_t s_in_off[GS_MAX_PARTS], s_ix_off[GS_MAX_PARTS];
-  const int P = ws.P, NC = 2 * P + 1;
-  const uint32_t C = (uint32_t)h->cand_len[layer];
-  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
-  int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
-  const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
-  if (threadIdx.x < P) {
-    s_in_off[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
-    s_ix_off[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
-  }
-  const int lane = lane_id(), w = warp_id();
-  const uint32_t ltm = lt_mask();
-  // A warp owns GS_IPT*32 consecutive positions of the tile (GS_IPT rounds of
-  // 32), so in-warp order is position order and one cross-warp prefix per tile
-  // is enough.
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
-  if (threadIdx.x < NC) s_run[t0 & 1][threadIdx.x] = ws.ctile_cnt[(size_t)threadIdx.x * ws.ctiles_max + blockIdx.x];
-  for (int t = t0; t < t1; t++) {
-    __syncthreads();
-    // A lane owns GS_IPT consecutive positions, a warp 32 * GS_IPT: in-warp order
-    // is position order, ONE packed scan per warp and tile gives every lane the
-    // per-part counts before its first position; it then ranks its own items.
-    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
-    const bool full = p0 + GS_IPT <= C;
-    uint32_t f[GS_IPT];
-    int32_t ci[GS_IPT], cv[GS_IPT];
-    if (full) {
-      const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
-      const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
-      ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
-      f[0] = f4.x; f[1] = f4.y; f[2] = f4.z; f[3] = f4.w;
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++) {
-        f[k] = GS_CF_LOOP;  // dead position: neither edge nor first
-        ci[k] = 0;
-        if (p0 + k < C) {
-          f[k] = ws.cflag[p0 + k];
-          ci[k] = ws.cand[p0 + k];
-        }
-      }
-    }
-    unsigned long long pi = 0ull, pe = 0ull;
+    // classes; bit 8: in_nodes first, bit 9: frontier first, bit 10: self entry whose node is never an edge source
+    unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
     uint32_t nf = 0u;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      // an edge candidate's claim on the frontier slot may have been revoked by
-      // the node's earlier self entry (k_cand_flags); leave kill[] zeroed
-      if ((f[k] & (GS_CF_FFIRST | GS_CF_SELF)) == GS_CF_FFIRST && ws.kill[p0 + k]) {
-        f[k] &= ~GS_CF_FFIRST;
-        ws.kill[p0 + k] = 0;
+      const uint32_t p = p0 + k, kind = fl[k] & GS_CK_MASK;
+      const int g = (int)(fl[k] >> GS_CF_PART_SHIFT);
+      if (kind == GS_CK_SELF) {
+        const uint32_t has = y[k], own = 1u << g;
+        if (x[k] > p) { fl[k] |= 0x200u; nf++; }
+        if (x[k] == GS_INF) fl[k] |= 0x400u;
+        po += pk_spread(has);
+        if (has & own) pw += pk_one(g);
+        if (has & ~own) pt += pk_one(g);
+      } else if (kind != GS_CK_DEAD) {
+        pe += pk_one(g);
+        if (x[k] == p) {
+          fl[k] |= 0x100u;
+          pi += pk_one(g);
+          if (kind == GS_CK_EDGE || p < y[k]) { fl[k] |= 0x200u; nf++; }
+        }
       }
-      cv[k] = (f[k] & GS_CF_SELF) ? front[ci[k]] : ci[k];
-      const int g = (int)(f[k] >> GS_CF_PART_SHIFT);
-      if (!(f[k] & (GS_CF_SELF | GS_CF_LOOP))) pe += pk_one(g);
-      if (f[k] & GS_CF_IFIRST) pi += pk_one(g);
-      nf += (f[k] & GS_CF_FFIRST) ? 1u : 0u;
     }
-    // exclusive packed prefixes over the warp's lanes; lane 31 publishes the totals
-    const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe);
+    // exclusive packed prefixes over the warp's lanes; lane 31 holds the totals
+    const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe), inc_o = pk_warp_incl(po),
+                             inc_w = pk_warp_incl(pw), inc_t = pk_warp_incl(pt);
     const uint32_t inc_f = warp_incl_scan(nf);
-    {  // lane = class: unpack this warp's totals (held by lane 31) once, one word per class
-      const unsigned long long tot_i = __shfl_sync(FULL, inc_i, 31), tot_e = __shfl_sync(FULL, inc_e, 31);
-      const uint32_t tot_f = __shfl_sync(FULL, inc_f, 31);
-      if (lane < NC)
-        s_wc[w][lane] = lane == 0 ? tot_f : (lane <= P ? pk_get(tot_i, lane - 1) : pk_get(tot_e, lane - 1 - P));
+    {
+      const unsigned long long t_i = __shfl_sync(FULL, inc_i, 31), t_e = __shfl_sync(FULL, inc_e, 31),
+                               t_o = __shfl_sync(FULL, inc_o, 31), t_w = __shfl_sync(FULL, inc_w, 31),
+                               t_t = __shfl_sync(FULL, inc_t, 31);
+      const uint32_t t_f = __shfl_sync(FULL, inc_f, 31);
+      if (lane < 8) {
+        s_wc[w][CS_IN(lane)] = pk_get(t_i, lane);
+        s_wc[w][CS_E(lane)] = pk_get(t_e, lane);
+        s_wc[w][CS_OUT(lane)] = pk_get(t_o, lane);
+        s_wc[w][CS_OWN(lane)] = pk_get(t_w, lane);
+        s_wc[w][CS_TO(lane)] = pk_get(t_t, lane);
+      }
+      if (lane == 8) s_wc[w][CS_NF] = t_f;
     }
     __syncthreads();
-    if (lane < NC) {  // this warp's base = running counts + earlier warps; warp 0 also advances the running counts
-      const int cc = lane;
-      uint32_t a = s_run[t & 1][cc];
-      if (w == 0) {
-        uint32_t all = 0u;
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);  // next tile of this CTA (read after the barrier below)
+    if (w == 0) {  // tile aggregate -> look-back -> tile prefix
+      uint32_t mine[2], excl[2];
 #pragma unroll
-        for (int k = 0; k < GS_NW; k++) all += s_wc[k][cc];
-        s_run[(t + 1) & 1][cc] = a + all;
-      } else {
-        for (int k = 0; k < w; k++) a += s_wc[k][cc];
+      for (int j = 0; j < 2; j++) {
+        const int c = lane + 32 * j;
+        uint32_t all = 0u;
+        if (c < CS_USED) {
+#pragma unroll
+          for (int k = 0; k < GS_NW; k++) all += s_wc[k][c];
+        }
+        mine[j] = all;
       }
-      s_base[w][cc] = a;
+      tile_lookback<uint32_t, 2, GS_CS_NC>(ws.cs_status, cs_agg, cs_inc, t, ep, mine, excl);
+      s_pre[lane] = excl[0];
+      s_pre[lane + 32] = excl[1];
+    } else if (w <= 2) {  // meanwhile: earlier warps of the tile
+      const int c = (int)threadIdx.x - 32;
+      if (c < CS_USED) {
+        uint32_t run = 0u;
+#pragma unroll
+        for (int k = 0; k < GS_NW; k++) {
+          s_base[k][c] = run;
+          run += s_wc[k][c];
+        }
+      }
     }
-    __syncwarp();
-    uint32_t rf = s_base[w][0] + inc_f - nf;
-    unsigned long long ri = inc_i - pi, re = inc_e - pe;  // packed counts of this warp before the lane's item
-    uint32_t myrank[GS_IPT];
+    __syncthreads();
+#define CS_B(c) (s_pre[c] + s_base[w][c])
+    uint32_t rf = CS_B(CS_NF) + inc_f - nf;
+    unsigned long long ri = inc_i - pi, re = inc_e - pe, ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
+    bool wrote = false;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      const int g = (int)(f[k] >> GS_CF_PART_SHIFT);
-      myrank[k] = 0u;
-      if (f[k] & GS_CF_FFIRST) fnext[rf++] = cv[k];
-      if (f[k] & GS_CF_SELF) {
-        uint32_t *rsp = ws.rowscan + ci[k];
-        for (int q = 0; q < P; q++, rsp += (size_t)ws.Fcap + 1) *rsp = s_base[w][1 + P + q] + pk_get(re, q);
-      } else if (!(f[k] & GS_CF_LOOP)) {
-        const uint32_t ex = s_base[w][1 + P + g] + pk_get(re, g);
-        // An edge whose source occurs here for the first time knows its own
-        // rank: it writes the final csr_indices value and records the rank at
-        // its position (irank).  Every other edge carries the position m of
-        // that first occurrence and leaves ~m (negative) for k_relabel.
-        int32_t ixv = ~cv[k];
-        if (f[k] & GS_CF_IFIRST) {
-          const uint32_t rk = s_base[w][1 + g] + pk_get(ri, g);
-          ws.slab[s_in_off[g] + rk] = cv[k];
-          myrank[k] = rk;
-          ixv = (int32_t)rk;
-          ri += pk_one(g);
+      const uint32_t kind = fl[k] & GS_CK_MASK;
+      const int g = (int)((fl[k] >> GS_CF_PART_SHIFT) & 7u);
+      if (kind == GS_CK_SELF) {
+        const int32_t nd = z[k];
+        const uint32_t has = y[k], own = 1u << g;
+        if (fl[k] & 0x200u) fnext[rf++] = nd;
+        int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+        for (uint32_t hb = has; hb; hb &= hb - 1u) {
+          const int q = __ffs((int)hb) - 1;
+          const uint32_t op = CS_B(CS_OUT(q)) + pk_get(ro, q);
+          const uint32_t ow = CS_B(CS_OWN(q)) + pk_get(rw, q);
+          ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd;
+          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)(CS_B(CS_E(q)) + pk_get(re, q));
+          if (q == g) {
+            ws.slab[s_fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+            op_own = (int32_t)op;
+          } else {
+            ws.slab[s_fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+          }
         }
-        ws.slab[s_ix_off[g] + ex] = ixv;
+        if (has & ~own) {
+          ws.slab[s_fo[g][GS_F_TO_IDS] + CS_B(CS_TO(g)) + pk_get(rt, g)] = op_own;
+          rt += pk_one(g);
+        }
+        const uint32_t sr = ws.selfrank[ci[k]];
+        ws.slab[s_fo[g][GS_F_SELF_OUT] + sr] = op_own;
+        if (fl[k] & 0x400u) ws.slab[s_fo[g][GS_F_SELF_IN] + sr] = -1;  // else: written by the node's first edge
+        ro += pk_spread(has);
+        if (has & own) rw += pk_one(g);
+      } else if (kind != GS_CK_DEAD) {
+        const uint32_t ex = CS_B(CS_E(g)) + pk_get(re, g);
+        if (fl[k] & 0x100u) {
+          // the first edge occurrence of a source knows its rank: final csr_indices
+          // value, in_nodes entry, relabel map entry; every other edge leaves ~m
+          // (m = position of that first occurrence) for relabel_role
+          const uint32_t rk = CS_B(CS_IN(g)) + pk_get(ri, g);
+          ws.slab[s_fo[g][GS_F_IN_NODES] + rk] = z[k];
+          ws.slab[s_fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)rk;
+          if (kind == GS_CK_FHIT) ws.slab[s_fo[g][GS_F_SELF_IN] + ws.selfrank[ci[k]]] = (int32_t)rk;
+          if (fl[k] & 0x200u) fnext[rf++] = z[k];
+          ci[k] = (int32_t)rk;
+          wrote = true;
+          ri += pk_one(g);
+        } else {
+          ws.slab[s_fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)~x[k];
+        }
         re += pk_one(g);
       }
     }
-    if (full) {
-      *reinterpret_cast<uint4 *>(ws.irank + p0) = make_uint4(myrank[0], myrank[1], myrank[2], myrank[3]);
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++)
-        if (p0 + k < C) ws.irank[p0 + k] = myrank[k];
-    }
-  }
-}
-
-// ------------------------------------------------------------ k_front_count
-// Row-side classes.  Row i (node nd, owner g0) with has_g = "emitted >= 1 edge
-// into part g":  out_g = has_g (bipartite.h:59-62); owned_g = has_g && g == g0
-// (bipartite.h:56-58); to_g0 = any has_h, h != g0 (slicer.cpp:41);
-// self_g0 = always (slicer.cpp:33-34).  from_g = out_g && g != g0 needs no
-// counter: its rank is rank(out_g) - rank(owned_g).
-// bit q of a mask -> byte q of a packed counter word
-// (multiply replicates the mask byte into all eight bytes, the AND keeps bit q in
-// byte q, + 0x7F carries any kept bit into bit 7 of its byte)
-__device__ __forceinline__ unsigned long long pk_spread(uint32_t mask, int /*P*/) {
-  const unsigned long long v = ((unsigned long long)(mask & 0xFFu) * 0x0101010101010101ull) & 0x8040201008040201ull;
-  return ((v + 0x7F7F7F7F7F7F7F7Full) >> 7) & 0x0101010101010101ull;
-}
-
-__global__ void GS_BOUNDS k_front_count(GsWs ws, int layer) {
-  gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
-  __shared__ uint32_t s_cnt[GS_NF_MAX];
-  __shared__ uint32_t s_tot[GS_NF_MAX];
-  __shared__ uint32_t s_w[GS_NW + 1];
-  const int P = ws.P, NF = 4 * P;
-  const int F = h->frontier_len[layer];
-  const int32_t *front = ws.fslab + h->frontier[layer].off;
-  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  if (threadIdx.x < GS_NF_MAX) s_cnt[threadIdx.x] = 0u;
-  __syncthreads();
-  uint32_t acc_out = 0u, acc_own = 0u, acc_to = 0u, acc_self = 0u;  // lane q < P: this warp's counts of part q
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
-  for (int t = t0; t < t1; t++) {
-    // a thread owns GS_IPT consecutive rows: per part, GS_IPT + 1 consecutive
-    // rowscan values give the rows' edge counts; classes are counted in packed
-    // words (one byte per part) and reduced once per warp and tile
-    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
-    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u};
-    if (i0 < F) {
-      const int nk = min(GS_IPT, F - i0);
-      for (int q = 0; q < P; q++) {
-        const uint32_t *rs = ws.rowscan + rs_at(ws, q, i0);
-        uint32_t prev = rs[0];
+#undef CS_B
+    if (wrote) {
+      if (full) {
+        *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      } else {
 #pragma unroll
         for (int k = 0; k < GS_IPT; k++)
-          if (k < nk) {
-            const uint32_t nx = rs[k + 1];
-            if (nx != prev) has[k] |= 1u << q;
-            prev = nx;
-          }
-      }
-    }
-    unsigned long long p_out = 0ull, p_own = 0ull, p_to = 0ull, p_self = 0ull;
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++)
-      if (i0 + k < F) {
-        const int g0 = owner_of(ws, front[i0 + k]);
-        p_out += pk_spread(has[k], P);
-        p_self += pk_one(g0);
-        if ((has[k] >> g0) & 1u) p_own += pk_one(g0);
-        if (has[k] & ~(1u << g0)) p_to += pk_one(g0);
-      }
-    if (i0 + GS_IPT <= F) {
-      *reinterpret_cast<uchar4 *>(ws.rowhas + i0) =
-          make_uchar4((unsigned char)has[0], (unsigned char)has[1], (unsigned char)has[2], (unsigned char)has[3]);
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++)
-        if (i0 + k < F) ws.rowhas[i0 + k] = (uint8_t)has[k];
-    }
-    p_out = pk_warp_sum(p_out);
-    p_own = pk_warp_sum(p_own);
-    p_to = pk_warp_sum(p_to);
-    p_self = pk_warp_sum(p_self);
-    // every lane holds the warp totals: lane q keeps the running counts of part q
-    const int lq = lane_id() & 7;
-    acc_out += pk_get(p_out, lq);
-    acc_own += pk_get(p_own, lq);
-    acc_to += pk_get(p_to, lq);
-    acc_self += pk_get(p_self, lq);
-  }
-  if (lane_id() < P) {
-    const int q = lane_id();
-    if (acc_out) atomicAdd(&s_cnt[q], acc_out);
-    if (acc_own) atomicAdd(&s_cnt[P + q], acc_own);
-    if (acc_to) atomicAdd(&s_cnt[2 * P + q], acc_to);
-    if (acc_self) atomicAdd(&s_cnt[3 * P + q], acc_self);
-  }
-  __syncthreads();
-  if (threadIdx.x < NF) ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x] = s_cnt[threadIdx.x];
-  if (!last_block(ws.tickets + 2)) return;
-  spine_scan<GS_NF_MAX>(ws.ftile_cnt, ws.ftiles_max, (int)gridDim.x, NF, s_tot, s_w);
-  if (threadIdx.x == 0) {
-    bool ok = true;
-    int64_t used = h->slab_used;
-    for (int q = 0; q < P && ok; q++) {
-      const uint32_t n_out = s_tot[q], n_own = s_tot[P + q], n_to = s_tot[2 * P + q],
-                     n_self = s_tot[3 * P + q];
-      gs_span *fl = h->field[layer][q];
-      const gs_span ip = slab_alloc(used, ws.slab_cap, n_out + 1u, ok);
-      fl[GS_F_OUT_NODES] = slab_alloc(used, ws.slab_cap, n_out, ok);
-      fl[GS_F_CSR_INDPTR] = ip;
-      fl[GS_F_OWNED_OUT] = slab_alloc(used, ws.slab_cap, n_own, ok);
-      fl[GS_F_FROM_IDS] = slab_alloc(used, ws.slab_cap, n_out - n_own, ok);
-      fl[GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, n_to, ok);
-      fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, n_self, ok);
-      fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, n_self, ok);
-      // row pointer sentinel = E_g (left in rowscan[F] by k_cand_flags' spine)
-      if (ok) ws.slab[ip.off + n_out] = (int32_t)ws.rowscan[rs_at(ws, q, F)];
-    }
-    if (ok) h->slab_used = used;
-    else h->status = (int32_t)GS_ERR_OVERFLOW;
-  }
-}
-
-// ------------------------------------------------------------ k_front_apply
-__global__ void GS_BOUNDS k_front_apply(GsWs ws, int layer) {
-  gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
-  __shared__ uint32_t s_wc[GS_NW][GS_NF_MAX];  // per-warp class totals of the tile (kind * P + part)
-  __shared__ uint32_t s_base[GS_NW][GS_NF_MAX];
-  __shared__ uint32_t s_run[2][GS_NF_MAX];
-  __shared__ int32_t s_off[GS_MAX_PARTS][GS_NUM_FIELDS];
-  const int P = ws.P, NF = 4 * P;
-  const int F = h->frontier_len[layer];
-  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
-  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  if (threadIdx.x < P * GS_NUM_FIELDS)
-    s_off[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
-        h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
-  const int lane = lane_id(), w = warp_id();
-  int t0, t1;
-  cta_tiles(ntiles, t0, t1);
-  if (threadIdx.x < NF) s_run[t0 & 1][threadIdx.x] = ws.ftile_cnt[(size_t)threadIdx.x * ws.ftiles_max + blockIdx.x];
-  for (int t = t0; t < t1; t++) {
-    __syncthreads();
-    // a lane owns GS_IPT consecutive rows (row order = list order); four packed
-    // scans per warp and tile give it the per-part ranks before its first row
-    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
-    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u};
-    int g0[GS_IPT];
-    int32_t nd[GS_IPT] = {0, 0, 0, 0};
-    if (i0 + GS_IPT <= F) {
-      const uchar4 h4 = *reinterpret_cast<const uchar4 *>(ws.rowhas + i0);
-      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
-      has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
-      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++)
-        if (i0 + k < F) {
-          has[k] = ws.rowhas[i0 + k];
-          nd[k] = front[i0 + k];
-        }
-    }
-    unsigned long long p_out = 0ull, p_own = 0ull, p_to = 0ull, p_self = 0ull;
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      g0[k] = -1;
-      if (i0 + k < F) {
-        g0[k] = owner_of(ws, nd[k]);
-        p_out += pk_spread(has[k], P);
-        p_self += pk_one(g0[k]);
-        if ((has[k] >> g0[k]) & 1u) p_own += pk_one(g0[k]);
-        if (has[k] & ~(1u << g0[k])) p_to += pk_one(g0[k]);
-      }
-    }
-    const unsigned long long i_out = pk_warp_incl(p_out), i_own = pk_warp_incl(p_own),
-                             i_to = pk_warp_incl(p_to), i_self = pk_warp_incl(p_self);
-    {  // lanes 0..7 unpack the part counts of the four kinds from lane 31's totals: one word per class
-      const unsigned long long t_out = __shfl_sync(FULL, i_out, 31), t_own = __shfl_sync(FULL, i_own, 31),
-                               t_to = __shfl_sync(FULL, i_to, 31), t_self = __shfl_sync(FULL, i_self, 31);
-      if (lane < P) {
-        s_wc[w][lane] = pk_get(t_out, lane);
-        s_wc[w][P + lane] = pk_get(t_own, lane);
-        s_wc[w][2 * P + lane] = pk_get(t_to, lane);
-        s_wc[w][3 * P + lane] = pk_get(t_self, lane);
+          if (p0 + k < C && (fl[k] & 0x100u)) ws.cand[p0 + k] = ci[k];
       }
     }
     __syncthreads();
-    if (lane < NF) {  // lane = class (kind * P + part): this warp's base, warp 0 also the next tile's start
-      uint32_t a = s_run[t & 1][lane];
-      if (w == 0) {
-        uint32_t all = 0u;
-#pragma unroll
-        for (int k = 0; k < GS_NW; k++) all += s_wc[k][lane];
-        s_run[(t + 1) & 1][lane] = a + all;
-      } else {
-        for (int k = 0; k < w; k++) a += s_wc[k][lane];
-      }
-      s_base[w][lane] = a;
-    }
-    __syncwarp();
-    unsigned long long r_out = i_out - p_out, r_own = i_own - p_own, r_to = i_to - p_to, r_self = i_self - p_self;
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      const int i = i0 + k;
-      if (i >= F) break;
-      const int gq = g0[k];
-      int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
-      for (int q = 0; q < P; q++)
-        if ((has[k] >> q) & 1u) {
-          const uint32_t op = s_base[w][q] + pk_get(r_out, q);
-          const uint32_t ow = s_base[w][P + q] + pk_get(r_own, q);
-          ws.slab[s_off[q][GS_F_OUT_NODES] + op] = nd[k];
-          ws.slab[s_off[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[rs_at(ws, q, i)];
-          if (q == gq) {
-            ws.slab[s_off[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
-            op_own = (int32_t)op;
-          } else {
-            ws.slab[s_off[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
-          }
-        }
-      if (has[k] & ~(1u << gq)) {
-        ws.slab[s_off[gq][GS_F_TO_IDS] + s_base[w][2 * P + gq] + pk_get(r_to, gq)] = op_own;
-        r_to += pk_one(gq);
-      }
-      const uint32_t p_self_rank = s_base[w][3 * P + gq] + pk_get(r_self, gq);
-      const uint32_t a = ws.rowa[i];  // position of the node's first edge occurrence, or INF: never an edge source
-      ws.slab[s_off[gq][GS_F_SELF_IN] + p_self_rank] = a == GS_INF ? -1 : (int32_t)__ldcg(ws.irank + a);
-      ws.slab[s_off[gq][GS_F_SELF_OUT] + p_self_rank] = op_own;
-      r_out += pk_spread(has[k], P);
-      r_self += pk_one(gq);
-      if ((has[k] >> gq) & 1u) r_own += pk_one(gq);
-    }
+    t = s_tile;
   }
 }
 
-// ---------------------------------------------------------------- k_relabel
-// csr_indices: edge-source ids -> positions in in_nodes_g through the table
-// (DuplicateRemover::replace, duplicate.cpp:35-39 -- what bipartite.cpp:5
-// would do if `indices` were ever filled).
-__global__ void GS_BOUNDS k_relabel(GsWs ws, int layer) {
-  gs_sample_header *h = ws.hdr;
+// ---------------------------------------------------------------- relabel
+// csr_indices: an edge that was not the first occurrence of its source holds ~m,
+// m the position of the first one; cand[m] is that source's rank in in_nodes_g
+// (DuplicateRemover::replace, duplicate.cpp:35-39 -- what bipartite.cpp:5 would do
+// if `indices` were ever filled).  Runs in the launch after k_cand, next to the
+// next layer's k_rows (or in k_tail).  bx / nb: this role's CTA index and count.
+__device__ void relabel_role(const GsWs &ws, int layer, int bx, int nb) {
+  const gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   const int P = ws.P;
   for (int q = 0; q < P; q++) {
     const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
     int32_t *ix = ws.slab + sp.off;
-    const int stride = gridDim.x * GS_TPB;
-    for (int e0 = blockIdx.x * GS_TPB + threadIdx.x; e0 < sp.len; e0 += GS_IPT * stride) {
-      int32_t v[GS_IPT];
-      uint32_t r[GS_IPT];
+    const int stride = nb * GS_TPB;
+    for (int e0 = bx * GS_TPB + threadIdx.x; e0 < sp.len; e0 += GS_IPT * stride) {
+      int32_t v[GS_IPT], r[GS_IPT];
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
         v[k] = e < sp.len ? ix[e] : 0;  // >= 0: already final (written by the first occurrence)
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(ws.irank + (uint32_t)~v[k]) : 0u;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(ws.cand + (uint32_t)~v[k]) : 0;
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        if (v[k] < 0) ix[e] = (int32_t)r[k];
+        if (v[k] < 0) ix[e] = r[k];
       }
     }
-  }
-}
-
-// ----------------------------------------------------------------- k_finish
-// Reset of the table (DuplicateRemover::clear, duplicate.cpp:28-33: only touched
-// entries -- every node touched in any layer is in the last frontier; dense
-// fill instead when the touched set covers most of the table's sectors),
-// then the sample header and, when asked, the used part of the slab are
-// mirrored to pinned host memory with 16-byte stores.
-__global__ void GS_BOUNDS k_finish(GsWs ws) {
-  gs_sample_header *h = ws.hdr;
-  const Tbl tbl(ws);
-  const int tid = blockIdx.x * GS_TPB + threadIdx.x, nth = gridDim.x * GS_TPB;
-  if (h->status == 0 && ws.tag_shift) {
-    // tagged table: nothing to reset, unless the NEXT sample would run out of tags
-    // (k_begin applies the same test and restarts the tag sequence)
-    if (__ldcg(ws.epoch) + (uint32_t)ws.L + 1u > (1u << (32 - ws.tag_shift))) {
-      uint4 *t4 = (uint4 *)ws.table;
-      const int64_t n4 = (int64_t)ws.num_nodes >> 2;
-      const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
-      for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
-      if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
-    }
-  } else if (h->status == 0) {
-    const int L = ws.L;
-    const int32_t *fl = ws.fslab + h->frontier[L].off;
-    const int FL = h->frontier_len[L];
-    if ((int64_t)FL * 8 > (int64_t)ws.num_nodes) {
-      // most 32-byte sectors of the table hold a touched entry: a streaming
-      // fill of the whole table moves fewer sectors than FL scattered stores
-      uint4 *t4 = (uint4 *)ws.table;
-      const int64_t n4 = (int64_t)ws.num_nodes >> 2;
-      const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
-      for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
-      if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
-    } else {
-      for (int i = tid; i < FL; i += nth) tbl.st(fl[i], GS_INF);
-    }
-  }
-  {
-    const int nw = (int)(sizeof(gs_sample_header) / 4);
-    const int32_t *src = (const int32_t *)h;
-    int32_t *dst = (int32_t *)ws.hdr_host;
-    for (int i = tid; i < nw; i += nth) dst[i] = src[i];
-  }
-  if (h->reserved[0] && ws.slab_host && h->status == 0) {
-    const int64_t n4 = h->slab_used >> 2;  // spans are 4-element aligned
-    const int4 *src = (const int4 *)ws.slab;
-    int4 *dst = (int4 *)ws.slab_host;
-    for (int64_t i = tid; i < n4; i += nth) dst[i] = src[i];
   }
 }
 
@@ -1053,16 +974,15 @@ __global__ void GS_BOUNDS k_finish(GsWs ws) {
 // One warp per row: out[r, :] = rows[id / div, :].  602 fp32 = 2408 B rows are
 // 8-byte but not 16-byte multiples, so the vector width is chosen from dim
 // (float4 / float2 / float); rows are contiguous, so unlike the id work above this
-// kernel streams whole lines and is bounded by plain HBM bandwidth.
-// Fused into every sample's graph: the rows of the last layer's in_nodes_g, part
-// after part -- the block of input features GPU g reads for this minibatch
+// streams whole lines and is bounded by plain HBM bandwidth.  Fused into every
+// sample's last launch: the rows of the last layer's in_nodes_g, part after part
+// -- the block of input features GPU g reads for this minibatch
 // (python/data/bipartite.py:61-67 gather, memory_manager.py:75-104 refresh).
 // With a cached store (FeatSrc) rows outside the HBM cache are read in place from
 // host memory by the same warp, so there is no per-batch refresh step and no
 // global_to_local table to patch and undo (memory_manager.py:77-104).
-__global__ void GS_BOUNDS k_gather_sample(GsWs ws) {
-  gs_sample_header *h = ws.hdr;
-  if (h->status != 0) return;
+__device__ void gather_role(const GsWs &ws, int bx, int nb) {
+  const gs_sample_header *h = ws.hdr;
   __shared__ int32_t s_off[GS_MAX_PARTS], s_start[GS_MAX_PARTS + 1];
   const int P = ws.P, l = ws.L - 1;
   if (threadIdx.x == 0) {
@@ -1073,16 +993,10 @@ __global__ void GS_BOUNDS k_gather_sample(GsWs ws) {
       acc += h->field[l][q][GS_F_IN_NODES].len;
     }
     s_start[P] = acc;
-    if (blockIdx.x == 0) {
-      const bool fits = (int64_t)acc <= ws.feat_cap_rows;
-      h->feature_rows = fits ? acc : 0;
-      for (int q = 0; q <= P; q++) h->feature_part_off[q] = q <= P ? s_start[q] : 0;
-      if (!fits) h->late_status = (int32_t)GS_ERR_OVERFLOW;  // folded into status by k_finish
-    }
   }
   __syncthreads();
   const int R = s_start[P];
-  if ((int64_t)R > ws.feat_cap_rows) return;
+  if ((int64_t)R > ws.feat_cap_rows) return;  // k_tail's last CTA reports the overflow
   const FeatSrc fs{ws.feat, ws.feat_slot, ws.feat_host};
   const int dim = ws.feat_dim, div = ws.feat_div;
   const int32_t *slab = ws.slab;
@@ -1092,8 +1006,92 @@ __global__ void GS_BOUNDS k_gather_sample(GsWs ws) {
     const int32_t id = slab[s_off[q] + ((int)r - s_start[q])];
     return fs.row((int64_t)(id / div), dim);
   };
-  gather_block(dim, (int64_t)R, ws.feat_out, src_of_row, (int64_t)blockIdx.x * GS_NW + warp_id(),
-               (int64_t)gridDim.x * GS_NW, lane_id());
+  gather_block(dim, (int64_t)R, ws.feat_out, src_of_row, (int64_t)bx * GS_NW + warp_id(), (int64_t)nb * GS_NW,
+               lane_id());
+}
+
+// ------------------------------------------------------------------ kernels
+template <bool FIRST>
+__global__ void GS_BOUNDS k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows) {
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  if ((int)blockIdx.x < grid_rows) rows_role<FIRST>(ws, layer);
+  else if (!FIRST) relabel_role(ws, layer - 1, (int)blockIdx.x - grid_rows, (int)gridDim.x - grid_rows);
+}
+
+template <int RNG>
+__global__ void GS_BOUNDS k_expand(const GsWs *__restrict__ wsv, int layer) {
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  expand_role<RNG>(ws, layer);
+}
+
+__global__ void GS_BOUNDS k_cand(const GsWs *__restrict__ wsv, int layer) {
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  cand_role(ws, layer);
+}
+
+// Last launch of a sample: relabel of the last layer, the fused feature gather,
+// and the slot's housekeeping -- every CTA takes its share of the rare dense
+// refills (dedup table out of tags: 1 sample in 2^(31-S) - 1; scan descriptors:
+// once per 2^30 scans), the last CTA to finish closes the header, mirrors it to
+// pinned host memory and prepares the slot's state for the next sample.
+__global__ void GS_BOUNDS k_tail(const GsWs *__restrict__ wsv, int grid_relabel, int grid_gather) {
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  gs_sample_header *h = ws.hdr;
+  const int st = h->status;
+  if (st == GS_SKIPPED) return;
+  const int L = ws.L, P = ws.P;
+  const int bx = (int)blockIdx.x;
+  if (st == 0) {
+    if (bx < grid_relabel) relabel_role(ws, L - 1, bx, grid_relabel);
+    else if (ws.feat && bx < grid_relabel + grid_gather) gather_role(ws, bx - grid_relabel, grid_gather);
+  }
+  const GsState stt = *ws.state;
+  const uint32_t ntags = 1u << (31 - ws.pos_bits);
+  const bool refill = stt.tag_idx + 1u > ntags - 1u;  // the next sample would have no tag left
+  const bool rescan = stt.scan_epoch + 4u * (uint32_t)L >= (1u << 30);
+  const int64_t tid = (int64_t)bx * GS_TPB + threadIdx.x, nth = (int64_t)gridDim.x * GS_TPB;
+  if (refill) {
+    uint4 *t4 = (uint4 *)ws.table;
+    const int64_t n4 = (int64_t)ws.num_nodes >> 2;
+    const uint4 inf = make_uint4(GS_INF, GS_INF, GS_INF, GS_INF);
+    for (int64_t i = tid; i < n4; i += nth) t4[i] = inf;
+    if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
+  }
+  if (rescan) {
+    for (int64_t i = tid; i < ws.ftiles_cap; i += nth) ws.rs_status[i] = 0u;
+    for (int64_t i = tid; i < ws.ctiles_cap; i += nth) ws.cs_status[i] = 0u;
+  }
+  if (!last_block(ws.tickets + L * GS_TICKETS)) return;
+  for (int i = threadIdx.x; i < L * GS_CNT_STRIDE; i += GS_TPB) ws.cnt[i] = 0u;
+  for (int i = threadIdx.x; i < L * GS_TICKETS; i += GS_TPB) ws.tickets[i] = 0u;
+  if (threadIdx.x == 0) {
+    if (ws.feat && st == 0) {
+      int32_t acc = 0;
+      for (int q = 0; q <= P; q++) {
+        h->feature_part_off[q] = acc;
+        if (q < P) acc += h->field[L - 1][q][GS_F_IN_NODES].len;
+      }
+      const bool fits = (int64_t)acc <= ws.feat_cap_rows;
+      h->feature_rows = fits ? acc : 0;
+      if (!fits) h->late_status = (int32_t)GS_ERR_OVERFLOW;
+    }
+    GsState nx;
+    nx.tag_idx = refill ? 1u : stt.tag_idx + 1u;
+    nx.scan_epoch = rescan ? 1u : stt.scan_epoch + 2u * (uint32_t)L;
+    nx.pad[0] = nx.pad[1] = 0u;
+    *ws.state = nx;
+  }
+  __syncthreads();
+  {
+    const int nw = (int)(sizeof(gs_sample_header) / 4);
+    const int32_t *src = (const int32_t *)h;
+    int32_t *dst = (int32_t *)ws.hdr_host;
+    for (int i = threadIdx.x; i < nw; i += GS_TPB) dst[i] = src[i];
+  }
 }
 
 __global__ void GS_BOUNDS k_gather_ids(FeatSrc fs, int dim, int div,
@@ -1224,41 +1222,70 @@ __global__ void k_narrow_ids(const int64_t *src, int32_t *dst, size_t n) {
     dst[i] = (int32_t)src[i];
 }
 
+// CSR validation (gs_graph_create): the kernels index table[] / indptr[] with the
+// ids they read from `indices`, so a bad file must be rejected here, not found as
+// silent corruption later.  err[0]: 1 + first index i with indptr[i] > indptr[i+1]
+// (or an end outside [0, M]); err[1]: 1 + first edge index with an id outside [0, N).
+__global__ void k_check_indptr(const int64_t *indptr, int64_t n, int64_t m, unsigned long long *err) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t a = indptr[i], b = indptr[i + 1];
+    if (a > b || a < 0 || b > m) atomicMin(err + 0, (unsigned long long)i + 1ull);
+  }
+}
+__global__ void k_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t num_nodes, unsigned long long *err) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int64_t v = ids[i];
+    if (v < 0 || v >= num_nodes) atomicMin(err + 1, (unsigned long long)(base + (int64_t)i) + 1ull);
+  }
+}
+
+// Random-sector yardstick (bench.py, roofline.random_access): every thread keeps
+// eight independent 4-byte reads in flight, each from a pseudo-random word of a
+// table of `elems` words -- one 32-byte DRAM sector per read once the table is
+// larger than L2.  This is the access pattern of the neighbour picks and of the
+// dedup-table reads; its rate is the ceiling the sector-granular bound is
+// divided by.
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull;
+  return x ^ (x >> 33);
+}
+__global__ void __launch_bounds__(256) k_sector_probe(const uint32_t *__restrict__ table, uint64_t elems, uint64_t n,
+                                                      uint32_t seed, uint32_t *sink) {
+  const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (uint64_t)gridDim.x * blockDim.x;
+  uint32_t acc = 0u;
+  for (uint64_t i = tid; i < n; i += nth * 8ull) {
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint64_t j = i + (uint64_t)k * nth;
+      const uint64_t idx = __umul64hi(mix64(j + ((uint64_t)seed << 32)), elems);
+      v[k] = j < n ? __ldg(table + idx) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) acc += v[k];
+  }
+  if (acc == 0x9E3779B9u) sink[0] = acc;  // keeps the loads alive; practically never taken
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- launchers
-void gs_launch_begin(const GsWs &ws, cudaStream_t st) { k_begin<<<1, 1024, 0, st>>>(ws); }
-void gs_launch_rows_count(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_rows_count<<<grid, GS_TPB, 0, st>>>(ws, layer);
+void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, int grid_relabel, cudaStream_t st) {
+  if (layer == 0) k_rows<true><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows);
+  else k_rows<false><<<dim3(grid_rows + grid_relabel, members), GS_TPB, 0, st>>>(wsv, layer, grid_rows);
 }
-void gs_launch_rows_scan(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_rows_scan<<<grid, GS_TPB, 0, st>>>(ws, layer);
+void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int grid, cudaStream_t st) {
+  const dim3 g(grid, members);
+  if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  else k_expand<(int)GS_RNG_PHILOX><<<g, GS_TPB, 0, st>>>(wsv, layer);
 }
-void gs_launch_expand(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  if (ws.rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS><<<grid, GS_TPB, 0, st>>>(ws, layer);
-  else if (ws.rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE><<<grid, GS_TPB, 0, st>>>(ws, layer);
-  else k_expand<(int)GS_RNG_PHILOX><<<grid, GS_TPB, 0, st>>>(ws, layer);
+void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st) {
+  k_cand<<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
 }
-void gs_launch_cand_flags(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_cand_flags<<<grid, GS_TPB, 0, st>>>(ws, layer);
-}
-void gs_launch_cand_apply(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_cand_apply<<<grid, GS_TPB, 0, st>>>(ws, layer);
-}
-void gs_launch_front_count(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_front_count<<<grid, GS_TPB, 0, st>>>(ws, layer);
-}
-void gs_launch_front_apply(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_front_apply<<<grid, GS_TPB, 0, st>>>(ws, layer);
-}
-void gs_launch_relabel(const GsWs &ws, int layer, int grid, cudaStream_t st) {
-  k_relabel<<<grid, GS_TPB, 0, st>>>(ws, layer);
-}
-void gs_launch_finish(const GsWs &ws, int grid, cudaStream_t st) {
-  k_finish<<<grid, GS_TPB, 0, st>>>(ws);
-}
-void gs_launch_gather_sample(const GsWs &ws, int grid, cudaStream_t st) {
-  k_gather_sample<<<grid, GS_TPB, 0, st>>>(ws);
+void gs_launch_tail(const GsWs *wsv, int members, int grid_relabel, int grid_gather, cudaStream_t st) {
+  k_tail<<<dim3(grid_relabel + grid_gather, members), GS_TPB, 0, st>>>(wsv, grid_relabel, grid_gather);
 }
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
@@ -1276,4 +1303,15 @@ void gs_launch_fill_u32(uint32_t *p, size_t n, uint32_t v, cudaStream_t st) {
 }
 void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream_t st) {
   k_narrow_ids<<<1184, 256, 0, st>>>(src, dst, n);
+}
+void gs_launch_check_indptr(const int64_t *indptr, int64_t n, int64_t m, unsigned long long *err, cudaStream_t st) {
+  k_check_indptr<<<1184, 256, 0, st>>>(indptr, n, m, err);
+}
+void gs_launch_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t num_nodes, unsigned long long *err,
+                         cudaStream_t st) {
+  k_check_ids<<<1184, 256, 0, st>>>(ids, n, base, num_nodes, err);
+}
+void gs_launch_sector_probe(const uint32_t *table, uint64_t elems, uint64_t n, uint32_t seed, uint32_t *sink,
+                            int grid, cudaStream_t st) {
+  k_sector_probe<<<grid, 256, 0, st>>>(table, elems, n, seed, sink);
 }

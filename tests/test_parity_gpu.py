@@ -186,6 +186,61 @@ def test_without_replacement_matches_oracle(fanouts, P, shape, batch):
         E.Slicer(E.Graph(ip, ix), fanouts, P, draws=np.zeros(4, np.uint32), replace=False)
 
 
+@pytest.mark.parametrize("group,slots,streams", [(2, 4, 2), (4, 4, 1), (3, 6, 2), (4, 8, 2)])
+def test_groups_of_minibatches_per_launch_match_oracle(group, slots, streams):
+    """gs_config.group_size: `group` consecutive slots share one launch sequence
+    (blockIdx.y = member).  Full groups replay the CUDA graph, a partly filled group
+    (a wait on a staged slot, flush) is launched eagerly with fewer members; ragged
+    and empty batches inside a group; slots are refilled as they are released."""
+    E = _engine()
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=21)
+    n = ip.size - 1
+    fan, P, batch = [15, 10, 5], 4, 384
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, fan, P, max_batch=batch, num_slots=slots, num_streams=streams, seed=5, group_size=group)
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=5)
+    rng = np.random.default_rng(8)
+    sizes = [batch, batch // 3, 0, batch, 1, batch, 77, batch, batch, 5, batch]
+    pending = []
+    for b, nb in enumerate(sizes):
+        seeds = rng.permutation(n)[:nb]
+        if len(pending) == slots:
+            slot, s_, bi = pending.pop(0)
+            v = sl.wait(slot)
+            _compare(v, orc.slice(s_, bi))
+            v.release()
+        pending.append((sl.submit(seeds, b), seeds, b))
+    sl.flush()
+    for slot, s_, bi in pending:  # the last group is partly filled: wait launches it
+        v = sl.wait(slot)
+        _compare(v, orc.slice(s_, bi))
+        v.release()
+    # a lone submit followed by wait: a group of one member out of `group`
+    seeds = rng.permutation(n)[:batch]
+    v = sl.slice(seeds, 99)
+    _compare(v, orc.slice(seeds, 99))
+    v.release()
+    sl.close(); g.close()
+
+
+def test_malformed_csr_is_rejected_at_create():
+    """gs_graph_create checks the CSR on the device before narrowing the ids: a
+    bad indices.bin must be an error, not an out-of-bounds atomic later."""
+    E = _engine()
+    from cslicer import _native as N
+    ip = np.array([0, 2, 3, 3], np.int64)
+    for bad_ix, what in (([1, 2, 3], b"indices[2]"), ([1, -1, 0], b"indices[1]"), ([1 << 32, 0, 1], b"indices[0]")):
+        with pytest.raises(N.SlicerError) as e:
+            E.Graph(ip, np.array(bad_ix, np.int64))
+        assert e.value.code == N.ERR_INVALID and what in str(e.value).encode()
+    with pytest.raises(N.SlicerError) as e:  # not monotone
+        E.Graph(np.array([0, 3, 2, 3], np.int64), np.array([1, 2, 0], np.int64))
+    assert e.value.code == N.ERR_INVALID and "indptr" in str(e.value)
+    g = E.Graph(ip, np.array([1, 2, 0], np.int64))  # the well-formed version still loads
+    g.close()
+
+
 def test_graph_and_eager_paths_agree_and_device_views_match_host():
     E = _engine()
     import torch
