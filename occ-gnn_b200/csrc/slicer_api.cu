@@ -419,6 +419,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   if (gsz > 16 || cfg->num_slots % gsz != 0)
     return fail(GS_ERR_INVALID, "group_size=%d must be in [1,16] and divide num_slots=%d", gsz, cfg->num_slots);
   CU(cudaSetDevice(g->device));
+  gs_kernels_prepare();
 
   gs_slicer *s = new (std::nothrow) gs_slicer();
   if (!s) return fail(GS_ERR_INVALID, "out of host memory");
@@ -659,7 +660,9 @@ int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_
       bool idle = true;
       for (int j = 0; j < cand.members; j++) {
         const int st = s->slots[cand.first + j].state;
-        if (st == SLOT_BUSY || st == SLOT_STAGED || (j == 0 && st != SLOT_FREE)) idle = false;
+        // a member that was launched but not waited on yet is complete as soon as slot 0 was
+        // released (one launch sequence serves the whole group); it is restaged only once free
+        if (st == SLOT_STAGED || (j == 0 && st != SLOT_FREE)) idle = false;
       }
       if (idle) pick = (s->next_group + t) % ng;
     }

@@ -34,7 +34,7 @@
 
 // decoupled look-back descriptors
 #define GS_RS_NC 16   // k_rows scan: candidates, drawing rows, rows per owner (uint64 each; 2 + P used)
-#define GS_CS_NC 64   // k_cand scan: 1 + 5 P counters (uint32; <= 41 used), padded to two lane rounds
+#define GS_CS_NC 48   // k_cand scan: 1 + 5 * 8 = 41 counters (uint32), padded
 #define GS_SKIPPED 1000  // header status of a group member that holds no minibatch
 
 // hand-over copy through the bulk-copy engine (cp.async.bulk); A/B with -DGS_PACK_TMA=0
@@ -134,6 +134,7 @@ struct GsRange {
 struct GsGrids {
   int rows, cand, relabel;  // CTAs of the three roles for one layer (static upper bounds)
 };
+void gs_kernels_prepare();  // once per device, before the first launch / graph capture
 void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, int grid_relabel, cudaStream_t st);
 void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int grid, cudaStream_t st);
 void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st);

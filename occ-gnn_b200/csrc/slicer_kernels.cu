@@ -31,15 +31,20 @@
 // work, HBM- and latency-bound: no tensor cores (nothing here is a contraction).
 #include "slicer_device.cuh"
 
-// Resident CTAs per SM the tiled kernels are compiled for (0: ptxas' choice).
-#ifndef GS_MINB
-#define GS_MINB 0
+// Resident CTAs per SM the tiled kernels are compiled for (register caps 65536 /
+// (GS_TPB * n)): the kernels wait on dependent random accesses, so what counts is
+// how many warps of all the launches in flight fit an SM.  ptxas -v at these
+// caps: k_rows 80 registers (64 B of spills), k_expand 63, k_cand 80, no spills.
+#ifndef GS_MINB_ROWS
+#define GS_MINB_ROWS 3
 #endif
-#if GS_MINB > 0
-#define GS_BOUNDS __launch_bounds__(GS_TPB, GS_MINB)
-#else
+#ifndef GS_MINB_EXPAND
+#define GS_MINB_EXPAND 4
+#endif
+#ifndef GS_MINB_CAND
+#define GS_MINB_CAND 3
+#endif
 #define GS_BOUNDS __launch_bounds__(GS_TPB)
-#endif
 
 namespace {
 
@@ -152,77 +157,85 @@ __device__ __forceinline__ void stage_ws(GsWs &dst, const GsWs *__restrict__ src
   __syncthreads();
 }
 
-// ------------------------------------------------------ decoupled look-back
-// Single-pass prefix over tiles handed out by a ticket (Merrill & Garland): a
-// tile publishes its aggregate, walks back over its predecessors' aggregates
-// until it meets a published inclusive prefix, then publishes its own.  Every
-// predecessor of a tile was drawn by a CTA that is already running, so the spin
-// always ends, whatever else shares the machine.  Executed by warp 0; counter c
-// lives in lane c % 32, round c / 32.  Status words carry the sample's scan
-// epoch, so descriptors are never reset (k_tail zeroes them once per 2^30 uses).
-template <typename T, int NPL, int NCPAD>
-__device__ __forceinline__ void tile_lookback(uint32_t *status, T *agg, T *inc, int tile, uint32_t ep,
-                                              const T (&mine)[NPL], T (&excl)[NPL]) {
-  const int lane = lane_id();
-  {
-    T *pub = (tile == 0 ? inc : agg) + (size_t)tile * NCPAD;
+// ------------------------------------------------------------ flat look-back
+// Single-pass prefix over UNITS (a tile of rows, a run of candidate tiles) handed
+// out by a ticket.  A unit publishes its aggregate and then sums the aggregates of
+// ALL its predecessors itself: thread j of the CTA reads unit base + j's counters
+// (independent loads: one L2 round trip), a CTA-wide reduction per counter gives
+// the exclusive prefix.  Nobody waits for anybody's PREFIX, only for aggregates,
+// and every predecessor was drawn by a CTA that is already running -- so the wait
+// is one status round trip whatever else shares the machine, and there is no chain
+// through the units in flight (the classic decoupled look-back walks 32 units per
+// round trip: with ~450 CTAs in flight that walk dominated the kernel).  Beyond
+// GS_TPB units the sum restarts from the inclusive prefix that every GS_TPB-th
+// unit publishes.  Status words carry the sample's scan epoch, so descriptors are
+// never reset (k_tail zeroes them once per 2^30 uses).  Called by the whole CTA;
+// s_mine[] must be visible (barrier) on entry, s_pre[] is on exit.
+__device__ __forceinline__ unsigned long long warp_sum_t(unsigned long long v) {
 #pragma unroll
-    for (int j = 0; j < NPL; j++)
-      if (lane + 32 * j < NCPAD) pub[lane + 32 * j] = mine[j];
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+  return v;
+}
+__device__ __forceinline__ uint32_t warp_sum_t(uint32_t v) { return __reduce_add_sync(FULL, v); }
+
+template <typename T, int NC, int NCPAD>
+__device__ __forceinline__ void flat_lookback(uint32_t *status, T *agg, T *inc, int r, uint32_t ep,
+                                              const T *s_mine, T *s_pre, T (*s_red)[NCPAD]) {
+  const int tid = threadIdx.x, lane = lane_id(), w = warp_id();
+  if (tid < NC) agg[(size_t)r * NCPAD + tid] = s_mine[tid];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
     __threadfence();
-    __syncwarp();
-    if (lane == 0) {
-      __threadfence();
-      st_release(status + tile, (ep << 2) | (tile == 0 ? 2u : 1u));
-    }
+    st_release(status + r, (ep << 2) | 1u);
   }
+  const int base = r & ~(GS_TPB - 1);
+  const int j = base + tid;
+  T v[NC];
 #pragma unroll
-  for (int j = 0; j < NPL; j++) excl[j] = (T)0;
-  if (tile == 0) return;
-  int t = tile - 1;
-  for (;;) {
-    const int tl = t - lane;
-    uint32_t pm, rm, need;
+  for (int c = 0; c < NC; c++) v[c] = (T)0;
+  if (j < r) {
     for (;;) {
-      const uint32_t st = tl >= 0 ? ld_acquire(status + tl) : ((ep << 2) | 2u);  // before tile 0: prefix 0
-      const bool ready = (st >> 2) == ep && (st & 3u) != 0u;
-      pm = __ballot_sync(FULL, ready && (st & 3u) == 2u);
-      rm = __ballot_sync(FULL, ready);
-      need = pm ? (((pm & (0u - pm)) << 1) - 1u) : FULL;  // lanes up to the nearest inclusive prefix
-      if ((rm & need) == need) break;
-      __nanosleep(32);
+      const uint32_t st = ld_acquire(status + j);
+      if ((st >> 2) == ep && (st & 3u) != 0u) break;
+      __nanosleep(64);
     }
-    __syncwarp();
-    const int np = pm ? (__ffs((int)pm) - 1) : 32;  // tiles t .. t-np+1 give aggregates, tile t-np its prefix
-    for (int j = 0; j < np; j++) {
-      const T *a = agg + (size_t)(t - j) * NCPAD;
+    const T *a = agg + (size_t)j * NCPAD;
 #pragma unroll
-      for (int jj = 0; jj < NPL; jj++)
-        if (lane + 32 * jj < NCPAD) excl[jj] += __ldcg(a + lane + 32 * jj);
-    }
-    if (pm) {
-      const int tp = t - np;
-      if (tp >= 0) {
-        const T *a = inc + (size_t)tp * NCPAD;
-#pragma unroll
-        for (int jj = 0; jj < NPL; jj++)
-          if (lane + 32 * jj < NCPAD) excl[jj] += __ldcg(a + lane + 32 * jj);
-      }
-      break;
-    }
-    t -= 32;
+    for (int c = 0; c < NC; c++) v[c] = __ldcg(a + c);
   }
-  {
-    T *pub = inc + (size_t)tile * NCPAD;
-#pragma unroll
-    for (int j = 0; j < NPL; j++)
-      if (lane + 32 * j < NCPAD) pub[lane + 32 * j] = excl[j] + mine[j];
-    __threadfence();
-    __syncwarp();
-    if (lane == 0) {
-      __threadfence();
-      st_release(status + tile, (ep << 2) | 2u);
+  T carry = (T)0;
+  if (base > 0 && tid < NC) {  // inclusive prefix of the unit before this chunk
+    for (;;) {
+      const uint32_t st = ld_acquire(status + base - 1);
+      if ((st >> 2) == ep && (st & 3u) == 2u) break;
+      __nanosleep(64);
     }
+    carry = __ldcg(inc + (size_t)(base - 1) * NCPAD + tid);
+  }
+  if (base < r) {  // CTA-wide sum per counter (uniform branch)
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+      const T sum = warp_sum_t(v[c]);
+      if (lane == (c & 31)) s_red[w][c] = sum;
+    }
+  }
+  __syncthreads();
+  const bool pub = (r & (GS_TPB - 1)) == GS_TPB - 1;
+  if (tid < NC) {
+    T tot = carry;
+    if (base < r) {
+#pragma unroll
+      for (int k = 0; k < GS_NW; k++) tot += s_red[k][tid];
+    }
+    s_pre[tid] = tot;
+    if (pub) inc[(size_t)r * NCPAD + tid] = tot + s_mine[tid];
+  }
+  if (pub) __threadfence();
+  __syncthreads();
+  if (pub && tid == 0) {
+    __threadfence();
+    st_release(status + r, (ep << 2) | 2u);
   }
 }
 
@@ -266,8 +279,10 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   __shared__ unsigned long long s_wc[GS_NW][GS_RS_NC];
   __shared__ unsigned long long s_base[GS_NW][GS_RS_NC];
   __shared__ unsigned long long s_agg[GS_RS_NC], s_pre[GS_RS_NC];
+  __shared__ unsigned long long s_red[GS_NW][GS_RS_NC];
   __shared__ int s_tile;
   if (!FIRST && h->status != 0) return;
+  if (threadIdx.x < GS_RS_NC) s_agg[threadIdx.x] = 0ull;  // counters beyond 2 + P stay zero
   const int P = ws.P, NC = 2 + P;
   const int lane = lane_id(), w = warp_id();
   int F;
@@ -382,14 +397,9 @@ __device__ void rows_role(const GsWs &ws, int layer) {
       s_base[w][lane] = a;
       if (w == 0) s_agg[lane] = all;
     }
-    if (w == 0) {
-      __syncwarp();
-      unsigned long long mine[1], excl[1];
-      mine[0] = lane < NC ? s_agg[lane] : 0ull;
-      tile_lookback<unsigned long long, 1, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, mine, excl);
-      if (lane < GS_RS_NC) s_pre[lane] = excl[0];
-    }
     __syncthreads();
+    flat_lookback<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, s_agg, s_pre,
+                                                                   s_red);
     if (FIRST && bad) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);
     unsigned long long base_c = s_pre[0] + s_base[w][0] + inc_c - c4;
     uint32_t base_s = (uint32_t)(s_pre[1] + s_base[w][1]) + inc_s - s4;
@@ -450,21 +460,19 @@ __device__ void rows_role(const GsWs &ws, int layer) {
 // Lays out every list of the layer.  Runs in the last CTA of k_expand: by then
 // the per-layer totals are exact (see expand_role), so k_cand writes each list
 // once, at its final place; a part's nine lists are contiguous.
-__device__ void layer_alloc(const GsWs &ws, int layer) {
+__device__ void layer_alloc(const GsWs &ws, int layer, const uint32_t *cnt /* shared memory copy */) {
   gs_sample_header *h = ws.hdr;
   const int P = ws.P;
-  const uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
   const int F = h->frontier_len[layer];
   bool ok = true;
-  const unsigned long long fnext = (unsigned long long)F + __ldcg(cnt + GS_CNT_NEW);
+  const unsigned long long fnext = (unsigned long long)F + cnt[GS_CNT_NEW];
   if (layer + 1 < ws.L && fnext > (unsigned long long)ws.Fcap) ok = false;
   int64_t used = h->slab_used, fused = h->reserved[1];
   const gs_span fs = slab_alloc(fused, ws.fslab_cap, (uint32_t)fnext, ok);
   int64_t edges = 0;
   for (int q = 0; q < P && ok; q++) {
-    const uint32_t n_in = __ldcg(cnt + GS_CNT_IN(P, q)), n_e = __ldcg(cnt + GS_CNT_E(P, q)),
-                   n_out = __ldcg(cnt + GS_CNT_OUT(P, q)), n_own = __ldcg(cnt + GS_CNT_OWN(P, q)),
-                   n_to = __ldcg(cnt + GS_CNT_TO(P, q)), n_self = __ldcg(cnt + GS_CNT_SELF(P, q));
+    const uint32_t n_in = cnt[GS_CNT_IN(P, q)], n_e = cnt[GS_CNT_E(P, q)], n_out = cnt[GS_CNT_OUT(P, q)],
+                   n_own = cnt[GS_CNT_OWN(P, q)], n_to = cnt[GS_CNT_TO(P, q)], n_self = cnt[GS_CNT_SELF(P, q)];
     gs_span *fl = h->field[layer][q];
     fl[GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, n_in, ok);
     fl[GS_F_OUT_NODES] = slab_alloc(used, ws.slab_cap, n_out, ok);
@@ -624,13 +632,28 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         old[k] = tbl.atom_min(v[k], tge | (p0 + k));
       }
     }
+    // first edge of a row into each part: one returning atomicOr per run of equal rows,
+    // issued before the atom.min results are looked at (independent of them)
+    uint32_t rbits[GS_IPT], was[GS_IPT];
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) rbits[k] = edge[k] ? 1u << g[k] : 0u;
+#pragma unroll
+    for (int k = 0; k + 1 < GS_IPT; k++)
+      if (row[k + 1] == row[k]) {
+        rbits[k + 1] |= rbits[k];
+        rbits[k] = 0u;
+      }
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      was[k] = 0u;
+      if (rbits[k]) was[k] = atomicOr(ws.rowhas + row[k], rbits[k]);
+    }
     int32_t cvv[GS_IPT];
-    uint32_t cf[GS_IPT], rbits[GS_IPT];
+    uint32_t cf[GS_IPT];
     unsigned long long pk_in = 0ull, pk_e = 0ull, pk_out = 0ull, pk_own = 0ull, pk_to = 0ull;
     uint32_t n_new = 0u;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      rbits[k] = 0u;
       if (slot[k] == 0) {
         cvv[k] = row[k];  // self entry: the row index; part = owner of the row's node
         cf[k] = GS_CK_SELF | ((uint32_t)owner_of(ws, nd1[k]) << GS_CF_PART_SHIFT);
@@ -641,7 +664,6 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         cvv[k] = v[k];
         cf[k] = GS_CK_EDGE | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
         pk_e += pk_one(g[k]);
-        rbits[k] = 1u << g[k];
         if (!tag.mine(old[k])) {  // first arrival for a node that is new to the frontier
           n_new++;
           pk_in += pk_one(g[k]);
@@ -653,24 +675,16 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         }
       }
     }
-    // first edge of a row into each part: one atomicOr per run of equal rows
-#pragma unroll
-    for (int k = 0; k + 1 < GS_IPT; k++)
-      if (row[k + 1] == row[k]) {
-        rbits[k + 1] |= rbits[k];
-        rbits[k] = 0u;
-      }
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++)
       if (rbits[k]) {
-        const uint32_t was = atomicOr(ws.rowhas + row[k], rbits[k]);
-        const uint32_t nb = rbits[k] & ~was;
+        const uint32_t nb = rbits[k] & ~was[k];
         if (nb) {
           const int g0 = owner_of(ws, nd1[k]);
           const uint32_t own = 1u << g0;
           pk_out += pk_spread(nb);
           if (nb & own) pk_own += pk_one(g0);
-          if ((nb & ~own) && !(was & ~own)) pk_to += pk_one(g0);
+          if ((nb & ~own) && !(was[k] & ~own)) pk_to += pk_one(g0);
         }
       }
     if (p0 + GS_IPT <= C) {
@@ -706,7 +720,9 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   __syncthreads();
   if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);
   if (!last_block(ws.tickets + layer * GS_TICKETS + 1)) return;
-  if (threadIdx.x == 0) layer_alloc(ws, layer);
+  if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = __ldcg(cnt + threadIdx.x);  // one round trip for all totals
+  __syncthreads();
+  if (threadIdx.x == 0) layer_alloc(ws, layer, s_cnt);
 }
 
 // ------------------------------------------------------------------- k_cand
@@ -733,19 +749,63 @@ __device__ void expand_role(const GsWs &ws, int layer) {
 #define CS_OWN(q) (25 + (q))
 #define CS_TO(q) (33 + (q))
 #define CS_USED 41
-__device__ void cand_role(const GsWs &ws, int layer) {
+#define CS_PAD GS_CS_NC  // descriptor / shared-memory row length
+#define CS_RMAX 8      // tiles of one run (held in shared memory between the two sweeps)
+
+// A CTA takes a RUN of up to CS_RMAX consecutive tiles (ticket order) and goes
+// over it twice.  Sweep 1 reads the stream, does the random reads (table / ea /
+// rowhas / off), classifies every candidate and keeps what the random reads
+// returned in shared memory; its per-(tile, warp) class totals, scanned in
+// place, are the run's aggregate.  ONE flat look-back per run turns that into
+// the run's exclusive prefix.  Sweep 2 replays the run from shared memory: packed
+// warp scans give every item its rank, the lists are written at their final place.
+// Each candidate is read from the stream twice (the second time out of L1/L2) and
+// looked up in the table once.
+struct CandSmem {
+  uint32_t x[CS_RMAX][GS_TILE];       // minimum position: of an edge's source / of a self entry's node as a source
+  uint8_t y[CS_RMAX][GS_TILE];        // self entry: rowhas; frontier-row edge: 1 = it precedes the row's self entry
+  uint16_t wt[CS_RMAX][GS_NW][CS_PAD];  // class totals per (tile, warp) -> exclusive prefix inside the run
+  uint32_t red[GS_NW][CS_PAD];
+  uint32_t agg[CS_PAD], pre[CS_PAD];
+  int32_t fo[GS_MAX_PARTS][GS_NUM_FIELDS];
+  int run;
+};
+
+// classes of one item; bit 8: in_nodes first, bit 9: frontier first, bit 10: self entry whose node is never a source
+__device__ __forceinline__ uint32_t cand_class(uint32_t fl, uint32_t p, uint32_t x, uint32_t y,
+                                               unsigned long long &pi, unsigned long long &pe,
+                                               unsigned long long &po, unsigned long long &pw,
+                                               unsigned long long &pt, uint32_t &nf) {
+  const uint32_t kind = fl & GS_CK_MASK;
+  const int g = (int)((fl >> GS_CF_PART_SHIFT) & 7u);
+  if (kind == GS_CK_SELF) {
+    const uint32_t own = 1u << g;
+    if (x > p) { fl |= 0x200u; nf++; }
+    if (x == GS_INF) fl |= 0x400u;
+    po += pk_spread(y);
+    if (y & own) pw += pk_one(g);
+    if (y & ~own) pt += pk_one(g);
+  } else if (kind != GS_CK_DEAD) {
+    pe += pk_one(g);
+    if (x == p) {
+      fl |= 0x100u;
+      pi += pk_one(g);
+      if (kind == GS_CK_EDGE || y) { fl |= 0x200u; nf++; }
+    }
+  }
+  return fl;
+}
+
+__device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
-  __shared__ uint32_t s_wc[GS_NW][GS_CS_NC];    // per-warp totals of the tile
-  __shared__ uint32_t s_base[GS_NW][GS_CS_NC];  // earlier warps of the tile (+ tile prefix, added below)
-  __shared__ uint32_t s_pre[GS_CS_NC];
-  __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
-  __shared__ int s_tile;
   const Tbl tbl(ws);
   const int P = ws.P;
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
   if (ntiles == 0) return;
+  const int R = min(CS_RMAX, (ntiles + (int)gridDim.x - 1) / (int)gridDim.x);
+  const int nruns = (ntiles + R - 1) / R;
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
   const GsState stt = *ws.state;
@@ -755,186 +815,194 @@ __device__ void cand_role(const GsWs &ws, int layer) {
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
   const int lane = lane_id(), w = warp_id();
   if (threadIdx.x < P * GS_NUM_FIELDS)
-    s_fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
+    sm.fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
         h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
-  if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);
-  __syncthreads();
-  int t = s_tile;
-  while (t < ntiles) {
-    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
-    const bool full = p0 + GS_IPT <= C;
-    uint32_t fl[GS_IPT];
-    int32_t ci[GS_IPT];
-    if (full) {
-      const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
-      const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
-      ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
-      fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
-    } else {
-#pragma unroll
-      for (int k = 0; k < GS_IPT; k++) {
-        fl[k] = GS_CK_DEAD;
-        ci[k] = 0;
-        if (p0 + k < C) {
-          fl[k] = ws.cflag[p0 + k];
-          ci[k] = ws.cand[p0 + k];
-        }
-      }
-    }
-    // x: minimum position (edge: of its source; self: of the row's node as an edge source)
-    // y: self: rowhas; frontier-row edge: the row's self position
-    // z: self / frontier-row edge: the node id
-    uint32_t x[GS_IPT], y[GS_IPT];
-    int32_t z[GS_IPT];
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      const uint32_t kind = fl[k] & GS_CK_MASK;
-      x[k] = GS_INF; y[k] = 0u; z[k] = ci[k];
-      if (kind == GS_CK_EDGE) {
-        x[k] = tbl.ld(ci[k]) & tag.pmask;
-      } else if (kind != GS_CK_DEAD) {
-        x[k] = __ldcg(ws.ea + ci[k]);
-        y[k] = kind == GS_CK_SELF ? __ldcg(ws.rowhas + ci[k]) : __ldcg(ws.off + ci[k]);
-        z[k] = front[ci[k]];
-      }
-    }
-    // classes; bit 8: in_nodes first, bit 9: frontier first, bit 10: self entry whose node is never an edge source
-    unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
-    uint32_t nf = 0u;
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      const uint32_t p = p0 + k, kind = fl[k] & GS_CK_MASK;
-      const int g = (int)(fl[k] >> GS_CF_PART_SHIFT);
-      if (kind == GS_CK_SELF) {
-        const uint32_t has = y[k], own = 1u << g;
-        if (x[k] > p) { fl[k] |= 0x200u; nf++; }
-        if (x[k] == GS_INF) fl[k] |= 0x400u;
-        po += pk_spread(has);
-        if (has & own) pw += pk_one(g);
-        if (has & ~own) pt += pk_one(g);
-      } else if (kind != GS_CK_DEAD) {
-        pe += pk_one(g);
-        if (x[k] == p) {
-          fl[k] |= 0x100u;
-          pi += pk_one(g);
-          if (kind == GS_CK_EDGE || p < y[k]) { fl[k] |= 0x200u; nf++; }
-        }
-      }
-    }
-    // exclusive packed prefixes over the warp's lanes; lane 31 holds the totals
-    const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe), inc_o = pk_warp_incl(po),
-                             inc_w = pk_warp_incl(pw), inc_t = pk_warp_incl(pt);
-    const uint32_t inc_f = warp_incl_scan(nf);
-    {
-      const unsigned long long t_i = __shfl_sync(FULL, inc_i, 31), t_e = __shfl_sync(FULL, inc_e, 31),
-                               t_o = __shfl_sync(FULL, inc_o, 31), t_w = __shfl_sync(FULL, inc_w, 31),
-                               t_t = __shfl_sync(FULL, inc_t, 31);
-      const uint32_t t_f = __shfl_sync(FULL, inc_f, 31);
-      if (lane < 8) {
-        s_wc[w][CS_IN(lane)] = pk_get(t_i, lane);
-        s_wc[w][CS_E(lane)] = pk_get(t_e, lane);
-        s_wc[w][CS_OUT(lane)] = pk_get(t_o, lane);
-        s_wc[w][CS_OWN(lane)] = pk_get(t_w, lane);
-        s_wc[w][CS_TO(lane)] = pk_get(t_t, lane);
-      }
-      if (lane == 8) s_wc[w][CS_NF] = t_f;
-    }
+  for (;;) {
+    __syncthreads();  // the previous run's shared memory is no longer read
+    if (threadIdx.x == 0) sm.run = (int)atomicAdd(tick, 1u);
     __syncthreads();
-    if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);  // next tile of this CTA (read after the barrier below)
-    if (w == 0) {  // tile aggregate -> look-back -> tile prefix
-      uint32_t mine[2], excl[2];
-#pragma unroll
-      for (int j = 0; j < 2; j++) {
-        const int c = lane + 32 * j;
-        uint32_t all = 0u;
-        if (c < CS_USED) {
-#pragma unroll
-          for (int k = 0; k < GS_NW; k++) all += s_wc[k][c];
-        }
-        mine[j] = all;
-      }
-      tile_lookback<uint32_t, 2, GS_CS_NC>(ws.cs_status, cs_agg, cs_inc, t, ep, mine, excl);
-      s_pre[lane] = excl[0];
-      s_pre[lane + 32] = excl[1];
-    } else if (w <= 2) {  // meanwhile: earlier warps of the tile
-      const int c = (int)threadIdx.x - 32;
-      if (c < CS_USED) {
-        uint32_t run = 0u;
-#pragma unroll
-        for (int k = 0; k < GS_NW; k++) {
-          s_base[k][c] = run;
-          run += s_wc[k][c];
-        }
-      }
-    }
-    __syncthreads();
-#define CS_B(c) (s_pre[c] + s_base[w][c])
-    uint32_t rf = CS_B(CS_NF) + inc_f - nf;
-    unsigned long long ri = inc_i - pi, re = inc_e - pe, ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
-    bool wrote = false;
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      const uint32_t kind = fl[k] & GS_CK_MASK;
-      const int g = (int)((fl[k] >> GS_CF_PART_SHIFT) & 7u);
-      if (kind == GS_CK_SELF) {
-        const int32_t nd = z[k];
-        const uint32_t has = y[k], own = 1u << g;
-        if (fl[k] & 0x200u) fnext[rf++] = nd;
-        int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
-        for (uint32_t hb = has; hb; hb &= hb - 1u) {
-          const int q = __ffs((int)hb) - 1;
-          const uint32_t op = CS_B(CS_OUT(q)) + pk_get(ro, q);
-          const uint32_t ow = CS_B(CS_OWN(q)) + pk_get(rw, q);
-          ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd;
-          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)(CS_B(CS_E(q)) + pk_get(re, q));
-          if (q == g) {
-            ws.slab[s_fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
-            op_own = (int32_t)op;
-          } else {
-            ws.slab[s_fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
-          }
-        }
-        if (has & ~own) {
-          ws.slab[s_fo[g][GS_F_TO_IDS] + CS_B(CS_TO(g)) + pk_get(rt, g)] = op_own;
-          rt += pk_one(g);
-        }
-        const uint32_t sr = ws.selfrank[ci[k]];
-        ws.slab[s_fo[g][GS_F_SELF_OUT] + sr] = op_own;
-        if (fl[k] & 0x400u) ws.slab[s_fo[g][GS_F_SELF_IN] + sr] = -1;  // else: written by the node's first edge
-        ro += pk_spread(has);
-        if (has & own) rw += pk_one(g);
-      } else if (kind != GS_CK_DEAD) {
-        const uint32_t ex = CS_B(CS_E(g)) + pk_get(re, g);
-        if (fl[k] & 0x100u) {
-          // the first edge occurrence of a source knows its rank: final csr_indices
-          // value, in_nodes entry, relabel map entry; every other edge leaves ~m
-          // (m = position of that first occurrence) for relabel_role
-          const uint32_t rk = CS_B(CS_IN(g)) + pk_get(ri, g);
-          ws.slab[s_fo[g][GS_F_IN_NODES] + rk] = z[k];
-          ws.slab[s_fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)rk;
-          if (kind == GS_CK_FHIT) ws.slab[s_fo[g][GS_F_SELF_IN] + ws.selfrank[ci[k]]] = (int32_t)rk;
-          if (fl[k] & 0x200u) fnext[rf++] = z[k];
-          ci[k] = (int32_t)rk;
-          wrote = true;
-          ri += pk_one(g);
-        } else {
-          ws.slab[s_fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)~x[k];
-        }
-        re += pk_one(g);
-      }
-    }
-#undef CS_B
-    if (wrote) {
+    const int r = sm.run;
+    if (r >= nruns) break;
+    const int t_lo = r * R, nt = min(R, ntiles - t_lo);
+    // ---- sweep 1: random reads, classes, totals
+    for (int k = 0; k < nt; k++) {
+      const uint32_t p0 = (uint32_t)(t_lo + k) * GS_TILE + GS_IPT * threadIdx.x;
+      const bool full = p0 + GS_IPT <= C;
+      uint32_t fl[GS_IPT];
+      int32_t ci[GS_IPT];
       if (full) {
-        *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+        const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+        const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
+        ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
+        fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
       } else {
 #pragma unroll
-        for (int k = 0; k < GS_IPT; k++)
-          if (p0 + k < C && (fl[k] & 0x100u)) ws.cand[p0 + k] = ci[k];
+        for (int i = 0; i < GS_IPT; i++) {
+          fl[i] = GS_CK_DEAD;
+          ci[i] = 0;
+          if (p0 + i < C) {
+            fl[i] = ws.cflag[p0 + i];
+            ci[i] = ws.cand[p0 + i];
+          }
+        }
       }
+      uint32_t x[GS_IPT], y[GS_IPT];
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++) {
+        const uint32_t kind = fl[i] & GS_CK_MASK;
+        x[i] = GS_INF; y[i] = 0u;
+        if (kind == GS_CK_EDGE) {
+          x[i] = tbl.ld(ci[i]) & tag.pmask;
+        } else if (kind != GS_CK_DEAD) {
+          x[i] = __ldcg(ws.ea + ci[i]);
+          y[i] = kind == GS_CK_SELF ? __ldcg(ws.rowhas + ci[i]) : __ldcg(ws.off + ci[i]);
+        }
+      }
+      unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
+      uint32_t nf = 0u;
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++) {
+        if ((fl[i] & GS_CK_MASK) == GS_CK_FHIT) y[i] = (p0 + i) < y[i] ? 1u : 0u;
+        cand_class(fl[i], p0 + i, x[i], y[i], pi, pe, po, pw, pt, nf);
+      }
+      *reinterpret_cast<uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]) = make_uint4(x[0], x[1], x[2], x[3]);
+      *reinterpret_cast<uchar4 *>(&sm.y[k][GS_IPT * threadIdx.x]) =
+          make_uchar4((unsigned char)y[0], (unsigned char)y[1], (unsigned char)y[2], (unsigned char)y[3]);
+      pi = pk_redux(pi); pe = pk_redux(pe); po = pk_redux(po); pw = pk_redux(pw); pt = pk_redux(pt);
+      nf = __reduce_add_sync(FULL, nf);
+      if (lane < 8) {
+        sm.wt[k][w][CS_IN(lane)] = (uint16_t)pk_get(pi, lane);
+        sm.wt[k][w][CS_E(lane)] = (uint16_t)pk_get(pe, lane);
+        sm.wt[k][w][CS_OUT(lane)] = (uint16_t)pk_get(po, lane);
+        sm.wt[k][w][CS_OWN(lane)] = (uint16_t)pk_get(pw, lane);
+        sm.wt[k][w][CS_TO(lane)] = (uint16_t)pk_get(pt, lane);
+      }
+      if (lane == 8) sm.wt[k][w][CS_NF] = (uint16_t)nf;
     }
     __syncthreads();
-    t = s_tile;
+    if (threadIdx.x < CS_PAD) {  // totals -> exclusive prefix over the run's (tile, warp) sequence
+      uint32_t run = 0u;
+      if (threadIdx.x < CS_USED)
+        for (int k = 0; k < nt; k++)
+#pragma unroll
+          for (int ww = 0; ww < GS_NW; ww++) {
+            const uint32_t tq = sm.wt[k][ww][threadIdx.x];
+            sm.wt[k][ww][threadIdx.x] = (uint16_t)run;
+            run += tq;
+          }
+      sm.agg[threadIdx.x] = run;
+    }
+    __syncthreads();
+    flat_lookback<uint32_t, CS_USED, GS_CS_NC>(ws.cs_status, cs_agg, cs_inc, r, ep, sm.agg, sm.pre, sm.red);
+    // ---- sweep 2: ranks and lists
+    for (int k = 0; k < nt; k++) {
+      const uint32_t p0 = (uint32_t)(t_lo + k) * GS_TILE + GS_IPT * threadIdx.x;
+      const bool full = p0 + GS_IPT <= C;
+      uint32_t fl[GS_IPT];
+      int32_t ci[GS_IPT];
+      if (full) {
+        const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+        const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
+        ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
+        fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < GS_IPT; i++) {
+          fl[i] = GS_CK_DEAD;
+          ci[i] = 0;
+          if (p0 + i < C) {
+            fl[i] = ws.cflag[p0 + i];
+            ci[i] = ws.cand[p0 + i];
+          }
+        }
+      }
+      const uint4 x4 = *reinterpret_cast<const uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]);
+      const uchar4 y4 = *reinterpret_cast<const uchar4 *>(&sm.y[k][GS_IPT * threadIdx.x]);
+      const uint32_t x[GS_IPT] = {x4.x, x4.y, x4.z, x4.w};
+      const uint32_t y[GS_IPT] = {y4.x, y4.y, y4.z, y4.w};
+      unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
+      uint32_t nf = 0u;
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++) fl[i] = cand_class(fl[i], p0 + i, x[i], y[i], pi, pe, po, pw, pt, nf);
+      // the node id of self entries and of first occurrences among frontier-row edges
+      int32_t z[GS_IPT];
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++) {
+        const uint32_t kind = fl[i] & GS_CK_MASK;
+        z[i] = ci[i];
+        if (kind == GS_CK_SELF || (kind == GS_CK_FHIT && (fl[i] & 0x100u))) z[i] = front[ci[i]];
+      }
+      // exclusive packed prefixes over the warp's lanes
+      const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe), inc_o = pk_warp_incl(po),
+                               inc_w = pk_warp_incl(pw), inc_t = pk_warp_incl(pt);
+      const uint32_t inc_f = warp_incl_scan(nf);
+      const uint16_t *wtb = sm.wt[k][w];
+#define CS_B(c) (sm.pre[c] + (uint32_t)wtb[c])
+      uint32_t rf = CS_B(CS_NF) + inc_f - nf;
+      unsigned long long ri = inc_i - pi, re = inc_e - pe, ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
+      bool wrote = false;
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++) {
+        const uint32_t kind = fl[i] & GS_CK_MASK;
+        const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
+        if (kind == GS_CK_SELF) {
+          const int32_t nd = z[i];
+          const uint32_t has = y[i], own = 1u << g;
+          if (fl[i] & 0x200u) fnext[rf++] = nd;
+          int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+          for (uint32_t hb = has; hb; hb &= hb - 1u) {
+            const int q = __ffs((int)hb) - 1;
+            const uint32_t op = CS_B(CS_OUT(q)) + pk_get(ro, q);
+            const uint32_t ow = CS_B(CS_OWN(q)) + pk_get(rw, q);
+            ws.slab[sm.fo[q][GS_F_OUT_NODES] + op] = nd;
+            ws.slab[sm.fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)(CS_B(CS_E(q)) + pk_get(re, q));
+            if (q == g) {
+              ws.slab[sm.fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+              op_own = (int32_t)op;
+            } else {
+              ws.slab[sm.fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+            }
+          }
+          if (has & ~own) {
+            ws.slab[sm.fo[g][GS_F_TO_IDS] + CS_B(CS_TO(g)) + pk_get(rt, g)] = op_own;
+            rt += pk_one(g);
+          }
+          const uint32_t sr = ws.selfrank[ci[i]];
+          ws.slab[sm.fo[g][GS_F_SELF_OUT] + sr] = op_own;
+          if (fl[i] & 0x400u) ws.slab[sm.fo[g][GS_F_SELF_IN] + sr] = -1;  // else: written by the node's first edge
+          ro += pk_spread(has);
+          if (has & own) rw += pk_one(g);
+        } else if (kind != GS_CK_DEAD) {
+          const uint32_t ex = CS_B(CS_E(g)) + pk_get(re, g);
+          if (fl[i] & 0x100u) {
+            // the first edge occurrence of a source knows its rank: final csr_indices
+            // value, in_nodes entry, relabel map entry; every other edge leaves ~m
+            // (m = position of that first occurrence) for relabel_role
+            const uint32_t rk = CS_B(CS_IN(g)) + pk_get(ri, g);
+            ws.slab[sm.fo[g][GS_F_IN_NODES] + rk] = z[i];
+            ws.slab[sm.fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)rk;
+            if (kind == GS_CK_FHIT) ws.slab[sm.fo[g][GS_F_SELF_IN] + ws.selfrank[ci[i]]] = (int32_t)rk;
+            if (fl[i] & 0x200u) fnext[rf++] = z[i];
+            ci[i] = (int32_t)rk;
+            wrote = true;
+            ri += pk_one(g);
+          } else {
+            ws.slab[sm.fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)~x[i];
+          }
+          re += pk_one(g);
+        }
+      }
+#undef CS_B
+      if (wrote) {
+        if (full) {
+          *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < GS_IPT; i++)
+            if (p0 + i < C && (fl[i] & 0x100u)) ws.cand[p0 + i] = ci[i];
+        }
+      }
+    }
   }
 }
 
@@ -1012,7 +1080,7 @@ __device__ void gather_role(const GsWs &ws, int bx, int nb) {
 
 // ------------------------------------------------------------------ kernels
 template <bool FIRST>
-__global__ void GS_BOUNDS k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows) {
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
   if ((int)blockIdx.x < grid_rows) rows_role<FIRST>(ws, layer);
@@ -1020,16 +1088,17 @@ __global__ void GS_BOUNDS k_rows(const GsWs *__restrict__ wsv, int layer, int gr
 }
 
 template <int RNG>
-__global__ void GS_BOUNDS k_expand(const GsWs *__restrict__ wsv, int layer) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand(const GsWs *__restrict__ wsv, int layer) {
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
   expand_role<RNG>(ws, layer);
 }
 
-__global__ void GS_BOUNDS k_cand(const GsWs *__restrict__ wsv, int layer) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand(const GsWs *__restrict__ wsv, int layer) {
   __shared__ GsWs ws;
+  extern __shared__ __align__(16) unsigned char s_dyn[];
   stage_ws(ws, wsv + blockIdx.y);
-  cand_role(ws, layer);
+  cand_role(ws, layer, *reinterpret_cast<CandSmem *>(s_dyn));
 }
 
 // Last launch of a sample: relabel of the last layer, the fused feature gather,
@@ -1281,8 +1350,11 @@ void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int
   else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE><<<g, GS_TPB, 0, st>>>(wsv, layer);
   else k_expand<(int)GS_RNG_PHILOX><<<g, GS_TPB, 0, st>>>(wsv, layer);
 }
+void gs_kernels_prepare() {  // per device: k_cand's run buffer needs more than the default 48 KB
+  cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CandSmem));
+}
 void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st) {
-  k_cand<<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
+  k_cand<<<dim3(grid, members), GS_TPB, sizeof(CandSmem), st>>>(wsv, layer);
 }
 void gs_launch_tail(const GsWs *wsv, int members, int grid_relabel, int grid_gather, cudaStream_t st) {
   k_tail<<<dim3(grid_relabel + grid_gather, members), GS_TPB, 0, st>>>(wsv, grid_relabel, grid_gather);
