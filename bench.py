@@ -209,7 +209,7 @@ def kernel_bytes(view, P):
     DESIGN section 5) -- the per-kernel roofline numerator."""
     out = {}
     L = view.num_layers
-    rel = {}
+    tail = {}
     for l in range(L):
         F, Fn, C = view.frontier_len[l], view.frontier_len[l + 1], view.cand_len[l]
         E = sum(view.field_len(l, g, "csr_indices") for g in range(P))
@@ -217,13 +217,14 @@ def kernel_bytes(view, P):
         n_out = sum(view.field_len(l, g, "out_nodes") for g in range(P))
         lists = sum(view.field_len(l, g, k) for g in range(P)
                     for k in ("owned_out_nodes", "from_ids", "to_ids", "self_ids_in", "self_ids_out"))
-        rel[l] = E * (4 + 4) + (E - n_in) * 4                             # csr_indices in/out + rank lookups
+        relabel = E * (4 + 4) + (E - n_in) * 4                            # csr_indices in/out + rank lookups
+        rowside = F * (4 * 4 + 4) + n_out * 4 + (2 * n_out + lists) * 4     # nd, rowhas, ea, selfrank, relabel map; rowscan; lists out
+        tail[l] = relabel + rowside
         rows = F * (4 + 16) + F * (16 + 4 + 4 + 4 + 4 + 4)                 # frontier + indptr pair in; rowinfo, off, selfrank, ea, rowhas, table mark out
-        out[f"rows@{l}" if l == 0 else f"rows+relabel@{l}"] = rows + (rel[l - 1] if l else 0)
-        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5            # rowinfo + off, pick + atom.min per edge, stream out
-        out[f"cand@{l}"] = (C * 5 + C * 4 + F * 12                        # stream in, table / ea read, rowhas + selfrank + frontier
-                            + (Fn + n_in + E + 2 * n_out + lists) * 4)    # every list of the layer out
-    out["relabel+finish"] = rel[L - 1]
+        out[f"rows@{l}" if l == 0 else f"rows+relabel+rowside@{l}"] = rows + (tail[l - 1] if l else 0)
+        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5 + (C - F) * 4   # rowinfo + off, pick + atom.min per edge, stream out, rowhas
+        out[f"cand@{l}"] = 2 * C * 5 + C * 4 + (Fn + n_in + E) * 4 + F * P * 4   # stream in (twice), table / ea read, lists + rowscan out
+    out["relabel+rowside+finish"] = tail[L - 1]
     return out
 
 

@@ -167,16 +167,18 @@ int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::ve
   int rc;
   const int L = s->cfg.num_layers;
   if ((rc = mark("start"))) return rc;
+  const bool wide = s->cfg.num_parts > 4;
   for (int l = 0; l < L; l++) {
-    gs_launch_rows(gr.wsv, members, l, s->grid_rows[l], l > 0 ? s->grid_relabel[l - 1] : 0, st);
-    if ((rc = mark(l == 0 ? "rows" : "rows+relabel"))) return rc;
-    gs_launch_expand(gr.wsv, members, s->cfg.rng_mode, l, s->grid_cand[l], st);
+    gs_launch_rows(gr.wsv, members, wide, l, s->grid_rows[l], l > 0 ? s->grid_relabel[l - 1] : 0,
+                   l > 0 ? s->grid_rows[l - 1] : 0, st);
+    if ((rc = mark(l == 0 ? "rows" : "rows+relabel+rowside"))) return rc;
+    gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, l, s->grid_cand[l], st);
     if ((rc = mark("expand"))) return rc;
-    gs_launch_cand(gr.wsv, members, l, s->grid_cand[l], st);
+    gs_launch_cand(gr.wsv, members, wide, l, s->grid_cand[l], st);
     if ((rc = mark("cand"))) return rc;
   }
-  gs_launch_tail(gr.wsv, members, s->grid_relabel[L - 1], s->feat ? s->grid_gather : 0, st);
-  if ((rc = mark(s->feat ? "relabel+gather_features+finish" : "relabel+finish"))) return rc;
+  gs_launch_tail(gr.wsv, members, wide, s->grid_relabel[L - 1], s->grid_rows[L - 1], s->feat ? s->grid_gather : 0, st);
+  if ((rc = mark(s->feat ? "relabel+rowside+gather_features+finish" : "relabel+rowside+finish"))) return rc;
   CU(cudaGetLastError());
   return GS_OK;
 }
@@ -567,6 +569,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.selfrank, s->Fcap);
     DA(w.ea, s->Fcap);
     DA(w.rowhas, s->Fcap);
+    DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
     DA(w.cand, s->Ccap + 4);
     DA(w.cflag, s->Ccap + 4);
     DA(w.tile_first, ctiles + 1);
@@ -576,6 +579,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.rs_val, 2 * (size_t)ftiles * GS_RS_NC);
     DA(w.cs_status, ctiles);
     DA(w.cs_val, 2 * (size_t)ctiles * GS_CS_NC);
+    DA(w.fs_status, ftiles);
+    DA(w.fs_val, 2 * (size_t)ftiles * GS_FS_NC);
     if (s->feat) {
       w.feat = s->feat->rows;
       w.feat_slot = s->feat->slot_of;
@@ -595,6 +600,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaMemset(w.tickets, 0, (size_t)(L + 1) * GS_TICKETS * sizeof(uint32_t)));
     CUS(cudaMemset(w.rs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
     CUS(cudaMemset(w.cs_status, 0, (size_t)ctiles * sizeof(uint32_t)));
+    CUS(cudaMemset(w.fs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
                       cudaHostAllocMapped));

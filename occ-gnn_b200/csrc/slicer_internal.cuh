@@ -30,11 +30,12 @@
 #define GS_CNT_OWN(P, q) (1 + 3 * (P) + (q))
 #define GS_CNT_TO(P, q) (1 + 4 * (P) + (q))
 #define GS_CNT_SELF(P, q) (1 + 5 * (P) + (q))  // rows owned by q (k_rows)
-#define GS_TICKETS 4                      // per layer: [0] k_rows tiles, [1] k_expand done, [2] k_cand tiles
+#define GS_TICKETS 4                      // per layer: [0] k_rows tiles, [1] k_expand done, [2] k_cand runs, [3] rowside tiles
 
 // decoupled look-back descriptors
 #define GS_RS_NC 16   // k_rows scan: candidates, drawing rows, rows per owner (uint64 each; 2 + P used)
-#define GS_CS_NC 48   // k_cand scan: 1 + 5 * 8 = 41 counters (uint32), padded
+#define GS_CS_NC 24   // k_cand scan: 1 + 2 * 8 = 17 counters (uint32), padded
+#define GS_FS_NC 24   // rowside scan: 3 * 8 counters (uint32)
 #define GS_SKIPPED 1000  // header status of a group member that holds no minibatch
 
 // hand-over copy through the bulk-copy engine (cp.async.bulk); A/B with -DGS_PACK_TMA=0
@@ -53,7 +54,7 @@ struct GsInput {
 // last CTA of sample k's k_tail, so no kernel of a sample ever has to reset anything.
 struct GsState {
   uint32_t tag_idx;     // tag index of the current sample; stored tag = ntags - 1 - tag_idx (index 0 = fill pattern)
-  uint32_t scan_epoch;  // scan descriptors of layer l: epoch scan_epoch + 2 l (k_rows), + 2 l + 1 (k_cand)
+  uint32_t scan_epoch;  // scan descriptors of layer l: epoch scan_epoch + 3 l (k_rows), + 1 (k_cand), + 2 (rowside)
   uint32_t pad[2];
 };
 
@@ -93,6 +94,7 @@ struct GsWs {
   uint32_t *selfrank;    // [Fcap]   # earlier rows with the same owner = rank in self_ids_* of that part
   uint32_t *ea;          // [Fcap]   minimum edge-source position of the row's node in this layer (GS_INF: none)
   uint32_t *rowhas;      // [Fcap]   bit q: the row emitted >= 1 edge into part q
+  uint32_t *rowscan;     // [P][Fcap+1] edges of part q emitted before row i (k_cand -> rowside)
   int32_t *cand;         // [Ccap]   candidate stream; after k_cand: in_nodes rank at first-occurrence positions
   uint8_t *cflag;        // [Ccap]
   uint32_t *tile_first;  // [ctiles_cap] row containing candidate t*GS_TILE
@@ -102,6 +104,8 @@ struct GsWs {
   unsigned long long *rs_val;  // [2][ftiles_cap][GS_RS_NC]  aggregates, inclusive prefixes
   uint32_t *cs_status;   // [ctiles_cap]
   uint32_t *cs_val;      // [2][ctiles_cap][GS_CS_NC]
+  uint32_t *fs_status;   // [ftiles_cap]
+  uint32_t *fs_val;      // [2][ftiles_cap][GS_FS_NC]
   int32_t Fcap, Ccap, ftiles_cap, ctiles_cap;
   // fused input-feature gather (optional)
   const float *feat;     // [rows][feat_dim] fp32 (cached store: the cached rows)
@@ -135,10 +139,13 @@ struct GsGrids {
   int rows, cand, relabel;  // CTAs of the three roles for one layer (static upper bounds)
 };
 void gs_kernels_prepare();  // once per device, before the first launch / graph capture
-void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, int grid_relabel, cudaStream_t st);
-void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int grid, cudaStream_t st);
-void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st);
-void gs_launch_tail(const GsWs *wsv, int members, int grid_relabel, int grid_gather, cudaStream_t st);
+// wide: more than 4 parts (64-bit packed per-part counters)
+void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid_rows, int grid_relabel,
+                    int grid_rowside, cudaStream_t st);
+void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, int layer, int grid, cudaStream_t st);
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st);
+void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
+                    cudaStream_t st);
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,
                           cudaStream_t st);

@@ -29,6 +29,8 @@
 // tickets, so a whole minibatch -- or a group of them, blockIdx.y -- is one
 // static CUDA graph of 3 L + 1 launches with no host round trip.  Integer / byte
 // work, HBM- and latency-bound: no tensor cores (nothing here is a contraction).
+#include <type_traits>
+
 #include "slicer_device.cuh"
 
 // Resident CTAs per SM the tiled kernels are compiled for (register caps 65536 /
@@ -315,7 +317,7 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   }
   const int fan = ws.fanouts[layer];
   const GsState stt = *ws.state;
-  const uint32_t ep = stt.scan_epoch + 2u * (uint32_t)layer;
+  const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer;
   const Tag tag(ws, stt);
   const Tbl tbl(ws);
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
@@ -456,6 +458,18 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   }
 }
 
+// Packed per-part counters: one byte per part in a 32-bit word (P <= 4) or a 64-bit word.
+template <typename PK> __device__ __forceinline__ PK pkt_one(int g) { return (PK)1 << (8 * g); }
+template <typename PK> __device__ __forceinline__ uint32_t pkt_get(PK v, int g) { return (uint32_t)(v >> (8 * g)) & 0xFFu; }
+__device__ __forceinline__ uint32_t pkt_redux(uint32_t v) { return __reduce_add_sync(FULL, v); }
+__device__ __forceinline__ unsigned long long pkt_redux(unsigned long long v) { return pk_redux(v); }
+__device__ __forceinline__ uint32_t pkt_incl(uint32_t v) { return warp_incl_scan(v); }
+__device__ __forceinline__ unsigned long long pkt_incl(unsigned long long v) { return pk_warp_incl(v); }
+__device__ __forceinline__ uint32_t pkt_spread(uint32_t mask, uint32_t) {  // bit q of mask -> byte q (q < 4)
+  return ((mask & 0xFu) * 0x00204081u) & 0x01010101u;
+}
+__device__ __forceinline__ unsigned long long pkt_spread(uint32_t mask, unsigned long long) { return pk_spread(mask); }
+
 // ----------------------------------------------------------------- k_expand
 // Lays out every list of the layer.  Runs in the last CTA of k_expand: by then
 // the per-layer totals are exact (see expand_role), so k_cand writes each list
@@ -518,7 +532,7 @@ __device__ void layer_alloc(const GsWs &ws, int layer, const uint32_t *cnt /* sh
 // these are ALL the list lengths of the layer, exact, before k_cand starts.
 // RNG (gs_rng_mode) is a template parameter: the pick path of the other two
 // modes costs instructions in a kernel bound by issue.
-template <int RNG>
+template <int RNG, typename PK>
 __device__ void expand_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -650,7 +664,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
     }
     int32_t cvv[GS_IPT];
     uint32_t cf[GS_IPT];
-    unsigned long long pk_in = 0ull, pk_e = 0ull, pk_out = 0ull, pk_own = 0ull, pk_to = 0ull;
+    PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
     uint32_t n_new = 0u;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
@@ -663,13 +677,13 @@ __device__ void expand_role(const GsWs &ws, int layer) {
       } else {
         cvv[k] = v[k];
         cf[k] = GS_CK_EDGE | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
-        pk_e += pk_one(g[k]);
+        pk_e += pkt_one<PK>(g[k]);
         if (!tag.mine(old[k])) {  // first arrival for a node that is new to the frontier
           n_new++;
-          pk_in += pk_one(g[k]);
+          pk_in += pkt_one<PK>(g[k]);
         } else if (!(old[k] & tag.kind)) {  // a row of the current frontier
           const uint32_t idx = old[k] & tag.pmask;
-          if (atomicMin(ws.ea + idx, p0 + k) == GS_INF) pk_in += pk_one(g[k]);
+          if (atomicMin(ws.ea + idx, p0 + k) == GS_INF) pk_in += pkt_one<PK>(g[k]);
           cvv[k] = (int32_t)idx;
           cf[k] = GS_CK_FHIT | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
         }
@@ -682,9 +696,9 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         if (nb) {
           const int g0 = owner_of(ws, nd1[k]);
           const uint32_t own = 1u << g0;
-          pk_out += pk_spread(nb);
-          if (nb & own) pk_own += pk_one(g0);
-          if ((nb & ~own) && !(was[k] & ~own)) pk_to += pk_one(g0);
+          pk_out += pkt_spread(nb, (PK)0);
+          if (nb & own) pk_own += pkt_one<PK>(g0);
+          if ((nb & ~own) && !(was[k] & ~own)) pk_to += pkt_one<PK>(g0);
         }
       }
     if (p0 + GS_IPT <= C) {
@@ -700,19 +714,19 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         }
     }
     // per-tile totals: a lane adds at most GS_IPT to a byte, a warp at most 128
-    pk_in = pk_redux(pk_in);
-    pk_e = pk_redux(pk_e);
-    pk_out = pk_redux(pk_out);
-    pk_own = pk_redux(pk_own);
-    pk_to = pk_redux(pk_to);
+    pk_in = pkt_redux(pk_in);
+    pk_e = pkt_redux(pk_e);
+    pk_out = pkt_redux(pk_out);
+    pk_own = pkt_redux(pk_own);
+    pk_to = pkt_redux(pk_to);
     n_new = __reduce_add_sync(FULL, n_new);
     if (lane < P) {
       uint32_t x;
-      if ((x = pk_get(pk_in, lane))) atomicAdd(&s_cnt[GS_CNT_IN(P, lane)], x);
-      if ((x = pk_get(pk_e, lane))) atomicAdd(&s_cnt[GS_CNT_E(P, lane)], x);
-      if ((x = pk_get(pk_out, lane))) atomicAdd(&s_cnt[GS_CNT_OUT(P, lane)], x);
-      if ((x = pk_get(pk_own, lane))) atomicAdd(&s_cnt[GS_CNT_OWN(P, lane)], x);
-      if ((x = pk_get(pk_to, lane))) atomicAdd(&s_cnt[GS_CNT_TO(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_in, lane))) atomicAdd(&s_cnt[GS_CNT_IN(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_e, lane))) atomicAdd(&s_cnt[GS_CNT_E(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_out, lane))) atomicAdd(&s_cnt[GS_CNT_OUT(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_own, lane))) atomicAdd(&s_cnt[GS_CNT_OWN(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_to, lane))) atomicAdd(&s_cnt[GS_CNT_TO(P, lane)], x);
     }
     if (lane == 31 && n_new) atomicAdd(&s_cnt[GS_CNT_NEW], n_new);
     __syncthreads();
@@ -732,70 +746,79 @@ __device__ void expand_role(const GsWs &ws, int layer) {
 //   edge of frontier ROW idx:    first edge occurrence iff ea[idx] == p -> in_nodes; it is the node's
 //                                frontier slot only if it precedes the row's self entry (p < off[idx]);
 //   self entry of row i at s:    frontier slot iff no edge of the node came earlier (ea[i] > s); it also
-//                                closes the ROW side: has = rowhas[i] says which parts the row has
-//                                edges in: out_g (bipartite.h:59-62), owned_g (:56-58), to_g0
-//                                (slicer.cpp:41), self_g0 (slicer.cpp:33-34), from_g = out_g minus
-//                                owned_g, csr_indptr = edges of part g before s.
-// Ranks = exclusive prefix over positions of 1 + 5 P counters: per-thread packed
-// counts (one byte per part), one packed warp scan per kind, cross-warp bases in
-// shared memory, tile prefix by decoupled look-back.  A first occurrence records
-// its in_nodes rank at its own position in the (now dead) candidate word: that is
-// the relabel map (DuplicateRemover::mask, duplicate.cpp:21) indexed by position,
-// which relabel_role reads for every later occurrence.
+//                                samples the running per-part edge counts (rowscan: the row's CSR row
+//                                pointer in every part) for rowside_role.
+// Ranks = exclusive prefix over positions of 1 + 2 P counters (next-frontier
+// firsts, in_nodes firsts and edges per part): per-thread packed counts (one byte
+// per part), one packed warp scan per kind.  A first occurrence records its
+// in_nodes rank at its own position in the (now dead) candidate word: that is the
+// relabel map (DuplicateRemover::mask, duplicate.cpp:21) indexed by position,
+// which relabel_role and rowside_role read for every later occurrence.
+//
+// A CTA takes a RUN of up to CS_RMAX consecutive tiles (ticket order) and goes
+// over it twice.  Sweep 1 reads the stream, does the random reads (table / ea /
+// off), classifies every candidate and keeps what the random reads returned in
+// shared memory; its per-(tile, warp) class totals, scanned in place, are the
+// run's aggregate.  ONE flat look-back per run turns that into the run's
+// exclusive prefix.  Sweep 2 replays the run from shared memory: packed warp
+// scans give every item its rank, the lists are written at their final place.
+// Each candidate is read from the stream twice (the second time out of L1/L2)
+// and looked up in the table once.
 #define CS_NF 0
 #define CS_IN(q) (1 + (q))
 #define CS_E(q) (9 + (q))
-#define CS_OUT(q) (17 + (q))
-#define CS_OWN(q) (25 + (q))
-#define CS_TO(q) (33 + (q))
-#define CS_USED 41
-#define CS_PAD GS_CS_NC  // descriptor / shared-memory row length
-#define CS_RMAX 8      // tiles of one run (held in shared memory between the two sweeps)
+#define CS_USED 17
+#define CS_RMAX 8           // tiles of one run (held in shared memory between the two sweeps)
+#define CS_BEFORE 0x80000000u  // frontier-row edge: it precedes the row's self entry (positions are < 2^30)
 
-// A CTA takes a RUN of up to CS_RMAX consecutive tiles (ticket order) and goes
-// over it twice.  Sweep 1 reads the stream, does the random reads (table / ea /
-// rowhas / off), classifies every candidate and keeps what the random reads
-// returned in shared memory; its per-(tile, warp) class totals, scanned in
-// place, are the run's aggregate.  ONE flat look-back per run turns that into
-// the run's exclusive prefix.  Sweep 2 replays the run from shared memory: packed
-// warp scans give every item its rank, the lists are written at their final place.
-// Each candidate is read from the stream twice (the second time out of L1/L2) and
-// looked up in the table once.
 struct CandSmem {
-  uint32_t x[CS_RMAX][GS_TILE];       // minimum position: of an edge's source / of a self entry's node as a source
-  uint8_t y[CS_RMAX][GS_TILE];        // self entry: rowhas; frontier-row edge: 1 = it precedes the row's self entry
-  uint16_t wt[CS_RMAX][GS_NW][CS_PAD];  // class totals per (tile, warp) -> exclusive prefix inside the run
-  uint32_t red[GS_NW][CS_PAD];
-  uint32_t agg[CS_PAD], pre[CS_PAD];
-  int32_t fo[GS_MAX_PARTS][GS_NUM_FIELDS];
+  uint32_t x[CS_RMAX][GS_TILE];            // minimum position: of an edge's source / of a self entry's node as a source
+  uint16_t wt[CS_RMAX][GS_NW][GS_CS_NC];   // class totals per (tile, warp) -> exclusive prefix inside the run
+  uint32_t red[GS_NW][GS_CS_NC];
+  uint32_t agg[GS_CS_NC], pre[GS_CS_NC];
+  int32_t fo_in[GS_MAX_PARTS], fo_ix[GS_MAX_PARTS];
   int run;
 };
 
-// classes of one item; bit 8: in_nodes first, bit 9: frontier first, bit 10: self entry whose node is never a source
-__device__ __forceinline__ uint32_t cand_class(uint32_t fl, uint32_t p, uint32_t x, uint32_t y,
-                                               unsigned long long &pi, unsigned long long &pe,
-                                               unsigned long long &po, unsigned long long &pw,
-                                               unsigned long long &pt, uint32_t &nf) {
+// class of one candidate; bit 8: in_nodes first, bit 9: frontier first
+template <typename PK>
+__device__ __forceinline__ uint32_t cand_class(uint32_t fl, uint32_t p, uint32_t x, PK &pi, PK &pe, uint32_t &nf) {
   const uint32_t kind = fl & GS_CK_MASK;
   const int g = (int)((fl >> GS_CF_PART_SHIFT) & 7u);
   if (kind == GS_CK_SELF) {
-    const uint32_t own = 1u << g;
     if (x > p) { fl |= 0x200u; nf++; }
-    if (x == GS_INF) fl |= 0x400u;
-    po += pk_spread(y);
-    if (y & own) pw += pk_one(g);
-    if (y & ~own) pt += pk_one(g);
   } else if (kind != GS_CK_DEAD) {
-    pe += pk_one(g);
-    if (x == p) {
+    pe += pkt_one<PK>(g);
+    if ((x & ~CS_BEFORE) == p) {
       fl |= 0x100u;
-      pi += pk_one(g);
-      if (kind == GS_CK_EDGE || y) { fl |= 0x200u; nf++; }
+      pi += pkt_one<PK>(g);
+      if (kind == GS_CK_EDGE || (x & CS_BEFORE)) { fl |= 0x200u; nf++; }
     }
   }
   return fl;
 }
 
+__device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t C, uint32_t (&fl)[GS_IPT],
+                                          int32_t (&ci)[GS_IPT]) {
+  if (p0 + GS_IPT <= C) {
+    const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+    const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
+    ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
+    fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < GS_IPT; i++) {
+      fl[i] = GS_CK_DEAD;
+      ci[i] = 0;
+      if (p0 + i < C) {
+        fl[i] = ws.cflag[p0 + i];
+        ci[i] = ws.cand[p0 + i];
+      }
+    }
+  }
+}
+
+template <typename PK>
 __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
@@ -809,14 +832,16 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
   const GsState stt = *ws.state;
-  const uint32_t ep = stt.scan_epoch + 2u * (uint32_t)layer + 1u;
+  const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 1u;
   const Tag tag(ws, stt);
   uint32_t *cs_agg = ws.cs_val, *cs_inc = ws.cs_val + (size_t)ws.ctiles_cap * GS_CS_NC;
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
   const int lane = lane_id(), w = warp_id();
-  if (threadIdx.x < P * GS_NUM_FIELDS)
-    sm.fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
-        h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
+  const size_t rs_stride = (size_t)ws.Fcap + 1;
+  if (threadIdx.x < P) {
+    sm.fo_in[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
+    sm.fo_ix[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
+  }
   for (;;) {
     __syncthreads();  // the previous run's shared memory is no longer read
     if (threadIdx.x == 0) sm.run = (int)atomicAdd(tick, 1u);
@@ -827,60 +852,40 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
     // ---- sweep 1: random reads, classes, totals
     for (int k = 0; k < nt; k++) {
       const uint32_t p0 = (uint32_t)(t_lo + k) * GS_TILE + GS_IPT * threadIdx.x;
-      const bool full = p0 + GS_IPT <= C;
       uint32_t fl[GS_IPT];
       int32_t ci[GS_IPT];
-      if (full) {
-        const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
-        const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
-        ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
-        fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
-      } else {
-#pragma unroll
-        for (int i = 0; i < GS_IPT; i++) {
-          fl[i] = GS_CK_DEAD;
-          ci[i] = 0;
-          if (p0 + i < C) {
-            fl[i] = ws.cflag[p0 + i];
-            ci[i] = ws.cand[p0 + i];
-          }
-        }
-      }
-      uint32_t x[GS_IPT], y[GS_IPT];
+      cand_load(ws, p0, C, fl, ci);
+      uint32_t x[GS_IPT], s[GS_IPT];
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++) {
         const uint32_t kind = fl[i] & GS_CK_MASK;
-        x[i] = GS_INF; y[i] = 0u;
+        x[i] = GS_INF; s[i] = 0u;
         if (kind == GS_CK_EDGE) {
           x[i] = tbl.ld(ci[i]) & tag.pmask;
         } else if (kind != GS_CK_DEAD) {
           x[i] = __ldcg(ws.ea + ci[i]);
-          y[i] = kind == GS_CK_SELF ? __ldcg(ws.rowhas + ci[i]) : __ldcg(ws.off + ci[i]);
+          if (kind == GS_CK_FHIT) s[i] = __ldcg(ws.off + ci[i]);
         }
       }
-      unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
+      PK pi = 0, pe = 0;
       uint32_t nf = 0u;
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++) {
-        if ((fl[i] & GS_CK_MASK) == GS_CK_FHIT) y[i] = (p0 + i) < y[i] ? 1u : 0u;
-        cand_class(fl[i], p0 + i, x[i], y[i], pi, pe, po, pw, pt, nf);
+        if ((fl[i] & GS_CK_MASK) == GS_CK_FHIT && (p0 + i) < s[i]) x[i] |= CS_BEFORE;
+        cand_class<PK>(fl[i], p0 + i, x[i], pi, pe, nf);
       }
       *reinterpret_cast<uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]) = make_uint4(x[0], x[1], x[2], x[3]);
-      *reinterpret_cast<uchar4 *>(&sm.y[k][GS_IPT * threadIdx.x]) =
-          make_uchar4((unsigned char)y[0], (unsigned char)y[1], (unsigned char)y[2], (unsigned char)y[3]);
-      pi = pk_redux(pi); pe = pk_redux(pe); po = pk_redux(po); pw = pk_redux(pw); pt = pk_redux(pt);
+      pi = pkt_redux(pi);
+      pe = pkt_redux(pe);
       nf = __reduce_add_sync(FULL, nf);
       if (lane < 8) {
-        sm.wt[k][w][CS_IN(lane)] = (uint16_t)pk_get(pi, lane);
-        sm.wt[k][w][CS_E(lane)] = (uint16_t)pk_get(pe, lane);
-        sm.wt[k][w][CS_OUT(lane)] = (uint16_t)pk_get(po, lane);
-        sm.wt[k][w][CS_OWN(lane)] = (uint16_t)pk_get(pw, lane);
-        sm.wt[k][w][CS_TO(lane)] = (uint16_t)pk_get(pt, lane);
+        sm.wt[k][w][CS_IN(lane)] = (uint16_t)(lane < (int)sizeof(PK) ? pkt_get<PK>(pi, lane) : 0u);
+        sm.wt[k][w][CS_E(lane)] = (uint16_t)(lane < (int)sizeof(PK) ? pkt_get<PK>(pe, lane) : 0u);
       }
       if (lane == 8) sm.wt[k][w][CS_NF] = (uint16_t)nf;
     }
     __syncthreads();
-    if (threadIdx.x < CS_PAD) {  // totals -> exclusive prefix over the run's (tile, warp) sequence
+    if (threadIdx.x < GS_CS_NC) {  // totals -> exclusive prefix over the run's (tile, warp) sequence
       uint32_t run = 0u;
       if (threadIdx.x < CS_USED)
         for (int k = 0; k < nt; k++)
@@ -900,96 +905,55 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
       const bool full = p0 + GS_IPT <= C;
       uint32_t fl[GS_IPT];
       int32_t ci[GS_IPT];
-      if (full) {
-        const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
-        const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
-        ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
-        fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
-      } else {
-#pragma unroll
-        for (int i = 0; i < GS_IPT; i++) {
-          fl[i] = GS_CK_DEAD;
-          ci[i] = 0;
-          if (p0 + i < C) {
-            fl[i] = ws.cflag[p0 + i];
-            ci[i] = ws.cand[p0 + i];
-          }
-        }
-      }
+      cand_load(ws, p0, C, fl, ci);
       const uint4 x4 = *reinterpret_cast<const uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]);
-      const uchar4 y4 = *reinterpret_cast<const uchar4 *>(&sm.y[k][GS_IPT * threadIdx.x]);
       const uint32_t x[GS_IPT] = {x4.x, x4.y, x4.z, x4.w};
-      const uint32_t y[GS_IPT] = {y4.x, y4.y, y4.z, y4.w};
-      unsigned long long pi = 0ull, pe = 0ull, po = 0ull, pw = 0ull, pt = 0ull;
+      PK pi = 0, pe = 0;
       uint32_t nf = 0u;
 #pragma unroll
-      for (int i = 0; i < GS_IPT; i++) fl[i] = cand_class(fl[i], p0 + i, x[i], y[i], pi, pe, po, pw, pt, nf);
-      // the node id of self entries and of first occurrences among frontier-row edges
+      for (int i = 0; i < GS_IPT; i++) fl[i] = cand_class<PK>(fl[i], p0 + i, x[i], pi, pe, nf);
+      // the node id of whatever enters a list: self entries that are frontier firsts,
+      // first occurrences among frontier-row edges (new nodes carry their id already)
       int32_t z[GS_IPT];
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++) {
         const uint32_t kind = fl[i] & GS_CK_MASK;
         z[i] = ci[i];
-        if (kind == GS_CK_SELF || (kind == GS_CK_FHIT && (fl[i] & 0x100u))) z[i] = front[ci[i]];
+        if ((kind == GS_CK_SELF && (fl[i] & 0x200u)) || (kind == GS_CK_FHIT && (fl[i] & 0x100u))) z[i] = front[ci[i]];
       }
-      // exclusive packed prefixes over the warp's lanes
-      const unsigned long long inc_i = pk_warp_incl(pi), inc_e = pk_warp_incl(pe), inc_o = pk_warp_incl(po),
-                               inc_w = pk_warp_incl(pw), inc_t = pk_warp_incl(pt);
+      const PK inc_i = pkt_incl(pi), inc_e = pkt_incl(pe);
       const uint32_t inc_f = warp_incl_scan(nf);
       const uint16_t *wtb = sm.wt[k][w];
 #define CS_B(c) (sm.pre[c] + (uint32_t)wtb[c])
       uint32_t rf = CS_B(CS_NF) + inc_f - nf;
-      unsigned long long ri = inc_i - pi, re = inc_e - pe, ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
+      PK ri = inc_i - pi, re = inc_e - pe;
       bool wrote = false;
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++) {
         const uint32_t kind = fl[i] & GS_CK_MASK;
         const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
         if (kind == GS_CK_SELF) {
-          const int32_t nd = z[i];
-          const uint32_t has = y[i], own = 1u << g;
-          if (fl[i] & 0x200u) fnext[rf++] = nd;
-          int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
-          for (uint32_t hb = has; hb; hb &= hb - 1u) {
-            const int q = __ffs((int)hb) - 1;
-            const uint32_t op = CS_B(CS_OUT(q)) + pk_get(ro, q);
-            const uint32_t ow = CS_B(CS_OWN(q)) + pk_get(rw, q);
-            ws.slab[sm.fo[q][GS_F_OUT_NODES] + op] = nd;
-            ws.slab[sm.fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)(CS_B(CS_E(q)) + pk_get(re, q));
-            if (q == g) {
-              ws.slab[sm.fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
-              op_own = (int32_t)op;
-            } else {
-              ws.slab[sm.fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
-            }
-          }
-          if (has & ~own) {
-            ws.slab[sm.fo[g][GS_F_TO_IDS] + CS_B(CS_TO(g)) + pk_get(rt, g)] = op_own;
-            rt += pk_one(g);
-          }
-          const uint32_t sr = ws.selfrank[ci[i]];
-          ws.slab[sm.fo[g][GS_F_SELF_OUT] + sr] = op_own;
-          if (fl[i] & 0x400u) ws.slab[sm.fo[g][GS_F_SELF_IN] + sr] = -1;  // else: written by the node's first edge
-          ro += pk_spread(has);
-          if (has & own) rw += pk_one(g);
+          if (fl[i] & 0x200u) fnext[rf++] = z[i];
+          // edges of every part emitted before this row: its CSR row pointers
+          uint32_t *rsp = ws.rowscan + ci[i];
+          for (int q = 0; q < P; q++, rsp += rs_stride) *rsp = CS_B(CS_E(q)) + pkt_get<PK>(re, q);
         } else if (kind != GS_CK_DEAD) {
-          const uint32_t ex = CS_B(CS_E(g)) + pk_get(re, g);
+          const uint32_t ex = CS_B(CS_E(g)) + pkt_get<PK>(re, g);
           if (fl[i] & 0x100u) {
             // the first edge occurrence of a source knows its rank: final csr_indices
             // value, in_nodes entry, relabel map entry; every other edge leaves ~m
             // (m = position of that first occurrence) for relabel_role
-            const uint32_t rk = CS_B(CS_IN(g)) + pk_get(ri, g);
-            ws.slab[sm.fo[g][GS_F_IN_NODES] + rk] = z[i];
-            ws.slab[sm.fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)rk;
-            if (kind == GS_CK_FHIT) ws.slab[sm.fo[g][GS_F_SELF_IN] + ws.selfrank[ci[i]]] = (int32_t)rk;
+            const uint32_t rk = CS_B(CS_IN(g)) + pkt_get<PK>(ri, g);
+            ws.slab[sm.fo_in[g] + rk] = z[i];
+            ws.slab[sm.fo_ix[g] + ex] = (int32_t)rk;
             if (fl[i] & 0x200u) fnext[rf++] = z[i];
             ci[i] = (int32_t)rk;
             wrote = true;
-            ri += pk_one(g);
+            ri += pkt_one<PK>(g);
           } else {
-            ws.slab[sm.fo[g][GS_F_CSR_INDICES] + ex] = (int32_t)~x[i];
+            ws.slab[sm.fo_ix[g] + ex] = (int32_t)~(x[i] & ~CS_BEFORE);
           }
-          re += pk_one(g);
+          re += pkt_one<PK>(g);
         }
       }
 #undef CS_B
@@ -1003,6 +967,149 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
         }
       }
     }
+  }
+}
+
+// ------------------------------------------------------------------ rowside
+// Row-side lists of layer `layer`, one dense pass over the frontier rows in the
+// launch after k_cand.  Row i (node nd, owner g0) with has_g = "emitted >= 1 edge
+// into part g" (rowhas, k_expand):  out_g = has_g (bipartite.h:59-62); owned_g =
+// has_g && g == g0 (bipartite.h:56-58); from_g = has_g && g != g0, rank = rank(out_g)
+// - rank(owned_g); to_g0 = any has_h, h != g0 (slicer.cpp:41); self_g0 = always
+// (slicer.cpp:33-34), slot = selfrank (k_rows); csr_indptr_g = rowscan (k_cand);
+// self_ids_in = in_nodes rank of the node's first edge occurrence (the relabel map
+// at position ea[i]) or -1.  3 P counters, flat look-back per tile of rows.
+#define FS_OUT(q) (q)
+#define FS_OWN(q) (8 + (q))
+#define FS_TO(q) (16 + (q))
+#define FS_USED 24
+template <typename PK>
+__device__ void rowside_role(const GsWs &ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  __shared__ uint32_t s_wc[GS_NW][GS_FS_NC];
+  __shared__ uint32_t s_base[GS_NW][GS_FS_NC];
+  __shared__ uint32_t s_agg[GS_FS_NC], s_pre[GS_FS_NC];
+  __shared__ uint32_t s_red[GS_NW][GS_FS_NC];
+  __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
+  __shared__ int s_tile;
+  if (h->status != 0) return;
+  const int P = ws.P;
+  const int F = h->frontier_len[layer];
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  if (ntiles == 0) return;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
+  const GsState stt = *ws.state;
+  const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 2u;
+  uint32_t *fs_agg = ws.fs_val, *fs_inc = ws.fs_val + (size_t)ws.ftiles_cap * GS_FS_NC;
+  uint32_t *tick = ws.tickets + layer * GS_TICKETS + 3;
+  const int lane = lane_id(), w = warp_id();
+  const size_t rs_stride = (size_t)ws.Fcap + 1;
+  if (threadIdx.x < P * GS_NUM_FIELDS)
+    s_fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
+        h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);
+  __syncthreads();
+  int t = s_tile;
+  while (t < ntiles) {
+    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u}, a[GS_IPT], sr[GS_IPT];
+    int32_t nd[GS_IPT] = {0, 0, 0, 0};
+    int g0[GS_IPT];
+    if (i0 + GS_IPT <= F) {
+      const uint4 h4 = *reinterpret_cast<const uint4 *>(ws.rowhas + i0);
+      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
+      const uint4 a4 = *reinterpret_cast<const uint4 *>(ws.ea + i0);
+      const uint4 s4 = *reinterpret_cast<const uint4 *>(ws.selfrank + i0);
+      has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
+      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
+      a[0] = a4.x; a[1] = a4.y; a[2] = a4.z; a[3] = a4.w;
+      sr[0] = s4.x; sr[1] = s4.y; sr[2] = s4.z; sr[3] = s4.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        a[k] = GS_INF; sr[k] = 0u;
+        if (i0 + k < F) {
+          has[k] = ws.rowhas[i0 + k];
+          nd[k] = front[i0 + k];
+          a[k] = ws.ea[i0 + k];
+          sr[k] = ws.selfrank[i0 + k];
+        }
+      }
+    }
+    // self_ids_in: the relabel map at the position of the node's first edge occurrence
+    int32_t sin[GS_IPT];
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) sin[k] = a[k] == GS_INF ? -1 : __ldcg(ws.cand + a[k]);
+    PK po = 0, pw = 0, pt = 0;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      g0[k] = -1;
+      if (i0 + k < F) {
+        g0[k] = owner_of(ws, nd[k]);
+        const uint32_t own = 1u << g0[k];
+        po += pkt_spread(has[k], (PK)0);
+        if (has[k] & own) pw += pkt_one<PK>(g0[k]);
+        if (has[k] & ~own) pt += pkt_one<PK>(g0[k]);
+      }
+    }
+    const PK inc_o = pkt_incl(po), inc_w = pkt_incl(pw), inc_t = pkt_incl(pt);
+    {
+      const PK t_o = __shfl_sync(FULL, inc_o, 31), t_w = __shfl_sync(FULL, inc_w, 31), t_t = __shfl_sync(FULL, inc_t, 31);
+      if (lane < 8) {
+        const bool in = lane < (int)sizeof(PK);
+        s_wc[w][FS_OUT(lane)] = in ? pkt_get<PK>(t_o, lane) : 0u;
+        s_wc[w][FS_OWN(lane)] = in ? pkt_get<PK>(t_w, lane) : 0u;
+        s_wc[w][FS_TO(lane)] = in ? pkt_get<PK>(t_t, lane) : 0u;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);  // next tile of this CTA (read after the barriers below)
+    if (threadIdx.x < FS_USED) {
+      uint32_t run = 0u;
+#pragma unroll
+      for (int k = 0; k < GS_NW; k++) {
+        s_base[k][threadIdx.x] = run;
+        run += s_wc[k][threadIdx.x];
+      }
+      s_agg[threadIdx.x] = run;
+    }
+    __syncthreads();
+    flat_lookback<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, fs_inc, t, ep, s_agg, s_pre, s_red);
+#define FS_B(c) (s_pre[c] + s_base[w][c])
+    PK ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      const int i = i0 + k;
+      if (i < F) {
+        const int gq = g0[k];
+        const uint32_t own = 1u << gq;
+        int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+        for (uint32_t hb = has[k]; hb; hb &= hb - 1u) {
+          const int q = __ffs((int)hb) - 1;
+          const uint32_t op = FS_B(FS_OUT(q)) + pkt_get<PK>(ro, q);
+          const uint32_t ow = FS_B(FS_OWN(q)) + pkt_get<PK>(rw, q);
+          ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd[k];
+          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)q * rs_stride + i];
+          if (q == gq) {
+            ws.slab[s_fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+            op_own = (int32_t)op;
+          } else {
+            ws.slab[s_fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+          }
+        }
+        if (has[k] & ~own) {
+          ws.slab[s_fo[gq][GS_F_TO_IDS] + FS_B(FS_TO(gq)) + pkt_get<PK>(rt, gq)] = op_own;
+          rt += pkt_one<PK>(gq);
+        }
+        ws.slab[s_fo[gq][GS_F_SELF_IN] + sr[k]] = sin[k];
+        ws.slab[s_fo[gq][GS_F_SELF_OUT] + sr[k]] = op_own;
+        ro += pkt_spread(has[k], (PK)0);
+        if (has[k] & own) rw += pkt_one<PK>(gq);
+      }
+    }
+#undef FS_B
+    __syncthreads();
+    t = s_tile;
   }
 }
 
@@ -1079,49 +1186,60 @@ __device__ void gather_role(const GsWs &ws, int bx, int nb) {
 }
 
 // ------------------------------------------------------------------ kernels
-template <bool FIRST>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows) {
+// WIDE: more than 4 parts -> packed per-part counters are 64-bit words (else 32-bit).
+template <bool FIRST, bool WIDE>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows,
+                                                                int grid_relabel) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
-  if ((int)blockIdx.x < grid_rows) rows_role<FIRST>(ws, layer);
-  else if (!FIRST) relabel_role(ws, layer - 1, (int)blockIdx.x - grid_rows, (int)gridDim.x - grid_rows);
+  const int bx = (int)blockIdx.x;
+  if (bx < grid_rows) rows_role<FIRST>(ws, layer);
+  else if (FIRST) return;
+  else if (bx < grid_rows + grid_relabel) relabel_role(ws, layer - 1, bx - grid_rows, grid_relabel);
+  else rowside_role<PK>(ws, layer - 1);
 }
 
-template <int RNG>
+template <int RNG, bool WIDE>
 __global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand(const GsWs *__restrict__ wsv, int layer) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
-  expand_role<RNG>(ws, layer);
+  expand_role<RNG, PK>(ws, layer);
 }
 
+template <bool WIDE>
 __global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand(const GsWs *__restrict__ wsv, int layer) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
-  extern __shared__ __align__(16) unsigned char s_dyn[];
+  __shared__ CandSmem sm;
   stage_ws(ws, wsv + blockIdx.y);
-  cand_role(ws, layer, *reinterpret_cast<CandSmem *>(s_dyn));
+  cand_role<PK>(ws, layer, sm);
 }
 
-// Last launch of a sample: relabel of the last layer, the fused feature gather,
-// and the slot's housekeeping -- every CTA takes its share of the rare dense
-// refills (dedup table out of tags: 1 sample in 2^(31-S) - 1; scan descriptors:
-// once per 2^30 scans), the last CTA to finish closes the header, mirrors it to
-// pinned host memory and prepares the slot's state for the next sample.
-__global__ void GS_BOUNDS k_tail(const GsWs *__restrict__ wsv, int grid_relabel, int grid_gather) {
+// Last launch of a sample: relabel and row side of the last layer, the fused
+// feature gather, and the slot's housekeeping -- every CTA takes its share of the
+// rare dense refills (dedup table out of tags: 1 sample in 2^(31-S) - 1; scan
+// descriptors: once per 2^30 scans), the last CTA to finish closes the header,
+// mirrors it to pinned host memory and prepares the slot's state for the next sample.
+template <bool WIDE>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_tail(const GsWs *__restrict__ wsv, int grid_relabel, int grid_rowside, int grid_gather) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
   gs_sample_header *h = ws.hdr;
   const int st = h->status;
-  if (st == GS_SKIPPED) return;
   const int L = ws.L, P = ws.P;
   const int bx = (int)blockIdx.x;
   if (st == 0) {
     if (bx < grid_relabel) relabel_role(ws, L - 1, bx, grid_relabel);
-    else if (ws.feat && bx < grid_relabel + grid_gather) gather_role(ws, bx - grid_relabel, grid_gather);
+    else if (bx < grid_relabel + grid_rowside) rowside_role<PK>(ws, L - 1);
+    else if (ws.feat) gather_role(ws, bx - grid_relabel - grid_rowside, grid_gather);
   }
   const GsState stt = *ws.state;
   const uint32_t ntags = 1u << (31 - ws.pos_bits);
   const bool refill = stt.tag_idx + 1u > ntags - 1u;  // the next sample would have no tag left
-  const bool rescan = stt.scan_epoch + 4u * (uint32_t)L >= (1u << 30);
+  const bool rescan = stt.scan_epoch + 6u * (uint32_t)L >= (1u << 30);
   const int64_t tid = (int64_t)bx * GS_TPB + threadIdx.x, nth = (int64_t)gridDim.x * GS_TPB;
   if (refill) {
     uint4 *t4 = (uint4 *)ws.table;
@@ -1131,7 +1249,10 @@ __global__ void GS_BOUNDS k_tail(const GsWs *__restrict__ wsv, int grid_relabel,
     if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
   }
   if (rescan) {
-    for (int64_t i = tid; i < ws.ftiles_cap; i += nth) ws.rs_status[i] = 0u;
+    for (int64_t i = tid; i < ws.ftiles_cap; i += nth) {
+      ws.rs_status[i] = 0u;
+      ws.fs_status[i] = 0u;
+    }
     for (int64_t i = tid; i < ws.ctiles_cap; i += nth) ws.cs_status[i] = 0u;
   }
   if (!last_block(ws.tickets + L * GS_TICKETS)) return;
@@ -1150,7 +1271,7 @@ __global__ void GS_BOUNDS k_tail(const GsWs *__restrict__ wsv, int grid_relabel,
     }
     GsState nx;
     nx.tag_idx = refill ? 1u : stt.tag_idx + 1u;
-    nx.scan_epoch = rescan ? 1u : stt.scan_epoch + 2u * (uint32_t)L;
+    nx.scan_epoch = rescan ? 1u : stt.scan_epoch + 3u * (uint32_t)L;
     nx.pad[0] = nx.pad[1] = 0u;
     *ws.state = nx;
   }
@@ -1340,24 +1461,37 @@ __global__ void __launch_bounds__(256) k_sector_probe(const uint32_t *__restrict
 }  // namespace
 
 // ---------------------------------------------------------------- launchers
-void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, int grid_relabel, cudaStream_t st) {
-  if (layer == 0) k_rows<true><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows);
-  else k_rows<false><<<dim3(grid_rows + grid_relabel, members), GS_TPB, 0, st>>>(wsv, layer, grid_rows);
+void gs_kernels_prepare() {}
+void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid_rows, int grid_relabel,
+                    int grid_rowside, cudaStream_t st) {
+  if (layer == 0) {
+    if (wide) k_rows<true, true><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows, 0);
+    else k_rows<true, false><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows, 0);
+    return;
+  }
+  const dim3 g(grid_rows + grid_relabel + grid_rowside, members);
+  if (wide) k_rows<false, true><<<g, GS_TPB, 0, st>>>(wsv, layer, grid_rows, grid_relabel);
+  else k_rows<false, false><<<g, GS_TPB, 0, st>>>(wsv, layer, grid_rows, grid_relabel);
 }
-void gs_launch_expand(const GsWs *wsv, int members, int rng_mode, int layer, int grid, cudaStream_t st) {
-  const dim3 g(grid, members);
-  if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS><<<g, GS_TPB, 0, st>>>(wsv, layer);
-  else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE><<<g, GS_TPB, 0, st>>>(wsv, layer);
-  else k_expand<(int)GS_RNG_PHILOX><<<g, GS_TPB, 0, st>>>(wsv, layer);
+template <bool WIDE>
+static void launch_expand_t(const GsWs *wsv, dim3 g, int rng_mode, int layer, cudaStream_t st) {
+  if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  else k_expand<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
 }
-void gs_kernels_prepare() {  // per device: k_cand's run buffer needs more than the default 48 KB
-  cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CandSmem));
+void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, int layer, int grid, cudaStream_t st) {
+  if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, layer, st);
+  else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, layer, st);
 }
-void gs_launch_cand(const GsWs *wsv, int members, int layer, int grid, cudaStream_t st) {
-  k_cand<<<dim3(grid, members), GS_TPB, sizeof(CandSmem), st>>>(wsv, layer);
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st) {
+  if (wide) k_cand<true><<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
+  else k_cand<false><<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
 }
-void gs_launch_tail(const GsWs *wsv, int members, int grid_relabel, int grid_gather, cudaStream_t st) {
-  k_tail<<<dim3(grid_relabel + grid_gather, members), GS_TPB, 0, st>>>(wsv, grid_relabel, grid_gather);
+void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
+                    cudaStream_t st) {
+  const dim3 g(grid_relabel + grid_rowside + grid_gather, members);
+  if (wide) k_tail<true><<<g, GS_TPB, 0, st>>>(wsv, grid_relabel, grid_rowside, grid_gather);
+  else k_tail<false><<<g, GS_TPB, 0, st>>>(wsv, grid_relabel, grid_rowside, grid_gather);
 }
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,
                           int div, int64_t rows, const int32_t *ids, int64_t n, float *out, int grid,

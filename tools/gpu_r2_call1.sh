@@ -9,7 +9,7 @@ tail -15 $out/parity.txt
 timeout 600 python -m pytest tests -q -m gpu --deselect tests/test_parity_gpu.py --deselect tests/test_random_sweep_gpu.py > $out/rest.txt 2>&1
 echo "rest rc=$?" | tee -a $out/rest.txt
 tail -8 $out/rest.txt
-for cfg in "1 12 12" "2 12 6" "4 12 3" "4 8 2" "2 8 4" "3 6 2"; do
+for cfg in "1 12 12" "2 12 6" "4 12 3" "1 6 6"; do
   set -- $cfg
   timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --group $1 --slots $2 --streams $3 > $out/bench_g$1_s$2_t$3.json 2> $out/bench_g$1_s$2_t$3.err
   echo "bench group=$1 slots=$2 streams=$3 rc=$?"
