@@ -412,7 +412,8 @@ __device__ void rows_role(const GsWs &ws, int layer) {
       if (i < F) {
         const uint32_t o = (uint32_t)base_c;
         ws.off[i] = o;
-        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k], (int)(uint32_t)((uint64_t)rs[k] >> 32), deg[k], nd[k]);
+        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
+                                  (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
         ws.selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
         ws.ea[i] = GS_INF;
         ws.rowhas[i] = 0u;
@@ -457,6 +458,27 @@ __device__ void rows_role(const GsWs &ws, int layer) {
     t = s_tile;
   }
 }
+
+// r % d for many r and one d (the picks of a row, slicer.cpp:16): the reciprocal is
+// computed once per row, every remainder is then a multiply-high and at most three
+// corrections.  inv <= floor(2^32 / d) by construction, so the quotient estimate
+// never exceeds the true quotient and the loop makes the result exact.
+struct Mod32 {
+  uint32_t d, inv;
+  __device__ __forceinline__ void set(uint32_t d_) {
+    d = d_;
+    const float f = __uint2float_ru(d_);
+    uint32_t i0 = __float2uint_rz(__uint_as_float(__float_as_uint(__frcp_rz(f)) + 0x0ffffffeu));
+    i0 += __umulhi(i0, (0u - d_) * i0);
+    while ((unsigned long long)i0 * d_ > 0x100000000ull) i0--;  // never taken in practice; keeps the bound provable
+    inv = d_ == 1u ? 0xFFFFFFFFu : i0;
+  }
+  __device__ __forceinline__ uint32_t rem(uint32_t r) const {
+    uint32_t x = r - __umulhi(r, inv) * d;
+    while (x >= d) x -= d;
+    return x;
+  }
+};
 
 // Packed per-part counters: one byte per part in a 32-bit word (P <= 4) or a 64-bit word.
 template <typename PK> __device__ __forceinline__ PK pkt_one(int g) { return (PK)1 << (8 * g); }
@@ -554,6 +576,19 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   const uint32_t tge = tag.tg | tag.kind;
   uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
   const int lane = lane_id();
+  // fields of the shared-memory copy of ws used per candidate, once into registers
+  const int32_t *__restrict__ indices = ws.indices;
+  const uint8_t *__restrict__ owner_tbl = ws.owner;
+  const int pmask = ws.pmask;
+  const uint32_t pmagic = ws.pmagic, seed_lo = ws.seed_lo, seed_hi = ws.seed_hi;
+  const uint64_t n_draws = ws.n_draws;
+  const bool hints = ws.l2_hints != 0;
+  auto own_of = [&](int32_t v) -> int {  // owner_of(ws, v) on the hoisted fields
+    if (owner_tbl) return (int)__ldg(owner_tbl + v);
+    if (pmask >= 0) return (int)(v & pmask);
+    int32_t r = v - (int32_t)(__umulhi((uint32_t)v, pmagic) * (uint32_t)P);
+    return r < 0 ? r + P : r;
+  };
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -568,14 +603,13 @@ __device__ void expand_role(const GsWs &ws, int layer) {
     const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     int row[GS_IPT], slot[GS_IPT];
     int32_t nd1[GS_IPT], deg[GS_IPT];
+    int g0[GS_IPT];
     int64_t rs[GS_IPT];
     int lo = 0;
-    if (p0 < C) {
-      int hi = cntr - 1;  // largest k with s_off[k] <= p0
-      while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (s_off[mid] <= p0) lo = mid; else hi = mid - 1;
-      }
+    if (p0 < C) {  // largest k < cntr with s_off[k] <= p0 (branch-free: s_off is ascending, s_off[0] <= p0)
+#pragma unroll
+      for (int step = GS_TILE; step > 0; step >>= 1)
+        if (lo + step < cntr && s_off[lo + step] <= p0) lo += step;
     }
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
@@ -590,16 +624,20 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         nd1[k] = nd1[k - 1];
         rs[k] = rs[k - 1];
         deg[k] = deg[k - 1];
+        g0[k] = g0[k - 1];
       } else {
         const int4 ri = ws.rowinfo[row[k]];
-        rs[k] = (int64_t)(((uint64_t)(uint32_t)ri.y << 32) | (uint32_t)ri.x);
+        rs[k] = (int64_t)(((uint64_t)((uint32_t)ri.y & 0x1FFFFFFFu) << 32) | (uint32_t)ri.x);
+        g0[k] = (int)((uint32_t)ri.y >> 29);
         deg[k] = ri.z;
         nd1[k] = ri.w;
       }
     }
     const int32_t *src[GS_IPT];
     uint4 blk = make_uint4(0u, 0u, 0u, 0u);
-    int blk_row = -1, blk_id = -1;
+    int blk_row = -1, blk_id = -1, mod_row = -1;
+    Mod32 md;
+    md.d = 1u; md.inv = 0u;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
       src[k] = nullptr;
@@ -609,29 +647,33 @@ __device__ void expand_role(const GsWs &ws, int layer) {
           uint32_t r;
           if (replay) {
             const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row[k]] + (uint32_t)pick;
-            r = di < ws.n_draws ? ws.draws[di] : 0u;
+            r = di < n_draws ? ws.draws[di] : 0u;
           } else {
             const int want = norepl ? GS_NR_KEY_BLOCK : (pick >> 2);
             if (blk_row != row[k] || blk_id != want) {
               blk_row = row[k];
               blk_id = want;
-              blk = philox_block(ws.seed_lo, ws.seed_hi, batch, layer, nd1[k], blk_id);
+              blk = philox_block(seed_lo, seed_hi, batch, layer, nd1[k], blk_id);
             }
             r = norepl ? nr_pick(blk, (uint32_t)pick, (uint32_t)deg[k]) : philox_word(blk, pick & 3);
           }
           if (norepl) {
             pick = (int32_t)r;  // already a member of [0, deg)
           } else {
-            pick = (int32_t)(r % (uint32_t)deg[k]);
+            if (mod_row != row[k]) {
+              mod_row = row[k];
+              md.set((uint32_t)deg[k]);
+            }
+            pick = (int32_t)md.rem(r);
           }
         }
-        src[k] = ws.indices + rs[k] + pick;
+        src[k] = indices + rs[k] + pick;
       }
     }
     int32_t v[GS_IPT];
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++)
-      if (src[k]) v[k] = ld_stream_i32(src[k], ws.l2_hints != 0, spol);
+      if (src[k]) v[k] = ld_stream_i32(src[k], hints, spol);
     // one returning atom.min per real edge source, all four in flight
     int g[GS_IPT];
     uint32_t old[GS_IPT];
@@ -642,7 +684,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
       g[k] = 0;
       old[k] = 0u;
       if (edge[k]) {
-        g[k] = owner_of(ws, v[k]);
+        g[k] = own_of(v[k]);
         old[k] = tbl.atom_min(v[k], tge | (p0 + k));
       }
     }
@@ -670,7 +712,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
     for (int k = 0; k < GS_IPT; k++) {
       if (slot[k] == 0) {
         cvv[k] = row[k];  // self entry: the row index; part = owner of the row's node
-        cf[k] = GS_CK_SELF | ((uint32_t)owner_of(ws, nd1[k]) << GS_CF_PART_SHIFT);
+        cf[k] = GS_CK_SELF | ((uint32_t)g0[k] << GS_CF_PART_SHIFT);
       } else if (!edge[k]) {
         cvv[k] = 0;
         cf[k] = GS_CK_DEAD;
@@ -694,11 +736,10 @@ __device__ void expand_role(const GsWs &ws, int layer) {
       if (rbits[k]) {
         const uint32_t nb = rbits[k] & ~was[k];
         if (nb) {
-          const int g0 = owner_of(ws, nd1[k]);
-          const uint32_t own = 1u << g0;
+          const uint32_t own = 1u << g0[k];
           pk_out += pkt_spread(nb, (PK)0);
-          if (nb & own) pk_own += pkt_one<PK>(g0);
-          if ((nb & ~own) && !(was[k] & ~own)) pk_to += pkt_one<PK>(g0);
+          if (nb & own) pk_own += pkt_one<PK>(g0[k]);
+          if ((nb & ~own) && !(was[k] & ~own)) pk_to += pkt_one<PK>(g0[k]);
         }
       }
     if (p0 + GS_IPT <= C) {
