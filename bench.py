@@ -96,6 +96,51 @@ def load_graph(shape, device):
     return ip, ix
 
 
+def graph_stats(shape, ip):
+    """state alpha and the maximum degree of the generated graph."""
+    from cslicer.synth import SHAPES
+    deg = np.diff(ip)
+    return {"degree_law": "discretised Pareto, destinations uniform", "alpha": SHAPES.get(shape, (0, 0, None))[2],
+            "mean_degree": round(float(deg.mean()), 2), "max_degree": int(deg.max()),
+            "rows_with_degree_0": int((deg == 0).sum())}
+
+
+def host_description():
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return {"cpu_model": model, "nproc": os.cpu_count(), "usable_cores": host_cores()}
+
+
+def load_graph_cpu_arm(shape):
+    """The graph for a CPU-only arm: this process must not create a CUDA context
+    (the driver classes an arm by the devices it touched).  The cached file is used
+    when present; otherwise a CHILD process generates it (on the GPU when there is
+    one: the 62 M-edge shape takes minutes on the host) and exits before any timing."""
+    f = os.path.join(CACHE, f"{shape}_{GRAPH_SEED}_cuda.npz")
+    fc = os.path.join(CACHE, f"{shape}_{GRAPH_SEED}_cpu.npz")
+    for cand in (f, fc):
+        if os.path.exists(cand):
+            try:
+                z = np.load(cand)
+                return z["indptr"], z["indices"]
+            except Exception:
+                pass
+    code = ("import sys; sys.argv=['bench.py']; import bench, torch; "
+            f"bench.load_graph({shape!r}, 'cuda:0' if torch.cuda.is_available() else 'cpu')")
+    subprocess.run([sys.executable, "-c", code], cwd=ROOT, check=True, stdout=subprocess.DEVNULL)
+    for cand in (f, fc):
+        if os.path.exists(cand):
+            z = np.load(cand)
+            return z["indptr"], z["indices"]
+    raise RuntimeError("graph generation in the child process left no cache file")
+
+
 def seed_batches(num_nodes, count, rank, world):
     """Reference behaviour (WorkerPool.cpp:40-49): a fixed permutation of all
     nodes cut into batches; rank r takes batches r, r+world, ..."""
@@ -245,21 +290,32 @@ def random_accesses(view, P):
     return csr, tab, pos
 
 
-def gather_yardstick(torch, table_elems, dtype, n=1 << 25):
-    """Random-read ceiling of this GPU for a table of the given footprint
-    (torch.index_select as a tuned gather; a yardstick like the copy peak)."""
-    t = torch.zeros(table_elems, dtype=dtype, device="cuda")
-    idx = torch.randint(0, table_elems, (n,), device="cuda", dtype=torch.int64)
-    for _ in range(2):
-        torch.index_select(t, 0, idx)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(3):
-        torch.index_select(t, 0, idx)
-    e1.record()
-    torch.cuda.synchronize()
-    return n * 3 / (e0.elapsed_time(e1) * 1e-3)
+def sector_probe(device, table_bytes, n=1 << 26):
+    """Random-sector ceiling of this GPU, measured by the library's own probe kernel
+    (csrc/slicer_kernels.cu k_sector_probe: eight independent 4-byte reads in flight
+    per thread, full occupancy) on a table of the given footprint -> reads/s."""
+    import ctypes
+    from cslicer import _native as N
+    out = ctypes.c_double(0.0)
+    N.check(N.lib().gs_bench_sector_probe(int(device), int(table_bytes), int(n), ctypes.byref(out)))
+    return out.value
+
+
+def sector_model(view, ip, fanouts):
+    """SURVEY 8(d), last sentence of "Algorithmic bytes": the same compulsory traffic
+    with every random gather charged one 32-byte sector -- the indptr pair of every
+    frontier row (16 B -> 32 B) and every sampled pick (4 B -> 32 B; rows expanded in
+    full are contiguous and stay at 4 B per neighbour).  -> (bytes, gathers)."""
+    extra = gathers = 0
+    deg = np.diff(ip)
+    for l in range(view.num_layers):
+        fr = view.frontier_numpy(l)
+        d = deg[fr]
+        fan = fanouts[l]
+        picks = int(fan * (d >= fan).sum()) if fan >= 0 else 0
+        extra += fr.size * (32 - 16) + picks * (32 - 4)
+        gathers += fr.size + picks
+    return view.algorithmic_bytes(owner_bytes=0, w=4) + extra, gathers
 
 
 # One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.97 MB read +
@@ -314,6 +370,7 @@ def own_arm(args):
     sizes = dict(frontier=v.frontier_len, candidates=v.cand_len, edges=v.edges,
                  slab_bytes=v.slab_used * 4)
     ra_csr, ra_tab, ra_pos = random_accesses(v, P)
+    sec_bytes, _ = sector_model(v, ip, FANOUTS)
     v.release()
 
     def barrier():
@@ -360,25 +417,33 @@ def own_arm(args):
         if (args.shape, FANOUTS, BATCH, P) == NCU_TRAFFIC["workload"] and top == NCU_TRAFFIC["kernel"]:
             roof["traffic"] = NCU_TRAFFIC["bytes"]
             roof["traffic_source"] = NCU_TRAFFIC["source"]
-        # what the path is really bound by: random sector accesses, not streamed bytes
-        g_csr = gather_yardstick(torch, ix.size, torch.int32)
-        g_tab = gather_yardstick(torch, n * args.slots, torch.int32)
+        # the sector-granular bound next to the algorithmic one, and the rate at which
+        # this GPU can serve random sectors at all (own probe kernel, tables of the same footprint)
+        roof["sector_bound"] = {"bytes_per_minibatch": int(sec_bytes), "achieved_gbs": round(sec_bytes * per_gpu_mb_s / 1e9, 2),
+                                "frac": round(sec_bytes * per_gpu_mb_s / 1e9 / peak, 4),
+                                "what": "algorithmic bytes with every random gather (indptr pair per row, every "
+                                        "sampled pick) charged one 32-byte sector, x minibatches/s per GPU, / the same peak"}
+        g_csr = sector_probe(local, ix.size * 4)
+        g_tab = sector_probe(local, n * 4 * args.slots)
         floor_s = ra_csr / g_csr + (ra_tab + ra_pos) / g_tab
         roof["random_access"] = {
             "per_minibatch": {"csr_4B": int(ra_csr), "table_4B": int(ra_tab), "rank_by_position_4B": int(ra_pos)},
-            "yardstick_gelem_s": {"csr_array": round(g_csr / 1e9, 2),
-                                  "tables_all_slots": round(g_tab / 1e9, 2)},
+            "yardstick": {"kernel": "k_sector_probe (csrc/slicer_kernels.cu): 8 independent 4-byte reads in flight per "
+                                    "thread, 8 CTAs of 256 threads per SM; one 32 B sector per read",
+                          "csr_array_gsector_s": round(g_csr / 1e9, 2), "csr_array_gbs": round(g_csr * 32 / 1e9, 1),
+                          "tables_all_slots_gsector_s": round(g_tab / 1e9, 2),
+                          "tables_all_slots_gbs": round(g_tab * 32 / 1e9, 1)},
             "floor_us_per_minibatch": round(floor_s * 1e6, 1),
             "achieved_us_per_minibatch": round(1e6 / per_gpu_mb_s, 1),
             "frac_of_random_access_floor": round(floor_s * per_gpu_mb_s, 3),
-            "note": "each access moves a 32 B sector; yardstick = torch.index_select over arrays of the "
-                    "same footprint, measured in this run"}
+            "note": "floor = this minibatch's random accesses at the probe's rate, nothing else counted"}
         out = {"metric": "sliced minibatches/s", "value": round(value, 2), "unit": "minibatches/s",
                "n_gpus": world, "steps": args.steps, "warmup": W,
                "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                "config": {"workload": f"{args.shape}-shaped synthetic graph N={n} M={ix.size} seed {GRAPH_SEED}; "
                                       f"{len(FANOUTS)}-layer fanout {FANOUTS}, batch {BATCH}, {P} parts (owner=id%P)",
+                          "graph": graph_stats(args.shape, ip), "host": host_description(),
                           "minibatches_per_step": mbs, "slots": args.slots, "streams": args.streams,
                           "minibatches_per_launch": args.group,
                           "sharding": "whole minibatches per rank, graph topology replicated",
@@ -823,9 +888,7 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-    dev = "cuda:0" if torch.cuda.is_available() else "cpu"
-    ip, ix = load_graph(args.shape, dev)
+    ip, ix = load_graph_cpu_arm(args.shape)
     n = ip.size - 1
     cores = host_cores()
     batches = seed_batches(n, 256, 0, 1)
@@ -881,7 +944,8 @@ def main():
     ap.add_argument("--parts", type=int, default=4)
     ap.add_argument("--batch", type=int, default=BATCH, help="seeds per minibatch (config 5: 8192)")
     ap.add_argument("--fanouts", default=",".join(map(str, FANOUTS)))
-    ap.add_argument("--mb-per-step", type=int, default=64)
+    ap.add_argument("--mb-per-step", type=int, default=640,
+                    help="minibatches per step (default: 20 steps are > 1 s of device time at 10 K minibatches/s)")
     ap.add_argument("--slots", type=int, default=12)
     ap.add_argument("--streams", type=int, default=12)
     ap.add_argument("--group", type=int, default=1,

@@ -267,6 +267,13 @@ int gs_slicer_profile(gs_slicer *s, const int64_t *seeds_host, int32_t n,
  * times with reset only on the first call.  Host-only; no device work. */
 int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
 
+/* Measurement aid ("each random 4/8-byte gather charged 32 B"): the rate
+ * at which this GPU serves independent random 4-byte reads from a table of
+ * table_bytes, eight in flight per thread -- one 32-byte DRAM sector each once the
+ * table exceeds L2.  bench.py divides the slicer's sector-granular byte bound by it.
+ * The reference has no counterpart (a CPU program). */
+int gs_bench_sector_probe(int device, int64_t table_bytes, int64_t n_reads, double *reads_per_s);
+
 /* Number of kernel launches one launch sequence performs (3 L + 1), shared by the
  * group_size minibatches of a group. */
 int gs_slicer_launches_per_sample(const gs_slicer *s);

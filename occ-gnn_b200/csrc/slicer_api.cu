@@ -1063,6 +1063,43 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset) {
   return GS_OK;
 }
 
+// Random-sector yardstick (roofline.random_access in bench.py): n_reads independent
+// 4-byte reads, eight in flight per thread, from pseudo-random words of a table of
+// table_bytes -- the access pattern of the neighbour picks and of the dedup-table
+// look-ups.  With a table larger than L2 every read moves one 32-byte DRAM sector.
+int gs_bench_sector_probe(int device, int64_t table_bytes, int64_t n_reads, double *reads_per_s) {
+  if (!reads_per_s || table_bytes < 4 || n_reads < 1) return fail(GS_ERR_INVALID, "gs_bench_sector_probe: bad argument");
+  CU(cudaSetDevice(device));
+  uint32_t *tab = nullptr, *sink = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  const uint64_t elems = (uint64_t)table_bytes / 4;
+  int rc = GS_OK;
+  cudaError_t e = cudaMalloc((void **)&tab, (size_t)elems * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&sink, 4);
+  if (e == cudaSuccess) e = cudaMemset(tab, 0x5A, (size_t)elems * 4);
+  if (e == cudaSuccess) e = cudaEventCreate(&e0);
+  if (e == cudaSuccess) e = cudaEventCreate(&e1);
+  if (e == cudaSuccess) {
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const int grid = sms * 8;
+    gs_launch_sector_probe(tab, elems, (uint64_t)n_reads, 1u, sink, grid, 0);  // warm-up
+    cudaEventRecord(e0, 0);
+    for (uint32_t rep = 0; rep < 3; rep++) gs_launch_sector_probe(tab, elems, (uint64_t)n_reads, 2u + rep, sink, grid, 0);
+    cudaEventRecord(e1, 0);
+    e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+    if (e == cudaSuccess) *reads_per_s = 3.0 * (double)n_reads / ((double)ms * 1e-3);
+  }
+  if (e != cudaSuccess) rc = fail(GS_ERR_CUDA, "gs_bench_sector_probe: %s", cudaGetErrorString(e));
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  cudaFree(tab);
+  cudaFree(sink);
+  return rc;
+}
+
 int gs_slicer_launches_per_sample(const gs_slicer *s) {
   return s ? 3 * s->cfg.num_layers + 1 : 0;
 }
