@@ -394,6 +394,7 @@ def own_arm(args):
 
     out = None
     if rank == 0:
+        dev_launches = dev.launches_per_sample
         prof = kernel_profile(dev, batches)
         chain_ms = sum(ms for _, ms in prof)
         top, top_ms = max(prof, key=lambda kv: kv[1])
@@ -490,6 +491,26 @@ def own_arm(args):
         except Exception as e:  # context only; never fail the bench line on it
             ho = {"unavailable": f"{type(e).__name__}: {e}"}
         if out is not None:
+            # N > 1: the contract line is the layout north_star names -- part g of every minibatch ends
+            # on GPU g.  Whole minibatches sliced where they fall and left there ("replicas") is kept
+            # as an extra key: it says how fast N independent slicers are, not how the job scales.
+            out["replicas"] = {"value": out["value"], "e2e": out["e2e"]["value"], "ms_per_step": out["ms_per_step"],
+                               "sampled_edges_per_s": out["sampled_edges_per_s"],
+                               "sharding": "whole minibatches per rank, graph topology replicated, parts stay "
+                                           "where they were sliced (no exchange)"}
+            if ho.get("value"):
+                out["value"], out["ms_per_step"] = ho["value"], ho["ms_per_step"]
+                out["config"]["minibatches_per_step"] = ho["minibatches_per_step"]
+                out["config"]["sharding"] = ("hand-over: whole minibatches per rank on a replicated topology, "
+                                             f"{world} parts, part g of every minibatch delivered to GPU g by the "
+                                             "packing kernel's own stores over NVLink (content-checked)")
+                out["config"]["workload"] = out["config"]["workload"].replace(f"{P} parts", f"{world} parts")
+                out["parity"] = ho["parity"]
+                out["gpu_launches"] = int((dev_launches / args.group + 1) * args.steps * ho["minibatches_per_step"] / world)
+                out["sampled_edges_per_s"] = None
+                if ho["e2e"].get("value"):
+                    out["e2e"] = ho["e2e"]
+                # value-first ordering keeps these keys inside any truncated tail of the record
             out["hand_over"] = ho
     g.close()
     if dist is not None and not args.no_partitioned:
@@ -506,19 +527,43 @@ def own_arm(args):
         emit(out)
 
 
-def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=64):
+def list_digest(t, torch):
+    """64-bit digest of an int32 device list (order-sensitive, wraps mod 2^64)."""
+    if t.numel() == 0:
+        return 0x9E3779B97F4A7C15
+    x = t.to(torch.int64)
+    i = torch.arange(1, x.numel() + 1, device=x.device, dtype=torch.int64)
+    return int(((x + 0x632BE5AB) * (2 * i + 1)).sum().item()) & 0xFFFFFFFFFFFFFFFF
+
+
+def part_digest(get_field, L, torch):
+    """Digest of every list of one part: get_field(layer, name) -> int32 device tensor."""
+    from cslicer import _native as N
+    d = 0
+    for l in range(L):
+        for f, name in enumerate(N.FIELDS):
+            d = (d * 0x100000001B3 + list_digest(get_field(l, name), torch) + 31 * l + f) & 0xFFFFFFFFFFFFFFFF
+    return d
+
+
+def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, rounds=None):
     """Split-parallel hand-over at N > 1: every rank slices its own
-    minibatches with `world` parts on the replicated topology, packs the parts
-    (gs_slicer_pack_parts) and ONE all-to-all over NVLink per round delivers part g
-    of `world` minibatches to rank g -- what the split-parallel training step
-    consumes (python/train.py:120-160), at the throughput of the replicated
-    slicer.  -> dict for the bench line (rank 0), None elsewhere."""
+    minibatches with `world` parts on the replicated topology and part g of every
+    minibatch is delivered to rank g -- what the split-parallel training step
+    consumes (python/train.py:120-160).  Two exchanges are measured: the packing
+    kernel's own stores into the owners' buffers (PeerScatter: the headline) and an
+    NCCL all-to-all of packed blocks.  Both end with a CONTENT check: every list of
+    the parts a rank received is compared, on the device, with part `rank` of the
+    same minibatch sliced by the rank's own single-GPU slicer.
+    -> dict for the bench line (rank 0), None elsewhere."""
     from cslicer import _native as N
     from cslicer.engine import Slicer
-    from cslicer.handover import HEADER_WORDS, PartBlock, PartScatter
-    from cslicer.sharding import reduce_job
-    sl = Slicer(g, FANOUTS, num_parts=world, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams,
-                seed=7, grid_ctas=args.grid_ctas, host_output=False)
+    from cslicer.handover import HEADER_WORDS, PartScatter, PeerScatter
+    steps = steps or args.steps
+    rounds = rounds or max(16, args.mb_per_step // 4)
+    kw = dict(num_parts=world, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
+              grid_ctas=args.grid_ctas, group_size=args.group)
+    sl = Slicer(g, FANOUTS, host_output=False, **kw)
     batches = seed_batches(n, 64, rank, world)  # rank r slices batches r, r + world, ...
     # one block size for the job: the largest part of a probe minibatch on any rank + 25 %
     slot = sl.submit(batches[0][1], batches[0][0])
@@ -529,33 +574,43 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
     sl.release(slot)
     t = torch.tensor([need], dtype=torch.int64, device=f"cuda:{local}")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    block_words = (int(t[0]) * 5 // 4 + 3) & ~3
+    need = int(t[0])
+    block_words = (need * 5 // 4 + 3) & ~3
     depth = args.slots
-    from cslicer.handover import PeerScatter
     results = {}
     sent = 4 * block_words * (world - 1)
-    for kind in ("peer_stores", "nccl_all_to_all"):
+    for kind in ("peer_stores", "peer_stores_e2e", "nccl_all_to_all"):
         try:  # constructor failures are collective (raised on every rank): the other arm still runs
-            ps = (PeerScatter if kind == "peer_stores" else PartScatter)(sl, dist, block_words, depth=depth)
+            ps = (PartScatter if kind == "nccl_all_to_all" else PeerScatter)(sl, dist, block_words, depth=depth)
         except RuntimeError as e:
             log(f"[bench] hand-over arm {kind} unavailable: {e}")
-            results[kind] = float("nan")
+            results[kind] = (float("nan"), "unavailable")
             continue
-        results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n)
+        mirror_words = min(block_words, (need * 21 // 20 + 3) & ~3) if kind.endswith("e2e") else 0
+        results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds if not mirror_words else max(8, rounds // 4),
+                                       torch, dist, local, rank, world, n, mirror_words)
         if hasattr(ps, "close"):
             ps.close()
         ps = None
     out = None
     if rank == 0:
-        total = steps * rounds * world
-        ms = results["peer_stores"]
-
-        def rate(t):  # NaN (arm unavailable or its delivery check failed) -> null: the line stays strict JSON
-            return None if t != t else round(total / (t * 1e-3), 2)
-        out = {"value": rate(ms),
+        def rate(kind, r):  # NaN (arm unavailable or its content check failed) -> null: the line stays strict JSON
+            ms = results[kind][0]
+            return None if ms != ms else round(steps * r * world / (ms * 1e-3), 2)
+        ms = results["peer_stores"][0]
+        out = {"value": rate("peer_stores", rounds),
                "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
-               "verified": "every rank received part `rank` of the expected minibatch from every source "
-                           "(a mismatch or an unavailable arm turns its value into null)",
+               "parity": results["peer_stores"][1],
+               "parity_check": "every list of every part received in the last round == part `rank` of the same "
+                               "minibatch from the rank's own single-GPU slicer (torch.equal + 64-bit digests on the "
+                               "device, all-reduce MIN of the verdict; a mismatch nulls the value)",
+               "ms_per_step": None if ms != ms else round(ms / steps, 4), "minibatches_per_step": rounds * world,
+               "e2e": {"value": rate("peer_stores_e2e", max(8, rounds // 4)), "unit": "minibatches/s",
+                       "parity": results["peer_stores_e2e"][1],
+                       "h2d_bytes_per_step": rounds * (BATCH * 8 + 16),
+                       "d2h_bytes_per_step": int(max(8, rounds // 4) * world * need * 4),
+                       "what": "host seeds in; every received part block copied to pinned host memory (one DMA "
+                               "per block, size from the running estimate, header-checked) inside the timed region"},
                "ranks": world, "parts": world, "rounds_in_flight": depth,
                "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
                "nvlink_bytes_sent_per_rank_per_round": int(sent),
@@ -565,62 +620,109 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=3, rounds=
                            "up, 16-byte stores below), one 4-byte all-reduce per round as the barrier; "
                            "overlapped with slicing",
                "same_with_nccl_all_to_all": {
-                   "value": rate(results["nccl_all_to_all"]),
+                   "value": rate("nccl_all_to_all", rounds), "parity": results["nccl_all_to_all"][1],
                    "exchange": "gs_slicer_pack_parts into a send buffer + all_to_all_single of equal blocks"}}
     sl.close()
     return out
 
 
-def _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n):
+def _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, rank, world, n, mirror_words=0):
+    """-> (device ms of steps * rounds rounds, max over ranks; parity verdict)."""
+    from cslicer import _native as N
     from cslicer.handover import HEADER_WORDS, PartBlock
     from cslicer.sharding import reduce_job
     release = getattr(ps, "release", lambda tk: None)
+    dev = f"cuda:{local}"
+    host = cstream = None
+    if mirror_words:
+        host = [torch.empty((world, mirror_words), dtype=torch.int32).pin_memory() for _ in range(2)]
+        cstream = torch.cuda.Stream(device=dev)
+    cdone = [torch.cuda.Event(), torch.cuda.Event()]
+    state = {"k": 0, "short": 0}
+
+    def mirror(buf):  # the round's blocks -> pinned host memory, one DMA per block
+        hb = host[state["k"] & 1]
+        cdone[state["k"] & 1].synchronize()  # the copy that used this host buffer two rounds ago
+        with torch.cuda.stream(cstream):
+            cstream.wait_stream(torch.cuda.current_stream(dev))
+            for src in range(world):
+                hb[src].copy_(buf[src, :mirror_words], non_blocking=True)
+            cdone[state["k"] & 1].record(cstream)
+        state["k"] += 1
+        return hb
 
     def run(k):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        inflight, last = [], None
+        inflight, last, last_host = [], None, None
         e0.record()
+        pend, G = [], max(1, sl.group_size)
         for i in range(k):
-            if len(inflight) == depth:
+            if len(inflight) + len(pend) == depth:
                 slot, tk = inflight.pop(0)
                 sl.wait_header(slot)
                 sl.release(slot)
-                ps.collect(tk, parse=False)
+                buf = ps.collect(tk, parse=False)
+                if mirror_words:
+                    mirror(buf)
+                    cstream.synchronize()  # the consumer holds the host copy before the round is released
                 release(tk)
             bi, seeds = batches[i % len(batches)]
-            slot = sl.submit(seeds, bi)
-            inflight.append((slot, ps.post(slot)))
+            pend.append(sl.submit(seeds, bi))
+            if len(pend) == G or i == k - 1:  # post once the group is launched (a post on a staged slot would launch it early)
+                sl.flush()
+                for slot in pend:
+                    inflight.append((slot, ps.post(slot)))
+                pend = []
         for slot, tk in inflight:
             sl.wait_header(slot)
             sl.release(slot)
-            last = ps.collect(tk, parse=False).clone()
+            buf = ps.collect(tk, parse=False)
+            if mirror_words:
+                last_host = mirror(buf)
+                cstream.synchronize()
+            last = buf.clone()
             release(tk)
         e1.record(ps.stream)
         e1.synchronize()
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1), last
-    run(2 * rounds)
+        return e0.elapsed_time(e1), last, last_host
+    run(2 * min(rounds, 32))
     dist.barrier()
     torch.cuda.synchronize()
-    ms, last = run(steps * rounds)
+    ms, last, last_host = run(steps * rounds)
     dist.barrier()
-    ms, _ = reduce_job(dist, f"cuda:{local}", ms, [0])
-    # what arrived last: part `rank` of the last round's minibatch of every source rank
+    ms, _ = reduce_job(dist, dev, ms, [0])
+    # content check of what arrived last: part `rank` of the last round's minibatch of every source rank
     hdr = last[:, :HEADER_WORDS].cpu().numpy()
     k_last = (steps * rounds - 1) % len(batches)
     ok = 1
-    for src in range(world):
-        try:
+    L = len(FANOUTS)
+    try:
+        for src in range(world):
             b = PartBlock(last[src], hdr[src])
-            want = seed_batches(n, 64, src, world)[k_last][0]
-            ok &= int(b.part == rank and b.batch_index == want)
-        except Exception:
-            ok = 0
+            bi, seeds = seed_batches(n, 64, src, world)[k_last]
+            ok &= int(b.part == rank and b.batch_index == bi)
+            v = sl.slice(seeds, bi)  # the same minibatch, sliced here: its part `rank` must be what arrived
+            for l in range(L):
+                for name in N.FIELDS:
+                    a, w = b.field(l, name), v.tensor(l, rank, name)
+                    ok &= int(a.numel() == w.numel() and bool(torch.equal(a, w)))
+            ok &= int(part_digest(lambda l, nm: b.field(l, nm), L, torch) ==
+                      part_digest(lambda l, nm: v.tensor(l, rank, nm), L, torch))
+            v.release()
+            if mirror_words:  # the host copy holds the same words (up to the words in use)
+                used = int(hdr[src][8])
+                ok &= int(used <= mirror_words and
+                          bool(torch.equal(last_host[src][:used], last[src][:used].cpu())))
+    except Exception as e:
+        log(f"[bench] hand-over content check raised: {type(e).__name__}: {e}")
+        ok = 0
     # collective verdict: a rank must not leave the sequence of collectives on its own
-    t = torch.tensor([ok], dtype=torch.int32, device=f"cuda:{local}")
+    t = torch.tensor([ok], dtype=torch.int32, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
-    return ms if int(t[0]) == 1 else float("nan")
+    good = int(t[0]) == 1
+    return (ms if good else float("nan")), ("digest-equal" if good else "MISMATCH")
 
 
 def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs=32, shard=None):

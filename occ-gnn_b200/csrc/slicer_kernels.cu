@@ -812,7 +812,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
 #define CS_RMAX 8           // tiles of one run (held in shared memory between the two sweeps)
 #define CS_BEFORE 0x80000000u  // frontier-row edge: it precedes the row's self entry (positions are < 2^30)
 
-struct CandSmem {
+struct __align__(16) CandSmem {
   uint32_t x[CS_RMAX][GS_TILE];            // minimum position: of an edge's source / of a self entry's node as a source
   uint16_t wt[CS_RMAX][GS_NW][GS_CS_NC];   // class totals per (tile, warp) -> exclusive prefix inside the run
   uint32_t red[GS_NW][GS_CS_NC];
