@@ -773,6 +773,33 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
     ms, (edges,) = reduce_job(dist, f"cuda:{local}", ms, [edges])
     v = ps.slice(batches[0][1], batches[0][0])
     fr = list(v.frontier_len)
+    # content check: this rank's part against part `rank` of the same minibatch from the
+    # single-GPU slicer (needs the whole graph on this rank: not available in shard mode)
+    parity = "unchecked (the whole graph exists on no rank in shard mode; same kernels as the checked runs)"
+    if shard is None:
+        from cslicer import _native as N
+        from cslicer.engine import Graph, Slicer
+        ok = 1
+        try:
+            g1 = Graph(ip, ix, device=local)
+            s1 = Slicer(g1, FANOUTS, num_parts=world, max_batch=BATCH, num_slots=1, num_streams=1, seed=7,
+                        host_output=False)
+            w = s1.slice(batches[0][1], batches[0][0])
+            for l in range(len(FANOUTS)):
+                for name in N.FIELDS:
+                    a, b = v.tensor(l, rank, name), w.tensor(l, rank, name)
+                    ok &= int(a.numel() == b.numel() and bool(torch.equal(a, b)))
+            ok &= int(part_digest(lambda l, nm: v.tensor(l, rank, nm), len(FANOUTS), torch) ==
+                      part_digest(lambda l, nm: w.tensor(l, rank, nm), len(FANOUTS), torch))
+            w.release()
+            s1.close()
+            g1.close()
+        except Exception as e:
+            log(f"[bench] partitioned content check raised: {type(e).__name__}: {e}")
+            ok = 0
+        tk = torch.tensor([ok], dtype=torch.int32, device=f"cuda:{local}")
+        dist.all_reduce(tk, op=dist.ReduceOp.MIN)
+        parity = "digest-equal" if int(tk[0]) == 1 else "MISMATCH"
     v.release()
     # every rank must hold the same replicated frontier sizes (a cheap cross-rank invariant)
     t = torch.tensor(fr, dtype=torch.int64, device=f"cuda:{local}")
@@ -785,7 +812,8 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
         per_mb = ms / (steps * mbs)
         e_mb = edges / (steps * mbs)
         xbytes = e_mb * (world - 1) / world * 9 + sum(fr[1:]) * 8 * (world - 1) + BATCH * 4
-        out = {"value": round(1e3 / per_mb, 2), "unit": "minibatches/s (whole job, every rank works on every minibatch)",
+        out = {"value": round(1e3 / per_mb, 2) if parity != "MISMATCH" else None,
+               "unit": "minibatches/s (whole job, every rank works on every minibatch)", "parity": parity,
                "ms_per_minibatch": round(per_mb, 4), "sampled_edges_per_s": round(edges / (ms * 1e-3), 1),
                "ranks": world, "parts": world, "lanes_per_rank": lanes, "launches_per_minibatch_per_rank": ps.launches_per_sample,
                "barriers_per_minibatch": 3 * len(FANOUTS) + 1,
