@@ -308,6 +308,7 @@ def test_split_parallel_shuffle_forward_and_backward(P, dim):
     import torch
     from cslicer.partitioned import LocalGroup
     from cslicer.synth import synth_graph
+    from oracle import shuffle_oracle as SO
     ip, ix = synth_graph("tiny", seed=31)
     n = ip.size - 1
     fan = [5, 5]
@@ -324,8 +325,18 @@ def test_split_parallel_shuffle_forward_and_backward(P, dim):
             rows = [torch.from_numpy(x).cuda() for x in parts]
             grp.shuffle(views, l, rows, backward)
             ref = _shuffle_reference(want, l, P, lambda v: v % P, parts, backward)
+            # the pinned oracle (oracle/shuffle_oracle.py: mergeKernel + merge order of the reference,
+            # held to tests/golden/shuffle.npz by tests/test_shuffle_oracle.py)
+            fr, to = SO.peer_lists(want, l, lambda v: v % P)
+            pinned = SO.shuffle_backward(parts, fr, to) if backward else SO.shuffle_forward(parts, fr, to)
             for g in range(P):
-                assert np.array_equal(rows[g].cpu().numpy(), ref[g]), (l, backward, g)
+                assert np.array_equal(rows[g].cpu().numpy(), pinned[g]), (l, backward, g)
+                assert np.array_equal(ref[g], pinned[g]), (l, backward, g)
+                # the per-peer lists the CUDA path emits in the slots the reference leaves empty
+                for q in range(P):
+                    if q != g:
+                        assert np.array_equal(views[g].numpy(l, q, "from_ids"), fr[g][q]), (l, g, q)
+                        assert np.array_equal(views[g].numpy(l, q, "to_ids"), to[g][q]), (l, g, q)
     for v in views:
         v.release()
     grp.close()
