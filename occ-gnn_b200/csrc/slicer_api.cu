@@ -235,6 +235,7 @@ int launch_group(gs_slicer *s, Group &gr) {
     CU(cudaEventRecord(gr.chain_done, gr.stream));
     CU(cudaStreamWaitEvent(s->copy_stream, gr.chain_done, 0));
   }
+  CU(cudaGetLastError());
   for (int j = 0; j < m; j++) {
     Slot &sl = s->slots[gr.first + j];
     sl.copied = 0;
@@ -566,9 +567,9 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.rowinfo, s->Fcap);
     DA(w.off, s->Fcap + 1);
     DA(w.samp_rank, s->Fcap);
-    DA(w.selfrank, s->Fcap);
-    DA(w.ea, s->Fcap);
-    DA(w.rowhas, s->Fcap);
+    DA(w.selfrank, 2 * (s->Fcap + 4));  // per-row arrays ping-pong by layer (rowside of layer l runs next to k_rows of l + 1)
+    DA(w.ea, 2 * (s->Fcap + 4));
+    DA(w.rowhas, 2 * (s->Fcap + 4));
     DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
     DA(w.cand, s->Ccap + 4);
     DA(w.cflag, s->Ccap + 4);
@@ -702,6 +703,10 @@ int gs_slicer_flush(gs_slicer *s) {
 
 static int finish_wait(gs_slicer *s, Slot &sl, const gs_sample_header **hdr_out) {
   sl.state = SLOT_DONE;
+  {
+    const cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) return fail(GS_ERR_CUDA, "sample failed on the device: %s", cudaGetErrorString(le));
+  }
   const int st = sl.hdr_host->status ? sl.hdr_host->status : sl.hdr_host->late_status;
   if (hdr_out) *hdr_out = sl.hdr_host;
   if (st != 0) {

@@ -91,9 +91,9 @@ struct GsWs {
   int4 *rowinfo;         // [Fcap] {indptr lo, indptr hi, degree, node id} of every frontier row
   uint32_t *off;         // [Fcap+1] first candidate position of row i
   uint32_t *samp_rank;   // [Fcap]   # earlier rows that draw (replay mode)
-  uint32_t *selfrank;    // [Fcap]   # earlier rows with the same owner = rank in self_ids_* of that part
-  uint32_t *ea;          // [Fcap]   minimum edge-source position of the row's node in this layer (GS_INF: none)
-  uint32_t *rowhas;      // [Fcap]   bit q: the row emitted >= 1 edge into part q
+  uint32_t *selfrank;    // [2][Fcap] # earlier rows with the same owner = rank in self_ids_* of that part
+  uint32_t *ea;          // [2][Fcap] minimum edge-source position of the row's node in this layer (GS_INF: none)
+  uint32_t *rowhas;      // [2][Fcap] (ping-pong by layer) bit q: the row emitted >= 1 edge into part q
   uint32_t *rowscan;     // [P][Fcap+1] edges of part q emitted before row i (k_cand -> rowside)
   int32_t *cand;         // [Ccap]   candidate stream; after k_cand: in_nodes rank at first-occurrence positions
   uint8_t *cflag;        // [Ccap]

@@ -318,6 +318,10 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   const int fan = ws.fanouts[layer];
   const GsState stt = *ws.state;
   const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer;
+  // per-row arrays ping-pong by layer: rowside of layer l reads them in the launch in which
+  // k_rows of layer l + 1 writes the next layer's
+  uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3), *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3),
+           *rw_selfrank = ws.selfrank + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);
   const Tag tag(ws, stt);
   const Tbl tbl(ws);
   const bool replay = ws.rng_mode == (int)GS_RNG_DRAWS;
@@ -414,9 +418,9 @@ __device__ void rows_role(const GsWs &ws, int layer) {
         ws.off[i] = o;
         ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
                                   (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
-        ws.selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
-        ws.ea[i] = GS_INF;
-        ws.rowhas[i] = 0u;
+        rw_selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
+        rw_ea[i] = GS_INF;
+        rw_rowhas[i] = 0u;
         if (replay) ws.samp_rank[i] = base_s;
         if (FIRST) {
           ws.fslab[i] = nd[k];
@@ -576,6 +580,9 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   const uint32_t tge = tag.tg | tag.kind;
   uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
   const int lane = lane_id();
+  // per-row arrays ping-pong by layer: rowside of layer l reads them in the launch in which
+  // k_rows of layer l + 1 writes the next layer's
+  uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3), *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);
   // fields of the shared-memory copy of ws used per candidate, once into registers
   const int32_t *__restrict__ indices = ws.indices;
   const uint8_t *__restrict__ owner_tbl = ws.owner;
@@ -702,7 +709,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
       was[k] = 0u;
-      if (rbits[k]) was[k] = atomicOr(ws.rowhas + row[k], rbits[k]);
+      if (rbits[k]) was[k] = atomicOr(rw_rowhas + row[k], rbits[k]);
     }
     int32_t cvv[GS_IPT];
     uint32_t cf[GS_IPT];
@@ -725,7 +732,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
           pk_in += pkt_one<PK>(g[k]);
         } else if (!(old[k] & tag.kind)) {  // a row of the current frontier
           const uint32_t idx = old[k] & tag.pmask;
-          if (atomicMin(ws.ea + idx, p0 + k) == GS_INF) pk_in += pkt_one<PK>(g[k]);
+          if (atomicMin(rw_ea + idx, p0 + k) == GS_INF) pk_in += pkt_one<PK>(g[k]);
           cvv[k] = (int32_t)idx;
           cf[k] = GS_CK_FHIT | ((uint32_t)g[k] << GS_CF_PART_SHIFT);
         }
@@ -874,6 +881,7 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
   int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
   const GsState stt = *ws.state;
   const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 1u;
+  const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);  // per-row arrays ping-pong by layer
   const Tag tag(ws, stt);
   uint32_t *cs_agg = ws.cs_val, *cs_inc = ws.cs_val + (size_t)ws.ctiles_cap * GS_CS_NC;
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
@@ -904,7 +912,7 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
         if (kind == GS_CK_EDGE) {
           x[i] = tbl.ld(ci[i]) & tag.pmask;
         } else if (kind != GS_CK_DEAD) {
-          x[i] = __ldcg(ws.ea + ci[i]);
+          x[i] = __ldcg(rw_ea + ci[i]);
           if (kind == GS_CK_FHIT) s[i] = __ldcg(ws.off + ci[i]);
         }
       }
@@ -1041,6 +1049,8 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   const GsState stt = *ws.state;
   const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 2u;
+  const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3), *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3),
+                 *rw_selfrank = ws.selfrank + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);  // ping-pong by layer (see rows_role)
   uint32_t *fs_agg = ws.fs_val, *fs_inc = ws.fs_val + (size_t)ws.ftiles_cap * GS_FS_NC;
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 3;
   const int lane = lane_id(), w = warp_id();
@@ -1057,10 +1067,10 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
     int32_t nd[GS_IPT] = {0, 0, 0, 0};
     int g0[GS_IPT];
     if (i0 + GS_IPT <= F) {
-      const uint4 h4 = *reinterpret_cast<const uint4 *>(ws.rowhas + i0);
+      const uint4 h4 = *reinterpret_cast<const uint4 *>(rw_rowhas + i0);
       const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
-      const uint4 a4 = *reinterpret_cast<const uint4 *>(ws.ea + i0);
-      const uint4 s4 = *reinterpret_cast<const uint4 *>(ws.selfrank + i0);
+      const uint4 a4 = *reinterpret_cast<const uint4 *>(rw_ea + i0);
+      const uint4 s4 = *reinterpret_cast<const uint4 *>(rw_selfrank + i0);
       has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
       nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
       a[0] = a4.x; a[1] = a4.y; a[2] = a4.z; a[3] = a4.w;
@@ -1070,10 +1080,10 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
       for (int k = 0; k < GS_IPT; k++) {
         a[k] = GS_INF; sr[k] = 0u;
         if (i0 + k < F) {
-          has[k] = ws.rowhas[i0 + k];
+          has[k] = rw_rowhas[i0 + k];
           nd[k] = front[i0 + k];
-          a[k] = ws.ea[i0 + k];
-          sr[k] = ws.selfrank[i0 + k];
+          a[k] = rw_ea[i0 + k];
+          sr[k] = rw_selfrank[i0 + k];
         }
       }
     }
