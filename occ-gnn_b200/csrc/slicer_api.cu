@@ -172,7 +172,7 @@ int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::ve
     gs_launch_rows(gr.wsv, members, wide, l, s->grid_rows[l], l > 0 ? s->grid_relabel[l - 1] : 0,
                    l > 0 ? s->grid_rows[l - 1] : 0, st);
     if ((rc = mark(l == 0 ? "rows" : "rows+relabel+rowside"))) return rc;
-    gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, l, s->grid_cand[l], st);
+    gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l], st);
     if ((rc = mark("expand"))) return rc;
     gs_launch_cand(gr.wsv, members, wide, l, s->grid_cand[l], st);
     if ((rc = mark("cand"))) return rc;
@@ -570,7 +570,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.selfrank, 2 * (s->Fcap + 4));  // per-row arrays ping-pong by layer (rowside of layer l runs next to k_rows of l + 1)
     DA(w.ea, 2 * (s->Fcap + 4));
     DA(w.rowhas, 2 * (s->Fcap + 4));
-    DA(w.rowscan, (s->Fcap + 1) * cfg->num_parts);
+    DA(w.rowscan, (s->Fcap + 1) * (cfg->num_parts > 4 ? 8 : 4));  // one record per row
     DA(w.cand, s->Ccap + 4);
     DA(w.cflag, s->Ccap + 4);
     DA(w.tile_first, ctiles + 1);

@@ -94,7 +94,7 @@ struct GsWs {
   uint32_t *selfrank;    // [2][Fcap] # earlier rows with the same owner = rank in self_ids_* of that part
   uint32_t *ea;          // [2][Fcap] minimum edge-source position of the row's node in this layer (GS_INF: none)
   uint32_t *rowhas;      // [2][Fcap] (ping-pong by layer) bit q: the row emitted >= 1 edge into part q
-  uint32_t *rowscan;     // [P][Fcap+1] edges of part q emitted before row i (k_cand -> rowside)
+  uint32_t *rowscan;     // [Fcap+1][4 or 8] edges of part q emitted before row i (k_cand -> rowside)
   int32_t *cand;         // [Ccap]   candidate stream; after k_cand: in_nodes rank at first-occurrence positions
   uint8_t *cflag;        // [Ccap]
   uint32_t *tile_first;  // [ctiles_cap] row containing candidate t*GS_TILE
@@ -142,7 +142,9 @@ void gs_kernels_prepare();  // once per device, before the first launch / graph 
 // wide: more than 4 parts (64-bit packed per-part counters)
 void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid_rows, int grid_relabel,
                     int grid_rowside, cudaStream_t st);
-void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, int layer, int grid, cudaStream_t st);
+// by_rows: sampled layer (fan > 0) -> one thread per (row, four picks); else candidate-parallel (fan = -1)
+void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
+                      cudaStream_t st);
 void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st);
 void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
                     cudaStream_t st);

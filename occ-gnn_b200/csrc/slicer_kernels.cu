@@ -432,11 +432,13 @@ __device__ void rows_role(const GsWs &ws, int layer) {
         } else {
           tbl.st(nd[k], tag.tg | (uint32_t)i);
         }
-        // candidate tiles that start inside this row
+        // candidate tiles that start inside this row (only the candidate-parallel k_expand of
+        // fan = -1 layers looks rows up by position)
         const unsigned long long end = base_c + c[k];
-        for (unsigned long long tb = (base_c + GS_TILE - 1) / GS_TILE;
-             tb * GS_TILE < end && tb < (unsigned long long)ws.ctiles_cap; tb++)
-          ws.tile_first[tb] = (uint32_t)i;
+        if (fan < 0)
+          for (unsigned long long tb = (base_c + GS_TILE - 1) / GS_TILE;
+               tb * GS_TILE < end && tb < (unsigned long long)ws.ctiles_cap; tb++)
+            ws.tile_first[tb] = (uint32_t)i;
         base_c = end;
         const bool samp = fan >= 0 && deg[k] >= fan;
         base_s += samp ? 1u : 0u;
@@ -787,6 +789,177 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   if (threadIdx.x == 0) layer_alloc(ws, layer, s_cnt);
 }
 
+// Row-parallel expansion for sampled layers (fan > 0): a row has at most fan + 1
+// candidates, so the work item is (row, block of four picks) -- exactly the unit
+// one Philox block serves.  One thread per item: row record and offsets are read
+// once, the Philox block and the reciprocal of the degree are computed once,
+// the positions are off[row] + 1 + pick index -- no search, no staging, no
+// redundant generator work (the candidate-parallel form below recomputes all of
+// that per thread and is kept for fan = -1, where rows are unbounded).  Dedup,
+// counting and the candidate stream are exactly those of expand_role.
+template <int RNG, typename PK>
+__device__ void expand_rows_role(const GsWs &ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  const Tbl tbl(ws);
+  const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
+  __shared__ uint32_t s_cnt[GS_CNT_STRIDE];
+  const int P = ws.P;
+  const int F = h->frontier_len[layer];
+  const int fan = ws.fanouts[layer];
+  const uint32_t batch = (uint32_t)h->batch_index;
+  constexpr bool replay = RNG == (int)GS_RNG_DRAWS;
+  constexpr bool norepl = RNG == (int)GS_RNG_PHILOX_NOREPLACE;
+  const uint64_t dbase = h->draw_base[layer];
+  const GsState stt = *ws.state;
+  const Tag tag(ws, stt);
+  const uint32_t tge = tag.tg | tag.kind;
+  uint32_t *cnt = ws.cnt + layer * GS_CNT_STRIDE;
+  const int lane = lane_id();
+  uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3),
+           *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);
+  const int32_t *__restrict__ indices = ws.indices;
+  const uint8_t *__restrict__ owner_tbl = ws.owner;
+  const int pmask = ws.pmask;
+  const uint32_t pmagic = ws.pmagic, seed_lo = ws.seed_lo, seed_hi = ws.seed_hi;
+  const uint64_t n_draws = ws.n_draws;
+  const bool hints = ws.l2_hints != 0;
+  auto own_of = [&](int32_t v) -> int {
+    if (owner_tbl) return (int)__ldg(owner_tbl + v);
+    if (pmask >= 0) return (int)(v & pmask);
+    int32_t r = v - (int32_t)(__umulhi((uint32_t)v, pmagic) * (uint32_t)P);
+    return r < 0 ? r + P : r;
+  };
+  const uint32_t nb = (uint32_t)(fan + 3) >> 2;                       // items per row
+  const uint32_t nbm = (uint32_t)((0x100000000ull + nb - 1) / nb);    // item / nb by multiply-high + one correction
+  const uint32_t nitems = (uint32_t)F * nb;                           // F < 2^30 / ... : fits (F * (fan + 1) <= Ccap < 2^30)
+  if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  for (uint32_t it0 = blockIdx.x * GS_TPB; it0 < nitems; it0 += gridDim.x * GS_TPB) {
+    const uint32_t item = it0 + threadIdx.x;
+    PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
+    uint32_t n_new = 0u;
+    if (item < nitems) {
+      uint32_t row = __umulhi(item, nbm);
+      if (row * nb > item) row--;
+      const uint32_t b = item - row * nb;
+      const int4 ri = ws.rowinfo[row];
+      const uint32_t o = ws.off[row], c = ws.off[row + 1] - o;
+      const int64_t rs = (int64_t)(((uint64_t)((uint32_t)ri.y & 0x1FFFFFFFu) << 32) | (uint32_t)ri.x);
+      const int g0 = (int)((uint32_t)ri.y >> 29);
+      const int32_t deg = ri.z, nd = ri.w;
+      const bool samp = deg >= fan;
+      const int j0 = (int)(4u * b);
+      const int nj = min(4, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
+      if (b == 0u) {  // the row's self entry (slicer.cpp:7)
+        ws.cand[o] = (int32_t)row;
+        ws.cflag[o] = (uint8_t)(GS_CK_SELF | ((uint32_t)g0 << GS_CF_PART_SHIFT));
+      }
+      if (nj > 0) {
+        uint4 blk = make_uint4(0u, 0u, 0u, 0u);
+        Mod32 md;
+        md.d = 1u; md.inv = 0u;
+        if (samp) {
+          if (!replay) blk = philox_block(seed_lo, seed_hi, batch, layer, nd, norepl ? GS_NR_KEY_BLOCK : (int)b);
+          if (!norepl) md.set((uint32_t)deg);
+        }
+        int32_t v[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          v[j] = nd;
+          if (j < nj) {
+            int32_t pick = j0 + j;
+            if (samp) {
+              if (norepl) {
+                pick = (int32_t)nr_pick(blk, (uint32_t)pick, (uint32_t)deg);
+              } else {
+                uint32_t r;
+                if (replay) {
+                  const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row] + (uint32_t)pick;
+                  r = di < n_draws ? ws.draws[di] : 0u;
+                } else {
+                  r = philox_word(blk, j);
+                }
+                pick = (int32_t)md.rem(r);
+              }
+            }
+            v[j] = ld_stream_i32(indices + rs + pick, hints, spol);
+          }
+        }
+        int g[4];
+        uint32_t old[4];
+        bool edge[4];
+        uint32_t rbits = 0u;
+        const uint32_t p1 = o + 1u + (uint32_t)j0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          edge[j] = j < nj && v[j] != nd;  // a sampled neighbour equal to the destination is a self edge (slicer.cpp:33)
+          g[j] = 0;
+          old[j] = 0u;
+          if (edge[j]) {
+            g[j] = own_of(v[j]);
+            old[j] = tbl.atom_min(v[j], tge | (p1 + j));
+            rbits |= 1u << g[j];
+          }
+        }
+        uint32_t was = 0u;
+        if (rbits) was = atomicOr(rw_rowhas + row, rbits);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          if (j < nj) {
+            int32_t cv = 0;
+            uint32_t cf = GS_CK_DEAD;
+            if (edge[j]) {
+              cv = v[j];
+              cf = GS_CK_EDGE | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
+              pk_e += pkt_one<PK>(g[j]);
+              if (!tag.mine(old[j])) {  // first arrival for a node that is new to the frontier
+                n_new++;
+                pk_in += pkt_one<PK>(g[j]);
+              } else if (!(old[j] & tag.kind)) {  // a row of the current frontier
+                const uint32_t idx = old[j] & tag.pmask;
+                if (atomicMin(rw_ea + idx, p1 + j) == GS_INF) pk_in += pkt_one<PK>(g[j]);
+                cv = (int32_t)idx;
+                cf = GS_CK_FHIT | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
+              }
+            }
+            ws.cand[p1 + j] = cv;
+            ws.cflag[p1 + j] = (uint8_t)cf;
+          }
+        }
+        const uint32_t nbits = rbits & ~was;
+        if (nbits) {  // first edge of the row into each of these parts
+          const uint32_t own = 1u << g0;
+          pk_out += pkt_spread(nbits, (PK)0);
+          if (nbits & own) pk_own += pkt_one<PK>(g0);
+          if ((nbits & ~own) && !(was & ~own)) pk_to += pkt_one<PK>(g0);
+        }
+      }
+    }
+    pk_in = pkt_redux(pk_in);
+    pk_e = pkt_redux(pk_e);
+    pk_out = pkt_redux(pk_out);
+    pk_own = pkt_redux(pk_own);
+    pk_to = pkt_redux(pk_to);
+    n_new = __reduce_add_sync(FULL, n_new);
+    if (lane < P) {
+      uint32_t x;
+      if ((x = pkt_get<PK>(pk_in, lane))) atomicAdd(&s_cnt[GS_CNT_IN(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_e, lane))) atomicAdd(&s_cnt[GS_CNT_E(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_out, lane))) atomicAdd(&s_cnt[GS_CNT_OUT(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_own, lane))) atomicAdd(&s_cnt[GS_CNT_OWN(P, lane)], x);
+      if ((x = pkt_get<PK>(pk_to, lane))) atomicAdd(&s_cnt[GS_CNT_TO(P, lane)], x);
+    }
+    if (lane == 31 && n_new) atomicAdd(&s_cnt[GS_CNT_NEW], n_new);
+  }
+  __syncthreads();
+  if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);
+  if (!last_block(ws.tickets + layer * GS_TICKETS + 1)) return;
+  if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = __ldcg(cnt + threadIdx.x);  // one round trip for all totals
+  __syncthreads();
+  if (threadIdx.x == 0) layer_alloc(ws, layer, s_cnt);
+}
+
 // ------------------------------------------------------------------- k_cand
 // The one pass over the candidate stream.  With every minimum in place:
 //   edge of a NEW node v at p:   first occurrence iff table[v] holds p  -> in_nodes of its
@@ -886,7 +1059,7 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
   uint32_t *cs_agg = ws.cs_val, *cs_inc = ws.cs_val + (size_t)ws.ctiles_cap * GS_CS_NC;
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
   const int lane = lane_id(), w = warp_id();
-  const size_t rs_stride = (size_t)ws.Fcap + 1;
+  const size_t rs_stride = sizeof(PK);  // rowscan: one record of 4 (P <= 4) or 8 words per row
   if (threadIdx.x < P) {
     sm.fo_in[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
     sm.fo_ix[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
@@ -961,15 +1134,6 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
       uint32_t nf = 0u;
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++) fl[i] = cand_class<PK>(fl[i], p0 + i, x[i], pi, pe, nf);
-      // the node id of whatever enters a list: self entries that are frontier firsts,
-      // first occurrences among frontier-row edges (new nodes carry their id already)
-      int32_t z[GS_IPT];
-#pragma unroll
-      for (int i = 0; i < GS_IPT; i++) {
-        const uint32_t kind = fl[i] & GS_CK_MASK;
-        z[i] = ci[i];
-        if ((kind == GS_CK_SELF && (fl[i] & 0x200u)) || (kind == GS_CK_FHIT && (fl[i] & 0x100u))) z[i] = front[ci[i]];
-      }
       const PK inc_i = pkt_incl(pi), inc_e = pkt_incl(pe);
       const uint32_t inc_f = warp_incl_scan(nf);
       const uint16_t *wtb = sm.wt[k][w];
@@ -982,10 +1146,14 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
         const uint32_t kind = fl[i] & GS_CK_MASK;
         const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
         if (kind == GS_CK_SELF) {
-          if (fl[i] & 0x200u) fnext[rf++] = z[i];
-          // edges of every part emitted before this row: its CSR row pointers
-          uint32_t *rsp = ws.rowscan + ci[i];
-          for (int q = 0; q < P; q++, rsp += rs_stride) *rsp = CS_B(CS_E(q)) + pkt_get<PK>(re, q);
+          if (fl[i] & 0x200u) fnext[rf++] = front[ci[i]];
+          // edges of every part emitted before this row: its CSR row pointers, one record per row
+          uint4 *rsp = reinterpret_cast<uint4 *>(ws.rowscan + (size_t)ci[i] * rs_stride);
+          rsp[0] = make_uint4(CS_B(CS_E(0)) + pkt_get<PK>(re, 0), CS_B(CS_E(1)) + pkt_get<PK>(re, 1),
+                              CS_B(CS_E(2)) + pkt_get<PK>(re, 2), CS_B(CS_E(3)) + pkt_get<PK>(re, 3));
+          if (sizeof(PK) > 4)
+            rsp[1] = make_uint4(CS_B(CS_E(4)) + pkt_get<PK>(re, 4), CS_B(CS_E(5)) + pkt_get<PK>(re, 5),
+                                CS_B(CS_E(6)) + pkt_get<PK>(re, 6), CS_B(CS_E(7)) + pkt_get<PK>(re, 7));
         } else if (kind != GS_CK_DEAD) {
           const uint32_t ex = CS_B(CS_E(g)) + pkt_get<PK>(re, g);
           if (fl[i] & 0x100u) {
@@ -993,9 +1161,10 @@ __device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
             // value, in_nodes entry, relabel map entry; every other edge leaves ~m
             // (m = position of that first occurrence) for relabel_role
             const uint32_t rk = CS_B(CS_IN(g)) + pkt_get<PK>(ri, g);
-            ws.slab[sm.fo_in[g] + rk] = z[i];
+            const int32_t z = kind == GS_CK_FHIT ? front[ci[i]] : ci[i];  // a new node carries its id, a frontier row its index
+            ws.slab[sm.fo_in[g] + rk] = z;
             ws.slab[sm.fo_ix[g] + ex] = (int32_t)rk;
-            if (fl[i] & 0x200u) fnext[rf++] = z[i];
+            if (fl[i] & 0x200u) fnext[rf++] = z;
             ci[i] = (int32_t)rk;
             wrote = true;
             ri += pkt_one<PK>(g);
@@ -1054,7 +1223,7 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
   uint32_t *fs_agg = ws.fs_val, *fs_inc = ws.fs_val + (size_t)ws.ftiles_cap * GS_FS_NC;
   uint32_t *tick = ws.tickets + layer * GS_TICKETS + 3;
   const int lane = lane_id(), w = warp_id();
-  const size_t rs_stride = (size_t)ws.Fcap + 1;
+  const size_t rs_stride = sizeof(PK);  // rowscan: one record of 4 (P <= 4) or 8 words per row
   if (threadIdx.x < P * GS_NUM_FIELDS)
     s_fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
         h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
@@ -1140,7 +1309,7 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
           const uint32_t op = FS_B(FS_OUT(q)) + pkt_get<PK>(ro, q);
           const uint32_t ow = FS_B(FS_OWN(q)) + pkt_get<PK>(rw, q);
           ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd[k];
-          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)q * rs_stride + i];
+          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * rs_stride + q];
           if (q == gq) {
             ws.slab[s_fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
             op_own = (int32_t)op;
@@ -1257,6 +1426,14 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand(const GsWs *_
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
   expand_role<RNG, PK>(ws, layer);
+}
+
+template <int RNG, bool WIDE>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand_rows(const GsWs *__restrict__ wsv, int layer) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  expand_rows_role<RNG, PK>(ws, layer);
 }
 
 template <bool WIDE>
@@ -1525,14 +1702,21 @@ void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid
   else k_rows<false, false><<<g, GS_TPB, 0, st>>>(wsv, layer, grid_rows, grid_relabel);
 }
 template <bool WIDE>
-static void launch_expand_t(const GsWs *wsv, dim3 g, int rng_mode, int layer, cudaStream_t st) {
+static void launch_expand_t(const GsWs *wsv, dim3 g, int rng_mode, bool by_rows, int layer, cudaStream_t st) {
+  if (by_rows) {  // sampled layer: one thread per (row, block of four picks)
+    if (rng_mode == (int)GS_RNG_DRAWS) k_expand_rows<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand_rows<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    else k_expand_rows<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    return;
+  }
   if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
   else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
   else k_expand<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
 }
-void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, int layer, int grid, cudaStream_t st) {
-  if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, layer, st);
-  else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, layer, st);
+void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
+                      cudaStream_t st) {
+  if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
+  else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
 }
 void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st) {
   if (wide) k_cand<true><<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
