@@ -268,7 +268,8 @@ def kernel_bytes(view, P):
         rows = F * (4 + 16) + F * (16 + 4 + 4 + 4 + 4 + 4)                 # frontier + indptr pair in; rowinfo, off, selfrank, ea, rowhas, table mark out
         out[f"rows@{l}" if l == 0 else f"rows+relabel+rowside@{l}"] = rows + (tail[l - 1] if l else 0)
         out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5 + (C - F) * 4   # rowinfo + off, pick + atom.min per edge, stream out, rowhas
-        out[f"cand@{l}"] = 2 * C * 5 + C * 4 + (Fn + n_in + E) * 4 + F * P * 4   # stream in (twice), table / ea read, lists + rowscan out
+        out[f"cand_flags@{l}"] = C * 5 + C * 4 + C * 1 + (E - n_in) * 4            # stream in, table / ea read, flags + moved words out
+        out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + F * 16              # stream in, lists + rowscan records out
     out["relabel+rowside+finish"] = tail[L - 1]
     return out
 

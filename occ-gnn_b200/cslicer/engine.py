@@ -338,7 +338,7 @@ class Slicer:
     def profile(self, seeds, batch_index=0):
         """-> list of (kernel name, ms) for one eager run with events between launches."""
         s = np.ascontiguousarray(seeds, dtype=np.int64)
-        cap = 4 + 3 * N.MAX_LAYERS
+        cap = 4 + 4 * N.MAX_LAYERS
         ms = (C.c_float * cap)()
         names = (C.c_char_p * cap)()
         n = C.c_int32(0)

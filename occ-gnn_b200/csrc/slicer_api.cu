@@ -174,8 +174,10 @@ int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::ve
     if ((rc = mark(l == 0 ? "rows" : "rows+relabel+rowside"))) return rc;
     gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l], st);
     if ((rc = mark("expand"))) return rc;
-    gs_launch_cand(gr.wsv, members, wide, l, s->grid_cand[l], st);
-    if ((rc = mark("cand"))) return rc;
+    gs_launch_cand(gr.wsv, members, wide, 0, l, s->grid_cand[l], st);
+    if ((rc = mark("cand_flags"))) return rc;
+    gs_launch_cand(gr.wsv, members, wide, 1, l, s->grid_cand[l], st);
+    if ((rc = mark("cand_apply"))) return rc;
   }
   gs_launch_tail(gr.wsv, members, wide, s->grid_relabel[L - 1], s->grid_rows[L - 1], s->feat ? s->grid_gather : 0, st);
   if ((rc = mark(s->feat ? "relabel+rowside+gather_features+finish" : "relabel+rowside+finish"))) return rc;
@@ -578,8 +580,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.tickets, (size_t)(L + 1) * GS_TICKETS);
     DA(w.rs_status, ftiles);
     DA(w.rs_val, 2 * (size_t)ftiles * GS_RS_NC);
-    DA(w.cs_status, ctiles);
-    DA(w.cs_val, 2 * (size_t)ctiles * GS_CS_NC);
+    w.cgrid_cap = s->grid;
+    DA(w.ccnt, (size_t)GS_CS_NC * s->grid);
     DA(w.fs_status, ftiles);
     DA(w.fs_val, 2 * (size_t)ftiles * GS_FS_NC);
     if (s->feat) {
@@ -600,7 +602,6 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaMemset(w.cnt, 0, (size_t)L * GS_CNT_STRIDE * sizeof(uint32_t)));
     CUS(cudaMemset(w.tickets, 0, (size_t)(L + 1) * GS_TICKETS * sizeof(uint32_t)));
     CUS(cudaMemset(w.rs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
-    CUS(cudaMemset(w.cs_status, 0, (size_t)ctiles * sizeof(uint32_t)));
     CUS(cudaMemset(w.fs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
@@ -1106,7 +1107,7 @@ int gs_bench_sector_probe(int device, int64_t table_bytes, int64_t n_reads, doub
 }
 
 int gs_slicer_launches_per_sample(const gs_slicer *s) {
-  return s ? 3 * s->cfg.num_layers + 1 : 0;
+  return s ? 4 * s->cfg.num_layers + 1 : 0;
 }
 int64_t gs_slicer_slot_bytes(const gs_slicer *s) { return s ? s->slot_bytes : 0; }
 int64_t gs_slicer_slab_capacity(const gs_slicer *s) { return s ? s->slab_cap : 0; }

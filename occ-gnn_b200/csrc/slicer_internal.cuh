@@ -102,8 +102,8 @@ struct GsWs {
   uint32_t *tickets;     // [L][GS_TICKETS] + [GS_TICKETS] (tail)
   uint32_t *rs_status;   // [ftiles_cap]
   unsigned long long *rs_val;  // [2][ftiles_cap][GS_RS_NC]  aggregates, inclusive prefixes
-  uint32_t *cs_status;   // [ctiles_cap]
-  uint32_t *cs_val;      // [2][ctiles_cap][GS_CS_NC]
+  uint32_t *ccnt;        // [GS_CS_NC][cgrid_cap] k_cand_flags: class counts per CTA -> exclusive prefixes
+  int32_t cgrid_cap;
   uint32_t *fs_status;   // [ftiles_cap]
   uint32_t *fs_val;      // [2][ftiles_cap][GS_FS_NC]
   int32_t Fcap, Ccap, ftiles_cap, ctiles_cap;
@@ -145,7 +145,7 @@ void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid
 // by_rows: sampled layer (fan > 0) -> one thread per (row, four picks); else candidate-parallel (fan = -1)
 void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
                       cudaStream_t st);
-void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st);
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, cudaStream_t st);
 void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
                     cudaStream_t st);
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,

@@ -44,7 +44,7 @@
 #define GS_MINB_EXPAND 4
 #endif
 #ifndef GS_MINB_CAND
-#define GS_MINB_CAND 3
+#define GS_MINB_CAND 5
 #endif
 #define GS_BOUNDS __launch_bounds__(GS_TPB)
 
@@ -840,8 +840,11 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
     PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
     uint32_t n_new = 0u;
     if (item < nitems) {
-      uint32_t row = __umulhi(item, nbm);
-      if (row * nb > item) row--;
+      uint32_t row = item;  // nb == 1: ceil(2^32 / nb) does not fit the magic word
+      if (nb > 1u) {
+        row = __umulhi(item, nbm);
+        if (row * nb > item) row--;
+      }
       const uint32_t b = item - row * nb;
       const int4 ri = ws.rowinfo[row];
       const uint32_t o = ws.off[row], c = ws.off[row + 1] - o;
@@ -961,63 +964,29 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
 }
 
 // ------------------------------------------------------------------- k_cand
-// The one pass over the candidate stream.  With every minimum in place:
+// Two lean passes over the candidate stream, both with every minimum in place:
 //   edge of a NEW node v at p:   first occurrence iff table[v] holds p  -> in_nodes of its
 //                                owner's part (bipartite.cpp:4) and the next frontier (slicer.cpp:45-49);
 //   edge of frontier ROW idx:    first edge occurrence iff ea[idx] == p -> in_nodes; it is the node's
 //                                frontier slot only if it precedes the row's self entry (p < off[idx]);
-//   self entry of row i at s:    frontier slot iff no edge of the node came earlier (ea[i] > s); it also
-//                                samples the running per-part edge counts (rowscan: the row's CSR row
-//                                pointer in every part) for rowside_role.
-// Ranks = exclusive prefix over positions of 1 + 2 P counters (next-frontier
-// firsts, in_nodes firsts and edges per part): per-thread packed counts (one byte
-// per part), one packed warp scan per kind.  A first occurrence records its
-// in_nodes rank at its own position in the (now dead) candidate word: that is the
-// relabel map (DuplicateRemover::mask, duplicate.cpp:21) indexed by position,
-// which relabel_role and rowside_role read for every later occurrence.
-//
-// A CTA takes a RUN of up to CS_RMAX consecutive tiles (ticket order) and goes
-// over it twice.  Sweep 1 reads the stream, does the random reads (table / ea /
-// off), classifies every candidate and keeps what the random reads returned in
-// shared memory; its per-(tile, warp) class totals, scanned in place, are the
-// run's aggregate.  ONE flat look-back per run turns that into the run's
-// exclusive prefix.  Sweep 2 replays the run from shared memory: packed warp
-// scans give every item its rank, the lists are written at their final place.
-// Each candidate is read from the stream twice (the second time out of L1/L2)
-// and looked up in the table once.
+//   self entry of row i at s:    frontier slot iff no edge of the node came earlier (ea[i] > s).
+// k_cand_flags does the random reads (table / ea / off), leaves the verdict in the
+// flag byte (GS_CF_FIRST / GS_CF_FFIRST) and, for every edge that is NOT a first
+// occurrence, the position of the first one in the candidate word; it counts the
+// 1 + 2 P classes per CTA and its last CTA turns the counts into prefixes.
+// k_cand_apply reads stream and prefixes only: ranks by packed warp scans, lists
+// written at their final place.
+// (Measured, profiles/README.md: the single-launch form of the two -- runs of tiles
+// kept in shared memory between the sweeps, one look-back per run -- takes the same
+// 73 us alone on layer 2 but needs 37 KB of shared memory and 80 registers per CTA
+// and parks every CTA at a grid-wide wait, so that other minibatches' kernels find
+// no SM slots: 4.1 K minibatches/s against the split form's rate.)
 #define CS_NF 0
 #define CS_IN(q) (1 + (q))
 #define CS_E(q) (9 + (q))
 #define CS_USED 17
-#define CS_RMAX 8           // tiles of one run (held in shared memory between the two sweeps)
-#define CS_BEFORE 0x80000000u  // frontier-row edge: it precedes the row's self entry (positions are < 2^30)
-
-struct __align__(16) CandSmem {
-  uint32_t x[CS_RMAX][GS_TILE];            // minimum position: of an edge's source / of a self entry's node as a source
-  uint16_t wt[CS_RMAX][GS_NW][GS_CS_NC];   // class totals per (tile, warp) -> exclusive prefix inside the run
-  uint32_t red[GS_NW][GS_CS_NC];
-  uint32_t agg[GS_CS_NC], pre[GS_CS_NC];
-  int32_t fo_in[GS_MAX_PARTS], fo_ix[GS_MAX_PARTS];
-  int run;
-};
-
-// class of one candidate; bit 8: in_nodes first, bit 9: frontier first
-template <typename PK>
-__device__ __forceinline__ uint32_t cand_class(uint32_t fl, uint32_t p, uint32_t x, PK &pi, PK &pe, uint32_t &nf) {
-  const uint32_t kind = fl & GS_CK_MASK;
-  const int g = (int)((fl >> GS_CF_PART_SHIFT) & 7u);
-  if (kind == GS_CK_SELF) {
-    if (x > p) { fl |= 0x200u; nf++; }
-  } else if (kind != GS_CK_DEAD) {
-    pe += pkt_one<PK>(g);
-    if ((x & ~CS_BEFORE) == p) {
-      fl |= 0x100u;
-      pi += pkt_one<PK>(g);
-      if (kind == GS_CK_EDGE || (x & CS_BEFORE)) { fl |= 0x200u; nf++; }
-    }
-  }
-  return fl;
-}
+#define GS_CF_FIRST 0x04u   // first occurrence as an edge source -> in_nodes of its part
+#define GS_CF_FFIRST 0x08u  // first occurrence in the layer's stream -> next frontier
 
 __device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t C, uint32_t (&fl)[GS_IPT],
                                           int32_t (&ci)[GS_IPT]) {
@@ -1040,149 +1009,207 @@ __device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t 
 }
 
 template <typename PK>
-__device__ void cand_role(const GsWs &ws, int layer, CandSmem &sm) {
+__device__ void cand_flags_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
+  __shared__ uint32_t s_cnt[GS_CS_NC];
+  __shared__ uint32_t s_tot[GS_CS_NC];
   const Tbl tbl(ws);
+  const uint32_t C = (uint32_t)h->cand_len[layer];
+  const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
+  const GsState stt = *ws.state;
+  const Tag tag(ws, stt);
+  const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);
+  const int lane = lane_id();
+  if (threadIdx.x < GS_CS_NC) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  uint32_t acc_i = 0u, acc_e = 0u, acc_f = 0u;  // lane q < 8: this warp's running counts of part q
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  for (int t = t0; t < t1; t++) {
+    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
+    uint32_t fl[GS_IPT];
+    int32_t ci[GS_IPT];
+    cand_load(ws, p0, C, fl, ci);
+    uint32_t x[GS_IPT], s[GS_IPT];
+#pragma unroll
+    for (int i = 0; i < GS_IPT; i++) {
+      const uint32_t kind = fl[i] & GS_CK_MASK;
+      x[i] = GS_INF; s[i] = 0u;
+      if (kind == GS_CK_EDGE) {
+        x[i] = tbl.ld(ci[i]) & tag.pmask;
+      } else if (kind != GS_CK_DEAD) {
+        x[i] = __ldcg(rw_ea + ci[i]);
+        if (kind == GS_CK_FHIT) s[i] = __ldcg(ws.off + ci[i]);
+      }
+    }
+    PK pi = 0, pe = 0;
+    uint32_t nf = 0u;
+    bool moved = false;
+#pragma unroll
+    for (int i = 0; i < GS_IPT; i++) {
+      const uint32_t p = p0 + i, kind = fl[i] & GS_CK_MASK;
+      const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
+      if (kind == GS_CK_SELF) {
+        if (x[i] > p) { fl[i] |= GS_CF_FFIRST; nf++; }
+      } else if (kind != GS_CK_DEAD) {
+        pe += pkt_one<PK>(g);
+        if (x[i] == p) {
+          fl[i] |= GS_CF_FIRST;
+          pi += pkt_one<PK>(g);
+          if (kind == GS_CK_EDGE || p < s[i]) { fl[i] |= GS_CF_FFIRST; nf++; }
+        } else {
+          ci[i] = (int32_t)x[i];  // position of the source's first occurrence: all a later pass needs
+          moved = true;
+        }
+      }
+    }
+    if (p0 + GS_IPT <= C) {
+      if (moved) *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
+          make_uchar4((unsigned char)fl[0], (unsigned char)fl[1], (unsigned char)fl[2], (unsigned char)fl[3]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < GS_IPT; i++)
+        if (p0 + i < C) {
+          ws.cand[p0 + i] = ci[i];
+          ws.cflag[p0 + i] = (uint8_t)fl[i];
+        }
+    }
+    pi = pkt_redux(pi);
+    pe = pkt_redux(pe);
+    nf = __reduce_add_sync(FULL, nf);
+    if (lane < (int)sizeof(PK)) {
+      acc_i += pkt_get<PK>(pi, lane);
+      acc_e += pkt_get<PK>(pe, lane);
+    }
+    acc_f += nf;
+  }
+  if (lane < 8) {
+    if (acc_i) atomicAdd(&s_cnt[CS_IN(lane)], acc_i);
+    if (acc_e) atomicAdd(&s_cnt[CS_E(lane)], acc_e);
+  }
+  if (lane == 8 && acc_f) atomicAdd(&s_cnt[CS_NF], acc_f);
+  __syncthreads();
+  if (threadIdx.x < CS_USED) ws.ccnt[(size_t)threadIdx.x * ws.cgrid_cap + blockIdx.x] = s_cnt[threadIdx.x];
+  if (!last_block(ws.tickets + layer * GS_TICKETS + 2)) return;
+  spine_scan<GS_CS_NC>(ws.ccnt, ws.cgrid_cap, (int)gridDim.x, CS_USED, s_tot, nullptr);
+}
+
+// Second pass: ranks and lists.  Same contiguous runs of tiles per CTA as
+// cand_flags_role (cta_tiles), so a CTA starts from its spine prefix and carries
+// the running class counts across its own tiles in shared memory.
+template <typename PK>
+__device__ void cand_apply_role(const GsWs &ws, int layer) {
+  gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_wc[GS_NW][GS_CS_NC];    // per-warp class totals of the tile
+  __shared__ uint32_t s_base[GS_NW][GS_CS_NC];  // CTA prefix + earlier tiles + earlier warps of the tile
+  __shared__ uint32_t s_run[2][GS_CS_NC];       // running class counts at the start of a tile (ping-pong)
+  __shared__ int32_t s_fo_in[GS_MAX_PARTS], s_fo_ix[GS_MAX_PARTS];
   const int P = ws.P;
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
-  if (ntiles == 0) return;
-  const int R = min(CS_RMAX, (ntiles + (int)gridDim.x - 1) / (int)gridDim.x);
-  const int nruns = (ntiles + R - 1) / R;
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   int32_t *fnext = ws.fslab + h->frontier[layer + 1].off;
-  const GsState stt = *ws.state;
-  const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 1u;
-  const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);  // per-row arrays ping-pong by layer
-  const Tag tag(ws, stt);
-  uint32_t *cs_agg = ws.cs_val, *cs_inc = ws.cs_val + (size_t)ws.ctiles_cap * GS_CS_NC;
-  uint32_t *tick = ws.tickets + layer * GS_TICKETS + 2;
   const int lane = lane_id(), w = warp_id();
   const size_t rs_stride = sizeof(PK);  // rowscan: one record of 4 (P <= 4) or 8 words per row
   if (threadIdx.x < P) {
-    sm.fo_in[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
-    sm.fo_ix[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
+    s_fo_in[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
+    s_fo_ix[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
   }
-  for (;;) {
-    __syncthreads();  // the previous run's shared memory is no longer read
-    if (threadIdx.x == 0) sm.run = (int)atomicAdd(tick, 1u);
+  int t0, t1;
+  cta_tiles(ntiles, t0, t1);
+  if (threadIdx.x < GS_CS_NC)
+    s_run[t0 & 1][threadIdx.x] =
+        threadIdx.x < CS_USED ? ws.ccnt[(size_t)threadIdx.x * ws.cgrid_cap + blockIdx.x] : 0u;
+  for (int t = t0; t < t1; t++) {
     __syncthreads();
-    const int r = sm.run;
-    if (r >= nruns) break;
-    const int t_lo = r * R, nt = min(R, ntiles - t_lo);
-    // ---- sweep 1: random reads, classes, totals
-    for (int k = 0; k < nt; k++) {
-      const uint32_t p0 = (uint32_t)(t_lo + k) * GS_TILE + GS_IPT * threadIdx.x;
-      uint32_t fl[GS_IPT];
-      int32_t ci[GS_IPT];
-      cand_load(ws, p0, C, fl, ci);
-      uint32_t x[GS_IPT], s[GS_IPT];
+    const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
+    const bool full = p0 + GS_IPT <= C;
+    uint32_t fl[GS_IPT];
+    int32_t ci[GS_IPT];
+    cand_load(ws, p0, C, fl, ci);
+    PK pi = 0, pe = 0;
+    uint32_t nf = 0u;
 #pragma unroll
-      for (int i = 0; i < GS_IPT; i++) {
-        const uint32_t kind = fl[i] & GS_CK_MASK;
-        x[i] = GS_INF; s[i] = 0u;
-        if (kind == GS_CK_EDGE) {
-          x[i] = tbl.ld(ci[i]) & tag.pmask;
-        } else if (kind != GS_CK_DEAD) {
-          x[i] = __ldcg(rw_ea + ci[i]);
-          if (kind == GS_CK_FHIT) s[i] = __ldcg(ws.off + ci[i]);
-        }
-      }
-      PK pi = 0, pe = 0;
-      uint32_t nf = 0u;
-#pragma unroll
-      for (int i = 0; i < GS_IPT; i++) {
-        if ((fl[i] & GS_CK_MASK) == GS_CK_FHIT && (p0 + i) < s[i]) x[i] |= CS_BEFORE;
-        cand_class<PK>(fl[i], p0 + i, x[i], pi, pe, nf);
-      }
-      *reinterpret_cast<uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]) = make_uint4(x[0], x[1], x[2], x[3]);
-      pi = pkt_redux(pi);
-      pe = pkt_redux(pe);
-      nf = __reduce_add_sync(FULL, nf);
+    for (int i = 0; i < GS_IPT; i++) {
+      const uint32_t kind = fl[i] & GS_CK_MASK;
+      const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
+      if (kind == GS_CK_EDGE || kind == GS_CK_FHIT) pe += pkt_one<PK>(g);
+      if (fl[i] & GS_CF_FIRST) pi += pkt_one<PK>(g);
+      nf += (fl[i] & GS_CF_FFIRST) ? 1u : 0u;
+    }
+    const PK inc_i = pkt_incl(pi), inc_e = pkt_incl(pe);
+    const uint32_t inc_f = warp_incl_scan(nf);
+    {
+      const PK t_i = __shfl_sync(FULL, inc_i, 31), t_e = __shfl_sync(FULL, inc_e, 31);
+      const uint32_t t_f = __shfl_sync(FULL, inc_f, 31);
       if (lane < 8) {
-        sm.wt[k][w][CS_IN(lane)] = (uint16_t)(lane < (int)sizeof(PK) ? pkt_get<PK>(pi, lane) : 0u);
-        sm.wt[k][w][CS_E(lane)] = (uint16_t)(lane < (int)sizeof(PK) ? pkt_get<PK>(pe, lane) : 0u);
+        const bool in = lane < (int)sizeof(PK);
+        s_wc[w][CS_IN(lane)] = in ? pkt_get<PK>(t_i, lane) : 0u;
+        s_wc[w][CS_E(lane)] = in ? pkt_get<PK>(t_e, lane) : 0u;
       }
-      if (lane == 8) sm.wt[k][w][CS_NF] = (uint16_t)nf;
+      if (lane == 8) s_wc[w][CS_NF] = t_f;
     }
     __syncthreads();
-    if (threadIdx.x < GS_CS_NC) {  // totals -> exclusive prefix over the run's (tile, warp) sequence
-      uint32_t run = 0u;
-      if (threadIdx.x < CS_USED)
-        for (int k = 0; k < nt; k++)
+    if (lane < CS_USED) {  // lane = class: this warp's base; warp 0 also advances the running counts
+      uint32_t a = s_run[t & 1][lane];
+      if (w == 0) {
+        uint32_t all = 0u;
 #pragma unroll
-          for (int ww = 0; ww < GS_NW; ww++) {
-            const uint32_t tq = sm.wt[k][ww][threadIdx.x];
-            sm.wt[k][ww][threadIdx.x] = (uint16_t)run;
-            run += tq;
-          }
-      sm.agg[threadIdx.x] = run;
-    }
-    __syncthreads();
-    flat_lookback<uint32_t, CS_USED, GS_CS_NC>(ws.cs_status, cs_agg, cs_inc, r, ep, sm.agg, sm.pre, sm.red);
-    // ---- sweep 2: ranks and lists
-    for (int k = 0; k < nt; k++) {
-      const uint32_t p0 = (uint32_t)(t_lo + k) * GS_TILE + GS_IPT * threadIdx.x;
-      const bool full = p0 + GS_IPT <= C;
-      uint32_t fl[GS_IPT];
-      int32_t ci[GS_IPT];
-      cand_load(ws, p0, C, fl, ci);
-      const uint4 x4 = *reinterpret_cast<const uint4 *>(&sm.x[k][GS_IPT * threadIdx.x]);
-      const uint32_t x[GS_IPT] = {x4.x, x4.y, x4.z, x4.w};
-      PK pi = 0, pe = 0;
-      uint32_t nf = 0u;
-#pragma unroll
-      for (int i = 0; i < GS_IPT; i++) fl[i] = cand_class<PK>(fl[i], p0 + i, x[i], pi, pe, nf);
-      const PK inc_i = pkt_incl(pi), inc_e = pkt_incl(pe);
-      const uint32_t inc_f = warp_incl_scan(nf);
-      const uint16_t *wtb = sm.wt[k][w];
-#define CS_B(c) (sm.pre[c] + (uint32_t)wtb[c])
-      uint32_t rf = CS_B(CS_NF) + inc_f - nf;
-      PK ri = inc_i - pi, re = inc_e - pe;
-      bool wrote = false;
-#pragma unroll
-      for (int i = 0; i < GS_IPT; i++) {
-        const uint32_t kind = fl[i] & GS_CK_MASK;
-        const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
-        if (kind == GS_CK_SELF) {
-          if (fl[i] & 0x200u) fnext[rf++] = front[ci[i]];
-          // edges of every part emitted before this row: its CSR row pointers, one record per row
-          uint4 *rsp = reinterpret_cast<uint4 *>(ws.rowscan + (size_t)ci[i] * rs_stride);
-          rsp[0] = make_uint4(CS_B(CS_E(0)) + pkt_get<PK>(re, 0), CS_B(CS_E(1)) + pkt_get<PK>(re, 1),
-                              CS_B(CS_E(2)) + pkt_get<PK>(re, 2), CS_B(CS_E(3)) + pkt_get<PK>(re, 3));
-          if (sizeof(PK) > 4)
-            rsp[1] = make_uint4(CS_B(CS_E(4)) + pkt_get<PK>(re, 4), CS_B(CS_E(5)) + pkt_get<PK>(re, 5),
-                                CS_B(CS_E(6)) + pkt_get<PK>(re, 6), CS_B(CS_E(7)) + pkt_get<PK>(re, 7));
-        } else if (kind != GS_CK_DEAD) {
-          const uint32_t ex = CS_B(CS_E(g)) + pkt_get<PK>(re, g);
-          if (fl[i] & 0x100u) {
-            // the first edge occurrence of a source knows its rank: final csr_indices
-            // value, in_nodes entry, relabel map entry; every other edge leaves ~m
-            // (m = position of that first occurrence) for relabel_role
-            const uint32_t rk = CS_B(CS_IN(g)) + pkt_get<PK>(ri, g);
-            const int32_t z = kind == GS_CK_FHIT ? front[ci[i]] : ci[i];  // a new node carries its id, a frontier row its index
-            ws.slab[sm.fo_in[g] + rk] = z;
-            ws.slab[sm.fo_ix[g] + ex] = (int32_t)rk;
-            if (fl[i] & 0x200u) fnext[rf++] = z;
-            ci[i] = (int32_t)rk;
-            wrote = true;
-            ri += pkt_one<PK>(g);
-          } else {
-            ws.slab[sm.fo_ix[g] + ex] = (int32_t)~(x[i] & ~CS_BEFORE);
-          }
-          re += pkt_one<PK>(g);
-        }
+        for (int k = 0; k < GS_NW; k++) all += s_wc[k][lane];
+        s_run[(t + 1) & 1][lane] = a + all;
+      } else {
+        for (int k = 0; k < w; k++) a += s_wc[k][lane];
       }
-#undef CS_B
-      if (wrote) {
-        if (full) {
-          *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      s_base[w][lane] = a;
+    }
+    __syncwarp();
+    const uint32_t *bw = s_base[w];
+    uint32_t rf = bw[CS_NF] + inc_f - nf;
+    PK ri = inc_i - pi, re = inc_e - pe;
+    bool wrote = false;
+#pragma unroll
+    for (int i = 0; i < GS_IPT; i++) {
+      const uint32_t kind = fl[i] & GS_CK_MASK;
+      const int g = (int)((fl[i] >> GS_CF_PART_SHIFT) & 7u);
+      if (kind == GS_CK_SELF) {
+        if (fl[i] & GS_CF_FFIRST) fnext[rf++] = front[ci[i]];
+        // edges of every part emitted before this row: its CSR row pointers, one record per row
+        uint4 *rsp = reinterpret_cast<uint4 *>(ws.rowscan + (size_t)ci[i] * rs_stride);
+        rsp[0] = make_uint4(bw[CS_E(0)] + pkt_get<PK>(re, 0), bw[CS_E(1)] + pkt_get<PK>(re, 1),
+                            bw[CS_E(2)] + pkt_get<PK>(re, 2), bw[CS_E(3)] + pkt_get<PK>(re, 3));
+        if (sizeof(PK) > 4)
+          rsp[1] = make_uint4(bw[CS_E(4)] + pkt_get<PK>(re, 4), bw[CS_E(5)] + pkt_get<PK>(re, 5),
+                              bw[CS_E(6)] + pkt_get<PK>(re, 6), bw[CS_E(7)] + pkt_get<PK>(re, 7));
+      } else if (kind != GS_CK_DEAD) {
+        const uint32_t ex = bw[CS_E(g)] + pkt_get<PK>(re, g);
+        if (fl[i] & GS_CF_FIRST) {
+          // the first edge occurrence of a source knows its rank: final csr_indices value,
+          // in_nodes entry, relabel map entry; every other edge carries the position m of
+          // that first occurrence and leaves ~m for relabel_role
+          const uint32_t rk = bw[CS_IN(g)] + pkt_get<PK>(ri, g);
+          const int32_t z = kind == GS_CK_FHIT ? front[ci[i]] : ci[i];  // a new node carries its id, a frontier row its index
+          ws.slab[s_fo_in[g] + rk] = z;
+          ws.slab[s_fo_ix[g] + ex] = (int32_t)rk;
+          if (fl[i] & GS_CF_FFIRST) fnext[rf++] = z;
+          ci[i] = (int32_t)rk;
+          wrote = true;
+          ri += pkt_one<PK>(g);
         } else {
-#pragma unroll
-          for (int i = 0; i < GS_IPT; i++)
-            if (p0 + i < C && (fl[i] & 0x100u)) ws.cand[p0 + i] = ci[i];
+          ws.slab[s_fo_ix[g] + ex] = ~ci[i];
         }
+        re += pkt_one<PK>(g);
+      }
+    }
+    if (wrote) {
+      if (full) {
+        *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < GS_IPT; i++)
+          if (p0 + i < C && (fl[i] & GS_CF_FIRST)) ws.cand[p0 + i] = ci[i];
       }
     }
   }
@@ -1437,12 +1464,19 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand_rows(const Gs
 }
 
 template <bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand(const GsWs *__restrict__ wsv, int layer) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand_flags(const GsWs *__restrict__ wsv, int layer) {
   typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
-  __shared__ CandSmem sm;
   stage_ws(ws, wsv + blockIdx.y);
-  cand_role<PK>(ws, layer, sm);
+  cand_flags_role<PK>(ws, layer);
+}
+
+template <bool WIDE>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand_apply(const GsWs *__restrict__ wsv, int layer) {
+  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  cand_apply_role<PK>(ws, layer);
 }
 
 // Last launch of a sample: relabel and row side of the last layer, the fused
@@ -1481,7 +1515,6 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_tail(const GsWs *__res
       ws.rs_status[i] = 0u;
       ws.fs_status[i] = 0u;
     }
-    for (int64_t i = tid; i < ws.ctiles_cap; i += nth) ws.cs_status[i] = 0u;
   }
   if (!last_block(ws.tickets + L * GS_TICKETS)) return;
   for (int i = threadIdx.x; i < L * GS_CNT_STRIDE; i += GS_TPB) ws.cnt[i] = 0u;
@@ -1718,9 +1751,16 @@ void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, boo
   if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
   else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
 }
-void gs_launch_cand(const GsWs *wsv, int members, bool wide, int layer, int grid, cudaStream_t st) {
-  if (wide) k_cand<true><<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
-  else k_cand<false><<<dim3(grid, members), GS_TPB, 0, st>>>(wsv, layer);
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, cudaStream_t st) {
+  // pass 0: flags, 1: apply.  Both must be given the same grid: a CTA's run of tiles is the same in both.
+  const dim3 g(grid, members);
+  if (pass == 0) {
+    if (wide) k_cand_flags<true><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    else k_cand_flags<false><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  } else {
+    if (wide) k_cand_apply<true><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    else k_cand_apply<false><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  }
 }
 void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
                     cudaStream_t st) {
