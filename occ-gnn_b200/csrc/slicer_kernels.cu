@@ -38,10 +38,10 @@
 // how many warps of all the launches in flight fit an SM.  ptxas -v at these
 // caps: k_rows 80 registers (64 B of spills), k_expand 63, k_cand 80, no spills.
 #ifndef GS_MINB_ROWS
-#define GS_MINB_ROWS 3
+#define GS_MINB_ROWS 4
 #endif
 #ifndef GS_MINB_EXPAND
-#define GS_MINB_EXPAND 4
+#define GS_MINB_EXPAND 5
 #endif
 #ifndef GS_MINB_CAND
 #define GS_MINB_CAND 5
@@ -182,9 +182,10 @@ __device__ __forceinline__ uint32_t warp_sum_t(uint32_t v) { return __reduce_add
 
 template <typename T, int NC, int NCPAD>
 __device__ __forceinline__ void flat_lookback(uint32_t *status, T *agg, T *inc, int r, uint32_t ep,
-                                              const T *s_mine, T *s_pre, T (*s_red)[NCPAD]) {
-  const int tid = threadIdx.x, lane = lane_id(), w = warp_id();
+                                              const T *s_mine, T *s_pre, T (*/*unused*/)[NCPAD]) {
+  const int tid = threadIdx.x;
   if (tid < NC) agg[(size_t)r * NCPAD + tid] = s_mine[tid];
+  if (tid < NCPAD) s_pre[tid] = (T)0;
   __threadfence();
   __syncthreads();
   if (tid == 0) {
@@ -192,52 +193,47 @@ __device__ __forceinline__ void flat_lookback(uint32_t *status, T *agg, T *inc, 
     st_release(status + r, (ep << 2) | 1u);
   }
   const int base = r & ~(GS_TPB - 1);
-  const int j = base + tid;
-  T v[NC];
-#pragma unroll
-  for (int c = 0; c < NC; c++) v[c] = (T)0;
-  if (j < r) {
-    for (;;) {
-      const uint32_t st = ld_acquire(status + j);
-      if ((st >> 2) == ep && (st & 3u) != 0u) break;
-      __nanosleep(64);
-    }
-    const T *a = agg + (size_t)j * NCPAD;
-#pragma unroll
-    for (int c = 0; c < NC; c++) v[c] = __ldcg(a + c);
-  }
-  T carry = (T)0;
-  if (base > 0 && tid < NC) {  // inclusive prefix of the unit before this chunk
-    for (;;) {
-      const uint32_t st = ld_acquire(status + base - 1);
-      if ((st >> 2) == ep && (st & 3u) == 2u) break;
-      __nanosleep(64);
-    }
-    carry = __ldcg(inc + (size_t)(base - 1) * NCPAD + tid);
-  }
-  if (base < r) {  // CTA-wide sum per counter (uniform branch)
-#pragma unroll
-    for (int c = 0; c < NC; c++) {
-      const T sum = warp_sum_t(v[c]);
-      if (lane == (c & 31)) s_red[w][c] = sum;
-    }
+  {  // every predecessor of this chunk has published its aggregate (thread j watches unit base + j)
+    const int j = base + tid;
+    if (j < r)
+      for (;;) {
+        const uint32_t st = ld_acquire(status + j);
+        if ((st >> 2) == ep && (st & 3u) != 0u) break;
+        __nanosleep(64);
+      }
+    if (base > 0 && tid == GS_TPB - 1)  // ... and the unit before the chunk its inclusive prefix
+      for (;;) {
+        const uint32_t st = ld_acquire(status + base - 1);
+        if ((st >> 2) == ep && (st & 3u) == 2u) break;
+        __nanosleep(64);
+      }
   }
   __syncthreads();
-  const bool pub = (r & (GS_TPB - 1)) == GS_TPB - 1;
-  if (tid < NC) {
-    T tot = carry;
-    if (base < r) {
-#pragma unroll
-      for (int k = 0; k < GS_NW; k++) tot += s_red[k][tid];
+  // thread (ju, c) sums counter c over the units base + ju, base + ju + UPP, ...: independent
+  // loads, one register of state; shared-memory atomics finish the sum
+  constexpr int UPP = GS_TPB / NCPAD;
+  const int c = tid % NCPAD, ju = tid / NCPAD;
+  if (ju < UPP && c < NC) {
+    T sum = (T)0;
+    int j = base + ju;
+    for (; j + 3 * UPP < r; j += 4 * UPP) {
+      const T a0 = __ldcg(agg + (size_t)j * NCPAD + c), a1 = __ldcg(agg + (size_t)(j + UPP) * NCPAD + c),
+              a2 = __ldcg(agg + (size_t)(j + 2 * UPP) * NCPAD + c), a3 = __ldcg(agg + (size_t)(j + 3 * UPP) * NCPAD + c);
+      sum += a0 + a1 + a2 + a3;
     }
-    s_pre[tid] = tot;
-    if (pub) inc[(size_t)r * NCPAD + tid] = tot + s_mine[tid];
+    for (; j < r; j += UPP) sum += __ldcg(agg + (size_t)j * NCPAD + c);
+    if (base > 0 && ju == 0) sum += __ldcg(inc + (size_t)(base - 1) * NCPAD + c);
+    if (sum != (T)0) atomicAdd(&s_pre[c], sum);
   }
-  if (pub) __threadfence();
   __syncthreads();
-  if (pub && tid == 0) {
+  if ((r & (GS_TPB - 1)) == GS_TPB - 1) {  // last unit of a chunk: publish the inclusive prefix
+    if (tid < NC) inc[(size_t)r * NCPAD + tid] = s_pre[tid] + s_mine[tid];
     __threadfence();
-    st_release(status + r, (ep << 2) | 2u);
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      st_release(status + r, (ep << 2) | 2u);
+    }
   }
 }
 
