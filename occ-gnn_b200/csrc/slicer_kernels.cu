@@ -41,10 +41,10 @@
 #define GS_MINB_ROWS 4
 #endif
 #ifndef GS_MINB_EXPAND
-#define GS_MINB_EXPAND 5
+#define GS_MINB_EXPAND 6
 #endif
 #ifndef GS_MINB_CAND
-#define GS_MINB_CAND 5
+#define GS_MINB_CAND 6
 #endif
 #define GS_BOUNDS __launch_bounds__(GS_TPB)
 
@@ -173,16 +173,11 @@ __device__ __forceinline__ void stage_ws(GsWs &dst, const GsWs *__restrict__ src
 // unit publishes.  Status words carry the sample's scan epoch, so descriptors are
 // never reset (k_tail zeroes them once per 2^30 uses).  Called by the whole CTA;
 // s_mine[] must be visible (barrier) on entry, s_pre[] is on exit.
-__device__ __forceinline__ unsigned long long warp_sum_t(unsigned long long v) {
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
-  return v;
-}
-__device__ __forceinline__ uint32_t warp_sum_t(uint32_t v) { return __reduce_add_sync(FULL, v); }
-
+// Two halves, so that a caller can do the work that does not need the prefix between them
+// (it then overlaps the wait for the predecessors).
 template <typename T, int NC, int NCPAD>
-__device__ __forceinline__ void flat_lookback(uint32_t *status, T *agg, T *inc, int r, uint32_t ep,
-                                              const T *s_mine, T *s_pre, T (*/*unused*/)[NCPAD]) {
+__device__ __forceinline__ void lookback_publish(uint32_t *status, T *agg, int r, uint32_t ep, const T *s_mine,
+                                                 T *s_pre) {
   const int tid = threadIdx.x;
   if (tid < NC) agg[(size_t)r * NCPAD + tid] = s_mine[tid];
   if (tid < NCPAD) s_pre[tid] = (T)0;
@@ -192,6 +187,11 @@ __device__ __forceinline__ void flat_lookback(uint32_t *status, T *agg, T *inc, 
     __threadfence();
     st_release(status + r, (ep << 2) | 1u);
   }
+}
+template <typename T, int NC, int NCPAD>
+__device__ __forceinline__ void lookback_collect(uint32_t *status, T *agg, T *inc, int r, uint32_t ep,
+                                                 const T *s_mine, T *s_pre) {
+  const int tid = threadIdx.x;
   const int base = r & ~(GS_TPB - 1);
   {  // every predecessor of this chunk has published its aggregate (thread j watches unit base + j)
     const int j = base + tid;
@@ -277,7 +277,6 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   __shared__ unsigned long long s_wc[GS_NW][GS_RS_NC];
   __shared__ unsigned long long s_base[GS_NW][GS_RS_NC];
   __shared__ unsigned long long s_agg[GS_RS_NC], s_pre[GS_RS_NC];
-  __shared__ unsigned long long s_red[GS_NW][GS_RS_NC];
   __shared__ int s_tile;
   if (!FIRST && h->status != 0) return;
   if (threadIdx.x < GS_RS_NC) s_agg[threadIdx.x] = 0ull;  // counters beyond 2 + P stay zero
@@ -400,9 +399,29 @@ __device__ void rows_role(const GsWs &ws, int layer) {
       if (w == 0) s_agg[lane] = all;
     }
     __syncthreads();
-    flat_lookback<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, s_agg, s_pre,
-                                                                   s_red);
-    if (FIRST && bad) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);
+    lookback_publish<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, t, ep, s_agg, s_pre);
+    // everything that does not need the prefix goes out while the predecessors' aggregates arrive
+    bool dup = false;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      const int i = i0 + k;
+      if (i < F) {
+        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
+                                  (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
+        rw_ea[i] = GS_INF;
+        rw_rowhas[i] = 0u;
+        if (FIRST) {
+          ws.fslab[i] = nd[k];
+          // a second claim of the same entry under this sample's tag is a duplicate seed
+          const uint32_t old = atomicMin(ws.table + nd[k], tag.tg | (uint32_t)i);
+          if (tag.mine(old)) dup = true;
+        } else {
+          tbl.st(nd[k], tag.tg | (uint32_t)i);
+        }
+      }
+    }
+    lookback_collect<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, s_agg, s_pre);
+    if (FIRST && (bad || dup)) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);  // after the look-back: behind init_header
     unsigned long long base_c = s_pre[0] + s_base[w][0] + inc_c - c4;
     uint32_t base_s = (uint32_t)(s_pre[1] + s_base[w][1]) + inc_s - s4;
     unsigned long long r_pk = inc_pk - pk4;
@@ -412,22 +431,8 @@ __device__ void rows_role(const GsWs &ws, int layer) {
       if (i < F) {
         const uint32_t o = (uint32_t)base_c;
         ws.off[i] = o;
-        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
-                                  (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
         rw_selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
-        rw_ea[i] = GS_INF;
-        rw_rowhas[i] = 0u;
         if (replay) ws.samp_rank[i] = base_s;
-        if (FIRST) {
-          ws.fslab[i] = nd[k];
-          // a second claim of the same entry under this sample's tag is a duplicate seed
-          if (!bad || nd[k] != 0 || ws.seeds_in[i] == 0) {
-            const uint32_t old = atomicMin(ws.table + nd[k], tag.tg | (uint32_t)i);
-            if (tag.mine(old)) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);
-          }
-        } else {
-          tbl.st(nd[k], tag.tg | (uint32_t)i);
-        }
         // candidate tiles that start inside this row (only the candidate-parallel k_expand of
         // fan = -1 layers looks rows up by position)
         const unsigned long long end = base_c + c[k];
@@ -1230,7 +1235,6 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
   __shared__ uint32_t s_wc[GS_NW][GS_FS_NC];
   __shared__ uint32_t s_base[GS_NW][GS_FS_NC];
   __shared__ uint32_t s_agg[GS_FS_NC], s_pre[GS_FS_NC];
-  __shared__ uint32_t s_red[GS_NW][GS_FS_NC];
   __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
   __shared__ int s_tile;
   if (h->status != 0) return;
@@ -1317,7 +1321,8 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
       s_agg[threadIdx.x] = run;
     }
     __syncthreads();
-    flat_lookback<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, fs_inc, t, ep, s_agg, s_pre, s_red);
+    lookback_publish<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, t, ep, s_agg, s_pre);
+    lookback_collect<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, fs_inc, t, ep, s_agg, s_pre);
 #define FS_B(c) (s_pre[c] + s_base[w][c])
     PK ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
 #pragma unroll
