@@ -274,6 +274,26 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
  * The reference has no counterpart (a CPU program). */
 int gs_bench_sector_probe(int device, int64_t table_bytes, int64_t n_reads, double *reads_per_s);
 
+/* Allocation-free frontier dedup.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * out_device[0..*count_host) = the distinct values of ids_device[0..n) in order of
+ * first occurrence -- the rule by which the slicer appends new nodes to a frontier
+ * (slicer.cpp:22-43), so for one seed whose neighbour list is `ids` it equals
+ * frontier 1 of gs_slicer_submit() minus the seed.  ids in [0, num_nodes).
+ * The dedup table, the per-CTA counts and the control words live in one static
+ * device array of 4 MiB + 4.25 KiB that every GPU loading the library holds until
+ * exit: num_nodes <= GS_NOALLOC_MAX_NODES and n <= GS_NOALLOC_MAX_IDS, larger
+ * sizes return GS_ERR_INVALID.  Calls no cudaMalloc / cudaFree; the caller owns
+ * ids_device and out_device (n int32 each, device memory).  Runs on the legacy
+ * default stream and returns when the result is complete.  All calls on a device
+ * share the array (cleared at the start of each call): calls that overlap on one
+ * GPU race -- serialise them. */
+#define GS_NOALLOC_MAX_NODES (1 << 20)
+#define GS_NOALLOC_MAX_IDS (1 << 24)
+int gs_unique_first_noalloc(int device, const int32_t *ids_device, int64_t n, int64_t num_nodes,
+                            int32_t *out_device, int64_t *count_host);
+
 /* Number of kernel launches one launch sequence performs (3 L + 1), shared by the
  * group_size minibatches of a group. */
 int gs_slicer_launches_per_sample(const gs_slicer *s);
