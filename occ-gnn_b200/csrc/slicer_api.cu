@@ -168,18 +168,38 @@ int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::ve
   const int L = s->cfg.num_layers;
   if ((rc = mark("start"))) return rc;
   const bool wide = s->cfg.num_parts > 4;
+  // DIAGNOSTIC ONLY (tools/chain_cost.py): GSPLIT_DIAG_STOP=k launches the first k kernels of the
+  // chain and a tail that only does the slot's housekeeping -- the samples are incomplete; the
+  // difference of two such rates is the machine time kernel k costs with all slots in flight.
+  static const int stop = [] {
+    const char *e = getenv("GSPLIT_DIAG_STOP");
+    return e && *e ? atoi(e) : 1 << 20;
+  }();
+  // GSPLIT_DIAG_ROLES: bit 0 drops the relabel roles, bit 1 the row-side roles (lists left unwritten)
+  static const int roles_off = [] {
+    const char *e = getenv("GSPLIT_DIAG_ROLES");
+    return e && *e ? atoi(e) : 0;
+  }();
+  const bool relabel_on = !(roles_off & 1), rowside_on = !(roles_off & 2);
+  int nl = 0;
   for (int l = 0; l < L; l++) {
-    gs_launch_rows(gr.wsv, members, wide, l, s->grid_rows[l], l > 0 ? s->grid_relabel[l - 1] : 0,
-                   l > 0 ? s->grid_rows[l - 1] : 0, st);
+    if (nl++ < stop)
+      gs_launch_rows(gr.wsv, members, wide, l, s->grid_rows[l], l > 0 && relabel_on ? s->grid_relabel[l - 1] : 0,
+                     l > 0 && rowside_on ? s->grid_rows[l - 1] : 0, st);
     if ((rc = mark(l == 0 ? "rows" : "rows+relabel+rowside"))) return rc;
-    gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l], st);
+    if (nl++ < stop)
+      gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l], st);
     if ((rc = mark("expand"))) return rc;
-    gs_launch_cand(gr.wsv, members, wide, 0, l, s->grid_cand[l], st);
-    if ((rc = mark("cand_flags"))) return rc;
-    gs_launch_cand(gr.wsv, members, wide, 1, l, s->grid_cand[l], st);
+    if (nl++ < stop) gs_launch_cand(gr.wsv, members, wide, 0, l, s->grid_cand[l], s->grid_rows[l], st);
+    if ((rc = mark("cand_flags+rowcount"))) return rc;
+    if (nl++ < stop) gs_launch_cand(gr.wsv, members, wide, 1, l, s->grid_cand[l], 0, st);
     if ((rc = mark("cand_apply"))) return rc;
   }
-  gs_launch_tail(gr.wsv, members, wide, s->grid_relabel[L - 1], s->grid_rows[L - 1], s->feat ? s->grid_gather : 0, st);
+  if (nl < stop)
+    gs_launch_tail(gr.wsv, members, wide, relabel_on ? s->grid_relabel[L - 1] : 0, rowside_on ? s->grid_rows[L - 1] : 0,
+                   s->feat ? s->grid_gather : (roles_off ? 1 : 0), st);
+  else
+    gs_launch_tail(gr.wsv, members, wide, 0, 0, 1, st);
   if ((rc = mark(s->feat ? "relabel+rowside+gather_features+finish" : "relabel+rowside+finish"))) return rc;
   CU(cudaGetLastError());
   return GS_OK;
@@ -582,8 +602,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.rs_val, 2 * (size_t)ftiles * GS_RS_NC);
     w.cgrid_cap = s->grid;
     DA(w.ccnt, (size_t)GS_CS_NC * s->grid);
-    DA(w.fs_status, ftiles);
-    DA(w.fs_val, 2 * (size_t)ftiles * GS_FS_NC);
+    DA(w.fcnt, (size_t)GS_FS_NC * s->grid);
     if (s->feat) {
       w.feat = s->feat->rows;
       w.feat_slot = s->feat->slot_of;
@@ -602,7 +621,6 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     CUS(cudaMemset(w.cnt, 0, (size_t)L * GS_CNT_STRIDE * sizeof(uint32_t)));
     CUS(cudaMemset(w.tickets, 0, (size_t)(L + 1) * GS_TICKETS * sizeof(uint32_t)));
     CUS(cudaMemset(w.rs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
-    CUS(cudaMemset(w.fs_status, 0, (size_t)ftiles * sizeof(uint32_t)));
     CUS(cudaHostAlloc((void **)&sl.input, sizeof(GsInput), cudaHostAllocMapped));
     CUS(cudaHostAlloc((void **)&sl.seeds, (size_t)cfg->max_batch * sizeof(int64_t),
                       cudaHostAllocMapped));

@@ -30,7 +30,7 @@
 #define GS_CNT_OWN(P, q) (1 + 3 * (P) + (q))
 #define GS_CNT_TO(P, q) (1 + 4 * (P) + (q))
 #define GS_CNT_SELF(P, q) (1 + 5 * (P) + (q))  // rows owned by q (k_rows)
-#define GS_TICKETS 4                      // per layer: [0] k_rows tiles, [1] k_expand done, [2] k_cand runs, [3] rowside tiles
+#define GS_TICKETS 4                      // per layer: [0] k_rows tiles, [1] k_expand done, [2] k_cand_flags done, [3] row counts done
 
 // decoupled look-back descriptors
 #define GS_RS_NC 16   // k_rows scan: candidates, drawing rows, rows per owner (uint64 each; 2 + P used)
@@ -104,8 +104,7 @@ struct GsWs {
   unsigned long long *rs_val;  // [2][ftiles_cap][GS_RS_NC]  aggregates, inclusive prefixes
   uint32_t *ccnt;        // [GS_CS_NC][cgrid_cap] k_cand_flags: class counts per CTA -> exclusive prefixes
   int32_t cgrid_cap;
-  uint32_t *fs_status;   // [ftiles_cap]
-  uint32_t *fs_val;      // [2][ftiles_cap][GS_FS_NC]
+  uint32_t *fcnt;        // [GS_FS_NC][cgrid_cap] row side: class counts per CTA run of rows -> exclusive prefixes
   int32_t Fcap, Ccap, ftiles_cap, ctiles_cap;
   // fused input-feature gather (optional)
   const float *feat;     // [rows][feat_dim] fp32 (cached store: the cached rows)
@@ -145,7 +144,9 @@ void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid
 // by_rows: sampled layer (fan > 0) -> one thread per (row, four picks); else candidate-parallel (fan = -1)
 void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
                       cudaStream_t st);
-void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, cudaStream_t st);
+// pass 0: flags (+ grid_rowcount CTAs that count the row-side classes), pass 1: apply
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, int grid_rowcount,
+                    cudaStream_t st);
 void gs_launch_tail(const GsWs *wsv, int members, bool wide, int grid_relabel, int grid_rowside, int grid_gather,
                     cudaStream_t st);
 void gs_launch_gather_ids(const float *feat, const int32_t *slot_of, const float *host_rows, int dim,

@@ -1009,8 +1009,29 @@ __device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t 
   }
 }
 
+// A role's contiguous run of tiles: CTA bx of the nb CTAs that play the role in this launch.
+__device__ __forceinline__ void role_tiles(int ntiles, int bx, int nb, int &t0, int &t1) {
+  const int per = (ntiles + nb - 1) / nb;
+  t0 = min(ntiles, bx * per);
+  t1 = min(ntiles, t0 + per);
+}
+// last_block for a role played by n CTAs of the launch (own ticket)
+__device__ __forceinline__ bool last_block_n(uint32_t *ticket, uint32_t n) {
+  __shared__ uint32_t s_last_n;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last_n = (t == n - 1u) ? 1u : 0u;
+    if (s_last_n) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last_n) __threadfence();
+  return s_last_n != 0u;
+}
+
 template <typename PK>
-__device__ void cand_flags_role(const GsWs &ws, int layer) {
+__device__ void cand_flags_role(const GsWs &ws, int layer, int bx, int nb) {
   gs_sample_header *h = ws.hdr;
   if (h->status != 0) return;
   __shared__ uint32_t s_cnt[GS_CS_NC];
@@ -1026,7 +1047,7 @@ __device__ void cand_flags_role(const GsWs &ws, int layer) {
   __syncthreads();
   uint32_t acc_i = 0u, acc_e = 0u, acc_f = 0u;  // lane q < 8: this warp's running counts of part q
   int t0, t1;
-  cta_tiles(ntiles, t0, t1);
+  role_tiles(ntiles, bx, nb, t0, t1);  // = cta_tiles of k_cand_apply, launched with nb CTAs
   for (int t = t0; t < t1; t++) {
     const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     uint32_t fl[GS_IPT];
@@ -1092,9 +1113,9 @@ __device__ void cand_flags_role(const GsWs &ws, int layer) {
   }
   if (lane == 8 && acc_f) atomicAdd(&s_cnt[CS_NF], acc_f);
   __syncthreads();
-  if (threadIdx.x < CS_USED) ws.ccnt[(size_t)threadIdx.x * ws.cgrid_cap + blockIdx.x] = s_cnt[threadIdx.x];
-  if (!last_block(ws.tickets + layer * GS_TICKETS + 2)) return;
-  spine_scan<GS_CS_NC>(ws.ccnt, ws.cgrid_cap, (int)gridDim.x, CS_USED, s_tot, nullptr);
+  if (threadIdx.x < CS_USED) ws.ccnt[(size_t)threadIdx.x * ws.cgrid_cap + bx] = s_cnt[threadIdx.x];
+  if (!last_block_n(ws.tickets + layer * GS_TICKETS + 2, (uint32_t)nb)) return;
+  spine_scan<GS_CS_NC>(ws.ccnt, ws.cgrid_cap, nb, CS_USED, s_tot, nullptr);
 }
 
 // Second pass: ranks and lists.  Same contiguous runs of tiles per CTA as
@@ -1229,35 +1250,101 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
 #define FS_OWN(q) (8 + (q))
 #define FS_TO(q) (16 + (q))
 #define FS_USED 24
+// Count pass of the row side (rides in the k_cand_flags launch: rowhas is final once
+// k_expand has run): the 3 P classes of every CTA run of rows, the last CTA turns
+// them into exclusive prefixes.  Same runs as rowside_role (role_tiles, same nb).
 template <typename PK>
-__device__ void rowside_role(const GsWs &ws, int layer) {
+__device__ void rowcount_role(const GsWs &ws, int layer, int bx, int nb) {
+  const gs_sample_header *h = ws.hdr;
+  if (h->status != 0) return;
+  __shared__ uint32_t s_cnt[GS_FS_NC];
+  __shared__ uint32_t s_tot[GS_FS_NC];
+  const int F = h->frontier_len[layer];
+  const int ntiles = (F + GS_TILE - 1) / GS_TILE;
+  const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
+  const uint32_t *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);
+  const int lane = lane_id();
+  if (threadIdx.x < GS_FS_NC) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  uint32_t acc_o = 0u, acc_w = 0u, acc_t = 0u;  // lane q < 8: this warp's running counts of part q
+  int t0, t1;
+  role_tiles(ntiles, bx, nb, t0, t1);
+  for (int t = t0; t < t1; t++) {
+    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u};
+    int32_t nd[GS_IPT] = {0, 0, 0, 0};
+    if (i0 + GS_IPT <= F) {
+      const uint4 h4 = *reinterpret_cast<const uint4 *>(rw_rowhas + i0);
+      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
+      has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
+      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++)
+        if (i0 + k < F) {
+          has[k] = rw_rowhas[i0 + k];
+          nd[k] = front[i0 + k];
+        }
+    }
+    PK po = 0, pw = 0, pt = 0;
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++)
+      if (has[k]) {
+        const int g0 = owner_of(ws, nd[k]);
+        const uint32_t own = 1u << g0;
+        po += pkt_spread(has[k], (PK)0);
+        if (has[k] & own) pw += pkt_one<PK>(g0);
+        if (has[k] & ~own) pt += pkt_one<PK>(g0);
+      }
+    po = pkt_redux(po);
+    pw = pkt_redux(pw);
+    pt = pkt_redux(pt);
+    if (lane < (int)sizeof(PK)) {
+      acc_o += pkt_get<PK>(po, lane);
+      acc_w += pkt_get<PK>(pw, lane);
+      acc_t += pkt_get<PK>(pt, lane);
+    }
+  }
+  if (lane < 8) {
+    if (acc_o) atomicAdd(&s_cnt[FS_OUT(lane)], acc_o);
+    if (acc_w) atomicAdd(&s_cnt[FS_OWN(lane)], acc_w);
+    if (acc_t) atomicAdd(&s_cnt[FS_TO(lane)], acc_t);
+  }
+  __syncthreads();
+  if (threadIdx.x < FS_USED) ws.fcnt[(size_t)threadIdx.x * ws.cgrid_cap + bx] = s_cnt[threadIdx.x];
+  if (!last_block_n(ws.tickets + layer * GS_TICKETS + 3, (uint32_t)nb)) return;
+  spine_scan<GS_FS_NC>(ws.fcnt, ws.cgrid_cap, nb, FS_USED, s_tot, nullptr);
+}
+
+// Apply pass of the row side, in the launch after k_cand_apply (next to the next layer's
+// k_rows, or in k_tail): CTA bx starts from rowcount_role's prefix of its run of rows and
+// carries the running class counts across its tiles -- no wait on any other CTA.
+template <typename PK>
+__device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
   gs_sample_header *h = ws.hdr;
   __shared__ uint32_t s_wc[GS_NW][GS_FS_NC];
   __shared__ uint32_t s_base[GS_NW][GS_FS_NC];
-  __shared__ uint32_t s_agg[GS_FS_NC], s_pre[GS_FS_NC];
+  __shared__ uint32_t s_run[GS_FS_NC];
   __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
-  __shared__ int s_tile;
   if (h->status != 0) return;
   const int P = ws.P;
   const int F = h->frontier_len[layer];
   const int ntiles = (F + GS_TILE - 1) / GS_TILE;
-  if (ntiles == 0) return;
+  int t0, t1;
+  role_tiles(ntiles, bx, nb, t0, t1);
+  if (t0 >= t1) return;
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
-  const GsState stt = *ws.state;
-  const uint32_t ep = stt.scan_epoch + 3u * (uint32_t)layer + 2u;
   const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3), *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3),
                  *rw_selfrank = ws.selfrank + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);  // ping-pong by layer (see rows_role)
-  uint32_t *fs_agg = ws.fs_val, *fs_inc = ws.fs_val + (size_t)ws.ftiles_cap * GS_FS_NC;
-  uint32_t *tick = ws.tickets + layer * GS_TICKETS + 3;
   const int lane = lane_id(), w = warp_id();
   const size_t rs_stride = sizeof(PK);  // rowscan: one record of 4 (P <= 4) or 8 words per row
   if (threadIdx.x < P * GS_NUM_FIELDS)
     s_fo[threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS] =
         h->field[layer][threadIdx.x / GS_NUM_FIELDS][threadIdx.x % GS_NUM_FIELDS].off;
-  if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);
+  if (threadIdx.x < GS_FS_NC)
+    s_run[threadIdx.x] = threadIdx.x < FS_USED ? ws.fcnt[(size_t)threadIdx.x * ws.cgrid_cap + bx] : 0u;
   __syncthreads();
-  int t = s_tile;
-  while (t < ntiles) {
+  for (int t = t0; t < t1; t++) {
     const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
     uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u}, a[GS_IPT], sr[GS_IPT];
     int32_t nd[GS_IPT] = {0, 0, 0, 0};
@@ -1310,20 +1397,17 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
       }
     }
     __syncthreads();
-    if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick, 1u);  // next tile of this CTA (read after the barriers below)
     if (threadIdx.x < FS_USED) {
-      uint32_t run = 0u;
+      uint32_t run = s_run[threadIdx.x];
 #pragma unroll
       for (int k = 0; k < GS_NW; k++) {
         s_base[k][threadIdx.x] = run;
         run += s_wc[k][threadIdx.x];
       }
-      s_agg[threadIdx.x] = run;
+      s_run[threadIdx.x] = run;
     }
     __syncthreads();
-    lookback_publish<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, t, ep, s_agg, s_pre);
-    lookback_collect<uint32_t, FS_USED, GS_FS_NC>(ws.fs_status, fs_agg, fs_inc, t, ep, s_agg, s_pre);
-#define FS_B(c) (s_pre[c] + s_base[w][c])
+#define FS_B(c) (s_base[w][c])
     PK ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
@@ -1356,8 +1440,6 @@ __device__ void rowside_role(const GsWs &ws, int layer) {
       }
     }
 #undef FS_B
-    __syncthreads();
-    t = s_tile;
   }
 }
 
@@ -1445,7 +1527,7 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__res
   if (bx < grid_rows) rows_role<FIRST>(ws, layer);
   else if (FIRST) return;
   else if (bx < grid_rows + grid_relabel) relabel_role(ws, layer - 1, bx - grid_rows, grid_relabel);
-  else rowside_role<PK>(ws, layer - 1);
+  else rowside_role<PK>(ws, layer - 1, bx - grid_rows - grid_relabel, (int)gridDim.x - grid_rows - grid_relabel);
 }
 
 template <int RNG, bool WIDE>
@@ -1465,11 +1547,14 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand_rows(const Gs
 }
 
 template <bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand_flags(const GsWs *__restrict__ wsv, int layer) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand_flags(const GsWs *__restrict__ wsv, int layer,
+                                                                      int grid_cand) {
   typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
-  cand_flags_role<PK>(ws, layer);
+  const int bx = (int)blockIdx.x;
+  if (bx < grid_cand) cand_flags_role<PK>(ws, layer, bx, grid_cand);
+  else rowcount_role<PK>(ws, layer, bx - grid_cand, (int)gridDim.x - grid_cand);
 }
 
 template <bool WIDE>
@@ -1496,7 +1581,7 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_tail(const GsWs *__res
   const int bx = (int)blockIdx.x;
   if (st == 0) {
     if (bx < grid_relabel) relabel_role(ws, L - 1, bx, grid_relabel);
-    else if (bx < grid_relabel + grid_rowside) rowside_role<PK>(ws, L - 1);
+    else if (bx < grid_relabel + grid_rowside) rowside_role<PK>(ws, L - 1, bx - grid_relabel, grid_rowside);
     else if (ws.feat) gather_role(ws, bx - grid_relabel - grid_rowside, grid_gather);
   }
   const GsState stt = *ws.state;
@@ -1512,10 +1597,7 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_tail(const GsWs *__res
     if (tid < (ws.num_nodes & 3)) ws.table[(n4 << 2) + tid] = GS_INF;
   }
   if (rescan) {
-    for (int64_t i = tid; i < ws.ftiles_cap; i += nth) {
-      ws.rs_status[i] = 0u;
-      ws.fs_status[i] = 0u;
-    }
+    for (int64_t i = tid; i < ws.ftiles_cap; i += nth) ws.rs_status[i] = 0u;
   }
   if (!last_block(ws.tickets + L * GS_TICKETS)) return;
   for (int i = threadIdx.x; i < L * GS_CNT_STRIDE; i += GS_TPB) ws.cnt[i] = 0u;
@@ -1752,12 +1834,15 @@ void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, boo
   if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
   else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
 }
-void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, cudaStream_t st) {
-  // pass 0: flags, 1: apply.  Both must be given the same grid: a CTA's run of tiles is the same in both.
+void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, int grid_rowcount,
+                    cudaStream_t st) {
+  // pass 0: flags, 1: apply.  Both must be given the same `grid`: a CTA's run of tiles is the same in both.
+  // grid_rowcount (pass 0): CTAs of the row-side count pass; the row side is later run with as many.
   const dim3 g(grid, members);
   if (pass == 0) {
-    if (wide) k_cand_flags<true><<<g, GS_TPB, 0, st>>>(wsv, layer);
-    else k_cand_flags<false><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    const dim3 g0(grid + grid_rowcount, members);
+    if (wide) k_cand_flags<true><<<g0, GS_TPB, 0, st>>>(wsv, layer, grid);
+    else k_cand_flags<false><<<g0, GS_TPB, 0, st>>>(wsv, layer, grid);
   } else {
     if (wide) k_cand_apply<true><<<g, GS_TPB, 0, st>>>(wsv, layer);
     else k_cand_apply<false><<<g, GS_TPB, 0, st>>>(wsv, layer);
