@@ -183,13 +183,12 @@ int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::ve
   const bool relabel_on = !(roles_off & 1), rowside_on = !(roles_off & 2);
   int nl = 0;
   for (int l = 0; l < L; l++) {
+    if (nl++ < stop) gs_launch_rows(gr.wsv, members, l, s->grid_rows[l], st);
+    if ((rc = mark("rows"))) return rc;
     if (nl++ < stop)
-      gs_launch_rows(gr.wsv, members, wide, l, s->grid_rows[l], l > 0 && relabel_on ? s->grid_relabel[l - 1] : 0,
-                     l > 0 && rowside_on ? s->grid_rows[l - 1] : 0, st);
-    if ((rc = mark(l == 0 ? "rows" : "rows+relabel+rowside"))) return rc;
-    if (nl++ < stop)
-      gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l], st);
-    if ((rc = mark("expand"))) return rc;
+      gs_launch_expand(gr.wsv, members, wide, s->cfg.rng_mode, s->cfg.fanouts[l] > 0, l, s->grid_cand[l],
+                       l > 0 && relabel_on ? s->grid_relabel[l - 1] : 0, l > 0 && rowside_on ? s->grid_rows[l - 1] : 0, st);
+    if ((rc = mark(l == 0 ? "expand" : "expand+relabel+rowside"))) return rc;
     if (nl++ < stop) gs_launch_cand(gr.wsv, members, wide, 0, l, s->grid_cand[l], s->grid_rows[l], st);
     if ((rc = mark("cand_flags+rowcount"))) return rc;
     if (nl++ < stop) gs_launch_cand(gr.wsv, members, wide, 1, l, s->grid_cand[l], 0, st);
@@ -593,7 +592,7 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.ea, 2 * (s->Fcap + 4));
     DA(w.rowhas, 2 * (s->Fcap + 4));
     DA(w.rowscan, (s->Fcap + 1) * (cfg->num_parts > 4 ? 8 : 4));  // one record per row
-    DA(w.cand, s->Ccap + 4);
+    DA(w.cand, 2 * ((s->Ccap + 7) & ~(int64_t)3));  // ping-pong by layer
     DA(w.cflag, s->Ccap + 4);
     DA(w.tile_first, ctiles + 1);
     DA(w.cnt, (size_t)L * GS_CNT_STRIDE);

@@ -95,7 +95,7 @@ struct GsWs {
   uint32_t *ea;          // [2][Fcap] minimum edge-source position of the row's node in this layer (GS_INF: none)
   uint32_t *rowhas;      // [2][Fcap] (ping-pong by layer) bit q: the row emitted >= 1 edge into part q
   uint32_t *rowscan;     // [Fcap+1][4 or 8] edges of part q emitted before row i (k_cand -> rowside)
-  int32_t *cand;         // [Ccap]   candidate stream; after k_cand: in_nodes rank at first-occurrence positions
+  int32_t *cand;         // [2][Ccap] (ping-pong by layer) candidate stream; after k_cand: in_nodes rank at first-occurrence positions
   uint8_t *cflag;        // [Ccap]
   uint32_t *tile_first;  // [ctiles_cap] row containing candidate t*GS_TILE
   uint32_t *cnt;         // [L][GS_CNT_STRIDE] per-layer totals
@@ -139,11 +139,11 @@ struct GsGrids {
 };
 void gs_kernels_prepare();  // once per device, before the first launch / graph capture
 // wide: more than 4 parts (64-bit packed per-part counters)
-void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid_rows, int grid_relabel,
-                    int grid_rowside, cudaStream_t st);
-// by_rows: sampled layer (fan > 0) -> one thread per (row, four picks); else candidate-parallel (fan = -1)
+void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, cudaStream_t st);
+// by_rows: sampled layer (fan > 0) -> one thread per (row, four picks); else candidate-parallel (fan = -1).
+// grid_relabel / grid_rowside: extra CTAs that finish the previous layer's lists.
 void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
-                      cudaStream_t st);
+                      int grid_relabel, int grid_rowside, cudaStream_t st);
 // pass 0: flags (+ grid_rowcount CTAs that count the row-side classes), pass 1: apply
 void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, int grid_rowcount,
                     cudaStream_t st);

@@ -274,8 +274,8 @@ __device__ void init_header(const GsWs &ws, int n, int status) {
 template <bool FIRST>
 __device__ void rows_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
-  __shared__ unsigned long long s_wc[GS_NW][GS_RS_NC];
-  __shared__ unsigned long long s_base[GS_NW][GS_RS_NC];
+  __shared__ unsigned long long s_wc[GS_IPT * GS_NW][2 + GS_MAX_PARTS];   // totals of block (k, warp)
+  __shared__ unsigned long long s_base[GS_IPT * GS_NW][2 + GS_MAX_PARTS]; // -> sums of the blocks before it
   __shared__ unsigned long long s_agg[GS_RS_NC], s_pre[GS_RS_NC];
   __shared__ int s_tile;
   if (!FIRST && h->status != 0) return;
@@ -327,89 +327,92 @@ __device__ void rows_role(const GsWs &ws, int layer) {
   int t = s_tile;
   while (t < ntiles) {
     if (FIRST && t == 0 && threadIdx.x == 0) init_header(ws, F, 0);
-    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
+    // Rows are dealt lane-consecutive (row of k = tile + k * 256 + thread): every per-row load and
+    // store of a warp then covers 32 consecutive rows = whole sectors.  The scan order is k-major:
+    // block (k, warp) of 32 rows, blocks in the order k * GS_NW + warp.
+    const int ib = t * GS_TILE + (int)threadIdx.x;
     int32_t nd[GS_IPT];
-    int64_t rs[GS_IPT];
     int32_t deg[GS_IPT];
     int g0[GS_IPT];
+    uint32_t c[GS_IPT];
     if (FIRST) {
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         nd[k] = 0;
-        if (i0 + k < F) {
-          const int64_t v = ws.seeds_in[i0 + k];
+        if (ib + k * GS_TPB < F) {
+          const int64_t v = ws.seeds_in[ib + k * GS_TPB];
           if (v < 0 || v >= (int64_t)ws.num_nodes) bad = true;
           else nd[k] = (int32_t)v;
         }
       }
-    } else if (i0 + GS_IPT <= F) {
-      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
-      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
     } else {
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) nd[k] = i0 + k < F ? front[i0 + k] : 0;
+      for (int k = 0; k < GS_IPT; k++) nd[k] = ib + k * GS_TPB < F ? front[ib + k * GS_TPB] : 0;
     }
-    int64_t e_[GS_IPT];
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      rs[k] = 0; e_[k] = 0;
-      if (i0 + k < F) {
-        rs[k] = __ldg(ws.indptr + nd[k]);
-        e_[k] = __ldg(ws.indptr + nd[k] + 1);
-      }
-    }
-    unsigned long long c4 = 0ull, pk4 = 0ull;
-    uint32_t s4 = 0u;
-    uint32_t c[GS_IPT];
-#pragma unroll
-    for (int k = 0; k < GS_IPT; k++) {
-      deg[k] = (int32_t)(e_[k] - rs[k]);
-      c[k] = 0u;
-      g0[k] = 0;
-      if (i0 + k < F) {
-        const bool samp = fan >= 0 && deg[k] >= fan;
-        c[k] = 1u + (uint32_t)(samp ? fan : deg[k]);
-        s4 += samp ? 1u : 0u;
-        g0[k] = owner_of(ws, nd[k]);
-        pk4 += pk_one(g0[k]);
-        c4 += c[k];
-      }
-    }
-    const unsigned long long inc_c = warp_incl_scan64(c4), inc_pk = pk_warp_incl(pk4);
-    const uint32_t inc_s = warp_incl_scan(s4);
     {
+      int64_t rs[GS_IPT], e_[GS_IPT];
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        rs[k] = 0; e_[k] = 0;
+        if (ib + k * GS_TPB < F) {
+          rs[k] = __ldg(ws.indptr + nd[k]);
+          e_[k] = __ldg(ws.indptr + nd[k] + 1);
+        }
+      }
+      // everything that does not need the prefix goes out right away
+#pragma unroll
+      for (int k = 0; k < GS_IPT; k++) {
+        const int i = ib + k * GS_TPB;
+        deg[k] = (int32_t)(e_[k] - rs[k]);
+        g0[k] = 0;
+        if (i < F) {
+          g0[k] = owner_of(ws, nd[k]);
+          ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
+                                    (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
+          rw_ea[i] = GS_INF;
+          rw_rowhas[i] = 0u;
+        }
+      }
+    }
+    unsigned long long ex_c[GS_IPT];  // exclusive within the (k, warp) block
+    uint32_t ex_s[GS_IPT], ex_g[GS_IPT];
+#pragma unroll
+    for (int k = 0; k < GS_IPT; k++) {
+      const bool in = ib + k * GS_TPB < F;
+      const bool samp = in && fan >= 0 && deg[k] >= fan;
+      c[k] = in ? 1u + (uint32_t)(samp ? fan : deg[k]) : 0u;
+      const unsigned long long pk1 = in ? pk_one(g0[k]) : 0ull;
+      const unsigned long long inc_c = warp_incl_scan64((unsigned long long)c[k]), inc_pk = pk_warp_incl(pk1);
+      const uint32_t inc_s = warp_incl_scan(samp ? 1u : 0u);
+      ex_c[k] = inc_c - c[k];
+      ex_s[k] = inc_s - (samp ? 1u : 0u);
+      ex_g[k] = pk_get(inc_pk - pk1, g0[k]);
       const unsigned long long tot_pk = __shfl_sync(FULL, inc_pk, 31);
       if (lane == 31) {
-        s_wc[w][0] = inc_c;
-        s_wc[w][1] = inc_s;
+        s_wc[k * GS_NW + w][0] = inc_c;
+        s_wc[k * GS_NW + w][1] = inc_s;
       }
-      if (lane < P) s_wc[w][2 + lane] = pk_get(tot_pk, lane);
+      if (lane < P) s_wc[k * GS_NW + w][2 + lane] = pk_get(tot_pk, lane);
     }
     __syncthreads();
     if (threadIdx.x == 0) s_tile = (int)atomicAdd(tick + 0, 1u);  // next tile of this CTA (read after the barrier below)
-    if (lane < NC) {
-      unsigned long long a = 0ull, all = 0ull;
-#pragma unroll
-      for (int k = 0; k < GS_NW; k++) {
-        const unsigned long long x = s_wc[k][lane];
-        if (k < w) a += x;
-        all += x;
+    if (threadIdx.x < NC) {
+      unsigned long long run = 0ull;
+#pragma unroll 8
+      for (int j = 0; j < GS_IPT * GS_NW; j++) {
+        s_base[j][threadIdx.x] = run;
+        run += s_wc[j][threadIdx.x];
       }
-      s_base[w][lane] = a;
-      if (w == 0) s_agg[lane] = all;
+      s_agg[threadIdx.x] = run;
     }
     __syncthreads();
     lookback_publish<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, t, ep, s_agg, s_pre);
-    // everything that does not need the prefix goes out while the predecessors' aggregates arrive
+    // the table marks go out while the predecessors' aggregates arrive
     bool dup = false;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      const int i = i0 + k;
+      const int i = ib + k * GS_TPB;
       if (i < F) {
-        ws.rowinfo[i] = make_int4((int)(uint32_t)rs[k],
-                                  (int)((uint32_t)((uint64_t)rs[k] >> 32) | ((uint32_t)g0[k] << 29)), deg[k], nd[k]);
-        rw_ea[i] = GS_INF;
-        rw_rowhas[i] = 0u;
         if (FIRST) {
           ws.fslab[i] = nd[k];
           // a second claim of the same entry under this sample's tag is a duplicate seed
@@ -422,17 +425,15 @@ __device__ void rows_role(const GsWs &ws, int layer) {
     }
     lookback_collect<unsigned long long, 2 + GS_MAX_PARTS, GS_RS_NC>(ws.rs_status, rs_agg, rs_inc, t, ep, s_agg, s_pre);
     if (FIRST && (bad || dup)) atomicCAS(&h->status, 0, (int)GS_ERR_SEED);  // after the look-back: behind init_header
-    unsigned long long base_c = s_pre[0] + s_base[w][0] + inc_c - c4;
-    uint32_t base_s = (uint32_t)(s_pre[1] + s_base[w][1]) + inc_s - s4;
-    unsigned long long r_pk = inc_pk - pk4;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      const int i = i0 + k;
+      const int i = ib + k * GS_TPB;
       if (i < F) {
-        const uint32_t o = (uint32_t)base_c;
-        ws.off[i] = o;
-        rw_selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + s_base[w][2 + g0[k]]) + pk_get(r_pk, g0[k]);
-        if (replay) ws.samp_rank[i] = base_s;
+        const unsigned long long *bs = s_base[k * GS_NW + w];
+        const unsigned long long base_c = s_pre[0] + bs[0] + ex_c[k];
+        ws.off[i] = (uint32_t)base_c;
+        rw_selfrank[i] = (uint32_t)(s_pre[2 + g0[k]] + bs[2 + g0[k]]) + ex_g[k];
+        if (replay) ws.samp_rank[i] = (uint32_t)(s_pre[1] + bs[1]) + ex_s[k];
         // candidate tiles that start inside this row (only the candidate-parallel k_expand of
         // fan = -1 layers looks rows up by position)
         const unsigned long long end = base_c + c[k];
@@ -440,10 +441,6 @@ __device__ void rows_role(const GsWs &ws, int layer) {
           for (unsigned long long tb = (base_c + GS_TILE - 1) / GS_TILE;
                tb * GS_TILE < end && tb < (unsigned long long)ws.ctiles_cap; tb++)
             ws.tile_first[tb] = (uint32_t)i;
-        base_c = end;
-        const bool samp = fan >= 0 && deg[k] >= fan;
-        base_s += samp ? 1u : 0u;
-        r_pk += pk_one(g0[k]);
       }
     }
     if (t == ntiles - 1 && threadIdx.x == 0) {
@@ -541,6 +538,38 @@ __device__ void layer_alloc(const GsWs &ws, int layer, const uint32_t *cnt /* sh
   }
 }
 
+// A role's contiguous run of tiles: CTA bx of the nb CTAs that play the role in this launch.
+__device__ __forceinline__ void role_tiles(int ntiles, int bx, int nb, int &t0, int &t1) {
+  const int per = (ntiles + nb - 1) / nb;
+  t0 = min(ntiles, bx * per);
+  t1 = min(ntiles, t0 + per);
+}
+// last_block for a role played by n CTAs of the launch (own ticket)
+__device__ __forceinline__ bool last_block_n(uint32_t *ticket, uint32_t n) {
+  __shared__ uint32_t s_last_n;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last_n = (t == n - 1u) ? 1u : 0u;
+    if (s_last_n) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last_n) __threadfence();
+  return s_last_n != 0u;
+}
+
+// -DGS_DIAG=bits: knock-out builds for tools/build_variants.sh (WRONG results; they only show what a
+// piece of work costs with all slots in flight).  1: row side writes nothing, 2: no relabel-map read.
+#ifndef GS_DIAG
+#define GS_DIAG 0
+#endif
+// The candidate words ping-pong by layer: relabel / row side of layer l read them in the
+// launch in which k_expand of layer l + 1 writes the next layer's stream.
+__device__ __forceinline__ int32_t *cand_buf(const GsWs &ws, int layer) {
+  return ws.cand + (size_t)(layer & 1) * (((size_t)ws.Ccap + 7) & ~(size_t)3);
+}
+
 // Candidate-parallel CSR row expansion (slicer.cpp:6-22).  A tile is GS_TILE
 // consecutive candidate positions, so load is balanced whatever the degree
 // skew; the rows a tile touches are found from tile_first[] and a binary
@@ -562,8 +591,9 @@ __device__ void layer_alloc(const GsWs &ws, int layer, const uint32_t *cnt /* sh
 // RNG (gs_rng_mode) is a template parameter: the pick path of the other two
 // modes costs instructions in a kernel bound by issue.
 template <int RNG, typename PK>
-__device__ void expand_role(const GsWs &ws, int layer) {
+__device__ void expand_role(const GsWs &ws, int layer, int nb_role) {
   gs_sample_header *h = ws.hdr;
+  int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   const Tbl tbl(ws);
   const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
@@ -601,7 +631,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   };
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
-  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+  for (int t = blockIdx.x; t < ntiles; t += nb_role) {  // the expand CTAs come first in the launch
     const int i_lo = (int)ws.tile_first[t];
     const int i_hi = (t + 1 < ntiles) ? (int)ws.tile_first[t + 1] : F - 1;
     const int cntr = i_hi - i_lo + 1;  // <= GS_TILE + 1 rows, each has >= 1 candidate
@@ -753,14 +783,14 @@ __device__ void expand_role(const GsWs &ws, int layer) {
         }
       }
     if (p0 + GS_IPT <= C) {
-      *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(cvv[0], cvv[1], cvv[2], cvv[3]);
+      *reinterpret_cast<int4 *>(cand + p0) = make_int4(cvv[0], cvv[1], cvv[2], cvv[3]);
       *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
           make_uchar4((unsigned char)cf[0], (unsigned char)cf[1], (unsigned char)cf[2], (unsigned char)cf[3]);
     } else {
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++)
         if (p0 + k < C) {
-          ws.cand[p0 + k] = cvv[k];
+          cand[p0 + k] = cvv[k];
           ws.cflag[p0 + k] = (uint8_t)cf[k];
         }
     }
@@ -784,7 +814,7 @@ __device__ void expand_role(const GsWs &ws, int layer) {
   }
   __syncthreads();
   if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);
-  if (!last_block(ws.tickets + layer * GS_TICKETS + 1)) return;
+  if (!last_block_n(ws.tickets + layer * GS_TICKETS + 1, (uint32_t)nb_role)) return;
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = __ldcg(cnt + threadIdx.x);  // one round trip for all totals
   __syncthreads();
   if (threadIdx.x == 0) layer_alloc(ws, layer, s_cnt);
@@ -799,8 +829,9 @@ __device__ void expand_role(const GsWs &ws, int layer) {
 // that per thread and is kept for fan = -1, where rows are unbounded).  Dedup,
 // counting and the candidate stream are exactly those of expand_role.
 template <int RNG, typename PK>
-__device__ void expand_rows_role(const GsWs &ws, int layer) {
+__device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
   gs_sample_header *h = ws.hdr;
+  int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   const Tbl tbl(ws);
   const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
@@ -836,7 +867,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
   const uint32_t nitems = (uint32_t)F * nb;                           // F < 2^30 / ... : fits (F * (fan + 1) <= Ccap < 2^30)
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
-  for (uint32_t it0 = blockIdx.x * GS_TPB; it0 < nitems; it0 += gridDim.x * GS_TPB) {
+  for (uint32_t it0 = blockIdx.x * GS_TPB; it0 < nitems; it0 += (uint32_t)nb_role * GS_TPB) {
     const uint32_t item = it0 + threadIdx.x;
     PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
     uint32_t n_new = 0u;
@@ -856,7 +887,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
       const int j0 = (int)(4u * b);
       const int nj = min(4, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
       if (b == 0u) {  // the row's self entry (slicer.cpp:7)
-        ws.cand[o] = (int32_t)row;
+        cand[o] = (int32_t)row;
         ws.cflag[o] = (uint8_t)(GS_CK_SELF | ((uint32_t)g0 << GS_CF_PART_SHIFT));
       }
       if (nj > 0) {
@@ -927,7 +958,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
                 cf = GS_CK_FHIT | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
               }
             }
-            ws.cand[p1 + j] = cv;
+            cand[p1 + j] = cv;
             ws.cflag[p1 + j] = (uint8_t)cf;
           }
         }
@@ -958,7 +989,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
   }
   __syncthreads();
   if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);
-  if (!last_block(ws.tickets + layer * GS_TICKETS + 1)) return;
+  if (!last_block_n(ws.tickets + layer * GS_TICKETS + 1, (uint32_t)nb_role)) return;
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = __ldcg(cnt + threadIdx.x);  // one round trip for all totals
   __syncthreads();
   if (threadIdx.x == 0) layer_alloc(ws, layer, s_cnt);
@@ -989,10 +1020,10 @@ __device__ void expand_rows_role(const GsWs &ws, int layer) {
 #define GS_CF_FIRST 0x04u   // first occurrence as an edge source -> in_nodes of its part
 #define GS_CF_FFIRST 0x08u  // first occurrence in the layer's stream -> next frontier
 
-__device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t C, uint32_t (&fl)[GS_IPT],
-                                          int32_t (&ci)[GS_IPT]) {
+__device__ __forceinline__ void cand_load(const GsWs &ws, const int32_t *cand, uint32_t p0, uint32_t C,
+                                          uint32_t (&fl)[GS_IPT], int32_t (&ci)[GS_IPT]) {
   if (p0 + GS_IPT <= C) {
-    const int4 c4 = *reinterpret_cast<const int4 *>(ws.cand + p0);
+    const int4 c4 = *reinterpret_cast<const int4 *>(cand + p0);
     const uchar4 f4 = *reinterpret_cast<const uchar4 *>(ws.cflag + p0);
     ci[0] = c4.x; ci[1] = c4.y; ci[2] = c4.z; ci[3] = c4.w;
     fl[0] = f4.x; fl[1] = f4.y; fl[2] = f4.z; fl[3] = f4.w;
@@ -1003,36 +1034,16 @@ __device__ __forceinline__ void cand_load(const GsWs &ws, uint32_t p0, uint32_t 
       ci[i] = 0;
       if (p0 + i < C) {
         fl[i] = ws.cflag[p0 + i];
-        ci[i] = ws.cand[p0 + i];
+        ci[i] = cand[p0 + i];
       }
     }
   }
 }
 
-// A role's contiguous run of tiles: CTA bx of the nb CTAs that play the role in this launch.
-__device__ __forceinline__ void role_tiles(int ntiles, int bx, int nb, int &t0, int &t1) {
-  const int per = (ntiles + nb - 1) / nb;
-  t0 = min(ntiles, bx * per);
-  t1 = min(ntiles, t0 + per);
-}
-// last_block for a role played by n CTAs of the launch (own ticket)
-__device__ __forceinline__ bool last_block_n(uint32_t *ticket, uint32_t n) {
-  __shared__ uint32_t s_last_n;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t t = atomicAdd(ticket, 1u);
-    s_last_n = (t == n - 1u) ? 1u : 0u;
-    if (s_last_n) *ticket = 0u;
-  }
-  __syncthreads();
-  if (s_last_n) __threadfence();
-  return s_last_n != 0u;
-}
-
 template <typename PK>
 __device__ void cand_flags_role(const GsWs &ws, int layer, int bx, int nb) {
   gs_sample_header *h = ws.hdr;
+  int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   __shared__ uint32_t s_cnt[GS_CS_NC];
   __shared__ uint32_t s_tot[GS_CS_NC];
@@ -1052,7 +1063,7 @@ __device__ void cand_flags_role(const GsWs &ws, int layer, int bx, int nb) {
     const uint32_t p0 = (uint32_t)t * GS_TILE + GS_IPT * threadIdx.x;
     uint32_t fl[GS_IPT];
     int32_t ci[GS_IPT];
-    cand_load(ws, p0, C, fl, ci);
+    cand_load(ws, cand, p0, C, fl, ci);
     uint32_t x[GS_IPT], s[GS_IPT];
 #pragma unroll
     for (int i = 0; i < GS_IPT; i++) {
@@ -1087,14 +1098,14 @@ __device__ void cand_flags_role(const GsWs &ws, int layer, int bx, int nb) {
       }
     }
     if (p0 + GS_IPT <= C) {
-      if (moved) *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+      if (moved) *reinterpret_cast<int4 *>(cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
       *reinterpret_cast<uchar4 *>(ws.cflag + p0) =
           make_uchar4((unsigned char)fl[0], (unsigned char)fl[1], (unsigned char)fl[2], (unsigned char)fl[3]);
     } else {
 #pragma unroll
       for (int i = 0; i < GS_IPT; i++)
         if (p0 + i < C) {
-          ws.cand[p0 + i] = ci[i];
+          cand[p0 + i] = ci[i];
           ws.cflag[p0 + i] = (uint8_t)fl[i];
         }
     }
@@ -1124,6 +1135,7 @@ __device__ void cand_flags_role(const GsWs &ws, int layer, int bx, int nb) {
 template <typename PK>
 __device__ void cand_apply_role(const GsWs &ws, int layer) {
   gs_sample_header *h = ws.hdr;
+  int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   __shared__ uint32_t s_wc[GS_NW][GS_CS_NC];    // per-warp class totals of the tile
   __shared__ uint32_t s_base[GS_NW][GS_CS_NC];  // CTA prefix + earlier tiles + earlier warps of the tile
@@ -1151,7 +1163,7 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
     const bool full = p0 + GS_IPT <= C;
     uint32_t fl[GS_IPT];
     int32_t ci[GS_IPT];
-    cand_load(ws, p0, C, fl, ci);
+    cand_load(ws, cand, p0, C, fl, ci);
     PK pi = 0, pe = 0;
     uint32_t nf = 0u;
 #pragma unroll
@@ -1227,11 +1239,11 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
     }
     if (wrote) {
       if (full) {
-        *reinterpret_cast<int4 *>(ws.cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
+        *reinterpret_cast<int4 *>(cand + p0) = make_int4(ci[0], ci[1], ci[2], ci[3]);
       } else {
 #pragma unroll
         for (int i = 0; i < GS_IPT; i++)
-          if (p0 + i < C && (fl[i] & GS_CF_FIRST)) ws.cand[p0 + i] = ci[i];
+          if (p0 + i < C && (fl[i] & GS_CF_FIRST)) cand[p0 + i] = ci[i];
       }
     }
   }
@@ -1322,8 +1334,12 @@ __device__ void rowcount_role(const GsWs &ws, int layer, int bx, int nb) {
 template <typename PK>
 __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
   gs_sample_header *h = ws.hdr;
-  __shared__ uint32_t s_wc[GS_NW][GS_FS_NC];
-  __shared__ uint32_t s_base[GS_NW][GS_FS_NC];
+  int32_t *const cand = cand_buf(ws, layer);
+  // Rows are dealt lane-consecutive (row = tile + k * 256 + thread): in every store below the 32 lanes
+  // of a warp append to a list at CONSECUTIVE places, so a warp store touches a few sectors instead of
+  // one per lane (four consecutive rows per thread cost 4x the sector writes; measured, profiles/README.md).
+  __shared__ uint32_t s_wc[GS_IPT * GS_NW][GS_FS_NC];   // class counts of (k, warp) = 32 consecutive rows
+  __shared__ uint32_t s_base[GS_IPT * GS_NW][GS_FS_NC]; // -> list places before them
   __shared__ uint32_t s_run[GS_FS_NC];
   __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
   if (h->status != 0) return;
@@ -1345,81 +1361,70 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
     s_run[threadIdx.x] = threadIdx.x < FS_USED ? ws.fcnt[(size_t)threadIdx.x * ws.cgrid_cap + bx] : 0u;
   __syncthreads();
   for (int t = t0; t < t1; t++) {
-    const int i0 = t * GS_TILE + GS_IPT * (int)threadIdx.x;
-    uint32_t has[GS_IPT] = {0u, 0u, 0u, 0u}, a[GS_IPT], sr[GS_IPT];
-    int32_t nd[GS_IPT] = {0, 0, 0, 0};
+    const int ib = t * GS_TILE + (int)threadIdx.x;  // row of k: ib + k * GS_TPB
+    uint32_t has[GS_IPT], a[GS_IPT], sr[GS_IPT];
+    int32_t nd[GS_IPT];
     int g0[GS_IPT];
-    if (i0 + GS_IPT <= F) {
-      const uint4 h4 = *reinterpret_cast<const uint4 *>(rw_rowhas + i0);
-      const int4 n4 = *reinterpret_cast<const int4 *>(front + i0);
-      const uint4 a4 = *reinterpret_cast<const uint4 *>(rw_ea + i0);
-      const uint4 s4 = *reinterpret_cast<const uint4 *>(rw_selfrank + i0);
-      has[0] = h4.x; has[1] = h4.y; has[2] = h4.z; has[3] = h4.w;
-      nd[0] = n4.x; nd[1] = n4.y; nd[2] = n4.z; nd[3] = n4.w;
-      a[0] = a4.x; a[1] = a4.y; a[2] = a4.z; a[3] = a4.w;
-      sr[0] = s4.x; sr[1] = s4.y; sr[2] = s4.z; sr[3] = s4.w;
-    } else {
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) {
-        a[k] = GS_INF; sr[k] = 0u;
-        if (i0 + k < F) {
-          has[k] = rw_rowhas[i0 + k];
-          nd[k] = front[i0 + k];
-          a[k] = rw_ea[i0 + k];
-          sr[k] = rw_selfrank[i0 + k];
-        }
+    for (int k = 0; k < GS_IPT; k++) {
+      const int i = ib + k * GS_TPB;
+      has[k] = 0u; nd[k] = 0; a[k] = GS_INF; sr[k] = 0u;
+      if (i < F) {
+        has[k] = rw_rowhas[i];
+        nd[k] = front[i];
+        a[k] = rw_ea[i];
+        sr[k] = rw_selfrank[i];
       }
     }
     // self_ids_in: the relabel map at the position of the node's first edge occurrence
     int32_t sin[GS_IPT];
 #pragma unroll
-    for (int k = 0; k < GS_IPT; k++) sin[k] = a[k] == GS_INF ? -1 : __ldcg(ws.cand + a[k]);
-    PK po = 0, pw = 0, pt = 0;
+    for (int k = 0; k < GS_IPT; k++) sin[k] = (a[k] == GS_INF || (GS_DIAG & 2)) ? -1 : __ldcg(cand + a[k]);
+    PK ro[GS_IPT], rw[GS_IPT], rt[GS_IPT];  // exclusive class counts within the (k, warp) block
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
+      PK po = 0, pw = 0, pt = 0;
       g0[k] = -1;
-      if (i0 + k < F) {
+      if (ib + k * GS_TPB < F) {
         g0[k] = owner_of(ws, nd[k]);
         const uint32_t own = 1u << g0[k];
-        po += pkt_spread(has[k], (PK)0);
-        if (has[k] & own) pw += pkt_one<PK>(g0[k]);
-        if (has[k] & ~own) pt += pkt_one<PK>(g0[k]);
+        po = pkt_spread(has[k], (PK)0);
+        if (has[k] & own) pw = pkt_one<PK>(g0[k]);
+        if (has[k] & ~own) pt = pkt_one<PK>(g0[k]);
       }
-    }
-    const PK inc_o = pkt_incl(po), inc_w = pkt_incl(pw), inc_t = pkt_incl(pt);
-    {
+      const PK inc_o = pkt_incl(po), inc_w = pkt_incl(pw), inc_t = pkt_incl(pt);
+      ro[k] = inc_o - po; rw[k] = inc_w - pw; rt[k] = inc_t - pt;
       const PK t_o = __shfl_sync(FULL, inc_o, 31), t_w = __shfl_sync(FULL, inc_w, 31), t_t = __shfl_sync(FULL, inc_t, 31);
       if (lane < 8) {
         const bool in = lane < (int)sizeof(PK);
-        s_wc[w][FS_OUT(lane)] = in ? pkt_get<PK>(t_o, lane) : 0u;
-        s_wc[w][FS_OWN(lane)] = in ? pkt_get<PK>(t_w, lane) : 0u;
-        s_wc[w][FS_TO(lane)] = in ? pkt_get<PK>(t_t, lane) : 0u;
+        s_wc[k * GS_NW + w][FS_OUT(lane)] = in ? pkt_get<PK>(t_o, lane) : 0u;
+        s_wc[k * GS_NW + w][FS_OWN(lane)] = in ? pkt_get<PK>(t_w, lane) : 0u;
+        s_wc[k * GS_NW + w][FS_TO(lane)] = in ? pkt_get<PK>(t_t, lane) : 0u;
       }
     }
     __syncthreads();
     if (threadIdx.x < FS_USED) {
       uint32_t run = s_run[threadIdx.x];
-#pragma unroll
-      for (int k = 0; k < GS_NW; k++) {
-        s_base[k][threadIdx.x] = run;
-        run += s_wc[k][threadIdx.x];
+#pragma unroll 8
+      for (int j = 0; j < GS_IPT * GS_NW; j++) {
+        s_base[j][threadIdx.x] = run;
+        run += s_wc[j][threadIdx.x];
       }
       s_run[threadIdx.x] = run;
     }
     __syncthreads();
-#define FS_B(c) (s_base[w][c])
-    PK ro = inc_o - po, rw = inc_w - pw, rt = inc_t - pt;
 #pragma unroll
     for (int k = 0; k < GS_IPT; k++) {
-      const int i = i0 + k;
-      if (i < F) {
+      const int i = ib + k * GS_TPB;
+      const uint32_t *bs = s_base[k * GS_NW + w];
+      if (i < F && !(GS_DIAG & 1)) {
         const int gq = g0[k];
         const uint32_t own = 1u << gq;
         int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
         for (uint32_t hb = has[k]; hb; hb &= hb - 1u) {
           const int q = __ffs((int)hb) - 1;
-          const uint32_t op = FS_B(FS_OUT(q)) + pkt_get<PK>(ro, q);
-          const uint32_t ow = FS_B(FS_OWN(q)) + pkt_get<PK>(rw, q);
+          const uint32_t op = bs[FS_OUT(q)] + pkt_get<PK>(ro[k], q);
+          const uint32_t ow = bs[FS_OWN(q)] + pkt_get<PK>(rw[k], q);
           ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd[k];
           ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * rs_stride + q];
           if (q == gq) {
@@ -1429,17 +1434,11 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
             ws.slab[s_fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
           }
         }
-        if (has[k] & ~own) {
-          ws.slab[s_fo[gq][GS_F_TO_IDS] + FS_B(FS_TO(gq)) + pkt_get<PK>(rt, gq)] = op_own;
-          rt += pkt_one<PK>(gq);
-        }
+        if (has[k] & ~own) ws.slab[s_fo[gq][GS_F_TO_IDS] + bs[FS_TO(gq)] + pkt_get<PK>(rt[k], gq)] = op_own;
         ws.slab[s_fo[gq][GS_F_SELF_IN] + sr[k]] = sin[k];
         ws.slab[s_fo[gq][GS_F_SELF_OUT] + sr[k]] = op_own;
-        ro += pkt_spread(has[k], (PK)0);
-        if (has[k] & own) rw += pkt_one<PK>(gq);
       }
     }
-#undef FS_B
   }
 }
 
@@ -1451,6 +1450,7 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
 // next layer's k_rows (or in k_tail).  bx / nb: this role's CTA index and count.
 __device__ void relabel_role(const GsWs &ws, int layer, int bx, int nb) {
   const gs_sample_header *h = ws.hdr;
+  int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   const int P = ws.P;
   for (int q = 0; q < P; q++) {
@@ -1465,7 +1465,7 @@ __device__ void relabel_role(const GsWs &ws, int layer, int bx, int nb) {
         v[k] = e < sp.len ? ix[e] : 0;  // >= 0: already final (written by the first occurrence)
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(ws.cand + (uint32_t)~v[k]) : 0;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(cand + (uint32_t)~v[k]) : 0;
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
@@ -1517,33 +1517,41 @@ __device__ void gather_role(const GsWs &ws, int bx, int nb) {
 
 // ------------------------------------------------------------------ kernels
 // WIDE: more than 4 parts -> packed per-part counters are 64-bit words (else 32-bit).
-template <bool FIRST, bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__restrict__ wsv, int layer, int grid_rows,
-                                                                int grid_relabel) {
+template <bool FIRST>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_rows(const GsWs *__restrict__ wsv, int layer) {
+  __shared__ GsWs ws;
+  stage_ws(ws, wsv + blockIdx.y);
+  rows_role<FIRST>(ws, layer);
+}
+
+// Extra CTAs of an expand launch: relabel and row side of the PREVIOUS layer (they need
+// k_cand_apply's output and nothing of this layer; none of their arrays is written here).
+template <typename PK>
+__device__ __forceinline__ void lists_roles(const GsWs &ws, int layer, int bx, int grid_relabel, int grid_rowside) {
+  if (bx < grid_relabel) relabel_role(ws, layer, bx, grid_relabel);
+  else rowside_role<PK>(ws, layer, bx - grid_relabel, grid_rowside);
+}
+
+template <int RNG, bool WIDE>
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand(const GsWs *__restrict__ wsv, int layer, int grid_expand,
+                                                                    int grid_relabel) {
   typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
   const int bx = (int)blockIdx.x;
-  if (bx < grid_rows) rows_role<FIRST>(ws, layer);
-  else if (FIRST) return;
-  else if (bx < grid_rows + grid_relabel) relabel_role(ws, layer - 1, bx - grid_rows, grid_relabel);
-  else rowside_role<PK>(ws, layer - 1, bx - grid_rows - grid_relabel, (int)gridDim.x - grid_rows - grid_relabel);
+  if (bx < grid_expand) expand_role<RNG, PK>(ws, layer, grid_expand);
+  else lists_roles<PK>(ws, layer - 1, bx - grid_expand, grid_relabel, (int)gridDim.x - grid_expand - grid_relabel);
 }
 
 template <int RNG, bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand(const GsWs *__restrict__ wsv, int layer) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand_rows(const GsWs *__restrict__ wsv, int layer,
+                                                                         int grid_expand, int grid_relabel) {
   typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
-  expand_role<RNG, PK>(ws, layer);
-}
-
-template <int RNG, bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_EXPAND) k_expand_rows(const GsWs *__restrict__ wsv, int layer) {
-  typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
-  __shared__ GsWs ws;
-  stage_ws(ws, wsv + blockIdx.y);
-  expand_rows_role<RNG, PK>(ws, layer);
+  const int bx = (int)blockIdx.x;
+  if (bx < grid_expand) expand_rows_role<RNG, PK>(ws, layer, grid_expand);
+  else lists_roles<PK>(ws, layer - 1, bx - grid_expand, grid_relabel, (int)gridDim.x - grid_expand - grid_relabel);
 }
 
 template <bool WIDE>
@@ -1571,7 +1579,7 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_cand_apply(const GsWs 
 // descriptors: once per 2^30 scans), the last CTA to finish closes the header,
 // mirrors it to pinned host memory and prepares the slot's state for the next sample.
 template <bool WIDE>
-__global__ void __launch_bounds__(GS_TPB, GS_MINB_ROWS) k_tail(const GsWs *__restrict__ wsv, int grid_relabel, int grid_rowside, int grid_gather) {
+__global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_tail(const GsWs *__restrict__ wsv, int grid_relabel, int grid_rowside, int grid_gather) {
   typedef typename std::conditional<WIDE, unsigned long long, uint32_t>::type PK;
   __shared__ GsWs ws;
   stage_ws(ws, wsv + blockIdx.y);
@@ -1806,33 +1814,30 @@ __global__ void __launch_bounds__(256) k_sector_probe(const uint32_t *__restrict
 
 // ---------------------------------------------------------------- launchers
 void gs_kernels_prepare() {}
-void gs_launch_rows(const GsWs *wsv, int members, bool wide, int layer, int grid_rows, int grid_relabel,
-                    int grid_rowside, cudaStream_t st) {
-  if (layer == 0) {
-    if (wide) k_rows<true, true><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows, 0);
-    else k_rows<true, false><<<dim3(grid_rows, members), GS_TPB, 0, st>>>(wsv, 0, grid_rows, 0);
-    return;
-  }
-  const dim3 g(grid_rows + grid_relabel + grid_rowside, members);
-  if (wide) k_rows<false, true><<<g, GS_TPB, 0, st>>>(wsv, layer, grid_rows, grid_relabel);
-  else k_rows<false, false><<<g, GS_TPB, 0, st>>>(wsv, layer, grid_rows, grid_relabel);
+void gs_launch_rows(const GsWs *wsv, int members, int layer, int grid_rows, cudaStream_t st) {
+  const dim3 g(grid_rows, members);
+  if (layer == 0) k_rows<true><<<g, GS_TPB, 0, st>>>(wsv, 0);
+  else k_rows<false><<<g, GS_TPB, 0, st>>>(wsv, layer);
 }
 template <bool WIDE>
-static void launch_expand_t(const GsWs *wsv, dim3 g, int rng_mode, bool by_rows, int layer, cudaStream_t st) {
+static void launch_expand_t(const GsWs *wsv, dim3 g, int rng_mode, bool by_rows, int layer, int ge, int gr,
+                            cudaStream_t st) {
   if (by_rows) {  // sampled layer: one thread per (row, block of four picks)
-    if (rng_mode == (int)GS_RNG_DRAWS) k_expand_rows<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
-    else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand_rows<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
-    else k_expand_rows<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+    if (rng_mode == (int)GS_RNG_DRAWS) k_expand_rows<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
+    else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand_rows<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
+    else k_expand_rows<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
     return;
   }
-  if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
-  else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
-  else k_expand<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer);
+  if (rng_mode == (int)GS_RNG_DRAWS) k_expand<(int)GS_RNG_DRAWS, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
+  else if (rng_mode == (int)GS_RNG_PHILOX_NOREPLACE) k_expand<(int)GS_RNG_PHILOX_NOREPLACE, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
+  else k_expand<(int)GS_RNG_PHILOX, WIDE><<<g, GS_TPB, 0, st>>>(wsv, layer, ge, gr);
 }
 void gs_launch_expand(const GsWs *wsv, int members, bool wide, int rng_mode, bool by_rows, int layer, int grid,
-                      cudaStream_t st) {
-  if (wide) launch_expand_t<true>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
-  else launch_expand_t<false>(wsv, dim3(grid, members), rng_mode, by_rows, layer, st);
+                      int grid_relabel, int grid_rowside, cudaStream_t st) {
+  // grid_relabel / grid_rowside: CTAs that finish the PREVIOUS layer's lists (0 for layer 0)
+  const dim3 g(grid + grid_relabel + grid_rowside, members);
+  if (wide) launch_expand_t<true>(wsv, g, rng_mode, by_rows, layer, grid, grid_relabel, st);
+  else launch_expand_t<false>(wsv, g, rng_mode, by_rows, layer, grid, grid_relabel, st);
 }
 void gs_launch_cand(const GsWs *wsv, int members, bool wide, int pass, int layer, int grid, int grid_rowcount,
                     cudaStream_t st) {
