@@ -97,6 +97,15 @@ __device__ __forceinline__ int32_t ld_stream_i32(const int32_t *a, bool hint, ui
   asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(a), "l"(pol));
   return r;
 }
+// Final list entries are written once and not read again by the chain: streaming stores
+// (evict-first) keep them from pushing the chain's intermediates out of L2.  -DGS_OUT_STREAM=0 for A/B.
+__device__ __forceinline__ void st_out(int32_t *p, int32_t v) {
+#if GS_OUT_STREAM
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -561,6 +570,9 @@ __device__ __forceinline__ bool last_block_n(uint32_t *ticket, uint32_t n) {
 
 // -DGS_DIAG=bits: knock-out builds for tools/build_variants.sh (WRONG results; they only show what a
 // piece of work costs with all slots in flight).  1: row side writes nothing, 2: no relabel-map read.
+#ifndef GS_OUT_STREAM
+#define GS_OUT_STREAM 1
+#endif
 #ifndef GS_DIAG
 #define GS_DIAG 0
 #endif
@@ -832,6 +844,8 @@ template <int RNG, typename PK>
 __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
   gs_sample_header *h = ws.hdr;
   int32_t *const cand = cand_buf(ws, layer);
+  __shared__ int32_t s_stage_c[GS_NW][160];
+  __shared__ uint8_t s_stage_f[GS_NW][160];
   if (h->status != 0) return;
   const Tbl tbl(ws);
   const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
@@ -871,24 +885,45 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
     const uint32_t item = it0 + threadIdx.x;
     PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
     uint32_t n_new = 0u;
+    // phase A: the item's row and the positions it owns
+    uint32_t row = 0u, b = 0u, o = 0u;
+    int4 ri = make_int4(0, 0, 0, 0);
+    int nj = 0, j0 = 0;
+    uint32_t lane_lo = GS_INF, lane_hi = 0u;
     if (item < nitems) {
-      uint32_t row = item;  // nb == 1: ceil(2^32 / nb) does not fit the magic word
+      row = item;  // nb == 1: ceil(2^32 / nb) does not fit the magic word
       if (nb > 1u) {
         row = __umulhi(item, nbm);
         if (row * nb > item) row--;
       }
-      const uint32_t b = item - row * nb;
-      const int4 ri = ws.rowinfo[row];
-      const uint32_t o = ws.off[row], c = ws.off[row + 1] - o;
+      b = item - row * nb;
+      ri = ws.rowinfo[row];
+      o = ws.off[row];
+      const uint32_t c = ws.off[row + 1] - o;
+      j0 = (int)(4u * b);
+      nj = min(4, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
+      if (nj > 0) {
+        lane_lo = o + 1u + (uint32_t)j0;
+        lane_hi = lane_lo + (uint32_t)nj;
+      }
+      if (b == 0u) {
+        lane_lo = o;
+        lane_hi = max(lane_hi, o + 1u);
+      }
+    }
+    // The items of a warp own one contiguous range of positions (< 160): staged in shared memory,
+    // written out as whole sectors (per-lane stores of four words at a stride cost 4x the sectors).
+    const uint32_t pmin = __reduce_min_sync(FULL, lane_lo), pmax = __reduce_max_sync(FULL, lane_hi);
+    int32_t *st_c = s_stage_c[warp_id()];
+    uint8_t *st_f = s_stage_f[warp_id()];
+    if (item < nitems) {
       const int64_t rs = (int64_t)(((uint64_t)((uint32_t)ri.y & 0x1FFFFFFFu) << 32) | (uint32_t)ri.x);
       const int g0 = (int)((uint32_t)ri.y >> 29);
       const int32_t deg = ri.z, nd = ri.w;
       const bool samp = deg >= fan;
-      const int j0 = (int)(4u * b);
-      const int nj = min(4, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
       if (b == 0u) {  // the row's self entry (slicer.cpp:7)
-        cand[o] = (int32_t)row;
-        ws.cflag[o] = (uint8_t)(GS_CK_SELF | ((uint32_t)g0 << GS_CF_PART_SHIFT));
+        st_c[o - pmin] = (int32_t)row;
+        st_f[o - pmin] = (uint8_t)(GS_CK_SELF | ((uint32_t)g0 << GS_CF_PART_SHIFT));
       }
       if (nj > 0) {
         uint4 blk = make_uint4(0u, 0u, 0u, 0u);
@@ -958,8 +993,8 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
                 cf = GS_CK_FHIT | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
               }
             }
-            cand[p1 + j] = cv;
-            ws.cflag[p1 + j] = (uint8_t)cf;
+            st_c[p1 + j - pmin] = cv;
+            st_f[p1 + j - pmin] = (uint8_t)cf;
           }
         }
         const uint32_t nbits = rbits & ~was;
@@ -971,6 +1006,15 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
         }
       }
     }
+    __syncwarp();
+    if (pmax > pmin) {
+      const uint32_t len = pmax - pmin;
+      for (uint32_t j = (uint32_t)lane; j < len; j += 32u) {
+        cand[pmin + j] = st_c[j];
+        ws.cflag[pmin + j] = st_f[j];
+      }
+    }
+    __syncwarp();
     pk_in = pkt_redux(pk_in);
     pk_e = pkt_redux(pk_e);
     pk_out = pkt_redux(pk_out);
@@ -1225,7 +1269,7 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
           // that first occurrence and leaves ~m for relabel_role
           const uint32_t rk = bw[CS_IN(g)] + pkt_get<PK>(ri, g);
           const int32_t z = kind == GS_CK_FHIT ? front[ci[i]] : ci[i];  // a new node carries its id, a frontier row its index
-          ws.slab[s_fo_in[g] + rk] = z;
+          st_out(ws.slab + s_fo_in[g] + rk, z);
           ws.slab[s_fo_ix[g] + ex] = (int32_t)rk;
           if (fl[i] & GS_CF_FFIRST) fnext[rf++] = z;
           ci[i] = (int32_t)rk;
@@ -1421,22 +1465,28 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
         const int gq = g0[k];
         const uint32_t own = 1u << gq;
         int32_t op_own = -1;  // position of nd in its own part's out_nodes, or -1
+        // the row's record (edges of every part emitted before it) in one or two 16-byte loads
+        uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
+        if (has[k] & 0x0Fu) r0 = *reinterpret_cast<const uint4 *>(ws.rowscan + (size_t)i * rs_stride);
+        if (sizeof(PK) > 4 && (has[k] & 0xF0u)) r1 = *reinterpret_cast<const uint4 *>(ws.rowscan + (size_t)i * rs_stride + 4);
         for (uint32_t hb = has[k]; hb; hb &= hb - 1u) {
           const int q = __ffs((int)hb) - 1;
           const uint32_t op = bs[FS_OUT(q)] + pkt_get<PK>(ro[k], q);
           const uint32_t ow = bs[FS_OWN(q)] + pkt_get<PK>(rw[k], q);
-          ws.slab[s_fo[q][GS_F_OUT_NODES] + op] = nd[k];
-          ws.slab[s_fo[q][GS_F_CSR_INDPTR] + op] = (int32_t)ws.rowscan[(size_t)i * rs_stride + q];
+          const uint4 rr = q < 4 ? r0 : r1;
+          const uint32_t rsq = (q & 3) == 0 ? rr.x : (q & 3) == 1 ? rr.y : (q & 3) == 2 ? rr.z : rr.w;
+          st_out(ws.slab + s_fo[q][GS_F_OUT_NODES] + op, nd[k]);
+          st_out(ws.slab + s_fo[q][GS_F_CSR_INDPTR] + op, (int32_t)rsq);
           if (q == gq) {
-            ws.slab[s_fo[q][GS_F_OWNED_OUT] + ow] = (int32_t)op;
+            st_out(ws.slab + s_fo[q][GS_F_OWNED_OUT] + ow, (int32_t)op);
             op_own = (int32_t)op;
           } else {
-            ws.slab[s_fo[q][GS_F_FROM_IDS] + (op - ow)] = (int32_t)op;
+            st_out(ws.slab + s_fo[q][GS_F_FROM_IDS] + (op - ow), (int32_t)op);
           }
         }
-        if (has[k] & ~own) ws.slab[s_fo[gq][GS_F_TO_IDS] + bs[FS_TO(gq)] + pkt_get<PK>(rt[k], gq)] = op_own;
-        ws.slab[s_fo[gq][GS_F_SELF_IN] + sr[k]] = sin[k];
-        ws.slab[s_fo[gq][GS_F_SELF_OUT] + sr[k]] = op_own;
+        if (has[k] & ~own) st_out(ws.slab + s_fo[gq][GS_F_TO_IDS] + bs[FS_TO(gq)] + pkt_get<PK>(rt[k], gq), op_own);
+        st_out(ws.slab + s_fo[gq][GS_F_SELF_IN] + sr[k], sin[k]);
+        st_out(ws.slab + s_fo[gq][GS_F_SELF_OUT] + sr[k], op_own);
       }
     }
   }
@@ -1469,7 +1519,7 @@ __device__ void relabel_role(const GsWs &ws, int layer, int bx, int nb) {
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        if (v[k] < 0) ix[e] = r[k];
+        if (v[k] < 0) st_out(ix + e, r[k]);
       }
     }
   }
