@@ -266,9 +266,11 @@ def kernel_bytes(view, P):
         rowside = F * (4 * 4 + 4) + n_out * 4 + (2 * n_out + lists) * 4     # nd, rowhas, ea, selfrank, relabel map; rowscan; lists out
         tail[l] = relabel + rowside
         rows = F * (4 + 16) + F * (16 + 4 + 4 + 4 + 4 + 4)                 # frontier + indptr pair in; rowinfo, off, selfrank, ea, rowhas, table mark out
-        out[f"rows@{l}" if l == 0 else f"rows+relabel+rowside@{l}"] = rows + (tail[l - 1] if l else 0)
-        out[f"expand@{l}"] = F * 20 + (C - F) * (4 + 4) + C * 5 + (C - F) * 4   # rowinfo + off, pick + atom.min per edge, stream out, rowhas
-        out[f"cand_flags@{l}"] = C * 5 + C * 4 + C * 1 + (E - n_in) * 4            # stream in, table / ea read, flags + moved words out
+        out[f"rows@{l}"] = rows
+        expand = F * 20 + (C - F) * (4 + 4) + C * 5 + (C - F) * 4               # rowinfo + off, pick + atom.min per edge, stream out, rowhas
+        # relabel and row side of layer l - 1 ride in this launch
+        out[f"expand@{l}" if l == 0 else f"expand+relabel+rowside@{l}"] = expand + (tail[l - 1] if l else 0)
+        out[f"cand_flags+rowcount@{l}"] = C * 5 + C * 4 + C * 1 + (E - n_in) * 4 + F * 8   # stream in, table / ea read, flags + moved words out; rowhas + ids
         out[f"cand_apply@{l}"] = C * 5 + (Fn + n_in + E) * 4 + F * 16              # stream in, lists + rowscan records out
     out["relabel+rowside+finish"] = tail[L - 1]
     return out
@@ -1068,7 +1070,7 @@ def main():
     global BATCH, FANOUTS
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--shape", default=SHAPE)

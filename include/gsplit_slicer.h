@@ -274,6 +274,36 @@ int gs_reference_shuffle(int64_t *nodes, int64_t n, int reset);
  * The reference has no counterpart (a CPU program). */
 int gs_bench_sector_probe(int device, int64_t table_bytes, int64_t n_reads, double *reads_per_s);
 
+/* ------------------------------------------------------------------------
+ * the edge partitioning of the Python sibling's sampler
+ * (Sampler.edge_partitioning, python/utils/sampler.py:64-134).  For one layer's
+ * edges (src = the sampled neighbour or the self loop, dest = the node it feeds):
+ *   every layer but the last  (last_layer = 0): the edge goes to the owner of src
+ *     (:76); owned_nds[g] = sorted unique dest owned by g (:80-81); shuffle_nds[g][r] =
+ *     sorted unique dest owned by r != g among g's edges (:83-87);
+ *   the last layer (last_layer = 1): if src is resident in the feature cache of
+ *     owner(dest) -- resident[src * P + owner(dest)], the reference's
+ *     memory_manager.node_gpu_mask -- the edge stays with owner(dest), else it goes
+ *     to owner(src) (:93-106); part g = its natural edges then its extra edges, each in
+ *     edge order (:107-110); shuffle_nds over g's extra edges only (:114-119).
+ * owner_host: int32[num_nodes] (workload_assignment); resident_host: uint8
+ * [num_nodes * num_parts] row-major, or NULL if last_layer is never used.
+ * gs_epart_run takes host int64 edge arrays (the reference's CPU tensors), runs on the
+ * GPU and returns when the lists are in the handle's pinned host buffers (and still on
+ * the device).  Errors: an endpoint outside [0, num_nodes) -> GS_ERR_INVALID. */
+typedef struct gs_epart gs_epart;
+enum { GS_EP_SRC = 0, GS_EP_DST = 1, GS_EP_OWNED = 2, GS_EP_SHUFFLE = 3, GS_EP_NUM_EXTRA = 4 };
+int gs_epart_create(int device, int64_t num_nodes, int32_t num_parts, const int32_t *owner_host,
+                    const uint8_t *resident_host, int64_t max_edges, gs_epart **out);
+int gs_epart_destroy(gs_epart *e);
+int gs_epart_run(gs_epart *e, const int64_t *src_host, const int64_t *dst_host, int64_t n_edges,
+                 int32_t last_layer);
+/* List `what` of part `part` (remote: the peer of GS_EP_SHUFFLE, else ignored) of the last
+ * run: host / device pointers (either may be NULL) and length.  GS_EP_NUM_EXTRA: *len =
+ * number of extra edges of the part (the reference's shuffle_nds is {} when it is 0). */
+int gs_epart_get(gs_epart *e, int32_t part, int32_t what, int32_t remote, const int32_t **host,
+                 const int32_t **device, int64_t *len);
+
 /* Allocation-free frontier dedup.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid it).

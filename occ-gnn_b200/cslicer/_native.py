@@ -27,7 +27,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_flush", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_slicer_slab_capacity", "gs_reference_shuffle", "gs_bench_sector_probe",
-           "gs_unique_first_noalloc",
+           "gs_unique_first_noalloc", "gs_epart_create", "gs_epart_destroy", "gs_epart_run", "gs_epart_get",
            "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
            "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts", "gs_slicer_scatter_parts",
@@ -137,6 +137,12 @@ def lib():
     L.gs_ipc_free.argtypes = [C.c_int, C.c_void_p]
     L.gs_reference_shuffle.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     L.gs_bench_sector_probe.argtypes = [C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_double)]
+    L.gs_epart_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64,
+                                  C.POINTER(C.c_void_p)]
+    L.gs_epart_destroy.argtypes = [C.c_void_p]
+    L.gs_epart_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]
+    L.gs_epart_get.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p),
+                               C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     L.gs_unique_first_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                           C.POINTER(C.c_int64)]
     L.gs_features_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
