@@ -483,6 +483,10 @@ def own_arm(args):
             except Exception as e:
                 out["owner_range"] = {"unavailable": f"{type(e).__name__}: {e}"}
             try:
+                out["edge_partitioning"] = edge_partitioning_line(n, P, sizes)
+            except Exception as e:
+                out["edge_partitioning"] = {"unavailable": f"{type(e).__name__}: {e}"}
+            try:
                 out["reference_config"] = reference_config(ip, ix, g, args, torch)
             except Exception as e:  # context only; never fail the bench line on it
                 out["reference_config"] = {"unavailable": f"{type(e).__name__}: {e}"}
@@ -936,6 +940,36 @@ def reference_config(ip, ix, g, args, torch):
             "cuda_value": round(5 * args.mb_per_step / (ms * 1e-3), 2),
             "cuda_e2e": round(3 * args.mb_per_step / (ms2 * 1e-3), 2),
             "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
+
+
+def edge_partitioning_line(n, P, sizes, reps=3):
+    """Sampler.edge_partitioning (python/utils/sampler.py:64-134) on blocks of
+    this workload's size -- the CUDA partitioner through its host-buffer C ABI (copies inside the
+    timed region) next to the numpy restatement of the reference method, same inputs."""
+    from cslicer.epart import EdgePartitioner
+    from oracle import sampler_oracle as SO
+    rng = np.random.default_rng(7)
+    owner = (np.arange(n) % P).astype(np.int32)
+    mask = rng.random((n, P)) < 0.25
+    mask[np.arange(n), owner] = True
+    blocks = [(rng.integers(0, n, c), rng.integers(0, n, c)) for c in sizes["candidates"]]
+    edges = sum(b[0].size for b in blocks)
+    ep = EdgePartitioner(owner, mask, P, max_edges=max(b[0].size for b in blocks))
+    ep.edge_partitioning(blocks)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        got = ep.edge_partitioning(blocks)
+    t_gpu = (time.perf_counter() - t0) / reps
+    ep.close()
+    t0 = time.perf_counter()
+    want = SO.edge_partitioning(blocks, owner, mask, P)
+    t_cpu = time.perf_counter() - t0
+    same = all(np.array_equal(a[k], b[k]) for gl, wl in zip(got, want) for a, b in zip(gl, wl) for k in ("src", "dest", "owned_nds"))
+    return {"edges_per_call": edges, "layers": len(blocks), "cuda_ms": round(t_gpu * 1e3, 3),
+            "cuda_edges_per_s": round(edges / t_gpu, 1), "cpu_restatement_ms": round(t_cpu * 1e3, 1),
+            "cpu_edges_per_s": round(edges / t_cpu, 1), "parity": "equal" if same else "DIFFERENT",
+            "what": "host int64 edge arrays in, per-GPU lists back in pinned host memory (H2D + D2H inside the time); "
+                    "25 % of the nodes cached per GPU on the last layer"}
 
 
 def _time_gather(F, ids, torch, reps=5):

@@ -182,9 +182,11 @@ class cslicer:
             self._submitted += 1
 
     def _live_count(self):
-        while self._live and (self._live[0]() is None or self._live[0]()._view._released):
+        # _live holds weak references to the SampleViews (not the samples): a slot stays taken
+        # for as long as ANY object -- the sample or a bipatite taken from it -- keeps its view alive
+        while self._live and (self._live[0]() is None or self._live[0]()._released):
             self._live.popleft()
-        return sum(1 for r in self._live if r() is not None and not r()._view._released)
+        return sum(1 for r in self._live if r() is not None and not r()._released)
 
     def getNoSamples(self):  # pyfrontend.cpp:80-83
         return self._total
@@ -196,21 +198,21 @@ class cslicer:
             # every slot is pinned by a sample the caller still holds: copy the
             # oldest one out of its slot (the reference deep-copies every sample)
             for r in list(self._live):
-                s = r()
-                if s is not None and not s._view._released:
-                    s._view.detach()
+                v = r()
+                if v is not None and not v._released:
+                    v.detach()
                     break
             self._fill()
         slot = self._inflight.popleft()
         view = self.slicer.wait(slot)
         s = sample(view, compat=self.compat)
-        self._live.append(weakref.ref(s))
+        self._live.append(weakref.ref(view))
         self._returned += 1
         if self._live_count() >= self.slicer.num_slots and self._returned < self._total:
             for r in list(self._live):
                 o = r()
-                if o is not None and o is not s and not o._view._released:
-                    o._view.detach()
+                if o is not None and o is not view and not o._released:
+                    o.detach()
                     break
         self._fill()
         return s

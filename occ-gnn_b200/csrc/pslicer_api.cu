@@ -337,21 +337,36 @@ int gs_pslicer_create(int device, int64_t N, int64_t n_local, int64_t m_local,
       return gs_set_error(GS_ERR_CUDA, keep.c_str());   \
     }                                                   \
   } while (0)
-  // graph shard
+  // graph shard; validated on the device like gs_graph_create's (the kernels index the
+  // shard's rows and the peers' tables with these ids)
   CUS(cudaMalloc((void **)&s->indptr, (size_t)(n_local + 1) * sizeof(int64_t)));
   CUS(cudaMemcpy(s->indptr, indptr_host, (size_t)(n_local + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
   CUS(cudaMalloc((void **)&s->indices, (size_t)std::max<int64_t>(m_local, 1) * sizeof(int32_t)));
   {
     const int64_t chunk = 1ll << 26;
     int64_t *tmp = nullptr;
+    unsigned long long *err = nullptr, bad[2] = {0, 0};
+    CUS(cudaMalloc((void **)&err, 2 * sizeof(unsigned long long)));
+    CUS(cudaMemset(err, 0xFF, 2 * sizeof(unsigned long long)));
+    gs_launch_check_indptr(s->indptr, n_local, m_local, err, 0);
     CUS(cudaMalloc((void **)&tmp, (size_t)std::min(chunk, std::max<int64_t>(m_local, 1)) * sizeof(int64_t)));
     for (int64_t o = 0; o < m_local; o += chunk) {
       const int64_t n = std::min(chunk, m_local - o);
       CUS(cudaMemcpy(tmp, indices_host + o, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice));
+      gs_launch_check_ids(tmp, (size_t)n, o, N, err, 0);
       gs_launch_narrow_ids(tmp, s->indices + o, (size_t)n, 0);
     }
+    CUS(cudaMemcpy(bad, err, sizeof bad, cudaMemcpyDeviceToHost));
     CUS(cudaDeviceSynchronize());
     cudaFree(tmp);
+    cudaFree(err);
+    if (bad[0] != ~0ull || bad[1] != ~0ull) {
+      gs_pslicer_destroy(s);
+      if (bad[0] != ~0ull)
+        return pfail(GS_ERR_INVALID, "indptr_local is not a non-decreasing sequence inside [0, m_local]: first bad row %llu",
+                     bad[0] - 1ull);
+      return pfail(GS_ERR_INVALID, "indices_local[%llu] lies outside [0, num_nodes_global)", bad[1] - 1ull);
+    }
   }
   // arena
   if (cfg->shuffle_rows_capacity < 0 || cfg->shuffle_max_dim < 0) {

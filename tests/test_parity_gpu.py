@@ -534,6 +534,28 @@ def test_reference_facing_module_end_to_end(tmp_path):
     csl.close()
 
 
+def test_bipatites_that_outlive_their_sample_keep_the_loop_running(tmp_path):
+    """A caller may keep one bipatite of every sample and drop the sample itself (the
+    reference returns deep copies): the slot stays pinned by the view, and getSample()
+    must make room by detaching the oldest view instead of failing with GS_ERR_BUSY."""
+    import gc
+    import cslicer as M
+    z = np.load(os.path.join(GOLD, "hubs.npz"))
+    m = META["hubs"]
+    M.write_dataset(str(tmp_path / "hubs"), z["indptr"], z["indices"])
+    csl = M.cslicer("hubs", 16, 32, 1, m["minibatch"], root=str(tmp_path), draws=O.mt19937_stream(400000))
+    kept, digests = [], []
+    for i in range(csl.getNoSamples()):
+        s = csl.getSample()
+        digests.append(refstream.digest_module_sample(s))
+        kept.append(s.layers[0][0])  # keeps the SampleView alive
+        del s
+        gc.collect()
+    assert digests == m["sha256"]
+    assert all(isinstance(b.in_nodes, list) for b in kept)  # still readable (detached copies)
+    csl.close()
+
+
 def test_nvtx_ranges_can_be_switched_on():
     """GSPLIT_NVTX=1 (tracing): the C ABI wraps submit / wait in NVTX
     ranges; results and exit status are unchanged (run in a child: the switch is read once)."""

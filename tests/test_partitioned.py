@@ -378,3 +378,22 @@ def test_missing_peer_times_out_with_err_peer_and_the_group_recovers():
             _compare_rank(v, want, g)
             v.release()
     grp.close()
+
+
+@pytest.mark.gpu
+def test_malformed_shard_is_rejected_at_create():
+    """gs_pslicer_create validates its CSR shard on the device like gs_graph_create: the
+    kernels index the shard's rows and the peers' tables with these ids."""
+    from cslicer import _native
+    from cslicer.partitioned import PartitionedSlicer
+    # rank 0 of 2 (owner = id % 2) of a 6-node graph owns nodes 0, 2, 4: three local rows
+    ip = np.array([0, 2, 3, 4], np.int64)
+    for bad_ix, what in (([1, 2, 6, 0], "indices_local[2]"), ([1, -1, 0, 3], "indices_local[1]")):
+        with pytest.raises(_native.SlicerError) as e:
+            PartitionedSlicer(ip, np.array(bad_ix, np.int64), 6, 0, 2, [2])
+        assert e.value.code == _native.ERR_INVALID and what in str(e.value)
+    with pytest.raises(_native.SlicerError) as e:  # not monotone
+        PartitionedSlicer(np.array([0, 3, 2, 4], np.int64), np.array([1, 2, 3, 0], np.int64), 6, 0, 2, [2])
+    assert e.value.code == _native.ERR_INVALID and "indptr_local" in str(e.value)
+    ps = PartitionedSlicer(ip, np.array([1, 2, 5, 0], np.int64), 6, 0, 2, [2])  # the well-formed shard loads
+    ps.close()
