@@ -245,6 +245,21 @@ int gs_slicer_pack_parts(gs_slicer *s, int32_t slot, int32_t *dst_device, int64_
 int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks,
                             int64_t block_words, void *after_event, void *consumer_stream);
 
+/* Direct hand-over: like gs_slicer_submit, but the sample's OWN kernels write every list
+ * of part g straight into dst_blocks[g] (local or peer memory, e.g. a buffer of rank g
+ * mapped with gs_ipc_open) in the block layout of gs_slicer_pack_parts -- each list
+ * crosses NVLink once, as it is produced; nothing is written to the slot's slab and no
+ * packing kernel runs.  after_event (a recorded cudaEvent_t or NULL): the sample's launch
+ * sequence first waits for it (the owners are done with these blocks).  Needs group_size
+ * = 1, host_output = 0, no fused feature gather.  gs_slicer_wait() then returns the
+ * header only (its spans are relative to the part's block); gs_slicer_scatter_parts()
+ * on such a slot moves nothing and only makes consumer_stream wait for the sample.
+ * block_words too small -> the sample's status is GS_ERR_OVERFLOW (also in every block
+ * header).  No counterpart in the reference (one process, host vectors). */
+int gs_slicer_submit_direct(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                            int32_t *const *dst_blocks, int64_t block_words, void *after_event,
+                            int32_t *slot_out);
+
 /* Device buffers another process can map (cudaIpcGetMemHandle / OpenMemHandle):
  * handle = 64 bytes.  gs_ipc_open enables peer access to the owner's GPU. */
 int gs_ipc_alloc(int device, int64_t bytes, void **dev_ptr, void *handle_out);

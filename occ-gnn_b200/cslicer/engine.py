@@ -295,6 +295,15 @@ class Slicer:
                                          C.byref(slot)))
         return slot.value
 
+    def submit_direct(self, seeds, batch_index, dst_blocks, block_words, after_event=0):
+        """gs_slicer_submit_direct: the sample's kernels write part g's lists straight into
+        dst_blocks[g] (a ctypes array of num_parts device pointers, local or peer memory)."""
+        s = np.ascontiguousarray(seeds, dtype=np.int64)
+        slot = C.c_int32(-1)
+        N.check(N.lib().gs_slicer_submit_direct(self._h, s.ctypes.data, s.size, int(batch_index), dst_blocks,
+                                                int(block_words), C.c_void_p(after_event), C.byref(slot)))
+        return slot.value
+
     def flush(self):
         """Launch the group being filled with the minibatches staged so far."""
         N.check(N.lib().gs_slicer_flush(self._h))

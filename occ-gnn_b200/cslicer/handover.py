@@ -317,3 +317,46 @@ class PeerScatter:
             self.dist.barrier(group=self.group)
             N.lib().gs_ipc_free(self.device, C.c_void_p(self._base))
             self._base = None
+
+
+class DirectScatter(PeerScatter):
+    """The hand-over without a packing pass: `submit` hands the slicer the P blocks of the
+    next ring buffer and the sample's OWN kernels write every list of part g into rank g's
+    block as they produce it (gs_slicer_submit_direct) -- a list crosses NVLink once and is
+    never written to, or read back from, the slicing GPU's memory.
+
+        slot = ds.submit(seeds, b)   # instead of slicer.submit
+        slicer.wait_header(slot)     # optional: status / sizes
+        k = ds.post(slot)            # ordering + barrier only (no kernel)
+        blocks = ds.collect(k); ...; ds.release(k); slicer._release(slot)
+
+    The target buffer of round X is fixed at submit time and its kernels wait for this
+    rank's barrier X - 1 - slack, so that barrier must have been posted already: at most
+    `slack` rounds may be submitted ahead of the last post (checked)."""
+
+    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3):
+        super().__init__(slicer, dist, block_words, depth=depth, group=group, slack=slack)
+        self._pending = {}
+        self._posted = 0
+
+    def submit(self, seeds, batch_index=0):
+        if self.ring.posted - self._posted >= max(1, self.slack):
+            raise RuntimeError(f"{self.ring.posted - self._posted} rounds submitted and not posted: "
+                               f"at most slack={self.slack} may be in flight before post()")
+        r, k, after = self.ring.next_post()
+        ev = self.done[after % self.nbuf].cuda_event if after is not None else 0
+        slot = self.slicer.submit_direct(seeds, batch_index, self._dst[k], self.block_words, ev)
+        self._pending[slot] = (r, k)
+        return slot
+
+    def post(self, slot):
+        torch = self._torch
+        r, k = self._pending.pop(slot)
+        N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
+                                                None, C.c_void_p(self.stream.cuda_stream)))
+        with torch.cuda.stream(self.stream):
+            self.dist.all_reduce(self._flag, group=self.group)  # barrier: every rank's blocks of round r have landed
+            self.done[k].record(self.stream)
+        self._posted += 1
+        return r
+

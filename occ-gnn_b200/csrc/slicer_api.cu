@@ -75,6 +75,7 @@ struct Slot {
   int64_t copied = 0;                // ... int32 elements of the slab the DMA of this sample moved
   int group = 0;
   int state = SLOT_FREE;
+  bool direct = false;               // submitted with gs_slicer_submit_direct: the lists are in the peers' blocks
 };
 
 // `members` consecutive slots share ONE launch sequence (grid.y = member): the
@@ -212,6 +213,8 @@ int stage_input(gs_slicer *s, Slot &sl, const int64_t *seeds, int32_t n, uint64_
   sl.input->n_seeds = n;
   sl.input->want_host = s->cfg.host_output;
   sl.input->batch_index = batch_index;
+  sl.input->direct = 0;
+  sl.direct = false;
   return GS_OK;
 }
 
@@ -594,6 +597,8 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
     DA(w.rowscan, (s->Fcap + 1) * (cfg->num_parts > 4 ? 8 : 4));  // one record per row
     DA(w.cand, 2 * ((s->Ccap + 7) & ~(int64_t)3));  // ping-pong by layer
     DA(w.cflag, s->Ccap + 4);
+    DA(w.ixs, s->Ccap + 64);
+    DA(w.tgt, 1);
     DA(w.tile_first, ctiles + 1);
     DA(w.cnt, (size_t)L * GS_CNT_STRIDE);
     DA(w.tickets, (size_t)(L + 1) * GS_TICKETS);
@@ -670,8 +675,13 @@ int gs_slicer_create(gs_graph *g, const gs_config *cfg, gs_slicer **out) {
   return GS_OK;
 }
 
-int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
-                     int32_t *slot_out) {
+struct DirectArgs {
+  int32_t *const *dst_blocks;
+  int64_t block_words;
+  void *after_event;
+};
+static int submit_impl(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                       int32_t *slot_out, const DirectArgs *da) {
   if (!s || !slot_out) return fail(GS_ERR_INVALID, "NULL argument");
   const GsRange trace("gs_slicer_submit");
   CU(cudaSetDevice(s->g->device));
@@ -705,11 +715,41 @@ int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_
                 gr.staged);
   int rc = stage_input(s, sl, seeds_host, n, batch_index);
   if (rc != GS_OK) return rc;
+  if (da) {
+    sl.input->direct = 1;
+    sl.input->block_words = da->block_words;
+    for (int g = 0; g < s->cfg.num_parts; g++) sl.input->part_dst[g] = da->dst_blocks[g];
+    sl.direct = true;
+    // the owners are done with these blocks once this event has completed
+    if (da->after_event) CU(cudaStreamWaitEvent(gr.stream, (cudaEvent_t)da->after_event, 0));
+  }
   sl.state = SLOT_STAGED;
   gr.staged++;
   *slot_out = k;
   if (gr.staged == gr.members) return launch_group(s, gr);
   return GS_OK;
+}
+
+int gs_slicer_submit(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                     int32_t *slot_out) {
+  return submit_impl(s, seeds_host, n, batch_index, slot_out, nullptr);
+}
+
+int gs_slicer_submit_direct(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
+                            int32_t *const *dst_blocks, int64_t block_words, void *after_event,
+                            int32_t *slot_out) {
+  if (!s || !slot_out) return fail(GS_ERR_INVALID, "NULL argument");
+  if (s->group_size != 1) return fail(GS_ERR_INVALID, "submit_direct: needs group_size = 1");
+  if (s->cfg.host_output) return fail(GS_ERR_INVALID, "submit_direct: create the slicer with host_output = 0 (the lists leave the GPU)");
+  if (s->feat) return fail(GS_ERR_INVALID, "submit_direct: not combined with the fused feature gather");
+  if (!dst_blocks || block_words < GS_PART_HEADER_WORDS || (block_words & 3) || block_words > 0x7FFFFFF0ll)
+    return fail(GS_ERR_INVALID, "submit_direct: block_words must be a multiple of 4 in [%d, 2^31)",
+                (int)GS_PART_HEADER_WORDS);
+  for (int g = 0; g < s->cfg.num_parts; g++)
+    if (!dst_blocks[g] || ((uintptr_t)dst_blocks[g] & 15))
+      return fail(GS_ERR_INVALID, "submit_direct: dst_blocks[%d] must be a 16-byte aligned device pointer", g);
+  const DirectArgs da{dst_blocks, block_words, after_event};
+  return submit_impl(s, seeds_host, n, batch_index, slot_out, &da);
 }
 
 int gs_slicer_flush(gs_slicer *s) {
@@ -821,6 +861,12 @@ static int scatter_parts(gs_slicer *s, int32_t slot, const GsPartDst &dst, int64
   int rc = flush_if_staged(s, sl);
   if (rc != GS_OK) return rc;
   cudaStream_t st = s->groups[sl.group].stream;
+  if (sl.direct) {
+    // gs_slicer_submit_direct: the sample's own kernels wrote the blocks; only the ordering is left
+    CU(cudaEventRecord(sl.pack_done, st));
+    CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, sl.pack_done, 0));
+    return GS_OK;
+  }
   if (after_event) CU(cudaStreamWaitEvent(st, (cudaEvent_t)after_event, 0));
   // on the group's own stream: after the sample's kernels, before the group's next launch.
   // >= 4 parts (most stores remote): bulk-copy engine, one CTA per SM over all parts keeps

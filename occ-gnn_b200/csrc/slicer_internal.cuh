@@ -48,6 +48,20 @@ struct GsInput {
   int32_t n_seeds;   // < 0: this member of the group holds no minibatch
   int32_t want_host;
   uint64_t batch_index;
+  // direct hand-over (gs_slicer_submit_direct): the lists of part q are written straight into
+  // block q -- local or PEER memory -- behind a block header, nothing into the slot's slab
+  int32_t direct, pad0;
+  int64_t block_words;
+  int32_t *part_dst[GS_MAX_PARTS];
+};
+
+// Where the lists of every part of the slot's current sample go (device memory; written by the
+// sample's first launch from GsInput, read by every later one).
+struct GsTargets {
+  int32_t *base[GS_MAX_PARTS];    // the slot's slab for every part, or the P hand-over blocks
+  int64_t cap;                    // words available behind a base
+  int64_t cursor[GS_MAX_PARTS];   // direct: words of block q in use (header included)
+  int32_t direct, pad0;
 };
 
 // Per-slot state carried from sample to sample; prepared for sample k + 1 by the
@@ -84,6 +98,8 @@ struct GsWs {
   uint32_t *table;       // [N] (tag | kind | payload): kind 0 = node of the current frontier, payload = its row;
                          //     kind 1 = minimum edge-source position of a node new to this layer
   int32_t pos_bits;      // S: payload bits; the kind bit is 1 << S, the tag sits above it
+  GsTargets *tgt;        // list bases of the current sample (slab, or hand-over blocks)
+  int32_t *ixs;          // [Ccap] csr_indices before relabel: rank, or ~position of the first occurrence
   int32_t *slab;         // sample slab: every bipartite list (mirrored to the host in e2e mode)
   int64_t slab_cap;
   int32_t *fslab;        // frontier slab: frontiers 0..L (device only; read back on demand)

@@ -252,6 +252,16 @@ __device__ __forceinline__ void lookback_collect(uint32_t *status, T *agg, T *in
 // after its look-back, which orders it behind that publication).
 __device__ void init_header(const GsWs &ws, int n, int status) {
   gs_sample_header *h = ws.hdr;
+  {
+    GsTargets *tg = ws.tgt;
+    const bool direct = ws.input->direct != 0;
+    tg->direct = direct ? 1 : 0;
+    tg->cap = direct ? ws.input->block_words : ws.slab_cap;
+    for (int q = 0; q < GS_MAX_PARTS; q++) {
+      tg->base[q] = direct && q < ws.P ? ws.input->part_dst[q] : ws.slab;
+      tg->cursor[q] = GS_PART_HEADER_WORDS;
+    }
+  }
   h->status = status;
   h->num_layers = ws.L;
   h->num_parts = ws.P;
@@ -519,25 +529,37 @@ __device__ void layer_alloc(const GsWs &ws, int layer, const uint32_t *cnt /* sh
   int64_t used = h->slab_used, fused = h->reserved[1];
   const gs_span fs = slab_alloc(fused, ws.fslab_cap, (uint32_t)fnext, ok);
   int64_t edges = 0;
+  // direct hand-over: part q's lists go behind the header of block q (offsets relative to the
+  // block); else every list shares the slot's slab (offsets into it)
+  GsTargets *tg = ws.tgt;
+  const bool direct = tg->direct != 0;
+  const int64_t cap = tg->cap;
   for (int q = 0; q < P && ok; q++) {
     const uint32_t n_in = cnt[GS_CNT_IN(P, q)], n_e = cnt[GS_CNT_E(P, q)], n_out = cnt[GS_CNT_OUT(P, q)],
                    n_own = cnt[GS_CNT_OWN(P, q)], n_to = cnt[GS_CNT_TO(P, q)], n_self = cnt[GS_CNT_SELF(P, q)];
     gs_span *fl = h->field[layer][q];
-    fl[GS_F_IN_NODES] = slab_alloc(used, ws.slab_cap, n_in, ok);
-    fl[GS_F_OUT_NODES] = slab_alloc(used, ws.slab_cap, n_out, ok);
-    fl[GS_F_OWNED_OUT] = slab_alloc(used, ws.slab_cap, n_own, ok);
-    fl[GS_F_FROM_IDS] = slab_alloc(used, ws.slab_cap, n_out - n_own, ok);
-    fl[GS_F_TO_IDS] = slab_alloc(used, ws.slab_cap, n_to, ok);
-    fl[GS_F_SELF_IN] = slab_alloc(used, ws.slab_cap, n_self, ok);
-    fl[GS_F_SELF_OUT] = slab_alloc(used, ws.slab_cap, n_self, ok);
-    const gs_span ip = slab_alloc(used, ws.slab_cap, n_out + 1u, ok);
+    int64_t cur = direct ? tg->cursor[q] : used;
+    fl[GS_F_IN_NODES] = slab_alloc(cur, cap, n_in, ok);
+    fl[GS_F_OUT_NODES] = slab_alloc(cur, cap, n_out, ok);
+    fl[GS_F_OWNED_OUT] = slab_alloc(cur, cap, n_own, ok);
+    fl[GS_F_FROM_IDS] = slab_alloc(cur, cap, n_out - n_own, ok);
+    fl[GS_F_TO_IDS] = slab_alloc(cur, cap, n_to, ok);
+    fl[GS_F_SELF_IN] = slab_alloc(cur, cap, n_self, ok);
+    fl[GS_F_SELF_OUT] = slab_alloc(cur, cap, n_self, ok);
+    const gs_span ip = slab_alloc(cur, cap, n_out + 1u, ok);
     fl[GS_F_CSR_INDPTR] = ip;
-    fl[GS_F_CSR_INDICES] = slab_alloc(used, ws.slab_cap, n_e, ok);
-    if (ok) ws.slab[ip.off + n_out] = (int32_t)n_e;  // row pointer sentinel
+    fl[GS_F_CSR_INDICES] = slab_alloc(cur, cap, n_e, ok);
+    if (ok) tg->base[q][ip.off + n_out] = (int32_t)n_e;  // row pointer sentinel
+    if (direct) {
+      tg->cursor[q] = cur;
+      used += cur;  // reported only
+    } else {
+      used = cur;
+    }
     edges += n_e;
   }
   if (ok) {
-    h->slab_used = used;
+    h->slab_used = direct ? 0 : used;
     h->reserved[1] = (int32_t)fused;
     h->frontier[layer + 1] = fs;
     h->frontier_len[layer + 1] = (int32_t)fnext;
@@ -1184,7 +1206,8 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
   __shared__ uint32_t s_wc[GS_NW][GS_CS_NC];    // per-warp class totals of the tile
   __shared__ uint32_t s_base[GS_NW][GS_CS_NC];  // CTA prefix + earlier tiles + earlier warps of the tile
   __shared__ uint32_t s_run[2][GS_CS_NC];       // running class counts at the start of a tile (ping-pong)
-  __shared__ int32_t s_fo_in[GS_MAX_PARTS], s_fo_ix[GS_MAX_PARTS];
+  __shared__ int32_t *s_in[GS_MAX_PARTS];
+  __shared__ int32_t s_fo_ix[GS_MAX_PARTS];
   const int P = ws.P;
   const uint32_t C = (uint32_t)h->cand_len[layer];
   const int ntiles = (int)((C + GS_TILE - 1) / GS_TILE);
@@ -1193,8 +1216,12 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
   const int lane = lane_id(), w = warp_id();
   const size_t rs_stride = sizeof(PK);  // rowscan: one record of 4 (P <= 4) or 8 words per row
   if (threadIdx.x < P) {
-    s_fo_in[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
-    s_fo_ix[threadIdx.x] = h->field[layer][threadIdx.x][GS_F_CSR_INDICES].off;
+    s_in[threadIdx.x] = ws.tgt->base[threadIdx.x] + h->field[layer][threadIdx.x][GS_F_IN_NODES].off;
+    // csr_indices go to the slot's edge scratch first (relabel_role writes the final list):
+    // part q's edges start where the parts before it end
+    int32_t at = 0;
+    for (int q = 0; q < (int)threadIdx.x; q++) at += (h->field[layer][q][GS_F_CSR_INDICES].len + 3) & ~3;
+    s_fo_ix[threadIdx.x] = at;
   }
   int t0, t1;
   cta_tiles(ntiles, t0, t1);
@@ -1269,14 +1296,14 @@ __device__ void cand_apply_role(const GsWs &ws, int layer) {
           // that first occurrence and leaves ~m for relabel_role
           const uint32_t rk = bw[CS_IN(g)] + pkt_get<PK>(ri, g);
           const int32_t z = kind == GS_CK_FHIT ? front[ci[i]] : ci[i];  // a new node carries its id, a frontier row its index
-          st_out(ws.slab + s_fo_in[g] + rk, z);
-          ws.slab[s_fo_ix[g] + ex] = (int32_t)rk;
+          st_out(s_in[g] + rk, z);
+          ws.ixs[s_fo_ix[g] + ex] = (int32_t)rk;
           if (fl[i] & GS_CF_FFIRST) fnext[rf++] = z;
           ci[i] = (int32_t)rk;
           wrote = true;
           ri += pkt_one<PK>(g);
         } else {
-          ws.slab[s_fo_ix[g] + ex] = ~ci[i];
+          ws.ixs[s_fo_ix[g] + ex] = ~ci[i];
         }
         re += pkt_one<PK>(g);
       }
@@ -1386,6 +1413,7 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
   __shared__ uint32_t s_base[GS_IPT * GS_NW][GS_FS_NC]; // -> list places before them
   __shared__ uint32_t s_run[GS_FS_NC];
   __shared__ int32_t s_fo[GS_MAX_PARTS][GS_NUM_FIELDS];
+  __shared__ int32_t *s_tb[GS_MAX_PARTS];  // list base of every part: the slab, or its hand-over block
   if (h->status != 0) return;
   const int P = ws.P;
   const int F = h->frontier_len[layer];
@@ -1393,6 +1421,7 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
   int t0, t1;
   role_tiles(ntiles, bx, nb, t0, t1);
   if (t0 >= t1) return;
+  if (threadIdx.x < P) s_tb[threadIdx.x] = ws.tgt->base[threadIdx.x];
   const int32_t *__restrict__ front = ws.fslab + h->frontier[layer].off;
   const uint32_t *rw_ea = ws.ea + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3), *rw_rowhas = ws.rowhas + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3),
                  *rw_selfrank = ws.selfrank + (size_t)(layer & 1) * (((size_t)ws.Fcap + 3) & ~(size_t)3);  // ping-pong by layer (see rows_role)
@@ -1475,18 +1504,18 @@ __device__ void rowside_role(const GsWs &ws, int layer, int bx, int nb) {
           const uint32_t ow = bs[FS_OWN(q)] + pkt_get<PK>(rw[k], q);
           const uint4 rr = q < 4 ? r0 : r1;
           const uint32_t rsq = (q & 3) == 0 ? rr.x : (q & 3) == 1 ? rr.y : (q & 3) == 2 ? rr.z : rr.w;
-          st_out(ws.slab + s_fo[q][GS_F_OUT_NODES] + op, nd[k]);
-          st_out(ws.slab + s_fo[q][GS_F_CSR_INDPTR] + op, (int32_t)rsq);
+          st_out(s_tb[q] + s_fo[q][GS_F_OUT_NODES] + op, nd[k]);
+          st_out(s_tb[q] + s_fo[q][GS_F_CSR_INDPTR] + op, (int32_t)rsq);
           if (q == gq) {
-            st_out(ws.slab + s_fo[q][GS_F_OWNED_OUT] + ow, (int32_t)op);
+            st_out(s_tb[q] + s_fo[q][GS_F_OWNED_OUT] + ow, (int32_t)op);
             op_own = (int32_t)op;
           } else {
-            st_out(ws.slab + s_fo[q][GS_F_FROM_IDS] + (op - ow), (int32_t)op);
+            st_out(s_tb[q] + s_fo[q][GS_F_FROM_IDS] + (op - ow), (int32_t)op);
           }
         }
-        if (has[k] & ~own) st_out(ws.slab + s_fo[gq][GS_F_TO_IDS] + bs[FS_TO(gq)] + pkt_get<PK>(rt[k], gq), op_own);
-        st_out(ws.slab + s_fo[gq][GS_F_SELF_IN] + sr[k], sin[k]);
-        st_out(ws.slab + s_fo[gq][GS_F_SELF_OUT] + sr[k], op_own);
+        if (has[k] & ~own) st_out(s_tb[gq] + s_fo[gq][GS_F_TO_IDS] + bs[FS_TO(gq)] + pkt_get<PK>(rt[k], gq), op_own);
+        st_out(s_tb[gq] + s_fo[gq][GS_F_SELF_IN] + sr[k], sin[k]);
+        st_out(s_tb[gq] + s_fo[gq][GS_F_SELF_OUT] + sr[k], op_own);
       }
     }
   }
@@ -1503,23 +1532,26 @@ __device__ void relabel_role(const GsWs &ws, int layer, int bx, int nb) {
   int32_t *const cand = cand_buf(ws, layer);
   if (h->status != 0) return;
   const int P = ws.P;
+  int32_t at = 0;
   for (int q = 0; q < P; q++) {
     const gs_span sp = h->field[layer][q][GS_F_CSR_INDICES];
-    int32_t *ix = ws.slab + sp.off;
+    const int32_t *__restrict__ src = ws.ixs + at;  // k_cand_apply's scratch (same layout rule)
+    int32_t *dst = ws.tgt->base[q] + sp.off;        // the final list: slab, or the part's hand-over block
+    at += (sp.len + 3) & ~3;
     const int stride = nb * GS_TPB;
     for (int e0 = bx * GS_TPB + threadIdx.x; e0 < sp.len; e0 += GS_IPT * stride) {
       int32_t v[GS_IPT], r[GS_IPT];
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        v[k] = e < sp.len ? ix[e] : 0;  // >= 0: already final (written by the first occurrence)
+        v[k] = e < sp.len ? __ldcs(src + e) : 0;  // >= 0: the rank itself (a first occurrence)
       }
 #pragma unroll
-      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(cand + (uint32_t)~v[k]) : 0;
+      for (int k = 0; k < GS_IPT; k++) r[k] = v[k] < 0 ? __ldcg(cand + (uint32_t)~v[k]) : v[k];
 #pragma unroll
       for (int k = 0; k < GS_IPT; k++) {
         const int e = e0 + k * stride;
-        if (v[k] < 0) st_out(ix + e, r[k]);
+        if (e < sp.len) st_out(dst + e, r[k]);  // every entry, whole sectors
       }
     }
   }
@@ -1554,7 +1586,7 @@ __device__ void gather_role(const GsWs &ws, int bx, int nb) {
   if ((int64_t)R > ws.feat_cap_rows) return;  // k_tail's last CTA reports the overflow
   const FeatSrc fs{ws.feat, ws.feat_slot, ws.feat_host};
   const int dim = ws.feat_dim, div = ws.feat_div;
-  const int32_t *slab = ws.slab;
+  const int32_t *slab = ws.slab;  // the fused gather is not combined with the direct hand-over
   auto src_of_row = [&](int64_t r) -> const float * {
     int q = 0;
     while (q + 1 < P && r >= s_start[q + 1]) q++;
@@ -1678,6 +1710,36 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_tail(const GsWs *__res
     *ws.state = nx;
   }
   __syncthreads();
+  if (ws.tgt->direct) {
+    // direct hand-over: the header of every part's block (layout of gs_slicer_pack_parts), last,
+    // so that a block whose header is in place is complete
+    const int status = h->status ? h->status : h->late_status;
+    const int ns = L * GS_NUM_FIELDS;
+    for (int q = 0; q < P; q++) {
+      int32_t *blk = ws.tgt->base[q];
+      for (int k = threadIdx.x; k < GS_PART_HEADER_WORDS; k += GS_TPB) {
+        int32_t v = 0;
+        if (k == 0) v = (int32_t)GS_PART_MAGIC;
+        else if (k == 1) v = status;
+        else if (k == 2) v = q;
+        else if (k == 3) v = L;
+        else if (k == 4) v = P;
+        else if (k == 5) v = h->n_seeds;
+        else if (k == 6) v = (int32_t)(uint32_t)(h->batch_index & 0xFFFFFFFFull);
+        else if (k == 7) v = (int32_t)(uint32_t)(h->batch_index >> 32);
+        else if (k == 8) v = status == 0 ? (int32_t)ws.tgt->cursor[q] : GS_PART_HEADER_WORDS;
+        else if (k == 9) {
+          if (status == 0)
+            for (int l = 0; l < L; l++) v += h->field[l][q][GS_F_CSR_INDICES].len;
+        } else if (k >= 16 && k < 16 + 2 * ns && status == 0) {
+          const int j = (k - 16) >> 1;
+          const gs_span sp = h->field[j / GS_NUM_FIELDS][q][j % GS_NUM_FIELDS];
+          v = ((k - 16) & 1) ? sp.len : sp.off;
+        }
+        blk[k] = v;
+      }
+    }
+  }
   {
     const int nw = (int)(sizeof(gs_sample_header) / 4);
     const int32_t *src = (const int32_t *)h;

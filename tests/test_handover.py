@@ -161,6 +161,66 @@ def test_pack_parts_matches_the_sample_and_the_oracle(P, fan, batch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("P,fan,batch", [(4, [15, 10, 5], 512), (8, [10, 10], 256), (3, [-1, 5], 128), (1, [5], 64)])
+def test_direct_hand_over_blocks_match_the_sample_and_the_oracle(P, fan, batch):
+    """gs_slicer_submit_direct on one GPU (all P blocks local): the blocks the slicing kernels
+    write themselves hold exactly the lists of an ordinary sample and of the oracle, in the
+    block format of gs_slicer_pack_parts; a block that is too small is an overflow status."""
+    import ctypes as C
+    import torch
+    from cslicer import _native as N
+    from cslicer.engine import Graph, Slicer
+    from cslicer.handover import HEADER_WORDS, PartBlock
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=4)
+    n = ip.size - 1
+    g = Graph(ip, ix)
+    sl = Slicer(g, fan, P, max_batch=batch, num_slots=2, num_streams=2, seed=31, host_output=False)
+    orc = O.OracleSlicer(ip, ix, fan, P, O.RNG_PHILOX, seed=31)
+    rng = np.random.default_rng(6)
+    words = 4 * (sl.slab_capacity_words() // 4 + HEADER_WORDS)
+    for bi in (0, 1, (3 << 32) | 9):
+        seeds = rng.permutation(n)[:batch]
+        dst = torch.full((P, words), -7, dtype=torch.int32, device="cuda:0")
+        torch.cuda.synchronize()
+        arr = (C.c_void_p * P)(*[dst[q].data_ptr() for q in range(P)])
+        slot = sl.submit_direct(seeds, bi, arr, words)
+        h = sl.wait_header(slot)
+        assert h.status == 0
+        sl._release(slot)
+        host = dst.cpu().numpy()
+        v = sl.slice(seeds, bi)  # the ordinary path on the same slicer, after a direct sample
+        want = orc.slice(seeds, bi)
+        for q in range(P):
+            b = PartBlock(host[q])
+            assert (b.part, b.num_layers, b.num_parts, b.n_seeds, b.batch_index) == (q, len(fan), P, batch, bi)
+            for l in range(len(fan)):
+                for name in N.FIELDS:
+                    a = b.field(l, name)
+                    assert np.array_equal(a, v.tensor(l, q, name).cpu().numpy()), (q, l, name)
+                    assert np.array_equal(a, want["layers"][l][q][name]), (q, l, name)
+            assert b.edges == sum(v.field_len(l, q, "csr_indices") for l in range(len(fan)))
+            assert (host[q][b.words:] == -7).all(), "wrote past the words in use"
+        v.release()
+    # too small a block: overflow status in the sample header and in the block headers, nothing past the end
+    small_w = HEADER_WORDS + 8
+    small = torch.full((P, small_w + 64), -7, dtype=torch.int32, device="cuda:0")
+    torch.cuda.synchronize()
+    arr = (C.c_void_p * P)(*[small[q].data_ptr() for q in range(P)])
+    slot = sl.submit_direct(seeds, 5, arr, small_w)
+    with pytest.raises(N.SlicerError) as e:
+        sl.wait_header(slot)
+    assert e.value.code == N.ERR_OVERFLOW
+    sl._release(slot)
+    sh = small.cpu().numpy()
+    assert (sh[:, small_w:] == -7).all() and (sh[:, 1] == N.ERR_OVERFLOW).all()
+    v = sl.slice(seeds, 5)  # the slicer recovers
+    v.release()
+    sl.close()
+    g.close()
+
+
+@pytest.mark.gpu
 def test_hand_over_between_real_ranks_nccl():
     import torch
     if torch.cuda.device_count() < 2:
