@@ -623,6 +623,7 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
                        "d2h_bytes_per_step": int(max(8, rounds // 4) * world * need * 4),
                        "what": "host seeds in; every received part block copied to pinned host memory (one DMA "
                                "per block, size from the running estimate, header-checked) inside the timed region"},
+               "barrier": "flag words stored into the peers' memory (gs_flags_post), no collective per round",
                "ranks": world, "parts": world, "rounds_in_flight": depth,
                "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
                "nvlink_bytes_sent_per_rank_per_round": int(sent),
@@ -631,12 +632,12 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
                           "e2e": rate("direct_e2e", max(8, rounds // 4)),
                           "exchange": "gs_slicer_submit_direct: the slicing kernels write every list of part g "
                                       "into rank g's receive buffer as they produce it (no slab write, no packing "
-                                      "pass; each list crosses NVLink once), 4-byte all-reduce per round as barrier"},
+                                      "pass; each list crosses NVLink once)"},
                "peer_stores": {"value": rate("peer_stores", rounds), "parity": results["peer_stores"][1],
                                "e2e": rate("peer_stores_e2e", max(8, rounds // 4))},
                "exchange": "gs_slicer_scatter_parts: the packing kernel writes every block straight into its "
                            "owner rank's receive buffer (CUDA IPC over NVLink; cp.async.bulk pieces from 4 parts "
-                           "up, 16-byte stores below), one 4-byte all-reduce per round as the barrier; "
+                           "up, 16-byte stores below); "
                            "overlapped with slicing",
                "same_with_nccl_all_to_all": {
                    "value": rate("nccl_all_to_all", rounds), "parity": results["nccl_all_to_all"][1],

@@ -260,6 +260,17 @@ int gs_slicer_submit_direct(gs_slicer *s, const int64_t *seeds_host, int32_t n, 
                             int32_t *const *dst_blocks, int64_t block_words, void *after_event,
                             int32_t *slot_out);
 
+/* The hand-over's barrier without a collective (one warp on `stream`): first stores
+ * signal_value into the n_signal words signal_words[i] (device pointers, local or peer
+ * memory mapped with gs_ipc_open) -- ordered, system-wide, after everything the stream
+ * did before -- then waits until every one of the n_wait LOCAL words wait_words[i] is
+ * >= wait_value (wrap-around compare).  A wait that lasts longer than timeout_ms (0 =
+ * 5000) sets *status_mapped (a pinned, mapped host word) to 1 and ends: no kernel hangs
+ * on a peer that died.  n_signal, n_wait <= GS_MAX_PARTS.  No counterpart in the reference. */
+int gs_flags_post(int device, uint32_t *const *signal_words, int32_t n_signal, uint32_t signal_value,
+                  const uint32_t *const *wait_words, int32_t n_wait, uint32_t wait_value,
+                  uint32_t timeout_ms, int32_t *status_mapped, void *stream);
+
 /* Device buffers another process can map (cudaIpcGetMemHandle / OpenMemHandle):
  * handle = 64 bytes.  gs_ipc_open enables peer access to the owner's GPU. */
 int gs_ipc_alloc(int device, int64_t bytes, void **dev_ptr, void *handle_out);

@@ -211,8 +211,14 @@ class PeerScatter:
     <= X - 1 - slack - depth = X - nbuf, the round this buffer held.  With slack > 0
     that barrier is several rounds old, so packs do not queue up behind barriers."""
 
-    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3):
+    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3, barrier="flags", timeout_ms=5000):
+        """barrier="flags" (default): arrival and release travel as flag words stored into the peers'
+        memory (gs_flags_post: one warp per round, no rank waits for a rank it does not need);
+        "allreduce": a 4-byte library all-reduce per round (lock-step; kept for A/B)."""
         import torch
+        if barrier not in ("flags", "allreduce"):
+            raise ValueError("barrier must be 'flags' or 'allreduce'")
+        self.barrier, self.timeout_ms = barrier, int(timeout_ms)
         self.slicer, self.dist, self.group = slicer, dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         if slicer.num_parts != self.world:
@@ -224,7 +230,11 @@ class PeerScatter:
         dev = torch.device("cuda", self.device)
         self.ring = RingSchedule(depth, slack)
         self.depth, self.slack, self.nbuf = self.ring.depth, self.ring.slack, self.ring.nbuf
-        nbytes = 4 * self.nbuf * self.world * self.block_words
+        # arena: the ring of blocks, then the flag words: arrived[nbuf][world] (written by the source
+        # ranks), released[world] (written by the owner ranks)
+        self._ring_words = self.nbuf * self.world * self.block_words
+        self._flag_words = _pad4(self.nbuf * self.world + self.world)
+        nbytes = 4 * (self._ring_words + self._flag_words)
         base, handle = C.c_void_p(), (C.c_char * 64)()
         rc = N.lib().gs_ipc_alloc(self.device, nbytes, C.byref(base), handle)
         self._base = base.value if rc == N.OK else None
@@ -268,6 +278,21 @@ class PeerScatter:
                 arr[q] = self._peer[q] + 4 * (k * self.world + self.rank) * self.block_words
             self._dst.append(arr)
         self.recv = torch.as_tensor(_DevWords(self._base, (self.nbuf, self.world, self.block_words)), device=dev)
+        flags = torch.as_tensor(_DevWords(self._base + 4 * self._ring_words, (self._flag_words,)), device=dev)
+        flags.zero_()
+        W, nb = self.world, self.nbuf
+        arrived = lambda q, k, src: self._peer[q] + 4 * (self._ring_words + k * W + src)
+        released = lambda q, owner: self._peer[q] + 4 * (self._ring_words + nb * W + owner)
+        # round in buffer k: tell every owner q "the blocks of source `rank` are complete"; watch my own row
+        self._sig_arrived = [(C.c_void_p * W)(*[arrived(q, k, self.rank) for q in range(W)]) for k in range(nb)]
+        self._wait_arrived = [(C.c_void_p * W)(*[arrived(self.rank, k, src) for src in range(W)]) for k in range(nb)]
+        # release: tell every source s "owner `rank` is done with your block"; watch what the owners told me
+        self._sig_released = (C.c_void_p * W)(*[released(s, self.rank) for s in range(W)])
+        self._wait_released = (C.c_void_p * W)(*[released(self.rank, q) for q in range(W)])
+        self._status = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._rel_stream = torch.cuda.Stream(device=dev)
+        self._rel_done = [torch.cuda.Event() for _ in range(nb)]
+        self._next_release = 0
         self.stream = torch.cuda.Stream(device=dev)
         self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -275,20 +300,46 @@ class PeerScatter:
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # every arena is mapped everywhere before the first store
 
-    def post(self, slot):
+    def _flags(self, sig, n_sig, sig_value, wait, n_wait, wait_value, stream):
+        N.check(N.lib().gs_flags_post(self.device, sig, n_sig, sig_value & 0xFFFFFFFF, wait, n_wait,
+                                      wait_value & 0xFFFFFFFF, self.timeout_ms,
+                                      C.c_void_p(self._status.data_ptr()), C.c_void_p(stream)))
+
+    def _buffer_free_event(self, r, k, after):
+        """-> handle of the event after which buffer k may be written for round r (0: at once)."""
+        if self.barrier == "allreduce":  # the barrier behind which every owner released round r - nbuf
+            return self.done[after % self.nbuf].cuda_event if after is not None else 0
+        if r < self.nbuf:
+            return 0
+        # every owner has released round r - nbuf (it stored r - nbuf + 1 into my `released` row)
+        self._flags(None, 0, 0, self._wait_released, self.world, r - self.nbuf + 1, self._rel_stream.cuda_stream)
+        self._rel_done[k].record(self._rel_stream)
+        return self._rel_done[k].cuda_event
+
+    def _round_barrier(self, r, k):
+        """On self.stream, behind the writes of this rank's blocks: tell the owners, wait for all sources."""
         torch = self._torch
-        r, k, after = self.ring.next_post()  # after: the barrier behind which every owner released round r - nbuf
-        ev = self.done[after % self.nbuf].cuda_event if after is not None else 0
+        with torch.cuda.stream(self.stream):
+            if self.barrier == "allreduce":
+                self.dist.all_reduce(self._flag, group=self.group)  # 4 bytes; the payload went by stores
+            else:
+                self._flags(self._sig_arrived[k], self.world, r + 1, self._wait_arrived[k], self.world, r + 1,
+                            self.stream.cuda_stream)
+            self.done[k].record(self.stream)
+
+    def post(self, slot):
+        r, k, after = self.ring.next_post()
+        ev = self._buffer_free_event(r, k, after)
         N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
                                                 C.c_void_p(ev), C.c_void_p(self.stream.cuda_stream)))
-        with torch.cuda.stream(self.stream):
-            self.dist.all_reduce(self._flag, group=self.group)  # barrier: 4 bytes; the payload went by stores
-            self.done[k].record(self.stream)
+        self._round_barrier(r, k)
         return r
 
     def collect(self, ticket, parse=True):
         k = ticket % self.nbuf
         self.done[k].synchronize()
+        if int(self._status[0]) != 0:
+            raise RuntimeError(f"hand-over: a peer's flag did not arrive within {self.timeout_ms} ms (round {ticket})")
         if not parse:
             return self.recv[k]
         hdr = self.recv[k][:, :HEADER_WORDS].cpu().numpy()
@@ -298,9 +349,17 @@ class PeerScatter:
         """The consumer is done with round `ticket` (work queued so far on torch's
         current stream included): its buffer may be overwritten."""
         torch = self._torch
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(self.recv.device))
-        self.stream.wait_event(ev)  # this rank's next barrier carries the release to the writers
+        cur = torch.cuda.current_stream(self.recv.device)
+        if self.barrier == "allreduce":
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self.stream.wait_event(ev)  # this rank's next barrier carries the release to the writers
+        else:
+            if ticket != self._next_release:
+                raise RuntimeError(f"rounds are released in order with barrier='flags' (expected {self._next_release})")
+            self._next_release += 1
+            # behind the consumer's work: store ticket + 1 into every source rank's `released` row
+            self._flags(self._sig_released, self.world, ticket + 1, None, 0, 0, cur.cuda_stream)
         self.ring.release(ticket)
 
     def nvlink_bytes_per_round(self):
@@ -334,29 +393,26 @@ class DirectScatter(PeerScatter):
     rank's barrier X - 1 - slack, so that barrier must have been posted already: at most
     `slack` rounds may be submitted ahead of the last post (checked)."""
 
-    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3):
-        super().__init__(slicer, dist, block_words, depth=depth, group=group, slack=slack)
+    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3, **kw):
+        super().__init__(slicer, dist, block_words, depth=depth, group=group, slack=slack, **kw)
         self._pending = {}
         self._posted = 0
 
     def submit(self, seeds, batch_index=0):
-        if self.ring.posted - self._posted >= max(1, self.slack):
+        if self.barrier == "allreduce" and self.ring.posted - self._posted >= max(1, self.slack):
             raise RuntimeError(f"{self.ring.posted - self._posted} rounds submitted and not posted: "
                                f"at most slack={self.slack} may be in flight before post()")
         r, k, after = self.ring.next_post()
-        ev = self.done[after % self.nbuf].cuda_event if after is not None else 0
+        ev = self._buffer_free_event(r, k, after)
         slot = self.slicer.submit_direct(seeds, batch_index, self._dst[k], self.block_words, ev)
         self._pending[slot] = (r, k)
         return slot
 
     def post(self, slot):
-        torch = self._torch
         r, k = self._pending.pop(slot)
         N.check(N.lib().gs_slicer_scatter_parts(self.slicer._h, int(slot), self._dst[k], self.block_words,
                                                 None, C.c_void_p(self.stream.cuda_stream)))
-        with torch.cuda.stream(self.stream):
-            self.dist.all_reduce(self._flag, group=self.group)  # barrier: every rank's blocks of round r have landed
-            self.done[k].record(self.stream)
+        self._round_barrier(r, k)
         self._posted += 1
         return r
 
