@@ -565,7 +565,7 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
     -> dict for the bench line (rank 0), None elsewhere."""
     from cslicer import _native as N
     from cslicer.engine import Slicer
-    from cslicer.handover import HEADER_WORDS, DirectScatter, PartScatter, PeerScatter
+    from cslicer.handover import HEADER_WORDS, DirectScatter, PartScatter, PeerScatter, StagedScatter
     steps = steps or args.steps
     rounds = rounds or max(16, args.mb_per_step // 4)
     kw = dict(num_parts=world, max_batch=BATCH, num_slots=args.slots, num_streams=args.streams, seed=7,
@@ -586,9 +586,10 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
     depth = args.slots
     results = {}
     sent = 4 * block_words * (world - 1)
-    for kind in ("direct", "direct_e2e", "peer_stores", "peer_stores_e2e", "nccl_all_to_all"):
+    for kind in ("staged", "staged_e2e", "direct", "direct_e2e", "peer_stores", "peer_stores_e2e", "nccl_all_to_all"):
         try:  # constructor failures are collective (raised on every rank): the other arm still runs
-            cls = PartScatter if kind == "nccl_all_to_all" else DirectScatter if kind.startswith("direct") else PeerScatter
+            cls = PartScatter if kind == "nccl_all_to_all" else DirectScatter if kind.startswith("direct") else \
+                StagedScatter if kind.startswith("staged") else PeerScatter
             ps = cls(sl, dist, block_words, depth=depth)
         except RuntimeError as e:
             log(f"[bench] hand-over arm {kind} unavailable: {e}")
@@ -606,8 +607,8 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
             ms = results[kind][0]
             return None if ms != ms else round(steps * r * world / (ms * 1e-3), 2)
         # headline: the faster of the two exchanges that need no library collective on the payload
-        d_ms, p_ms = results["direct"][0], results["peer_stores"][0]
-        head = "direct" if d_ms == d_ms and not (p_ms == p_ms and p_ms < d_ms) else "peer_stores"
+        cands = [(results[kd][0], kd) for kd in ("staged", "direct", "peer_stores") if results[kd][0] == results[kd][0]]
+        head = min(cands)[1] if cands else "peer_stores"
         ms = results[head][0]
         out = {"value": rate(head, rounds),
                "unit": "minibatches/s (whole job; rank g ends up holding part g of every minibatch)",
@@ -628,6 +629,11 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
                "block_bytes": block_words * 4, "payload_bytes_per_minibatch": slab_words * 4,
                "nvlink_bytes_sent_per_rank_per_round": int(sent),
                "nvlink_gbs_per_rank": None if ms != ms else round(sent * steps * rounds / (ms * 1e-3) / 1e9, 2),
+               "staged": {"value": rate("staged", rounds), "parity": results["staged"][1],
+                          "e2e": rate("staged_e2e", max(8, rounds // 4)),
+                          "exchange": "gs_slicer_submit_direct into LOCAL staging blocks (each part's lists written "
+                                      "once, contiguously) + gs_slicer_push_parts: one copy-engine transfer per "
+                                      "part to its owner; no SM store crosses NVLink"},
                "direct": {"value": rate("direct", rounds), "parity": results["direct"][1],
                           "e2e": rate("direct_e2e", max(8, rounds // 4)),
                           "exchange": "gs_slicer_submit_direct: the slicing kernels write every list of part g "
@@ -677,6 +683,40 @@ def _hand_over_run(ps, sl, batches, depth, steps, rounds, torch, dist, local, ra
         inflight, last, last_host = [], None, None
         e0.record()
         pend, G = [], max(1, sl.group_size)
+        if getattr(ps, "deferred", False):
+            # post() needs the finished sample: submits run `ahead` rounds in front of it
+            ahead, submitted = max(1, depth // 2), []
+
+            def consume(slot, tk, keep=False):
+                nonlocal last, last_host
+                buf = ps.collect(tk, parse=False)
+                if mirror_words:
+                    hb = mirror(buf)
+                    cstream.synchronize()
+                    if keep:
+                        last_host = hb
+                if keep:
+                    last = buf.clone()
+                release(tk)
+
+            for i in range(k):
+                if len(submitted) == ahead:
+                    slot = submitted.pop(0)
+                    inflight.append((slot, ps.post(slot)))
+                    sl.release(slot)
+                if len(inflight) == depth - ahead:
+                    consume(*inflight.pop(0))
+                bi, seeds = batches[i % len(batches)]
+                submitted.append(ps.submit(seeds, bi))
+            for slot in submitted:
+                inflight.append((slot, ps.post(slot)))
+                sl.release(slot)
+            for slot, tk in inflight:
+                consume(slot, tk, keep=True)
+            e1.record(ps.stream)
+            e1.synchronize()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1), last, last_host
         for i in range(k):
             if len(inflight) + len(pend) == depth:
                 slot, tk = inflight.pop(0)

@@ -93,7 +93,8 @@ typedef struct {
   uint64_t draw_base[GS_MAX_LAYERS];
   int32_t late_status;   /* device-internal: error raised inside a tiled kernel */
   int32_t feature_rows;  /* rows written by the fused feature gather (0 without features) */
-  int32_t feature_part_off[GS_MAX_PARTS + 1]; /* row offset of each part's block in the feature slab */
+  int32_t feature_part_off[GS_MAX_PARTS + 1]; /* row offset of each part's block in the feature slab; a direct
+                                               * submit (no fused gather): words in use of part q's block */
   int32_t reserved[3];   /* [0] host mirror wanted, [1] frontier slab elements in use, [2] 1: `frontier`
                           * spans index the frontier slab (gs_slicer_frontiers), 0: the sample slab */
 } gs_sample_header;
@@ -259,6 +260,16 @@ int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_bloc
 int gs_slicer_submit_direct(gs_slicer *s, const int64_t *seeds_host, int32_t n, uint64_t batch_index,
                             int32_t *const *dst_blocks, int64_t block_words, void *after_event,
                             int32_t *slot_out);
+
+/* Staged hand-over: for a slot submitted with gs_slicer_submit_direct into LOCAL blocks
+ * (a staging area: the sample's kernels then write each part's lists once, contiguously,
+ * behind its block header) and waited for: copies block q -- only its words in use, which
+ * the sample left in gs_sample_header.feature_part_off[q] -- to dst_blocks[q] (peer memory)
+ * with the COPY ENGINES, one stream per part; the copies first wait for after_event (may be
+ * NULL), consumer_stream waits for all of them.  No SM is involved in the exchange.  A block
+ * whose destination equals its staging address is not copied. */
+int gs_slicer_push_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks, void *after_event,
+                         void *consumer_stream);
 
 /* The hand-over's barrier without a collective (one warp on `stream`): first stores
  * signal_value into the n_signal words signal_words[i] (device pointers, local or peer

@@ -30,7 +30,7 @@ SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_cre
            "gs_unique_first_noalloc", "gs_epart_create", "gs_epart_destroy", "gs_epart_run", "gs_epart_get",
            "gs_features_create",
            "gs_features_destroy", "gs_features_gather", "gs_features_create_cached", "gs_features_info", "gs_slicer_feature_slab",
-           "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts", "gs_slicer_scatter_parts", "gs_slicer_submit_direct", "gs_flags_post",
+           "gs_slicer_frontiers", "gs_slicer_read_frontier", "gs_slicer_pack_parts", "gs_slicer_scatter_parts", "gs_slicer_submit_direct", "gs_slicer_push_parts", "gs_flags_post",
            "gs_ipc_alloc", "gs_ipc_open", "gs_ipc_close", "gs_ipc_free",
            # partitioned mode (one rank per GPU)
            "gs_pconfig_default", "gs_pslicer_create", "gs_pslicer_destroy", "gs_pslicer_ipc_handle",
@@ -139,6 +139,7 @@ def lib():
     L.gs_bench_sector_probe.argtypes = [C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_double)]
     L.gs_slicer_submit_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64, C.c_void_p, C.c_int64,
                                           C.c_void_p, C.POINTER(C.c_int32)]
+    L.gs_slicer_push_parts.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gs_flags_post.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_uint32, C.c_void_p, C.c_int32, C.c_uint32,
                                 C.c_uint32, C.c_void_p, C.c_void_p]
     L.gs_epart_create.argtypes = [C.c_int, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64,

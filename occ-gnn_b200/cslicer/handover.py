@@ -416,3 +416,47 @@ class DirectScatter(PeerScatter):
         self._posted += 1
         return r
 
+
+class StagedScatter(PeerScatter):
+    """The hand-over through the copy engines: `submit` lets the slicing kernels write every part's
+    lists ONCE, contiguously, into a LOCAL staging block (gs_slicer_submit_direct with local
+    targets -- no slab write, no packing pass), and `post` -- called once the sample is complete,
+    it waits for its header to learn the sizes -- sends block g to rank g with one copy-engine
+    transfer per part (gs_slicer_push_parts): no SM stores cross NVLink, and the link runs at its
+    bulk rate (measured on 8 B200: 307 GB/s sent per rank by copy engines against < 190 GB/s
+    for stores issued by the slicing or packing kernels).  Barrier as in PeerScatter (flags).
+
+        slot = ss.submit(seeds, b)        # several rounds ahead
+        k = ss.post(slot)                 # blocks the host until THIS sample is sliced
+        slicer._release(slot); blocks = ss.collect(k); ...; ss.release(k)"""
+
+    deferred = True  # post() needs the finished sample: keep a few submits ahead of it
+
+    def __init__(self, slicer, dist, block_words, depth=2, group=None, slack=3, **kw):
+        super().__init__(slicer, dist, block_words, depth=depth, group=group, slack=slack, **kw)
+        torch = self._torch
+        dev = torch.device("cuda", self.device)
+        self._stage = torch.empty((self.nbuf, self.world, self.block_words), dtype=torch.int32, device=dev)
+        self._stage_dst = [(C.c_void_p * self.world)(*[self._stage[k][q].data_ptr() for q in range(self.world)])
+                           for k in range(self.nbuf)]
+        self._sent = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self._pending = {}
+
+    def submit(self, seeds, batch_index=0):
+        r, k, after = self.ring.next_post()
+        # staging block k was last read by the transfers of round r - nbuf
+        ev = self._sent[k].cuda_event if r >= self.nbuf else 0
+        slot = self.slicer.submit_direct(seeds, batch_index, self._stage_dst[k], self.block_words, ev)
+        self._pending[slot] = (r, k, after)
+        return slot
+
+    def post(self, slot):
+        r, k, after = self._pending.pop(slot)
+        self.slicer.wait_header(slot)  # raises on a failed sample; the header now holds the words in use
+        ev = self._buffer_free_event(r, k, after)
+        N.check(N.lib().gs_slicer_push_parts(self.slicer._h, int(slot), self._dst[k], C.c_void_p(ev),
+                                             C.c_void_p(self.stream.cuda_stream)))
+        self._sent[k].record(self.stream)  # behind every transfer of the round
+        self._round_barrier(r, k)
+        return r
+

@@ -132,6 +132,8 @@ struct gs_slicer {
   int64_t mirror_est = 0;              // running estimate of slab_used (int32 elements) + margin
   std::vector<Slot> slots;
   std::vector<Group> groups;
+  cudaStream_t push_stream[GS_MAX_PARTS] = {nullptr};  // gs_slicer_push_parts: one copy-engine stream per part
+  cudaEvent_t push_ev[GS_MAX_PARTS] = {nullptr};
   int cur_group = -1;                  // group being filled by gs_slicer_submit (-1: none)
   int next_group = 0;
   int64_t slot_bytes = 0;
@@ -414,6 +416,10 @@ int gs_slicer_destroy(gs_slicer *s) {
   }
   for (cudaStream_t st : s->streams) cudaStreamDestroy(st);
   if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+  for (int q = 0; q < GS_MAX_PARTS; q++) {
+    if (s->push_stream[q]) cudaStreamDestroy(s->push_stream[q]);
+    if (s->push_ev[q]) cudaEventDestroy(s->push_ev[q]);
+  }
   cudaFree(s->owner);
   cudaFree(s->draws);
   cudaFree(s->draw_cursor);
@@ -910,6 +916,36 @@ int gs_slicer_scatter_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_bloc
     dst.blk[g] = dst_blocks[g];
   }
   return scatter_parts(s, slot, dst, block_words, after_event, consumer_stream);
+}
+
+int gs_slicer_push_parts(gs_slicer *s, int32_t slot, int32_t *const *dst_blocks, void *after_event,
+                         void *consumer_stream) {
+  if (!s || slot < 0 || slot >= (int)s->slots.size() || !dst_blocks) return fail(GS_ERR_INVALID, "push_parts: bad argument");
+  Slot &sl = s->slots[slot];
+  if (!sl.direct || sl.state != SLOT_DONE)
+    return fail(GS_ERR_STATE, "push_parts: slot %d must hold a sample submitted with gs_slicer_submit_direct and waited for", slot);
+  const GsRange trace("gs_slicer_push_parts");
+  CU(cudaSetDevice(s->g->device));
+  const int P = s->cfg.num_parts;
+  const int st0 = sl.hdr_host->status ? sl.hdr_host->status : sl.hdr_host->late_status;
+  for (int q = 0; q < P; q++) {
+    if (!dst_blocks[q]) return fail(GS_ERR_INVALID, "push_parts: dst_blocks[%d] is NULL", q);
+    if (!s->push_stream[q]) {
+      CU(cudaStreamCreateWithFlags(&s->push_stream[q], cudaStreamNonBlocking));
+      CU(cudaEventCreateWithFlags(&s->push_ev[q], cudaEventDisableTiming));
+    }
+    // words of block q in use: left in the header by the sample's last launch (direct mode)
+    const int64_t words = st0 == 0 ? (int64_t)sl.hdr_host->feature_part_off[q] : (int64_t)GS_PART_HEADER_WORDS;
+    if (words < GS_PART_HEADER_WORDS || words > sl.input->block_words)
+      return fail(GS_ERR_STATE, "push_parts: block %d reports %lld words in use", q, (long long)words);
+    cudaStream_t st = s->push_stream[q];
+    if (after_event) CU(cudaStreamWaitEvent(st, (cudaEvent_t)after_event, 0));
+    if (dst_blocks[q] != sl.input->part_dst[q])
+      CU(cudaMemcpyAsync(dst_blocks[q], sl.input->part_dst[q], (size_t)words * sizeof(int32_t), cudaMemcpyDefault, st));
+    CU(cudaEventRecord(s->push_ev[q], st));
+    CU(cudaStreamWaitEvent((cudaStream_t)consumer_stream, s->push_ev[q], 0));
+  }
+  return GS_OK;
 }
 
 int gs_ipc_alloc(int device, int64_t bytes, void **dev_ptr, void *handle_out) {

@@ -1715,6 +1715,9 @@ __global__ void __launch_bounds__(GS_TPB, GS_MINB_CAND) k_tail(const GsWs *__res
     // so that a block whose header is in place is complete
     const int status = h->status ? h->status : h->late_status;
     const int ns = L * GS_NUM_FIELDS;
+    // words in use of every block, for the host (gs_slicer_push_parts sizes its copies with them)
+    if (threadIdx.x < P) h->feature_part_off[threadIdx.x] = (int32_t)ws.tgt->cursor[threadIdx.x];
+    __syncthreads();
     for (int q = 0; q < P; q++) {
       int32_t *blk = ws.tgt->base[q];
       for (int k = threadIdx.x; k < GS_PART_HEADER_WORDS; k += GS_TPB) {

@@ -33,12 +33,15 @@ def main():
     perm = np.random.default_rng(8).permutation(n)
     batches = [perm[(i * batch) % (n - batch):][:batch] for i in range(rounds * world)]
     words = sl.slab_capacity_words() // world + HEADER_WORDS
-    for kind in ("nccl all-to-all", "peer stores", "peer stores, bulk-copy engine", "direct"):
+    for kind in ("nccl all-to-all", "peer stores", "peer stores, bulk-copy engine", "direct", "staged"):
         # 2 ranks would use plain stores: force the cp.async.bulk path over NVLink as well
         os.environ["GSPLIT_PACK_TMA"] = "1" if kind.endswith("engine") else "0"
         if kind == "direct":  # the slicing kernels write the owners' blocks themselves
             from cslicer.handover import DirectScatter
             ps = DirectScatter(sl, dist, block_words=words, depth=2)
+        elif kind == "staged":  # ... local staging blocks, sent by the copy engines
+            from cslicer.handover import StagedScatter
+            ps = StagedScatter(sl, dist, block_words=words, depth=2)
         elif kind.startswith("peer stores"):
             from cslicer.handover import PeerScatter
             ps = PeerScatter(sl, dist, block_words=words, depth=2)
@@ -47,16 +50,16 @@ def main():
         tickets = []
         for k in range(rounds):                      # two rounds in flight
             b = k * world + rank
-            slot = ps.submit(batches[b], b) if kind == "direct" else sl.submit(batches[b], b)
+            slot = ps.submit(batches[b], b) if kind in ("direct", "staged") else sl.submit(batches[b], b)
             tickets.append(ps.post(slot))
             sl.release(slot)
             if k >= 1:
                 _check(ps, tickets[k - 1], k - 1, world, rank, orc, batches, fan, N)
         _check(ps, tickets[-1], rounds - 1, world, rank, orc, batches, fan, N)
-        if kind.startswith("peer stores") or kind == "direct":
+        if kind.startswith("peer stores") or kind in ("direct", "staged"):
             try:                                     # discipline: an un-released round blocks the buffer ring
                 for k in range(4):
-                    slot = ps.submit(batches[0], 0) if kind == "direct" else sl.submit(batches[0], 0)
+                    slot = ps.submit(batches[0], 0) if kind in ("direct", "staged") else sl.submit(batches[0], 0)
                     ps.post(slot)
                     sl.release(slot)
                 raise AssertionError("post did not refuse to overwrite an un-released round")

@@ -58,10 +58,23 @@ def post_nobarrier(ps, slot):
     return r
 
 
-for name, cls_kw, local_only in (("A direct, flag barrier", dict(barrier="flags"), False),
-                                 ("B direct, all-reduce barrier", dict(barrier="allreduce"), False),
-                                 ("C direct, flags, LOCAL blocks", dict(barrier="flags"), True)):
-    ps = DirectScatter(sl, dist, words, depth=depth, **cls_kw)
+class NoBarrier(DirectScatter):  # timing only: nothing tells a rank that a round has arrived
+    def _round_barrier(self, r, k):
+        with torch.cuda.stream(self.stream):
+            self.done[k].record(self.stream)
+
+    def _buffer_free_event(self, r, k, after):
+        return 0
+
+    def release(self, ticket):
+        self.ring.release(ticket)
+
+
+for name, cls, cls_kw, local_only in (("A direct, flag barrier", DirectScatter, dict(barrier="flags"), False),
+                                      ("C direct, flags, LOCAL blocks", DirectScatter, dict(barrier="flags"), True),
+                                      ("D direct, NO barrier", NoBarrier, {}, False),
+                                      ("E LOCAL blocks, NO barrier", NoBarrier, {}, True)):
+    ps = cls(sl, dist, words, depth=depth, **cls_kw)
     if local_only:
         for k in range(ps.nbuf):
             for q in range(world):
