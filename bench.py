@@ -321,11 +321,12 @@ def sector_model(view, ip, fanouts):
     return view.algorithmic_bytes(owner_bytes=0, w=4) + extra, gathers
 
 
-# One launch of k_expand, layer 2 (the dominant kernel), default workload: 85.97 MB read +
-# 2.70 MB written to DRAM (cold L2; the 12 MB candidate stream it writes stays in L2) against
-# 35.9 MB algorithmic -- the excess is 32-byte sectors moved for 4-byte neighbour picks.
-NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "r1:expand@2", "bytes": 89627904,
-               "source": "profiles/r1_ncu_expand_full_raw.csv (ncu --set full, tools/capture_evidence.sh)"}
+# One launch of k_expand_rows, layer 2 (the dominant launch: expansion of the third layer + relabel
+# and row side of the second), default workload: 96.03 MB read + 7.07 MB written to DRAM (one warm
+# minibatch, single slot) against 53.2 MB algorithmic -- the excess is 32-byte sectors moved for
+# 4-byte neighbour picks and table atomics that miss L2.
+NCU_TRAFFIC = {"workload": ("products", [15, 10, 5], 4096, 4), "kernel": "expand+relabel+rowside@2", "bytes": 103100416,
+               "source": "profiles/r2_ncu_expand_rows_full_raw.csv (ncu --set full, tools/gpu_r2_final_n1.sh)"}
 
 
 def own_arm(args):
@@ -586,7 +587,12 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
     depth = args.slots
     results = {}
     sent = 4 * block_words * (world - 1)
-    for kind in ("staged", "staged_e2e", "direct", "direct_e2e", "peer_stores", "peer_stores_e2e", "nccl_all_to_all"):
+    all_kinds = ("staged", "staged_e2e", "direct", "direct_e2e", "peer_stores", "peer_stores_e2e", "nccl_all_to_all")
+    only = [a for a in getattr(args, "hand_over_arms", "").split(",") if a]
+    for kind in all_kinds:
+        if only and kind.replace("_e2e", "") not in only:
+            results[kind] = (float("nan"), "not run (--hand-over-arms)")
+            continue
         try:  # constructor failures are collective (raised on every rank): the other arm still runs
             cls = PartScatter if kind == "nccl_all_to_all" else DirectScatter if kind.startswith("direct") else \
                 StagedScatter if kind.startswith("staged") else PeerScatter
@@ -1179,6 +1185,7 @@ def main():
     ap.add_argument("--lanes", type=int, default=8, help="partitioned mode: minibatches in flight per rank")
     ap.add_argument("--partitioned-shards", action="store_true",
                     help="N > 1: only the partitioned slicer, graph generated shard by shard (config 5 at scale)")
+    ap.add_argument("--hand-over-arms", default="", help="N > 1: comma list of staged,direct,peer_stores,nccl_all_to_all (default: all)")
     ap.add_argument("--no-hand-over", action="store_true",
                     help="N > 1: skip the split-parallel hand-over (slice anywhere, part g -> rank g) measurement")
     ap.add_argument("--no-partitioned", action="store_true",
