@@ -509,12 +509,18 @@ def own_arm(args):
             if ho.get("value"):
                 out["value"], out["ms_per_step"] = ho["value"], ho["ms_per_step"]
                 out["config"]["minibatches_per_step"] = ho["minibatches_per_step"]
+                how = {"staged": "written once into local part-contiguous blocks by the slicing kernels and sent to "
+                                 "GPU g by the copy engines",
+                       "direct": "written straight into GPU g's receive buffer by the slicing kernels",
+                       "peer_stores": "delivered to GPU g by the packing kernel's own stores"}[ho["headline_exchange"]]
                 out["config"]["sharding"] = ("hand-over: whole minibatches per rank on a replicated topology, "
-                                             f"{world} parts, part g of every minibatch delivered to GPU g by the "
-                                             "packing kernel's own stores over NVLink (content-checked)")
+                                             f"{world} parts, part g of every minibatch {how} over NVLink; barrier by "
+                                             "flag words in the peers' memory (content-checked)")
                 out["config"]["workload"] = out["config"]["workload"].replace(f"{P} parts", f"{world} parts")
                 out["parity"] = ho["parity"]
-                out["gpu_launches"] = int((dev_launches / args.group + 1) * args.steps * ho["minibatches_per_step"] / world)
+                # per minibatch: the chain + the round's flag kernel + the release flag kernel (+ the packing kernel)
+                extra = 3 if ho["headline_exchange"] == "peer_stores" else 2
+                out["gpu_launches"] = int((dev_launches / args.group + extra) * args.steps * ho["minibatches_per_step"] / world)
                 out["sampled_edges_per_s"] = None
                 if ho["e2e"].get("value"):
                     out["e2e"] = ho["e2e"]
@@ -894,7 +900,67 @@ def partitioned_line(args, torch, dist, ip, ix, local, rank, world, steps=3, mbs
                        "bandwidth-bound"}
     dist.barrier()
     ps.close()
+    try:  # the split-parallel shuffle of partial rows, forward + backward, every layer
+        sh = shuffle_line(torch, dist, lip, lix, n, m_global, local, rank, world, batches, okw)
+    except Exception as e:
+        log(f"[bench] shuffle leg raised: {type(e).__name__}: {e}")
+        sh = {"unavailable": f"{type(e).__name__}: {e}"}
+    if out is not None:
+        out["shuffle"] = sh
     return out
+
+
+def shuffle_line(torch, dist, lip, lix, n, m_global, local, rank, world, batches, okw, dim=128, reps=5):
+    """gs_pslicer_shuffle (replaces pull_for_remotes / push_from_remotes + mergeKernel,
+    python/data/bipartite.py:88-99, src/gnn/dist_sage.cu:193-220): partial rows of [|out_nodes|, dim]
+    fp32 pushed into the owners' arenas over NVLink and merged there; backward hands them back.
+    Timed per layer with the host blocked until done (max over ranks); bytes = rows this rank sends x
+    dim x 4.  Checked against a restatement on the device: forward then backward of all-ones rows."""
+    from cslicer.partitioned import PartitionedSlicer, connect_process_group
+    import time as _t
+    ps = PartitionedSlicer(lip, lix, n, rank, world, FANOUTS, device=local, max_batch=BATCH, num_slots=2, seed=7,
+                           host_output=False, num_edges_global=m_global, shuffle_rows_capacity=1 << 19,
+                           shuffle_max_dim=dim, timeout_ms=5000, **okw)
+    connect_process_group(ps, dist)
+    v = ps.slice(batches[0][1], batches[0][0])
+    L = len(FANOUTS)
+    sent = t_f = t_b = 0.0
+    per_layer = []
+    ok = 1
+    for l in range(L):
+        n_out = v.field_len(l, rank, "out_nodes")
+        n_from = v.field_len(l, rank, "from_ids")
+        rows = torch.ones((n_out, dim), dtype=torch.float32, device=f"cuda:{local}")
+        ps.shuffle(v, l, rows, False)  # warm
+        tf = tb = 0.0
+        for _ in range(reps):
+            rows.fill_(1.0)
+            torch.cuda.synchronize(); dist.barrier()
+            t0 = _t.perf_counter(); ps.shuffle(v, l, rows, False); tf += _t.perf_counter() - t0
+            if _ == 0:
+                # owned rows hold 1 + (number of peers that contributed); all entries of a row agree
+                own = rows[v.tensor(l, rank, "owned_out_nodes").long()]
+                ok &= int(bool((own >= 1).all()) and bool((own == own[:, :1]).all()) and bool((own == own.round()).all()))
+            torch.cuda.synchronize(); dist.barrier()
+            t0 = _t.perf_counter(); ps.shuffle(v, l, rows, True); tb += _t.perf_counter() - t0
+        tt = torch.tensor([tf / reps, tb / reps], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        b = n_from * dim * 4
+        per_layer.append({"rows_sent": int(n_from), "forward_ms": round(float(tt[0]) * 1e3, 4),
+                          "backward_ms": round(float(tt[1]) * 1e3, 4)})
+        sent += b; t_f += float(tt[0]); t_b += float(tt[1])
+    v.release()
+    tk = torch.tensor([ok], dtype=torch.int32, device=f"cuda:{local}")
+    dist.all_reduce(tk, op=dist.ReduceOp.MIN)
+    dist.barrier()
+    ps.close()
+    return {"dim": dim, "layers": per_layer, "bytes_sent_per_rank_forward": int(sent),
+            "forward_gbs_per_rank": round(sent / t_f / 1e9, 2), "backward_gbs_per_rank": round(sent / t_b / 1e9, 2),
+            "nvlink_peak_gbs_per_direction": 900, "frac_of_nvlink_forward": round(sent / t_f / 1e9 / 900, 4),
+            "check": "merge-consistent" if int(tk[0]) == 1 else "INCONSISTENT",
+            "what": "one minibatch of this workload, every layer's partial rows (fp32, dim 128): push into the owners' "
+                    "arenas + merge (forward), hand back (backward); host-blocking calls, max over ranks; "
+                    "bit-exactness against the restated mergeKernel is in tests/test_partitioned.py"}
 
 
 def partitioned_shards_arm(args):
