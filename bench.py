@@ -608,10 +608,17 @@ def hand_over_line(args, torch, dist, g, n, local, rank, world, steps=None, roun
             results[kind] = (float("nan"), "unavailable")
             continue
         mirror_words = min(block_words, (need * 21 // 20 + 3) & ~3) if kind.endswith("e2e") else 0
-        results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds if not mirror_words else max(8, rounds // 4),
-                                       torch, dist, local, rank, world, n, mirror_words)
-        if hasattr(ps, "close"):
-            ps.close()
+        try:
+            results[kind] = _hand_over_run(ps, sl, batches, depth, steps, rounds if not mirror_words else max(8, rounds // 4),
+                                           torch, dist, local, rank, world, n, mirror_words)
+        except Exception as e:  # the flag waits time out, so a failing rank does not leave the others hanging
+            log(f"[bench] hand-over arm {kind} failed on rank {rank}: {type(e).__name__}: {e}")
+            results[kind] = (float("nan"), "failed")
+        try:
+            if hasattr(ps, "close"):
+                ps.close()
+        except Exception as e:
+            log(f"[bench] hand-over arm {kind}: close failed: {type(e).__name__}: {e}")
         ps = None
     out = None
     if rank == 0:

@@ -592,6 +592,11 @@ __device__ __forceinline__ bool last_block_n(uint32_t *ticket, uint32_t n) {
 
 // -DGS_DIAG=bits: knock-out builds for tools/build_variants.sh (WRONG results; they only show what a
 // piece of work costs with all slots in flight).  1: row side writes nothing, 2: no relabel-map read.
+// picks per work item of k_expand_rows (4 or 8): more picks in flight per dependent round trip
+// (8: +2.4 % on the products workload, A/B on one B200 with tools/gpu_r2_call16.sh)
+#ifndef GS_PB
+#define GS_PB 8
+#endif
 #ifndef GS_OUT_STREAM
 #define GS_OUT_STREAM 1
 #endif
@@ -866,8 +871,8 @@ template <int RNG, typename PK>
 __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
   gs_sample_header *h = ws.hdr;
   int32_t *const cand = cand_buf(ws, layer);
-  __shared__ int32_t s_stage_c[GS_NW][160];
-  __shared__ uint8_t s_stage_f[GS_NW][160];
+  __shared__ int32_t s_stage_c[GS_NW][32 * (GS_PB + 1)];
+  __shared__ uint8_t s_stage_f[GS_NW][32 * (GS_PB + 1)];
   if (h->status != 0) return;
   const Tbl tbl(ws);
   const uint64_t spol = ws.l2_hints ? l2_policy_stream() : 0ull;
@@ -898,7 +903,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
     int32_t r = v - (int32_t)(__umulhi((uint32_t)v, pmagic) * (uint32_t)P);
     return r < 0 ? r + P : r;
   };
-  const uint32_t nb = (uint32_t)(fan + 3) >> 2;                       // items per row
+  const uint32_t nb = (uint32_t)(fan + GS_PB - 1) / GS_PB;            // items per row
   const uint32_t nbm = (uint32_t)((0x100000000ull + nb - 1) / nb);    // item / nb by multiply-high + one correction
   const uint32_t nitems = (uint32_t)F * nb;                           // F < 2^30 / ... : fits (F * (fan + 1) <= Ccap < 2^30)
   if (threadIdx.x < GS_CNT_STRIDE) s_cnt[threadIdx.x] = 0u;
@@ -906,6 +911,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
   for (uint32_t it0 = blockIdx.x * GS_TPB; it0 < nitems; it0 += (uint32_t)nb_role * GS_TPB) {
     const uint32_t item = it0 + threadIdx.x;
     PK pk_in = 0, pk_e = 0, pk_out = 0, pk_own = 0, pk_to = 0;
+    PK pk_in2 = 0, pk_e2 = 0;  // picks 4..7 of an item: a byte of a warp total holds at most 32 x 4
     uint32_t n_new = 0u;
     // phase A: the item's row and the positions it owns
     uint32_t row = 0u, b = 0u, o = 0u;
@@ -922,8 +928,8 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
       ri = ws.rowinfo[row];
       o = ws.off[row];
       const uint32_t c = ws.off[row + 1] - o;
-      j0 = (int)(4u * b);
-      nj = min(4, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
+      j0 = (int)((uint32_t)GS_PB * b);
+      nj = min(GS_PB, (int)c - 1 - j0);  // picks of this item (<= 0: none; the row is shorter)
       if (nj > 0) {
         lane_lo = o + 1u + (uint32_t)j0;
         lane_hi = lane_lo + (uint32_t)nj;
@@ -933,7 +939,7 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
         lane_hi = max(lane_hi, o + 1u);
       }
     }
-    // The items of a warp own one contiguous range of positions (< 160): staged in shared memory,
+    // The items of a warp own one contiguous range of positions (<= 32 * (GS_PB + 1)): staged in shared memory,
     // written out as whole sectors (per-lane stores of four words at a stride cost 4x the sectors).
     const uint32_t pmin = __reduce_min_sync(FULL, lane_lo), pmax = __reduce_max_sync(FULL, lane_hi);
     int32_t *st_c = s_stage_c[warp_id()];
@@ -948,29 +954,37 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
         st_f[o - pmin] = (uint8_t)(GS_CK_SELF | ((uint32_t)g0 << GS_CF_PART_SHIFT));
       }
       if (nj > 0) {
-        uint4 blk = make_uint4(0u, 0u, 0u, 0u);
+        uint4 blk[GS_PB / 4];  // one Philox block serves four picks
         Mod32 md;
         md.d = 1u; md.inv = 0u;
+#pragma unroll
+        for (int q4 = 0; q4 < GS_PB / 4; q4++) blk[q4] = make_uint4(0u, 0u, 0u, 0u);
         if (samp) {
-          if (!replay) blk = philox_block(seed_lo, seed_hi, batch, layer, nd, norepl ? GS_NR_KEY_BLOCK : (int)b);
+          if (!replay) {
+#pragma unroll
+            for (int q4 = 0; q4 < GS_PB / 4; q4++)
+              if (q4 == 0 || (!norepl && nj > 4 * q4))
+                blk[q4] = philox_block(seed_lo, seed_hi, batch, layer, nd,
+                                       norepl ? GS_NR_KEY_BLOCK : (int)(b * (GS_PB / 4) + q4));
+          }
           if (!norepl) md.set((uint32_t)deg);
         }
-        int32_t v[4];
+        int32_t v[GS_PB];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < GS_PB; j++) {
           v[j] = nd;
           if (j < nj) {
             int32_t pick = j0 + j;
             if (samp) {
               if (norepl) {
-                pick = (int32_t)nr_pick(blk, (uint32_t)pick, (uint32_t)deg);
+                pick = (int32_t)nr_pick(blk[0], (uint32_t)pick, (uint32_t)deg);
               } else {
                 uint32_t r;
                 if (replay) {
                   const uint64_t di = dbase + (uint64_t)fan * ws.samp_rank[row] + (uint32_t)pick;
                   r = di < n_draws ? ws.draws[di] : 0u;
                 } else {
-                  r = philox_word(blk, j);
+                  r = philox_word(blk[j >> 2], j & 3);
                 }
                 pick = (int32_t)md.rem(r);
               }
@@ -978,13 +992,13 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
             v[j] = ld_stream_i32(indices + rs + pick, hints, spol);
           }
         }
-        int g[4];
-        uint32_t old[4];
-        bool edge[4];
+        int g[GS_PB];
+        uint32_t old[GS_PB];
+        bool edge[GS_PB];
         uint32_t rbits = 0u;
         const uint32_t p1 = o + 1u + (uint32_t)j0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < GS_PB; j++) {
           edge[j] = j < nj && v[j] != nd;  // a sampled neighbour equal to the destination is a self edge (slicer.cpp:33)
           g[j] = 0;
           old[j] = 0u;
@@ -997,20 +1011,21 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
         uint32_t was = 0u;
         if (rbits) was = atomicOr(rw_rowhas + row, rbits);
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < GS_PB; j++) {
           if (j < nj) {
             int32_t cv = 0;
             uint32_t cf = GS_CK_DEAD;
             if (edge[j]) {
+              PK &a_e = (GS_PB > 4 && j >= 4) ? pk_e2 : pk_e, &a_in = (GS_PB > 4 && j >= 4) ? pk_in2 : pk_in;
               cv = v[j];
               cf = GS_CK_EDGE | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
-              pk_e += pkt_one<PK>(g[j]);
+              a_e += pkt_one<PK>(g[j]);
               if (!tag.mine(old[j])) {  // first arrival for a node that is new to the frontier
                 n_new++;
-                pk_in += pkt_one<PK>(g[j]);
+                a_in += pkt_one<PK>(g[j]);
               } else if (!(old[j] & tag.kind)) {  // a row of the current frontier
                 const uint32_t idx = old[j] & tag.pmask;
-                if (atomicMin(rw_ea + idx, p1 + j) == GS_INF) pk_in += pkt_one<PK>(g[j]);
+                if (atomicMin(rw_ea + idx, p1 + j) == GS_INF) a_in += pkt_one<PK>(g[j]);
                 cv = (int32_t)idx;
                 cf = GS_CK_FHIT | ((uint32_t)g[j] << GS_CF_PART_SHIFT);
               }
@@ -1052,6 +1067,15 @@ __device__ void expand_rows_role(const GsWs &ws, int layer, int nb_role) {
       if ((x = pkt_get<PK>(pk_to, lane))) atomicAdd(&s_cnt[GS_CNT_TO(P, lane)], x);
     }
     if (lane == 31 && n_new) atomicAdd(&s_cnt[GS_CNT_NEW], n_new);
+    if (GS_PB > 4) {
+      pk_in2 = pkt_redux(pk_in2);
+      pk_e2 = pkt_redux(pk_e2);
+      if (lane < P) {
+        uint32_t x;
+        if ((x = pkt_get<PK>(pk_in2, lane))) atomicAdd(&s_cnt[GS_CNT_IN(P, lane)], x);
+        if ((x = pkt_get<PK>(pk_e2, lane))) atomicAdd(&s_cnt[GS_CNT_E(P, lane)], x);
+      }
+    }
   }
   __syncthreads();
   if (threadIdx.x < 1 + 5 * P && s_cnt[threadIdx.x]) atomicAdd(cnt + threadIdx.x, s_cnt[threadIdx.x]);

@@ -1,0 +1,9 @@
+#!/bin/bash
+# A/B of compile-time variants: parity of each variant's library, then its pipelined rate
+V=$PWD/occ-gnn_b200/cslicer/variants
+timeout 300 python tools/rate.py 1 8 8 2 2>&1 | grep "mb/s"
+for v in "$@"; do
+  echo "variant $v"
+  GSPLIT_SLICER_LIB=$V/lib_$v.so timeout 600 python -m pytest tests/test_parity_gpu.py tests/test_random_sweep_gpu.py -x -q -m gpu 2>&1 | tail -1
+  GSPLIT_SLICER_LIB=$V/lib_$v.so timeout 300 python tools/rate.py 1 8 8 2 2>&1 | grep "mb/s"
+done
