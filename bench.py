@@ -484,6 +484,10 @@ def own_arm(args):
             except Exception as e:
                 out["owner_range"] = {"unavailable": f"{type(e).__name__}: {e}"}
             try:
+                out["loader"] = loader_line(ip, ix, torch)
+            except Exception as e:
+                out["loader"] = {"unavailable": f"{type(e).__name__}: {e}"}
+            try:
                 out["edge_partitioning"] = edge_partitioning_line(n, P, sizes)
             except Exception as e:
                 out["edge_partitioning"] = {"unavailable": f"{type(e).__name__}: {e}"}
@@ -1072,6 +1076,39 @@ def reference_config(ip, ix, g, args, torch):
             "cuda_value": round(5 * args.mb_per_step / (ms * 1e-3), 2),
             "cuda_e2e": round(3 * args.mb_per_step / (ms2 * 1e-3), 2),
             "cuda_sampled_edges_per_s": round(edges / (ms * 1e-3), 1)}
+
+
+def loader_line(ip, ix, torch):
+    """the workload's graph written in the reference's on-disk layout, then
+    loaded (a) by gs_graph_load -- files streamed through pinned staging buffers into HBM, checked
+    and narrowed on the device -- and (b) the reference's way: whole files into host arrays
+    (Dataset, dataset.cpp:18-36, with its checksums) and uploaded.  Page cache warm in both."""
+    import shutil
+    import cslicer
+    from cslicer.engine import Graph
+    d = tempfile.mkdtemp(prefix="gsplit_ds_")
+    try:
+        cslicer.write_dataset(d, ip, ix, features=np.zeros((ip.size - 1, 1), np.float32))
+        nbytes = ip.size * 8 + ix.size * 8
+        Graph.from_directory(d).close()
+        t0 = time.perf_counter()
+        g = Graph.from_directory(d)
+        torch.cuda.synchronize()
+        t_dev = time.perf_counter() - t0
+        same = (g.num_nodes, g.num_edges) == (ip.size - 1, ix.size)
+        g.close()
+        t0 = time.perf_counter()
+        ds = cslicer.Dataset(d, load_node_data=False)
+        g = Graph(ds.indptr, ds.indices)
+        torch.cuda.synchronize()
+        t_host = time.perf_counter() - t0
+        g.close()
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    return {"file_bytes": int(nbytes), "gs_graph_load_s": round(t_dev, 3), "gs_graph_load_gbs": round(nbytes / t_dev / 1e9, 2),
+            "host_arrays_then_upload_s": round(t_host, 3), "host_arrays_then_upload_gbs": round(nbytes / t_host / 1e9, 2),
+            "sizes_agree": bool(same),
+            "what": "indptr.bin + indices.bin (int64) -> validated int32 CSR in HBM, checksums verified, page cache warm"}
 
 
 def edge_partitioning_line(n, P, sizes, reps=3):

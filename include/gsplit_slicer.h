@@ -145,6 +145,13 @@ void gs_config_default(gs_config *cfg);
 int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
                     const int64_t *indptr_host, const int64_t *indices_host,
                     gs_graph **out);
+/* SURVEY 8(f) row N4 -- replaces Dataset::read_graph (dataset.cpp:18-36) for the files
+ * convert_dgl_dataset.py:99-127 writes: `directory`/meta.txt (num_nodes, num_edges,
+ * csum_offsets, csum_edges), indptr.bin int64[N+1], indices.bin int64[M], streamed from
+ * disk through two pinned staging buffers into HBM; the device validates, checksums
+ * (verify_checksums != 0: the sums the reference only asserts in debug builds,
+ * dataset.cpp:27,35) and narrows the ids as they arrive -- the host never holds the graph. */
+int gs_graph_load(int device, const char *directory, int verify_checksums, gs_graph **out);
 int gs_graph_destroy(gs_graph *g);
 int64_t gs_graph_num_nodes(const gs_graph *g);
 int64_t gs_graph_num_edges(const gs_graph *g);

@@ -23,7 +23,7 @@ NUM_FIELDS = len(FIELDS)
 
 # every symbol include/gsplit_slicer.h declares (tests check the export table)
 SYMBOLS = ["gs_last_error", "gs_abi_version", "gs_config_default", "gs_graph_create",
-           "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
+           "gs_graph_load", "gs_graph_destroy", "gs_graph_num_nodes", "gs_graph_num_edges", "gs_slicer_create",
            "gs_slicer_destroy", "gs_slicer_submit", "gs_slicer_flush", "gs_slicer_wait", "gs_slicer_slab",
            "gs_slicer_release", "gs_slicer_profile", "gs_slicer_launches_per_sample",
            "gs_slicer_slot_bytes", "gs_slicer_slab_capacity", "gs_reference_shuffle", "gs_bench_sector_probe",
@@ -104,6 +104,7 @@ def lib():
     L.gs_config_default.argtypes = [C.POINTER(Config)]
     L.gs_graph_create.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                   C.POINTER(C.c_void_p)]
+    L.gs_graph_load.argtypes = [C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
     L.gs_graph_destroy.argtypes = [C.c_void_p]
     L.gs_graph_num_nodes.restype = C.c_int64
     L.gs_graph_num_nodes.argtypes = [C.c_void_p]

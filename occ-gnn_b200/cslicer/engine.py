@@ -35,6 +35,19 @@ class Graph:
                                         ip.ctypes.data, ix.ctypes.data, C.byref(h)))
         self._h = h
 
+    @classmethod
+    def from_directory(cls, directory, device=0, verify=True):
+        """The reference's on-disk layout (meta.txt, indptr.bin, indices.bin) streamed straight
+        into HBM by gs_graph_load: the host never holds the arrays; checksums, offsets and ids
+        are verified on the device."""
+        self = cls.__new__(cls)
+        h = C.c_void_p()
+        N.check(N.lib().gs_graph_load(int(device), str(directory).encode(), int(bool(verify)), C.byref(h)))
+        self._h, self.device = h, int(device)
+        self.num_nodes = int(N.lib().gs_graph_num_nodes(h))
+        self.num_edges = int(N.lib().gs_graph_num_edges(h))
+        return self
+
     def close(self):
         if getattr(self, "_h", None) and N is not None and N.lib is not None:
             N.lib().gs_graph_destroy(self._h)

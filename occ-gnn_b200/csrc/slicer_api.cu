@@ -10,6 +10,10 @@
 #include <string>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <nvtx3/nvToolsExt.h>
 
 #include "slicer_internal.cuh"
@@ -381,6 +385,158 @@ int gs_graph_create(int device, int64_t num_nodes, int64_t num_edges,
     return bail(fail(GS_ERR_INVALID, "indices[%llu] lies outside [0, num_nodes)", bad[1] - 1ull));
   cudaFree(err);
   cudaFree(tmp);
+  *out = g;
+  return GS_OK;
+}
+
+// the reference's on-disk layout (dataset.cpp:18-36, written by
+// convert_dgl_dataset.py:99-127) straight into HBM.  meta.txt gives the sizes and checksums;
+// indptr.bin / indices.bin stream through two pinned staging buffers (pread -> H2D copy -> device
+// passes), so the host never holds the graph -- 13 GB of int64 indices for papers100M -- and the
+// device validates (monotone offsets, ids in range), sums (the checksums the reference compiles out
+// under NDEBUG, dataset.cpp:27,35) and narrows the ids as they arrive.
+int gs_graph_load(int device, const char *directory, int verify_checksums, gs_graph **out) {
+  if (!out || !directory) return fail(GS_ERR_INVALID, "NULL argument");
+  *out = nullptr;
+  const std::string dir(directory);
+  long long n = -1, m = -1, cs_off = 0, cs_edges = 0;
+  bool has_off = false, has_edges = false;
+  {
+    FILE *f = fopen((dir + "/meta.txt").c_str(), "r");
+    if (!f) return fail(GS_ERR_INVALID, "cannot open %s/meta.txt", directory);
+    char line[512];
+    while (fgets(line, sizeof line, f)) {
+      char *eq = strchr(line, '=');
+      if (!eq) continue;
+      *eq = 0;
+      const std::string key(line);
+      char *end = nullptr;
+      long long v = strtoll(eq + 1, &end, 10);
+      if (end && (*end == '.' || *end == 'e' || *end == 'E')) v = (long long)strtod(eq + 1, nullptr);
+      if (key == "num_nodes") n = v;
+      else if (key == "num_edges") m = v;
+      else if (key == "csum_offsets") { cs_off = v; has_off = true; }
+      else if (key == "csum_edges") { cs_edges = v; has_edges = true; }
+    }
+    fclose(f);
+  }
+  if (n < 1 || n >= (1ll << 31) - 1 || m < 0) return fail(GS_ERR_INVALID, "meta.txt: num_nodes / num_edges missing or out of range");
+  const int fd_p = open((dir + "/indptr.bin").c_str(), O_RDONLY), fd_x = open((dir + "/indices.bin").c_str(), O_RDONLY);
+  auto close_fds = [&] { if (fd_p >= 0) close(fd_p); if (fd_x >= 0) close(fd_x); };
+  struct stat sp, sx;
+  if (fd_p < 0 || fd_x < 0 || fstat(fd_p, &sp) || fstat(fd_x, &sx) || sp.st_size != (off_t)((n + 1) * 8) ||
+      sx.st_size != (off_t)(m * 8)) {
+    close_fds();
+    return fail(GS_ERR_INVALID, "indptr.bin / indices.bin missing or their size disagrees with meta.txt");
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    close_fds();
+    return fail(GS_ERR_CUDA, "no CUDA device %d (%s): this library has no CPU fallback", device,
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count");
+  }
+  gs_graph *g = new (std::nothrow) gs_graph();
+  if (!g) { close_fds(); return fail(GS_ERR_INVALID, "out of host memory"); }
+  g->device = device;
+  g->num_nodes = n;
+  g->num_edges = m;
+  const size_t CH = 4u << 20;  // int64 elements per staging buffer (32 MiB)
+  int64_t *pin[2] = {nullptr, nullptr}, *tmp[2] = {nullptr, nullptr};
+  unsigned long long *err = nullptr;  // [0] bad row + 1, [1] bad edge + 1, [2] sum(indptr), [3] sum(indices)
+  cudaStream_t st[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  auto cleanup = [&] {
+    for (int i = 0; i < 2; i++) {
+      if (pin[i]) cudaFreeHost(pin[i]);
+      if (tmp[i]) cudaFree(tmp[i]);
+      if (st[i]) cudaStreamDestroy(st[i]);
+      if (ev[i]) cudaEventDestroy(ev[i]);
+    }
+    cudaFree(err);
+    close_fds();
+  };
+  auto bail = [&](int code) {
+    std::string keep = g_err;
+    cleanup();
+    gs_graph_destroy(g);
+    g_err = keep;
+    return code;
+  };
+#define CUL(call)                                                                                  \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return bail(fail(GS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__)); \
+  } while (0)
+  CUL(cudaSetDevice(device));
+  CUL(cudaMalloc((void **)&g->indptr, (size_t)(n + 1) * sizeof(int64_t)));
+  CUL(cudaMalloc((void **)&g->indices, (size_t)std::max<long long>(m, 1) * sizeof(int32_t)));
+  CUL(cudaMalloc((void **)&err, 4 * sizeof(unsigned long long)));
+  {
+    const unsigned long long init[4] = {~0ull, ~0ull, 0ull, 0ull};
+    CUL(cudaMemcpy(err, init, sizeof init, cudaMemcpyHostToDevice));
+  }
+  for (int i = 0; i < 2; i++) {
+    CUL(cudaHostAlloc((void **)&pin[i], CH * sizeof(int64_t), cudaHostAllocDefault));
+    CUL(cudaMalloc((void **)&tmp[i], CH * sizeof(int64_t)));
+    CUL(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
+    CUL(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+  }
+  // one pass over a file: chunk k goes through staging buffer k & 1
+  auto stream_file = [&](int fd, long long count, bool is_indices) -> int {
+    int k = 0;
+    for (long long o = 0; o < count; o += (long long)CH, k++) {
+      const int b = k & 1;
+      const size_t cnt = (size_t)std::min<long long>((long long)CH, count - o);
+      CUL(cudaEventSynchronize(ev[b]));  // the copy that last read this pinned buffer is done
+      size_t got = 0;
+      while (got < cnt * 8) {
+        const ssize_t r = pread(fd, (char *)pin[b] + got, cnt * 8 - got, (off_t)(o * 8 + (long long)got));
+        if (r <= 0) return bail(fail(GS_ERR_INVALID, "short read in %s", is_indices ? "indices.bin" : "indptr.bin"));
+        got += (size_t)r;
+      }
+      int64_t *dst = is_indices ? tmp[b] : g->indptr + o;
+      CUL(cudaMemcpyAsync(dst, pin[b], cnt * 8, cudaMemcpyHostToDevice, st[b]));
+      CUL(cudaEventRecord(ev[b], st[b]));
+      gs_launch_sum_i64(dst, cnt, err + (is_indices ? 3 : 2), st[b]);
+      if (is_indices) {
+        gs_launch_check_ids(tmp[b], cnt, o, n, err, st[b]);
+        gs_launch_narrow_ids(tmp[b], g->indices + o, cnt, st[b]);
+        // the next use of tmp[b] is two chunks away on the same stream: ordered
+      }
+      CUL(cudaGetLastError());
+    }
+    return GS_OK;
+  };
+  int rc = stream_file(fd_p, n + 1, false);
+  if (rc != GS_OK) return rc;
+  CUL(cudaStreamSynchronize(st[0]));
+  CUL(cudaStreamSynchronize(st[1]));
+  gs_launch_check_indptr(g->indptr, n, m, err, st[0]);
+  rc = stream_file(fd_x, m, true);
+  if (rc != GS_OK) return rc;
+  CUL(cudaStreamSynchronize(st[0]));
+  CUL(cudaStreamSynchronize(st[1]));
+  unsigned long long res[4] = {0, 0, 0, 0};
+  long long first = -1, last = -1;
+  CUL(cudaMemcpy(res, err, sizeof res, cudaMemcpyDeviceToHost));
+  CUL(cudaMemcpy(&first, g->indptr, 8, cudaMemcpyDeviceToHost));
+  CUL(cudaMemcpy(&last, g->indptr + n, 8, cudaMemcpyDeviceToHost));
+#undef CUL
+  if (first != 0 || last != m) return bail(fail(GS_ERR_INVALID, "indptr[0] != 0 or indptr[N] != num_edges"));
+  if (res[0] != ~0ull)
+    return bail(fail(GS_ERR_INVALID, "indptr is not a non-decreasing sequence inside [0, num_edges]: first bad row %llu",
+                     res[0] - 1ull));
+  if (res[1] != ~0ull) return bail(fail(GS_ERR_INVALID, "indices[%llu] lies outside [0, num_nodes)", res[1] - 1ull));
+  if (verify_checksums) {
+    if (has_off && (long long)res[2] != cs_off)
+      return bail(fail(GS_ERR_INVALID, "indptr checksum mismatch: file sums to %lld, meta.txt says %lld", (long long)res[2], cs_off));
+    if (has_edges && (long long)res[3] != cs_edges)
+      return bail(fail(GS_ERR_INVALID, "indices checksum mismatch: file sums to %lld, meta.txt says %lld", (long long)res[3], cs_edges));
+  }
+  cleanup();
   *out = g;
   return GS_OK;
 }

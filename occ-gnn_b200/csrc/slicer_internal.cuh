@@ -177,6 +177,8 @@ void gs_launch_narrow_ids(const int64_t *src, int32_t *dst, size_t n, cudaStream
 void gs_launch_check_indptr(const int64_t *indptr, int64_t n, int64_t m, unsigned long long *err, cudaStream_t st);
 void gs_launch_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t num_nodes, unsigned long long *err,
                          cudaStream_t st);
+// wrapping sum of an int64 array into *out (atomicAdd; zero it first): the dataset checksums
+void gs_launch_sum_i64(const int64_t *src, size_t n, unsigned long long *out, cudaStream_t st);
 // random-sector yardstick (bench): n reads of one 4-byte word each from a table of `elems` words
 void gs_launch_sector_probe(const uint32_t *table, uint64_t elems, uint64_t n, uint32_t seed, uint32_t *sink,
                             int grid, cudaStream_t st);

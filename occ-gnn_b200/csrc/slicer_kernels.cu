@@ -1920,6 +1920,24 @@ __global__ void k_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t 
   }
 }
 
+// Wrapping 64-bit sum of an int64 array (the dataset's checksums, dataset.cpp:27,35): one
+// shuffle reduction per warp, one atomic per CTA.
+__global__ void __launch_bounds__(256) k_sum_i64(const int64_t *src, size_t n, unsigned long long *out) {
+  unsigned long long acc = 0ull;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    acc += (unsigned long long)src[i];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(FULL, acc, d);
+  __shared__ unsigned long long s_w[8];
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0ull;
+    for (int k = 0; k < 8; k++) t += s_w[k];
+    atomicAdd(out, t);
+  }
+}
+
 // Random-sector yardstick (bench.py, roofline.random_access): every thread keeps
 // eight independent 4-byte reads in flight, each from a pseudo-random word of a
 // table of `elems` words -- one 32-byte DRAM sector per read once the table is
@@ -2021,6 +2039,9 @@ void gs_launch_check_indptr(const int64_t *indptr, int64_t n, int64_t m, unsigne
 void gs_launch_check_ids(const int64_t *ids, size_t n, int64_t base, int64_t num_nodes, unsigned long long *err,
                          cudaStream_t st) {
   k_check_ids<<<1184, 256, 0, st>>>(ids, n, base, num_nodes, err);
+}
+void gs_launch_sum_i64(const int64_t *src, size_t n, unsigned long long *out, cudaStream_t st) {
+  k_sum_i64<<<592, 256, 0, st>>>(src, n, out);
 }
 void gs_launch_sector_probe(const uint32_t *table, uint64_t elems, uint64_t n, uint32_t seed, uint32_t *sink,
                             int grid, cudaStream_t st) {
