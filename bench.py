@@ -525,7 +525,9 @@ def own_arm(args):
                 # per minibatch: the chain + the round's flag kernel + the release flag kernel (+ the packing kernel)
                 extra = 3 if ho["headline_exchange"] == "peer_stores" else 2
                 out["gpu_launches"] = int((dev_launches / args.group + extra) * args.steps * ho["minibatches_per_step"] / world)
-                out["sampled_edges_per_s"] = None
+                # the same minibatches as the replicas leg (rank r slices batches r, r + world, ...): edges per minibatch carry over
+                out["sampled_edges_per_s"] = round(out["replicas"]["sampled_edges_per_s"] * ho["value"] / out["replicas"]["value"], 1) \
+                    if out["replicas"]["value"] else None
                 if ho["e2e"].get("value"):
                     out["e2e"] = ho["e2e"]
                 # value-first ordering keeps these keys inside any truncated tail of the record
