@@ -13,7 +13,7 @@
  * bounded queue, WorkerPool.cpp:23-24), in groups of `group_size` consecutive
  * slots.  gs_slicer_submit() stages one minibatch in the next slot of the group
  * being filled; the submit that fills the group launches it -- ONE pre-captured
- * CUDA graph of 3 L + 1 kernels for all `group_size` minibatches (blockIdx.y =
+ * CUDA graph of 4 L + 1 kernels for all `group_size` minibatches (blockIdx.y =
  * member) on the group's stream -- and returns at once.  gs_slicer_wait() blocks
  * until that slot's sample is complete (launching a partly filled group first);
  * gs_slicer_release() hands the slot back.  group_size = 1 is the reference's
@@ -368,7 +368,7 @@ int gs_epart_get(gs_epart *e, int32_t part, int32_t what, int32_t remote, const 
 int gs_unique_first_noalloc(int device, const int32_t *ids_device, int64_t n, int64_t num_nodes,
                             int32_t *out_device, int64_t *count_host);
 
-/* Number of kernel launches one launch sequence performs (3 L + 1), shared by the
+/* Number of kernel launches one launch sequence performs (4 L + 1), shared by the
  * group_size minibatches of a group. */
 int gs_slicer_launches_per_sample(const gs_slicer *s);
 /* Device bytes held by one slot / by the slicer. */

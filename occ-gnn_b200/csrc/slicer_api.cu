@@ -84,7 +84,7 @@ struct Slot {
 
 // `members` consecutive slots share ONE launch sequence (grid.y = member): the
 // kernels of small layers then fill the machine, and a minibatch costs
-// (3 L + 1) / members launches.
+// (4 L + 1) / members launches.
 struct Group {
   int first = 0, members = 0;        // slots [first, first + members)
   GsWs *wsv = nullptr;               // device copy of the members' GsWs
@@ -157,7 +157,7 @@ int dev_alloc(Slot &sl, T **p, size_t n, int64_t *bytes) {
 }
 
 // The static launch sequence of `members` minibatches of one group (grid.y =
-// member): 3 launches per layer + 1.  `ev` (optional) receives one event after
+// member): 4 launches per layer + 1.  `ev` (optional) receives one event after
 // every launch, for gs_slicer_profile.
 int enqueue_group(gs_slicer *s, Group &gr, int members, cudaStream_t st, std::vector<cudaEvent_t> *ev,
                   std::vector<const char *> *names) {

@@ -1,21 +1,27 @@
 // slicer_kernels.cu -- hand-written sm_100a kernels of the minibatch slicer.
 //
 // One layer of the reference's sequential slice_layer (slicer.cpp:25-64) +
-// BiPartite::reorder (bipartite.cpp:3-17) becomes THREE data-parallel launches,
-// each a single pass over its stream:
+// BiPartite::reorder (bipartite.cpp:3-17) becomes FOUR data-parallel launches, each
+// a single pass over its stream; a launch hosts several roles (CTA ranges):
 //
-//   k_rows    frontier rows: CSR extents, candidate offsets (decoupled look-back
-//             scan), the rows' rank among the rows of their owner, and the mark
-//             "node v is row i of the current frontier" in the dedup table
-//             (+ in the same launch: the relabel of the PREVIOUS layer's edges);
-//   k_expand  candidate-parallel CSR expansion + Philox picks; one returning
-//             atom.min per edge source finds out whether the source is new to the
-//             layer or already a frontier row, and that answer makes every list
-//             length of the layer exact BEFORE any list is written: the last CTA
-//             lays the whole layer out in the sample slab;
-//   k_cand    one pass over the candidate stream with a decoupled look-back scan of
-//             1 + 5 P counters: next frontier, in_nodes, csr_indices, out_nodes,
-//             csr_indptr, owned / from / to / self lists -- every list of every part.
+//   k_rows         frontier rows: CSR extents, candidate offsets (flat decoupled look-back
+//                  scan -- the only cross-CTA wait of the chain), the rows' rank among the
+//                  rows of their owner, and the mark "node v is row i of the current
+//                  frontier" in the dedup table;
+//   k_expand_rows  (fan > 0; k_expand for fan = -1) CSR expansion + Philox picks; one
+//                  returning atom.min per edge source finds out whether the source is new
+//                  to the layer or already a frontier row, and that answer makes every
+//                  list length of the layer exact BEFORE any list is written: the last CTA
+//                  lays the whole layer out in the sample slab (or in the parts' hand-over
+//                  blocks).  Extra CTAs finish the PREVIOUS layer's lists: relabel and
+//                  row side;
+//   k_cand_flags   verdict per candidate (first occurrence / frontier slot), class counts
+//                  per CTA run, spine scan by the last CTA; extra CTAs count the row-side
+//                  classes the same way;
+//   k_cand_apply   ranks inside a run from the spine prefix: next frontier, in_nodes, edge
+//                  scratch (-> csr_indices), relabel map, per-row edge counts;
+//   k_tail         relabel and row side of the last layer, fused feature gather, the
+//                  slot's housekeeping for the next sample, header to the host.
 //
 // The sequential order the reference's lists are in (first occurrence in a scan
 // over frontier rows and, inside a row, over [self, neighbours...]) is carried by
@@ -27,7 +33,7 @@
 //
 // All sizes live in device memory (gs_sample_header); tiles are handed out by
 // tickets, so a whole minibatch -- or a group of them, blockIdx.y -- is one
-// static CUDA graph of 3 L + 1 launches with no host round trip.  Integer / byte
+// static CUDA graph of 4 L + 1 launches with no host round trip.  Integer / byte
 // work, HBM- and latency-bound: no tensor cores (nothing here is a contraction).
 #include <type_traits>
 
@@ -36,7 +42,8 @@
 // Resident CTAs per SM the tiled kernels are compiled for (register caps 65536 /
 // (GS_TPB * n)): the kernels wait on dependent random accesses, so what counts is
 // how many warps of all the launches in flight fit an SM.  ptxas -v at these
-// caps: k_rows 80 registers (64 B of spills), k_expand 63, k_cand 80, no spills.
+// caps: k_rows 64 registers, the others 40 (a few dozen bytes of spills each);
+// A/B of the caps: profiles/r2_variants_table.txt.
 #ifndef GS_MINB_ROWS
 #define GS_MINB_ROWS 4
 #endif
