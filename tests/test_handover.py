@@ -305,3 +305,73 @@ def test_ring_protocol_never_overwrites_an_unreleased_round(world, depth, slack)
         ring = RingSchedule(depth, slack)
         for _ in range(depth + 1):
             ring.next_post()
+
+
+@pytest.mark.parametrize("world,depth,slack", [(2, 1, 0), (2, 2, 3), (4, 3, 1), (8, 2, 0), (3, 4, 2)])
+def test_flag_protocol_never_overwrites_an_unreleased_round(world, depth, slack):
+    """Model of the flag barrier (barrier="flags", gs_flags_post) against the real RingSchedule.
+    Flag words: arrived[owner][buffer][source] and released[source][owner], values only grow.
+    A rank's writes for round r (direct / staged / packed alike) start once released[rank][q] >=
+    r - nbuf + 1 for every owner q; when they are complete the rank stores r + 1 into
+    arrived[q][r % nbuf][rank] of every owner; an owner consumes round r once its whole row holds
+    r + 1 and releases in order by storing r + 1 into released[s][owner] of every source.  Random
+    interleavings of hosts and devices: a write must never land in a buffer whose previous round
+    the owner has not released, the consumer must read the round it expects, nothing stalls."""
+    from cslicer.handover import RingSchedule
+    rng = np.random.default_rng(7 + 100 * world + 10 * depth + slack)
+    rounds = 60
+    rings = [RingSchedule(depth, slack) for _ in range(world)]
+    nbuf = rings[0].nbuf
+    arrived = np.zeros((world, nbuf, world), np.int64)     # [owner][buffer][source]
+    released = np.zeros((world, world), np.int64)          # [source][owner]
+    writes = [dict() for _ in range(world)]                # per source: round -> "queued" | "done"
+    signalled = [set() for _ in range(world)]
+    owner_released = [0] * world                           # rounds the owner's host has released (in order)
+    collected = [0] * world
+    holds = [dict() for _ in range(world)]                 # per owner: (buffer, source) -> round
+    idle = 0
+    for _ in range(300000):
+        i = int(rng.integers(world))
+        act = int(rng.integers(4))
+        ring = rings[i]
+        progressed = False
+        if act == 0 and ring.posted < rounds:              # host: submit / post the next round
+            if ring.posted - depth < 0 or (ring.posted - depth) in ring.released:
+                r, k, _after = ring.next_post()
+                writes[i][r] = "queued"
+                progressed = True
+        elif act == 1:                                     # device: the writes of a round whose buffers are free
+            ready = [r for r, st in writes[i].items() if st == "queued" and
+                     (r < nbuf or all(released[i][q] >= r - nbuf + 1 for q in range(world)))]
+            if ready:
+                r = int(rng.choice(ready))                 # chains sit on different streams: any order
+                for q in range(world):
+                    assert r < nbuf or owner_released[q] >= r - nbuf + 1, (i, q, r)
+                    holds[q][(r % nbuf, i)] = r
+                writes[i][r] = "done"
+                progressed = True
+        elif act == 2:                                     # device: the round's flag kernel (signal after the writes)
+            todo = sorted(r for r, st in writes[i].items() if st == "done" and r not in signalled[i])
+            if todo:
+                r = todo[0]                                # one comm stream per rank: in order
+                if all(rr in signalled[i] for rr in range(r)):
+                    for q in range(world):
+                        arrived[q][r % nbuf][i] = r + 1
+                    signalled[i].add(r)
+                    progressed = True
+        else:                                              # host + device: consume and release the oldest round
+            r = collected[i]
+            if r < rounds and all(arrived[i][r % nbuf][s] >= r + 1 for s in range(world)):
+                for s in range(world):
+                    assert holds[i][(r % nbuf, s)] == r, (i, s, r, holds[i][(r % nbuf, s)])
+                owner_released[i] = r + 1
+                for s in range(world):
+                    released[s][i] = r + 1
+                ring.release(r)
+                collected[i] += 1
+                progressed = True
+        idle = 0 if progressed else idle + 1
+        if all(c == rounds for c in collected):
+            break
+        assert idle < 20000, "the protocol stalled"
+    assert all(c == rounds for c in collected)
