@@ -556,6 +556,28 @@ def test_bipatites_that_outlive_their_sample_keep_the_loop_running(tmp_path):
     csl.close()
 
 
+def test_bench_byte_model_names_every_launch_of_the_chain():
+    """bench.py's per-kernel roofline divides each launch's algorithmic bytes by its time:
+    the byte model must know every launch gs_slicer_profile reports (a renamed launch once
+    left the dominant kernel with 0 bytes)."""
+    import sys
+    E = _engine()
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from cslicer.synth import synth_graph
+    ip, ix = synth_graph("small", seed=5)
+    g = E.Graph(ip, ix)
+    sl = E.Slicer(g, [15, 10, 5], 4, max_batch=256, num_slots=1, num_streams=1, seed=1, use_graph=False)
+    seeds = np.random.default_rng(2).permutation(ip.size - 1)[:256]
+    names = [k for k, _ in bench.kernel_profile(sl, [(0, seeds)], reps=1)]
+    assert len(names) == sl.launches_per_sample == 13
+    v = sl.slice(seeds, 0)
+    model = bench.kernel_bytes(v, 4)
+    assert sorted(model) == sorted(names), (sorted(model), sorted(names))
+    assert all(b > 0 for b in model.values())
+    v.release(); sl.close(); g.close()
+
+
 def test_nvtx_ranges_can_be_switched_on():
     """GSPLIT_NVTX=1 (tracing): the C ABI wraps submit / wait in NVTX
     ranges; results and exit status are unchanged (run in a child: the switch is read once)."""
