@@ -124,3 +124,38 @@ def test_module_surface_of_the_reference():
     assert b.gpu_id == 2 and b.in_nodes == [] and b.from_ids == [[], [], [], []]
     b.in_nodes = [5]  # def_readwrite
     assert b.in_nodes == [5]
+
+
+def test_round2_entry_points_validate_their_arguments_without_a_device():
+    """The entry points added in round 2 reject bad arguments before they touch a GPU, and none
+    of them computes on the CPU when there is no device."""
+    import torch
+    L = N.lib()
+    h = C.c_void_p()
+    own = np.zeros(10, np.int32)
+    # edge partitioner (SURVEY 8(f) N1)
+    assert L.gs_epart_create(0, 10, 9, own.ctypes.data, None, 100, C.byref(h)) == N.ERR_INVALID      # parts > 8
+    assert L.gs_epart_create(0, 0, 4, own.ctypes.data, None, 100, C.byref(h)) == N.ERR_INVALID       # no nodes
+    bad = own.copy(); bad[3] = 4
+    assert L.gs_epart_create(0, 10, 4, bad.ctypes.data, None, 100, C.byref(h)) == N.ERR_INVALID      # owner outside [0, P)
+    assert b"owner[3]" in L.gs_last_error()
+    assert L.gs_epart_run(None, None, None, 0, 0) == N.ERR_INVALID
+    # flag barrier
+    assert L.gs_flags_post(0, None, 9, 1, None, 0, 0, 0, None, None) == N.ERR_INVALID                # > GS_MAX_PARTS words
+    assert L.gs_flags_post(0, None, 0, 0, None, 2, 1, 0, None, None) == N.ERR_INVALID                # wait without words / status
+    # direct / staged hand-over
+    slot = C.c_int32(-1)
+    assert L.gs_slicer_submit_direct(None, None, 0, 0, None, 0, None, C.byref(slot)) == N.ERR_INVALID
+    assert L.gs_slicer_push_parts(None, 0, None, None, None) == N.ERR_INVALID
+    if not torch.cuda.is_available():
+        assert L.gs_epart_create(0, 10, 4, own.ctypes.data, None, 100, C.byref(h)) == N.ERR_CUDA
+        assert b"no CPU fallback" in L.gs_last_error()
+        cnt = C.c_int64(-1)
+        one = np.zeros(4, np.int32)
+        assert L.gs_unique_first_noalloc(0, one.ctypes.data, 4, 16, one.ctypes.data, C.byref(cnt)) == N.ERR_CUDA
+
+
+def test_edge_partitioner_mirror_checks_shapes_before_the_library():
+    from cslicer.epart import EdgePartitioner
+    with pytest.raises(ValueError):
+        EdgePartitioner(np.zeros(10, np.int32), np.ones((10, 3), bool), num_parts=4)
